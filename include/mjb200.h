@@ -1,0 +1,100 @@
+/* mjb200.h -- C ABI of libmjb200.so, the B200 (sm_100a) implementation of MuJoCo Warp's batched
+ * physics step.
+ *
+ * The reference exposes this path only as Python functions over Warp arrays
+ * (reference mujoco_warp/__init__.py:25-112); there is no FFI in the reference to bind to, so
+ * each entry point below names the Python function it replaces.  All functions are
+ * asynchronous on the given CUDA stream, allocate nothing, never synchronise the device and are
+ * CUDA-graph capturable.  Pointers are *borrowed* device pointers owned by the caller
+ * (PyTorch in the bundled host layer).  No torch / C++ types cross this boundary.
+ *
+ * Return value: 0 on success, negative on error (see mjb_last_error()).
+ */
+#ifndef MJB200_H_
+#define MJB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "mjb_fields.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct MjbModel MjbModel; /* immutable device model (reference types.Model, types.py:834) */
+typedef struct MjbData MjbData;   /* bound nworld-batched data (reference types.Data, types.py:1703) */
+
+/* Options are passed by value on every call because reference users mutate m.opt.* freely
+ * between calls (reference io.py:2498 override_model, broadphase_test.py:123). */
+typedef struct MjbOption {
+#define X(name) int name;
+  MJB_OPT_INT_FIELDS(X)
+#undef X
+#define X(name) float name;
+  MJB_OPT_REAL_FIELDS(X)
+#undef X
+} MjbOption;
+
+/* Field-table introspection, used by the host layer to build pointer tables in the right order.
+ * kind: 0 model sizes, 1 model int, 2 model real, 3 opt int, 4 opt real, 5 data sizes,
+ *       6 data int, 7 data real.  Returns NULL past the end. */
+const char* mjb_field_name(int kind, int index);
+int mjb_field_count(int kind);
+
+/* Replaces put_model's device upload (reference io.py:641-645).  `blob` is a device buffer of
+ * `nbytes` bytes holding every model array back to back; int_offsets / real_offsets give the
+ * byte offset (16-byte aligned) of each array in MJB_MODEL_INT_FIELDS / MJB_MODEL_REAL_FIELDS
+ * order; sizes follow MJB_MODEL_SIZES order.  The blob must outlive the model. */
+int mjb_model_create(const int* sizes, int nsizes, const void* blob, size_t nbytes,
+                     const int* int_offsets, int nint, const int* real_offsets, int nreal,
+                     MjbModel** out);
+void mjb_model_destroy(MjbModel* m);
+
+/* Replaces make_data/put_data's device allocation (reference io.py:859, :1016): binds borrowed
+ * device pointers.  int_ptrs / real_ptrs follow MJB_DATA_INT_FIELDS / MJB_DATA_REAL_FIELDS
+ * order; sizes follow MJB_DATA_SIZES order. */
+int mjb_data_bind(const MjbModel* m, const int* sizes, int nsizes, int* const* int_ptrs, int nint,
+                  float* const* real_ptrs, int nreal, MjbData** out);
+void mjb_data_destroy(MjbData* d);
+
+/* Runs the pipeline stages selected by `stages` (MJB_STAGE_* bits) in pipeline order in ONE
+ * kernel launch, one warp per world.  Every per-stage reference function f(m, d)
+ * (kinematics, com_pos, crb, factor_m, collision, make_constraint, transmission,
+ * fwd_velocity, fwd_actuation, fwd_acceleration, solve, euler, implicit; reference
+ * __init__.py:25-112) maps to one bit. */
+int mjb_run_stages(const MjbModel* m, MjbData* d, const MjbOption* opt, uint32_t stages,
+                   void* cuda_stream);
+
+/* mjw.step (reference forward.py:1004) / mjw.forward (:973) / step1 (:1022) / step2 (:1050). */
+int mjb_step(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_forward(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_step1(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_step2(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+
+/* smooth.solve_m (reference smooth.py:2848): x = M^-1 y using d.qLD; x, y are (nworld, nv). */
+int mjb_solve_m(const MjbModel* m, MjbData* d, float* x, const float* y, void* cuda_stream);
+/* support.mul_m (reference support.py:133): res = qM @ vec; (nworld, nv). */
+int mjb_mul_m(const MjbModel* m, MjbData* d, float* res, const float* vec, void* cuda_stream);
+
+/* benchmark.ctrl_noise (reference benchmark.py:42): Ornstein-Uhlenbeck control noise with
+ * Halton-sequence noise; ctrl_center may be NULL. */
+int mjb_ctrl_noise(const MjbModel* m, MjbData* d, const MjbOption* opt, const float* ctrl_center,
+                   int step, float ctrlnoisestd, float ctrlnoiserate, void* cuda_stream);
+
+/* Number of kernel launches issued by this library since load (for bench.py's gpu_launches). */
+long long mjb_launch_count(void);
+/* Duration bookkeeping for bench.py: records CUDA events around every stage launch when enabled
+ * and returns the accumulated milliseconds of the main kernel (synchronises the events). */
+void mjb_timing_enable(int on);
+double mjb_timing_ms(void);
+long long mjb_timing_launches(void);
+void mjb_timing_reset(void);
+
+const char* mjb_last_error(void);
+const char* mjb_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MJB200_H_ */

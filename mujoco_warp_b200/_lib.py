@@ -1,0 +1,167 @@
+"""ctypes binding of libmjb200.so (the C ABI declared in include/mjb200.h).
+
+The library is built in-tree by `build()` (nvcc, sm_100a).  There is no fallback: if the shared
+object is missing or fails to load, every device entry point raises.
+"""
+
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+import threading
+
+import torch
+
+from . import types
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_HERE)
+CSRC = os.path.join(_HERE, "csrc")
+LIB_PATH = os.path.join(CSRC, "libmjb200.so")
+INCLUDE = os.path.join(_ROOT, "include")
+
+NVCC_FLAGS = [
+  "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--use_fast_math=false",
+]  # fmt: skip
+
+_lock = threading.Lock()
+_lib = None
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+  """Compiles csrc/*.cu into csrc/libmjb200.so for sm_100a (works without a GPU)."""
+  srcs = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith(".cu")]
+  deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
+  deps += [os.path.join(INCLUDE, f) for f in os.listdir(INCLUDE)]
+  if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(p) for p in deps):
+    return LIB_PATH
+  cmd = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xptxas", "-v" if verbose else "-O3",
+         "-shared", "-Xcompiler", "-fPIC", "-I", INCLUDE, "-I", CSRC, "-o", LIB_PATH] + srcs  # fmt: skip
+  res = subprocess.run(cmd, capture_output=True, text=True)
+  if res.returncode != 0:
+    raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+  if verbose:
+    print(res.stderr)
+  return LIB_PATH
+
+
+class MjbOption(ctypes.Structure):
+  _fields_ = [(n, ctypes.c_int) for n in types.OPT_INT_FIELDS] + [(n, ctypes.c_float) for n in types.OPT_REAL_FIELDS]
+
+
+def load():
+  """Loads libmjb200.so (raises if it is missing -- there is no CPU / eager fallback)."""
+  global _lib
+  with _lock:
+    if _lib is not None:
+      return _lib
+    if not os.path.exists(LIB_PATH):
+      raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (needs nvcc). There is no CPU fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    vp, ip = ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)
+    lib.mjb_field_name.restype = ctypes.c_char_p
+    lib.mjb_field_name.argtypes = [ctypes.c_int, ctypes.c_int]
+    lib.mjb_field_count.restype = ctypes.c_int
+    lib.mjb_field_count.argtypes = [ctypes.c_int]
+    lib.mjb_model_create.restype = ctypes.c_int
+    lib.mjb_model_create.argtypes = [ip, ctypes.c_int, vp, ctypes.c_size_t, ip, ctypes.c_int, ip, ctypes.c_int, ctypes.POINTER(vp)]
+    lib.mjb_model_destroy.argtypes = [vp]
+    lib.mjb_data_bind.restype = ctypes.c_int
+    lib.mjb_data_bind.argtypes = [vp, ip, ctypes.c_int, ctypes.POINTER(vp), ctypes.c_int, ctypes.POINTER(vp), ctypes.c_int, ctypes.POINTER(vp)]
+    lib.mjb_data_destroy.argtypes = [vp]
+    for name in ("mjb_step", "mjb_forward", "mjb_step1", "mjb_step2"):
+      fn = getattr(lib, name)
+      fn.restype = ctypes.c_int
+      fn.argtypes = [vp, vp, ctypes.POINTER(MjbOption), vp]
+    lib.mjb_run_stages.restype = ctypes.c_int
+    lib.mjb_run_stages.argtypes = [vp, vp, ctypes.POINTER(MjbOption), ctypes.c_uint32, vp]
+    lib.mjb_solve_m.restype = ctypes.c_int
+    lib.mjb_solve_m.argtypes = [vp, vp, vp, vp, vp]
+    lib.mjb_mul_m.restype = ctypes.c_int
+    lib.mjb_mul_m.argtypes = [vp, vp, vp, vp, vp]
+    lib.mjb_ctrl_noise.restype = ctypes.c_int
+    lib.mjb_ctrl_noise.argtypes = [vp, vp, ctypes.POINTER(MjbOption), vp, ctypes.c_int, ctypes.c_float, ctypes.c_float, vp]
+    lib.mjb_launch_count.restype = ctypes.c_longlong
+    lib.mjb_timing_enable.argtypes = [ctypes.c_int]
+    lib.mjb_timing_ms.restype = ctypes.c_double
+    lib.mjb_timing_launches.restype = ctypes.c_longlong
+    lib.mjb_last_error.restype = ctypes.c_char_p
+    lib.mjb_version.restype = ctypes.c_char_p
+    _check_tables(lib)
+    _lib = lib
+    return lib
+
+
+def field_names(lib, kind: int):
+  return [lib.mjb_field_name(kind, i).decode() for i in range(lib.mjb_field_count(kind))]
+
+
+def _check_tables(lib):
+  """The Python shape tables must list exactly the fields of include/mjb_fields.h, in order."""
+  want = [
+    types.MODEL_SIZES, list(types.MODEL_INT_FIELDS), list(types.MODEL_REAL_FIELDS), types.OPT_INT_FIELDS,
+    types.OPT_REAL_FIELDS, types.DATA_SIZES, list(types.DATA_INT_FIELDS), list(types.DATA_REAL_FIELDS),
+  ]  # fmt: skip
+  for kind, names in enumerate(want):
+    got = field_names(lib, kind)
+    if got != list(names):
+      raise RuntimeError(f"field table {kind} mismatch between include/mjb_fields.h and types.py: {set(got) ^ set(names)}")
+
+
+def check(lib, rc: int):
+  if rc != 0:
+    raise RuntimeError(f"libmjb200 error {rc}: {lib.mjb_last_error().decode()}")
+
+
+def make_option(m) -> MjbOption:
+  """Snapshot of m.opt / m.stat for one call (options are passed by value)."""
+  o = m.opt
+  g = o.gravity.reshape(-1)
+  return MjbOption(
+    integrator=int(o.integrator), cone=int(o.cone), solver=int(o.solver), iterations=int(o.iterations),
+    ls_iterations=int(o.ls_iterations), disableflags=int(o.disableflags), enableflags=int(o.enableflags),
+    broadphase=int(o.broadphase), broadphase_filter=int(o.broadphase_filter),
+    run_collision_detection=int(bool(o.run_collision_detection)),
+    timestep=float(o.timestep.reshape(-1)[0]), tolerance=float(o.tolerance.reshape(-1)[0]),
+    ls_tolerance=float(o.ls_tolerance.reshape(-1)[0]), gravity_x=float(g[0]), gravity_y=float(g[1]), gravity_z=float(g[2]),
+    impratio_invsqrt=float(o.impratio_invsqrt.reshape(-1)[0]), meaninertia=float(m.stat.meaninertia.reshape(-1)[0]),
+  )  # fmt: skip
+
+
+def model_create(lib, m, int_names, real_names):
+  sizes = (ctypes.c_int * len(types.MODEL_SIZES))(*[int(m.sizes[n]) for n in types.MODEL_SIZES])
+  ioff = (ctypes.c_int * len(int_names))(*[m._offsets[n] for n in int_names])
+  roff = (ctypes.c_int * len(real_names))(*[m._offsets[n] for n in real_names])
+  out = ctypes.c_void_p()
+  check(lib, lib.mjb_model_create(sizes, len(types.MODEL_SIZES), ctypes.c_void_p(m._blob.data_ptr()), m._blob.numel(), ioff,
+                                  len(int_names), roff, len(real_names), ctypes.byref(out)))  # fmt: skip
+  return out
+
+
+def data_ptr_signature(d):
+  return tuple(d.field(n).data_ptr() for n in list(types.DATA_INT_FIELDS) + list(types.DATA_REAL_FIELDS))
+
+
+def data_bind(lib, m, d):
+  int_names, real_names = list(types.DATA_INT_FIELDS), list(types.DATA_REAL_FIELDS)
+  for n in int_names:
+    t = d.field(n)
+    assert t.dtype == torch.int32 and t.is_contiguous() and t.device == m.device, n
+  for n in real_names:
+    t = d.field(n)
+    assert t.dtype == torch.float32 and t.is_contiguous() and t.device == m.device, n
+  sizes = (ctypes.c_int * len(types.DATA_SIZES))(*[int(d._sizes[n]) for n in types.DATA_SIZES])
+  ip = (ctypes.c_void_p * len(int_names))(*[d.field(n).data_ptr() for n in int_names])
+  rp = (ctypes.c_void_p * len(real_names))(*[d.field(n).data_ptr() for n in real_names])
+  out = ctypes.c_void_p()
+  check(lib, lib.mjb_data_bind(m._handle, sizes, len(types.DATA_SIZES), ip, len(int_names), rp, len(real_names), ctypes.byref(out)))
+  return out
+
+
+def data_destroy(lib, handle):
+  lib.mjb_data_destroy(handle)
+
+
+def stream_ptr():
+  return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
