@@ -1,0 +1,346 @@
+// mjb_api.cu -- extern "C" entry points of libmjb200.so (see include/mjb200.h).
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "mjb200.h"
+#include "mjb_kernels.cuh"
+
+static thread_local std::string g_err;
+static long long g_launches = 0;
+static int g_timing = 0;
+static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_events;
+static std::mutex g_mu;
+
+static int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+#define CUDA_OK(expr)                                                                            \
+  do {                                                                                           \
+    cudaError_t e__ = (expr);                                                                    \
+    if (e__ != cudaSuccess) return fail(-10, std::string(#expr) + ": " + cudaGetErrorString(e__)); \
+  } while (0)
+
+struct MjbModel {
+  ModelSizes ms;
+  ModelOffsets mo;
+  const unsigned char* blob;
+  int blob_bytes;
+};
+
+struct MjbData {
+  const MjbModel* m;
+  DataSizes dsz;
+  DataPtrs d;
+  DataStrides st;
+  int scratch_floats;
+  int device;
+  int nsm;
+  int smem_optin;
+};
+
+// ---- field-table introspection --------------------------------------------------------------
+static const char* const k_names0[] = {
+#define X(n) #n,
+    MJB_MODEL_SIZES(X)
+#undef X
+        nullptr};
+static const char* const k_names1[] = {
+#define X(n) #n,
+    MJB_MODEL_INT_FIELDS(X)
+#undef X
+        nullptr};
+static const char* const k_names2[] = {
+#define X(n) #n,
+    MJB_MODEL_REAL_FIELDS(X)
+#undef X
+        nullptr};
+static const char* const k_names3[] = {
+#define X(n) #n,
+    MJB_OPT_INT_FIELDS(X)
+#undef X
+        nullptr};
+static const char* const k_names4[] = {
+#define X(n) #n,
+    MJB_OPT_REAL_FIELDS(X)
+#undef X
+        nullptr};
+static const char* const k_names5[] = {
+#define X(n) #n,
+    MJB_DATA_SIZES(X)
+#undef X
+        nullptr};
+static const char* const k_names6[] = {
+#define X(n, c) #n,
+    MJB_DATA_INT_FIELDS(X)
+#undef X
+        nullptr};
+static const char* const k_names7[] = {
+#define X(n, c) #n,
+    MJB_DATA_REAL_FIELDS(X)
+#undef X
+        nullptr};
+static const char* const* const k_tables[8] = {k_names0, k_names1, k_names2, k_names3, k_names4, k_names5, k_names6, k_names7};
+
+extern "C" int mjb_field_count(int kind) {
+  if (kind < 0 || kind > 7) return 0;
+  int n = 0;
+  while (k_tables[kind][n]) n++;
+  return n;
+}
+extern "C" const char* mjb_field_name(int kind, int index) {
+  if (index < 0 || index >= mjb_field_count(kind)) return nullptr;
+  return k_tables[kind][index];
+}
+
+// ---- model / data handles -------------------------------------------------------------------
+extern "C" int mjb_model_create(const int* sizes, int nsizes, const void* blob, size_t nbytes, const int* int_offsets, int nint,
+                                const int* real_offsets, int nreal, MjbModel** out) {
+  if (nsizes != mjb_field_count(0) || nint != mjb_field_count(1) || nreal != mjb_field_count(2))
+    return fail(-1, "mjb_model_create: field table size mismatch");
+  if (nbytes % 16 != 0 || (reinterpret_cast<uintptr_t>(blob) & 15)) return fail(-2, "mjb_model_create: blob must be 16-byte aligned/sized");
+  MjbModel* m = new MjbModel();
+  int k = 0;
+#define X(n) m->ms.n = sizes[k++];
+  MJB_MODEL_SIZES(X)
+#undef X
+  k = 0;
+#define X(n) m->mo.n = int_offsets[k++];
+  MJB_MODEL_INT_FIELDS(X)
+#undef X
+  k = 0;
+#define X(n) m->mo.n = real_offsets[k++];
+  MJB_MODEL_REAL_FIELDS(X)
+#undef X
+  if (m->ms.is_sparse) {
+    delete m;
+    return fail(-3, "sparse models are not implemented");
+  }
+  if (m->ms.nv > 64) {
+    delete m;
+    return fail(-3, "nv > 64 is not implemented");
+  }
+  m->blob = static_cast<const unsigned char*>(blob);
+  m->blob_bytes = (int)nbytes;
+  *out = m;
+  return 0;
+}
+extern "C" void mjb_model_destroy(MjbModel* m) { delete m; }
+
+extern "C" int mjb_data_bind(const MjbModel* m, const int* sizes, int nsizes, int* const* int_ptrs, int nint, float* const* real_ptrs,
+                             int nreal, MjbData** out) {
+  if (nsizes != mjb_field_count(5) || nint != mjb_field_count(6) || nreal != mjb_field_count(7))
+    return fail(-1, "mjb_data_bind: field table size mismatch");
+  MjbData* d = new MjbData();
+  d->m = m;
+  int k = 0;
+#define X(n) d->dsz.n = sizes[k++];
+  MJB_DATA_SIZES(X)
+#undef X
+  k = 0;
+#define X(n, c) d->d.n = int_ptrs[k++];
+  MJB_DATA_INT_FIELDS(X)
+#undef X
+  k = 0;
+#define X(n, c) d->d.n = real_ptrs[k++];
+  MJB_DATA_REAL_FIELDS(X)
+#undef X
+  {  // per-world strides from the size expressions of the field tables
+#define X(n) const int n = m->ms.n; (void)n;
+    MJB_MODEL_SIZES(X)
+#undef X
+#define X(n) const int n = d->dsz.n; (void)n;
+    MJB_DATA_SIZES(X)
+#undef X
+#define X(n, c) d->st.n = (c);
+    MJB_DATA_INT_FIELDS(X)
+    MJB_DATA_REAL_FIELDS(X)
+#undef X
+  }
+  d->scratch_floats = mjb_scratch_floats(m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad);
+  cudaError_t e = cudaGetDevice(&d->device);
+  if (e != cudaSuccess) {
+    delete d;
+    return fail(-10, std::string("cudaGetDevice: ") + cudaGetErrorString(e));
+  }
+  cudaDeviceGetAttribute(&d->nsm, cudaDevAttrMultiProcessorCount, d->device);
+  cudaDeviceGetAttribute(&d->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, d->device);
+  *out = d;
+  return 0;
+}
+extern "C" void mjb_data_destroy(MjbData* d) { delete d; }
+
+// ---- launches -------------------------------------------------------------------------------
+static void fill_params(KParams& K, const MjbModel* m, const MjbData* d, const MjbOption* opt, uint32_t stages) {
+  memset(&K, 0, sizeof(K));
+  K.ms = m->ms;
+  K.mo = m->mo;
+  K.dsz = d->dsz;
+  K.d = d->d;
+  K.st = d->st;
+  static_assert(sizeof(OptView) == sizeof(MjbOption), "option struct mismatch");
+  memcpy(&K.o, opt, sizeof(OptView));
+  K.blob = m->blob;
+  K.blob_bytes = m->blob_bytes;
+  K.scratch_floats = d->scratch_floats;
+  K.stages = stages;
+}
+
+static int warps_per_block() {
+  static int wpb = 0;
+  if (wpb == 0) {
+    const char* e = getenv("MJB_WARPS_PER_BLOCK");
+    wpb = e ? atoi(e) : 4;
+    if (wpb < 1) wpb = 1;
+    if (wpb > 8) wpb = 8;
+  }
+  return wpb;
+}
+
+template <typename F>
+static int timed_launch(cudaStream_t stream, F&& launch) {
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (g_timing) {
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    cudaEventRecord(e0, stream);
+  }
+  launch();
+  if (g_timing) {
+    cudaEventRecord(e1, stream);
+    std::lock_guard<std::mutex> lk(g_mu);
+    g_events.emplace_back(e0, e1);
+  }
+  g_launches++;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(-11, std::string("kernel launch: ") + cudaGetErrorString(e));
+  return 0;
+}
+
+extern "C" int mjb_run_stages(const MjbModel* m, MjbData* d, const MjbOption* opt, uint32_t stages, void* cuda_stream) {
+  if (!m || !d || !opt) return fail(-1, "null handle");
+  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+  if (opt->cone != 0) return fail(-4, "elliptic cones are not implemented");
+  if (opt->solver != SOLVER_NEWTON && opt->solver != SOLVER_CG) return fail(-4, "unsupported solver");
+  if (stages & MJB_STAGE_IMPLICIT) return fail(-4, "implicitfast integrator is not implemented");
+  KParams K;
+  fill_params(K, m, d, opt, stages);
+  if ((stages & MJB_STAGE_COLLISION) && opt->run_collision_detection) {  // collision_driver.py:779
+    CUDA_OK(cudaMemsetAsync(d->d.nacon, 0, sizeof(int), stream));
+    CUDA_OK(cudaMemsetAsync(d->d.ncollision, 0, sizeof(int), stream));
+  }
+  const int wpb = warps_per_block();
+  const size_t scr_bytes = (size_t)wpb * d->scratch_floats * sizeof(float);
+  const bool in_smem = (size_t)m->blob_bytes + 16 + scr_bytes <= (size_t)d->smem_optin && m->blob_bytes <= 96 * 1024;
+  const size_t smem = in_smem ? (size_t)m->blob_bytes + 16 + scr_bytes : scr_bytes;
+  if (smem > (size_t)d->smem_optin) return fail(-5, "model needs more shared memory than the device offers");
+  auto kern = in_smem ? mjb_pipeline_kernel<true> : mjb_pipeline_kernel<false>;
+  CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 1;
+  CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * wpb, smem));
+  if (occ < 1) occ = 1;
+  int grid = (d->dsz.nworld + wpb - 1) / wpb;
+  const int maxgrid = d->nsm * occ;
+  if (grid > maxgrid) grid = maxgrid;
+  return timed_launch(stream, [&] { kern<<<grid, 32 * wpb, smem, stream>>>(K); });
+}
+
+static uint32_t integrator_stage(const MjbOption* opt) {
+  if (opt->integrator == 0) return MJB_STAGE_EULER;
+  if (opt->integrator == 3) return MJB_STAGE_IMPLICIT;
+  return 0;
+}
+
+extern "C" int mjb_forward(const MjbModel* m, MjbData* d, const MjbOption* opt, void* s) { return mjb_run_stages(m, d, opt, MJB_STAGES_FORWARD, s); }
+extern "C" int mjb_step(const MjbModel* m, MjbData* d, const MjbOption* opt, void* s) {
+  if (!opt) return fail(-1, "null option");
+  const uint32_t integ = integrator_stage(opt);
+  if (!integ) return fail(-4, "integrator not implemented (RK4 is driven from the host layer)");
+  return mjb_run_stages(m, d, opt, MJB_STAGES_FORWARD | integ, s);
+}
+extern "C" int mjb_step1(const MjbModel* m, MjbData* d, const MjbOption* opt, void* s) {
+  return mjb_run_stages(m, d, opt, MJB_STAGES_FWD_POSITION | MJB_STAGE_FACTOR_M | MJB_STAGE_ZERO_SENSOR | MJB_STAGE_FWD_VELOCITY, s);
+}
+extern "C" int mjb_step2(const MjbModel* m, MjbData* d, const MjbOption* opt, void* s) {
+  if (!opt) return fail(-1, "null option");
+  uint32_t integ = integrator_stage(opt);
+  if (!integ) integ = MJB_STAGE_EULER;  // forward.py:1063: RK4 defaults to Euler in step2
+  return mjb_run_stages(m, d, opt, MJB_STAGE_FWD_ACTUATION | MJB_STAGE_FWD_ACCELERATION | MJB_STAGE_SOLVE | integ, s);
+}
+
+extern "C" int mjb_solve_m(const MjbModel* m, MjbData* d, float* x, const float* y, void* s) {
+  if (!m || !d) return fail(-1, "null handle");
+  cudaStream_t stream = static_cast<cudaStream_t>(s);
+  KParams K;
+  MjbOption o;
+  memset(&o, 0, sizeof(o));
+  fill_params(K, m, d, &o, 0);
+  K.x = x;
+  K.y = y;
+  const int wpb = warps_per_block();
+  const size_t smem = (size_t)wpb * d->scratch_floats * sizeof(float);
+  CUDA_OK(cudaFuncSetAttribute(mjb_solve_m_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int grid = (d->dsz.nworld + wpb - 1) / wpb;
+  if (grid > d->nsm * 8) grid = d->nsm * 8;
+  return timed_launch(stream, [&] { mjb_solve_m_kernel<<<grid, 32 * wpb, smem, stream>>>(K); });
+}
+
+extern "C" int mjb_mul_m(const MjbModel* m, MjbData* d, float* res, const float* vec, void* s) {
+  if (!m || !d) return fail(-1, "null handle");
+  cudaStream_t stream = static_cast<cudaStream_t>(s);
+  KParams K;
+  MjbOption o;
+  memset(&o, 0, sizeof(o));
+  fill_params(K, m, d, &o, 0);
+  K.x = res;
+  K.y = vec;
+  const int n = d->dsz.nworld * m->ms.nv;
+  if (n == 0) return 0;
+  return timed_launch(stream, [&] { mjb_mul_m_kernel<<<(n + 255) / 256, 256, 0, stream>>>(K); });
+}
+
+extern "C" int mjb_ctrl_noise(const MjbModel* m, MjbData* d, const MjbOption* opt, const float* ctrl_center, int step, float ctrlnoisestd,
+                              float ctrlnoiserate, void* s) {
+  if (!m || !d || !opt) return fail(-1, "null handle");
+  cudaStream_t stream = static_cast<cudaStream_t>(s);
+  KParams K;
+  fill_params(K, m, d, opt, 0);
+  const int n = d->dsz.nworld * m->ms.nu;
+  if (n == 0) return 0;
+  const int timing = g_timing;
+  g_timing = 0;  // not part of the step
+  int rc = timed_launch(stream, [&] { mjb_ctrl_noise_kernel<<<(n + 255) / 256, 256, 0, stream>>>(K, ctrl_center, step, ctrlnoisestd, ctrlnoiserate); });
+  g_timing = timing;
+  g_launches--;
+  return rc;
+}
+
+extern "C" long long mjb_launch_count(void) { return g_launches; }
+extern "C" void mjb_timing_enable(int on) { g_timing = on; }
+extern "C" void mjb_timing_reset(void) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  for (auto& p : g_events) {
+    cudaEventDestroy(p.first);
+    cudaEventDestroy(p.second);
+  }
+  g_events.clear();
+}
+extern "C" long long mjb_timing_launches(void) { return (long long)g_events.size(); }
+extern "C" double mjb_timing_ms(void) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  double total = 0;
+  for (auto& p : g_events) {
+    cudaEventSynchronize(p.second);
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, p.first, p.second) == cudaSuccess) total += ms;
+  }
+  return total;
+}
+extern "C" const char* mjb_last_error(void) { return g_err.c_str(); }
+extern "C" const char* mjb_version(void) { return "mjb200 0.1 (sm_100a)"; }

@@ -1,0 +1,347 @@
+// mjb_collision.cuh -- NXN broadphase + primitive narrowphase, one warp per world.
+//
+// Reference: collision_driver.py:755 collision, :647 _nxn_broadphase, :274 _broadphase_filter,
+// collision_primitive.py:1300 _primitive_narrowphase, collision_core.py:160 write_contact,
+// :236 contact_params, collision_primitive_core.py:107-443 pair functions.
+//
+// The reference appends geom pairs and contacts to global pools with one atomic per element, so
+// its ordering is nondeterministic.  Here each warp filters the static pair list of its world
+// 32 pairs at a time, compacts survivors with ballots into a small shared-memory queue, runs the
+// narrowphase with one lane per surviving pair, and reserves pool slots with ONE atomicAdd per
+// queue flush (usually one per world): contacts of a world are emitted in pair-list order and
+// the per-world list `wcon` records their pool indices for make_constraint.
+#pragma once
+
+#include "mjb_types.cuh"
+
+// collision_driver.py:91-111, 218-271
+__device__ __forceinline__ bool bp_filter(const KParams& K, const unsigned char* mb, int w, int g1, int g2) {
+  const float rb1 = MR(geom_rbound)[g1], rb2 = MR(geom_rbound)[g2];
+  const float margin = MR(geom_margin)[g1] + MR(geom_margin)[g2];
+  const V3 p1 = ld3(DW(geom_xpos) + 3 * g1), p2 = ld3(DW(geom_xpos) + 3 * g2);
+  const int filter = K.o.broadphase_filter;
+  if (rb1 == 0.f || rb2 == 0.f) {
+    if (filter & BF_PLANE) {
+      if (rb1 == 0.f) {
+        const float* r = DW(geom_xmat) + 9 * g1;
+        return dot(p2 - p1, V3{r[2], r[5], r[8]}) <= rb2 + margin;
+      } else {
+        const float* r = DW(geom_xmat) + 9 * g2;
+        return dot(p1 - p2, V3{r[2], r[5], r[8]}) <= rb1 + margin;
+      }
+    }
+    return true;
+  }
+  if (filter & BF_SPHERE) {
+    const float bound = rb1 + rb2 + margin;
+    const V3 dif = p2 - p1;
+    if (!(dot(dif, dif) <= bound * bound)) return false;
+  }
+  if (filter & (BF_AABB | BF_OBB)) {
+    const M3 r1 = ldm3(DW(geom_xmat) + 9 * g1), r2 = ldm3(DW(geom_xmat) + 9 * g2);
+    const float* a1 = MR(geom_aabb) + 6 * g1;
+    const float* a2 = MR(geom_aabb) + 6 * g2;
+    const V3 c1 = mat_vec(r1, ld3(a1)) + p1, c2 = mat_vec(r2, ld3(a2)) + p2;
+    const V3 s1 = ld3(a1 + 3), s2 = ld3(a2 + 3);
+    if (filter & BF_AABB) {  // collision_driver.py:116-213: world AABBs of the two boxes
+      float h1[3], h2[3];
+#pragma unroll
+      for (int i = 0; i < 3; i++) {
+        h1[i] = fabsf(r1.m[3 * i] * s1.x) + fabsf(r1.m[3 * i + 1] * s1.y) + fabsf(r1.m[3 * i + 2] * s1.z);
+        h2[i] = fabsf(r2.m[3 * i] * s2.x) + fabsf(r2.m[3 * i + 1] * s2.y) + fabsf(r2.m[3 * i + 2] * s2.z);
+      }
+      const float cc1[3] = {c1.x, c1.y, c1.z}, cc2[3] = {c2.x, c2.y, c2.z};
+#pragma unroll
+      for (int i = 0; i < 3; i++) {
+        if (cc1[i] + h1[i] + margin < cc2[i] - h2[i]) return false;
+        if (cc2[i] + h2[i] + margin < cc1[i] - h1[i]) return false;
+      }
+    }
+    if (filter & BF_OBB) {  // 6 face normals only
+#pragma unroll
+      for (int j = 0; j < 2; j++) {
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+          const V3 n = j == 0 ? mat_col(r1, k) : mat_col(r2, k);
+          const float rad1 = fabsf(s1.x * dot(mat_col(r1, 0), n)) + fabsf(s1.y * dot(mat_col(r1, 1), n)) + fabsf(s1.z * dot(mat_col(r1, 2), n));
+          const float rad2 = fabsf(s2.x * dot(mat_col(r2, 0), n)) + fabsf(s2.y * dot(mat_col(r2, 1), n)) + fabsf(s2.z * dot(mat_col(r2, 2), n));
+          if (rad1 + rad2 + margin < fabsf(dot(c2, n) - dot(c1, n))) return false;
+        }
+      }
+    }
+  }
+  return true;
+}
+
+struct PairGeom {
+  V3 p1, p2, n1, n2, s1, s2;  // positions, z axes, sizes
+  int t1, t2;
+};
+
+// collision_primitive_core.py:115-143
+__device__ __forceinline__ void c_sphere_sphere(V3 p1, float r1, V3 p2, float r2, float& dist, V3& pos, V3& n) {
+  const V3 dir = p2 - p1;
+  const float dd = norm(dir);
+  n = dd == 0.f ? V3{1.f, 0.f, 0.f} : dir * (1.0f / dd);
+  dist = dd - (r1 + r2);
+  pos = p1 + n * (r1 + 0.5f * dist);
+}
+
+// Number of candidate contacts of a pair type (collision_primitive.py wrappers).
+__device__ __forceinline__ int pair_ncand(int t1, int t2) {
+  if (t1 == GEOM_PLANE) return t2 == GEOM_SPHERE ? 1 : (t2 == GEOM_CAPSULE ? 2 : (t2 == GEOM_BOX ? 8 : 0));
+  if (t1 == GEOM_SPHERE) return (t2 == GEOM_SPHERE || t2 == GEOM_CAPSULE) ? 1 : 0;
+  if (t1 == GEOM_CAPSULE && t2 == GEOM_CAPSULE) return 2;
+  return 0;
+}
+
+// k-th candidate contact of the pair: distance, position, frame.  `r2` = rotation of geom 2.
+__device__ __forceinline__ void pair_contact(const PairGeom& g, const float* r2, float margin, int k, float& dist, V3& pos, M3& frame) {
+  dist = INFINITY;
+  pos = V3{0.f, 0.f, 0.f};
+#pragma unroll
+  for (int i = 0; i < 9; i++) frame.m[i] = 0.f;
+  if (g.t1 == GEOM_PLANE) {
+    const V3 n = g.n1;
+    if (g.t2 == GEOM_SPHERE) {  // core :107
+      dist = dot(g.p2 - g.p1, n) - g.s2.x;
+      pos = g.p2 - n * (g.s2.x + 0.5f * dist);
+      frame = make_frame(n);
+    } else if (g.t2 == GEOM_CAPSULE) {  // core :312-361
+      V3 b = g.n2 - n * dot(n, g.n2);
+      const float nb = norm(b);
+      if (nb != 0.f) b = b * (1.0f / nb);
+      if (nb < 0.5f) b = (-0.5f < n.y && n.y < 0.5f) ? V3{0.f, 1.f, 0.f} : V3{0.f, 0.f, 1.f};
+      const V3 c = cross(n, b);
+      frame.m[0] = n.x; frame.m[1] = n.y; frame.m[2] = n.z; frame.m[3] = b.x; frame.m[4] = b.y; frame.m[5] = b.z;
+      frame.m[6] = c.x; frame.m[7] = c.y; frame.m[8] = c.z;
+      const V3 e = g.p2 + g.n2 * (k == 0 ? g.s2.y : -g.s2.y);
+      dist = dot(e - g.p1, n) - g.s2.x;
+      pos = e - n * (g.s2.x + 0.5f * dist);
+    } else {  // plane-box, core :396-443
+      const V3 corner = V3{(k & 1) ? g.s2.x : -g.s2.x, (k & 2) ? g.s2.y : -g.s2.y, (k & 4) ? g.s2.z : -g.s2.z};
+      const V3 cw = V3{r2[0] * corner.x + r2[1] * corner.y + r2[2] * corner.z, r2[3] * corner.x + r2[4] * corner.y + r2[5] * corner.z,
+                       r2[6] * corner.x + r2[7] * corner.y + r2[8] * corner.z};
+      dist = dot(g.p2 - g.p1, n) + dot(n, cw);
+      pos = cw + g.p2 - n * (0.5f * dist);
+      frame = make_frame(n);
+    }
+    return;
+  }
+  V3 nrm = V3{1.f, 0.f, 0.f};
+  if (g.t1 == GEOM_SPHERE && g.t2 == GEOM_SPHERE) {
+    c_sphere_sphere(g.p1, g.s1.x, g.p2, g.s2.x, dist, pos, nrm);
+  } else if (g.t1 == GEOM_SPHERE) {  // sphere-capsule, core :147-178
+    const V3 a = g.p2 - g.n2 * g.s2.y, ab = g.n2 * (2.0f * g.s2.y);
+    const float t = clampf(dot(g.p1 - a, ab) / (dot(ab, ab) + 1e-6f), 0.f, 1.f);
+    c_sphere_sphere(g.p1, g.s1.x, a + ab * t, g.s2.x, dist, pos, nrm);
+  } else {  // capsule-capsule, core :182-308
+    const V3 ax1 = g.n1 * g.s1.y, ax2 = g.n2 * g.s2.y, dif = g.p1 - g.p2;
+    const float ma = dot(ax1, ax1), mb = -dot(ax1, ax2), mc = dot(ax2, ax2), u = -dot(ax1, dif), v = dot(ax2, dif);
+    const float det = ma * mc - mb * mb;
+    if (fabsf(det) >= MJ_MINVAL) {
+      if (k > 0) return;
+      float x1 = (mc * u - mb * v) / det, x2 = (ma * v - mb * u) / det;
+      if (x1 > 1.f) { x1 = 1.f; x2 = (v - mb) / mc; } else if (x1 < -1.f) { x1 = -1.f; x2 = (v + mb) / mc; }
+      if (x2 > 1.f) { x2 = 1.f; x1 = clampf((u - mb) / ma, -1.f, 1.f); }
+      else if (x2 < -1.f) { x2 = -1.f; x1 = clampf((u + mb) / ma, -1.f, 1.f); }
+      float dd;
+      V3 pp;
+      c_sphere_sphere(g.p1 + ax1 * x1, g.s1.x, g.p2 + ax2 * x2, g.s2.x, dd, pp, nrm);
+      if (dd <= margin) { dist = dd; pos = pp; }
+    } else {  // parallel axes: first two of the four end-point tests that pass the margin check
+      int cnt = 0;
+      for (int e = 0; e < 4; e++) {
+        float x1, x2;
+        if (e == 0) { x1 = 1.f; x2 = clampf((v - mb) / mc, -1.f, 1.f); }
+        else if (e == 1) { x1 = -1.f; x2 = clampf((v + mb) / mc, -1.f, 1.f); }
+        else if (e == 2) { x2 = 1.f; x1 = clampf((u - mb) / ma, -1.f, 1.f); }
+        else { x2 = -1.f; x1 = clampf((u + mb) / ma, -1.f, 1.f); }
+        float dd;
+        V3 pp, nn;
+        c_sphere_sphere(g.p1 + ax1 * x1, g.s1.x, g.p2 + ax2 * x2, g.s2.x, dd, pp, nn);
+        if (dd <= margin) {
+          if (cnt == k) { dist = dd; pos = pp; nrm = nn; }
+          cnt++;
+          if (cnt > k) break;
+        }
+      }
+    }
+    if (dist == INFINITY) return;
+  }
+  frame = make_frame(nrm);
+}
+
+struct ContactParams {
+  float margin, gap, friction[5], solref[2], solreffriction[2], solimp[5];
+  int condim;
+};
+
+// collision_core.py:236-341
+__device__ __forceinline__ void contact_params(const KParams& K, const unsigned char* mb, int g1, int g2, int pairid, ContactParams& c) {
+  if (pairid > -1) {
+    c.margin = MR(pair_margin)[pairid];
+    c.gap = MR(pair_gap)[pairid];
+    c.condim = MI(pair_dim)[pairid];
+#pragma unroll
+    for (int i = 0; i < 5; i++) { c.friction[i] = MR(pair_friction)[5 * pairid + i]; c.solimp[i] = MR(pair_solimp)[5 * pairid + i]; }
+#pragma unroll
+    for (int i = 0; i < 2; i++) { c.solref[i] = MR(pair_solref)[2 * pairid + i]; c.solreffriction[i] = MR(pair_solreffriction)[2 * pairid + i]; }
+  } else {
+    const float sm1 = MR(geom_solmix)[g1], sm2 = MR(geom_solmix)[g2];
+    const int p1 = MI(geom_priority)[g1], p2 = MI(geom_priority)[g2];
+    const V3 f1 = ld3(MR(geom_friction) + 3 * g1), f2 = ld3(MR(geom_friction) + 3 * g2);
+    float mix;
+    V3 f;
+    if (p1 > p2) { mix = 1.f; c.condim = MI(geom_condim)[g1]; f = f1; }
+    else if (p2 > p1) { mix = 0.f; c.condim = MI(geom_condim)[g2]; f = f2; }
+    else {
+      mix = safe_div(sm1, sm1 + sm2);
+      if (sm1 < MJ_MINVAL && sm2 < MJ_MINVAL) mix = 0.5f;
+      if (sm1 < MJ_MINVAL && sm2 >= MJ_MINVAL) mix = 0.f;
+      if (sm1 >= MJ_MINVAL && sm2 < MJ_MINVAL) mix = 1.f;
+      c.condim = max(MI(geom_condim)[g1], MI(geom_condim)[g2]);
+      f = V3{fmaxf(f1.x, f2.x), fmaxf(f1.y, f2.y), fmaxf(f1.z, f2.z)};
+    }
+    c.friction[0] = f.x; c.friction[1] = f.x; c.friction[2] = f.y; c.friction[3] = f.z; c.friction[4] = f.z;
+    const float* sr1 = MR(geom_solref) + 2 * g1;
+    const float* sr2 = MR(geom_solref) + 2 * g2;
+    if (sr1[0] > 0.f && sr2[0] > 0.f) {
+      c.solref[0] = mix * sr1[0] + (1.f - mix) * sr2[0];
+      c.solref[1] = mix * sr1[1] + (1.f - mix) * sr2[1];
+    } else {
+      c.solref[0] = fminf(sr1[0], sr2[0]);
+      c.solref[1] = fminf(sr1[1], sr2[1]);
+    }
+    c.solreffriction[0] = c.solreffriction[1] = 0.f;
+#pragma unroll
+    for (int i = 0; i < 5; i++) c.solimp[i] = mix * MR(geom_solimp)[5 * g1 + i] + (1.f - mix) * MR(geom_solimp)[5 * g2 + i];
+    c.margin = MR(geom_margin)[g1] + MR(geom_margin)[g2];
+    c.gap = MR(geom_gap)[g1] + MR(geom_gap)[g2];
+  }
+#pragma unroll
+  for (int i = 0; i < 5; i++) c.friction[i] = fmaxf(MJ_MINMU, c.friction[i]);
+}
+
+// Narrowphase for up to 32 queued pairs (one lane each); appends contacts to the pool.
+__device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsigned char* mb, int w, int lane, const int* queue, int count,
+                                                  int& nw) {
+  const bool has = lane < count;
+  int g1 = 0, g2 = 0, pid0 = -2, pid1 = -1, ncand = 0, nact = 0;
+  PairGeom g;
+  ContactParams cp;
+  const float* r2 = nullptr;
+  if (has) {
+    const int p = queue[lane];
+    const int ga = MI(nxn_pair)[2 * p], gb = MI(nxn_pair)[2 * p + 1];
+    pid0 = MI(nxn_pairid)[2 * p];
+    pid1 = MI(nxn_pairid)[2 * p + 1];
+    const bool swap = MI(geom_type)[ga] > MI(geom_type)[gb];  // collision_driver.py:351
+    g1 = swap ? gb : ga;
+    g2 = swap ? ga : gb;
+    g.t1 = MI(geom_type)[g1];
+    g.t2 = MI(geom_type)[g2];
+    g.p1 = ld3(DW(geom_xpos) + 3 * g1);
+    g.p2 = ld3(DW(geom_xpos) + 3 * g2);
+    const float* r1 = DW(geom_xmat) + 9 * g1;
+    r2 = DW(geom_xmat) + 9 * g2;
+    g.n1 = V3{r1[2], r1[5], r1[8]};
+    g.n2 = V3{r2[2], r2[5], r2[8]};
+    g.s1 = ld3(MR(geom_size) + 3 * g1);
+    g.s2 = ld3(MR(geom_size) + 3 * g2);
+    contact_params(K, mb, g1, g2, pid0, cp);
+    ncand = pair_ncand(g.t1, g.t2);
+    for (int k = 0; k < ncand; k++) {  // pass 1: count (write_contact filter, collision_core.py:199-203)
+      float dist;
+      V3 pos;
+      M3 frame;
+      pair_contact(g, r2, cp.margin, k, dist, pos, frame);
+      const bool active = dist < cp.margin;
+      if (!((pid0 == -2 || !active) && pid1 == -1)) nact++;
+    }
+  }
+  const int off = warp_excl_scan(nact, lane);
+  const int total = __shfl_sync(FULL, off + nact, 31);
+  if (total == 0) return;
+  int base = 0;
+  if (lane == 0) base = atomicAdd(K.d.nacon, total);
+  base = __shfl_sync(FULL, base, 0);
+  if (has && nact > 0) {
+    const int nmp = K.ms.nmaxpyramid;
+    int slot = off;
+    for (int k = 0; k < ncand; k++) {  // pass 2: write
+      float dist;
+      V3 pos;
+      M3 frame;
+      pair_contact(g, r2, cp.margin, k, dist, pos, frame);
+      const bool active = dist < cp.margin;
+      if ((pid0 == -2 || !active) && pid1 == -1) continue;
+      const int cid = base + slot;
+      const int widx = nw + slot;
+      slot++;
+      if (cid >= K.dsz.naconmax) {
+        atomicOr(DW(status), MJB_STATUS_NCON_OVERFLOW);
+        continue;
+      }
+      int type = 0;
+      if (pid0 >= -1 && active) type |= 1;
+      if (pid1 >= 0) type |= 2;
+      K.d.contact_dist[cid] = dist;
+      st3(K.d.contact_pos + 3 * cid, pos);
+      stm3(K.d.contact_frame + 9 * cid, frame);
+      K.d.contact_includemargin[cid] = cp.margin - cp.gap;
+#pragma unroll
+      for (int i = 0; i < 5; i++) { K.d.contact_friction[5 * cid + i] = cp.friction[i]; K.d.contact_solimp[5 * cid + i] = cp.solimp[i]; }
+      K.d.contact_solref[2 * cid] = cp.solref[0];
+      K.d.contact_solref[2 * cid + 1] = cp.solref[1];
+      K.d.contact_solreffriction[2 * cid] = cp.solreffriction[0];
+      K.d.contact_solreffriction[2 * cid + 1] = cp.solreffriction[1];
+      K.d.contact_dim[cid] = cp.condim;
+      K.d.contact_geom[2 * cid] = g1;
+      K.d.contact_geom[2 * cid + 1] = g2;
+      K.d.contact_worldid[cid] = w;
+      K.d.contact_type[cid] = type;
+      K.d.contact_geomcollisionid[cid] = k;
+      for (int i = 0; i < nmp; i++) K.d.contact_efc_address[cid * nmp + i] = -1;
+      if (widx < K.dsz.nwconmax) DW(wcon)[widx] = cid;
+      else atomicOr(DW(status), MJB_STATUS_WCON_OVERFLOW);
+    }
+  }
+  nw += total;
+}
+
+// collision_driver.collision (collision_driver.py:755).  queue: 64 ints of shared scratch.
+__device__ __forceinline__ void s_collision(const KParams& K, const unsigned char* mb, int w, int lane, int* queue) {
+  int nw = 0, ncol = 0, qn = 0;
+  const bool enabled = K.dsz.naconmax > 0 && !(K.o.disableflags & (DSBL_CONSTRAINT | DSBL_CONTACT));
+  if (enabled) {
+    const int nxn = K.ms.nxn;
+    for (int p0 = 0; p0 < nxn; p0 += 32) {
+      const int p = p0 + lane;
+      bool pass = false;
+      if (p < nxn) pass = bp_filter(K, mb, w, MI(nxn_pair)[2 * p], MI(nxn_pair)[2 * p + 1]) || MI(nxn_pairid)[2 * p + 1] >= 0;
+      const unsigned mask = __ballot_sync(FULL, pass);
+      if (pass) queue[qn + __popc(mask & ((1u << lane) - 1u))] = p;
+      qn += __popc(mask);
+      ncol += __popc(mask);
+      __syncwarp();
+      if (qn >= 32) {
+        narrowphase_flush(K, mb, w, lane, queue, 32, nw);
+        __syncwarp();
+        const int rem = qn - 32;
+        int v = 0;
+        if (lane < rem) v = queue[32 + lane];
+        __syncwarp();
+        if (lane < rem) queue[lane] = v;
+        qn = rem;
+        __syncwarp();
+      }
+    }
+    if (qn > 0) narrowphase_flush(K, mb, w, lane, queue, qn, nw);
+  }
+  if (lane == 0) {
+    DW(wcon_n)[0] = min(nw, K.dsz.nwconmax);
+    if (ncol) atomicAdd(K.d.ncollision, ncol);
+  }
+  __syncwarp();
+}

@@ -1,0 +1,262 @@
+// mjb_constraint.cuh -- constraint.make_constraint (reference constraint.py:2210), one warp per world.
+//
+// Row classes are emitted in the reference's launch order (equality, friction, limit, contact;
+// constraint.py:2220-2779) because the solver classifies rows by index (solver.py:584-598).
+// Within a class the reference's order is an atomic race; here rows are in MuJoCo-C order
+// (object id, then contact index, then pyramid edge), assigned with ballots / prefix sums.
+// Dense Jacobian rows (nv_pad floats) are written cooperatively: lane = dof column.
+#pragma once
+
+#include "mjb_types.cuh"
+
+struct EfcRow {
+  float D, vel, aref, pos, margin, frictionloss;
+};
+
+// constraint.py:53-121
+__device__ __forceinline__ EfcRow efc_row(const KParams& K, float pos_aref, float pos_imp, float invweight, const float* solref,
+                                          const float* solimp, float margin, float vel, float frictionloss) {
+  float timeconst = solref[0];
+  const float dampratio = solref[1];
+  float dmin = solimp[0], dmax = solimp[1], width = solimp[2], mid = solimp[3], power = solimp[4];
+  if (!(K.o.disableflags & DSBL_REFSAFE)) timeconst = fmaxf(timeconst, 2.0f * K.o.timestep);
+  dmin = clampf(dmin, MJ_MINIMP, MJ_MAXIMP);
+  dmax = clampf(dmax, MJ_MINIMP, MJ_MAXIMP);
+  width = fmaxf(MJ_MINVAL, width);
+  mid = clampf(mid, MJ_MINIMP, MJ_MAXIMP);
+  power = fmaxf(1.0f, power);
+  const float dmax_sq = dmax * dmax;
+  float k = 1.0f / (dmax_sq * timeconst * timeconst * dampratio * dampratio);
+  float b = 2.0f / (dmax * timeconst);
+  if (solref[0] <= 0.f) k = -solref[0] / dmax_sq;
+  if (solref[1] <= 0.f) b = -solref[1] / dmax;
+  const float imp_x = fabsf(pos_imp) / width;
+  const float imp_a = (1.0f / powf(mid, power - 1.0f)) * powf(imp_x, power);
+  const float imp_b = 1.0f - (1.0f / powf(1.0f - mid, power - 1.0f)) * powf(1.0f - imp_x, power);
+  const float imp_y = imp_x < mid ? imp_a : imp_b;
+  float imp = clampf(dmin + imp_y * (dmax - dmin), dmin, dmax);
+  if (imp_x > 1.0f) imp = dmax;
+  EfcRow r;
+  r.D = 1.0f / fmaxf(invweight * (1.0f - imp) / imp, MJ_MINVAL);
+  r.vel = vel;
+  r.aref = -k * imp * pos_aref - b * vel;
+  r.pos = pos_aref + margin;
+  r.margin = margin;
+  r.frictionloss = frictionloss;
+  return r;
+}
+
+__device__ __forceinline__ void store_row(const KParams& K, int w, int r, const EfcRow& e, int type, int id) {
+  DW(efc_D)[r] = e.D;
+  DW(efc_vel)[r] = e.vel;
+  DW(efc_aref)[r] = e.aref;
+  DW(efc_pos)[r] = e.pos;
+  DW(efc_margin)[r] = e.margin;
+  DW(efc_frictionloss)[r] = e.frictionloss;
+  DW(efc_type)[r] = type;
+  DW(efc_id)[r] = id;
+}
+
+// Rows with at most two non-zeros (equality joint, dof friction, joint limit): every lane of the
+// warp proposes a row (`active`), rows are numbered by ballot prefix, then each row's Jacobian is
+// filled cooperatively.
+__device__ __forceinline__ int emit_simple_rows(const KParams& K, int w, int lane, bool active, int nefc, const EfcRow& e, int type, int id,
+                                                int c0, float v0, int c1, float v1) {
+  const unsigned mask = __ballot_sync(FULL, active);
+  const int njmax = K.dsz.njmax, np = K.ms.nv_pad;
+  const int r = nefc + __popc(mask & ((1u << lane) - 1u));
+  if (active && r < njmax) store_row(K, w, r, e, type, id);
+  unsigned mm = mask;
+  while (mm) {
+    const int src = __ffs(mm) - 1;
+    mm &= mm - 1;
+    const int rr = __shfl_sync(FULL, r, src);
+    const int cc0 = __shfl_sync(FULL, c0, src), cc1 = __shfl_sync(FULL, c1, src);
+    const float vv0 = __shfl_sync(FULL, v0, src), vv1 = __shfl_sync(FULL, v1, src);
+    if (rr < njmax) {
+      float* J = DW(efc_J) + (size_t)rr * np;
+      for (int c = lane; c < np; c += 32) J[c] = (c == cc0) ? vv0 : ((c == cc1) ? vv1 : 0.f);
+    }
+  }
+  return nefc + __popc(mask);
+}
+
+__device__ __forceinline__ void s_make_constraint(const KParams& K, const unsigned char* mb, int w, int lane) {
+  const int nv = K.ms.nv, np = K.ms.nv_pad, njmax = K.dsz.njmax;
+  int nefc = 0, ne = 0, nf = 0, nl = 0;
+  const float* qpos = DW(qpos);
+  const float* qvel = DW(qvel);
+  const int dsbl = K.o.disableflags;
+  if (!(dsbl & DSBL_CONSTRAINT)) {
+    if (!(dsbl & DSBL_EQUALITY)) {  // constraint.py:368-497
+      for (int k0 = 0; k0 < K.ms.neqjnt; k0 += 32) {
+        const int k = k0 + lane;
+        bool active = false;
+        EfcRow e = {};
+        int eq = 0, c0 = -1, c1 = -1;
+        float v0 = 0.f, v1 = 0.f;
+        if (k < K.ms.neqjnt) {
+          eq = MI(eq_jnt_adr)[k];
+          active = DW(eq_active)[eq] != 0;
+          if (active) {
+            const int j1 = MI(eq_obj1id)[eq], j2 = MI(eq_obj2id)[eq];
+            const float* data = MR(eq_data) + 11 * eq;
+            const int da1 = MI(jnt_dofadr)[j1], qa1 = MI(jnt_qposadr)[j1];
+            float pos, Jqvel, invweight;
+            c0 = da1;
+            v0 = 1.0f;
+            if (j2 > -1) {
+              const int qa2 = MI(jnt_qposadr)[j2], da2 = MI(jnt_dofadr)[j2];
+              const float dif = qpos[qa2] - MR(qpos0)[qa2];
+              const float rhs = data[0] + dif * (data[1] + dif * (data[2] + dif * (data[3] + dif * data[4])));
+              const float deriv2 = data[1] + dif * (2.0f * data[2] + dif * (3.0f * data[3] + dif * 4.0f * data[4]));
+              pos = qpos[qa1] - MR(qpos0)[qa1] - rhs;
+              Jqvel = qvel[da1] - qvel[da2] * deriv2;
+              invweight = MR(dof_invweight0)[da1] + MR(dof_invweight0)[da2];
+              c1 = da2;
+              v1 = -deriv2;
+            } else {
+              pos = qpos[qa1] - MR(qpos0)[qa1] - data[0];
+              Jqvel = qvel[da1];
+              invweight = MR(dof_invweight0)[da1];
+            }
+            e = efc_row(K, pos, pos, invweight, MR(eq_solref) + 2 * eq, MR(eq_solimp) + 5 * eq, 0.f, Jqvel, 0.f);
+          }
+        }
+        const int n2 = emit_simple_rows(K, w, lane, active, nefc, e, CT_EQUALITY, eq, c0, v0, c1, v1);
+        ne += n2 - nefc;
+        nefc = n2;
+      }
+    }
+    if (!(dsbl & DSBL_FRICTIONLOSS)) {  // constraint.py:1114
+      for (int k0 = 0; k0 < K.ms.nfrictiondof; k0 += 32) {
+        const int k = k0 + lane;
+        const bool active = k < K.ms.nfrictiondof;
+        EfcRow e = {};
+        int dof = 0;
+        if (active) {
+          dof = MI(dof_friction_adr)[k];
+          e = efc_row(K, 0.f, 0.f, MR(dof_invweight0)[dof], MR(dof_solref) + 2 * dof, MR(dof_solimp) + 5 * dof, 0.f, qvel[dof],
+                      MR(dof_frictionloss)[dof]);
+        }
+        const int n2 = emit_simple_rows(K, w, lane, active, nefc, e, CT_FRICTION_DOF, dof, dof, 1.0f, -1, 0.f);
+        nf += n2 - nefc;
+        nefc = n2;
+      }
+    }
+    if (!(dsbl & DSBL_LIMIT)) {  // constraint.py:1317-1418
+      for (int k0 = 0; k0 < K.ms.nlimit; k0 += 32) {
+        const int k = k0 + lane;
+        bool active = false;
+        EfcRow e = {};
+        int j = 0, da = -1;
+        float Jv = 0.f;
+        if (k < K.ms.nlimit) {
+          j = MI(jnt_limited_adr)[k];
+          const float q = qpos[MI(jnt_qposadr)[j]], mg = MR(jnt_margin)[j];
+          const float dist_min = q - MR(jnt_range)[2 * j], dist_max = MR(jnt_range)[2 * j + 1] - q;
+          const float pos = fminf(dist_min, dist_max) - mg;
+          active = pos < 0.f;
+          if (active) {
+            da = MI(jnt_dofadr)[j];
+            Jv = dist_min < dist_max ? 1.0f : -1.0f;
+            e = efc_row(K, pos, pos, MR(dof_invweight0)[da], MR(jnt_solref) + 2 * j, MR(jnt_solimp) + 5 * j, mg, Jv * qvel[da], 0.f);
+          }
+        }
+        const int n2 = emit_simple_rows(K, w, lane, active, nefc, e, CT_LIMIT_JOINT, j, da, Jv, -1, 0.f);
+        nl += n2 - nefc;
+        nefc = n2;
+      }
+    }
+    if (!(dsbl & DSBL_CONTACT)) {  // constraint.py:1669-1936, pyramidal cones
+      const int ncon = DW(wcon_n)[0], nmp = K.ms.nmaxpyramid;
+      const float* scom = DW(subtree_com);
+      const float* cdof = DW(cdof);
+      const float imp2 = K.o.impratio_invsqrt * K.o.impratio_invsqrt;
+      for (int ci = 0; ci < ncon; ci++) {
+        const int cid = DW(wcon)[ci];
+        if (!(K.d.contact_type[cid] & 1)) continue;
+        const int condim = K.d.contact_dim[cid];
+        const float includemargin = K.d.contact_includemargin[cid];
+        const float pos = K.d.contact_dist[cid] - includemargin;
+        if (!(pos < 0.f)) continue;
+        const int nrow = condim == 1 ? 1 : 2 * (condim - 1);
+        const int b1 = MI(geom_bodyid)[K.d.contact_geom[2 * cid]], b2 = MI(geom_bodyid)[K.d.contact_geom[2 * cid + 1]];
+        const int wb1 = MI(body_weldid)[b1], wb2 = MI(body_weldid)[b2];
+        const V3 cpos = ld3(K.d.contact_pos + 3 * cid);
+        const M3 frame = ldm3(K.d.contact_frame + 9 * cid);
+        const float* fri = K.d.contact_friction + 5 * cid;
+        const V3 off1 = cpos - ld3(scom + 3 * MI(body_rootid)[wb1]), off2 = cpos - ld3(scom + 3 * MI(body_rootid)[wb2]);
+        const float invw0 = MR(body_invweight0)[2 * b1] + MR(body_invweight0)[2 * b2];
+        // rows of this contact: address = -1 if beyond njmax (constraint.py:1749)
+        if (lane < nrow) K.d.contact_efc_address[cid * nmp + lane] = (nefc + lane < njmax) ? nefc + lane : -1;
+        // per-dof Jacobian differences projected on the frame axes (support.jac_dof, support.py:397)
+        // proj[0] = normal, proj[1..2] = tangents (translation), proj[3..5] = frame rows . rotation
+        for (int d0 = 0; d0 < nv; d0 += 32) {
+          const int dof = d0 + lane;
+          float proj[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+          if (dof < nv) {
+            const int db = MI(dof_bodyid)[dof];
+            // dof's body is an ancestor-or-self of body  <=>  db <= body < subtreeend[db]
+            const int dend = MI(body_subtreeend)[db];
+            const bool in1 = wb1 != 0 && db <= wb1 && wb1 < dend, in2 = wb2 != 0 && db <= wb2 && wb2 < dend;
+            if (in1 != in2) {  // common ancestors contribute exactly zero
+              const S6 cd = ld6(cdof + 6 * dof);
+              const V3 ang = top(cd), lin = bot(cd);
+              V3 dp = V3{0.f, 0.f, 0.f}, dr = V3{0.f, 0.f, 0.f};
+              if (in2) { dp = dp + lin + cross(ang, off2); dr = dr + ang; }
+              if (in1) { dp = dp - (lin + cross(ang, off1)); dr = dr - ang; }
+#pragma unroll
+              for (int a = 0; a < 3; a++) {
+                proj[a] = frame.m[3 * a] * dp.x + frame.m[3 * a + 1] * dp.y + frame.m[3 * a + 2] * dp.z;
+                proj[3 + a] = frame.m[3 * a] * dr.x + frame.m[3 * a + 1] * dr.y + frame.m[3 * a + 2] * dr.z;
+              }
+            }
+          }
+          for (int dimid = 0; dimid < nrow; dimid++) {
+            const int r = nefc + dimid;
+            float Jv = proj[0];
+            if (condim > 1) {
+              const int dimid2 = dimid / 2 + 1;
+              float Ji = proj[1];
+#pragma unroll
+              for (int a = 2; a < 6; a++) Ji = (dimid2 == a) ? proj[a] : Ji;
+              const float frii = fri[dimid2 - 1];
+              Jv += (dimid & 1) ? -Ji * frii : Ji * frii;
+            }
+            if (r < njmax && dof < np) DW(efc_J)[(size_t)r * np + dof] = dof < nv ? Jv : 0.f;
+          }
+        }
+        __syncwarp();
+        // efc_vel = J . qvel per row, then the row scalars (lane = pyramid edge)
+        for (int dimid = 0; dimid < nrow; dimid++) {
+          const int r = nefc + dimid;
+          if (r >= njmax) continue;
+          float part = 0.f;
+          for (int dof = lane; dof < nv; dof += 32) part += DW(efc_J)[(size_t)r * np + dof] * qvel[dof];
+          const float Jqvel = warp_sum(part);
+          if (lane == dimid) {
+            float invweight = invw0;
+            if (condim > 1) {
+              const float fri0 = fri[0];
+              invweight = invweight + fri0 * fri0 * invweight;
+              invweight = invweight * 2.0f * fri0 * fri0 * imp2;
+            }
+            const EfcRow e = efc_row(K, pos, pos, invweight, K.d.contact_solref + 2 * cid, K.d.contact_solimp + 5 * cid, includemargin,
+                                     Jqvel, 0.f);
+            store_row(K, w, r, e, condim == 1 ? CT_CONTACT_FRICTIONLESS : CT_CONTACT_PYRAMIDAL, cid);
+          }
+        }
+        nefc += nrow;
+      }
+    }
+  }
+  if (lane == 0) {
+    DW(ne)[0] = ne;
+    DW(nf)[0] = nf;
+    DW(nl)[0] = nl;
+    DW(nefc)[0] = nefc;
+    if (nefc > njmax) DW(status)[0] |= MJB_STATUS_NEFC_OVERFLOW;
+  }
+  __syncwarp();
+}

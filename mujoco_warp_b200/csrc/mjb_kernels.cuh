@@ -1,0 +1,151 @@
+// mjb_kernels.cuh -- the persistent one-warp-per-world pipeline kernel and small utility kernels.
+#pragma once
+
+#include "mjb_collision.cuh"
+#include "mjb_constraint.cuh"
+#include "mjb_smooth.cuh"
+#include "mjb_solver.cuh"
+#include "mjb_types.cuh"
+
+__host__ __device__ inline int mjb_scratch_floats(int nv, int nv_pad, int njmax_pad) {
+  int a = solver_scratch_floats(nv, nv_pad, njmax_pad);
+  int b = nv * (nv | 1) + nv_pad + 8;  // factor / solve
+  int c = 64 + 8;                      // collision queue
+  int m = a > b ? a : b;
+  m = m > c ? m : c;
+  return (m + 3) & ~3;
+}
+
+// Stages the model blob into shared memory with one TMA bulk copy (cp.async.bulk, completion on
+// an mbarrier).  All threads of the CTA wait on the barrier's phase 0.
+__device__ __forceinline__ void stage_model_blob(unsigned char* dst, const unsigned char* src, int nbytes, uint64_t* bar) {
+  const uint32_t bar_s = (uint32_t)__cvta_generic_to_shared(bar);
+  const uint32_t dst_s = (uint32_t)__cvta_generic_to_shared(dst);
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"((uint32_t)nbytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_s), "l"(src),
+                 "r"((uint32_t)nbytes), "r"(bar_s)
+                 : "memory");
+  }
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar_s), "r"(0u)
+        : "memory");
+  }
+}
+
+template <bool BLOB_IN_SMEM>
+__global__ void __launch_bounds__(256) mjb_pipeline_kernel(const __grid_constant__ KParams K) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const unsigned char* mb;
+  float* scr_base;
+  if (BLOB_IN_SMEM) {
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + K.blob_bytes);
+    stage_model_blob(smem, K.blob, K.blob_bytes, bar);
+    mb = smem;
+    scr_base = reinterpret_cast<float*>(smem + K.blob_bytes + 16);
+  } else {
+    mb = K.blob;
+    scr_base = reinterpret_cast<float*>(smem);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  float* scr = scr_base + (size_t)warp * K.scratch_floats;
+  const uint32_t st = K.stages;
+  for (int w = blockIdx.x * wpb + warp; w < K.dsz.nworld; w += gridDim.x * wpb) {
+    if (st & MJB_STAGE_KINEMATICS) s_kinematics(K, mb, w, lane);
+    if (st & MJB_STAGE_COM_POS) s_com_pos(K, mb, w, lane);
+    if (st & MJB_STAGE_CRB) s_crb(K, mb, w, lane);
+    if (st & MJB_STAGE_FACTOR_M) s_factor_m(K, w, lane, scr);
+    if ((st & MJB_STAGE_COLLISION) && K.o.run_collision_detection) s_collision(K, mb, w, lane, reinterpret_cast<int*>(scr));
+    if (st & MJB_STAGE_MAKE_CONSTRAINT) s_make_constraint(K, mb, w, lane);
+    if (st & MJB_STAGE_TRANSMISSION) s_transmission(K, mb, w, lane);
+    if (st & MJB_STAGE_ZERO_SENSOR) {
+      if (lane < 2) DW(energy)[lane] = 0.f;
+    }
+    if (st & MJB_STAGE_FWD_VELOCITY) s_fwd_velocity(K, mb, w, lane);
+    if (st & MJB_STAGE_FWD_ACTUATION) s_fwd_actuation(K, mb, w, lane);
+    if (st & MJB_STAGE_FWD_ACCELERATION) s_fwd_acceleration(K, mb, w, lane, scr, false);
+    if (st & MJB_STAGE_FWD_ACC_FACTOR) s_fwd_acceleration(K, mb, w, lane, scr, true);
+    if (st & MJB_STAGE_SOLVE) s_solve(K, mb, w, lane, scr);
+    if (st & MJB_STAGE_EULER) s_euler(K, mb, w, lane, scr);
+  }
+}
+
+// smooth.solve_m (smooth.py:2848): x = (L L^T)^-1 y with L = d.qLD
+__global__ void __launch_bounds__(256) mjb_solve_m_kernel(const __grid_constant__ KParams K) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  float* scr = reinterpret_cast<float*>(smem) + (size_t)warp * K.scratch_floats;
+  const int nv = K.ms.nv, ld = nv | 1;
+  for (int w = blockIdx.x * wpb + warp; w < K.dsz.nworld; w += gridDim.x * wpb) {
+    load_lower(scr, ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
+    float* x = scr + nv * ld;
+    for (int i = lane; i < nv; i += 32) x[i] = K.y[(size_t)w * nv + i];
+    __syncwarp();
+    warp_chol_solve(scr, ld, nv, x, lane);
+    for (int i = lane; i < nv; i += 32) K.x[(size_t)w * nv + i] = x[i];
+    __syncwarp();
+  }
+}
+
+// support.mul_m dense (support.py:105-129)
+__global__ void mjb_mul_m_kernel(const __grid_constant__ KParams K) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nv = K.ms.nv, np = K.ms.nv_pad;
+  if (t >= K.dsz.nworld * nv) return;
+  const int w = t / nv, i = t - w * nv;
+  const float* row = DW(qM) + (size_t)i * np;
+  const float* v = K.y + (size_t)w * nv;
+  float s = 0.f;
+  for (int j = 0; j < nv; j++) s += row[j] * v[j];
+  K.x[(size_t)w * nv + i] = s;
+}
+
+// util_misc.halton (util_misc.py:60-73)
+__device__ __forceinline__ float halton(int index, int base) {
+  int n0 = index;
+  const float b = (float)base;
+  float f = 1.0f / b, hn = 0.f;
+  while (n0 > 0) {
+    const int n1 = n0 / base;
+    const int r = n0 - n1 * base;
+    hn += f * (float)r;
+    f /= b;
+    n0 = n1;
+  }
+  return hn;
+}
+
+// benchmark.ctrl_noise (benchmark.py:42-83)
+__global__ void mjb_ctrl_noise_kernel(const __grid_constant__ KParams K, const float* ctrl_center, int step, float ctrlnoisestd,
+                                      float ctrlnoiserate) {
+  const unsigned char* mb = K.blob;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nu = K.ms.nu;
+  if (t >= K.dsz.nworld * nu) return;
+  const int w = t / nu, a = t - w * nu;
+  const float rate = expf(-K.o.timestep / ctrlnoiserate);
+  const float scale = ctrlnoisestd * sqrtf(1.0f - rate * rate);
+  float midpoint = 0.f, halfrange = 1.f;
+  const float lo = MR(actuator_ctrlrange)[2 * a], hi = MR(actuator_ctrlrange)[2 * a + 1];
+  const bool limited = MI(actuator_ctrllimited)[a] != 0;
+  if (limited) {
+    midpoint = 0.5f * (hi + lo);
+    halfrange = 0.5f * (hi - lo);
+  }
+  if (ctrl_center != nullptr) midpoint = ctrl_center[a];
+  float ctrl = rate * DW(ctrl)[a] + (1.0f - rate) * midpoint;
+  ctrl += scale * halfrange * (2.0f * halton((step + 1) * (w + 1), a + 2) - 1.0f);
+  if (limited) ctrl = clampf(ctrl, lo, hi);
+  DW(ctrl)[a] = ctrl;
+}

@@ -1,0 +1,615 @@
+// mjb_smooth.cuh -- position / velocity / actuation / acceleration stages, one warp per world.
+//
+// Replaces the reference's per-level kernel fan-out with float atomics (reference
+// mujoco_warp/_src/smooth.py:358 kinematics, :602 com_pos, :889 crb, :1104 factor_m, :2015 com_vel,
+// :1259 rne, :2605 transmission; forward.py:593-969) by warp-cooperative device functions:
+// tree recursions are level-synchronous (__syncwarp between depth levels), subtree sums use the
+// depth-first id ranges [b, subtreeend[b]) so that no atomics are needed and results are
+// deterministic.
+#pragma once
+
+#include "mjb_types.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// smooth.kinematics (smooth.py:45-224)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void s_kinematics(const KParams& K, const unsigned char* mb, int w, int lane) {
+  const float* qpos = DW(qpos);
+  float* xpos_o = DW(xpos);
+  float* xquat_o = DW(xquat);
+  float* xanchor_o = DW(xanchor);
+  float* xaxis_o = DW(xaxis);
+  const int* tree = MI(body_tree);
+  const int* tree_adr = MI(body_tree_adr);
+  for (int lv = 1; lv < K.ms.nlevel; lv++) {
+    const int a1 = tree_adr[lv + 1];
+    for (int i = tree_adr[lv] + lane; i < a1; i += 32) {
+      const int b = tree[i];
+      const int pid = MI(body_parentid)[b];
+      int jadr = MI(body_jntadr)[b];
+      const int jnum = MI(body_jntnum)[b];
+      if (jnum == 1 && MI(jnt_type)[jadr] == JNT_FREE) {  // smooth.py:83-95
+        const int qa = MI(jnt_qposadr)[jadr];
+        V3 p = ld3(qpos + qa);
+        Q4 q = normalize(ld4(qpos + qa + 3));
+        st3(xpos_o + 3 * b, p);
+        st4(xquat_o + 4 * b, q);
+        st3(xanchor_o + 3 * jadr, p);
+        st3(xaxis_o + 3 * jadr, ld3(MR(jnt_axis) + 3 * jadr));
+        continue;
+      }
+      V3 xpos;
+      Q4 xquat;
+      const int mocapid = MI(body_mocapid)[b];
+      if (mocapid >= 0) {
+        xpos = ld3(DW(mocap_pos) + 3 * mocapid);
+        xquat = ld4(DW(mocap_quat) + 4 * mocapid);
+      } else {
+        xpos = ld3(MR(body_pos) + 3 * b);
+        xquat = ld4(MR(body_quat) + 4 * b);
+      }
+      {
+        Q4 pq = ld4(xquat_o + 4 * pid);
+        xpos = rot_vec_quat(xpos, pq) + ld3(xpos_o + 3 * pid);
+        xquat = mul_quat(pq, xquat);
+      }
+      for (int k = 0; k < jnum; k++, jadr++) {  // smooth.py:115-139
+        const int qa = MI(jnt_qposadr)[jadr];
+        const int jt = MI(jnt_type)[jadr];
+        const V3 jaxis = ld3(MR(jnt_axis) + 3 * jadr);
+        const V3 jpos = ld3(MR(jnt_pos) + 3 * jadr);
+        const V3 xanchor = rot_vec_quat(jpos, xquat) + xpos;
+        const V3 xaxis = rot_vec_quat(jaxis, xquat);
+        if (jt == JNT_BALL) {
+          Q4 ql = normalize(ld4(qpos + qa));
+          xquat = mul_quat(xquat, ql);
+          xpos = xanchor - rot_vec_quat(jpos, xquat);
+        } else if (jt == JNT_SLIDE) {
+          xpos = xpos + xaxis * (qpos[qa] - MR(qpos0)[qa]);
+        } else if (jt == JNT_HINGE) {
+          Q4 ql = axis_angle_to_quat(jaxis, qpos[qa] - MR(qpos0)[qa]);
+          xquat = mul_quat(xquat, ql);
+          xpos = xanchor - rot_vec_quat(jpos, xquat);
+        }
+        st3(xanchor_o + 3 * jadr, xanchor);
+        st3(xaxis_o + 3 * jadr, xaxis);
+      }
+      st3(xpos_o + 3 * b, xpos);
+      st4(xquat_o + 4 * b, normalize(xquat));
+    }
+    __syncwarp();
+  }
+  // body matrices and inertial frames (smooth.py:147-173)
+  for (int b = lane; b < K.ms.nbody; b += 32) {
+    const Q4 q = ld4(xquat_o + 4 * b);
+    stm3(DW(xmat) + 9 * b, quat_to_mat(q));
+    st3(DW(xipos) + 3 * b, ld3(xpos_o + 3 * b) + rot_vec_quat(ld3(MR(body_ipos) + 3 * b), q));
+    stm3(DW(ximat) + 9 * b, quat_to_mat(mul_quat(q, ld4(MR(body_iquat) + 4 * b))));
+  }
+  // geoms (smooth.py:177-203); static world geoms keep their make_data pose
+  for (int g = lane; g < K.ms.ngeom; g += 32) {
+    if (MI(geom_static)[g]) continue;
+    const int b = MI(geom_bodyid)[g];
+    const Q4 q = ld4(xquat_o + 4 * b);
+    st3(DW(geom_xpos) + 3 * g, ld3(xpos_o + 3 * b) + rot_vec_quat(ld3(MR(geom_pos) + 3 * g), q));
+    stm3(DW(geom_xmat) + 9 * g, quat_to_mat(mul_quat(q, ld4(MR(geom_quat) + 4 * g))));
+  }
+  for (int s = lane; s < K.ms.nsite; s += 32) {  // smooth.py:207-224
+    const int b = MI(site_bodyid)[s];
+    const Q4 q = ld4(xquat_o + 4 * b);
+    st3(DW(site_xpos) + 3 * s, ld3(xpos_o + 3 * b) + rot_vec_quat(ld3(MR(site_pos) + 3 * s), q));
+    stm3(DW(site_xmat) + 9 * s, quat_to_mat(mul_quat(q, ld4(MR(site_quat) + 4 * s))));
+  }
+  __syncwarp();
+}
+
+// ---------------------------------------------------------------------------------------------
+// smooth.com_pos (smooth.py:464-632)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void s_com_pos(const KParams& K, const unsigned char* mb, int w, int lane) {
+  const float* xipos = DW(xipos);
+  float* scom = DW(subtree_com);
+  const int nb = K.ms.nbody;
+  for (int b = lane; b < nb; b += 32) {  // subtree = id range [b, end)
+    const int end = MI(body_subtreeend)[b];
+    V3 acc = V3{0.f, 0.f, 0.f};
+    for (int c = b; c < end; c++) acc = acc + ld3(xipos + 3 * c) * MR(body_mass)[c];
+    const float mass = MR(body_subtreemass)[b];
+    if (mass != 0.f) acc = acc * (1.0f / mass);
+    st3(scom + 3 * b, acc);
+  }
+  __syncwarp();
+  for (int b = lane; b < nb; b += 32) {  // smooth.py:511-553 (mju_inertCom)
+    const M3 mat = ldm3(DW(ximat) + 9 * b);
+    const V3 inert = ld3(MR(body_inertia) + 3 * b);
+    const float mass = MR(body_mass)[b];
+    const V3 dif = ld3(xipos + 3 * b) - ld3(scom + 3 * MI(body_rootid)[b]);
+    const float* a = mat.m;
+    float* res = DW(cinert) + 10 * b;
+    // tmp = mat * diag(inert) * mat^T
+    const float t00 = a[0] * a[0] * inert.x + a[1] * a[1] * inert.y + a[2] * a[2] * inert.z;
+    const float t11 = a[3] * a[3] * inert.x + a[4] * a[4] * inert.y + a[5] * a[5] * inert.z;
+    const float t22 = a[6] * a[6] * inert.x + a[7] * a[7] * inert.y + a[8] * a[8] * inert.z;
+    const float t01 = a[0] * a[3] * inert.x + a[1] * a[4] * inert.y + a[2] * a[5] * inert.z;
+    const float t02 = a[0] * a[6] * inert.x + a[1] * a[7] * inert.y + a[2] * a[8] * inert.z;
+    const float t12 = a[3] * a[6] * inert.x + a[4] * a[7] * inert.y + a[5] * a[8] * inert.z;
+    res[0] = t00 + mass * (dif.y * dif.y + dif.z * dif.z);
+    res[1] = t11 + mass * (dif.x * dif.x + dif.z * dif.z);
+    res[2] = t22 + mass * (dif.x * dif.x + dif.y * dif.y);
+    res[3] = t01 - mass * dif.x * dif.y;
+    res[4] = t02 - mass * dif.x * dif.z;
+    res[5] = t12 - mass * dif.y * dif.z;
+    res[6] = mass * dif.x;
+    res[7] = mass * dif.y;
+    res[8] = mass * dif.z;
+    res[9] = mass;
+  }
+  for (int j = lane; j < K.ms.njnt; j += 32) {  // smooth.py:557-598
+    const int b = MI(jnt_bodyid)[j];
+    const int jt = MI(jnt_type)[j];
+    float* res = DW(cdof) + 6 * MI(jnt_dofadr)[j];
+    const V3 off = ld3(scom + 3 * MI(body_rootid)[b]) - ld3(DW(xanchor) + 3 * j);
+    if (jt == JNT_FREE || jt == JNT_BALL) {
+      const M3 xmat = ldm3(DW(xmat) + 9 * b);
+      if (jt == JNT_FREE) {
+        for (int i = 0; i < 18; i++) res[i] = 0.f;
+        res[3] = 1.f;
+        res[6 + 4] = 1.f;
+        res[12 + 5] = 1.f;
+        res += 18;
+      }
+#pragma unroll
+      for (int a = 0; a < 3; a++) {
+        const V3 ax = mat_col(xmat, a);
+        st6(res + 6 * a, mk6(ax, cross(ax, off)));
+      }
+    } else if (jt == JNT_SLIDE) {
+      st6(res, mk6(V3{0.f, 0.f, 0.f}, ld3(DW(xaxis) + 3 * j)));
+    } else {
+      const V3 ax = ld3(DW(xaxis) + 3 * j);
+      st6(res, mk6(ax, cross(ax, off)));
+    }
+  }
+  __syncwarp();
+}
+
+// ---------------------------------------------------------------------------------------------
+// smooth.crb (smooth.py:807-912), dense qM (nv_pad x nv_pad, symmetric, zero padded)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void s_crb(const KParams& K, const unsigned char* mb, int w, int lane) {
+  const int nb = K.ms.nbody, nv = K.ms.nv, np = K.ms.nv_pad;
+  const float* cinert = DW(cinert);
+  float* crb = DW(crb);
+  for (int b = lane; b < nb; b += 32) {
+    // reference accumulates children into parents except into the world body (smooth.py:820)
+    const int end = b == 0 ? 1 : MI(body_subtreeend)[b];
+    float acc[10];
+#pragma unroll
+    for (int i = 0; i < 10; i++) acc[i] = 0.f;
+    for (int c = b; c < end; c++) {
+#pragma unroll
+      for (int i = 0; i < 10; i++) acc[i] += cinert[10 * c + i];
+    }
+#pragma unroll
+    for (int i = 0; i < 10; i++) crb[10 * b + i] = acc[i];
+  }
+  float* qM = DW(qM);
+  {
+    float4* q4 = reinterpret_cast<float4*>(qM);
+    const int n4 = (np * np) >> 2;
+    for (int i = lane; i < n4; i += 32) q4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  __syncwarp();
+  const float* cdof = DW(cdof);
+  for (int i = lane; i < nv; i += 32) {  // smooth.py:856-885
+    const S6 ci = ld6(cdof + 6 * i);
+    const S6 buf = inert_vec(crb + 10 * MI(dof_bodyid)[i], ci);
+    qM[i * np + i] = MR(dof_armature)[i] + dot6(ci, buf);
+    for (int j = MI(dof_parentid)[i]; j >= 0; j = MI(dof_parentid)[j]) {
+      const float v = dot6(ld6(cdof + 6 * j), buf);
+      qM[i * np + j] = v;
+      qM[j * np + i] = v;
+    }
+  }
+  __syncwarp();
+}
+
+// ---------------------------------------------------------------------------------------------
+// dense Cholesky in shared memory: A (n x n, leading dimension ld, lower triangle used) is
+// overwritten by L with A = L L^T (wp.tile_cholesky semantics, smooth.py:1085).  Left-looking,
+// lane = row.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void warp_cholesky(float* A, int ld, int n, int lane) {
+  for (int j = 0; j < n; j++) {
+    const float* rj = A + j * ld;
+    float s0 = 0.f, s1 = 0.f;
+    const int i0 = lane, i1 = lane + 32;
+    if (i0 >= j && i0 < n) {
+      const float* ri = A + i0 * ld;
+      s0 = ri[j];
+      for (int k = 0; k < j; k++) s0 -= ri[k] * rj[k];
+    }
+    if (i1 >= j && i1 < n) {
+      const float* ri = A + i1 * ld;
+      s1 = ri[j];
+      for (int k = 0; k < j; k++) s1 -= ri[k] * rj[k];
+    }
+    float sj = __shfl_sync(FULL, (j < 32) ? s0 : s1, j & 31);
+    const float ljj = sqrtf(fmaxf(sj, MJ_MINVAL));
+    const float inv = 1.0f / ljj;
+    if (i0 >= j && i0 < n) A[i0 * ld + j] = (i0 == j) ? ljj : s0 * inv;
+    if (i1 >= j && i1 < n) A[i1 * ld + j] = (i1 == j) ? ljj : s1 * inv;
+    __syncwarp();
+  }
+}
+
+// x <- (L L^T)^-1 x with L in shared memory, x in shared memory (n <= 64).
+__device__ __forceinline__ void warp_chol_solve(const float* L, int ld, int n, float* x, int lane) {
+  const int i0 = lane, i1 = lane + 32;
+  float x0 = i0 < n ? x[i0] : 0.f, x1 = i1 < n ? x[i1] : 0.f;
+  const float d0 = i0 < n ? L[i0 * ld + i0] : 1.f, d1 = i1 < n ? L[i1 * ld + i1] : 1.f;
+  for (int j = 0; j < n; j++) {  // forward: L y = b
+    const float xj = __shfl_sync(FULL, (j < 32) ? x0 / d0 : x1 / d1, j & 31);
+    if (i0 == j) x0 = xj;
+    if (i1 == j) x1 = xj;
+    if (i0 > j && i0 < n) x0 -= L[i0 * ld + j] * xj;
+    if (i1 > j && i1 < n) x1 -= L[i1 * ld + j] * xj;
+  }
+  for (int j = n - 1; j >= 0; j--) {  // backward: L^T x = y
+    const float xj = __shfl_sync(FULL, (j < 32) ? x0 / d0 : x1 / d1, j & 31);
+    if (i0 == j) x0 = xj;
+    if (i1 == j) x1 = xj;
+    if (i0 < j) x0 -= L[j * ld + i0] * xj;
+    if (i1 < j) x1 -= L[j * ld + i1] * xj;
+  }
+  if (i0 < n) x[i0] = x0;
+  if (i1 < n) x[i1] = x1;
+  __syncwarp();
+}
+
+// copies the lower triangle of the (n x n, ld_src) global matrix into shared memory (ld)
+__device__ __forceinline__ void load_lower(float* A, int ld, const float* src, int ld_src, int n, int lane, const float* diag_add,
+                                           float diag_scale) {
+  for (int i = 0; i < n; i++) {
+    for (int j = lane; j <= i; j += 32) {
+      float v = src[i * ld_src + j];
+      if (diag_add != nullptr && i == j) v += diag_scale * diag_add[i];
+      A[i * ld + j] = v;
+    }
+  }
+  __syncwarp();
+}
+
+// smooth.factor_m dense (smooth.py:1091-1109): qLD = chol(qM).  scr needs nv*ldh floats.
+__device__ __forceinline__ void s_factor_m(const KParams& K, int w, int lane, float* scr) {
+  const int nv = K.ms.nv, ld = nv | 1;
+  load_lower(scr, ld, DW(qM), K.ms.nv_pad, nv, lane, nullptr, 0.f);
+  warp_cholesky(scr, ld, nv, lane);
+  float* qLD = DW(qLD);
+  for (int i = 0; i < nv; i++)
+    for (int j = lane; j < nv; j += 32) qLD[i * nv + j] = (j <= i) ? scr[i * ld + j] : 0.f;
+  __syncwarp();
+}
+
+// ---------------------------------------------------------------------------------------------
+// smooth.transmission (smooth.py:2042-2149): JOINT / JOINTINPARENT.  The sparse moment layout
+// (rownnz/rowadr/colind) is static for joint transmissions and is written once by make_data; the
+// reference re-derives it every step with a per-world atomic counter (smooth.py:2094).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void s_transmission(const KParams& K, const unsigned char* mb, int w, int lane) {
+  const float* qpos = DW(qpos);
+  for (int a = lane; a < K.ms.nu; a += 32) {
+    const int j = MI(actuator_trnid)[2 * a];
+    const int jt = MI(jnt_type)[j], qa = MI(jnt_qposadr)[j];
+    const int trn = MI(actuator_trntype)[a];
+    const float* gear = MR(actuator_gear) + 6 * a;
+    float* mom = DW(actuator_moment) + DW(moment_rowadr)[a];
+    if (jt == JNT_FREE) {
+      DW(actuator_length)[a] = 0.f;
+      V3 g3 = ld3(gear + 3);
+      if (trn == 1) {
+        Q4 q = normalize(ld4(qpos + qa + 3));
+        g3 = rot_vec_quat(g3, Q4{q.w, -q.x, -q.y, -q.z});
+      }
+      mom[0] = gear[0]; mom[1] = gear[1]; mom[2] = gear[2];
+      st3(mom + 3, g3);
+    } else if (jt == JNT_BALL) {
+      Q4 q = normalize(ld4(qpos + qa));
+      V3 g3 = ld3(gear);
+      if (trn == 1) g3 = rot_vec_quat(g3, Q4{q.w, -q.x, -q.y, -q.z});
+      DW(actuator_length)[a] = dot(quat_to_vel(q), g3);
+      st3(mom, g3);
+    } else {
+      DW(actuator_length)[a] = qpos[qa] * gear[0];
+      mom[0] = gear[0];
+    }
+  }
+  __syncwarp();
+}
+
+// ---------------------------------------------------------------------------------------------
+// forward.fwd_velocity (forward.py:593): actuator_velocity (:541), com_vel (smooth.py:1936-2038),
+// passive spring/damper (passive.py:71-180, 536-565), rne (smooth.py:1113-1274)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned char* mb, int w, int lane) {
+  const int nb = K.ms.nbody, nv = K.ms.nv;
+  const float* qvel = DW(qvel);
+  const float* qpos = DW(qpos);
+  const float* cdof = DW(cdof);
+  float* cdof_dot = DW(cdof_dot);
+  float* cvel = DW(cvel);
+  float* cacc = DW(cacc);
+  float* cfrc = DW(cfrc_int);
+  const int* tree = MI(body_tree);
+  const int* tree_adr = MI(body_tree_adr);
+
+  for (int a = lane; a < K.ms.nu; a += 32) {
+    const int adr = DW(moment_rowadr)[a], nnz = DW(moment_rownnz)[a];
+    float v = 0.f;
+    for (int i = 0; i < nnz; i++) v += DW(actuator_moment)[adr + i] * qvel[DW(moment_colind)[adr + i]];
+    DW(actuator_velocity)[a] = v;
+  }
+  // passive forces: lane per joint
+  const int dsbl_spring = K.o.disableflags & DSBL_SPRING, dsbl_damper = K.o.disableflags & DSBL_DAMPER;
+  for (int j = lane; j < K.ms.njnt; j += 32) {
+    const int da = MI(jnt_dofadr)[j], qa = MI(jnt_qposadr)[j], jt = MI(jnt_type)[j];
+    const float k = MR(jnt_stiffness)[j], c = MR(dof_damping)[da];
+    const bool hs = k != 0.f && !dsbl_spring, hd = c != 0.f && !dsbl_damper;
+    const int n = jt == JNT_FREE ? 6 : (jt == JNT_BALL ? 3 : 1);
+    float sp[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (hs) {
+      if (jt == JNT_FREE) {
+        sp[0] = -k * (qpos[qa] - MR(qpos_spring)[qa]);
+        sp[1] = -k * (qpos[qa + 1] - MR(qpos_spring)[qa + 1]);
+        sp[2] = -k * (qpos[qa + 2] - MR(qpos_spring)[qa + 2]);
+        V3 dif = quat_sub(normalize(ld4(qpos + qa + 3)), ld4(MR(qpos_spring) + qa + 3));
+        sp[3] = -k * dif.x; sp[4] = -k * dif.y; sp[5] = -k * dif.z;
+      } else if (jt == JNT_BALL) {
+        V3 dif = quat_sub(normalize(ld4(qpos + qa)), ld4(MR(qpos_spring) + qa));
+        sp[0] = -k * dif.x; sp[1] = -k * dif.y; sp[2] = -k * dif.z;
+      } else {
+        sp[0] = -k * (qpos[qa] - MR(qpos_spring)[qa]);
+      }
+    }
+    for (int i = 0; i < n; i++) {
+      const float dm = hd ? -c * qvel[da + i] : 0.f;
+      DW(qfrc_spring)[da + i] = sp[i];
+      DW(qfrc_damper)[da + i] = dm;
+      DW(qfrc_gravcomp)[da + i] = 0.f;
+      DW(qfrc_fluid)[da + i] = 0.f;
+      DW(qfrc_passive)[da + i] = sp[i] + dm;
+    }
+  }
+  // com_vel + cacc, level-synchronous (cacc needs cdof_dot of the same body only)
+  if (lane < 6) {
+    cvel[lane] = 0.f;
+    float g = 0.f;
+    if (!(K.o.disableflags & DSBL_GRAVITY)) g = lane == 3 ? -K.o.gravity_x : (lane == 4 ? -K.o.gravity_y : (lane == 5 ? -K.o.gravity_z : 0.f));
+    cacc[lane] = g;
+  }
+  __syncwarp();
+  for (int lv = 1; lv < K.ms.nlevel; lv++) {
+    const int a1 = tree_adr[lv + 1];
+    for (int i = tree_adr[lv] + lane; i < a1; i += 32) {
+      const int b = tree[i], pid = MI(body_parentid)[b];
+      S6 v = ld6(cvel + 6 * pid);
+      S6 acc = ld6(cacc + 6 * pid);
+      int dof = MI(body_dofadr)[b];
+      const int j0 = MI(body_jntadr)[b], jn = MI(body_jntnum)[b];
+      for (int j = j0; j < j0 + jn; j++) {
+        const int jt = MI(jnt_type)[j];
+        if (jt == JNT_FREE) {
+          for (int k = 0; k < 3; k++) {
+            axpy6(v, qvel[dof + k], ld6(cdof + 6 * (dof + k)));
+            st6(cdof_dot + 6 * (dof + k), S6{{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}});
+          }
+          for (int k = 3; k < 6; k++) {
+            const S6 cd = motion_cross(v, ld6(cdof + 6 * (dof + k)));
+            st6(cdof_dot + 6 * (dof + k), cd);
+            axpy6(acc, qvel[dof + k], cd);
+          }
+          for (int k = 3; k < 6; k++) axpy6(v, qvel[dof + k], ld6(cdof + 6 * (dof + k)));
+          dof += 6;
+        } else if (jt == JNT_BALL) {
+          for (int k = 0; k < 3; k++) {
+            const S6 cd = motion_cross(v, ld6(cdof + 6 * (dof + k)));
+            st6(cdof_dot + 6 * (dof + k), cd);
+            axpy6(acc, qvel[dof + k], cd);
+          }
+          for (int k = 0; k < 3; k++) axpy6(v, qvel[dof + k], ld6(cdof + 6 * (dof + k)));
+          dof += 3;
+        } else {
+          const S6 c = ld6(cdof + 6 * dof);
+          const S6 cd = motion_cross(v, c);
+          st6(cdof_dot + 6 * dof, cd);
+          axpy6(acc, qvel[dof], cd);
+          axpy6(v, qvel[dof], c);
+          dof += 1;
+        }
+      }
+      st6(cvel + 6 * b, v);
+      st6(cacc + 6 * b, acc);
+      // body force (smooth.py:1188-1209), own contribution; subtree sums follow
+      const float* ci = DW(cinert) + 10 * b;
+      S6 f = inert_vec(ci, acc);
+      const S6 u = motion_cross_force(v, inert_vec(ci, v));
+#pragma unroll
+      for (int k = 0; k < 6; k++) f.v[k] += u.v[k];
+      st6(DW(cfrc_ext) + 6 * b, f);  // staging: cfrc_ext is rewritten to zero below
+    }
+    __syncwarp();
+  }
+  // cfrc_int[b] = sum of the own forces over the subtree (smooth.py:1219-1240 without atomics)
+  for (int b = lane; b < nb; b += 32) {
+    const int end = MI(body_subtreeend)[b];
+    S6 acc = S6{{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+    for (int c = (b == 0 ? 1 : b); c < end; c++) axpy6(acc, 1.0f, ld6(DW(cfrc_ext) + 6 * c));
+    st6(cfrc + 6 * b, acc);
+  }
+  __syncwarp();
+  for (int b = lane; b < nb; b += 32) st6(DW(cfrc_ext) + 6 * b, S6{{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}});
+  for (int i = lane; i < nv; i += 32) DW(qfrc_bias)[i] = dot6(ld6(cdof + 6 * i), ld6(cfrc + 6 * MI(dof_bodyid)[i]));
+  __syncwarp();
+}
+
+// support.next_act (support.py:38-64)
+__device__ __forceinline__ float next_act(float dt, int dyntype, const float* dynprm, const float* actrange, float act, float act_dot,
+                                          float scale, bool clamp) {
+  if (dyntype == 3) {
+    const float tau = fmaxf(MJ_MINVAL, dynprm[0]);
+    act = act + scale * act_dot * tau * (1.0f - expf(-dt / tau));
+  } else if (dyntype == 5) {
+    return act;
+  } else {
+    act = act + scale * act_dot * dt;
+  }
+  if (clamp) act = clampf(act, actrange[0], actrange[1]);
+  return act;
+}
+
+// forward.fwd_actuation (forward.py:617-927), no muscles / tendons
+__device__ __forceinline__ void s_fwd_actuation(const KParams& K, const unsigned char* mb, int w, int lane) {
+  const int nv = K.ms.nv, nu = K.ms.nu;
+  if (!nu || (K.o.disableflags & DSBL_ACTUATION)) {
+    for (int i = lane; i < K.ms.na; i += 32) DW(act_dot)[i] = 0.f;
+    for (int i = lane; i < nv; i += 32) DW(qfrc_actuator)[i] = 0.f;
+    __syncwarp();
+    return;
+  }
+  for (int u = lane; u < nu; u += 32) {
+    float ctrl = DW(ctrl)[u];
+    if (MI(actuator_ctrllimited)[u] && !(K.o.disableflags & DSBL_CLAMPCTRL))
+      ctrl = clampf(ctrl, MR(actuator_ctrlrange)[2 * u], MR(actuator_ctrlrange)[2 * u + 1]);
+    float ctrl_act = ctrl;
+    const int af = MI(actuator_actadr)[u];
+    if (K.ms.na && af >= 0) {
+      const int al = af + MI(actuator_actnum)[u] - 1, dyn = MI(actuator_dyntype)[u];
+      const float* dynprm = MR(actuator_dynprm) + 10 * u;
+      float act_dot = 0.f, act = 0.f;
+      if (dyn == 1) act_dot = ctrl;
+      else if (dyn == 2 || dyn == 3) { act = DW(act)[al]; act_dot = (ctrl - act) / fmaxf(dynprm[0], MJ_MINVAL); }
+      DW(act_dot)[al] = act_dot;
+      if (MI(actuator_actearly)[u]) {
+        if (dyn == 1 || dyn == 0) act = DW(act)[al];
+        ctrl_act = next_act(K.o.timestep, dyn, dynprm, MR(actuator_actrange) + 2 * u, act, act_dot, 1.0f, MI(actuator_actlimited)[u] != 0);
+      } else {
+        ctrl_act = DW(act)[al];
+      }
+    }
+    const float len = DW(actuator_length)[u], vel = DW(actuator_velocity)[u];
+    const float* gp = MR(actuator_gainprm) + 10 * u;
+    const float* bp = MR(actuator_biasprm) + 10 * u;
+    float gain = 0.f, bias = 0.f;
+    const int gt = MI(actuator_gaintype)[u];
+    if (gt == 0) gain = gp[0];
+    else if (gt == 1) gain = gp[0] + gp[1] * len + gp[2] * vel;
+    if (MI(actuator_biastype)[u] == 1) bias = bp[0] + bp[1] * len + bp[2] * vel;
+    float force = gain * ctrl_act + bias;
+    if (MI(actuator_forcelimited)[u]) force = clampf(force, MR(actuator_forcerange)[2 * u], MR(actuator_forcerange)[2 * u + 1]);
+    DW(actuator_force)[u] = force;
+  }
+  __syncwarp();
+  // qfrc_actuator = moment^T force: lane per dof gathers (deterministic, no atomics; forward.py:783)
+  const int nJ = K.ms.nJmom;
+  for (int i = lane; i < nv; i += 32) {
+    float q = 0.f;
+    for (int u = 0; u < nu; u++) {
+      const int adr = DW(moment_rowadr)[u], nnz = DW(moment_rownnz)[u];
+      for (int k = 0; k < nnz; k++)
+        if (DW(moment_colind)[adr + k] == i) q += DW(actuator_moment)[adr + k] * DW(actuator_force)[u];
+    }
+    (void)nJ;
+    const int j = MI(dof_jntid)[i];
+    if (K.ms.ngravcomp && MI(jnt_actgravcomp)[j]) q += DW(qfrc_gravcomp)[i];
+    if (MI(jnt_actfrclimited)[j]) q = clampf(q, MR(jnt_actfrcrange)[2 * j], MR(jnt_actfrcrange)[2 * j + 1]);
+    DW(qfrc_actuator)[i] = q;
+  }
+  __syncwarp();
+}
+
+// forward.fwd_acceleration (forward.py:931-969) + support.apply_ft (support.py:175-216).
+// scr: nv*ldh + nv_pad floats.
+__device__ __forceinline__ void s_fwd_acceleration(const KParams& K, const unsigned char* mb, int w, int lane, float* scr, bool factorize) {
+  const int nv = K.ms.nv, nb = K.ms.nbody, ld = nv | 1;
+  float* x = scr + nv * ld;
+  const float* xfrc = DW(xfrc_applied);
+  for (int i = lane; i < nv; i += 32) {
+    float q = DW(qfrc_passive)[i] - DW(qfrc_bias)[i] + DW(qfrc_actuator)[i] + DW(qfrc_applied)[i];
+    const S6 cd = ld6(DW(cdof) + 6 * i);
+    const int db = MI(dof_bodyid)[i], end = MI(body_subtreeend)[db];
+    for (int b = db; b < end; b++) {  // bodies in the subtree of the dof's body
+      const S6 ft = ld6(xfrc + 6 * b);
+      if (ft.v[0] == 0.f && ft.v[1] == 0.f && ft.v[2] == 0.f && ft.v[3] == 0.f && ft.v[4] == 0.f && ft.v[5] == 0.f) continue;
+      const V3 off = ld3(DW(xipos) + 3 * b) - ld3(DW(subtree_com) + 3 * MI(body_rootid)[b]);
+      q += dot(bot(cd), top(ft)) + dot(top(cd), bot(ft)) + dot(cross(top(cd), off), top(ft));
+    }
+    DW(qfrc_smooth)[i] = q;
+    x[i] = q;
+  }
+  __syncwarp();
+  if (factorize) {
+    load_lower(scr, ld, DW(qM), K.ms.nv_pad, nv, lane, nullptr, 0.f);
+    warp_cholesky(scr, ld, nv, lane);
+    float* qLD = DW(qLD);
+    for (int i = 0; i < nv; i++)
+      for (int j = lane; j < nv; j += 32) qLD[i * nv + j] = (j <= i) ? scr[i * ld + j] : 0.f;
+  } else {
+    load_lower(scr, ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
+  }
+  __syncwarp();
+  warp_chol_solve(scr, ld, nv, x, lane);
+  for (int i = lane; i < nv; i += 32) DW(qacc_smooth)[i] = x[i];
+  __syncwarp();
+}
+
+// forward.euler (forward.py:327-354) + _advance (:213-274).  scr: nv*ldh + nv_pad floats.
+__device__ __forceinline__ void s_euler(const KParams& K, const unsigned char* mb, int w, int lane, float* scr) {
+  const int nv = K.ms.nv, ld = nv | 1;
+  const float dt = K.o.timestep;
+  float* x = scr + nv * ld;
+  const bool damp = !(K.o.disableflags & (DSBL_EULERDAMP | DSBL_DAMPER));
+  if (damp) {  // (M + dt diag(damping)) qacc' = Ma
+    load_lower(scr, ld, DW(qM), K.ms.nv_pad, nv, lane, MR(dof_damping), dt);
+    warp_cholesky(scr, ld, nv, lane);
+    for (int i = lane; i < nv; i += 32) x[i] = DW(efc_Ma)[i];
+    __syncwarp();
+    warp_chol_solve(scr, ld, nv, x, lane);
+  } else {
+    for (int i = lane; i < nv; i += 32) x[i] = DW(qacc)[i];
+    __syncwarp();
+  }
+  for (int u = lane; u < K.ms.nu; u += 32) {
+    const int a0 = MI(actuator_actadr)[u];
+    if (a0 < 0) continue;
+    for (int j = a0; j < a0 + MI(actuator_actnum)[u]; j++)
+      DW(act)[j] = next_act(dt, MI(actuator_dyntype)[u], MR(actuator_dynprm) + 10 * u, MR(actuator_actrange) + 2 * u, DW(act)[j],
+                            DW(act_dot)[j], 1.0f, MI(actuator_actlimited)[u] != 0);
+  }
+  float* qvel = DW(qvel);
+  float* qpos = DW(qpos);
+  for (int i = lane; i < nv; i += 32) {
+    qvel[i] += x[i] * dt;
+    DW(qacc_warmstart)[i] = DW(qacc)[i];
+  }
+  __syncwarp();
+  for (int j = lane; j < K.ms.njnt; j += 32) {  // forward.py:52-112
+    const int qa = MI(jnt_qposadr)[j], da = MI(jnt_dofadr)[j], jt = MI(jnt_type)[j];
+    if (jt == JNT_FREE) {
+      qpos[qa] += dt * qvel[da];
+      qpos[qa + 1] += dt * qvel[da + 1];
+      qpos[qa + 2] += dt * qvel[da + 2];
+      st4(qpos + qa + 3, quat_integrate(ld4(qpos + qa + 3), ld3(qvel + da + 3), dt));
+    } else if (jt == JNT_BALL) {
+      st4(qpos + qa, quat_integrate(ld4(qpos + qa), ld3(qvel + da), dt));
+    } else {
+      qpos[qa] += dt * qvel[da];
+    }
+  }
+  if (lane == 0) {
+    DW(time)[0] += dt;
+    int st = 0;
+    if (DW(nefc)[0] > K.dsz.njmax) st |= MJB_STATUS_NEFC_OVERFLOW;  // forward.py:194
+    if (st) DW(status)[0] |= st;
+  }
+  __syncwarp();
+}

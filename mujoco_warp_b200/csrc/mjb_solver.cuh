@@ -1,0 +1,360 @@
+// mjb_solver.cuh -- solver.solve (reference solver.py:3297): primal Newton / CG with the exact
+// iterative bracketing linesearch, pyramidal cones, dense Jacobian.  One warp per world; the whole
+// iteration loop runs inside the kernel with per-world convergence.
+//
+// The reference drives ~12-15 kernel launches per iteration from a CUDA conditional-graph while
+// node and polls a global `nsolving` counter (solver.py:3188-3343).  Here:
+//   * dof vectors (qacc, Ma, grad, Mgrad, search, mv) and per-row vectors (Jaref, jv, D, force) live
+//     in the warp's shared-memory scratch;
+//   * H = M + J^T D J (solver.py:2368) is accumulated in a 4x8 register tile per lane over 32x32
+//     blocks, only for rows whose QUADRATIC state changed (incremental update, solver.py:2055),
+//     then added to the shared-memory copy of H;
+//   * Cholesky + triangular solves run in shared memory (lane = row, shuffles for broadcasts);
+//   * the linesearch evaluates lo/hi/mid candidates with lanes over rows and 9 warp reductions.
+#pragma once
+
+#include "mjb_smooth.cuh"
+#include "mjb_types.cuh"
+
+struct Pt3 {
+  float c, g, h;
+};
+__device__ __forceinline__ Pt3 operator+(Pt3 a, Pt3 b) { return Pt3{a.c + b.c, a.g + b.g, a.h + b.h}; }
+__device__ __forceinline__ Pt3 warp_sum(Pt3 p) { return Pt3{warp_sum(p.c), warp_sum(p.g), warp_sum(p.h)}; }
+
+// solver.py:571-598 (_compute_efc_eval_pt_pyramidal)
+__device__ __forceinline__ Pt3 efc_eval_pt(int r, float alpha, int ne, int nf, float D, float floss, float jaref, float jv) {
+  const float x = jaref + alpha * jv;
+  const float jvD = jv * D;
+  const Pt3 quad = Pt3{0.5f * D * x * x, jvD * x, jv * jvD};
+  if (r >= ne + nf) return x < 0.f ? quad : Pt3{0.f, 0.f, 0.f};
+  if (r >= ne) {  // solver.py:224
+    const float rf = safe_div(floss, D);
+    if (-rf < x && x < rf) return quad;
+    if (x <= -rf) return Pt3{floss * (-0.5f * rf - x), -floss * jv, 0.f};
+    return Pt3{floss * (-0.5f * rf + x), floss * jv, 0.f};
+  }
+  return quad;
+}
+// solver.py:198
+__device__ __forceinline__ Pt3 eval_pt_quad(float q0, float q1, float q2, float alpha) {
+  const float aq2 = alpha * q2;
+  return Pt3{alpha * aq2 + alpha * q1 + q0, 2.0f * aq2 + q1, 2.0f * q2};
+}
+__device__ __forceinline__ bool in_bracket(Pt3 x, Pt3 y) { return (x.g < y.g && y.g < 0.f) || (x.g > y.g && y.g > 0.f); }
+
+struct SolverScr {
+  float *H, *L, *x, *grad, *search, *mv, *qacc, *Ma, *qfs, *Jaref, *jv, *D, *coef, *force;
+  int ld;
+};
+__host__ __device__ inline int solver_scratch_floats(int nv, int nv_pad, int njmax_pad) {
+  return 2 * nv * (nv | 1) + 7 * nv_pad + 5 * njmax_pad + 8;
+}
+__device__ __forceinline__ SolverScr solver_scr(float* scr, int nv, int nvp, int njp) {
+  SolverScr s;
+  s.ld = nv | 1;
+  s.H = scr;
+  s.L = s.H + nv * s.ld;
+  float* v = s.L + nv * s.ld;
+  v += (4 - ((2 * nv * s.ld) & 3)) & 3;  // keep the vectors 16-byte aligned
+  s.x = v; s.grad = v + nvp; s.search = v + 2 * nvp; s.mv = v + 3 * nvp; s.qacc = v + 4 * nvp; s.Ma = v + 5 * nvp; s.qfs = v + 6 * nvp;
+  float* r = v + 7 * nvp;
+  s.Jaref = r; s.jv = r + njp; s.D = r + 2 * njp; s.coef = r + 3 * njp; s.force = r + 4 * njp;
+  return s;
+}
+
+// res[row] = A[row, :n] . vec for rows handled by this lane (A row-major, 16-byte aligned rows)
+__device__ __forceinline__ float row_dot(const float* __restrict__ row, const float* __restrict__ vec, int n4) {
+  const float4* a = reinterpret_cast<const float4*>(row);
+  const float4* v = reinterpret_cast<const float4*>(vec);
+  float s = 0.f;
+  for (int k = 0; k < n4; k++) {
+    const float4 x = a[k], y = v[k];
+    s += x.x * y.x + x.y * y.y + x.z * y.z + x.w * y.w;
+  }
+  return s;
+}
+
+// H(lower) += sum_r coef[r] * J[r]^T J[r], register tiles of 4 rows x 8 columns per lane over
+// 32x32 blocks (solver.py:2368 JTDAJ and :2055 incremental update in one routine).
+__device__ __forceinline__ void h_accumulate(const KParams& K, int w, int lane, const SolverScr& s, int nefc) {
+  const int nv = K.ms.nv, np = K.ms.nv_pad, ld = s.ld;
+  const float* J = DW(efc_J);
+  const int a = lane >> 2, b = lane & 3;
+  const int nblk = (nv + 31) >> 5;
+  for (int bi = 0; bi < nblk; bi++) {
+    for (int bj = 0; bj <= bi; bj++) {
+      const int r0 = 32 * bi + 4 * a, c0 = 32 * bj + 8 * b;
+      const bool rin = r0 < np, cin0 = c0 < np, cin1 = c0 + 4 < np;
+      const bool need = rin && cin0 && (r0 + 3 >= c0);
+      float acc[4][8];
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
+      for (int r = 0; r < nefc; r++) {
+        const float cf = s.coef[r];
+        if (cf == 0.f) continue;  // warp-uniform
+        if (need) {
+          const float* Jr = J + (size_t)r * np;
+          const float4 ji = *reinterpret_cast<const float4*>(Jr + r0);
+          const float4 ja = *reinterpret_cast<const float4*>(Jr + c0);
+          const float4 jb = cin1 ? *reinterpret_cast<const float4*>(Jr + c0 + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+          const float vi[4] = {ji.x * cf, ji.y * cf, ji.z * cf, ji.w * cf};
+          const float vj[8] = {ja.x, ja.y, ja.z, ja.w, jb.x, jb.y, jb.z, jb.w};
+#pragma unroll
+          for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int j = 0; j < 8; j++) acc[i][j] += vi[i] * vj[j];
+        }
+      }
+      if (need) {
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+          for (int j = 0; j < 8; j++) {
+            const int ri = r0 + i, cj = c0 + j;
+            if (ri < nv && cj <= ri) s.H[ri * ld + cj] += acc[i][j];
+          }
+      }
+    }
+  }
+  __syncwarp();
+}
+
+// solver.py:2154-2219 _update_constraint.  Returns the cost; sets force/state (global), coef.
+__device__ __forceinline__ void update_constraint(const KParams& K, int w, int lane, const SolverScr& s, int nefc, int ne, int nf, bool first,
+                                                  float& cost, float& gauss, bool& any_change) {
+  const int nv = K.ms.nv, np = K.ms.nv_pad;
+  float c = 0.f;
+  bool changed = false;
+  int* state = DW(efc_state);
+  for (int r = lane; r < nefc; r += 32) {
+    const float D = s.D[r], ja = s.Jaref[r];
+    float f;
+    int st;
+    if (r < ne) {
+      f = -D * ja; st = ST_QUADRATIC; c += 0.5f * D * ja * ja;
+    } else if (r < ne + nf) {
+      const float fl = DW(efc_frictionloss)[r], rf = safe_div(fl, D);
+      if (ja <= -rf) { f = fl; st = ST_LINEARNEG; c += -fl * (0.5f * rf + ja); }
+      else if (ja >= rf) { f = -fl; st = ST_LINEARPOS; c += -fl * (0.5f * rf - ja); }
+      else { f = -D * ja; st = ST_QUADRATIC; c += 0.5f * D * ja * ja; }
+    } else {
+      if (ja >= 0.f) { f = 0.f; st = ST_SATISFIED; }
+      else { f = -D * ja; st = ST_QUADRATIC; c += 0.5f * D * ja * ja; }
+    }
+    const bool newq = st == ST_QUADRATIC;
+    const bool oldq = first ? false : (state[r] == ST_QUADRATIC);
+    s.coef[r] = newq == oldq ? 0.f : (newq ? D : -D);
+    changed |= newq != oldq;
+    s.force[r] = f;
+    state[r] = st;
+    DW(efc_force)[r] = f;
+  }
+  any_change = __any_sync(FULL, changed);
+  __syncwarp();
+  // qfrc_constraint = J^T force (solver.py:1988): lane = dof, uniform loop over rows with force
+  const float* J = DW(efc_J);
+  float g = 0.f;
+  for (int i0 = 0; i0 < nv; i0 += 32) {
+    const int i = i0 + lane;
+    float q = 0.f;
+    for (int r = 0; r < nefc; r++) {
+      const float f = s.force[r];
+      if (f != 0.f && i < nv) q += J[(size_t)r * np + i] * f;
+    }
+    if (i < nv) {
+      DW(qfrc_constraint)[i] = q;
+      // grad = Ma - qfrc_smooth - qfrc_constraint (solver.py:2238)
+      s.grad[i] = s.Ma[i] - s.qfs[i] - q;
+      g += (s.Ma[i] - s.qfs[i]) * (s.qacc[i] - DW(qacc_smooth)[i]);
+    }
+  }
+  gauss = 0.5f * warp_sum(g);
+  cost = warp_sum(c) + gauss;
+  __syncwarp();
+}
+
+__device__ __forceinline__ Pt3 ls_rows(const KParams& K, int w, int lane, const SolverScr& s, int nefc, int ne, int nf, float alpha) {
+  Pt3 t = Pt3{0.f, 0.f, 0.f};
+  for (int r = lane; r < nefc; r += 32) {
+    const float fl = (r >= ne && r < ne + nf) ? DW(efc_frictionloss)[r] : 0.f;
+    t = t + efc_eval_pt(r, alpha, ne, nf, s.D[r], fl, s.Jaref[r], s.jv[r]);
+  }
+  return t;
+}
+
+// solver.py:887-1341 linesearch_iterative (pyramidal); updates qacc, Ma, Jaref in scratch.
+__device__ __forceinline__ void linesearch(const KParams& K, int w, int lane, const SolverScr& s, int nefc, int ne, int nf, float gauss,
+                                           float search_dot) {
+  const int nv = K.ms.nv, np = K.ms.nv_pad, n4 = np >> 2;
+  // mv = M search, jv = J search
+  for (int i = lane; i < nv; i += 32) s.mv[i] = row_dot(DW(qM) + (size_t)i * np, s.search, n4);
+  for (int r = lane; r < nefc; r += 32) s.jv[r] = row_dot(DW(efc_J) + (size_t)r * np, s.search, n4);
+  __syncwarp();
+  const float scale = K.o.meaninertia * (float)nv;
+  const float gtol = fmaxf(K.o.tolerance * K.o.ls_tolerance * sqrtf(search_dot) * scale, 1e-6f);
+  float q1 = 0.f, q2 = 0.f;
+  for (int i = lane; i < nv; i += 32) {
+    q1 += s.search[i] * (s.Ma[i] - s.qfs[i]);
+    q2 += 0.5f * s.search[i] * s.mv[i];
+  }
+  q1 = warp_sum(q1);
+  q2 = warp_sum(q2);
+  const float q0 = gauss;
+  Pt3 p0 = warp_sum(ls_rows(K, w, lane, s, nefc, ne, nf, 0.f)) + Pt3{q0, q1, 2.0f * q2};
+  const float lo_alpha_in = -safe_div(p0.g, p0.h);
+  Pt3 lo_in = warp_sum(ls_rows(K, w, lane, s, nefc, ne, nf, lo_alpha_in)) + eval_pt_quad(q0, q1, q2, lo_alpha_in);
+  float alpha;
+  if (fabsf(lo_in.g) < gtol && lo_in.c < p0.c) {
+    alpha = lo_alpha_in;
+  } else {
+    alpha = 0.f;
+    const bool lo_less = lo_in.g < p0.g;
+    Pt3 lo = lo_less ? lo_in : p0, hi = lo_less ? p0 : lo_in;
+    float lo_alpha = lo_less ? lo_alpha_in : 0.f, hi_alpha = lo_less ? 0.f : lo_alpha_in;
+    for (int it = 0; it < K.o.ls_iterations; it++) {
+      const float lo_next_alpha = lo_alpha - safe_div(lo.g, lo.h);
+      const float hi_next_alpha = hi_alpha - safe_div(hi.g, hi.h);
+      const float mid_alpha = 0.5f * (lo_alpha + hi_alpha);
+      Pt3 a = Pt3{0.f, 0.f, 0.f}, b = a, c = a;
+      for (int r = lane; r < nefc; r += 32) {
+        const float fl = (r >= ne && r < ne + nf) ? DW(efc_frictionloss)[r] : 0.f;
+        const float D = s.D[r], ja = s.Jaref[r], jv = s.jv[r];
+        a = a + efc_eval_pt(r, lo_next_alpha, ne, nf, D, fl, ja, jv);
+        b = b + efc_eval_pt(r, hi_next_alpha, ne, nf, D, fl, ja, jv);
+        c = c + efc_eval_pt(r, mid_alpha, ne, nf, D, fl, ja, jv);
+      }
+      const Pt3 lo_next = warp_sum(a) + eval_pt_quad(q0, q1, q2, lo_next_alpha);
+      const Pt3 hi_next = warp_sum(b) + eval_pt_quad(q0, q1, q2, hi_next_alpha);
+      const Pt3 mid = warp_sum(c) + eval_pt_quad(q0, q1, q2, mid_alpha);
+      // bracket swapping, solver.py:1293-1316
+      const bool s1 = in_bracket(lo, lo_next);
+      if (s1) { lo = lo_next; lo_alpha = lo_next_alpha; }
+      const bool s2 = in_bracket(lo, mid);
+      if (s2) { lo = mid; lo_alpha = mid_alpha; }
+      const bool s3 = in_bracket(lo, hi_next);
+      if (s3) { lo = hi_next; lo_alpha = hi_next_alpha; }
+      const bool h1 = in_bracket(hi, hi_next);
+      if (h1) { hi = hi_next; hi_alpha = hi_next_alpha; }
+      const bool h2 = in_bracket(hi, mid);
+      if (h2) { hi = mid; hi_alpha = mid_alpha; }
+      const bool h3 = in_bracket(hi, lo_next);
+      if (h3) { hi = lo_next; hi_alpha = lo_next_alpha; }
+      const bool swap_lo = s1 || s2 || s3, swap_hi = h1 || h2 || h3;
+      const bool ls_done = (!swap_lo && !swap_hi) || (lo.g < 0.f && lo.g > -gtol) || (hi.g > 0.f && hi.g < gtol);
+      const bool improved = lo.c < p0.c || hi.c < p0.c, lo_better = lo.c < hi.c;
+      if (improved) alpha = lo_better ? lo_alpha : hi_alpha;
+      if (ls_done) break;
+    }
+  }
+  for (int i = lane; i < nv; i += 32) {
+    s.qacc[i] += alpha * s.search[i];
+    s.Ma[i] += alpha * s.mv[i];
+  }
+  for (int r = lane; r < nefc; r += 32) s.Jaref[r] += alpha * s.jv[r];
+  __syncwarp();
+}
+
+// Newton: factor H, Mgrad = H^-1 grad.  CG: Mgrad = M^-1 grad with the factor held in s.L.
+__device__ __forceinline__ void solve_direction(const KParams& K, int lane, const SolverScr& s, bool newton) {
+  const int nv = K.ms.nv, ld = s.ld;
+  if (newton) {
+    for (int i = 0; i < nv; i++)
+      for (int j = lane; j <= i; j += 32) s.L[i * ld + j] = s.H[i * ld + j];
+    __syncwarp();
+    warp_cholesky(s.L, ld, nv, lane);
+  }
+  for (int i = lane; i < nv; i += 32) s.x[i] = s.grad[i];
+  __syncwarp();
+  warp_chol_solve(s.L, ld, nv, s.x, lane);
+}
+
+__device__ __forceinline__ void s_solve(const KParams& K, const unsigned char* mb, int w, int lane, float* scr) {
+  const int nv = K.ms.nv, np = K.ms.nv_pad, njmax = K.dsz.njmax;
+  if (njmax == 0 || nv == 0) {  // solver.py:3298
+    for (int i = lane; i < nv; i += 32) DW(qacc)[i] = DW(qacc_smooth)[i];
+    if (lane == 0) DW(solver_niter)[0] = 0;
+    __syncwarp();
+    return;
+  }
+  const SolverScr s = solver_scr(scr, nv, np, K.dsz.njmax_pad);
+  const int nefc = min(DW(nefc)[0], njmax), ne = DW(ne)[0], nf = DW(nf)[0];
+  const bool newton = K.o.solver == SOLVER_NEWTON;
+  const float* src = (K.o.disableflags & DSBL_WARMSTART) ? DW(qacc_smooth) : DW(qacc_warmstart);
+  for (int i = lane; i < np; i += 32) {
+    s.qacc[i] = i < nv ? src[i] : 0.f;
+    s.qfs[i] = i < nv ? DW(qfrc_smooth)[i] : 0.f;
+    s.search[i] = 0.f;
+  }
+  for (int r = lane; r < nefc; r += 32) s.D[r] = DW(efc_D)[r];
+  __syncwarp();
+  // init_context, solver.py:3257: Jaref = J qacc - aref, Ma = M qacc
+  const int n4 = np >> 2;
+  for (int r = lane; r < nefc; r += 32) s.Jaref[r] = row_dot(DW(efc_J) + (size_t)r * np, s.qacc, n4) - DW(efc_aref)[r];
+  for (int i = lane; i < nv; i += 32) s.Ma[i] = row_dot(DW(qM) + (size_t)i * np, s.qacc, n4);
+  __syncwarp();
+  float cost, gauss, prev_cost;
+  bool any_change;
+  update_constraint(K, w, lane, s, nefc, ne, nf, true, cost, gauss, any_change);
+  if (newton) {
+    load_lower(s.H, s.ld, DW(qM), np, nv, lane, nullptr, 0.f);
+    if (any_change) h_accumulate(K, w, lane, s, nefc);
+  } else {
+    load_lower(s.L, s.ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
+  }
+  solve_direction(K, lane, s, newton);
+  float grad_dot = 0.f, search_dot = 0.f;
+  for (int i = lane; i < nv; i += 32) {
+    const float v = -s.x[i];
+    s.search[i] = v;
+    search_dot += v * v;
+  }
+  search_dot = warp_sum(search_dot);
+  __syncwarp();
+  const float scl = 1.0f / (K.o.meaninertia * (float)nv);
+  float* prev_grad = s.H;            // CG only (H is unused by CG)
+  float* prev_Mgrad = s.H + np;
+  int niter = 0;
+  for (int it = 0; it < K.o.iterations; it++) {  // _solver_iteration, solver.py:3188
+    linesearch(K, w, lane, s, nefc, ne, nf, gauss, search_dot);
+    if (!newton) {
+      for (int i = lane; i < nv; i += 32) { prev_grad[i] = s.grad[i]; prev_Mgrad[i] = s.x[i]; }
+      __syncwarp();
+    }
+    prev_cost = cost;
+    update_constraint(K, w, lane, s, nefc, ne, nf, false, cost, gauss, any_change);
+    if (newton && any_change) h_accumulate(K, w, lane, s, nefc);
+    solve_direction(K, lane, s, newton);
+    float beta = 0.f;
+    if (!newton) {  // Polak-Ribiere, solver.py:3081
+      float num = 0.f, den = 0.f;
+      for (int i = lane; i < nv; i += 32) { num += s.grad[i] * (s.x[i] - prev_Mgrad[i]); den += prev_grad[i] * prev_Mgrad[i]; }
+      beta = fmaxf(0.f, warp_sum(num) / fmaxf(MJ_MINVAL, warp_sum(den)));
+    }
+    grad_dot = 0.f;
+    search_dot = 0.f;
+    for (int i = lane; i < nv; i += 32) {
+      float v = -s.x[i];
+      if (!newton) v += beta * s.search[i];
+      s.search[i] = v;
+      search_dot += v * v;
+      grad_dot += s.grad[i] * s.grad[i];
+    }
+    search_dot = warp_sum(search_dot);
+    grad_dot = warp_sum(grad_dot);
+    __syncwarp();
+    niter++;
+    const float improvement = (prev_cost - cost) * scl, gradient = sqrtf(grad_dot) * scl;  // solver.py:3177
+    if (improvement < K.o.tolerance || gradient < K.o.tolerance) break;
+  }
+  for (int i = lane; i < nv; i += 32) {
+    const float q = s.qacc[i];
+    DW(qacc)[i] = q;
+    DW(efc_Ma)[i] = s.Ma[i];
+    if (!(q == q)) atomicOr(DW(status), MJB_STATUS_NAN_QACC);
+  }
+  if (lane == 0) DW(solver_niter)[0] = niter;
+  __syncwarp();
+}
