@@ -43,6 +43,9 @@ struct MjbData {
   int device;
   int nsm;
   int smem_optin;
+  // launch configuration of the pipeline kernel, resolved on the first launch
+  int cfg_ready, cfg_wpb, cfg_grid, cfg_in_smem;
+  size_t cfg_smem;
 };
 
 // ---- field-table introspection --------------------------------------------------------------
@@ -235,19 +238,29 @@ extern "C" int mjb_run_stages(const MjbModel* m, MjbData* d, const MjbOption* op
     CUDA_OK(cudaMemsetAsync(d->d.nacon, 0, sizeof(int), stream));
     CUDA_OK(cudaMemsetAsync(d->d.ncollision, 0, sizeof(int), stream));
   }
-  const int wpb = warps_per_block();
-  const size_t scr_bytes = (size_t)wpb * d->scratch_floats * sizeof(float);
-  const bool in_smem = (size_t)m->blob_bytes + 16 + scr_bytes <= (size_t)d->smem_optin && m->blob_bytes <= 96 * 1024;
-  const size_t smem = in_smem ? (size_t)m->blob_bytes + 16 + scr_bytes : scr_bytes;
-  if (smem > (size_t)d->smem_optin) return fail(-5, "model needs more shared memory than the device offers");
-  auto kern = in_smem ? mjb_pipeline_kernel<true> : mjb_pipeline_kernel<false>;
-  CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int occ = 1;
-  CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * wpb, smem));
-  if (occ < 1) occ = 1;
-  int grid = (d->dsz.nworld + wpb - 1) / wpb;
-  const int maxgrid = d->nsm * occ;
-  if (grid > maxgrid) grid = maxgrid;
+  if (!d->cfg_ready) {
+    const int wpb = warps_per_block();
+    const size_t scr_bytes = (size_t)wpb * d->scratch_floats * sizeof(float);
+    const bool in_smem = (size_t)m->blob_bytes + 16 + scr_bytes <= (size_t)d->smem_optin && m->blob_bytes <= 96 * 1024;
+    const size_t smem = in_smem ? (size_t)m->blob_bytes + 16 + scr_bytes : scr_bytes;
+    if (smem > (size_t)d->smem_optin) return fail(-5, "model needs more shared memory than the device offers");
+    auto k0 = in_smem ? mjb_pipeline_kernel<true> : mjb_pipeline_kernel<false>;
+    CUDA_OK(cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 1;
+    CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k0, 32 * wpb, smem));
+    if (occ < 1) occ = 1;
+    int grid = (d->dsz.nworld + wpb - 1) / wpb;
+    const int maxgrid = d->nsm * occ;
+    if (grid > maxgrid) grid = maxgrid;
+    d->cfg_wpb = wpb;
+    d->cfg_grid = grid;
+    d->cfg_in_smem = in_smem;
+    d->cfg_smem = smem;
+    d->cfg_ready = 1;
+  }
+  const int wpb = d->cfg_wpb, grid = d->cfg_grid;
+  const size_t smem = d->cfg_smem;
+  auto kern = d->cfg_in_smem ? mjb_pipeline_kernel<true> : mjb_pipeline_kernel<false>;
   return timed_launch(stream, [&] { kern<<<grid, 32 * wpb, smem, stream>>>(K); });
 }
 
