@@ -31,9 +31,16 @@ __device__ __forceinline__ EfcRow efc_row(const KParams& K, float pos_aref, floa
   if (solref[0] <= 0.f) k = -solref[0] / dmax_sq;
   if (solref[1] <= 0.f) b = -solref[1] / dmax;
   const float imp_x = fabsf(pos_imp) / width;
-  const float imp_a = (1.0f / powf(mid, power - 1.0f)) * powf(imp_x, power);
-  const float imp_b = 1.0f - (1.0f / powf(1.0f - mid, power - 1.0f)) * powf(1.0f - imp_x, power);
-  const float imp_y = imp_x < mid ? imp_a : imp_b;
+  float imp_y;
+  if (power == 1.0f) {  // pow(x, 0) == 1: both branches reduce to imp_x
+    imp_y = imp_x;
+  } else if (power == 2.0f) {
+    imp_y = imp_x < mid ? imp_x * imp_x / mid : 1.0f - (1.0f - imp_x) * (1.0f - imp_x) / (1.0f - mid);
+  } else if (imp_x < mid) {
+    imp_y = (1.0f / powf(mid, power - 1.0f)) * powf(imp_x, power);
+  } else {
+    imp_y = 1.0f - (1.0f / powf(1.0f - mid, power - 1.0f)) * powf(1.0f - imp_x, power);
+  }
   float imp = clampf(dmin + imp_y * (dmax - dmin), dmin, dmax);
   if (imp_x > 1.0f) imp = dmax;
   EfcRow r;

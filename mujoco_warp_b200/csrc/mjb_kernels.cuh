@@ -9,10 +9,8 @@
 
 __host__ __device__ inline int mjb_scratch_floats(int nv, int nv_pad, int njmax_pad) {
   int a = solver_scratch_floats(nv, nv_pad, njmax_pad);
-  int b = nv * (nv | 1) + nv_pad + 8;  // factor / solve
-  int c = 64 + 8;                      // collision queue
-  int m = a > b ? a : b;
-  m = m > c ? m : c;
+  int c = 64 + 8;  // collision queue
+  int m = a > c ? a : c;
   return (m + 3) & ~3;
 }
 
@@ -86,9 +84,9 @@ __global__ void __launch_bounds__(256) mjb_solve_m_kernel(const __grid_constant_
   extern __shared__ __align__(16) unsigned char smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
   float* scr = reinterpret_cast<float*>(smem) + (size_t)warp * K.scratch_floats;
-  const int nv = K.ms.nv, ld = nv | 1;
+  const int nv = K.ms.nv, ld = chol_ld(K.ms.nv_pad);
   for (int w = blockIdx.x * wpb + warp; w < K.dsz.nworld; w += gridDim.x * wpb) {
-    load_lower(scr, ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
+    load_rows(scr, ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
     float* x = scr + nv * ld;
     for (int i = lane; i < nv; i += 32) x[i] = K.y[(size_t)w * nv + i];
     __syncwarp();

@@ -215,30 +215,58 @@ __device__ __forceinline__ void s_crb(const KParams& K, const unsigned char* mb,
 }
 
 // ---------------------------------------------------------------------------------------------
+// Per-warp shared-memory scratch layout, shared by factor_m / fwd_acceleration / solve / euler:
+//   H (nv x ld) | L (nv x ld) | 7 dof vectors (nv_pad each) | 5 row vectors (njmax_pad each)
+// ld is a multiple of 4 with ld/4 odd so that LDS.128 row accesses by consecutive lanes are
+// bank-conflict free.
+// ---------------------------------------------------------------------------------------------
+__host__ __device__ inline int chol_ld(int nv_pad) { return ((nv_pad >> 2) & 1) ? nv_pad : nv_pad + 4; }
+struct SolverScr {
+  float *H, *L, *x, *grad, *search, *mv, *qacc, *Ma, *qfs, *Jaref, *jv, *D, *coef, *force;
+  int ld;
+};
+__host__ __device__ inline int solver_scratch_floats(int nv, int nv_pad, int njmax_pad) {
+  return 2 * nv * chol_ld(nv_pad) + 7 * nv_pad + 5 * njmax_pad;
+}
+__device__ __forceinline__ SolverScr solver_scr(float* scr, int nv, int nvp, int njp) {
+  SolverScr s;
+  s.ld = chol_ld(nvp);
+  s.H = scr;
+  s.L = s.H + nv * s.ld;
+  float* v = s.L + nv * s.ld;
+  s.x = v; s.grad = v + nvp; s.search = v + 2 * nvp; s.mv = v + 3 * nvp; s.qacc = v + 4 * nvp; s.Ma = v + 5 * nvp; s.qfs = v + 6 * nvp;
+  float* r = v + 7 * nvp;
+  s.Jaref = r; s.jv = r + njp; s.D = r + 2 * njp; s.coef = r + 3 * njp; s.force = r + 4 * njp;
+  return s;
+}
+
+// ---------------------------------------------------------------------------------------------
 // dense Cholesky in shared memory: A (n x n, leading dimension ld, lower triangle used) is
 // overwritten by L with A = L L^T (wp.tile_cholesky semantics, smooth.py:1085).  Left-looking,
-// lane = row.
+// lane = row, 128-bit shared-memory loads for the row dot products.
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float chol_row_dot(const float* ri, const float* rj, int j, float s) {
+  const float4* a4 = reinterpret_cast<const float4*>(ri);
+  const float4* b4 = reinterpret_cast<const float4*>(rj);
+  const int j4 = j >> 2;
+  for (int q = 0; q < j4; q++) {
+    const float4 a = a4[q], b = b4[q];
+    s -= a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+  }
+  for (int k = j4 << 2; k < j; k++) s -= ri[k] * rj[k];
+  return s;
+}
 __device__ __forceinline__ void warp_cholesky(float* A, int ld, int n, int lane) {
+  const int i0 = lane, i1 = lane + 32;
   for (int j = 0; j < n; j++) {
     const float* rj = A + j * ld;
     float s0 = 0.f, s1 = 0.f;
-    const int i0 = lane, i1 = lane + 32;
-    if (i0 >= j && i0 < n) {
-      const float* ri = A + i0 * ld;
-      s0 = ri[j];
-      for (int k = 0; k < j; k++) s0 -= ri[k] * rj[k];
-    }
-    if (i1 >= j && i1 < n) {
-      const float* ri = A + i1 * ld;
-      s1 = ri[j];
-      for (int k = 0; k < j; k++) s1 -= ri[k] * rj[k];
-    }
-    float sj = __shfl_sync(FULL, (j < 32) ? s0 : s1, j & 31);
-    const float ljj = sqrtf(fmaxf(sj, MJ_MINVAL));
-    const float inv = 1.0f / ljj;
-    if (i0 >= j && i0 < n) A[i0 * ld + j] = (i0 == j) ? ljj : s0 * inv;
-    if (i1 >= j && i1 < n) A[i1 * ld + j] = (i1 == j) ? ljj : s1 * inv;
+    if (i0 >= j && i0 < n) s0 = chol_row_dot(A + i0 * ld, rj, j, A[i0 * ld + j]);
+    if (i1 >= j && i1 < n) s1 = chol_row_dot(A + i1 * ld, rj, j, A[i1 * ld + j]);
+    const float sj = __shfl_sync(FULL, (j < 32) ? s0 : s1, j & 31);
+    const float inv = rsqrtf(fmaxf(sj, MJ_MINVAL));
+    if (i0 >= j && i0 < n) A[i0 * ld + j] = (i0 == j) ? sj * inv : s0 * inv;
+    if (i1 >= j && i1 < n) A[i1 * ld + j] = (i1 == j) ? sj * inv : s1 * inv;
     __syncwarp();
   }
 }
@@ -247,47 +275,80 @@ __device__ __forceinline__ void warp_cholesky(float* A, int ld, int n, int lane)
 __device__ __forceinline__ void warp_chol_solve(const float* L, int ld, int n, float* x, int lane) {
   const int i0 = lane, i1 = lane + 32;
   float x0 = i0 < n ? x[i0] : 0.f, x1 = i1 < n ? x[i1] : 0.f;
-  const float d0 = i0 < n ? L[i0 * ld + i0] : 1.f, d1 = i1 < n ? L[i1 * ld + i1] : 1.f;
-  for (int j = 0; j < n; j++) {  // forward: L y = b
-    const float xj = __shfl_sync(FULL, (j < 32) ? x0 / d0 : x1 / d1, j & 31);
-    if (i0 == j) x0 = xj;
-    if (i1 == j) x1 = xj;
-    if (i0 > j && i0 < n) x0 -= L[i0 * ld + j] * xj;
-    if (i1 > j && i1 < n) x1 -= L[i1 * ld + j] * xj;
-  }
-  for (int j = n - 1; j >= 0; j--) {  // backward: L^T x = y
-    const float xj = __shfl_sync(FULL, (j < 32) ? x0 / d0 : x1 / d1, j & 31);
-    if (i0 == j) x0 = xj;
-    if (i1 == j) x1 = xj;
-    if (i0 < j) x0 -= L[j * ld + i0] * xj;
-    if (i1 < j) x1 -= L[j * ld + i1] * xj;
+  const float d0 = i0 < n ? 1.0f / L[i0 * ld + i0] : 1.f, d1 = i1 < n ? 1.0f / L[i1 * ld + i1] : 1.f;
+  if (n <= 32) {
+    for (int j = 0; j < n; j++) {  // forward: L y = b
+      const float xj = __shfl_sync(FULL, x0 * d0, j);
+      if (i0 == j) x0 = xj;
+      if (i0 > j && i0 < n) x0 -= L[i0 * ld + j] * xj;
+    }
+    for (int j = n - 1; j >= 0; j--) {  // backward: L^T x = y
+      const float xj = __shfl_sync(FULL, x0 * d0, j);
+      if (i0 == j) x0 = xj;
+      if (i0 < j) x0 -= L[j * ld + i0] * xj;
+    }
+  } else {
+    for (int j = 0; j < n; j++) {
+      const float xj = __shfl_sync(FULL, (j < 32) ? x0 * d0 : x1 * d1, j & 31);
+      if (i0 == j) x0 = xj;
+      if (i1 == j) x1 = xj;
+      if (i0 > j && i0 < n) x0 -= L[i0 * ld + j] * xj;
+      if (i1 > j && i1 < n) x1 -= L[i1 * ld + j] * xj;
+    }
+    for (int j = n - 1; j >= 0; j--) {
+      const float xj = __shfl_sync(FULL, (j < 32) ? x0 * d0 : x1 * d1, j & 31);
+      if (i0 == j) x0 = xj;
+      if (i1 == j) x1 = xj;
+      if (i0 < j) x0 -= L[j * ld + i0] * xj;
+      if (i1 < j) x1 -= L[j * ld + i1] * xj;
+    }
   }
   if (i0 < n) x[i0] = x0;
   if (i1 < n) x[i1] = x1;
   __syncwarp();
 }
 
-// copies the lower triangle of the (n x n, ld_src) global matrix into shared memory (ld)
-__device__ __forceinline__ void load_lower(float* A, int ld, const float* src, int ld_src, int n, int lane, const float* diag_add,
-                                           float diag_scale) {
-  for (int i = 0; i < n; i++) {
-    for (int j = lane; j <= i; j += 32) {
-      float v = src[i * ld_src + j];
-      if (diag_add != nullptr && i == j) v += diag_scale * diag_add[i];
-      A[i * ld + j] = v;
+// copies the n leading rows of a global matrix (ld_src) into shared memory (ld); rows are copied
+// whole (the Cholesky only reads the lower triangle).  Optional diagonal shift.
+__device__ __forceinline__ void load_rows(float* A, int ld, const float* src, int ld_src, int n, int lane, const float* diag_add,
+                                          float diag_scale) {
+  if ((ld_src & 3) == 0) {
+    const int c4 = ld_src >> 2, ld4 = ld >> 2;
+    const float4* s4 = reinterpret_cast<const float4*>(src);
+    float4* a4 = reinterpret_cast<float4*>(A);
+    for (int idx = lane; idx < n * c4; idx += 32) {
+      const int i = idx / c4, q = idx - i * c4;
+      a4[i * ld4 + q] = s4[idx];
+    }
+  } else {
+    for (int idx = lane; idx < n * ld_src; idx += 32) {
+      const int i = idx / ld_src, j = idx - i * ld_src;
+      A[i * ld + j] = src[idx];
     }
   }
   __syncwarp();
+  if (diag_add != nullptr) {
+    for (int i = lane; i < n; i += 32) A[i * ld + i] += diag_scale * diag_add[i];
+    __syncwarp();
+  }
 }
 
-// smooth.factor_m dense (smooth.py:1091-1109): qLD = chol(qM).  scr needs nv*ldh floats.
-__device__ __forceinline__ void s_factor_m(const KParams& K, int w, int lane, float* scr) {
-  const int nv = K.ms.nv, ld = nv | 1;
-  load_lower(scr, ld, DW(qM), K.ms.nv_pad, nv, lane, nullptr, 0.f);
-  warp_cholesky(scr, ld, nv, lane);
+// writes the lower-triangular factor held in shared memory to d.qLD (nv x nv, zero upper part)
+__device__ __forceinline__ void store_qLD(const KParams& K, int w, int lane, const float* L, int ld) {
+  const int nv = K.ms.nv;
   float* qLD = DW(qLD);
-  for (int i = 0; i < nv; i++)
-    for (int j = lane; j < nv; j += 32) qLD[i * nv + j] = (j <= i) ? scr[i * ld + j] : 0.f;
+  for (int idx = lane; idx < nv * nv; idx += 32) {
+    const int i = idx / nv, j = idx - i * nv;
+    qLD[idx] = (j <= i) ? L[i * ld + j] : 0.f;
+  }
+}
+
+// smooth.factor_m dense (smooth.py:1091-1109): qLD = chol(qM).
+__device__ __forceinline__ void s_factor_m(const KParams& K, int w, int lane, float* scr) {
+  const SolverScr s = solver_scr(scr, K.ms.nv, K.ms.nv_pad, K.dsz.njmax_pad);
+  load_rows(s.L, s.ld, DW(qM), K.ms.nv_pad, K.ms.nv, lane, nullptr, 0.f);
+  warp_cholesky(s.L, s.ld, K.ms.nv, lane);
+  store_qLD(K, w, lane, s.L, s.ld);
   __syncwarp();
 }
 
@@ -528,10 +589,11 @@ __device__ __forceinline__ void s_fwd_actuation(const KParams& K, const unsigned
 }
 
 // forward.fwd_acceleration (forward.py:931-969) + support.apply_ft (support.py:175-216).
-// scr: nv*ldh + nv_pad floats.
+// Leaves chol(qM) in the scratch L slot.
 __device__ __forceinline__ void s_fwd_acceleration(const KParams& K, const unsigned char* mb, int w, int lane, float* scr, bool factorize) {
-  const int nv = K.ms.nv, nb = K.ms.nbody, ld = nv | 1;
-  float* x = scr + nv * ld;
+  const int nv = K.ms.nv;
+  const SolverScr s = solver_scr(scr, nv, K.ms.nv_pad, K.dsz.njmax_pad);
+  float* x = s.x;
   const float* xfrc = DW(xfrc_applied);
   for (int i = lane; i < nv; i += 32) {
     float q = DW(qfrc_passive)[i] - DW(qfrc_bias)[i] + DW(qfrc_actuator)[i] + DW(qfrc_applied)[i];
@@ -548,32 +610,31 @@ __device__ __forceinline__ void s_fwd_acceleration(const KParams& K, const unsig
   }
   __syncwarp();
   if (factorize) {
-    load_lower(scr, ld, DW(qM), K.ms.nv_pad, nv, lane, nullptr, 0.f);
-    warp_cholesky(scr, ld, nv, lane);
-    float* qLD = DW(qLD);
-    for (int i = 0; i < nv; i++)
-      for (int j = lane; j < nv; j += 32) qLD[i * nv + j] = (j <= i) ? scr[i * ld + j] : 0.f;
+    load_rows(s.L, s.ld, DW(qM), K.ms.nv_pad, nv, lane, nullptr, 0.f);
+    warp_cholesky(s.L, s.ld, nv, lane);
+    store_qLD(K, w, lane, s.L, s.ld);
   } else {
-    load_lower(scr, ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
+    load_rows(s.L, s.ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
   }
   __syncwarp();
-  warp_chol_solve(scr, ld, nv, x, lane);
+  warp_chol_solve(s.L, s.ld, nv, x, lane);
   for (int i = lane; i < nv; i += 32) DW(qacc_smooth)[i] = x[i];
   __syncwarp();
 }
 
-// forward.euler (forward.py:327-354) + _advance (:213-274).  scr: nv*ldh + nv_pad floats.
+// forward.euler (forward.py:327-354) + _advance (:213-274).
 __device__ __forceinline__ void s_euler(const KParams& K, const unsigned char* mb, int w, int lane, float* scr) {
-  const int nv = K.ms.nv, ld = nv | 1;
+  const int nv = K.ms.nv;
+  const SolverScr s = solver_scr(scr, nv, K.ms.nv_pad, K.dsz.njmax_pad);
   const float dt = K.o.timestep;
-  float* x = scr + nv * ld;
+  float* x = s.x;
   const bool damp = !(K.o.disableflags & (DSBL_EULERDAMP | DSBL_DAMPER));
   if (damp) {  // (M + dt diag(damping)) qacc' = Ma
-    load_lower(scr, ld, DW(qM), K.ms.nv_pad, nv, lane, MR(dof_damping), dt);
-    warp_cholesky(scr, ld, nv, lane);
+    load_rows(s.L, s.ld, DW(qM), K.ms.nv_pad, nv, lane, MR(dof_damping), dt);
+    warp_cholesky(s.L, s.ld, nv, lane);
     for (int i = lane; i < nv; i += 32) x[i] = DW(efc_Ma)[i];
     __syncwarp();
-    warp_chol_solve(scr, ld, nv, x, lane);
+    warp_chol_solve(s.L, s.ld, nv, x, lane);
   } else {
     for (int i = lane; i < nv; i += 32) x[i] = DW(qacc)[i];
     __syncwarp();

@@ -43,26 +43,6 @@ __device__ __forceinline__ Pt3 eval_pt_quad(float q0, float q1, float q2, float 
 }
 __device__ __forceinline__ bool in_bracket(Pt3 x, Pt3 y) { return (x.g < y.g && y.g < 0.f) || (x.g > y.g && y.g > 0.f); }
 
-struct SolverScr {
-  float *H, *L, *x, *grad, *search, *mv, *qacc, *Ma, *qfs, *Jaref, *jv, *D, *coef, *force;
-  int ld;
-};
-__host__ __device__ inline int solver_scratch_floats(int nv, int nv_pad, int njmax_pad) {
-  return 2 * nv * (nv | 1) + 7 * nv_pad + 5 * njmax_pad + 8;
-}
-__device__ __forceinline__ SolverScr solver_scr(float* scr, int nv, int nvp, int njp) {
-  SolverScr s;
-  s.ld = nv | 1;
-  s.H = scr;
-  s.L = s.H + nv * s.ld;
-  float* v = s.L + nv * s.ld;
-  v += (4 - ((2 * nv * s.ld) & 3)) & 3;  // keep the vectors 16-byte aligned
-  s.x = v; s.grad = v + nvp; s.search = v + 2 * nvp; s.mv = v + 3 * nvp; s.qacc = v + 4 * nvp; s.Ma = v + 5 * nvp; s.qfs = v + 6 * nvp;
-  float* r = v + 7 * nvp;
-  s.Jaref = r; s.jv = r + njp; s.D = r + 2 * njp; s.coef = r + 3 * njp; s.force = r + 4 * njp;
-  return s;
-}
-
 // res[row] = A[row, :n] . vec for rows handled by this lane (A row-major, 16-byte aligned rows)
 __device__ __forceinline__ float row_dot(const float* __restrict__ row, const float* __restrict__ vec, int n4) {
   const float4* a = reinterpret_cast<const float4*>(row);
@@ -258,11 +238,13 @@ __device__ __forceinline__ void linesearch(const KParams& K, int w, int lane, co
 }
 
 // Newton: factor H, Mgrad = H^-1 grad.  CG: Mgrad = M^-1 grad with the factor held in s.L.
-__device__ __forceinline__ void solve_direction(const KParams& K, int lane, const SolverScr& s, bool newton) {
+// The factor is only recomputed when H changed since the last factorisation.
+__device__ __forceinline__ void solve_direction(const KParams& K, int lane, const SolverScr& s, bool refactor) {
   const int nv = K.ms.nv, ld = s.ld;
-  if (newton) {
-    for (int i = 0; i < nv; i++)
-      for (int j = lane; j <= i; j += 32) s.L[i * ld + j] = s.H[i * ld + j];
+  if (refactor) {
+    const float4* h4 = reinterpret_cast<const float4*>(s.H);
+    float4* l4 = reinterpret_cast<float4*>(s.L);
+    for (int i = lane; i < (nv * ld) >> 2; i += 32) l4[i] = h4[i];
     __syncwarp();
     warp_cholesky(s.L, ld, nv, lane);
   }
@@ -298,13 +280,16 @@ __device__ __forceinline__ void s_solve(const KParams& K, const unsigned char* m
   float cost, gauss, prev_cost;
   bool any_change;
   update_constraint(K, w, lane, s, nefc, ne, nf, true, cost, gauss, any_change);
+  // chol(qM) is already in s.L when fwd_acceleration ran for this world in the same launch
+  const bool l_is_chol_m = (K.stages & (MJB_STAGE_FWD_ACCELERATION | MJB_STAGE_FWD_ACC_FACTOR)) != 0;
   if (newton) {
-    load_lower(s.H, s.ld, DW(qM), np, nv, lane, nullptr, 0.f);
+    load_rows(s.H, s.ld, DW(qM), np, nv, lane, nullptr, 0.f);
     if (any_change) h_accumulate(K, w, lane, s, nefc);
+    solve_direction(K, lane, s, any_change || !l_is_chol_m);
   } else {
-    load_lower(s.L, s.ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
+    if (!l_is_chol_m) load_rows(s.L, s.ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
+    solve_direction(K, lane, s, false);
   }
-  solve_direction(K, lane, s, newton);
   float grad_dot = 0.f, search_dot = 0.f;
   for (int i = lane; i < nv; i += 32) {
     const float v = -s.x[i];
@@ -326,7 +311,7 @@ __device__ __forceinline__ void s_solve(const KParams& K, const unsigned char* m
     prev_cost = cost;
     update_constraint(K, w, lane, s, nefc, ne, nf, false, cost, gauss, any_change);
     if (newton && any_change) h_accumulate(K, w, lane, s, nefc);
-    solve_direction(K, lane, s, newton);
+    solve_direction(K, lane, s, newton && any_change);
     float beta = 0.f;
     if (!newton) {  // Polak-Ribiere, solver.py:3081
       float num = 0.f, den = 0.f;
