@@ -90,6 +90,11 @@ void mjb_timing_enable(int on);
 double mjb_timing_ms(void);
 long long mjb_timing_launches(void);
 void mjb_timing_reset(void);
+/* The step is issued as one launch per stage group (smooth_position, collision, make_constraint,
+ * smooth_velocity, solve, euler); these report the time of one group's launches since the reset. */
+double mjb_timing_group_ms(int group);
+int mjb_group_count(void);
+const char* mjb_group_name(int group);
 
 const char* mjb_last_error(void);
 const char* mjb_version(void);

@@ -86,6 +86,11 @@ def load():
     lib.mjb_timing_enable.argtypes = [ctypes.c_int]
     lib.mjb_timing_ms.restype = ctypes.c_double
     lib.mjb_timing_launches.restype = ctypes.c_longlong
+    lib.mjb_timing_group_ms.restype = ctypes.c_double
+    lib.mjb_timing_group_ms.argtypes = [ctypes.c_int]
+    lib.mjb_group_count.restype = ctypes.c_int
+    lib.mjb_group_name.restype = ctypes.c_char_p
+    lib.mjb_group_name.argtypes = [ctypes.c_int]
     lib.mjb_last_error.restype = ctypes.c_char_p
     lib.mjb_version.restype = ctypes.c_char_p
     _check_tables(lib)

@@ -14,7 +14,11 @@
 static thread_local std::string g_err;
 static long long g_launches = 0;
 static int g_timing = 0;
-static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_events;
+struct TimedLaunch {
+  cudaEvent_t first, second;
+  int group;  // StageGroup, or -1 for the utility kernels
+};
+static std::vector<TimedLaunch> g_events;
 static std::mutex g_mu;
 
 static int fail(int code, const std::string& msg) {
@@ -44,8 +48,10 @@ struct MjbData {
   int nsm;
   int smem_optin;
   // launch configuration of the pipeline kernel, resolved on the first launch
-  int cfg_ready, cfg_wpb, cfg_grid, cfg_in_smem;
-  size_t cfg_smem;
+  struct GroupCfg {  // launch configuration of one stage-group kernel, resolved on first use
+    int ready, wpb, grid, in_smem, scratch_floats;
+    size_t smem;
+  } cfg[G_COUNT];
 };
 
 // ---- field-table introspection --------------------------------------------------------------
@@ -166,7 +172,8 @@ extern "C" int mjb_data_bind(const MjbModel* m, const int* sizes, int nsizes, in
     MJB_DATA_REAL_FIELDS(X)
 #undef X
   }
-  d->scratch_floats = mjb_scratch_floats(m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad);
+  d->scratch_floats = chol_scratch_floats(m->ms.nv, m->ms.nv_pad);
+  memset(d->cfg, 0, sizeof(d->cfg));
   cudaError_t e = cudaGetDevice(&d->device);
   if (e != cudaSuccess) {
     delete d;
@@ -195,19 +202,19 @@ static void fill_params(KParams& K, const MjbModel* m, const MjbData* d, const M
   K.stages = stages;
 }
 
-static int warps_per_block() {
-  static int wpb = 0;
-  if (wpb == 0) {
+// warps (= worlds in flight) per CTA; MJB_WARPS_PER_BLOCK overrides the per-group default
+static int warps_per_block(int dflt) {
+  static int env = -1;
+  if (env < 0) {
     const char* e = getenv("MJB_WARPS_PER_BLOCK");
-    wpb = e ? atoi(e) : 4;
-    if (wpb < 1) wpb = 1;
-    if (wpb > 8) wpb = 8;
+    env = e ? atoi(e) : 0;
+    if (env > 8) env = 8;
   }
-  return wpb;
+  return env > 0 ? env : dflt;
 }
 
 template <typename F>
-static int timed_launch(cudaStream_t stream, F&& launch) {
+static int timed_launch(cudaStream_t stream, F&& launch, int group = -1) {
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (g_timing) {
     cudaEventCreate(&e0);
@@ -218,12 +225,60 @@ static int timed_launch(cudaStream_t stream, F&& launch) {
   if (g_timing) {
     cudaEventRecord(e1, stream);
     std::lock_guard<std::mutex> lk(g_mu);
-    g_events.emplace_back(e0, e1);
+    g_events.push_back(TimedLaunch{e0, e1, group});
   }
   g_launches++;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(-11, std::string("kernel launch: ") + cudaGetErrorString(e));
   return 0;
+}
+
+typedef void (*GroupKernel)(const KParams);
+template <int G>
+static GroupKernel group_kernel(bool in_smem) {
+  return in_smem ? mjb_group_kernel<G, true> : mjb_group_kernel<G, false>;
+}
+static GroupKernel group_kernel_of(int g, bool in_smem) {
+  switch (g) {
+    case G_POS: return group_kernel<G_POS>(in_smem);
+    case G_COL: return group_kernel<G_COL>(in_smem);
+    case G_CON: return group_kernel<G_CON>(in_smem);
+    case G_VEL: return group_kernel<G_VEL>(in_smem);
+    case G_SOL: return group_kernel<G_SOL>(in_smem);
+    default: return group_kernel<G_EUL>(in_smem);
+  }
+}
+
+static int launch_group(int g, const MjbModel* m, MjbData* d, KParams& K, uint32_t stages, cudaStream_t stream) {
+  MjbData::GroupCfg& c = d->cfg[g];
+  if (!c.ready) {
+    const int wpb = warps_per_block(g == G_SOL ? 4 : 8);
+    c.scratch_floats = group_scratch_floats(g, m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad);
+    const size_t scr_bytes = (size_t)wpb * c.scratch_floats * sizeof(float);
+    const bool in_smem =
+        group_uses_blob(g) && (size_t)m->blob_bytes + 16 + scr_bytes <= (size_t)d->smem_optin && m->blob_bytes <= 96 * 1024;
+    const size_t smem = in_smem ? (size_t)m->blob_bytes + 16 + scr_bytes : scr_bytes;
+    if (smem > (size_t)d->smem_optin) return fail(-5, "model needs more shared memory than the device offers");
+    GroupKernel k0 = group_kernel_of(g, in_smem);
+    CUDA_OK(cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 1;
+    CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k0, 32 * wpb, smem));
+    if (occ < 1) occ = 1;
+    int grid = (d->dsz.nworld + wpb - 1) / wpb;
+    const int maxgrid = d->nsm * occ;
+    if (grid > maxgrid) grid = maxgrid;
+    c.wpb = wpb;
+    c.grid = grid;
+    c.in_smem = in_smem;
+    c.smem = smem;
+    c.ready = 1;
+  }
+  K.stages = stages;
+  K.scratch_floats = c.scratch_floats;
+  GroupKernel kern = group_kernel_of(g, c.in_smem != 0);
+  const int grid = c.grid, threads = 32 * c.wpb;
+  const size_t smem = c.smem;
+  return timed_launch(stream, [&] { kern<<<grid, threads, smem, stream>>>(K); }, g);
 }
 
 extern "C" int mjb_run_stages(const MjbModel* m, MjbData* d, const MjbOption* opt, uint32_t stages, void* cuda_stream) {
@@ -238,30 +293,14 @@ extern "C" int mjb_run_stages(const MjbModel* m, MjbData* d, const MjbOption* op
     CUDA_OK(cudaMemsetAsync(d->d.nacon, 0, sizeof(int), stream));
     CUDA_OK(cudaMemsetAsync(d->d.ncollision, 0, sizeof(int), stream));
   }
-  if (!d->cfg_ready) {
-    const int wpb = warps_per_block();
-    const size_t scr_bytes = (size_t)wpb * d->scratch_floats * sizeof(float);
-    const bool in_smem = (size_t)m->blob_bytes + 16 + scr_bytes <= (size_t)d->smem_optin && m->blob_bytes <= 96 * 1024;
-    const size_t smem = in_smem ? (size_t)m->blob_bytes + 16 + scr_bytes : scr_bytes;
-    if (smem > (size_t)d->smem_optin) return fail(-5, "model needs more shared memory than the device offers");
-    auto k0 = in_smem ? mjb_pipeline_kernel<true> : mjb_pipeline_kernel<false>;
-    CUDA_OK(cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int occ = 1;
-    CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k0, 32 * wpb, smem));
-    if (occ < 1) occ = 1;
-    int grid = (d->dsz.nworld + wpb - 1) / wpb;
-    const int maxgrid = d->nsm * occ;
-    if (grid > maxgrid) grid = maxgrid;
-    d->cfg_wpb = wpb;
-    d->cfg_grid = grid;
-    d->cfg_in_smem = in_smem;
-    d->cfg_smem = smem;
-    d->cfg_ready = 1;
+  for (int g = 0; g < G_COUNT; g++) {
+    const uint32_t gs = stages & group_mask(g);
+    if (!gs) continue;
+    if (g == G_COL && !opt->run_collision_detection) continue;
+    const int rc = launch_group(g, m, d, K, gs, stream);
+    if (rc) return rc;
   }
-  const int wpb = d->cfg_wpb, grid = d->cfg_grid;
-  const size_t smem = d->cfg_smem;
-  auto kern = d->cfg_in_smem ? mjb_pipeline_kernel<true> : mjb_pipeline_kernel<false>;
-  return timed_launch(stream, [&] { kern<<<grid, 32 * wpb, smem, stream>>>(K); });
+  return 0;
 }
 
 static uint32_t integrator_stage(const MjbOption* opt) {
@@ -296,7 +335,7 @@ extern "C" int mjb_solve_m(const MjbModel* m, MjbData* d, float* x, const float*
   fill_params(K, m, d, &o, 0);
   K.x = x;
   K.y = y;
-  const int wpb = warps_per_block();
+  const int wpb = warps_per_block(4);
   const size_t smem = (size_t)wpb * d->scratch_floats * sizeof(float);
   CUDA_OK(cudaFuncSetAttribute(mjb_solve_m_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = (d->dsz.nworld + wpb - 1) / wpb;
@@ -354,6 +393,22 @@ extern "C" double mjb_timing_ms(void) {
     if (cudaEventElapsedTime(&ms, p.first, p.second) == cudaSuccess) total += ms;
   }
   return total;
+}
+extern "C" double mjb_timing_group_ms(int group) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  double total = 0;
+  for (auto& p : g_events) {
+    if (p.group != group) continue;
+    cudaEventSynchronize(p.second);
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, p.first, p.second) == cudaSuccess) total += ms;
+  }
+  return total;
+}
+extern "C" int mjb_group_count(void) { return G_COUNT; }
+extern "C" const char* mjb_group_name(int group) {
+  static const char* names[G_COUNT] = {"smooth_position", "collision", "make_constraint", "smooth_velocity", "solve", "euler"};
+  return (group >= 0 && group < G_COUNT) ? names[group] : nullptr;
 }
 extern "C" const char* mjb_last_error(void) { return g_err.c_str(); }
 extern "C" const char* mjb_version(void) { return "mjb200 0.1 (sm_100a)"; }

@@ -7,12 +7,37 @@
 #include "mjb_solver.cuh"
 #include "mjb_types.cuh"
 
-__host__ __device__ inline int mjb_scratch_floats(int nv, int nv_pad, int njmax_pad) {
-  int a = solver_scratch_floats(nv, nv_pad, njmax_pad);
-  int c = 64 + 8;  // collision queue
-  int m = a > c ? a : c;
-  return (m + 3) & ~3;
+// The step is issued as one launch per stage GROUP.  Every group is its own kernel instantiation:
+// compact code (the instruction cache holds it while warps drift apart), its own register budget
+// and its own shared-memory scratch.  Intermediate results travel between groups through L2/HBM.
+enum StageGroup { G_POS = 0, G_COL, G_CON, G_VEL, G_SOL, G_EUL, G_COUNT };
+
+__host__ __device__ inline uint32_t group_mask(int g) {
+  switch (g) {
+    case G_POS: return MJB_STAGE_KINEMATICS | MJB_STAGE_COM_POS | MJB_STAGE_CRB | MJB_STAGE_FACTOR_M | MJB_STAGE_TRANSMISSION;
+    case G_COL: return MJB_STAGE_COLLISION;
+    case G_CON: return MJB_STAGE_MAKE_CONSTRAINT;
+    case G_VEL: return MJB_STAGE_ZERO_SENSOR | MJB_STAGE_FWD_VELOCITY | MJB_STAGE_FWD_ACTUATION | MJB_STAGE_FWD_ACCELERATION | MJB_STAGE_FWD_ACC_FACTOR;
+    case G_SOL: return MJB_STAGE_SOLVE;
+    case G_EUL: return MJB_STAGE_EULER;
+  }
+  return 0;
 }
+
+// per-warp shared-memory scratch (floats) of a group
+__host__ __device__ inline int group_scratch_floats(int g, int nv, int nv_pad, int njmax_pad) {
+  int n = 0;
+  switch (g) {
+    case G_POS:
+    case G_VEL:
+    case G_EUL: n = chol_scratch_floats(nv, nv_pad); break;
+    case G_COL: n = 64 + 8; break;
+    case G_CON: n = 0; break;
+    case G_SOL: n = solver_scratch_floats(nv, nv_pad, njmax_pad); break;
+  }
+  return (n + 3) & ~3;
+}
+__host__ __device__ inline bool group_uses_blob(int g) { return g != G_SOL; }
 
 // Stages the model blob into shared memory with one TMA bulk copy (cp.async.bulk, completion on
 // an mbarrier).  All threads of the CTA wait on the barrier's phase 0.
@@ -42,8 +67,8 @@ __device__ __forceinline__ void stage_model_blob(unsigned char* dst, const unsig
   }
 }
 
-template <bool BLOB_IN_SMEM>
-__global__ void __launch_bounds__(256) mjb_pipeline_kernel(const __grid_constant__ KParams K) {
+template <int G, bool BLOB_IN_SMEM>
+__global__ void __launch_bounds__(256) mjb_group_kernel(const __grid_constant__ KParams K) {
   extern __shared__ __align__(16) unsigned char smem[];
   const unsigned char* mb;
   float* scr_base;
@@ -60,22 +85,28 @@ __global__ void __launch_bounds__(256) mjb_pipeline_kernel(const __grid_constant
   float* scr = scr_base + (size_t)warp * K.scratch_floats;
   const uint32_t st = K.stages;
   for (int w = blockIdx.x * wpb + warp; w < K.dsz.nworld; w += gridDim.x * wpb) {
-    if (st & MJB_STAGE_KINEMATICS) s_kinematics(K, mb, w, lane);
-    if (st & MJB_STAGE_COM_POS) s_com_pos(K, mb, w, lane);
-    if (st & MJB_STAGE_CRB) s_crb(K, mb, w, lane);
-    if (st & MJB_STAGE_FACTOR_M) s_factor_m(K, w, lane, scr);
-    if ((st & MJB_STAGE_COLLISION) && K.o.run_collision_detection) s_collision(K, mb, w, lane, reinterpret_cast<int*>(scr));
-    if (st & MJB_STAGE_MAKE_CONSTRAINT) s_make_constraint(K, mb, w, lane);
-    if (st & MJB_STAGE_TRANSMISSION) s_transmission(K, mb, w, lane);
-    if (st & MJB_STAGE_ZERO_SENSOR) {
-      if (lane < 2) DW(energy)[lane] = 0.f;
+    if constexpr (G == G_POS) {
+      if (st & MJB_STAGE_KINEMATICS) s_kinematics(K, mb, w, lane);
+      if (st & MJB_STAGE_COM_POS) s_com_pos(K, mb, w, lane);
+      if (st & MJB_STAGE_CRB) s_crb(K, mb, w, lane);
+      if (st & MJB_STAGE_FACTOR_M) s_factor_m(K, w, lane, scr);
+      if (st & MJB_STAGE_TRANSMISSION) s_transmission(K, mb, w, lane);
+    } else if constexpr (G == G_COL) {
+      if (K.o.run_collision_detection) s_collision(K, mb, w, lane, reinterpret_cast<int*>(scr));
+    } else if constexpr (G == G_CON) {
+      s_make_constraint(K, mb, w, lane);
+    } else if constexpr (G == G_VEL) {
+      if (st & MJB_STAGE_ZERO_SENSOR) {
+        if (lane < 2) DW(energy)[lane] = 0.f;
+      }
+      if (st & MJB_STAGE_FWD_VELOCITY) s_fwd_velocity(K, mb, w, lane);
+      if (st & MJB_STAGE_FWD_ACTUATION) s_fwd_actuation(K, mb, w, lane);
+      if (st & (MJB_STAGE_FWD_ACCELERATION | MJB_STAGE_FWD_ACC_FACTOR)) s_fwd_acceleration(K, mb, w, lane, scr, (st & MJB_STAGE_FWD_ACC_FACTOR) != 0);
+    } else if constexpr (G == G_SOL) {
+      s_solve(K, mb, w, lane, scr);
+    } else {
+      s_euler(K, mb, w, lane, scr);
     }
-    if (st & MJB_STAGE_FWD_VELOCITY) s_fwd_velocity(K, mb, w, lane);
-    if (st & MJB_STAGE_FWD_ACTUATION) s_fwd_actuation(K, mb, w, lane);
-    if (st & MJB_STAGE_FWD_ACCELERATION) s_fwd_acceleration(K, mb, w, lane, scr, false);
-    if (st & MJB_STAGE_FWD_ACC_FACTOR) s_fwd_acceleration(K, mb, w, lane, scr, true);
-    if (st & MJB_STAGE_SOLVE) s_solve(K, mb, w, lane, scr);
-    if (st & MJB_STAGE_EULER) s_euler(K, mb, w, lane, scr);
   }
 }
 
@@ -84,10 +115,12 @@ __global__ void __launch_bounds__(256) mjb_solve_m_kernel(const __grid_constant_
   extern __shared__ __align__(16) unsigned char smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
   float* scr = reinterpret_cast<float*>(smem) + (size_t)warp * K.scratch_floats;
-  const int nv = K.ms.nv, ld = chol_ld(K.ms.nv_pad);
+  const int nv = K.ms.nv;
+  const CholScr c = chol_scr(scr, nv, K.ms.nv_pad);
+  const int ld = c.ld;
+  float* x = c.x;
   for (int w = blockIdx.x * wpb + warp; w < K.dsz.nworld; w += gridDim.x * wpb) {
     load_rows(scr, ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
-    float* x = scr + nv * ld;
     for (int i = lane; i < nv; i += 32) x[i] = K.y[(size_t)w * nv + i];
     __syncwarp();
     warp_chol_solve(scr, ld, nv, x, lane);

@@ -221,6 +221,19 @@ __device__ __forceinline__ void s_crb(const KParams& K, const unsigned char* mb,
 // bank-conflict free.
 // ---------------------------------------------------------------------------------------------
 __host__ __device__ inline int chol_ld(int nv_pad) { return ((nv_pad >> 2) & 1) ? nv_pad : nv_pad + 4; }
+// compact scratch of the stages that only factor / solve with one matrix: L (nv x ld) | x (nv_pad)
+struct CholScr {
+  float *L, *x;
+  int ld;
+};
+__host__ __device__ inline int chol_scratch_floats(int nv, int nv_pad) { return nv * chol_ld(nv_pad) + nv_pad; }
+__device__ __forceinline__ CholScr chol_scr(float* scr, int nv, int nvp) {
+  CholScr c;
+  c.ld = chol_ld(nvp);
+  c.L = scr;
+  c.x = scr + nv * c.ld;
+  return c;
+}
 struct SolverScr {
   float *H, *L, *x, *grad, *search, *mv, *qacc, *Ma, *qfs, *Jaref, *jv, *D, *coef, *force;
   int ld;
@@ -345,7 +358,7 @@ __device__ __forceinline__ void store_qLD(const KParams& K, int w, int lane, con
 
 // smooth.factor_m dense (smooth.py:1091-1109): qLD = chol(qM).
 __device__ __forceinline__ void s_factor_m(const KParams& K, int w, int lane, float* scr) {
-  const SolverScr s = solver_scr(scr, K.ms.nv, K.ms.nv_pad, K.dsz.njmax_pad);
+  const CholScr s = chol_scr(scr, K.ms.nv, K.ms.nv_pad);
   load_rows(s.L, s.ld, DW(qM), K.ms.nv_pad, K.ms.nv, lane, nullptr, 0.f);
   warp_cholesky(s.L, s.ld, K.ms.nv, lane);
   store_qLD(K, w, lane, s.L, s.ld);
@@ -589,10 +602,9 @@ __device__ __forceinline__ void s_fwd_actuation(const KParams& K, const unsigned
 }
 
 // forward.fwd_acceleration (forward.py:931-969) + support.apply_ft (support.py:175-216).
-// Leaves chol(qM) in the scratch L slot.
 __device__ __forceinline__ void s_fwd_acceleration(const KParams& K, const unsigned char* mb, int w, int lane, float* scr, bool factorize) {
   const int nv = K.ms.nv;
-  const SolverScr s = solver_scr(scr, nv, K.ms.nv_pad, K.dsz.njmax_pad);
+  const CholScr s = chol_scr(scr, nv, K.ms.nv_pad);
   float* x = s.x;
   const float* xfrc = DW(xfrc_applied);
   for (int i = lane; i < nv; i += 32) {
@@ -625,7 +637,7 @@ __device__ __forceinline__ void s_fwd_acceleration(const KParams& K, const unsig
 // forward.euler (forward.py:327-354) + _advance (:213-274).
 __device__ __forceinline__ void s_euler(const KParams& K, const unsigned char* mb, int w, int lane, float* scr) {
   const int nv = K.ms.nv;
-  const SolverScr s = solver_scr(scr, nv, K.ms.nv_pad, K.dsz.njmax_pad);
+  const CholScr s = chol_scr(scr, nv, K.ms.nv_pad);
   const float dt = K.o.timestep;
   float* x = s.x;
   const bool damp = !(K.o.disableflags & (DSBL_EULERDAMP | DSBL_DAMPER));

@@ -280,14 +280,12 @@ __device__ __forceinline__ void s_solve(const KParams& K, const unsigned char* m
   float cost, gauss, prev_cost;
   bool any_change;
   update_constraint(K, w, lane, s, nefc, ne, nf, true, cost, gauss, any_change);
-  // chol(qM) is already in s.L when fwd_acceleration ran for this world in the same launch
-  const bool l_is_chol_m = (K.stages & (MJB_STAGE_FWD_ACCELERATION | MJB_STAGE_FWD_ACC_FACTOR)) != 0;
   if (newton) {
     load_rows(s.H, s.ld, DW(qM), np, nv, lane, nullptr, 0.f);
     if (any_change) h_accumulate(K, w, lane, s, nefc);
-    solve_direction(K, lane, s, any_change || !l_is_chol_m);
+    solve_direction(K, lane, s, true);
   } else {
-    if (!l_is_chol_m) load_rows(s.L, s.ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
+    load_rows(s.L, s.ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
     solve_direction(K, lane, s, false);
   }
   float grad_dot = 0.f, search_dot = 0.f;
