@@ -25,6 +25,42 @@ sys.path.insert(0, ROOT)
 HUMANOID = os.path.join(ROOT, "benchmarks", "humanoid", "humanoid.xml")
 NCONMAX, NJMAX = 24, 64  # reference benchmarks/config.txt:23
 ALG_BYTES_PER_ENV_STEP = 32000  # contract traffic of one humanoid env-step
+# Algorithmic traffic of each stage-group kernel: Data fields it must read (produced by an earlier
+# kernel or the caller) and fields it defines, write-once/read-once, capacity-sized for the pooled /
+# padded arrays (DESIGN.md "Roofline accounting").  bytes/world = 4 x sum of per-world element counts.
+GROUP_IO = {
+  "smooth_position": (["qpos"],
+                      ["xpos", "xquat", "xmat", "xipos", "ximat", "xanchor", "xaxis", "geom_xpos", "geom_xmat", "site_xpos", "site_xmat",
+                       "subtree_com", "cdof", "cinert", "crb", "qM", "actuator_length", "actuator_moment"]),
+  "collision": (["geom_xpos", "geom_xmat"],
+                ["contact_dist", "contact_pos", "contact_frame", "contact_includemargin", "contact_friction", "contact_solref",
+                 "contact_solreffriction", "contact_solimp", "contact_dim", "contact_geom", "contact_worldid", "contact_type",
+                 "contact_geomcollisionid"]),
+  "make_constraint": (["qpos", "qvel", "cdof", "subtree_com", "contact_dist", "contact_pos", "contact_frame", "contact_includemargin",
+                       "contact_friction", "contact_solref", "contact_solimp", "contact_dim", "contact_geom"],
+                      ["efc_J", "efc_pos", "efc_margin", "efc_D", "efc_vel", "efc_aref", "efc_frictionloss", "efc_type", "efc_id",
+                       "contact_efc_address"]),
+  "smooth_velocity": (["qpos", "qvel", "ctrl", "act", "cdof", "cinert", "qM", "actuator_length", "actuator_moment", "qfrc_applied",
+                       "xfrc_applied", "xipos", "subtree_com"],
+                      ["actuator_velocity", "cvel", "cdof_dot", "qfrc_spring", "qfrc_damper", "qfrc_passive", "qfrc_bias", "cacc",
+                       "cfrc_int", "actuator_force", "qfrc_actuator", "act_dot", "qfrc_smooth", "qacc_smooth", "qLD"]),
+  "solve": (["efc_J", "efc_D", "efc_aref", "efc_frictionloss", "qM", "qacc_warmstart", "qfrc_smooth", "qacc_smooth"],
+            ["efc_force", "efc_state", "qfrc_constraint", "qacc", "efc_Ma", "solver_niter"]),
+  "euler": (["qM", "efc_Ma", "qacc", "qpos", "qvel", "act", "act_dot"], ["qpos", "qvel", "act", "qacc_warmstart", "time"]),
+}
+
+
+def group_alg_bytes(d, nworld):
+  """Algorithmic bytes per world of every stage-group kernel (see GROUP_IO)."""
+  out = {}
+  for g, (rd, wr) in GROUP_IO.items():
+    n = 0
+    for name in rd + wr:
+      n += d.field(name).numel() * d.field(name).element_size()
+    out[g] = n / nworld
+  return out
+
+
 METRIC = "humanoid env-steps/sec at nworld=8192, 1/2/4/8 B200; % of HBM roofline"
 
 
@@ -208,7 +244,8 @@ def main():
     for _ in range(nk):
       one_step()
     stream.synchronize()
-    kernel_ms = lib.mjb_timing_ms() / max(lib.mjb_timing_launches(), 1)
+    group_ms = {lib.mjb_group_name(g).decode(): lib.mjb_timing_group_ms(g) / nk for g in range(lib.mjb_group_count())}
+    kernel_ms = lib.mjb_timing_ms() / nk  # all kernels of one step
     lib.mjb_timing_enable(0)
     lib.mjb_timing_reset()
 
@@ -270,20 +307,25 @@ def main():
 
   nan_worlds = int(torch.isnan(d.qpos).any(dim=1).sum())
   status = int(torch.bitwise_or(d.status, torch.zeros_like(d.status)).max()) if nworld else 0
-  t = torch.tensor([ms, e2e_s * 1e3, kernel_ms], dtype=torch.float64, device="cuda")
+  gnames = list(group_ms)
+  t = torch.tensor([ms, e2e_s * 1e3, kernel_ms] + [group_ms[g] for g in gnames], dtype=torch.float64, device="cuda")
   if dist is not None:
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     # optional observation gather over NVLink (the only collective of the path; outside timing)
     obs = torch.cat([d.qpos, d.qvel], dim=1)
     gathered = torch.empty((world * nworld, obs.shape[1]), dtype=obs.dtype, device="cuda")
     dist.all_gather_into_tensor(gathered, obs)
-  ms, e2e_ms, kernel_ms = [float(x) for x in t.tolist()]
+  ms, e2e_ms, kernel_ms = [float(x) for x in t.tolist()[:3]]
+  group_ms = {g: float(x) for g, x in zip(gnames, t.tolist()[3:])}
 
   if rank == 0:
     peak, peak_src = _peaks()
     value = world * nworld * K / (ms * 1e-3)
     e2e_value = world * nworld * Ke / (e2e_ms * 1e-3)
-    achieved = ALG_BYTES_PER_ENV_STEP * nworld / (kernel_ms * 1e-3) / 1e9
+    gbytes = group_alg_bytes(d, nworld)
+    dom = max(group_ms, key=lambda g: group_ms[g])  # the dominant kernel of the step
+    achieved = gbytes[dom] * nworld / (group_ms[dom] * 1e-3) / 1e9
+    step_achieved = ALG_BYTES_PER_ENV_STEP * nworld / (kernel_ms * 1e-3) / 1e9
     out = {
       "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K, "warmup": W,
       "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -299,8 +341,13 @@ def main():
               "steps": Ke},
       "gpu_launches": int(gpu_launches),
       "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                   "kernel": "mjb_pipeline_kernel", "kernel_ms": kernel_ms, "alg_bytes_per_launch": ALG_BYTES_PER_ENV_STEP * nworld,
-                   "peak_source": peak_src},
+                   "kernel": f"mjb_group_kernel<{dom}>", "kernel_ms": group_ms[dom], "share_of_step": group_ms[dom] / kernel_ms,
+                   "alg_bytes_per_launch": gbytes[dom] * nworld, "peak_source": peak_src,
+                   "step": {"kernels_ms": kernel_ms, "alg_bytes_per_env_step": ALG_BYTES_PER_ENV_STEP, "achieved": step_achieved,
+                            "frac": step_achieved / peak},
+                   "groups": {g: {"ms": group_ms[g], "alg_bytes_per_world": gbytes[g],
+                                  "frac": gbytes[g] * nworld / (group_ms[g] * 1e-3) / 1e9 / peak if group_ms[g] > 0 else None}
+                              for g in gnames}},
     }  # fmt: skip
     if not args.no_cpu_baseline and world == 1:
       out["cpu_baseline"] = cpu_baseline(os.cpu_count() or 1)

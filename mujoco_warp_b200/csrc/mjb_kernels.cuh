@@ -81,7 +81,9 @@ __global__ void __launch_bounds__(256) mjb_group_kernel(const __grid_constant__ 
     mb = K.blob;
     scr_base = reinterpret_cast<float*>(smem);
   }
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  // broadcast from lane 0 so that the compiler can treat the warp index (and every loop / branch
+  // that depends on it) as warp-uniform
+  const int lane = threadIdx.x & 31, warp = __shfl_sync(FULL, threadIdx.x >> 5, 0), wpb = blockDim.x >> 5;
   float* scr = scr_base + (size_t)warp * K.scratch_floats;
   const uint32_t st = K.stages;
   for (int w = blockIdx.x * wpb + warp; w < K.dsz.nworld; w += gridDim.x * wpb) {

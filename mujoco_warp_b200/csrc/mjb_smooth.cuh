@@ -269,7 +269,7 @@ __device__ __forceinline__ float chol_row_dot(const float* ri, const float* rj, 
   for (int k = j4 << 2; k < j; k++) s -= ri[k] * rj[k];
   return s;
 }
-__device__ __forceinline__ void warp_cholesky(float* A, int ld, int n, int lane) {
+__device__ __noinline__ void warp_cholesky_smem(float* A, int ld, int n, int lane) {
   const int i0 = lane, i1 = lane + 32;
   for (int j = 0; j < n; j++) {
     const float* rj = A + j * ld;
@@ -285,7 +285,7 @@ __device__ __forceinline__ void warp_cholesky(float* A, int ld, int n, int lane)
 }
 
 // x <- (L L^T)^-1 x with L in shared memory, x in shared memory (n <= 64).
-__device__ __forceinline__ void warp_chol_solve(const float* L, int ld, int n, float* x, int lane) {
+__device__ __noinline__ void warp_chol_solve_smem(const float* L, int ld, int n, float* x, int lane) {
   const int i0 = lane, i1 = lane + 32;
   float x0 = i0 < n ? x[i0] : 0.f, x1 = i1 < n ? x[i1] : 0.f;
   const float d0 = i0 < n ? 1.0f / L[i0 * ld + i0] : 1.f, d1 = i1 < n ? 1.0f / L[i1 * ld + i1] : 1.f;
@@ -319,6 +319,98 @@ __device__ __forceinline__ void warp_chol_solve(const float* L, int ld, int n, f
   if (i0 < n) x[i0] = x0;
   if (i1 < n) x[i1] = x1;
   __syncwarp();
+}
+
+// Register-resident variants for n <= 32 (N = n rounded up to a multiple of 4, compile time):
+// lane i owns row i of the matrix in registers; the padded rows/columns are the identity, so the
+// fully unrolled loops need no bounds tests.  Right-looking: column j is scaled, broadcast lane by
+// lane with shuffles and subtracted from the trailing rows (n^2/2 shuffle+FMA pairs, no shared-memory
+// traffic besides one 128-bit row load and store per lane).
+template <int N>
+__device__ __noinline__ void warp_cholesky_reg(float* A, int ld, int n, int lane) {
+  float r[N];
+  const bool in = lane < n;
+  const float4* row4 = reinterpret_cast<const float4*>(A + (in ? lane : 0) * ld);
+#pragma unroll
+  for (int q = 0; q < N / 4; q++) {
+    const float4 v = row4[q];
+    r[4 * q] = v.x; r[4 * q + 1] = v.y; r[4 * q + 2] = v.z; r[4 * q + 3] = v.w;
+  }
+#pragma unroll
+  for (int k = 0; k < N; k++) {
+    if (!in) r[k] = (k == lane) ? 1.0f : 0.0f;
+    if (k >= N - 4 && k >= n) r[k] = (k == lane) ? 1.0f : 0.0f;
+  }
+#pragma unroll
+  for (int j = 0; j < N; j++) {
+    const float ajj = __shfl_sync(FULL, r[j], j);
+    const float lij = r[j] * rsqrtf(fmaxf(ajj, MJ_MINVAL));
+    r[j] = lij;
+#pragma unroll
+    for (int k = j + 1; k < N; k++) r[k] -= lij * __shfl_sync(FULL, lij, k);
+  }
+  if (in) {
+    float4* out4 = reinterpret_cast<float4*>(A + lane * ld);
+#pragma unroll
+    for (int q = 0; q < N / 4; q++) out4[q] = make_float4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]);
+  }
+  __syncwarp();
+}
+
+template <int N>
+__device__ __noinline__ void warp_chol_solve_reg(const float* L, int ld, int n, float* x, int lane) {
+  float r[N], c[N];  // r = row `lane` of L left of the diagonal, c = column `lane` of L below it
+  const bool in = lane < n;
+  const int i = in ? lane : 0;
+  const float4* row4 = reinterpret_cast<const float4*>(L + i * ld);
+#pragma unroll
+  for (int q = 0; q < N / 4; q++) {
+    const float4 v = row4[q];
+    r[4 * q] = v.x; r[4 * q + 1] = v.y; r[4 * q + 2] = v.z; r[4 * q + 3] = v.w;
+  }
+#pragma unroll
+  for (int j = 0; j < N; j++) {
+    r[j] = (j < lane && in) ? r[j] : 0.f;
+    c[j] = (j > lane && j < n) ? L[j * ld + i] : 0.f;
+  }
+  float xi = in ? x[lane] : 0.f;
+  const float dinv = in ? 1.0f / L[i * ld + i] : 0.f;
+  // forward L y = b: lane i accumulates b_i - sum_{k<i} L_ik y_k; y_k = that * dinv_k is broadcast
+#pragma unroll
+  for (int j = 0; j < N; j++) xi = fmaf(-r[j], __shfl_sync(FULL, xi * dinv, j), xi);
+  xi *= dinv;
+  // backward L^T x = y
+#pragma unroll
+  for (int j = N - 1; j >= 0; j--) xi = fmaf(-c[j], __shfl_sync(FULL, xi * dinv, j), xi);
+  if (in) x[lane] = xi * dinv;
+  __syncwarp();
+}
+
+__device__ __forceinline__ void warp_cholesky(float* A, int ld, int n, int lane) {
+  switch ((n + 3) >> 2) {
+    case 1: warp_cholesky_reg<4>(A, ld, n, lane); break;
+    case 2: warp_cholesky_reg<8>(A, ld, n, lane); break;
+    case 3: warp_cholesky_reg<12>(A, ld, n, lane); break;
+    case 4: warp_cholesky_reg<16>(A, ld, n, lane); break;
+    case 5: warp_cholesky_reg<20>(A, ld, n, lane); break;
+    case 6: warp_cholesky_reg<24>(A, ld, n, lane); break;
+    case 7: warp_cholesky_reg<28>(A, ld, n, lane); break;
+    case 8: warp_cholesky_reg<32>(A, ld, n, lane); break;
+    default: warp_cholesky_smem(A, ld, n, lane); break;
+  }
+}
+__device__ __forceinline__ void warp_chol_solve(const float* L, int ld, int n, float* x, int lane) {
+  switch ((n + 3) >> 2) {
+    case 1: warp_chol_solve_reg<4>(L, ld, n, x, lane); break;
+    case 2: warp_chol_solve_reg<8>(L, ld, n, x, lane); break;
+    case 3: warp_chol_solve_reg<12>(L, ld, n, x, lane); break;
+    case 4: warp_chol_solve_reg<16>(L, ld, n, x, lane); break;
+    case 5: warp_chol_solve_reg<20>(L, ld, n, x, lane); break;
+    case 6: warp_chol_solve_reg<24>(L, ld, n, x, lane); break;
+    case 7: warp_chol_solve_reg<28>(L, ld, n, x, lane); break;
+    case 8: warp_chol_solve_reg<32>(L, ld, n, x, lane); break;
+    default: warp_chol_solve_smem(L, ld, n, x, lane); break;
+  }
 }
 
 // copies the n leading rows of a global matrix (ld_src) into shared memory (ld); rows are copied

@@ -187,7 +187,7 @@ __device__ __forceinline__ void linesearch(const KParams& K, int w, int lane, co
   const float lo_alpha_in = -safe_div(p0.g, p0.h);
   Pt3 lo_in = warp_sum(ls_rows(K, w, lane, s, nefc, ne, nf, lo_alpha_in)) + eval_pt_quad(q0, q1, q2, lo_alpha_in);
   float alpha;
-  if (fabsf(lo_in.g) < gtol && lo_in.c < p0.c) {
+  if (uniform_b(fabsf(lo_in.g) < gtol && lo_in.c < p0.c)) {
     alpha = lo_alpha_in;
   } else {
     alpha = 0.f;
@@ -226,7 +226,7 @@ __device__ __forceinline__ void linesearch(const KParams& K, int w, int lane, co
       const bool ls_done = (!swap_lo && !swap_hi) || (lo.g < 0.f && lo.g > -gtol) || (hi.g > 0.f && hi.g < gtol);
       const bool improved = lo.c < p0.c || hi.c < p0.c, lo_better = lo.c < hi.c;
       if (improved) alpha = lo_better ? lo_alpha : hi_alpha;
-      if (ls_done) break;
+      if (uniform_b(ls_done)) break;
     }
   }
   for (int i = lane; i < nv; i += 32) {
@@ -262,7 +262,7 @@ __device__ __forceinline__ void s_solve(const KParams& K, const unsigned char* m
     return;
   }
   const SolverScr s = solver_scr(scr, nv, np, K.dsz.njmax_pad);
-  const int nefc = min(DW(nefc)[0], njmax), ne = DW(ne)[0], nf = DW(nf)[0];
+  const int nefc = uniform_i(min(DW(nefc)[0], njmax)), ne = uniform_i(DW(ne)[0]), nf = uniform_i(DW(nf)[0]);
   const bool newton = K.o.solver == SOLVER_NEWTON;
   const float* src = (K.o.disableflags & DSBL_WARMSTART) ? DW(qacc_smooth) : DW(qacc_warmstart);
   for (int i = lane; i < np; i += 32) {
@@ -277,50 +277,41 @@ __device__ __forceinline__ void s_solve(const KParams& K, const unsigned char* m
   for (int r = lane; r < nefc; r += 32) s.Jaref[r] = row_dot(DW(efc_J) + (size_t)r * np, s.qacc, n4) - DW(efc_aref)[r];
   for (int i = lane; i < nv; i += 32) s.Ma[i] = row_dot(DW(qM) + (size_t)i * np, s.qacc, n4);
   __syncwarp();
-  float cost, gauss, prev_cost;
-  bool any_change;
-  update_constraint(K, w, lane, s, nefc, ne, nf, true, cost, gauss, any_change);
-  if (newton) {
-    load_rows(s.H, s.ld, DW(qM), np, nv, lane, nullptr, 0.f);
-    if (any_change) h_accumulate(K, w, lane, s, nefc);
-    solve_direction(K, lane, s, true);
-  } else {
-    load_rows(s.L, s.ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
-    solve_direction(K, lane, s, false);
-  }
-  float grad_dot = 0.f, search_dot = 0.f;
-  for (int i = lane; i < nv; i += 32) {
-    const float v = -s.x[i];
-    s.search[i] = v;
-    search_dot += v * v;
-  }
-  search_dot = warp_sum(search_dot);
-  __syncwarp();
+  // Newton: H starts as qM.  CG: the preconditioner is the factor of qM (qLD).
+  load_rows(newton ? s.H : s.L, s.ld, newton ? DW(qM) : DW(qLD), newton ? np : nv, nv, lane, nullptr, 0.f);
+  float cost = 0.f, gauss = 0.f, prev_cost = 0.f, search_dot = 0.f;
   const float scl = 1.0f / (K.o.meaninertia * (float)nv);
-  float* prev_grad = s.H;            // CG only (H is unused by CG)
+  float* prev_grad = s.H;  // CG only (H is unused by CG)
   float* prev_Mgrad = s.H + np;
   int niter = 0;
-  for (int it = 0; it < K.o.iterations; it++) {  // _solver_iteration, solver.py:3188
-    linesearch(K, w, lane, s, nefc, ne, nf, gauss, search_dot);
-    if (!newton) {
-      for (int i = lane; i < nv; i += 32) { prev_grad[i] = s.grad[i]; prev_Mgrad[i] = s.x[i]; }
-      __syncwarp();
+  // Pass 0 is solver.py:3257 init_context (constraint update, gradient, first search direction);
+  // passes 1.. are solver.py:3188 _solver_iteration.  One loop body keeps a single copy of every
+  // routine in the instruction stream.
+  for (int it = 0; it <= K.o.iterations; it++) {
+    const bool init = it == 0;
+    if (!init) {
+      linesearch(K, w, lane, s, nefc, ne, nf, gauss, search_dot);
+      if (!newton) {
+        for (int i = lane; i < nv; i += 32) { prev_grad[i] = s.grad[i]; prev_Mgrad[i] = s.x[i]; }
+        __syncwarp();
+      }
+      prev_cost = cost;
     }
-    prev_cost = cost;
-    update_constraint(K, w, lane, s, nefc, ne, nf, false, cost, gauss, any_change);
+    bool any_change;
+    update_constraint(K, w, lane, s, nefc, ne, nf, init, cost, gauss, any_change);
     if (newton && any_change) h_accumulate(K, w, lane, s, nefc);
-    solve_direction(K, lane, s, newton && any_change);
+    solve_direction(K, lane, s, newton && (any_change || init));
     float beta = 0.f;
-    if (!newton) {  // Polak-Ribiere, solver.py:3081
+    if (!newton && !init) {  // Polak-Ribiere, solver.py:3081
       float num = 0.f, den = 0.f;
       for (int i = lane; i < nv; i += 32) { num += s.grad[i] * (s.x[i] - prev_Mgrad[i]); den += prev_grad[i] * prev_Mgrad[i]; }
       beta = fmaxf(0.f, warp_sum(num) / fmaxf(MJ_MINVAL, warp_sum(den)));
     }
-    grad_dot = 0.f;
+    float grad_dot = 0.f;
     search_dot = 0.f;
     for (int i = lane; i < nv; i += 32) {
       float v = -s.x[i];
-      if (!newton) v += beta * s.search[i];
+      if (!newton && !init) v += beta * s.search[i];
       s.search[i] = v;
       search_dot += v * v;
       grad_dot += s.grad[i] * s.grad[i];
@@ -328,9 +319,10 @@ __device__ __forceinline__ void s_solve(const KParams& K, const unsigned char* m
     search_dot = warp_sum(search_dot);
     grad_dot = warp_sum(grad_dot);
     __syncwarp();
+    if (init) continue;
     niter++;
     const float improvement = (prev_cost - cost) * scl, gradient = sqrtf(grad_dot) * scl;  // solver.py:3177
-    if (improvement < K.o.tolerance || gradient < K.o.tolerance) break;
+    if (uniform_b(improvement < K.o.tolerance || gradient < K.o.tolerance)) break;
   }
   for (int i = lane; i < nv; i += 32) {
     const float q = s.qacc[i];

@@ -257,6 +257,12 @@ __device__ __forceinline__ M3 make_frame(V3 a) {
 }
 
 // warp helpers
+// Broadcast from lane 0: tells the compiler that a value that is equal on all lanes by construction
+// (a load from a warp-uniform address, the result of a full reduction) is warp-uniform, so branches
+// on it need no divergence handling.
+__device__ __forceinline__ int uniform_i(int v) { return __shfl_sync(FULL, v, 0); }
+__device__ __forceinline__ bool uniform_b(bool v) { return __shfl_sync(FULL, v ? 1 : 0, 0) != 0; }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
