@@ -1522,3 +1522,35 @@ void mjo_mul_m(int nv, int nv_pad, const double* qM, const double* vec, double* 
   }
 }
 void mjo_solve_m(int nv, const double* qLD, const double* y, double* x) { chol_solve(x, qLD, nv, y, nv); }
+
+/* math.py:285-314 closest_segment_to_segment_points (pinned by the reference's math_test.py:27-95) */
+void mjo_closest_segment_to_segment_points(const double* a0, const double* a1, const double* b0, const double* b1, double* best_a,
+                                           double* best_b) {
+  double da[3], db[3], am[3], bm[3], tr[3], la, lb;
+  for (int i = 0; i < 3; i++) { da[i] = a1[i] - a0[i]; db[i] = b1[i] - b0[i]; }
+  la = sqrt(da[0] * da[0] + da[1] * da[1] + da[2] * da[2]);
+  lb = sqrt(db[0] * db[0] + db[1] * db[1] + db[2] * db[2]);
+  if (la != 0.0) for (int i = 0; i < 3; i++) da[i] /= la; /* math.py:261-265 */
+  if (lb != 0.0) for (int i = 0; i < 3; i++) db[i] /= lb;
+  const double ha = 0.5 * la, hb = 0.5 * lb;
+  for (int i = 0; i < 3; i++) { am[i] = a0[i] + da[i] * ha; bm[i] = b0[i] + db[i] * hb; tr[i] = am[i] - bm[i]; }
+  const double ab = da[0] * db[0] + da[1] * db[1] + da[2] * db[2];
+  const double at = da[0] * tr[0] + da[1] * tr[1] + da[2] * tr[2];
+  const double bt = db[0] * tr[0] + db[1] * tr[1] + db[2] * tr[2];
+  const double denom = 1.0 - ab * ab;
+  const double ota = (-at + ab * bt) / (denom + 1e-6), otb = bt + ota * ab;
+  const double ta = ota < -ha ? -ha : (ota > ha ? ha : ota), tb = otb < -hb ? -hb : (otb > hb ? hb : otb);
+  double pa[3], pb[3], na[3], nb[3], d1 = 0.0, d2 = 0.0;
+  for (int i = 0; i < 3; i++) { pa[i] = am[i] + da[i] * ta; pb[i] = bm[i] + db[i] * tb; }
+  closest_segment_point(na, a0, a1, pb);
+  closest_segment_point(nb, b0, b1, pa);
+  for (int i = 0; i < 3; i++) { d1 += (pb[i] - na[i]) * (pb[i] - na[i]); d2 += (pa[i] - nb[i]) * (pa[i] - nb[i]); }
+  if (d1 < d2) { memcpy(best_a, na, sizeof(na)); memcpy(best_b, pb, sizeof(pb)); }
+  else { memcpy(best_a, pa, sizeof(pa)); memcpy(best_b, nb, sizeof(nb)); }
+}
+/* math.py:322-333 (pinned by math_test.py:97-126) */
+int mjo_upper_tri_index(int n, int i, int j) { return (i * (2 * n - i - 3)) / 2 + j - 1; }
+int mjo_upper_trid_index(int n, int i, int j) {
+  if (j < i) { int t = i; i = j; j = t; }
+  return (i * (2 * n - i - 1)) / 2 + j;
+}

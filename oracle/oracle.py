@@ -42,7 +42,7 @@ def build(force: bool = False) -> str:
   hdr = os.path.join(os.path.dirname(_HERE), "include", "mjb_fields.h")
   if not force and os.path.exists(LIB) and os.path.getmtime(LIB) >= max(os.path.getmtime(SRC), os.path.getmtime(hdr)):
     return LIB
-  cmd = ["gcc", "-O3", "-march=native", "-fPIC", "-shared", "-fopenmp", "-o", LIB, SRC, "-lm"]
+  cmd = ["gcc", "-O3", "-march=x86-64-v3", "-fPIC", "-shared", "-fopenmp", "-o", LIB, SRC, "-lm"]
   res = subprocess.run(cmd, capture_output=True, text=True)
   if res.returncode != 0:
     raise RuntimeError("gcc failed:\n" + res.stderr)

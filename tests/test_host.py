@@ -1,0 +1,172 @@
+"""Host-side logic (no GPU): MJCF-lite compiler, put_model derived tables, make_data sizing and argument
+validation (same exception types as the reference, io.py:100-144 and :893-918), put_data /
+get_data_into / reset_data on host tensors."""
+
+import numpy as np
+import pytest
+import torch
+
+import mujoco_warp_b200 as mjw
+from mujoco_warp_b200 import constants as C
+from mujoco_warp_b200 import io as mio
+from mujoco_warp_b200 import types
+
+
+def test_humanoid_sizes(humanoid):
+  m = humanoid
+  assert (m.nq, m.nv, m.nu, m.nbody, m.njnt, m.ngeom) == (28, 27, 21, 17, 22, 20)
+  assert m.nkey >= 1 and np.asarray(m.key_qpos).shape[1] == 28
+  assert abs(float(np.sum(m.body_mass)) - 40.84) < 0.01
+
+
+def test_put_model_derived_tables(humanoid):
+  m = mjw.put_model(humanoid, device="cpu")
+  s = m.sizes
+  assert s["nv_pad"] == 28 and s["nlevel"] == 7
+  assert s["nxn"] == 161  # 190 geom pairs - same body - parent/child (reference io.py:270-358)
+  hm = m._host
+  # DFS pre-order: every body's subtree is the id range [b, subtreeend[b])
+  end = hm.ints["body_subtreeend"]
+  parent = hm.ints["body_parentid"]
+  for b in range(1, s["nbody"]):
+    assert parent[b] < b and end[parent[b]] >= end[b] > b
+  # tree levels partition the bodies
+  tree = hm.ints["body_tree"]
+  assert sorted(tree.tolist()) == list(range(s["nbody"]))
+  # tensors are float32 / int32 views with the reference's logical shapes
+  assert m.body_mass.shape == (1, 17) and m.body_mass.dtype == torch.float32
+  assert m.geom_size.shape == (1, 20, 3)
+  assert m.jnt_type.dtype == torch.int32
+  assert float(m.opt.tolerance) >= np.float32(1e-6)  # io.py: tolerance floored for float32
+
+
+def test_is_sparse_and_padding_rules(humanoid):
+  assert not mio.is_sparse(humanoid)
+  assert mio._get_padded_sizes(27, 0, False, 16)[1] == 28
+  assert mio._get_padded_sizes(40, 0, False, 16)[1] == 48
+
+
+def test_make_data_shapes_and_defaults(humanoid):
+  d = mjw.make_data(humanoid, nworld=3, nconmax=24, njmax=64, device="cpu")
+  assert d.nworld == 3 and d.njmax == 64 and d.naconmax == 72
+  assert d.qpos.shape == (3, 28) and d.qvel.shape == (3, 27) and d.ctrl.shape == (3, 21)
+  assert d.xquat.shape == (3, 17, 4) and d.xmat.shape == (3, 17, 3, 3) and d.cdof.shape == (3, 27, 6)
+  assert d.qM.shape == (3, 28, 28) and d.qLD.shape == (3, 27, 27)
+  assert d.efc.J.shape == (3, 64, 28) and d.efc.force.shape == (3, 64) and d.efc.state.dtype == torch.int32
+  assert d.contact.dist.shape == (72,) and d.contact.frame.shape == (72, 3, 3) and d.contact.geom.shape == (72, 2)
+  assert d.nefc.shape == (3,) and d.nacon.shape == (1,)
+  np.testing.assert_allclose(d.qpos[0].numpy(), np.asarray(humanoid.qpos0), rtol=1e-6)
+  assert float(d.xquat[1, 5, 0]) == 1.0  # identity quaternions
+  # the flat-name accessor and the nested views alias the same storage
+  assert d.field("efc_J").data_ptr() == d.efc.J.data_ptr()
+  assert d.field("contact_dist").data_ptr() == d.contact.dist.data_ptr()
+
+
+@pytest.mark.parametrize(
+  "kwargs,msg",
+  [
+    ({"nworld": 0}, "nworld"),
+    ({"nconmax": -1}, "nconmax"),
+    ({"njmax": -1}, "njmax"),
+    ({"naconmax": -1}, "naconmax"),
+    ({"nccdmax": 30, "nconmax": 24}, "ccdmax"),
+    ({"naccdmax": 9999, "naconmax": 10}, "naccdmax"),
+  ],
+)
+def test_make_data_rejects_bad_sizes(humanoid, kwargs, msg):
+  args = dict(nworld=2, nconmax=24, njmax=64, device="cpu")
+  args.update(kwargs)
+  with pytest.raises(ValueError, match=msg):
+    mjw.make_data(humanoid, **args)
+
+
+UNSUPPORTED = [
+  ('<option cone="elliptic"/>', "elliptic"),
+  ('<option jacobian="sparse"/>', "sparse"),
+  ('<option solver="PGS"/>', "PGS"),
+  ('<option integrator="implicit"/>', "IMPLICIT"),
+  ('<option noslip_iterations="2"/>', "noslip"),
+]
+
+
+@pytest.mark.parametrize("snippet,msg", UNSUPPORTED)
+def test_put_model_rejects_unsupported_features(snippet, msg):
+  xml = f"""<mujoco>{snippet}<worldbody><body><joint type="slide"/><geom type="sphere" size=".1"/></body></worldbody></mujoco>"""
+  mjm = mjw.load_mjcf_string(xml)
+  with pytest.raises(NotImplementedError, match=msg):
+    mjw.put_model(mjm, device="cpu")
+
+
+def test_put_model_rejects_unimplemented_geom_pairs():
+  xml = """<mujoco><worldbody>
+    <body><freejoint/><geom type="box" size=".1 .1 .1"/></body>
+    <body pos="1 0 0"><freejoint/><geom type="box" size=".1 .1 .1"/></body>
+  </worldbody></mujoco>"""
+  with pytest.raises(NotImplementedError, match="BOX"):
+    mjw.put_model(mjw.load_mjcf_string(xml), device="cpu")
+
+
+def test_device_is_mandatory_for_compute(humanoid):
+  if torch.cuda.is_available():
+    pytest.skip("a CUDA device is present")
+  with pytest.raises(RuntimeError, match="CUDA"):
+    mjw.put_model(humanoid)
+  m = mjw.put_model(humanoid, device="cpu")
+  d = mjw.make_data(humanoid, nworld=1, device="cpu")
+  with pytest.raises(RuntimeError, match="no CPU fallback"):
+    mjw.step(m, d)
+
+
+def test_put_data_tiles_host_state_and_get_data_into_reads_it_back(humanoid):
+  hd = mjw.make_host_data(humanoid)
+  hd.qpos[:] = np.asarray(humanoid.key_qpos[0])
+  hd.qvel[:] = np.linspace(-1, 1, humanoid.nv)
+  hd.ctrl[:] = 0.25
+  hd.time = 1.5
+  d = mjw.put_data(humanoid, hd, nworld=4, nconmax=24, njmax=64, device="cpu")
+  for w in range(4):
+    np.testing.assert_allclose(d.qpos[w].numpy(), hd.qpos, rtol=1e-6)
+    np.testing.assert_allclose(d.qvel[w].numpy(), hd.qvel, rtol=1e-6)
+  assert float(d.time[2]) == 1.5
+  d.qvel[3] += 1.0
+  out = mjw.make_host_data(humanoid)
+  mjw.get_data_into(out, humanoid, d, world_id=3)
+  np.testing.assert_allclose(out.qvel, hd.qvel + 1.0, rtol=1e-6)
+  assert out.qvel.dtype == np.float64 and out.nefc == 0 and out.ncon == 0
+
+
+def test_reset_data_masked(humanoid):
+  m = mjw.put_model(humanoid, device="cpu")
+  d = mjw.make_data(humanoid, nworld=4, nconmax=24, njmax=64, device="cpu")
+  d.qpos.add_(0.5)
+  d.qvel.fill_(2.0)
+  d.qacc_warmstart.fill_(3.0)
+  d.time.fill_(9.0)
+  mjw.reset_data(m, d, reset=np.array([True, False, True, False]))
+  for w in (0, 2):
+    np.testing.assert_allclose(d.qpos[w].numpy(), np.asarray(humanoid.qpos0), rtol=1e-6)
+    assert float(d.qvel[w].abs().max()) == 0 and float(d.time[w]) == 0 and float(d.qacc_warmstart[w].abs().max()) == 0
+  for w in (1, 3):
+    assert float(d.qvel[w, 0]) == 2.0 and float(d.time[w]) == 9.0
+  mjw.reset_data(m, d)
+  assert float(d.qvel.abs().max()) == 0
+
+
+def test_override_model_accepts_reference_style_keys(humanoid):
+  m = mjw.put_model(humanoid, device="cpu")
+  mjw.override_model(m, {"opt.solver": "cg", "opt.iterations": 7, "opt.ls_iterations": 3})
+  assert int(m.opt.solver) == int(C.SolverType.CG) and int(m.opt.iterations) == 7 and int(m.opt.ls_iterations) == 3
+
+
+def test_field_tables_cover_every_dataclass_field():
+  for name in types.DATA_REAL_FIELDS:
+    assert name not in types.DATA_INT_FIELDS
+  assert "qpos" in types.DATA_REAL_FIELDS and "nefc" in types.DATA_INT_FIELDS
+  # Contact / Constraint mirrors of the reference dataclasses (types.py:1618, :1659)
+  import dataclasses
+
+  assert {"dist", "pos", "frame", "includemargin", "friction", "solref", "solreffriction", "solimp", "dim", "geom", "efc_address",
+          "worldid"} <= {f.name for f in dataclasses.fields(types.Contact)}  # fmt: skip
+  assert {"J", "pos", "margin", "D", "vel", "aref", "frictionloss", "force", "state", "type", "id"} <= {
+    f.name for f in dataclasses.fields(types.Constraint)
+  }

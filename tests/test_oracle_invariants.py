@@ -1,0 +1,187 @@
+"""Validates the CPU oracle through physics invariants (the substitute for a live MuJoCo C
+comparison, which is unavailable here) and against the committed golden fixture."""
+
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+import mujoco_warp_b200 as mjw
+from oracle import oracle as O
+from tests import helpers as H
+
+GOLDEN = os.path.join(H.ROOT, "tests", "golden", "humanoid_forward_step.npz")
+NW = 6
+
+
+@pytest.fixture(scope="module")
+def fwd(humanoid):
+  qpos, qvel, ctrl = H.make_states(humanoid, NW, seed=7)
+  om, d = H.oracle_data(humanoid, qpos, qvel, ctrl, 24, 64)
+  O.run(om, d, "forward")
+  return om, d
+
+
+def dense_m(d, w, nv):
+  return np.array(d.qM[w, :nv, :nv])
+
+
+def test_mass_matrix_symmetric_positive_definite(fwd):
+  om, d = fwd
+  nv = om.sizes["nv"]
+  for w in range(NW):
+    M = dense_m(d, w, nv)
+    np.testing.assert_allclose(M, M.T, atol=1e-12)
+    assert np.linalg.eigvalsh(M).min() > 0
+
+
+def test_cholesky_factor_reproduces_mass_matrix(fwd):
+  om, d = fwd
+  nv = om.sizes["nv"]
+  for w in range(NW):
+    L = np.tril(np.array(d.qLD[w]).reshape(nv, nv))
+    np.testing.assert_allclose(L @ L.T, dense_m(d, w, nv), atol=1e-10)
+
+
+def test_smooth_acceleration_solves_m_qacc_eq_qfrc(fwd):
+  om, d = fwd
+  nv = om.sizes["nv"]
+  for w in range(NW):
+    np.testing.assert_allclose(dense_m(d, w, nv) @ d.qacc_smooth[w], d.qfrc_smooth[w], atol=1e-9)
+
+
+def test_mul_m_and_solve_m_helpers_match_dense_algebra(fwd):
+  om, d = fwd
+  lib = O.load()
+  nv, nvp = om.sizes["nv"], om.sizes["nv_pad"]
+  rng = np.random.default_rng(0)
+  P = lambda a: a.ctypes.data_as(ctypes.POINTER(ctypes.c_double))  # noqa: E731
+  for w in range(NW):
+    x = rng.normal(size=nv)
+    res, sol = np.zeros(nv), np.zeros(nv)
+    qM = np.ascontiguousarray(d.qM[w]).reshape(-1)
+    lib.mjo_mul_m(nv, nvp, P(qM), P(x), P(res))
+    np.testing.assert_allclose(res, dense_m(d, w, nv) @ x, atol=1e-10)
+    qLD = np.ascontiguousarray(d.qLD[w]).reshape(-1)
+    lib.mjo_solve_m(nv, P(qLD), P(res), P(sol))
+    np.testing.assert_allclose(sol, x, atol=1e-8)
+
+
+def test_contact_frames_are_orthonormal_and_right_handed(fwd):
+  _, d = fwd
+  n = int(d.nacon[0])
+  assert n > 0
+  F = np.array(d.contact_frame[:n]).reshape(n, 3, 3)
+  for f in F:
+    np.testing.assert_allclose(f @ f.T, np.eye(3), atol=1e-12)
+    np.testing.assert_allclose(np.cross(f[0], f[1]), f[2], atol=1e-12)
+
+
+def test_contact_rows_are_consistent_with_contacts(fwd):
+  om, d = fwd
+  for w in range(NW):
+    nefc, ne, nf, nl = int(d.nefc[w]), int(d.ne[w]), int(d.nf[w]), int(d.nl[w])
+    ncon_rows = nefc - ne - nf - nl
+    ids = d.wcon[w, : int(d.wcon_n[w])]
+    expect = 0
+    for c in ids:
+      dim = int(d.contact_dim[c])
+      nrow = 1 if dim == 1 else 2 * (dim - 1)  # pyramidal cone, constraint.py:1669
+      active = d.contact_dist[c] < d.contact_includemargin[c]
+      adr = d.contact_efc_address[c]
+      if active:
+        expect += nrow
+        assert (adr[:nrow] >= 0).all()
+        # contact row position is the contact distance (margin bookkeeping: pos = dist - margin + margin)
+        np.testing.assert_allclose(d.efc_pos[w, adr[:nrow]], d.contact_dist[c], atol=1e-12)
+      else:
+        assert (adr == -1).all()
+    assert ncon_rows == expect
+
+
+def test_solver_satisfies_kkt_conditions(fwd):
+  """At the solver's fixed point M qacc - qfrc_smooth = J^T force with force from the row state machine."""
+  om, d = fwd
+  nv = om.sizes["nv"]
+  scale = 1.0 / (om.meaninertia * nv)
+  for w in range(NW):
+    nefc = int(d.nefc[w])
+    J = np.array(d.efc_J[w, :nefc, :nv])
+    f = np.array(d.efc_force[w, :nefc])
+    res = dense_m(d, w, nv) @ d.qacc[w] - d.qfrc_smooth[w] - J.T @ f
+    assert np.linalg.norm(res) * scale < 1e-5
+    # complementarity of the inequality rows: force >= 0 and zero where the row is satisfied
+    ineq = slice(int(d.ne[w]) + int(d.nf[w]), nefc)
+    assert (f[ineq] >= -1e-12).all()
+    jar = J @ d.qacc[w] - d.efc_aref[w, :nefc]
+    sat = jar[ineq] >= 0
+    np.testing.assert_allclose(f[ineq][sat], 0.0, atol=1e-12)
+    np.testing.assert_allclose(d.qfrc_constraint[w], J.T @ f, atol=1e-9)
+
+
+def test_rne_bias_matches_mass_matrix_at_zero_acceleration(humanoid):
+  """qfrc_bias(q, v=0) is pure gravity: -J_com^T m g, i.e. its root-translation entries are 0, 0, m g."""
+  qpos, qvel, ctrl = H.make_states(humanoid, 2, seed=3)
+  qvel[:] = 0
+  om, d = H.oracle_data(humanoid, qpos, qvel, ctrl, 24, 64)
+  O.run(om, d, "forward")
+  mass = float(np.sum(humanoid.body_mass))
+  np.testing.assert_allclose(d.qfrc_bias[:, :3], np.array([[0, 0, 9.81 * mass]] * 2), atol=1e-9)
+
+
+def test_free_fall_without_contacts_conserves_horizontal_momentum_and_accelerates_at_g(humanoid):
+  qpos = np.array(humanoid.key_qpos[0])[None].copy()
+  qpos[0, 2] += 5.0  # far above the floor
+  om, d = H.oracle_data(humanoid, qpos, np.zeros((1, humanoid.nv)), np.zeros((1, humanoid.nu)), 24, 64)
+  O.run(om, d, "forward")
+  assert int(d.nacon[0]) == 0
+  com0 = np.array(d.subtree_com[0, 1])
+  for _ in range(20):
+    O.run(om, d, "step")
+  O.run(om, d, "forward")
+  com1 = np.array(d.subtree_com[0, 1])
+  t = 20 * om.opt["timestep"]
+  # internal joint forces cannot move the centre of mass (up to the O(dt^2) error of the integrator)
+  np.testing.assert_allclose(com1[:2], com0[:2], atol=1e-4)
+  # semi-implicit Euler: z(t) = z0 - g dt^2 n(n+1)/2
+  np.testing.assert_allclose(com1[2] - com0[2], -9.81 * om.opt["timestep"] ** 2 * 20 * 21 / 2, rtol=5e-3)
+  assert abs(float(d.time[0]) - t) < 1e-12
+
+
+def test_oracle_reproduces_golden_fixture(humanoid):
+  g = np.load(GOLDEN)
+  om, d = H.oracle_data(humanoid, g["qpos0"], g["qvel0"], g["ctrl"], int(g["nconmax"]), int(g["njmax"]))
+  O.run(om, d, "forward")
+  for f in ["qM", "qacc_smooth", "efc_J", "efc_D", "efc_aref", "efc_force", "qacc"]:
+    np.testing.assert_allclose(getattr(d, f), g["fwd_" + f], rtol=1e-9, atol=1e-9, err_msg=f)
+  for f in ["nefc", "ne", "nf", "nl", "wcon_n"]:
+    np.testing.assert_array_equal(getattr(d, f), g["fwd_" + f])
+  om, d = H.oracle_data(humanoid, g["qpos0"], g["qvel0"], g["ctrl"], int(g["nconmax"]), int(g["njmax"]))
+  for k in range(g["traj_qpos"].shape[0]):
+    O.run(om, d, "step")
+    np.testing.assert_allclose(d.qpos, g["traj_qpos"][k], rtol=1e-8, atol=1e-8)
+    np.testing.assert_array_equal(d.nefc, g["traj_nefc"][k])
+
+
+def test_oracle_threads_and_world_ranges_are_equivalent(humanoid):
+  """Running [0, n) in one call, in two halves, or with several OpenMP threads gives identical per-world results."""
+  qpos, qvel, ctrl = H.make_states(humanoid, 8, seed=11)
+  om, a = H.oracle_data(humanoid, qpos, qvel, ctrl, 24, 64)
+  O.run(om, a, "forward")
+  _, b = H.oracle_data(humanoid, qpos, qvel, ctrl, 24, 64)
+  O.run(om, b, "forward", nthread=4)
+  for f in ["qacc", "efc_force", "nefc", "qM"]:
+    np.testing.assert_array_equal(getattr(a, f), getattr(b, f))
+  # contact pool order may differ between thread schedules, per-world content may not
+  for w in range(8):
+    np.testing.assert_allclose(np.sort(H.world_contacts_orc(a, w, "contact_dist")), np.sort(H.world_contacts_orc(b, w, "contact_dist")))
+
+
+def test_cg_and_newton_agree(humanoid):
+  qpos, qvel, ctrl = H.make_states(humanoid, 4, seed=5)
+  om, a = H.oracle_data(humanoid, qpos, qvel, ctrl, 24, 64)
+  O.run(om, a, "forward", opt={"iterations": 100, "tolerance": 1e-10})
+  _, b = H.oracle_data(humanoid, qpos, qvel, ctrl, 24, 64)
+  O.run(om, b, "forward", opt={"solver": 1, "iterations": 500, "tolerance": 1e-10})
+  np.testing.assert_allclose(a.qacc, b.qacc, rtol=1e-4, atol=1e-4)
