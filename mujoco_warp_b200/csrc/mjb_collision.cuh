@@ -307,7 +307,8 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
       else atomicOr(DW(status), MJB_STATUS_WCON_OVERFLOW);
     }
   }
-  nw += total;
+  // only the contacts that fitted into the pool enter the world's list (they are the first slots)
+  nw += max(0, min(total, K.dsz.naconmax - base));
 }
 
 // collision_driver.collision (collision_driver.py:755).  queue: 64 ints of shared scratch.

@@ -1,0 +1,282 @@
+"""CUDA path vs oracle under non-default options, on small hand-written models that reach the row types the
+humanoid does not (joint equality, dof friction, slide limits, plane-box, sphere-capsule), at the edges
+(overflowing njmax / nconmax, nworld 1, worlds not a multiple of the CTA width, no constraints at all),
+and size-independent properties at the benchmark's full size (nworld 8192)."""
+
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+import mujoco_warp_b200 as mjw
+from mujoco_warp_b200 import constants as C
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+DB = C.DisableBit
+
+
+def run_both(mjm, qpos, qvel, ctrl, nconmax, njmax, stage="forward", opt=None, nstep=1):
+  from oracle import oracle as O
+
+  om, od = H.oracle_data(mjm, qpos, qvel, ctrl, nconmax, njmax)
+  m, d = H.device_data(mjw, mjm, qpos, qvel, ctrl, nconmax, njmax)
+  for k, v in (opt or {}).items():
+    setattr(m.opt, k, v)
+  for _ in range(nstep):
+    O.run(om, od, stage, opt=opt, nthread=4)
+    (mjw.forward if stage == "forward" else mjw.step)(m, d)
+  torch.cuda.synchronize()
+  return om, od, m, d
+
+
+def assert_forward_close(od, d, tol_solver=2e-2, tol_smooth=5e-5):
+  for f in ["ne", "nf", "nl", "nefc", "wcon_n", "nacon"]:
+    np.testing.assert_array_equal(H.dev_np(d, f), getattr(od, f), err_msg=f)
+  for f in ["qfrc_bias", "qfrc_passive", "qfrc_actuator", "qfrc_smooth"]:
+    assert H.max_err(H.dev_np(d, f), getattr(od, f)) < tol_smooth, f
+  if tol_solver is None:
+    return
+  for f in ["qacc", "qfrc_constraint"]:
+    assert H.max_err(H.dev_np(d, f), getattr(od, f)) < tol_solver, f
+
+
+@pytest.mark.parametrize(
+  "flags",
+  [DB.CONTACT, DB.LIMIT, DB.CONSTRAINT, DB.GRAVITY, DB.WARMSTART, DB.ACTUATION, DB.CLAMPCTRL, DB.SPRING | DB.DAMPER, DB.EULERDAMP, DB.REFSAFE,
+   DB.FILTERPARENT],
+)  # fmt: skip
+def test_disable_flags(humanoid, flags):
+  qpos, qvel, ctrl = H.make_states(humanoid, 16, seed=10)
+  ctrl *= 3.0  # exercise the control clamp
+  _, od, _, d = run_both(humanoid, qpos, qvel, ctrl, 24, 64, stage="step", opt={"disableflags": int(flags)}, nstep=2)
+  # after stepping, the float32 state itself has drifted from the float64 one (qvel ~1e-3)
+  assert_forward_close(od, d, tol_solver=5e-2, tol_smooth=2e-3)
+  assert H.max_err(H.dev_np(d, "qpos"), od.qpos) < 1e-5
+  assert H.max_err(H.dev_np(d, "qvel"), od.qvel) < 5e-3
+
+
+def test_cg_solver(humanoid):
+  qpos, qvel, ctrl = H.make_states(humanoid, 16, seed=11)
+  opt = {"solver": int(C.SolverType.CG), "iterations": 100}
+  _, od, _, d = run_both(humanoid, qpos, qvel, ctrl, 24, 64, opt=opt)
+  assert_forward_close(od, d, tol_solver=5e-2)
+
+
+@pytest.mark.parametrize("iterations,ls_iterations", [(1, 50), (3, 2), (100, 50)])
+def test_iteration_limits(humanoid, iterations, ls_iterations):
+  qpos, qvel, ctrl = H.make_states(humanoid, 16, seed=12)
+  _, od, _, d = run_both(humanoid, qpos, qvel, ctrl, 24, 64, opt={"iterations": iterations, "ls_iterations": ls_iterations})
+  assert int(H.dev_np(d, "solver_niter").max()) <= iterations
+  # a truncated solve is not a fixed point: float32 and float64 line searches may stop at different alphas,
+  # so the solver outputs are only compared when the iteration budget lets both converge
+  assert_forward_close(od, d, tol_solver=5e-2 if iterations >= 100 else None)
+  assert not torch.isnan(d.qacc).any()
+
+
+SMALL_MODELS = {
+  "equality_friction_limits": """
+    <mujoco><option timestep="0.002"/>
+      <worldbody>
+        <body pos="0 0 1"><joint name="a" type="hinge" axis="0 1 0" frictionloss="0.3" damping="0.1"/><geom type="capsule" size=".05 .2" fromto="0 0 0 .4 0 0"/>
+          <body pos=".4 0 0"><joint name="b" type="hinge" axis="0 1 0" limited="true" range="-20 20" stiffness="2"/><geom type="capsule" size=".04 .2" fromto="0 0 0 .3 0 0"/></body>
+        </body>
+        <body pos="0 1 1"><joint name="c" type="slide" axis="0 0 1" limited="true" range="-0.05 0.05"/><geom type="sphere" size=".1"/></body>
+      </worldbody>
+      <equality><joint joint1="a" joint2="b" polycoef="0.1 0.5 0 0 0"/></equality>
+      <actuator><motor joint="a" gear="2" ctrllimited="true" ctrlrange="-1 1"/><position joint="c" kp="20"/></actuator>
+    </mujoco>""",
+  "box_and_spheres_on_plane": """
+    <mujoco>
+      <worldbody>
+        <geom type="plane" size="5 5 .01" contype="3"/>
+        <body pos="0 0 0.09"><freejoint/><geom type="box" size=".1 .15 .1" contype="0" conaffinity="2"/></body>
+        <body pos="0.5 0 0.08"><freejoint/><geom type="sphere" size=".1"/></body>
+        <body pos="0.62 0 0.12"><freejoint/><geom type="capsule" size=".05 .1"/></body>
+        <body pos="0.5 0.15 0.1"><freejoint/><geom type="sphere" size=".08" condim="1"/></body>
+      </worldbody>
+    </mujoco>""",
+  "no_constraints_no_actuators": """
+    <mujoco><worldbody>
+      <body pos="0 0 1"><joint type="ball"/><geom type="capsule" size=".05 .2"/>
+        <body pos="0 0 -.5"><joint type="hinge" axis="1 0 0"/><geom type="sphere" size=".1"/></body>
+      </body>
+    </worldbody></mujoco>""",
+}
+
+
+@pytest.mark.parametrize("name", list(SMALL_MODELS))
+def test_small_models(name):
+  mjm = mjw.load_mjcf_string(SMALL_MODELS[name])
+  rng = np.random.default_rng(5)
+  nw = 8
+  qpos = np.repeat(np.asarray(mjm.qpos0, dtype=np.float64)[None], nw, axis=0)
+  for j in range(mjm.njnt):
+    jt, qa = int(mjm.jnt_type[j]), int(mjm.jnt_qposadr[j])
+    if jt in (2, 3):
+      qpos[:, qa] += rng.uniform(-0.3, 0.3, nw)
+    elif jt == 0:
+      qpos[:, qa + 2] += rng.uniform(-0.02, 0.02, nw)
+  qvel = rng.uniform(-0.5, 0.5, (nw, mjm.nv))
+  ctrl = rng.uniform(-2, 2, (nw, mjm.nu))
+  _, od, _, d = run_both(mjm, qpos, qvel, ctrl, 32, 64, stage="step", nstep=3)
+  assert_forward_close(od, d, tol_solver=5e-2, tol_smooth=2e-3)
+  assert H.max_err(H.dev_np(d, "qpos"), od.qpos) < 1e-4
+  if name == "equality_friction_limits":
+    assert int(od.ne.max()) == 1 and int(od.nf.max()) >= 1
+  if name == "box_and_spheres_on_plane":
+    assert int(od.nacon[0]) > 0
+
+
+def test_njmax_overflow_sets_status_and_clamps(humanoid):
+  qpos, qvel, ctrl = H.make_states(humanoid, 8, seed=13)
+  qpos[:, 2] -= 0.2  # push into the floor: many contacts
+  _, od, _, d = run_both(humanoid, qpos, qvel, ctrl, 24, 8)
+  np.testing.assert_array_equal(H.dev_np(d, "nefc"), od.nefc)  # the attempted row count is reported, as in the oracle
+  assert int(od.nefc.max()) > 8
+  assert int(d.status.max()) & 1  # MJB_STATUS_NEFC_OVERFLOW
+  adr_dev = H.dev_np(d, "contact_efc_address")
+  assert (adr_dev < 8).all()
+  assert not torch.isnan(d.qacc).any()
+
+
+def test_nconmax_overflow_sets_status(humanoid):
+  qpos, qvel, ctrl = H.make_states(humanoid, 8, seed=14)
+  qpos[:, 2] -= 0.25
+  m, d = H.device_data(mjw, humanoid, qpos, qvel, ctrl, 1, 64)
+  mjw.forward(m, d)
+  # like the reference's atomic counter (collision_core.py:160-213) nacon counts attempts and may exceed the pool
+  assert int(d.nacon[0]) > d.naconmax
+  assert int(d.wcon_n.sum()) <= d.naconmax
+  assert int(d.status.max()) & 6  # NCON / WCON overflow bits
+  assert not torch.isnan(d.qacc).any()
+
+
+@pytest.mark.parametrize("nworld", [1, 5, 33])
+def test_ragged_world_counts(humanoid, nworld):
+  qpos, qvel, ctrl = H.make_states(humanoid, nworld, seed=15)
+  _, od, _, d = run_both(humanoid, qpos, qvel, ctrl, 24, 64)
+  assert_forward_close(od, d)
+
+
+def test_njmax_zero_means_unconstrained(humanoid):
+  qpos, qvel, ctrl = H.make_states(humanoid, 4, seed=16)
+  m, d = H.device_data(mjw, humanoid, qpos, qvel, ctrl, 0, 0)
+  mjw.forward(m, d)
+  assert torch.equal(d.qacc, d.qacc_smooth)
+  assert int(d.solver_niter.max()) == 0
+
+
+def test_rk4_matches_host_composition_of_oracle_forwards(humanoid):
+  """forward.py:458 rungekutta4: three extra forward passes; checked against the oracle's forward driven by numpy."""
+  from oracle import oracle as O
+
+  lib = O.load()
+  qpos, qvel, ctrl = H.make_states(humanoid, 4, seed=17)
+  om, od = H.oracle_data(humanoid, qpos, qvel, ctrl, 24, 64)
+  dt = om.opt["timestep"]
+
+  def integrate_pos(q0, v, h):
+    out = q0.copy()
+    for w in range(q0.shape[0]):
+      for j in range(humanoid.njnt):
+        jt, qa, da = int(humanoid.jnt_type[j]), int(humanoid.jnt_qposadr[j]), int(humanoid.jnt_dofadr[j])
+        if jt == 0:
+          out[w, qa : qa + 3] = q0[w, qa : qa + 3] + h * v[w, da : da + 3]
+          quat, om3 = q0[w, qa + 3 : qa + 7].copy(), v[w, da + 3 : da + 6].copy()  # copies: the oracle integrates in place
+          lib.mjo_quat_integrate(quat.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), om3.ctypes.data_as(ctypes.POINTER(ctypes.c_double)),
+                                 ctypes.c_double(h))  # fmt: skip
+          out[w, qa + 3 : qa + 7] = quat
+        else:
+          out[w, qa] = q0[w, qa] + h * v[w, da]
+    return out
+
+  O.run(om, od, "forward")
+  A, B = [0.5, 0.5, 1.0], [1 / 6, 1 / 3, 1 / 3, 1 / 6]
+  q0, v0 = od.qpos.copy(), od.qvel.copy()
+  vrk, ark = B[0] * od.qvel, B[0] * od.qacc
+  for i in range(3):
+    od.qpos[:] = integrate_pos(q0, od.qvel, A[i] * dt)
+    od.qvel[:] = v0 + A[i] * dt * od.qacc
+    O.run(om, od, "forward")
+    vrk += B[i + 1] * od.qvel
+    ark += B[i + 1] * od.qacc
+  v1 = v0 + dt * ark
+  q1 = integrate_pos(q0, vrk, dt)
+
+  m, d = H.device_data(mjw, humanoid, qpos, qvel, ctrl, 24, 64)
+  m.opt.integrator = int(C.IntegratorType.RK4)
+  mjw.step(m, d)
+  eq, ev = H.max_err(H.dev_np(d, "qpos"), q1), H.max_err(H.dev_np(d, "qvel"), v1)
+  assert eq < 1e-5 and ev < 5e-3, (eq, ev)
+  assert abs(float(d.time[0]) - dt) < 1e-7
+
+
+def test_reset_then_step_equals_fresh_data(humanoid):
+  qpos, qvel, ctrl = H.make_states(humanoid, 8, seed=18)
+  m, d = H.device_data(mjw, humanoid, qpos, qvel, ctrl, 24, 64)
+  for _ in range(3):
+    mjw.step(m, d)
+  mjw.reset_data(m, d)
+  fresh = mjw.make_data(humanoid, nworld=8, nconmax=24, njmax=64)
+  mjw.step(m, d)
+  mjw.step(m, fresh)
+  assert torch.equal(d.qpos, fresh.qpos) and torch.equal(d.qvel, fresh.qvel)
+
+
+def test_get_data_into_after_forward(humanoid):
+  from oracle import oracle as O
+
+  qpos, qvel, ctrl = H.make_states(humanoid, 4, seed=19)
+  om, od = H.oracle_data(humanoid, qpos, qvel, ctrl, 24, 64)
+  O.run(om, od, "forward")
+  m, d = H.device_data(mjw, humanoid, qpos, qvel, ctrl, 24, 64)
+  mjw.forward(m, d)
+  out = mjw.make_host_data(humanoid)
+  mjw.get_data_into(out, humanoid, d, world_id=2)
+  assert out.nefc == int(od.nefc[2]) and out.ncon == int(od.wcon_n[2])
+  assert out.efc_J.shape == (out.nefc, humanoid.nv)
+  assert H.max_err(out.qacc, od.qacc[2]) < 2e-2
+  np.testing.assert_array_equal(out.contact.geom, H.world_contacts_orc(od, 2, "contact_geom"))
+
+
+def test_full_size_properties(humanoid):
+  """nworld = 8192 (BASELINE.json configs[1]): size-independent properties + a 32-world oracle sample."""
+  from oracle import oracle as O
+
+  nworld = 8192
+  qpos, qvel, ctrl = H.make_states(humanoid, nworld, seed=20)
+  m, d = H.device_data(mjw, humanoid, qpos, qvel, ctrl, 24, 64)
+  for _ in range(3):
+    mjw.step(m, d)
+  mjw.forward(m, d)
+  torch.cuda.synchronize()
+  assert int(d.status.max()) == 0
+  assert not torch.isnan(d.qpos).any() and not torch.isnan(d.qacc).any()
+  nefc = d.nefc.long()
+  assert int(nefc.max()) <= 64 and int(d.nacon[0]) == int(d.wcon_n.sum()) <= d.naconmax
+  assert torch.equal(nefc, (d.ne + d.nf + d.nl).long() + (nefc - (d.ne + d.nf + d.nl).long()))
+  # quaternions stay normalised; M qacc_smooth = qfrc_smooth; contact frames orthonormal
+  assert float((d.qpos[:, 3:7].norm(dim=1) - 1).abs().max()) < 1e-5
+  M = d.qM[:, :27, :27].double()
+  res = torch.einsum("wij,wj->wi", M, d.qacc_smooth.double()) - d.qfrc_smooth.double()
+  assert float(res.abs().max() / (1 + d.qfrc_smooth.abs().max())) < 1e-3
+  n = int(d.nacon[0])
+  F = d.contact.frame[:n].double()
+  assert float((F @ F.transpose(1, 2) - torch.eye(3, device="cuda", dtype=torch.float64)).abs().max()) < 1e-5
+  # KKT residual of every world
+  f = torch.where(torch.arange(64, device="cuda")[None] < nefc[:, None], d.efc.force, torch.zeros_like(d.efc.force)).double()
+  J = d.efc.J[:, :, :27].double()
+  kkt = torch.einsum("wij,wj->wi", M, d.qacc.double()) - d.qfrc_smooth.double() - torch.einsum("wri,wr->wi", J, f)
+  scale = 1.0 / (float(m.stat.meaninertia) * 27)
+  # float32 noise floor of the gradient: ~1e-4 worst case, ~2e-6 median (tolerance is 1e-6)
+  assert float(kkt.norm(dim=1).max()) * scale < 5e-3
+  assert float(kkt.norm(dim=1).median()) * scale < 1e-4
+  # a sample of worlds against the oracle, from the device's own state
+  idx = np.arange(0, nworld, nworld // 32)[:32]
+  om, od = H.oracle_data(humanoid, H.dev_np(d, "qpos")[idx], H.dev_np(d, "qvel")[idx], H.dev_np(d, "ctrl")[idx], 24, 64,
+                         warmstart=H.dev_np(d, "qacc_warmstart")[idx])  # fmt: skip
+  O.run(om, od, "forward", nthread=4)
+  np.testing.assert_array_equal(H.dev_np(d, "nefc")[idx], od.nefc)
+  assert H.max_err(H.dev_np(d, "qacc")[idx], od.qacc) < 2e-2
