@@ -64,6 +64,23 @@ def group_alg_bytes(d, nworld):
 METRIC = "humanoid env-steps/sec at nworld=8192, 1/2/4/8 B200; % of HBM roofline"
 
 
+def workload_name(nworld):
+  return (f"benchmarks/humanoid/humanoid.xml nworld={nworld} per GPU, nconmax=24 njmax=64, Newton solver, dense Jacobian, Euler, "
+          "keyframe 'squat' + OU/Halton ctrl noise")  # fmt: skip
+
+
+def _ncu_traffic(kernel):
+  """DRAM bytes per launch of `kernel` from the newest committed `ncu --set full` summary (profiles/rN_ncu_full_groups.json)."""
+  import glob
+
+  files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_groups.json")))
+  if not files:
+    return None, None
+  with open(files[-1]) as f:
+    e = json.load(f).get(kernel)
+  return (e["dram_bytes_per_launch"], os.path.relpath(files[-1], ROOT)) if e else (None, None)
+
+
 def _peaks():
   p = os.path.join(ROOT, "MEASURED_PEAKS.json")
   if os.path.exists(p):
@@ -175,7 +192,7 @@ def run_reference(args, rank):
   print(json.dumps({
     "impl": "reference", "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": args.gpus, "steps": steps,
     "warmup": warmup, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-    "dtype": "f64", "data": "synthetic", "config": {"workload": f"humanoid.xml nworld={nw} sample, nconmax=24 njmax=64, Newton, Euler, CPU"},
+    "dtype": "f64", "data": "synthetic", "config": {"workload": workload_name(args.nworld), "sample": f"each step advances a bounded sample of {nw} of the {args.nworld} worlds on the host cores"},
     "cpu_baseline": cb, "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
   }))  # fmt: skip
 
@@ -326,12 +343,13 @@ def main():
     dom = max(group_ms, key=lambda g: group_ms[g])  # the dominant kernel of the step
     achieved = gbytes[dom] * nworld / (group_ms[dom] * 1e-3) / 1e9
     step_achieved = ALG_BYTES_PER_ENV_STEP * nworld / (kernel_ms * 1e-3) / 1e9
+    traffic, traffic_src = _ncu_traffic(f"mjb_group_kernel<{dom}>")
     out = {
       "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K, "warmup": W,
       "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
       "data": "synthetic",
       "config": {
-        "workload": f"benchmarks/humanoid/humanoid.xml nworld={nworld} per GPU, nconmax=24 njmax=64, Newton solver, dense Jacobian, Euler, keyframe 'squat' + OU/Halton ctrl noise",
+        "workload": workload_name(nworld),
         "parallelism": f"worlds sharded over {world} GPU(s), no per-step collective",
         "l2": "per-GPU working set (~40 kB/world x nworld = ~330 MB) exceeds the 126 MB L2; no explicit flush",
         "cuda_graph": graph is not None, "nan_worlds": nan_worlds, "status_bits": status,
@@ -340,7 +358,7 @@ def main():
       "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": nworld * nu * 4, "d2h_bytes_per_step": nworld * (nq + nv) * 4,
               "steps": Ke},
       "gpu_launches": int(gpu_launches),
-      "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+      "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                    "kernel": f"mjb_group_kernel<{dom}>", "kernel_ms": group_ms[dom], "share_of_step": group_ms[dom] / kernel_ms,
                    "alg_bytes_per_launch": gbytes[dom] * nworld, "peak_source": peak_src,
                    "step": {"kernels_ms": kernel_ms, "alg_bytes_per_env_step": ALG_BYTES_PER_ENV_STEP, "achieved": step_achieved,

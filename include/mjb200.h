@@ -77,6 +77,28 @@ int mjb_solve_m(const MjbModel* m, MjbData* d, float* x, const float* y, void* c
 /* support.mul_m (reference support.py:133): res = qM @ vec; (nworld, nv). */
 int mjb_mul_m(const MjbModel* m, MjbData* d, float* res, const float* vec, void* cuda_stream);
 
+/* One entry per stage function f(m, d) of the reference's public surface (mujoco_warp/__init__.py:25-112):
+ * smooth.py:358 kinematics, :602 com_pos, :889 crb, :1104 factor_m, :2605 transmission;
+ * collision_driver.py:755 collision; constraint.py:2210 make_constraint; forward.py:514 fwd_position,
+ * :593 fwd_velocity, :837 fwd_actuation, :950 fwd_acceleration, :327 euler; solver.py:3297 solve. */
+int mjb_kinematics(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_com_pos(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_crb(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_factor_m(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_collision(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_make_constraint(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_transmission(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_fwd_position(const MjbModel* m, MjbData* d, const MjbOption* opt, int factorize, void* cuda_stream);
+int mjb_fwd_velocity(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_fwd_actuation(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_fwd_acceleration(const MjbModel* m, MjbData* d, const MjbOption* opt, int factorize, void* cuda_stream);
+int mjb_solve(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_euler(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+/* Replaces the reference's device printf on overflow (forward.py:194-210, collision_core.py:213):
+ * ORs the per-world status words (MJB_STATUS_* bits) into *host_flags.  Synchronises the stream;
+ * the step entry points never do. */
+int mjb_status(MjbData* d, uint32_t* host_flags, void* cuda_stream);
+
 /* benchmark.ctrl_noise (reference benchmark.py:42): Ornstein-Uhlenbeck control noise with
  * Halton-sequence noise; ctrl_center may be NULL. */
 int mjb_ctrl_noise(const MjbModel* m, MjbData* d, const MjbOption* opt, const float* ctrl_center,

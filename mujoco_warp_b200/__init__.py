@@ -41,6 +41,7 @@ from .forward import mul_m as mul_m
 from .forward import rungekutta4 as rungekutta4
 from .forward import solve as solve
 from .forward import solve_m as solve_m
+from .forward import status as status
 from .forward import step as step
 from .forward import step1 as step1
 from .forward import step2 as step2

@@ -326,6 +326,43 @@ extern "C" int mjb_step2(const MjbModel* m, MjbData* d, const MjbOption* opt, vo
   return mjb_run_stages(m, d, opt, MJB_STAGE_FWD_ACTUATION | MJB_STAGE_FWD_ACCELERATION | MJB_STAGE_SOLVE | integ, s);
 }
 
+// one entry point per stage function of the reference (f(m, d) in mujoco_warp/__init__.py:25-112)
+#define MJB_STAGE_ENTRY(name, bits) \
+  extern "C" int mjb_##name(const MjbModel* m, MjbData* d, const MjbOption* opt, void* s) { return mjb_run_stages(m, d, opt, (bits), s); }
+MJB_STAGE_ENTRY(kinematics, MJB_STAGE_KINEMATICS)
+MJB_STAGE_ENTRY(com_pos, MJB_STAGE_COM_POS)
+MJB_STAGE_ENTRY(crb, MJB_STAGE_CRB)
+MJB_STAGE_ENTRY(factor_m, MJB_STAGE_FACTOR_M)
+MJB_STAGE_ENTRY(collision, MJB_STAGE_COLLISION)
+MJB_STAGE_ENTRY(make_constraint, MJB_STAGE_MAKE_CONSTRAINT)
+MJB_STAGE_ENTRY(transmission, MJB_STAGE_TRANSMISSION)
+MJB_STAGE_ENTRY(fwd_velocity, MJB_STAGE_FWD_VELOCITY)
+MJB_STAGE_ENTRY(fwd_actuation, MJB_STAGE_FWD_ACTUATION)
+MJB_STAGE_ENTRY(solve, MJB_STAGE_SOLVE)
+MJB_STAGE_ENTRY(euler, MJB_STAGE_EULER)
+#undef MJB_STAGE_ENTRY
+extern "C" int mjb_fwd_position(const MjbModel* m, MjbData* d, const MjbOption* opt, int factorize, void* s) {
+  return mjb_run_stages(m, d, opt, MJB_STAGES_FWD_POSITION | (factorize ? MJB_STAGE_FACTOR_M : 0), s);
+}
+extern "C" int mjb_fwd_acceleration(const MjbModel* m, MjbData* d, const MjbOption* opt, int factorize, void* s) {
+  return mjb_run_stages(m, d, opt, factorize ? MJB_STAGE_FWD_ACC_FACTOR : MJB_STAGE_FWD_ACCELERATION, s);
+}
+// Reads the device status word (overflow / NaN bits ORed over worlds).  Synchronises the stream.
+extern "C" int mjb_status(MjbData* d, uint32_t* host_flags, void* s) {
+  if (!d || !host_flags) return fail(-1, "null handle");
+  cudaStream_t stream = static_cast<cudaStream_t>(s);
+  const int n = d->dsz.nworld;
+  std::vector<int> h(n > 0 ? n : 1, 0);
+  if (n > 0) {
+    CUDA_OK(cudaMemcpyAsync(h.data(), d->d.status, sizeof(int) * n, cudaMemcpyDeviceToHost, stream));
+    CUDA_OK(cudaStreamSynchronize(stream));
+  }
+  uint32_t f = 0;
+  for (int i = 0; i < n; i++) f |= (uint32_t)h[i];
+  *host_flags = f;
+  return 0;
+}
+
 extern "C" int mjb_solve_m(const MjbModel* m, MjbData* d, float* x, const float* y, void* s) {
   if (!m || !d) return fail(-1, "null handle");
   cudaStream_t stream = static_cast<cudaStream_t>(s);

@@ -244,3 +244,14 @@ def ctrl_noise(m, d, step_index: int, ctrl_center=None, ctrlnoisestd: float = 0.
   opt = _lib.make_option(m)
   cptr = ctypes.c_void_p(ctrl_center.data_ptr()) if ctrl_center is not None else ctypes.c_void_p(0)
   _lib.check(lib, lib.mjb_ctrl_noise(m._handle, d._handle, ctypes.byref(opt), cptr, int(step_index), float(ctrlnoisestd), float(ctrlnoiserate), _lib.stream_ptr()))
+
+
+def status(m, d) -> int:
+  """ORed per-world status bits (MJB_STATUS_*: nefc / contact-pool overflow, NaN in qacc).
+
+  Replaces the reference's device printf diagnostics (forward.py:194-210).  Synchronises the stream."""
+  lib = _lib.load()
+  _ensure_bound(m, d)
+  flags = ctypes.c_uint32(0)
+  _lib.check(lib, lib.mjb_status(d._handle, ctypes.byref(flags), _lib.stream_ptr()))
+  return int(flags.value)

@@ -132,10 +132,11 @@ def test_small_models(name):
 def test_njmax_overflow_sets_status_and_clamps(humanoid):
   qpos, qvel, ctrl = H.make_states(humanoid, 8, seed=13)
   qpos[:, 2] -= 0.2  # push into the floor: many contacts
-  _, od, _, d = run_both(humanoid, qpos, qvel, ctrl, 24, 8)
+  _, od, _m, d = run_both(humanoid, qpos, qvel, ctrl, 24, 8)
   np.testing.assert_array_equal(H.dev_np(d, "nefc"), od.nefc)  # the attempted row count is reported, as in the oracle
   assert int(od.nefc.max()) > 8
   assert int(d.status.max()) & 1  # MJB_STATUS_NEFC_OVERFLOW
+  assert mjw.status(_m, d) & 1
   adr_dev = H.dev_np(d, "contact_efc_address")
   assert (adr_dev < 8).all()
   assert not torch.isnan(d.qacc).any()
