@@ -155,7 +155,7 @@ def cpu_baseline(nthread):
   from oracle import oracle as O
 
   om, d, nw, rate = _cpu_sample(nthread)
-  ns = int(max(20, min(5000, rate * 12.0)))
+  ns = int(max(20, min(100000, rate * 12.0)))
   t0 = time.perf_counter()
   for _ in range(ns):
     O.run(om, d, "step", nthread=nthread)
