@@ -56,9 +56,10 @@ def load():
   with _lock:
     if _lib is not None:
       return _lib
-    if not os.path.exists(LIB_PATH):
-      raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (needs nvcc). There is no CPU fallback.")
-    lib = ctypes.CDLL(LIB_PATH)
+    path = os.environ.get("MJB200_LIB", LIB_PATH)  # A/B builds of the same sources (tools/ab_build.py)
+    if not os.path.exists(path):
+      raise RuntimeError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (needs nvcc). There is no CPU fallback.")
+    lib = ctypes.CDLL(path)
     vp, ip = ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)
     lib.mjb_field_name.restype = ctypes.c_char_p
     lib.mjb_field_name.argtypes = [ctypes.c_int, ctypes.c_int]

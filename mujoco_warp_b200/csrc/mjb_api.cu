@@ -252,7 +252,8 @@ static GroupKernel group_kernel_of(int g, bool in_smem) {
 static int launch_group(int g, const MjbModel* m, MjbData* d, KParams& K, uint32_t stages, cudaStream_t stream) {
   MjbData::GroupCfg& c = d->cfg[g];
   if (!c.ready) {
-    const int wpb = warps_per_block(g == G_SOL ? 4 : 8);
+    int wpb = warps_per_block(g == G_SOL ? group_threads(G_SOL) / 32 : 8);
+    if (32 * wpb > group_threads(g)) wpb = group_threads(g) / 32;
     c.scratch_floats = group_scratch_floats(g, m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad);
     const size_t scr_bytes = (size_t)wpb * c.scratch_floats * sizeof(float);
     const bool in_smem =

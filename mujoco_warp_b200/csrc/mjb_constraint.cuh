@@ -13,9 +13,12 @@ struct EfcRow {
   float D, vel, aref, pos, margin, frictionloss;
 };
 
-// constraint.py:53-121
-__device__ __forceinline__ EfcRow efc_row(const KParams& K, float pos_aref, float pos_imp, float invweight, const float* solref,
-                                          const float* solimp, float margin, float vel, float frictionloss) {
+// constraint.py:53-121, the part of _efc_row that does not depend on the row's velocity:
+// D and the spring / damper coefficients of aref = -ki * pos_aref - b * vel.
+struct EfcParams {
+  float D, ki, b;
+};
+__device__ __forceinline__ EfcParams efc_params(const KParams& K, float pos_imp, float invweight, const float* solref, const float* solimp) {
   float timeconst = solref[0];
   const float dampratio = solref[1];
   float dmin = solimp[0], dmax = solimp[1], width = solimp[2], mid = solimp[3], power = solimp[4];
@@ -43,10 +46,20 @@ __device__ __forceinline__ EfcRow efc_row(const KParams& K, float pos_aref, floa
   }
   float imp = clampf(dmin + imp_y * (dmax - dmin), dmin, dmax);
   if (imp_x > 1.0f) imp = dmax;
-  EfcRow r;
+  EfcParams r;
   r.D = 1.0f / fmaxf(invweight * (1.0f - imp) / imp, MJ_MINVAL);
+  r.ki = k * imp;
+  r.b = b;
+  return r;
+}
+
+__device__ __forceinline__ EfcRow efc_row(const KParams& K, float pos_aref, float pos_imp, float invweight, const float* solref,
+                                          const float* solimp, float margin, float vel, float frictionloss) {
+  const EfcParams p = efc_params(K, pos_imp, invweight, solref, solimp);
+  EfcRow r;
+  r.D = p.D;
   r.vel = vel;
-  r.aref = -k * imp * pos_aref - b * vel;
+  r.aref = -p.ki * pos_aref - p.b * vel;
   r.pos = pos_aref + margin;
   r.margin = margin;
   r.frictionloss = frictionloss;
@@ -180,81 +193,115 @@ __device__ __forceinline__ void s_make_constraint(const KParams& K, const unsign
       const float* scom = DW(subtree_com);
       const float* cdof = DW(cdof);
       const float imp2 = K.o.impratio_invsqrt * K.o.impratio_invsqrt;
-      for (int ci = 0; ci < ncon; ci++) {
-        const int cid = DW(wcon)[ci];
-        if (!(K.d.contact_type[cid] & 1)) continue;
-        const int condim = K.d.contact_dim[cid];
-        const float includemargin = K.d.contact_includemargin[cid];
-        const float pos = K.d.contact_dist[cid] - includemargin;
-        if (!(pos < 0.f)) continue;
-        const int nrow = condim == 1 ? 1 : 2 * (condim - 1);
-        const int b1 = MI(geom_bodyid)[K.d.contact_geom[2 * cid]], b2 = MI(geom_bodyid)[K.d.contact_geom[2 * cid + 1]];
-        const int wb1 = MI(body_weldid)[b1], wb2 = MI(body_weldid)[b2];
-        const V3 cpos = ld3(K.d.contact_pos + 3 * cid);
-        const M3 frame = ldm3(K.d.contact_frame + 9 * cid);
-        const float* fri = K.d.contact_friction + 5 * cid;
-        const V3 off1 = cpos - ld3(scom + 3 * MI(body_rootid)[wb1]), off2 = cpos - ld3(scom + 3 * MI(body_rootid)[wb2]);
-        const float invw0 = MR(body_invweight0)[2 * b1] + MR(body_invweight0)[2 * b2];
-        // rows of this contact: address = -1 if beyond njmax (constraint.py:1749)
-        if (lane < nrow) K.d.contact_efc_address[cid * nmp + lane] = (nefc + lane < njmax) ? nefc + lane : -1;
-        // per-dof Jacobian differences projected on the frame axes (support.jac_dof, support.py:397)
-        // proj[0] = normal, proj[1..2] = tangents (translation), proj[3..5] = frame rows . rotation
-        for (int d0 = 0; d0 < nv; d0 += 32) {
-          const int dof = d0 + lane;
-          float proj[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-          if (dof < nv) {
-            const int db = MI(dof_bodyid)[dof];
-            // dof's body is an ancestor-or-self of body  <=>  db <= body < subtreeend[db]
-            const int dend = MI(body_subtreeend)[db];
-            const bool in1 = wb1 != 0 && db <= wb1 && wb1 < dend, in2 = wb2 != 0 && db <= wb2 && wb2 < dend;
-            if (in1 != in2) {  // common ancestors contribute exactly zero
-              const S6 cd = ld6(cdof + 6 * dof);
-              const V3 ang = top(cd), lin = bot(cd);
-              V3 dp = V3{0.f, 0.f, 0.f}, dr = V3{0.f, 0.f, 0.f};
-              if (in2) { dp = dp + lin + cross(ang, off2); dr = dr + ang; }
-              if (in1) { dp = dp - (lin + cross(ang, off1)); dr = dr - ang; }
-#pragma unroll
-              for (int a = 0; a < 3; a++) {
-                proj[a] = frame.m[3 * a] * dp.x + frame.m[3 * a + 1] * dp.y + frame.m[3 * a + 2] * dp.z;
-                proj[3 + a] = frame.m[3 * a] * dr.x + frame.m[3 * a + 1] * dr.y + frame.m[3 * a + 2] * dr.z;
-              }
-            }
-          }
-          for (int dimid = 0; dimid < nrow; dimid++) {
-            const int r = nefc + dimid;
-            float Jv = proj[0];
+      for (int c0 = 0; c0 < ncon; c0 += 32) {
+        // phase A, lane = contact: activity, row count and the velocity-independent row scalars
+        // (_efc_row is evaluated once per contact; the rows of a pyramid differ only in J and vel)
+        const int ci = c0 + lane;
+        int cid = 0, condim = 1, nrow = 0;
+        float pos = 0.f, includemargin = 0.f;
+        EfcParams ep = {0.f, 0.f, 0.f};
+        if (ci < ncon) {
+          cid = DW(wcon)[ci];
+          condim = K.d.contact_dim[cid];
+          includemargin = K.d.contact_includemargin[cid];
+          pos = K.d.contact_dist[cid] - includemargin;
+          if ((K.d.contact_type[cid] & 1) && pos < 0.f) {
+            nrow = condim == 1 ? 1 : 2 * (condim - 1);
+            const int b1 = MI(geom_bodyid)[K.d.contact_geom[2 * cid]], b2 = MI(geom_bodyid)[K.d.contact_geom[2 * cid + 1]];
+            float invweight = MR(body_invweight0)[2 * b1] + MR(body_invweight0)[2 * b2];
             if (condim > 1) {
-              const int dimid2 = dimid / 2 + 1;
-              float Ji = proj[1];
-#pragma unroll
-              for (int a = 2; a < 6; a++) Ji = (dimid2 == a) ? proj[a] : Ji;
-              const float frii = fri[dimid2 - 1];
-              Jv += (dimid & 1) ? -Ji * frii : Ji * frii;
-            }
-            if (r < njmax && dof < np) DW(efc_J)[(size_t)r * np + dof] = dof < nv ? Jv : 0.f;
-          }
-        }
-        __syncwarp();
-        // efc_vel = J . qvel per row, then the row scalars (lane = pyramid edge)
-        for (int dimid = 0; dimid < nrow; dimid++) {
-          const int r = nefc + dimid;
-          if (r >= njmax) continue;
-          float part = 0.f;
-          for (int dof = lane; dof < nv; dof += 32) part += DW(efc_J)[(size_t)r * np + dof] * qvel[dof];
-          const float Jqvel = warp_sum(part);
-          if (lane == dimid) {
-            float invweight = invw0;
-            if (condim > 1) {
-              const float fri0 = fri[0];
+              const float fri0 = K.d.contact_friction[5 * cid];
               invweight = invweight + fri0 * fri0 * invweight;
               invweight = invweight * 2.0f * fri0 * fri0 * imp2;
             }
-            const EfcRow e = efc_row(K, pos, pos, invweight, K.d.contact_solref + 2 * cid, K.d.contact_solimp + 5 * cid, includemargin,
-                                     Jqvel, 0.f);
-            store_row(K, w, r, e, condim == 1 ? CT_CONTACT_FRICTIONLESS : CT_CONTACT_PYRAMIDAL, cid);
+            ep = efc_params(K, pos, invweight, K.d.contact_solref + 2 * cid, K.d.contact_solimp + 5 * cid);
           }
         }
-        nefc += nrow;
+        const int base = nefc + warp_excl_scan(nrow, lane);
+        unsigned act = __ballot_sync(FULL, nrow > 0);
+        nefc = __shfl_sync(FULL, base + nrow, 31);
+        // phase B, one active contact at a time, lane = dof: Jacobian rows and their velocities
+        while (act) {
+          const int src = __ffs(act) - 1;
+          act &= act - 1;
+          const int ccid = __shfl_sync(FULL, cid, src), cdim = __shfl_sync(FULL, condim, src), cnrow = __shfl_sync(FULL, nrow, src);
+          const int row0 = __shfl_sync(FULL, base, src);
+          const float cpos_ = __shfl_sync(FULL, pos, src), cmargin = __shfl_sync(FULL, includemargin, src);
+          const float cD = __shfl_sync(FULL, ep.D, src), cki = __shfl_sync(FULL, ep.ki, src), cb = __shfl_sync(FULL, ep.b, src);
+          const int b1 = MI(geom_bodyid)[K.d.contact_geom[2 * ccid]], b2 = MI(geom_bodyid)[K.d.contact_geom[2 * ccid + 1]];
+          const int wb1 = MI(body_weldid)[b1], wb2 = MI(body_weldid)[b2];
+          const V3 cpos = ld3(K.d.contact_pos + 3 * ccid);
+          const M3 frame = ldm3(K.d.contact_frame + 9 * ccid);
+          const float* fri = K.d.contact_friction + 5 * ccid;
+          const V3 off1 = cpos - ld3(scom + 3 * MI(body_rootid)[wb1]), off2 = cpos - ld3(scom + 3 * MI(body_rootid)[wb2]);
+          // rows of this contact: address = -1 if beyond njmax (constraint.py:1749)
+          if (lane < cnrow) K.d.contact_efc_address[ccid * nmp + lane] = (row0 + lane < njmax) ? row0 + lane : -1;
+          // per-dof Jacobian differences projected on the frame axes (support.jac_dof, support.py:397)
+          // proj[0] = normal, proj[1..2] = tangents (translation), proj[3..5] = frame rows . rotation
+          float S[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // S[a] = sum_dof proj[a] * qvel[dof]
+          for (int d0 = 0; d0 < np; d0 += 32) {
+            const int dof = d0 + lane;
+            float proj[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            if (dof < nv) {
+              const int db = MI(dof_bodyid)[dof];
+              // dof's body is an ancestor-or-self of body  <=>  db <= body < subtreeend[db]
+              const int dend = MI(body_subtreeend)[db];
+              const bool in1 = wb1 != 0 && db <= wb1 && wb1 < dend, in2 = wb2 != 0 && db <= wb2 && wb2 < dend;
+              if (in1 != in2) {  // common ancestors contribute exactly zero
+                const S6 cd = ld6(cdof + 6 * dof);
+                const V3 ang = top(cd), lin = bot(cd);
+                V3 dp = lin + cross(ang, in2 ? off2 : off1), dr = ang;
+                if (in1) { dp = V3{0.f, 0.f, 0.f} - dp; dr = V3{0.f, 0.f, 0.f} - dr; }
+                const float qv = qvel[dof];
+#pragma unroll
+                for (int a = 0; a < 3; a++) {
+                  proj[a] = frame.m[3 * a] * dp.x + frame.m[3 * a + 1] * dp.y + frame.m[3 * a + 2] * dp.z;
+                  proj[3 + a] = frame.m[3 * a] * dr.x + frame.m[3 * a + 1] * dr.y + frame.m[3 * a + 2] * dr.z;
+                  S[a] += proj[a] * qv;
+                  S[3 + a] += proj[3 + a] * qv;
+                }
+              }
+            }
+            if (dof < np) {
+              for (int dimid = 0; dimid < cnrow; dimid++) {
+                const int r = row0 + dimid;
+                float Jv = proj[0];
+                if (cdim > 1) {
+                  const int dimid2 = dimid / 2 + 1;
+                  float Ji = proj[1];
+#pragma unroll
+                  for (int a = 2; a < 6; a++) Ji = (dimid2 == a) ? proj[a] : Ji;
+                  const float frii = fri[dimid2 - 1];
+                  Jv += (dimid & 1) ? -Ji * frii : Ji * frii;
+                }
+                if (r < njmax) DW(efc_J)[(size_t)r * np + dof] = Jv;
+              }
+            }
+          }
+          // efc_vel = J . qvel of row dimid = S[0] +- friction * S[dimid / 2 + 1]
+#pragma unroll
+          for (int a = 0; a < 6; a++)
+            if (a < cdim) S[a] = warp_sum(S[a]);
+          if (lane < cnrow && row0 + lane < njmax) {
+            float vel = S[0];
+            if (cdim > 1) {
+              const int dimid2 = lane / 2 + 1;
+              float Si = S[1];
+#pragma unroll
+              for (int a = 2; a < 6; a++) Si = (dimid2 == a) ? S[a] : Si;
+              const float frii = fri[dimid2 - 1];
+              vel += (lane & 1) ? -Si * frii : Si * frii;
+            }
+            EfcRow e;
+            e.D = cD;
+            e.vel = vel;
+            e.aref = -cki * cpos_ - cb * vel;
+            e.pos = cpos_ + cmargin;
+            e.margin = cmargin;
+            e.frictionloss = 0.f;
+            store_row(K, w, row0 + lane, e, cdim == 1 ? CT_CONTACT_FRICTIONLESS : CT_CONTACT_PYRAMIDAL, ccid);
+          }
+        }
       }
     }
   }

@@ -10,6 +10,18 @@
 // The step is issued as one launch per stage GROUP.  Every group is its own kernel instantiation:
 // compact code (the instruction cache holds it while warps drift apart), its own register budget
 // and its own shared-memory scratch.  Intermediate results travel between groups through L2/HBM.
+#ifndef MJB_SOL_MIN_CTAS
+#define MJB_SOL_MIN_CTAS 5
+#endif
+#ifndef MJB_SOL_SYNC
+#define MJB_SOL_SYNC 0
+#endif
+#ifndef MJB_SOL_THREADS
+#define MJB_SOL_THREADS 128
+#endif
+#ifndef MJB_COL_MIN_CTAS
+#define MJB_COL_MIN_CTAS 2
+#endif
 enum StageGroup { G_POS = 0, G_COL, G_CON, G_VEL, G_SOL, G_EUL, G_COUNT };
 
 __host__ __device__ inline uint32_t group_mask(int g) {
@@ -67,8 +79,12 @@ __device__ __forceinline__ void stage_model_blob(unsigned char* dst, const unsig
   }
 }
 
+// CTA width and minimum resident CTAs per SM of a group (register budget = 65536 / (threads x CTAs))
+__host__ __device__ constexpr int group_threads(int g) { return g == G_SOL ? MJB_SOL_THREADS : 256; }
+__host__ __device__ constexpr int group_min_ctas(int g) { return g == G_SOL ? MJB_SOL_MIN_CTAS : (g == G_COL ? MJB_COL_MIN_CTAS : 1); }
+
 template <int G, bool BLOB_IN_SMEM>
-__global__ void __launch_bounds__(256) mjb_group_kernel(const __grid_constant__ KParams K) {
+__global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group_kernel(const __grid_constant__ KParams K) {
   extern __shared__ __align__(16) unsigned char smem[];
   const unsigned char* mb;
   float* scr_base;
@@ -86,6 +102,12 @@ __global__ void __launch_bounds__(256) mjb_group_kernel(const __grid_constant__ 
   const int lane = threadIdx.x & 31, warp = __shfl_sync(FULL, threadIdx.x >> 5, 0), wpb = blockDim.x >> 5;
   float* scr = scr_base + (size_t)warp * K.scratch_floats;
   const uint32_t st = K.stages;
+#if MJB_SOL_SYNC
+  if constexpr (G == G_SOL) {
+    s_solve_cta(K, lane, warp, wpb, scr);
+    return;
+  }
+#endif
   for (int w = blockIdx.x * wpb + warp; w < K.dsz.nworld; w += gridDim.x * wpb) {
     if constexpr (G == G_POS) {
       if (st & MJB_STAGE_KINEMATICS) s_kinematics(K, mb, w, lane);
@@ -123,9 +145,10 @@ __global__ void __launch_bounds__(256) mjb_solve_m_kernel(const __grid_constant_
   float* x = c.x;
   for (int w = blockIdx.x * wpb + warp; w < K.dsz.nworld; w += gridDim.x * wpb) {
     load_rows(scr, ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
+    chol_rdiag(scr, ld, nv, c.rd, lane);
     for (int i = lane; i < nv; i += 32) x[i] = K.y[(size_t)w * nv + i];
     __syncwarp();
-    warp_chol_solve(scr, ld, nv, x, lane);
+    warp_chol_solve<false>(scr, ld, nv, c.rd, x, lane);
     for (int i = lane; i < nv; i += 32) K.x[(size_t)w * nv + i] = x[i];
     __syncwarp();
   }

@@ -8,6 +8,7 @@
 // deterministic.
 #pragma once
 
+
 #include "mjb_types.cuh"
 
 // ---------------------------------------------------------------------------------------------
@@ -221,17 +222,18 @@ __device__ __forceinline__ void s_crb(const KParams& K, const unsigned char* mb,
 // bank-conflict free.
 // ---------------------------------------------------------------------------------------------
 __host__ __device__ inline int chol_ld(int nv_pad) { return ((nv_pad >> 2) & 1) ? nv_pad : nv_pad + 4; }
-// compact scratch of the stages that only factor / solve with one matrix: L (nv x ld) | x (nv_pad)
+// compact scratch of the stages that only factor / solve with one matrix: L (nv x ld) | x (nv_pad) | rd (nv_pad)
 struct CholScr {
-  float *L, *x;
+  float *L, *x, *rd;  // factor, right-hand side / solution, reciprocal diagonal of L
   int ld;
 };
-__host__ __device__ inline int chol_scratch_floats(int nv, int nv_pad) { return nv * chol_ld(nv_pad) + nv_pad; }
+__host__ __device__ inline int chol_scratch_floats(int nv, int nv_pad) { return nv * chol_ld(nv_pad) + 2 * nv_pad; }
 __device__ __forceinline__ CholScr chol_scr(float* scr, int nv, int nvp) {
   CholScr c;
   c.ld = chol_ld(nvp);
   c.L = scr;
   c.x = scr + nv * c.ld;
+  c.rd = c.x + nvp;
   return c;
 }
 struct SolverScr {
@@ -386,7 +388,153 @@ __device__ __noinline__ void warp_chol_solve_reg(const float* L, int ld, int n, 
   __syncwarp();
 }
 
-__device__ __forceinline__ void warp_cholesky(float* A, int ld, int n, int lane) {
+__device__ __forceinline__ float dot4(const float4 a, const float4 b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
+
+__device__ __noinline__ void warp_cholesky_blk(float* A, int ld, int n, float* rdiag, int lane) {
+  const int nb = (n + 3) >> 2;
+  #pragma unroll 1
+  for (int J = 0; J < nb; J++) {
+    const int c0 = 4 * J;
+    // rows of the diagonal block; rows past the end alias the last row and are masked below
+    const int r1 = min(c0 + 1, n - 1), r2 = min(c0 + 2, n - 1), r3 = min(c0 + 3, n - 1);
+    const bool v1 = c0 + 1 < n, v2 = c0 + 2 < n, v3 = c0 + 3 < n;
+    const float4* p0 = reinterpret_cast<const float4*>(A + c0 * ld);
+    const float4* p1 = reinterpret_cast<const float4*>(A + r1 * ld);
+    const float4* p2 = reinterpret_cast<const float4*>(A + r2 * ld);
+    const float4* p3 = reinterpret_cast<const float4*>(A + r3 * ld);
+    #pragma unroll 1
+    for (int i = lane; i < n; i += 32) {
+      if (i < c0) continue;
+      float4* own = reinterpret_cast<float4*>(A + i * ld);
+      float4 acc = own[J];
+      #pragma unroll 1
+      for (int q = 0; q < J; q++) {
+        const float4 o = own[q];
+        acc.x -= dot4(o, p0[q]);
+        acc.y -= dot4(o, p1[q]);
+        acc.z -= dot4(o, p2[q]);
+        acc.w -= dot4(o, p3[q]);
+      }
+      own[J] = acc;
+    }
+    __syncwarp();
+    // 4x4 diagonal block -> its Cholesky factor (all lanes, from broadcast loads)
+    const float4 s0 = p0[J], s1 = p1[J], s2 = p2[J], s3 = p3[J];
+    const float d0 = fmaxf(s0.x, MJ_MINVAL), i0 = rsqrtf(d0);
+    const float l10 = v1 ? s1.x * i0 : 0.f;
+    const float d1 = v1 ? fmaxf(s1.y - l10 * l10, MJ_MINVAL) : 1.f, i1 = rsqrtf(d1);
+    const float l20 = v2 ? s2.x * i0 : 0.f, l21 = v2 ? (s2.y - l20 * l10) * i1 : 0.f;
+    const float d2 = v2 ? fmaxf(s2.z - l20 * l20 - l21 * l21, MJ_MINVAL) : 1.f, i2 = rsqrtf(d2);
+    const float l30 = v3 ? s3.x * i0 : 0.f, l31 = v3 ? (s3.y - l30 * l10) * i1 : 0.f, l32 = v3 ? (s3.z - l30 * l20 - l31 * l21) * i2 : 0.f;
+    const float d3 = v3 ? fmaxf(s3.w - l30 * l30 - l31 * l31 - l32 * l32, MJ_MINVAL) : 1.f, i3 = rsqrtf(d3);
+    if (lane == 0) reinterpret_cast<float4*>(rdiag)[J] = make_float4(i0, i1, i2, i3);  // 1 / L_jj
+    __syncwarp();
+    #pragma unroll 1
+    for (int i = lane; i < n; i += 32) {
+      if (i < c0) continue;
+      float4* own = reinterpret_cast<float4*>(A + i * ld);
+      const float4 a = own[J];
+      const int m = i - c0;  // position inside the diagonal block (>= 4: below it)
+      float4 l;
+      l.x = (m == 0) ? d0 * i0 : a.x * i0;
+      l.y = (m == 1) ? d1 * i1 : (a.y - l.x * l10) * i1;
+      l.z = (m == 2) ? d2 * i2 : (a.z - l.x * l20 - l.y * l21) * i2;
+      l.w = (m == 3) ? d3 * i3 : (a.w - l.x * l30 - l.y * l31 - l.z * l32) * i3;
+      // zero the strictly upper part of the diagonal block and the padding columns
+      if (m < 1 || !v1) l.y = 0.f;
+      if (m < 2 || !v2) l.z = 0.f;
+      if (m < 3 || !v3) l.w = 0.f;
+      own[J] = l;
+    }
+    __syncwarp();
+  }
+}
+
+// the 4x4 diagonal block J of L (rows/columns past n behave as identity)
+struct DiagBlock {
+  float r0, r1, r2, r3;  // reciprocal diagonal
+  float l10, l20, l21, l30, l31, l32;
+};
+__device__ __forceinline__ DiagBlock load_diag_block(const float* L, int ld, int n, const float* rdiag, int J) {
+  const int c0 = 4 * J;
+  const bool v1 = c0 + 1 < n, v2 = c0 + 2 < n, v3 = c0 + 3 < n;
+  const float4 rd = reinterpret_cast<const float4*>(rdiag)[J];
+  const float4 s1 = reinterpret_cast<const float4*>(L + min(c0 + 1, n - 1) * ld)[J];
+  const float4 s2 = reinterpret_cast<const float4*>(L + min(c0 + 2, n - 1) * ld)[J];
+  const float4 s3 = reinterpret_cast<const float4*>(L + min(c0 + 3, n - 1) * ld)[J];
+  DiagBlock b;
+  b.r0 = rd.x; b.r1 = rd.y; b.r2 = rd.z; b.r3 = rd.w;
+  b.l10 = v1 ? s1.x : 0.f;
+  b.l20 = v2 ? s2.x : 0.f;
+  b.l21 = v2 ? s2.y : 0.f;
+  b.l30 = v3 ? s3.x : 0.f;
+  b.l31 = v3 ? s3.y : 0.f;
+  b.l32 = v3 ? s3.z : 0.f;
+  return b;
+}
+
+// reciprocal diagonal of a factor that was loaded rather than computed here (padding entries are 1)
+__device__ __forceinline__ void chol_rdiag(const float* L, int ld, int n, float* rdiag, int lane) {
+  for (int i = lane; i < ((n + 3) & ~3); i += 32) rdiag[i] = i < n ? 1.0f / L[i * ld + i] : 1.0f;
+  __syncwarp();
+}
+
+// x <- (L L^T)^-1 x with L and x in shared memory (x padded to a multiple of 4 entries).
+// Blocked substitution: the 4x4 diagonal systems are solved redundantly by all lanes, the
+// off-diagonal part is one strip (forward: 128-bit row load, backward: four column loads) per lane.
+__device__ __noinline__ void warp_chol_solve_blk(const float* L, int ld, int n, const float* rdiag, float* x, int lane) {
+  const int nb = (n + 3) >> 2;
+  float4* x4 = reinterpret_cast<float4*>(x);
+  #pragma unroll 1
+  for (int i = n + lane; i < 4 * nb; i += 32) x[i] = 0.f;
+  __syncwarp();
+  #pragma unroll 1
+  for (int J = 0; J < nb; J++) {  // forward: L y = b
+    const DiagBlock b = load_diag_block(L, ld, n, rdiag, J);
+    const float4 t = x4[J];
+    float4 y;
+    y.x = t.x * b.r0;
+    y.y = (t.y - b.l10 * y.x) * b.r1;
+    y.z = (t.z - b.l20 * y.x - b.l21 * y.y) * b.r2;
+    y.w = (t.w - b.l30 * y.x - b.l31 * y.y - b.l32 * y.z) * b.r3;
+    __syncwarp();
+    if (lane == 0) x4[J] = y;
+    #pragma unroll 1
+    for (int i = 4 * J + 4 + lane; i < n; i += 32) x[i] -= dot4(reinterpret_cast<const float4*>(L + i * ld)[J], y);
+    __syncwarp();
+  }
+  #pragma unroll 1
+  for (int J = nb - 1; J >= 0; J--) {  // backward: L^T x = y
+    const DiagBlock b = load_diag_block(L, ld, n, rdiag, J);
+    const float4 t = x4[J];
+    float4 z;
+    z.w = t.w * b.r3;
+    z.z = (t.z - b.l32 * z.w) * b.r2;
+    z.y = (t.y - b.l21 * z.z - b.l31 * z.w) * b.r1;
+    z.x = (t.x - b.l10 * z.y - b.l20 * z.z - b.l30 * z.w) * b.r0;
+    __syncwarp();
+    if (lane == 0) x4[J] = z;
+    const int c0 = 4 * J;
+    const float* q0 = L + c0 * ld;
+    const float* q1 = L + min(c0 + 1, n - 1) * ld;
+    const float* q2 = L + min(c0 + 2, n - 1) * ld;
+    const float* q3 = L + min(c0 + 3, n - 1) * ld;
+    // rows past n have z == 0 there (identity padding), so the aliased loads contribute nothing
+    #pragma unroll 1
+    for (int i = lane; i < c0; i += 32) x[i] -= q0[i] * z.x + q1[i] * z.y + q2[i] * z.z + q3[i] * z.w;
+    __syncwarp();
+  }
+}
+
+// REG = true: register-resident variant (fewest instructions, large straight-line code, 60+ registers):
+// used by the solver kernel.  REG = false: blocked shared-memory variant with rolled loops (compact code,
+// few registers): used by the smooth-dynamics kernels, where occupancy matters more.
+template <bool REG>
+__device__ __forceinline__ void warp_cholesky(float* A, int ld, int n, float* rdiag, int lane) {
+  if (!REG) {
+    warp_cholesky_blk(A, ld, n, rdiag, lane);
+    return;
+  }
   switch ((n + 3) >> 2) {
     case 1: warp_cholesky_reg<4>(A, ld, n, lane); break;
     case 2: warp_cholesky_reg<8>(A, ld, n, lane); break;
@@ -399,7 +547,12 @@ __device__ __forceinline__ void warp_cholesky(float* A, int ld, int n, int lane)
     default: warp_cholesky_smem(A, ld, n, lane); break;
   }
 }
-__device__ __forceinline__ void warp_chol_solve(const float* L, int ld, int n, float* x, int lane) {
+template <bool REG>
+__device__ __forceinline__ void warp_chol_solve(const float* L, int ld, int n, const float* rdiag, float* x, int lane) {
+  if (!REG) {
+    warp_chol_solve_blk(L, ld, n, rdiag, x, lane);
+    return;
+  }
   switch ((n + 3) >> 2) {
     case 1: warp_chol_solve_reg<4>(L, ld, n, x, lane); break;
     case 2: warp_chol_solve_reg<8>(L, ld, n, x, lane); break;
@@ -452,7 +605,7 @@ __device__ __forceinline__ void store_qLD(const KParams& K, int w, int lane, con
 __device__ __forceinline__ void s_factor_m(const KParams& K, int w, int lane, float* scr) {
   const CholScr s = chol_scr(scr, K.ms.nv, K.ms.nv_pad);
   load_rows(s.L, s.ld, DW(qM), K.ms.nv_pad, K.ms.nv, lane, nullptr, 0.f);
-  warp_cholesky(s.L, s.ld, K.ms.nv, lane);
+  warp_cholesky<false>(s.L, s.ld, K.ms.nv, s.rd, lane);
   store_qLD(K, w, lane, s.L, s.ld);
   __syncwarp();
 }
@@ -715,13 +868,14 @@ __device__ __forceinline__ void s_fwd_acceleration(const KParams& K, const unsig
   __syncwarp();
   if (factorize) {
     load_rows(s.L, s.ld, DW(qM), K.ms.nv_pad, nv, lane, nullptr, 0.f);
-    warp_cholesky(s.L, s.ld, nv, lane);
+    warp_cholesky<false>(s.L, s.ld, nv, s.rd, lane);
     store_qLD(K, w, lane, s.L, s.ld);
   } else {
     load_rows(s.L, s.ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
+    chol_rdiag(s.L, s.ld, nv, s.rd, lane);
   }
   __syncwarp();
-  warp_chol_solve(s.L, s.ld, nv, x, lane);
+  warp_chol_solve<false>(s.L, s.ld, nv, s.rd, x, lane);
   for (int i = lane; i < nv; i += 32) DW(qacc_smooth)[i] = x[i];
   __syncwarp();
 }
@@ -735,10 +889,10 @@ __device__ __forceinline__ void s_euler(const KParams& K, const unsigned char* m
   const bool damp = !(K.o.disableflags & (DSBL_EULERDAMP | DSBL_DAMPER));
   if (damp) {  // (M + dt diag(damping)) qacc' = Ma
     load_rows(s.L, s.ld, DW(qM), K.ms.nv_pad, nv, lane, MR(dof_damping), dt);
-    warp_cholesky(s.L, s.ld, nv, lane);
+    warp_cholesky<false>(s.L, s.ld, nv, s.rd, lane);
     for (int i = lane; i < nv; i += 32) x[i] = DW(efc_Ma)[i];
     __syncwarp();
-    warp_chol_solve(s.L, s.ld, nv, x, lane);
+    warp_chol_solve<false>(s.L, s.ld, nv, s.rd, x, lane);
   } else {
     for (int i = lane; i < nv; i += 32) x[i] = DW(qacc)[i];
     __syncwarp();

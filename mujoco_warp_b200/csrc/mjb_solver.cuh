@@ -246,23 +246,35 @@ __device__ __forceinline__ void solve_direction(const KParams& K, int lane, cons
     float4* l4 = reinterpret_cast<float4*>(s.L);
     for (int i = lane; i < (nv * ld) >> 2; i += 32) l4[i] = h4[i];
     __syncwarp();
-    warp_cholesky(s.L, ld, nv, lane);
+    warp_cholesky<true>(s.L, ld, nv, nullptr, lane);
   }
   for (int i = lane; i < nv; i += 32) s.x[i] = s.grad[i];
   __syncwarp();
-  warp_chol_solve(s.L, ld, nv, s.x, lane);
+  warp_chol_solve<true>(s.L, ld, nv, nullptr, s.x, lane);
 }
 
-__device__ __forceinline__ void s_solve(const KParams& K, const unsigned char* mb, int w, int lane, float* scr) {
+// Solver state of one world that lives in registers across passes.
+struct SolveState {
+  int it, niter, nefc, ne, nf;
+  float cost, gauss, prev_cost, search_dot;
+};
+
+// init_context part 1 (solver.py:3257): loads the world into shared memory.  Returns false when there is
+// nothing to solve (solver.py:3298).
+__device__ __forceinline__ bool solve_begin(const KParams& K, int w, int lane, const SolverScr& s, SolveState& st) {
   const int nv = K.ms.nv, np = K.ms.nv_pad, njmax = K.dsz.njmax;
-  if (njmax == 0 || nv == 0) {  // solver.py:3298
+  if (njmax == 0 || nv == 0) {
     for (int i = lane; i < nv; i += 32) DW(qacc)[i] = DW(qacc_smooth)[i];
     if (lane == 0) DW(solver_niter)[0] = 0;
     __syncwarp();
-    return;
+    return false;
   }
-  const SolverScr s = solver_scr(scr, nv, np, K.dsz.njmax_pad);
-  const int nefc = uniform_i(min(DW(nefc)[0], njmax)), ne = uniform_i(DW(ne)[0]), nf = uniform_i(DW(nf)[0]);
+  st.nefc = uniform_i(min(DW(nefc)[0], njmax));
+  st.ne = uniform_i(DW(ne)[0]);
+  st.nf = uniform_i(DW(nf)[0]);
+  st.it = 0;
+  st.niter = 0;
+  st.cost = st.gauss = st.prev_cost = st.search_dot = 0.f;
   const bool newton = K.o.solver == SOLVER_NEWTON;
   const float* src = (K.o.disableflags & DSBL_WARMSTART) ? DW(qacc_smooth) : DW(qacc_warmstart);
   for (int i = lane; i < np; i += 32) {
@@ -270,60 +282,75 @@ __device__ __forceinline__ void s_solve(const KParams& K, const unsigned char* m
     s.qfs[i] = i < nv ? DW(qfrc_smooth)[i] : 0.f;
     s.search[i] = 0.f;
   }
-  for (int r = lane; r < nefc; r += 32) s.D[r] = DW(efc_D)[r];
+  for (int r = lane; r < st.nefc; r += 32) s.D[r] = DW(efc_D)[r];
   __syncwarp();
-  // init_context, solver.py:3257: Jaref = J qacc - aref, Ma = M qacc
+  // Jaref = J qacc - aref, Ma = M qacc
   const int n4 = np >> 2;
-  for (int r = lane; r < nefc; r += 32) s.Jaref[r] = row_dot(DW(efc_J) + (size_t)r * np, s.qacc, n4) - DW(efc_aref)[r];
+  for (int r = lane; r < st.nefc; r += 32) s.Jaref[r] = row_dot(DW(efc_J) + (size_t)r * np, s.qacc, n4) - DW(efc_aref)[r];
   for (int i = lane; i < nv; i += 32) s.Ma[i] = row_dot(DW(qM) + (size_t)i * np, s.qacc, n4);
   __syncwarp();
   // Newton: H starts as qM.  CG: the preconditioner is the factor of qM (qLD).
   load_rows(newton ? s.H : s.L, s.ld, newton ? DW(qM) : DW(qLD), newton ? np : nv, nv, lane, nullptr, 0.f);
-  float cost = 0.f, gauss = 0.f, prev_cost = 0.f, search_dot = 0.f;
-  const float scl = 1.0f / (K.o.meaninertia * (float)nv);
+  return true;
+}
+
+// One pass.  Pass 0 is the rest of init_context (constraint update, gradient, first search direction);
+// passes 1.. are solver.py:3188 _solver_iteration.  One body keeps a single copy of every routine in
+// the instruction stream.  Returns true when the world is finished.
+__device__ __forceinline__ bool solve_pass(const KParams& K, int w, int lane, const SolverScr& s, SolveState& st) {
+  const int nv = K.ms.nv, np = K.ms.nv_pad;
+  const bool newton = K.o.solver == SOLVER_NEWTON;
+  const bool init = st.it == 0;
   float* prev_grad = s.H;  // CG only (H is unused by CG)
   float* prev_Mgrad = s.H + np;
-  int niter = 0;
-  // Pass 0 is solver.py:3257 init_context (constraint update, gradient, first search direction);
-  // passes 1.. are solver.py:3188 _solver_iteration.  One loop body keeps a single copy of every
-  // routine in the instruction stream.
-  for (int it = 0; it <= K.o.iterations; it++) {
-    const bool init = it == 0;
-    if (!init) {
-      linesearch(K, w, lane, s, nefc, ne, nf, gauss, search_dot);
-      if (!newton) {
-        for (int i = lane; i < nv; i += 32) { prev_grad[i] = s.grad[i]; prev_Mgrad[i] = s.x[i]; }
-        __syncwarp();
-      }
-      prev_cost = cost;
+  if (!init) {
+    linesearch(K, w, lane, s, st.nefc, st.ne, st.nf, st.gauss, st.search_dot);
+    if (!newton) {
+      for (int i = lane; i < nv; i += 32) { prev_grad[i] = s.grad[i]; prev_Mgrad[i] = s.x[i]; }
+      __syncwarp();
     }
-    bool any_change;
-    update_constraint(K, w, lane, s, nefc, ne, nf, init, cost, gauss, any_change);
-    if (newton && any_change) h_accumulate(K, w, lane, s, nefc);
-    solve_direction(K, lane, s, newton && (any_change || init));
-    float beta = 0.f;
-    if (!newton && !init) {  // Polak-Ribiere, solver.py:3081
-      float num = 0.f, den = 0.f;
-      for (int i = lane; i < nv; i += 32) { num += s.grad[i] * (s.x[i] - prev_Mgrad[i]); den += prev_grad[i] * prev_Mgrad[i]; }
-      beta = fmaxf(0.f, warp_sum(num) / fmaxf(MJ_MINVAL, warp_sum(den)));
-    }
-    float grad_dot = 0.f;
-    search_dot = 0.f;
-    for (int i = lane; i < nv; i += 32) {
-      float v = -s.x[i];
-      if (!newton && !init) v += beta * s.search[i];
-      s.search[i] = v;
-      search_dot += v * v;
-      grad_dot += s.grad[i] * s.grad[i];
-    }
-    search_dot = warp_sum(search_dot);
-    grad_dot = warp_sum(grad_dot);
-    __syncwarp();
-    if (init) continue;
-    niter++;
-    const float improvement = (prev_cost - cost) * scl, gradient = sqrtf(grad_dot) * scl;  // solver.py:3177
-    if (uniform_b(improvement < K.o.tolerance || gradient < K.o.tolerance)) break;
+    st.prev_cost = st.cost;
   }
+  bool any_change;
+  update_constraint(K, w, lane, s, st.nefc, st.ne, st.nf, init, st.cost, st.gauss, any_change);
+  // solver.py:3177 solve_done.  The reference evaluates it after the next search direction has been
+  // computed; the direction of a finished world is never used, so it is tested first and the Hessian
+  // update, factorisation and solve of the last pass are skipped (outputs are identical).
+  if (!init) {
+    float grad_dot = 0.f;
+    for (int i = lane; i < nv; i += 32) grad_dot += s.grad[i] * s.grad[i];
+    grad_dot = warp_sum(grad_dot);
+    st.niter++;
+    const float scl = 1.0f / (K.o.meaninertia * (float)nv);
+    const float improvement = (st.prev_cost - st.cost) * scl, gradient = sqrtf(grad_dot) * scl;
+    if (uniform_b(improvement < K.o.tolerance || gradient < K.o.tolerance) || st.niter >= K.o.iterations) return true;
+  } else if (K.o.iterations <= 0) {
+    return true;
+  }
+  if (newton && any_change) h_accumulate(K, w, lane, s, st.nefc);
+  solve_direction(K, lane, s, newton && (any_change || init));
+  float beta = 0.f;
+  if (!newton && !init) {  // Polak-Ribiere, solver.py:3081
+    float num = 0.f, den = 0.f;
+    for (int i = lane; i < nv; i += 32) { num += s.grad[i] * (s.x[i] - prev_Mgrad[i]); den += prev_grad[i] * prev_Mgrad[i]; }
+    beta = fmaxf(0.f, warp_sum(num) / fmaxf(MJ_MINVAL, warp_sum(den)));
+  }
+  float search_dot = 0.f;
+  for (int i = lane; i < nv; i += 32) {
+    float v = -s.x[i];
+    if (!newton && !init) v += beta * s.search[i];
+    s.search[i] = v;
+    search_dot += v * v;
+  }
+  st.search_dot = warp_sum(search_dot);
+  __syncwarp();
+  st.it++;
+  return false;
+}
+
+__device__ __forceinline__ void solve_finish(const KParams& K, int w, int lane, const SolverScr& s, const SolveState& st) {
+  const int nv = K.ms.nv;
+  const int niter = st.niter;
   for (int i = lane; i < nv; i += 32) {
     const float q = s.qacc[i];
     DW(qacc)[i] = q;
@@ -332,4 +359,39 @@ __device__ __forceinline__ void s_solve(const KParams& K, const unsigned char* m
   }
   if (lane == 0) DW(solver_niter)[0] = niter;
   __syncwarp();
+}
+
+// one world, start to finish (used when the solver is fused with other stages)
+__device__ __forceinline__ void s_solve(const KParams& K, const unsigned char* mb, int w, int lane, float* scr) {
+  const SolverScr s = solver_scr(scr, K.ms.nv, K.ms.nv_pad, K.dsz.njmax_pad);
+  SolveState st;
+  if (!solve_begin(K, w, lane, s, st)) return;
+  while (!solve_pass(K, w, lane, s, st)) {
+  }
+  solve_finish(K, w, lane, s, st);
+}
+
+// All worlds of a CTA, pass-synchronous: the warps of the CTA take their solver passes together (a
+// CTA-wide barrier per pass), each on its own world and at its own iteration number; a warp whose world
+// has converged picks up its next world and rejoins at pass 0.  The barrier keeps the resident warps of
+// an SM in the same phase of the (large) solver code, so they share instruction-cache lines instead of
+// evicting each other's.
+__device__ __forceinline__ void s_solve_cta(const KParams& K, int lane, int warp, int wpb, float* scr) {
+  const SolverScr s = solver_scr(scr, K.ms.nv, K.ms.nv_pad, K.dsz.njmax_pad);
+  const int stride = gridDim.x * wpb;
+  int w = blockIdx.x * wpb + warp;
+  SolveState st;
+  bool running = false;  // a world is loaded and not yet finished
+  while (true) {
+    while (!running && w < K.dsz.nworld) {  // fetch worlds until one needs solving
+      running = solve_begin(K, w, lane, s, st);
+      if (!running) w += stride;
+    }
+    if (!__syncthreads_or(running ? 1 : 0)) break;
+    if (running && solve_pass(K, w, lane, s, st)) {
+      solve_finish(K, w, lane, s, st);
+      running = false;
+      w += stride;
+    }
+  }
 }
