@@ -88,15 +88,19 @@ __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group
   extern __shared__ __align__(16) unsigned char smem[];
   const unsigned char* mb;
   float* scr_base;
+  // let the next group's grid start launching as soon as SM resources free up (PDL)
+  asm volatile("griddepcontrol.launch_dependents;");
   if (BLOB_IN_SMEM) {
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem + K.blob_bytes);
-    stage_model_blob(smem, K.blob, K.blob_bytes, bar);
+    stage_model_blob(smem, K.blob, K.blob_bytes, bar);  // the model is constant: no dependency on the previous grid
     mb = smem;
     scr_base = reinterpret_cast<float*>(smem + K.blob_bytes + 16);
   } else {
     mb = K.blob;
     scr_base = reinterpret_cast<float*>(smem);
   }
+  // Data written by the previous group is visible only after the previous grid has completed
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   // broadcast from lane 0 so that the compiler can treat the warp index (and every loop / branch
   // that depends on it) as warp-uniform
   const int lane = threadIdx.x & 31, warp = __shfl_sync(FULL, threadIdx.x >> 5, 0), wpb = blockDim.x >> 5;
