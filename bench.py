@@ -299,27 +299,58 @@ def main():
     # ---- end to end through the public API with HOST buffers: per step H2D of the controls from
     # pinned memory, mjw.step, D2H of the observation (qpos | qvel) into pinned memory
     nu, nq, nv = m.nu, m.nq, m.nv
-    h_ctrl = torch.empty((nworld, nu), dtype=torch.float32).pin_memory()
-    h_ctrl.uniform_(-0.1, 0.1)
-    h_obs = torch.empty((nworld, nq + nv), dtype=torch.float32).pin_memory()
+    h_ctrl = [torch.empty((nworld, nu), dtype=torch.float32).pin_memory() for _ in range(2)]
+    for h in h_ctrl:
+      h.uniform_(-0.1, 0.1)
+    h_obs = [torch.empty((nworld, nq + nv), dtype=torch.float32).pin_memory() for _ in range(2)]
+    d_ctrl_stage = [torch.empty_like(d.ctrl) for _ in range(2)]
+    d_obs = [torch.empty((nworld, nq + nv), dtype=torch.float32, device="cuda") for _ in range(2)]
     Ke = min(K, 100)
+    copy_stream = torch.cuda.Stream()
+    ev_ctrl = [torch.cuda.Event() for _ in range(2)]   # ctrl k uploaded
+    ev_step = [torch.cuda.Event() for _ in range(2)]   # step k finished, observation k snapshotted
+    ev_obs = [torch.cuda.Event() for _ in range(2)]    # observation k on the host
 
-    def e2e_step():
-      d.ctrl.copy_(h_ctrl, non_blocking=True)
-      mjw.step(m, d)
-      h_obs[:, :nq].copy_(d.qpos, non_blocking=True)
-      h_obs[:, nq:].copy_(d.qvel, non_blocking=True)
-      stream.synchronize()  # the caller consumes the observation every step
+    # Software pipeline over two buffers, every transfer inside the timed region:
+    #   copy stream:    H2D ctrl[k+1] into a staging buffer | D2H obs[k] (after step k)
+    #   compute stream: ctrl <- staged ctrl[k], mjw.step (public API), snapshot qpos|qvel
+    #   host:           waits for obs[k-1] while step k runs (one step of observation latency)
+    def upload(k):
+      with torch.cuda.stream(copy_stream):
+        d_ctrl_stage[k & 1].copy_(h_ctrl[k & 1], non_blocking=True)
+        ev_ctrl[k & 1].record(copy_stream)
 
-    for _ in range(3):
-      e2e_step()
+    def e2e_step(k):
+      upload(k + 1)
+      stream.wait_event(ev_ctrl[k & 1])
+      d.ctrl.copy_(d_ctrl_stage[k & 1], non_blocking=True)
+      if graph is not None:
+        graph.replay()  # mjw.step captured once, as the reference's benchmark loop does (benchmark.py:124-137)
+      else:
+        mjw.step(m, d)
+      d_obs[k & 1][:, :nq].copy_(d.qpos, non_blocking=True)
+      d_obs[k & 1][:, nq:].copy_(d.qvel, non_blocking=True)
+      ev_step[k & 1].record(stream)
+      with torch.cuda.stream(copy_stream):
+        copy_stream.wait_event(ev_step[k & 1])
+        h_obs[k & 1].copy_(d_obs[k & 1], non_blocking=True)
+        ev_obs[k & 1].record(copy_stream)
+      if k > 0:
+        ev_obs[(k - 1) & 1].synchronize()  # the caller consumes observation k-1 here
+
+    def e2e_run(n):
+      upload(0)
+      for k in range(n):
+        e2e_step(k)
+      ev_obs[(n - 1) & 1].synchronize()
+      torch.cuda.synchronize()
+
+    e2e_run(4)
     if dist is not None:
       dist.barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    for _ in range(Ke):
-      e2e_step()
-    torch.cuda.synchronize()
+    e2e_run(Ke)
     e2e_s = time.perf_counter() - t0
 
   nan_worlds = int(torch.isnan(d.qpos).any(dim=1).sum())

@@ -120,19 +120,35 @@ def check(lib, rc: int):
     raise RuntimeError(f"libmjb200 error {rc}: {lib.mjb_last_error().decode()}")
 
 
+_OPT_TENSORS = ("timestep", "tolerance", "ls_tolerance", "gravity", "impratio_invsqrt")
+_OPT_INTS = ("integrator", "cone", "solver", "iterations", "ls_iterations", "disableflags", "enableflags", "broadphase", "broadphase_filter",
+             "run_collision_detection")  # fmt: skip
+
+
 def make_option(m) -> MjbOption:
-  """Snapshot of m.opt / m.stat for one call (options are passed by value)."""
+  """Snapshot of m.opt / m.stat for one call (options are passed by value).
+
+  Users mutate m.opt between steps, so the struct is rebuilt whenever an int field, a tensor object or a
+  tensor's in-place version counter changed; otherwise the cached struct is reused (this sits on the
+  per-step host path)."""
   o = m.opt
+  mi = m.stat.meaninertia
+  key = tuple(getattr(o, n) for n in _OPT_INTS) + tuple(x for n in _OPT_TENSORS for x in (id(getattr(o, n)), getattr(o, n)._version)) + (id(mi), mi._version)
+  cached = getattr(m, "_opt_cache", None)
+  if cached is not None and cached[0] == key:
+    return cached[1]
   g = o.gravity.reshape(-1)
-  return MjbOption(
+  opt = MjbOption(
     integrator=int(o.integrator), cone=int(o.cone), solver=int(o.solver), iterations=int(o.iterations),
     ls_iterations=int(o.ls_iterations), disableflags=int(o.disableflags), enableflags=int(o.enableflags),
     broadphase=int(o.broadphase), broadphase_filter=int(o.broadphase_filter),
     run_collision_detection=int(bool(o.run_collision_detection)),
     timestep=float(o.timestep.reshape(-1)[0]), tolerance=float(o.tolerance.reshape(-1)[0]),
     ls_tolerance=float(o.ls_tolerance.reshape(-1)[0]), gravity_x=float(g[0]), gravity_y=float(g[1]), gravity_z=float(g[2]),
-    impratio_invsqrt=float(o.impratio_invsqrt.reshape(-1)[0]), meaninertia=float(m.stat.meaninertia.reshape(-1)[0]),
+    impratio_invsqrt=float(o.impratio_invsqrt.reshape(-1)[0]), meaninertia=float(mi.reshape(-1)[0]),
   )  # fmt: skip
+  m._opt_cache = (key, opt)
+  return opt
 
 
 def model_create(lib, m, int_names, real_names):

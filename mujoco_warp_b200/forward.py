@@ -42,8 +42,12 @@ STAGES_FORWARD = STAGES_FWD_POSITION | STAGE_ZERO_SENSOR | STAGE_FWD_VELOCITY | 
 
 def _ensure_bound(m: types.Model, d: types.Data):
   """Binds (or re-binds, if the user replaced a tensor) the data pointers to the C library."""
+  if d._handle is not None and d._model is m and d._bound_epoch == types._EPOCH[0]:
+    return  # fast path: no tensor attribute of any Data was assigned since the bind
   if d._handle is None or d._model is not m or d._bound_ptrs != _lib.data_ptr_signature(d):
     _io.bind(m, d)
+  else:
+    d._bound_epoch = types._EPOCH[0]
 
 
 def _run(m: types.Model, d: types.Data, stages: int):

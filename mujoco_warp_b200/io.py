@@ -505,6 +505,7 @@ def bind(m: types.Model, d: types.Data):
   d._handle = _lib.data_bind(lib, m, d)
   d._model = m
   d._bound_ptrs = _lib.data_ptr_signature(d)
+  d._bound_epoch = types._EPOCH[0]  # set last: the assignments above bump the epoch
 
 
 class MjDataLite(SimpleNamespace):

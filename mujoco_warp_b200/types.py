@@ -384,8 +384,20 @@ class Model:
     raise AttributeError(name)
 
 
+# Bumped whenever a tensor attribute of any Data / Contact / Constraint object is (re)assigned; lets the
+# step path detect a replaced tensor (`d.ctrl = new`) without walking all ~90 fields on every call.
+_EPOCH = [0]
+
+
+class _TracksAssignment:
+  def __setattr__(self, name, value):
+    if not name.startswith("_"):  # private bookkeeping (handles, bind epoch) is not device data
+      _EPOCH[0] += 1
+    object.__setattr__(self, name, value)
+
+
 @dataclasses.dataclass
-class Contact:
+class Contact(_TracksAssignment):
   """Pooled contact arrays (reference types.py:1618-1655); row i belongs to world worldid[i]."""
 
   dist: Any = None
@@ -407,7 +419,7 @@ class Contact:
 
 
 @dataclasses.dataclass
-class Constraint:
+class Constraint(_TracksAssignment):
   """Per-world constraint rows (reference types.py:1659-1700), dense Jacobian."""
 
   type: Any = None
@@ -427,7 +439,7 @@ class Constraint:
   Ma: Any = None
 
 
-class Data:
+class Data(_TracksAssignment):
   """nworld-batched simulation state and outputs (reference types.py:1703-1896)."""
 
   def __init__(self):

@@ -220,3 +220,27 @@ def test_solve_m_and_mul_m(pair):
   assert H.max_err(res.cpu().numpy(), ref) < 1e-5
   mjw.solve_m(m, d, x, res)
   assert H.max_err(x.cpu().numpy(), y.cpu().numpy()) < 5e-3
+
+
+def test_replacing_a_data_tensor_rebinds(humanoid):
+  """`d.ctrl = new_tensor` (attribute assignment, not copy_) must be picked up by the next step."""
+  qpos, qvel, ctrl = H.make_states(humanoid, 8, seed=6)
+  m, a = H.device_data(mjw, humanoid, qpos, qvel, ctrl, NCONMAX, NJMAX)
+  _, b = H.device_data(mjw, humanoid, qpos, qvel, ctrl * 0, NCONMAX, NJMAX)
+  mjw.step(m, b)  # binds b with its original (zero) ctrl tensor
+  _, c = H.device_data(mjw, humanoid, qpos, qvel, ctrl * 0, NCONMAX, NJMAX)
+  c.ctrl = torch.from_numpy(ctrl.astype(np.float32)).cuda()  # replaced before the first bind
+  mjw.step(m, a)
+  mjw.step(m, c)
+  assert torch.equal(a.qvel, c.qvel)
+  b.qpos.copy_(a.qpos * 0 + torch.from_numpy(qpos.astype(np.float32)).cuda())
+  b.qvel = torch.from_numpy(qvel.astype(np.float32)).cuda()  # replaced after a bind
+  b.ctrl = torch.from_numpy(ctrl.astype(np.float32)).cuda()
+  b.qacc_warmstart.zero_()
+  b.time.zero_()
+  mjw.step(m, b)
+  assert torch.equal(a.qvel, b.qvel)
+  m.opt.timestep.fill_(0.001)  # in-place option change is honoured on the next call
+  t0 = float(a.time[0])
+  mjw.step(m, a)
+  assert abs(float(a.time[0]) - t0 - 0.001) < 1e-7
