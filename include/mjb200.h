@@ -94,6 +94,8 @@ int mjb_fwd_actuation(const MjbModel* m, MjbData* d, const MjbOption* opt, void*
 int mjb_fwd_acceleration(const MjbModel* m, MjbData* d, const MjbOption* opt, int factorize, void* cuda_stream);
 int mjb_solve(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
 int mjb_euler(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+/* forward.py:495 implicit (integrator IMPLICITFAST): (qM - dt qDeriv) solve + _advance */
+int mjb_implicit(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
 /* Replaces the reference's device printf on overflow (forward.py:194-210, collision_core.py:213):
  * ORs the per-world status words (MJB_STATUS_* bits) into *host_flags.  Synchronises the stream;
  * the step entry points never do. */

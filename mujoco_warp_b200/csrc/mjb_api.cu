@@ -302,7 +302,7 @@ extern "C" int mjb_run_stages(const MjbModel* m, MjbData* d, const MjbOption* op
   cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
   if (opt->cone != 0) return fail(-4, "elliptic cones are not implemented");
   if (opt->solver != SOLVER_NEWTON && opt->solver != SOLVER_CG) return fail(-4, "unsupported solver");
-  if (stages & MJB_STAGE_IMPLICIT) return fail(-4, "implicitfast integrator is not implemented");
+  if ((stages & MJB_STAGE_IMPLICIT) && (stages & MJB_STAGE_EULER)) return fail(-4, "euler and implicit stages are exclusive");
   KParams K;
   fill_params(K, m, d, opt, stages);
   if ((stages & MJB_STAGE_COLLISION) && opt->run_collision_detection) {  // collision_driver.py:779
@@ -356,6 +356,7 @@ MJB_STAGE_ENTRY(fwd_velocity, MJB_STAGE_FWD_VELOCITY)
 MJB_STAGE_ENTRY(fwd_actuation, MJB_STAGE_FWD_ACTUATION)
 MJB_STAGE_ENTRY(solve, MJB_STAGE_SOLVE)
 MJB_STAGE_ENTRY(euler, MJB_STAGE_EULER)
+MJB_STAGE_ENTRY(implicit, MJB_STAGE_IMPLICIT)
 #undef MJB_STAGE_ENTRY
 extern "C" int mjb_fwd_position(const MjbModel* m, MjbData* d, const MjbOption* opt, int factorize, void* s) {
   return mjb_run_stages(m, d, opt, MJB_STAGES_FWD_POSITION | (factorize ? MJB_STAGE_FACTOR_M : 0), s);

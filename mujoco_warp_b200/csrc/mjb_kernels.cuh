@@ -31,7 +31,7 @@ __host__ __device__ inline uint32_t group_mask(int g) {
     case G_CON: return MJB_STAGE_MAKE_CONSTRAINT;
     case G_VEL: return MJB_STAGE_ZERO_SENSOR | MJB_STAGE_FWD_VELOCITY | MJB_STAGE_FWD_ACTUATION | MJB_STAGE_FWD_ACCELERATION | MJB_STAGE_FWD_ACC_FACTOR;
     case G_SOL: return MJB_STAGE_SOLVE;
-    case G_EUL: return MJB_STAGE_EULER;
+    case G_EUL: return MJB_STAGE_EULER | MJB_STAGE_IMPLICIT;
   }
   return 0;
 }
@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group
     } else if constexpr (G == G_SOL) {
       s_solve(K, mb, w, lane, scr);
     } else {
-      s_euler(K, mb, w, lane, scr);
+      s_integrate(K, mb, w, lane, scr, (st & MJB_STAGE_IMPLICIT) != 0);
     }
   }
 }

@@ -880,15 +880,58 @@ __device__ __forceinline__ void s_fwd_acceleration(const KParams& K, const unsig
   __syncwarp();
 }
 
-// forward.euler (forward.py:327-354) + _advance (:213-274).
-__device__ __forceinline__ void s_euler(const KParams& K, const unsigned char* mb, int w, int lane, float* scr) {
+// derivative.py:31-108 _qderiv_actuator_passive_vel: d(actuator force) / d(actuator velocity)
+__device__ __forceinline__ float act_vel_deriv(const KParams& K, const unsigned char* mb, int w, int u) {
+  const float gain = MI(actuator_gaintype)[u] == 1 ? MR(actuator_gainprm)[10 * u + 2] : 0.f;
+  const float bias = MI(actuator_biastype)[u] == 1 ? MR(actuator_biasprm)[10 * u + 2] : 0.f;
+  if (bias == 0.f && gain == 0.f) return 0.f;
+  if (MI(actuator_forcelimited)[u]) {  // a clamped force does not depend on the velocity
+    const float f = DW(actuator_force)[u];
+    if (f <= MR(actuator_forcerange)[2 * u] || f >= MR(actuator_forcerange)[2 * u + 1]) return 0.f;
+  }
+  float vel = bias;
+  if (MI(actuator_dyntype)[u] != 0) {
+    if (gain != 0.f) {
+      const int adr = MI(actuator_actadr)[u] + MI(actuator_actnum)[u] - 1;
+      float act = DW(act)[adr];
+      if (MI(actuator_actearly)[u])
+        act = next_act(K.o.timestep, MI(actuator_dyntype)[u], MR(actuator_dynprm) + 10 * u, MR(actuator_actrange) + 2 * u, act,
+                       DW(act_dot)[adr], 1.0f, MI(actuator_actlimited)[u] != 0);
+      vel += gain * act;
+    }
+  } else if (gain != 0.f) {
+    vel += gain * DW(ctrl)[u];
+  }
+  return vel;
+}
+
+// forward.euler (forward.py:327-354) and forward.implicit (implicitfast, forward.py:495-512 with
+// derivative.deriv_smooth_vel dense, derivative.py:321-420), both followed by _advance (:213-274).
+//   euler:        (qM + dt diag(damping)) qacc' = efc_Ma
+//   implicitfast: (qM - dt qDeriv) qacc' = efc_Ma,  qDeriv = moment^T diag(dforce/dvel) moment - diag(damping)
+__device__ __forceinline__ void s_integrate(const KParams& K, const unsigned char* mb, int w, int lane, float* scr, bool implicit) {
   const int nv = K.ms.nv;
   const CholScr s = chol_scr(scr, nv, K.ms.nv_pad);
   const float dt = K.o.timestep;
   float* x = s.x;
-  const bool damp = !(K.o.disableflags & (DSBL_EULERDAMP | DSBL_DAMPER));
-  if (damp) {  // (M + dt diag(damping)) qacc' = Ma
-    load_rows(s.L, s.ld, DW(qM), K.ms.nv_pad, nv, lane, MR(dof_damping), dt);
+  const int dsbl = K.o.disableflags;
+  const bool damper = !(dsbl & DSBL_DAMPER);
+  const int all3 = DSBL_ACTUATION | DSBL_SPRING | DSBL_DAMPER;
+  const bool solve = implicit ? (dsbl & all3) != all3 : (damper && !(dsbl & DSBL_EULERDAMP));
+  if (solve) {
+    load_rows(s.L, s.ld, DW(qM), K.ms.nv_pad, nv, lane, damper ? MR(dof_damping) : nullptr, dt);
+    if (implicit && K.ms.nu > 0 && !(dsbl & DSBL_ACTUATION)) {
+      for (int u = 0; u < K.ms.nu; u++) {  // rows are short (one entry for joint transmissions)
+        const float vel = act_vel_deriv(K, mb, w, u);
+        if (vel == 0.f) continue;
+        const int adr = DW(moment_rowadr)[u], nnz = DW(moment_rownnz)[u];
+        for (int idx = lane; idx < nnz * nnz; idx += 32) {
+          const int a = idx / nnz, b = idx - a * nnz;
+          s.L[DW(moment_colind)[adr + a] * s.ld + DW(moment_colind)[adr + b]] -= dt * DW(actuator_moment)[adr + a] * DW(actuator_moment)[adr + b] * vel;
+        }
+        __syncwarp();
+      }
+    }
     warp_cholesky<false>(s.L, s.ld, nv, s.rd, lane);
     for (int i = lane; i < nv; i += 32) x[i] = DW(efc_Ma)[i];
     __syncwarp();

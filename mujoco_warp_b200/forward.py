@@ -123,8 +123,8 @@ def euler(m, d):
 
 
 def implicit(m, d):
-  """implicitfast integrator (reference forward.py:495) -- not implemented yet."""
-  raise NotImplementedError("integrator IMPLICITFAST not implemented.")
+  """implicitfast integrator (reference forward.py:495)."""
+  _run(m, d, STAGE_IMPLICIT)
 
 
 def forward(m, d):
@@ -197,7 +197,7 @@ def _rk_integrate_pos(m, d, qpos0, qvel, h):
 def step(m, d):
   """Advances the simulation by one timestep (reference forward.py:1004)."""
   integrator = int(m.opt.integrator)
-  if integrator == C.IntegratorType.EULER:
+  if integrator in (C.IntegratorType.EULER, C.IntegratorType.IMPLICITFAST):
     lib = _lib.load()
     _ensure_bound(m, d)
     opt = _lib.make_option(m)

@@ -1419,6 +1419,57 @@ static void o_euler(const OModel* m, const OOpt* o, OData* d) {
   }
 }
 
+/* derivative.py:31-108 _qderiv_actuator_passive_vel: d(actuator force)/d(actuator velocity) */
+static real act_vel_deriv(const OModel* m, const OOpt* o, const OData* d, int u) {
+  real gain = m->actuator_gaintype[u] == 1 ? m->actuator_gainprm[10 * u + 2] : 0.0;
+  real bias = m->actuator_biastype[u] == 1 ? m->actuator_biasprm[10 * u + 2] : 0.0;
+  if (bias == 0.0 && gain == 0.0) return 0.0;
+  if (m->actuator_forcelimited[u]) { /* clamped force has no velocity dependence */
+    real f = d->actuator_force[u];
+    if (f <= m->actuator_forcerange[2 * u] || f >= m->actuator_forcerange[2 * u + 1]) return 0.0;
+  }
+  real vel = bias;
+  if (m->actuator_dyntype[u] != 0) {
+    if (gain != 0.0) {
+      int adr = m->actuator_actadr[u] + m->actuator_actnum[u] - 1;
+      real act = d->act[adr];
+      if (m->actuator_actearly[u])
+        act = next_act(o->timestep, m->actuator_dyntype[u], m->actuator_dynprm + 10 * u, m->actuator_actrange + 2 * u, d->act[adr],
+                       d->act_dot[adr], 1.0, m->actuator_actlimited[u]);
+      vel += gain * act;
+    }
+  } else if (gain != 0.0) {
+    vel += gain * d->ctrl[u];
+  }
+  return vel;
+}
+/* forward.implicit (forward.py:495-512) + derivative.deriv_smooth_vel dense (derivative.py:321-420):
+ * (qM - dt * qDeriv) qacc' = efc_Ma, qDeriv = moment^T diag(dforce/dvel) moment - diag(damping) */
+static void o_implicit(const OModel* m, const OOpt* o, OData* d) {
+  int nv = m->nv, np = m->nv_pad;
+  int all = DSBL_ACTUATION | DSBL_SPRING | DSBL_DAMPER;
+  if ((o->disableflags & all) == all) { o_advance(m, o, d, d->qacc); return; }
+  real* A = (real*)malloc(sizeof(real) * (2 * nv * nv + nv));
+  real *L = A + nv * nv, *qacc = L + nv * nv;
+  for (int i = 0; i < nv; i++)
+    for (int j = 0; j < nv; j++) A[i * nv + j] = d->qM[i * np + j];
+  if (m->nu > 0 && !(o->disableflags & DSBL_ACTUATION))
+    for (int u = 0; u < m->nu; u++) {
+      real vel = act_vel_deriv(m, o, d, u);
+      if (vel == 0.0) continue;
+      int adr = d->moment_rowadr[u], nnz = d->moment_rownnz[u];
+      for (int a = 0; a < nnz; a++)
+        for (int b = 0; b < nnz; b++)
+          A[d->moment_colind[adr + a] * nv + d->moment_colind[adr + b]] -= o->timestep * d->actuator_moment[adr + a] * d->actuator_moment[adr + b] * vel;
+    }
+  if (!(o->disableflags & DSBL_DAMPER))
+    for (int i = 0; i < nv; i++) A[i * nv + i] += o->timestep * m->dof_damping[i];
+  chol_factor(L, nv, A, nv, nv);
+  chol_solve(qacc, L, nv, d->efc_Ma, nv);
+  o_advance(m, o, d, qacc);
+  free(A);
+}
+
 /* ------------------------------------------------------------------------------------------ */
 /* entry point                                                                                 */
 /* ------------------------------------------------------------------------------------------ */
@@ -1506,6 +1557,7 @@ int mjo_run_stages(const int* msizes, const int* const* mint, const double* cons
     if (stages & MJB_STAGE_FWD_ACC_FACTOR) o_fwd_acceleration(&m, &v, 1);
     if (stages & MJB_STAGE_SOLVE) o_solve(&m, &o, &v, &d);
     if (stages & MJB_STAGE_EULER) o_euler(&m, &o, &v);
+    if (stages & MJB_STAGE_IMPLICIT) o_implicit(&m, &o, &v);
   }
   return rc;
 }

@@ -33,6 +33,7 @@ STAGE = {
 STAGE["fwd_position"] = STAGE["kinematics"] | STAGE["com_pos"] | STAGE["crb"] | STAGE["collision"] | STAGE["make_constraint"] | STAGE["transmission"]
 STAGE["forward"] = STAGE["fwd_position"] | STAGE["zero_sensor"] | STAGE["fwd_velocity"] | STAGE["fwd_actuation"] | STAGE["fwd_acc_factor"] | STAGE["solve"]
 STAGE["step"] = STAGE["forward"] | STAGE["euler"]
+STAGE["step_implicitfast"] = STAGE["forward"] | STAGE["implicit"]
 
 _lib = None
 

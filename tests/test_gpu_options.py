@@ -24,8 +24,9 @@ def run_both(mjm, qpos, qvel, ctrl, nconmax, njmax, stage="forward", opt=None, n
   m, d = H.device_data(mjw, mjm, qpos, qvel, ctrl, nconmax, njmax)
   for k, v in (opt or {}).items():
     setattr(m.opt, k, v)
+  ostage = "step_implicitfast" if stage == "step" and (opt or {}).get("integrator") == int(C.IntegratorType.IMPLICITFAST) else stage
   for _ in range(nstep):
-    O.run(om, od, stage, opt=opt, nthread=4)
+    O.run(om, od, ostage, opt=opt, nthread=4)
     (mjw.forward if stage == "forward" else mjw.step)(m, d)
   torch.cuda.synchronize()
   return om, od, m, d
@@ -85,7 +86,7 @@ SMALL_MODELS = {
         <body pos="0 1 1"><joint name="c" type="slide" axis="0 0 1" limited="true" range="-0.05 0.05"/><geom type="sphere" size=".1"/></body>
       </worldbody>
       <equality><joint joint1="a" joint2="b" polycoef="0.1 0.5 0 0 0"/></equality>
-      <actuator><motor joint="a" gear="2" ctrllimited="true" ctrlrange="-1 1"/><position joint="c" kp="20"/></actuator>
+      <actuator><motor joint="a" gear="2" ctrllimited="true" ctrlrange="-1 1"/><position joint="c" kp="20" kv="2"/><velocity joint="b" kv="1.5" forcelimited="true" forcerange="-0.4 0.4"/></actuator>
     </mujoco>""",
   "box_and_spheres_on_plane": """
     <mujoco>
@@ -127,6 +128,26 @@ def test_small_models(name):
     assert int(od.ne.max()) == 1 and int(od.nf.max()) >= 1
   if name == "box_and_spheres_on_plane":
     assert int(od.nacon[0]) > 0
+
+
+@pytest.mark.parametrize("name", ["humanoid", "equality_friction_limits"])
+def test_implicitfast_integrator(humanoid, name):
+  """forward.py:495 implicit + derivative.py:321 deriv_smooth_vel (actuator velocity gains, joint damping)."""
+  mjm = humanoid if name == "humanoid" else mjw.load_mjcf_string(SMALL_MODELS[name])
+  rng = np.random.default_rng(21)
+  if name == "humanoid":
+    qpos, qvel, ctrl = H.make_states(mjm, 8, seed=21)
+  else:
+    qpos = np.repeat(np.asarray(mjm.qpos0, dtype=np.float64)[None], 8, axis=0) + rng.uniform(-0.2, 0.2, (8, mjm.nq))
+    qvel, ctrl = rng.uniform(-1, 1, (8, mjm.nv)), rng.uniform(-1, 1, (8, mjm.nu))
+  opt = {"integrator": int(C.IntegratorType.IMPLICITFAST)}
+  _, od, _, d = run_both(mjm, qpos, qvel, ctrl, 24, 64, stage="step", opt=opt, nstep=3)
+  assert H.max_err(H.dev_np(d, "qpos"), od.qpos) < 1e-5
+  assert H.max_err(H.dev_np(d, "qvel"), od.qvel) < 5e-3
+  # and it differs from Euler where actuators have velocity gains
+  if name != "humanoid":
+    _, oe, _, _ = run_both(mjm, qpos, qvel, ctrl, 24, 64, stage="step", nstep=3)
+    assert np.abs(oe.qvel - od.qvel).max() > 1e-4
 
 
 def test_njmax_overflow_sets_status_and_clamps(humanoid):
