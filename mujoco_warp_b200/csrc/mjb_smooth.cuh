@@ -7,6 +7,9 @@
 // depth-first id ranges [b, subtreeend[b]) so that no atomics are needed and results are
 // deterministic.
 #pragma once
+#ifndef MJB_SOL_COMPACT
+#define MJB_SOL_COMPACT 1
+#endif
 
 
 #include "mjb_types.cuh"
@@ -217,7 +220,7 @@ __device__ __forceinline__ void s_crb(const KParams& K, const unsigned char* mb,
 
 // ---------------------------------------------------------------------------------------------
 // Per-warp shared-memory scratch layout, shared by factor_m / fwd_acceleration / solve / euler:
-//   H (nv x ld) | L (nv x ld) | 7 dof vectors (nv_pad each) | 5 row vectors (njmax_pad each)
+//   H (nv x ld) | L (nv x ld) | 8 dof vectors (nv_pad each) | 5 row vectors (njmax_pad each)
 // ld is a multiple of 4 with ld/4 odd so that LDS.128 row accesses by consecutive lanes are
 // bank-conflict free.
 // ---------------------------------------------------------------------------------------------
@@ -237,11 +240,11 @@ __device__ __forceinline__ CholScr chol_scr(float* scr, int nv, int nvp) {
   return c;
 }
 struct SolverScr {
-  float *H, *L, *x, *grad, *search, *mv, *qacc, *Ma, *qfs, *Jaref, *jv, *D, *coef, *force;
+  float *H, *L, *x, *grad, *search, *mv, *qacc, *Ma, *qfs, *rd, *Jaref, *jv, *D, *coef, *force;
   int ld;
 };
 __host__ __device__ inline int solver_scratch_floats(int nv, int nv_pad, int njmax_pad) {
-  return 2 * nv * chol_ld(nv_pad) + 7 * nv_pad + 5 * njmax_pad;
+  return 2 * nv * chol_ld(nv_pad) + 8 * nv_pad + 5 * njmax_pad;
 }
 __device__ __forceinline__ SolverScr solver_scr(float* scr, int nv, int nvp, int njp) {
   SolverScr s;
@@ -249,8 +252,8 @@ __device__ __forceinline__ SolverScr solver_scr(float* scr, int nv, int nvp, int
   s.H = scr;
   s.L = s.H + nv * s.ld;
   float* v = s.L + nv * s.ld;
-  s.x = v; s.grad = v + nvp; s.search = v + 2 * nvp; s.mv = v + 3 * nvp; s.qacc = v + 4 * nvp; s.Ma = v + 5 * nvp; s.qfs = v + 6 * nvp;
-  float* r = v + 7 * nvp;
+  s.x = v; s.grad = v + nvp; s.search = v + 2 * nvp; s.mv = v + 3 * nvp; s.qacc = v + 4 * nvp; s.Ma = v + 5 * nvp; s.qfs = v + 6 * nvp; s.rd = v + 7 * nvp;
+  float* r = v + 8 * nvp;
   s.Jaref = r; s.jv = r + njp; s.D = r + 2 * njp; s.coef = r + 3 * njp; s.force = r + 4 * njp;
   return s;
 }
@@ -568,7 +571,12 @@ __device__ __forceinline__ void warp_chol_solve(const float* L, int ld, int n, c
 
 // copies the n leading rows of a global matrix (ld_src) into shared memory (ld); rows are copied
 // whole (the Cholesky only reads the lower triangle).  Optional diagonal shift.
-__device__ __forceinline__ void load_rows(float* A, int ld, const float* src, int ld_src, int n, int lane, const float* diag_add,
+#if MJB_SOL_COMPACT
+__device__ __noinline__
+#else
+__device__ __forceinline__
+#endif
+void load_rows(float* A, int ld, const float* src, int ld_src, int n, int lane, const float* diag_add,
                                           float diag_scale) {
   if ((ld_src & 3) == 0) {
     const int c4 = ld_src >> 2, ld4 = ld >> 2;

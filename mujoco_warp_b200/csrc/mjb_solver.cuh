@@ -14,6 +14,11 @@
 #pragma once
 
 #include "mjb_smooth.cuh"
+#if MJB_SOL_COMPACT
+#define MJB_ROLL _Pragma("unroll 1")
+#else
+#define MJB_ROLL
+#endif
 #include "mjb_types.cuh"
 
 struct Pt3 {
@@ -48,12 +53,37 @@ __device__ __forceinline__ float row_dot(const float* __restrict__ row, const fl
   const float4* a = reinterpret_cast<const float4*>(row);
   const float4* v = reinterpret_cast<const float4*>(vec);
   float s = 0.f;
+  if (n4 <= 8) {  // nv_pad <= 32: issue every global load of the row before the first use
+    float4 x[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) x[k] = k < n4 ? a[k] : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      if (k < n4) {
+        const float4 y = v[k];
+        s += x[k].x * y.x + x[k].y * y.y + x[k].z * y.z + x[k].w * y.w;
+      }
+    }
+    return s;
+  }
   for (int k = 0; k < n4; k++) {
     const float4 x = a[k], y = v[k];
     s += x.x * y.x + x.y * y.y + x.z * y.z + x.w * y.w;
   }
   return s;
 }
+
+// out[r] = A[r, :] . vec - sub[r] for r < nrows (A row-major in global memory, rows of 4*n4 floats, 16-byte
+// aligned; vec in shared memory).  One out-of-line copy serves J qacc, M qacc, M p and J p: the solver kernel
+// is instruction-fetch bound when its hot code outgrows the 32 kB instruction cache.
+__device__ __noinline__ void mat_vec(const float* __restrict__ A, int n4, int nrows, const float* vec, float* out, const float* sub, int lane) {
+#pragma unroll 1
+  for (int r = lane; r < nrows; r += 32) {
+    const float s = row_dot(A + (size_t)r * (4 * n4), vec, n4);
+    out[r] = sub ? s - sub[r] : s;
+  }
+}
+__device__ __noinline__ float warp_sum_ol(float v) { return warp_sum(v); }  // out-of-line copy
 
 // H(lower) += sum_r coef[r] * J[r]^T J[r], register tiles of 4 rows x 8 columns per lane over
 // 32x32 blocks (solver.py:2368 JTDAJ and :2055 incremental update in one routine).
@@ -62,7 +92,9 @@ __device__ __forceinline__ void h_accumulate(const KParams& K, int w, int lane, 
   const float* J = DW(efc_J);
   const int a = lane >> 2, b = lane & 3;
   const int nblk = (nv + 31) >> 5;
+  MJB_ROLL
   for (int bi = 0; bi < nblk; bi++) {
+    MJB_ROLL
     for (int bj = 0; bj <= bi; bj++) {
       const int r0 = 32 * bi + 4 * a, c0 = 32 * bj + 8 * b;
       const bool rin = r0 < np, cin0 = c0 < np, cin1 = c0 + 4 < np;
@@ -72,23 +104,59 @@ __device__ __forceinline__ void h_accumulate(const KParams& K, int w, int lane, 
       for (int i = 0; i < 4; i++)
 #pragma unroll
         for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
-      for (int r = 0; r < nefc; r++) {
-        const float cf = s.coef[r];
-        if (cf == 0.f) continue;  // warp-uniform
+      // two rows per iteration: the six 128-bit loads of both rows are issued before the 64 FMAs
+      const int nefc2 = (nefc + 1) & ~1;
+      MJB_ROLL
+      for (int r = 0; r < nefc2; r += 2) {
+        const float cf0 = s.coef[r], cf1 = (r + 1 < nefc) ? s.coef[r + 1] : 0.f;
+        if (cf0 == 0.f && cf1 == 0.f) continue;  // warp-uniform
         if (need) {
-          const float* Jr = J + (size_t)r * np;
-          const float4 ji = *reinterpret_cast<const float4*>(Jr + r0);
-          const float4 ja = *reinterpret_cast<const float4*>(Jr + c0);
-          const float4 jb = cin1 ? *reinterpret_cast<const float4*>(Jr + c0 + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
-          const float vi[4] = {ji.x * cf, ji.y * cf, ji.z * cf, ji.w * cf};
-          const float vj[8] = {ja.x, ja.y, ja.z, ja.w, jb.x, jb.y, jb.z, jb.w};
+          const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          const float* Jr0 = J + (size_t)r * np;
+          const float* Jr1 = J + (size_t)min(r + 1, nefc - 1) * np;
+          const bool u0 = cf0 != 0.f, u1 = cf1 != 0.f;
+          const float4 ji0 = u0 ? *reinterpret_cast<const float4*>(Jr0 + r0) : z4;
+          const float4 ja0 = u0 ? *reinterpret_cast<const float4*>(Jr0 + c0) : z4;
+          const float4 jb0 = (u0 && cin1) ? *reinterpret_cast<const float4*>(Jr0 + c0 + 4) : z4;
+          const float4 ji1 = u1 ? *reinterpret_cast<const float4*>(Jr1 + r0) : z4;
+          const float4 ja1 = u1 ? *reinterpret_cast<const float4*>(Jr1 + c0) : z4;
+          const float4 jb1 = (u1 && cin1) ? *reinterpret_cast<const float4*>(Jr1 + c0 + 4) : z4;
+          {
+            const float vi[4] = {ji0.x * cf0, ji0.y * cf0, ji0.z * cf0, ji0.w * cf0};
+            const float vj[8] = {ja0.x, ja0.y, ja0.z, ja0.w, jb0.x, jb0.y, jb0.z, jb0.w};
 #pragma unroll
-          for (int i = 0; i < 4; i++)
+            for (int i = 0; i < 4; i++)
 #pragma unroll
-            for (int j = 0; j < 8; j++) acc[i][j] += vi[i] * vj[j];
+              for (int j = 0; j < 8; j++) acc[i][j] += vi[i] * vj[j];
+          }
+          {
+            const float vi[4] = {ji1.x * cf1, ji1.y * cf1, ji1.z * cf1, ji1.w * cf1};
+            const float vj[8] = {ja1.x, ja1.y, ja1.z, ja1.w, jb1.x, jb1.y, jb1.z, jb1.w};
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+#pragma unroll
+              for (int j = 0; j < 8; j++) acc[i][j] += vi[i] * vj[j];
+          }
         }
       }
       if (need) {
+#if MJB_SOL_COMPACT
+        // whole 4x8 tiles with 128-bit accesses; elements above the diagonal receive their (symmetric) values too
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          if (r0 + i < nv) {
+            float4* h = reinterpret_cast<float4*>(s.H + (r0 + i) * ld + c0);
+            float4 v = h[0];
+            v.x += acc[i][0]; v.y += acc[i][1]; v.z += acc[i][2]; v.w += acc[i][3];
+            h[0] = v;
+            if (cin1) {
+              v = h[1];
+              v.x += acc[i][4]; v.y += acc[i][5]; v.z += acc[i][6]; v.w += acc[i][7];
+              h[1] = v;
+            }
+          }
+        }
+#else
 #pragma unroll
         for (int i = 0; i < 4; i++)
 #pragma unroll
@@ -96,6 +164,7 @@ __device__ __forceinline__ void h_accumulate(const KParams& K, int w, int lane, 
             const int ri = r0 + i, cj = c0 + j;
             if (ri < nv && cj <= ri) s.H[ri * ld + cj] += acc[i][j];
           }
+#endif
       }
     }
   }
@@ -109,6 +178,7 @@ __device__ __forceinline__ void update_constraint(const KParams& K, int w, int l
   float c = 0.f;
   bool changed = false;
   int* state = DW(efc_state);
+  MJB_ROLL
   for (int r = lane; r < nefc; r += 32) {
     const float D = s.D[r], ja = s.Jaref[r];
     float f;
@@ -134,15 +204,24 @@ __device__ __forceinline__ void update_constraint(const KParams& K, int w, int l
   }
   any_change = __any_sync(FULL, changed);
   __syncwarp();
-  // qfrc_constraint = J^T force (solver.py:1988): lane = dof, uniform loop over rows with force
+  // qfrc_constraint = J^T force (solver.py:1988): lane = dof; four rows per iteration so that four
+  // independent (coalesced) global loads are in flight; groups of rows without force are skipped
   const float* J = DW(efc_J);
+  const int nefc4 = (nefc + 3) & ~3, rlast = K.dsz.njmax - 1;
+  for (int r = nefc + lane; r < nefc4; r += 32) s.force[r] = 0.f;
+  __syncwarp();
   float g = 0.f;
   for (int i0 = 0; i0 < nv; i0 += 32) {
     const int i = i0 + lane;
+    const float* Jc = J + (i < nv ? i : 0);
     float q = 0.f;
-    for (int r = 0; r < nefc; r++) {
-      const float f = s.force[r];
-      if (f != 0.f && i < nv) q += J[(size_t)r * np + i] * f;
+    MJB_ROLL
+    for (int r = 0; r < nefc4; r += 4) {
+      const float4 f = *reinterpret_cast<const float4*>(s.force + r);
+      if (f.x == 0.f && f.y == 0.f && f.z == 0.f && f.w == 0.f) continue;  // warp-uniform
+      const float j0 = Jc[(size_t)r * np], j1 = Jc[(size_t)min(r + 1, rlast) * np], j2 = Jc[(size_t)min(r + 2, rlast) * np],
+                  j3 = Jc[(size_t)min(r + 3, rlast) * np];
+      q += (f.x != 0.f ? j0 * f.x : 0.f) + (f.y != 0.f ? j1 * f.y : 0.f) + (f.z != 0.f ? j2 * f.z : 0.f) + (f.w != 0.f ? j3 * f.w : 0.f);
     }
     if (i < nv) {
       DW(qfrc_constraint)[i] = q;
@@ -158,6 +237,7 @@ __device__ __forceinline__ void update_constraint(const KParams& K, int w, int l
 
 __device__ __forceinline__ Pt3 ls_rows(const KParams& K, int w, int lane, const SolverScr& s, int nefc, int ne, int nf, float alpha) {
   Pt3 t = Pt3{0.f, 0.f, 0.f};
+  MJB_ROLL
   for (int r = lane; r < nefc; r += 32) {
     const float fl = (r >= ne && r < ne + nf) ? DW(efc_frictionloss)[r] : 0.f;
     t = t + efc_eval_pt(r, alpha, ne, nf, s.D[r], fl, s.Jaref[r], s.jv[r]);
@@ -170,12 +250,20 @@ __device__ __forceinline__ void linesearch(const KParams& K, int w, int lane, co
                                            float search_dot) {
   const int nv = K.ms.nv, np = K.ms.nv_pad, n4 = np >> 2;
   // mv = M search, jv = J search
+#if MJB_SOL_COMPACT
+  mat_vec(DW(qM), n4, nv, s.search, s.mv, nullptr, lane);
+  mat_vec(DW(efc_J), n4, nefc, s.search, s.jv, nullptr, lane);
+#else
+  MJB_ROLL
   for (int i = lane; i < nv; i += 32) s.mv[i] = row_dot(DW(qM) + (size_t)i * np, s.search, n4);
+  MJB_ROLL
   for (int r = lane; r < nefc; r += 32) s.jv[r] = row_dot(DW(efc_J) + (size_t)r * np, s.search, n4);
+#endif
   __syncwarp();
   const float scale = K.o.meaninertia * (float)nv;
   const float gtol = fmaxf(K.o.tolerance * K.o.ls_tolerance * sqrtf(search_dot) * scale, 1e-6f);
   float q1 = 0.f, q2 = 0.f;
+  MJB_ROLL
   for (int i = lane; i < nv; i += 32) {
     q1 += s.search[i] * (s.Ma[i] - s.qfs[i]);
     q2 += 0.5f * s.search[i] * s.mv[i];
@@ -194,11 +282,13 @@ __device__ __forceinline__ void linesearch(const KParams& K, int w, int lane, co
     const bool lo_less = lo_in.g < p0.g;
     Pt3 lo = lo_less ? lo_in : p0, hi = lo_less ? p0 : lo_in;
     float lo_alpha = lo_less ? lo_alpha_in : 0.f, hi_alpha = lo_less ? 0.f : lo_alpha_in;
+    MJB_ROLL
     for (int it = 0; it < K.o.ls_iterations; it++) {
       const float lo_next_alpha = lo_alpha - safe_div(lo.g, lo.h);
       const float hi_next_alpha = hi_alpha - safe_div(hi.g, hi.h);
       const float mid_alpha = 0.5f * (lo_alpha + hi_alpha);
       Pt3 a = Pt3{0.f, 0.f, 0.f}, b = a, c = a;
+      MJB_ROLL
       for (int r = lane; r < nefc; r += 32) {
         const float fl = (r >= ne && r < ne + nf) ? DW(efc_frictionloss)[r] : 0.f;
         const float D = s.D[r], ja = s.Jaref[r], jv = s.jv[r];
@@ -229,10 +319,12 @@ __device__ __forceinline__ void linesearch(const KParams& K, int w, int lane, co
       if (uniform_b(ls_done)) break;
     }
   }
+  MJB_ROLL
   for (int i = lane; i < nv; i += 32) {
     s.qacc[i] += alpha * s.search[i];
     s.Ma[i] += alpha * s.mv[i];
   }
+  MJB_ROLL
   for (int r = lane; r < nefc; r += 32) s.Jaref[r] += alpha * s.jv[r];
   __syncwarp();
 }
@@ -244,13 +336,15 @@ __device__ __forceinline__ void solve_direction(const KParams& K, int lane, cons
   if (refactor) {
     const float4* h4 = reinterpret_cast<const float4*>(s.H);
     float4* l4 = reinterpret_cast<float4*>(s.L);
+    MJB_ROLL
     for (int i = lane; i < (nv * ld) >> 2; i += 32) l4[i] = h4[i];
     __syncwarp();
-    warp_cholesky<true>(s.L, ld, nv, nullptr, lane);
+    warp_cholesky<!MJB_SOL_COMPACT>(s.L, ld, nv, s.rd, lane);
   }
+  MJB_ROLL
   for (int i = lane; i < nv; i += 32) s.x[i] = s.grad[i];
   __syncwarp();
-  warp_chol_solve<true>(s.L, ld, nv, nullptr, s.x, lane);
+  warp_chol_solve<!MJB_SOL_COMPACT>(s.L, ld, nv, s.rd, s.x, lane);
 }
 
 // Solver state of one world that lives in registers across passes.
@@ -264,6 +358,7 @@ struct SolveState {
 __device__ __forceinline__ bool solve_begin(const KParams& K, int w, int lane, const SolverScr& s, SolveState& st) {
   const int nv = K.ms.nv, np = K.ms.nv_pad, njmax = K.dsz.njmax;
   if (njmax == 0 || nv == 0) {
+    MJB_ROLL
     for (int i = lane; i < nv; i += 32) DW(qacc)[i] = DW(qacc_smooth)[i];
     if (lane == 0) DW(solver_niter)[0] = 0;
     __syncwarp();
@@ -277,20 +372,30 @@ __device__ __forceinline__ bool solve_begin(const KParams& K, int w, int lane, c
   st.cost = st.gauss = st.prev_cost = st.search_dot = 0.f;
   const bool newton = K.o.solver == SOLVER_NEWTON;
   const float* src = (K.o.disableflags & DSBL_WARMSTART) ? DW(qacc_smooth) : DW(qacc_warmstart);
+  MJB_ROLL
   for (int i = lane; i < np; i += 32) {
     s.qacc[i] = i < nv ? src[i] : 0.f;
     s.qfs[i] = i < nv ? DW(qfrc_smooth)[i] : 0.f;
     s.search[i] = 0.f;
   }
+  MJB_ROLL
   for (int r = lane; r < st.nefc; r += 32) s.D[r] = DW(efc_D)[r];
   __syncwarp();
   // Jaref = J qacc - aref, Ma = M qacc
   const int n4 = np >> 2;
+#if MJB_SOL_COMPACT
+  mat_vec(DW(efc_J), n4, st.nefc, s.qacc, s.Jaref, DW(efc_aref), lane);
+  mat_vec(DW(qM), n4, nv, s.qacc, s.Ma, nullptr, lane);
+#else
+  MJB_ROLL
   for (int r = lane; r < st.nefc; r += 32) s.Jaref[r] = row_dot(DW(efc_J) + (size_t)r * np, s.qacc, n4) - DW(efc_aref)[r];
+  MJB_ROLL
   for (int i = lane; i < nv; i += 32) s.Ma[i] = row_dot(DW(qM) + (size_t)i * np, s.qacc, n4);
+#endif
   __syncwarp();
   // Newton: H starts as qM.  CG: the preconditioner is the factor of qM (qLD).
   load_rows(newton ? s.H : s.L, s.ld, newton ? DW(qM) : DW(qLD), newton ? np : nv, nv, lane, nullptr, 0.f);
+  if (!newton) chol_rdiag(s.L, s.ld, nv, s.rd, lane);
   return true;
 }
 
@@ -306,6 +411,7 @@ __device__ __forceinline__ bool solve_pass(const KParams& K, int w, int lane, co
   if (!init) {
     linesearch(K, w, lane, s, st.nefc, st.ne, st.nf, st.gauss, st.search_dot);
     if (!newton) {
+      MJB_ROLL
       for (int i = lane; i < nv; i += 32) { prev_grad[i] = s.grad[i]; prev_Mgrad[i] = s.x[i]; }
       __syncwarp();
     }
@@ -318,6 +424,7 @@ __device__ __forceinline__ bool solve_pass(const KParams& K, int w, int lane, co
   // update, factorisation and solve of the last pass are skipped (outputs are identical).
   if (!init) {
     float grad_dot = 0.f;
+    MJB_ROLL
     for (int i = lane; i < nv; i += 32) grad_dot += s.grad[i] * s.grad[i];
     grad_dot = warp_sum(grad_dot);
     st.niter++;
@@ -332,10 +439,12 @@ __device__ __forceinline__ bool solve_pass(const KParams& K, int w, int lane, co
   float beta = 0.f;
   if (!newton && !init) {  // Polak-Ribiere, solver.py:3081
     float num = 0.f, den = 0.f;
+    MJB_ROLL
     for (int i = lane; i < nv; i += 32) { num += s.grad[i] * (s.x[i] - prev_Mgrad[i]); den += prev_grad[i] * prev_Mgrad[i]; }
     beta = fmaxf(0.f, warp_sum(num) / fmaxf(MJ_MINVAL, warp_sum(den)));
   }
   float search_dot = 0.f;
+  MJB_ROLL
   for (int i = lane; i < nv; i += 32) {
     float v = -s.x[i];
     if (!newton && !init) v += beta * s.search[i];
@@ -351,6 +460,7 @@ __device__ __forceinline__ bool solve_pass(const KParams& K, int w, int lane, co
 __device__ __forceinline__ void solve_finish(const KParams& K, int w, int lane, const SolverScr& s, const SolveState& st) {
   const int nv = K.ms.nv;
   const int niter = st.niter;
+  MJB_ROLL
   for (int i = lane; i < nv; i += 32) {
     const float q = s.qacc[i];
     DW(qacc)[i] = q;
