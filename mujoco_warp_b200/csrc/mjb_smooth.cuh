@@ -578,19 +578,25 @@ __device__ __forceinline__
 #endif
 void load_rows(float* A, int ld, const float* src, int ld_src, int n, int lane, const float* diag_add,
                                           float diag_scale) {
+  // a row / column walk with running indices instead of a division per element (compact code)
   if ((ld_src & 3) == 0) {
     const int c4 = ld_src >> 2, ld4 = ld >> 2;
     const float4* s4 = reinterpret_cast<const float4*>(src);
     float4* a4 = reinterpret_cast<float4*>(A);
-    for (int idx = lane; idx < n * c4; idx += 32) {
-      const int i = idx / c4, q = idx - i * c4;
-      a4[i * ld4 + q] = s4[idx];
+    if (c4 <= 8) {  // rows of <= 32 floats: 4 rows per pass, lane = (row % 4, float4 column)
+      const int q = lane & 7;
+#pragma unroll 2
+      for (int i = lane >> 3; i < n; i += 4)
+        if (q < c4) a4[i * ld4 + q] = s4[i * c4 + q];
+    } else {
+#pragma unroll 1
+      for (int i = 0; i < n; i++)
+        for (int q = lane; q < c4; q += 32) a4[i * ld4 + q] = s4[i * c4 + q];
     }
   } else {
-    for (int idx = lane; idx < n * ld_src; idx += 32) {
-      const int i = idx / ld_src, j = idx - i * ld_src;
-      A[i * ld + j] = src[idx];
-    }
+#pragma unroll 1
+    for (int i = 0; i < n; i++)
+      for (int j = lane; j < ld_src; j += 32) A[i * ld + j] = src[i * ld_src + j];
   }
   __syncwarp();
   if (diag_add != nullptr) {
@@ -603,9 +609,13 @@ void load_rows(float* A, int ld, const float* src, int ld_src, int n, int lane, 
 __device__ __forceinline__ void store_qLD(const KParams& K, int w, int lane, const float* L, int ld) {
   const int nv = K.ms.nv;
   float* qLD = DW(qLD);
-  for (int idx = lane; idx < nv * nv; idx += 32) {
-    const int i = idx / nv, j = idx - i * nv;
-    qLD[idx] = (j <= i) ? L[i * ld + j] : 0.f;
+  if (nv <= 32) {
+#pragma unroll 4
+    for (int i = 0; i < nv; i++)
+      if (lane < nv) qLD[i * nv + lane] = (lane <= i) ? L[i * ld + lane] : 0.f;
+  } else {
+    for (int i = 0; i < nv; i++)
+      for (int j = lane; j < nv; j += 32) qLD[i * nv + j] = (j <= i) ? L[i * ld + j] : 0.f;
   }
 }
 

@@ -25,7 +25,21 @@ struct Pt3 {
   float c, g, h;
 };
 __device__ __forceinline__ Pt3 operator+(Pt3 a, Pt3 b) { return Pt3{a.c + b.c, a.g + b.g, a.h + b.h}; }
-__device__ __forceinline__ Pt3 warp_sum(Pt3 p) { return Pt3{warp_sum(p.c), warp_sum(p.g), warp_sum(p.h)}; }
+// one out-of-line copy of the three interleaved reductions (the line search calls it in many places)
+#if MJB_SOL_COMPACT
+__device__ __noinline__
+#else
+__device__ __forceinline__
+#endif
+Pt3 warp_sum(Pt3 p) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    p.c += __shfl_xor_sync(FULL, p.c, o);
+    p.g += __shfl_xor_sync(FULL, p.g, o);
+    p.h += __shfl_xor_sync(FULL, p.h, o);
+  }
+  return p;
+}
 
 // solver.py:571-598 (_compute_efc_eval_pt_pyramidal)
 __device__ __forceinline__ Pt3 efc_eval_pt(int r, float alpha, int ne, int nf, float D, float floss, float jaref, float jv) {

