@@ -19,6 +19,9 @@
 #ifndef MJB_SOL_THREADS
 #define MJB_SOL_THREADS 128
 #endif
+#ifndef MJB_CON_MIN_CTAS
+#define MJB_CON_MIN_CTAS 3
+#endif
 #ifndef MJB_COL_MIN_CTAS
 #define MJB_COL_MIN_CTAS 2
 #endif
@@ -81,7 +84,11 @@ __device__ __forceinline__ void stage_model_blob(unsigned char* dst, const unsig
 
 // CTA width and minimum resident CTAs per SM of a group (register budget = 65536 / (threads x CTAs))
 __host__ __device__ constexpr int group_threads(int g) { return g == G_SOL ? MJB_SOL_THREADS : 256; }
-__host__ __device__ constexpr int group_min_ctas(int g) { return g == G_SOL ? MJB_SOL_MIN_CTAS : (g == G_COL ? MJB_COL_MIN_CTAS : 1); }
+__host__ __device__ constexpr int group_min_ctas(int g) {
+  // caps the register allocation (65536 / (threads x CTAs)): without it ptxas spends registers on unrolling
+  // and the smooth kernels lose half of their occupancy
+  return g == G_SOL ? MJB_SOL_MIN_CTAS : g == G_COL ? MJB_COL_MIN_CTAS : g == G_POS ? 4 : g == G_CON ? MJB_CON_MIN_CTAS : 3;
+}
 
 template <int G, bool BLOB_IN_SMEM>
 __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group_kernel(const __grid_constant__ KParams K) {
