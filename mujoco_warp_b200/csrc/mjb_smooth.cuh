@@ -846,16 +846,34 @@ __device__ __forceinline__ void s_fwd_actuation(const KParams& K, const unsigned
     DW(actuator_force)[u] = force;
   }
   __syncwarp();
-  // qfrc_actuator = moment^T force: lane per dof gathers (deterministic, no atomics; forward.py:783)
-  const int nJ = K.ms.nJmom;
-  for (int i = lane; i < nv; i += 32) {
+  // qfrc_actuator = moment^T force (forward.py:783), deterministic and without atomics: lane u holds the
+  // k-th entry (column, moment * force) of actuator u's moment row; the entries are broadcast one by one
+  // and the lane that owns the dof adds them up
+  for (int i = lane; i < ((nv + 31) & ~31); i += 32) {
     float q = 0.f;
-    for (int u = 0; u < nu; u++) {
-      const int adr = DW(moment_rowadr)[u], nnz = DW(moment_rownnz)[u];
-      for (int k = 0; k < nnz; k++)
-        if (DW(moment_colind)[adr + k] == i) q += DW(actuator_moment)[adr + k] * DW(actuator_force)[u];
+    for (int u0 = 0; u0 < nu; u0 += 32) {
+      const int u = u0 + lane, cnt = min(32, nu - u0);
+      int adr = 0, nnz = 0;
+      float force = 0.f;
+      if (u < nu) {
+        adr = DW(moment_rowadr)[u];
+        nnz = DW(moment_rownnz)[u];
+        force = DW(actuator_force)[u];
+      }
+      int maxnnz = nnz;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) maxnnz = max(maxnnz, __shfl_xor_sync(FULL, maxnnz, o));
+      for (int k = 0; k < maxnnz; k++) {
+        const int col = k < nnz ? DW(moment_colind)[adr + k] : -1;
+        const float val = k < nnz ? DW(actuator_moment)[adr + k] * force : 0.f;
+        for (int uu = 0; uu < cnt; uu++) {
+          const int c = __shfl_sync(FULL, col, uu);
+          const float v = __shfl_sync(FULL, val, uu);
+          if (c == i) q += v;
+        }
+      }
     }
-    (void)nJ;
+    if (i >= nv) continue;
     const int j = MI(dof_jntid)[i];
     if (K.ms.ngravcomp && MI(jnt_actgravcomp)[j]) q += DW(qfrc_gravcomp)[i];
     if (MI(jnt_actfrclimited)[j]) q = clampf(q, MR(jnt_actfrcrange)[2 * j], MR(jnt_actfrcrange)[2 * j + 1]);
