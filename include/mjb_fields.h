@@ -27,7 +27,8 @@
   X(nfrictiondof) /* dofs with frictionloss > 0 */ \
   X(neqjnt)     /* joint equalities (reference io.py:447) */ \
   X(nJmom)      /* actuator moment non-zeros */ \
-  X(nmaxcondim) X(nmaxpyramid) X(ngravcomp) X(is_sparse) X(nM) X(ntree)
+  X(nmaxcondim) X(nmaxpyramid) X(ngravcomp) X(is_sparse) X(nM) X(ntree) \
+  X(ngeompair)  /* ngeom (ngeom - 1) / 2: entries of the upper-triangular pair table (SAP broadphase) */
 
 /* ---- model int arrays ---------------------------------------------------------------------- */
 #define MJB_MODEL_INT_FIELDS(X) \
@@ -40,7 +41,9 @@
   X(dof_bodyid) X(dof_jntid) X(dof_parentid) X(dof_friction_adr) \
   X(geom_type) X(geom_bodyid) X(geom_condim) X(geom_priority) X(geom_static) \
   X(site_bodyid) \
-  X(nxn_pair) X(nxn_pairid) X(pair_dim) \
+  X(nxn_pair) X(nxn_pairid) \
+  X(nxn_lookup) /* upper_tri_index(g1, g2) -> index into nxn_pair, or -1 (reference io.py:346 nxn_pairid) */ \
+  X(pair_dim) \
   X(actuator_trntype) X(actuator_trnid) X(actuator_dyntype) X(actuator_gaintype) \
   X(actuator_biastype) X(actuator_actadr) X(actuator_actnum) X(actuator_ctrllimited) \
   X(actuator_forcelimited) X(actuator_actlimited) X(actuator_actearly) \

@@ -254,7 +254,7 @@ static int launch_group(int g, const MjbModel* m, MjbData* d, KParams& K, uint32
   if (!c.ready) {
     int wpb = warps_per_block(g == G_SOL ? group_threads(G_SOL) / 32 : 8);
     if (32 * wpb > group_threads(g)) wpb = group_threads(g) / 32;
-    c.scratch_floats = group_scratch_floats(g, m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad);
+    c.scratch_floats = group_scratch_floats(g, m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad, m->ms.ngeom, m->ms.nxn);
     const size_t scr_bytes = (size_t)wpb * c.scratch_floats * sizeof(float);
     const bool in_smem =
         group_uses_blob(g) && (size_t)m->blob_bytes + 16 + scr_bytes <= (size_t)d->smem_optin && m->blob_bytes <= 96 * 1024;

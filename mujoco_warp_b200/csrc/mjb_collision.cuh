@@ -311,16 +311,88 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
   nw += max(0, min(total, K.dsz.naconmax - base));
 }
 
-// collision_driver.collision (collision_driver.py:755).  queue: 64 ints of shared scratch.
+// Per-warp shared scratch of the collision stage, in 32-bit words: the pair queue (64 + 8), then the
+// sweep-and-prune workspace (lower, upper, order, range prefix: 4 ngeom words; candidate bit set).
+__host__ __device__ inline int collision_scratch_words(int ngeom, int nxn) { return 72 + 4 * ngeom + (nxn + 31) / 32 + 1; }
+
+// Sweep-and-prune candidate set (collision_driver.py:554 sap_broadphase).  The reference projects the bounding
+// spheres on a fixed direction (:573), sorts per world by the lower end (tile sort or segmented sort, :458/:617),
+// finds per sorted geom the range of followers whose lower end does not exceed its upper end -- plus one
+// (_sap_range :411: limit = min(ngeom - 1, first lower > upper)) -- and tests the flattened (geom, follower) work
+// items (:485-551).  One warp does the same for its world: rank sort (lane = geom), warp scan of the ranges, lanes
+// over the flattened items; items that exist in the statically filtered pair table set a bit of `bits`, which the
+// pair loop of s_collision then uses as a pre-filter, so contacts keep the pair-list order of the NXN path.
+__device__ __forceinline__ void sap_candidates(const KParams& K, const unsigned char* mb, int w, int lane, int* ws, unsigned* bits) {
+  const int ng = K.ms.ngeom, nxn = K.ms.nxn;
+  float* lower = reinterpret_cast<float*>(ws);
+  float* upper = lower + ng;
+  int* order = ws + 2 * ng;
+  int* cum = ws + 3 * ng;
+  const float inv = rsqrtf(0.5935f * 0.5935f + 0.7790f * 0.7790f + 0.1235f * 0.1235f);
+  const V3 dir{0.5935f * inv, 0.7790f * inv, 0.1235f * inv};
+  for (int g = lane; g < ng; g += 32) {
+    float rb = MR(geom_rbound)[g];
+    if (rb == 0.f) rb = MJ_MAXVAL;
+    const float radius = rb + MR(geom_margin)[g], c = dot(dir, ld3(DW(geom_xpos) + 3 * g));
+    const bool bad = c != c;
+    lower[g] = bad ? MJ_MAXVAL : c - radius;
+    upper[g] = bad ? MJ_MAXVAL : c + radius;
+  }
+  for (int i = lane; i < (nxn + 31) / 32; i += 32) bits[i] = 0u;
+  __syncwarp();
+  for (int g = lane; g < ng; g += 32) {  // stable rank sort by lower end
+    const float lg = lower[g];
+    int rank = 0;
+    for (int h = 0; h < ng; h++) {
+      const float lh = lower[h];
+      rank += (lh < lg || (lh == lg && h < g)) ? 1 : 0;
+    }
+    order[rank] = g;
+  }
+  __syncwarp();
+  int running = 0;
+  for (int i0 = 0; i0 < ng; i0 += 32) {  // followers per sorted position, inclusive prefix sums into cum[]
+    const int i = i0 + lane;
+    int range = 0;
+    if (i < ng) {
+      const float up = upper[order[i]];
+      int limit = i + 1;
+      while (limit < ng && !(lower[order[limit]] > up)) limit++;
+      range = min(limit, ng - 1) - i;
+    }
+    const int ex = warp_excl_scan(range, lane);
+    if (i < ng) cum[i] = running + ex + range;
+    running += __shfl_sync(FULL, ex + range, 31);
+  }
+  __syncwarp();
+  for (int k = lane; k < running; k += 32) {  // flattened work items (collision_driver.py:488-506)
+    int lo = 0, hi = ng;
+    while (lo < hi) {  // first position whose inclusive prefix exceeds k
+      const int mid = (lo + hi) >> 1;
+      if (cum[mid] > k) hi = mid; else lo = mid + 1;
+    }
+    const int i = hi, j = i + 1 + k - (i > 0 ? cum[i - 1] : 0);
+    int a = order[i], b = order[j];
+    if (b < a) { const int t = a; a = b; b = t; }
+    const int p = MI(nxn_lookup)[(a * (2 * ng - a - 3)) / 2 + b - 1];
+    if (p >= 0) atomicOr(bits + (p >> 5), 1u << (p & 31));
+  }
+  __syncwarp();
+}
+
+// collision_driver.collision (collision_driver.py:755).  scratch: collision_scratch_words() ints per warp.
 __device__ __forceinline__ void s_collision(const KParams& K, const unsigned char* mb, int w, int lane, int* queue) {
   int nw = 0, ncol = 0, qn = 0;
   const bool enabled = K.dsz.naconmax > 0 && !(K.o.disableflags & (DSBL_CONSTRAINT | DSBL_CONTACT));
   if (enabled) {
     const int nxn = K.ms.nxn;
+    const bool sap = uniform_b(K.o.broadphase != 0 && nxn > 0);
+    unsigned* bits = reinterpret_cast<unsigned*>(queue + 72 + 4 * K.ms.ngeom);
+    if (sap) sap_candidates(K, mb, w, lane, queue + 72, bits);
     for (int p0 = 0; p0 < nxn; p0 += 32) {
       const int p = p0 + lane;
       bool pass = false;
-      if (p < nxn) pass = bp_filter(K, mb, w, MI(nxn_pair)[2 * p], MI(nxn_pair)[2 * p + 1]) || MI(nxn_pairid)[2 * p + 1] >= 0;
+      if (p < nxn && (!sap || (bits[p >> 5] >> (p & 31) & 1u))) pass = bp_filter(K, mb, w, MI(nxn_pair)[2 * p], MI(nxn_pair)[2 * p + 1]) || MI(nxn_pairid)[2 * p + 1] >= 0;
       const unsigned mask = __ballot_sync(FULL, pass);
       if (pass) queue[qn + __popc(mask & ((1u << lane) - 1u))] = p;
       qn += __popc(mask);

@@ -209,6 +209,9 @@ def host_model(mjm) -> SimpleNamespace:
   ints["nxn_pair"] = np.stack((geom1, geom2), axis=1)[include].astype(i32).reshape(-1, 2)
   ints["nxn_pairid"] = np.stack((pairid_contact, pairid_collision), axis=1)[include].astype(i32).reshape(-1, 2)
   nxn = int(include.sum())
+  lookup = -1 * np.ones(len(geom1), dtype=i32)  # pair table position -> filtered pair index (sweep-and-prune path)
+  lookup[include] = np.arange(nxn, dtype=i32)
+  ints["nxn_lookup"] = lookup
 
   # supported narrowphase pair types (primitive analytic functions only in this round)
   supported = {
@@ -242,7 +245,7 @@ def host_model(mjm) -> SimpleNamespace:
     nfrictiondof=int(ints["dof_friction_adr"].size), neqjnt=int(ints["eq_jnt_adr"].size), nJmom=nJmom,
     nmaxcondim=nmaxcondim, nmaxpyramid=int(max(1, 2 * (nmaxcondim - 1))),
     ngravcomp=int((reals["body_gravcomp"] != 0).sum()), is_sparse=int(sparse), nM=int(getattr(mjm, "nM", 0)),
-    ntree=int(getattr(mjm, "ntree", 0)),
+    ntree=int(getattr(mjm, "ntree", 0)), ngeompair=int(len(geom1)),
   )  # fmt: skip
   extra = dict(
     nsensordata=int(getattr(mjm, "nsensordata", 0)), ncam=int(getattr(mjm, "ncam", 0)), nlight=int(getattr(mjm, "nlight", 0)),

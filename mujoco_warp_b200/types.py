@@ -50,7 +50,7 @@ TILE_SIZE_JTDAJ_DENSE = 16  # reference types.py:35
 # ----------------------------------------------------------------------------------------------
 MODEL_SIZES = (
   "nq nv nu na nbody njnt ngeom nsite nmocap neq npair nxn nlevel nv_pad nlimit nlimitball "
-  "nfrictiondof neqjnt nJmom nmaxcondim nmaxpyramid ngravcomp is_sparse nM ntree"
+  "nfrictiondof neqjnt nJmom nmaxcondim nmaxpyramid ngravcomp is_sparse nM ntree ngeompair"
 ).split()
 
 MODEL_INT_FIELDS = {
@@ -85,6 +85,7 @@ MODEL_INT_FIELDS = {
   "site_bodyid": ("nsite",),
   "nxn_pair": ("nxn", 2),
   "nxn_pairid": ("nxn", 2),
+  "nxn_lookup": ("ngeompair",),
   "pair_dim": ("npair",),
   "actuator_trntype": ("nu",),
   "actuator_trnid": ("nu", 2),

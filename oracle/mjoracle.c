@@ -667,6 +667,47 @@ static void contact_params(const OModel* m, int g1, int g2, int pairid, real* ma
   for (int i = 0; i < 5; i++) friction[i] = friction[i] > MJ_MINMU ? friction[i] : MJ_MINMU;
 }
 
+/* collision_driver.sap_broadphase (collision_driver.py:554-644): bounding spheres (radius rbound + margin, planes
+ * unbounded) are projected on one fixed direction (:573-574), sorted by their lower end (:458-482), and every geom
+ * is paired with the geoms that follow it in sorted order up to and INCLUDING the first one whose lower end lies
+ * beyond its upper end (_sap_range :411-432: limit = min(ngeom - 1, first index with lower > upper)).  The pairs
+ * then go through the same static table and geometric filter as the NXN path (:485-551).  cand[p] marks entries of
+ * the filtered pair list that the sweep reaches. */
+static void sap_candidates(const OModel* m, const OData* d, unsigned char* cand) {
+  const int ng = m->ngeom;
+  real dir[3] = {0.5935, 0.7790, 0.1235};
+  real nrm = sqrt(dot3(dir, dir));
+  for (int i = 0; i < 3; i++) dir[i] /= nrm;
+  real* lower = (real*)malloc(sizeof(real) * 2 * ng);
+  real* upper = lower + ng;
+  int* order = (int*)malloc(sizeof(int) * ng);
+  for (int g = 0; g < ng; g++) {
+    real rb = m->geom_rbound[g];
+    if (rb == 0.0) rb = MJ_MAXVAL;
+    real radius = rb + m->geom_margin[g], centre = dot3(dir, d->geom_xpos + 3 * g);
+    if (isnan(centre)) { lower[g] = upper[g] = MJ_MAXVAL; } else { lower[g] = centre - radius; upper[g] = centre + radius; }
+    order[g] = g;
+  }
+  for (int i = 1; i < ng; i++) { /* stable insertion sort by lower end */
+    int g = order[i], j = i - 1;
+    while (j >= 0 && lower[order[j]] > lower[g]) { order[j + 1] = order[j]; j--; }
+    order[j + 1] = g;
+  }
+  memset(cand, 0, m->nxn);
+  for (int i = 0; i < ng; i++) {
+    int limit = i + 1;
+    while (limit < ng && !(lower[order[limit]] > upper[order[i]])) limit++;
+    if (limit > ng - 1) limit = ng - 1;
+    for (int j = i + 1; j <= limit; j++) {
+      int a = order[i], b = order[j];
+      if (b < a) { int t = a; a = b; b = t; }
+      int p = m->nxn_lookup[(a * (2 * ng - a - 3)) / 2 + b - 1];
+      if (p >= 0) cand[p] = 1;
+    }
+  }
+  free(lower); free(order);
+}
+
 #define O_MAXWCON 512
 typedef struct {
   OContactGeom g;
@@ -681,9 +722,15 @@ static int o_collision(const OModel* m, const OOpt* o, OData* d, const OData* gl
   OContactFull* buf = (OContactFull*)malloc(sizeof(OContactFull) * O_MAXWCON);
   d->wcon_n[0] = 0;
   if (glob->naconmax == 0 || (o->disableflags & (DSBL_CONSTRAINT | DSBL_CONTACT))) { free(buf); return 0; }
+  unsigned char* cand = NULL;
+  if (o->broadphase != 0 && m->nxn > 0) { /* BroadphaseType.SAP_TILE / SAP_SEGMENTED (types.py) differ only in the sort */
+    cand = (unsigned char*)malloc(m->nxn);
+    sap_candidates(m, d, cand);
+  }
   for (int p = 0; p < m->nxn; p++) {
     int ga = m->nxn_pair[2 * p], gb = m->nxn_pair[2 * p + 1];
     int pid0 = m->nxn_pairid[2 * p], pid1 = m->nxn_pairid[2 * p + 1];
+    if (cand && !cand[p]) continue;
     if (!(broadphase_filter(m, d, o->broadphase_filter, ga, gb) || pid1 >= 0)) continue;
     ncol++;
     int g1 = ga, g2 = gb;
@@ -709,6 +756,7 @@ static int o_collision(const OModel* m, const OOpt* o, OData* d, const OData* gl
       ncon++;
     }
   }
+  free(cand);
   if (ncon > O_MAXWCON) ncon = O_MAXWCON;
   int base, cbase;
 #pragma omp atomic capture

@@ -304,3 +304,29 @@ def test_full_size_properties(humanoid):
   O.run(om, od, "forward", nthread=4)
   np.testing.assert_array_equal(H.dev_np(d, "nefc")[idx], od.nefc)
   assert H.max_err(H.dev_np(d, "qacc")[idx], od.qacc) < 2e-2
+
+
+BF = C.BroadphaseFilter
+
+
+@pytest.mark.parametrize("broadphase", [C.BroadphaseType.SAP_TILE, C.BroadphaseType.SAP_SEGMENTED])
+@pytest.mark.parametrize("bfilter", [BF.PLANE | BF.SPHERE | BF.OBB, BF.PLANE | BF.AABB, BF.PLANE | BF.OBB, 0])
+def test_sweep_and_prune_broadphase(humanoid, broadphase, bfilter):
+  """reference collision_driver.py:554: the sweep result feeds the same filters as NXN.  Counts, contact lists
+  and the solved forces must equal the oracle's sweep; with the sphere filter on they also equal NXN's."""
+  qpos, qvel, ctrl = H.make_states(humanoid, 33, seed=40)
+  opt = {"broadphase": int(broadphase), "broadphase_filter": int(bfilter)}
+  _, od, m, d = run_both(humanoid, qpos, qvel, ctrl, 24, 64, opt=opt)
+  assert int(d.status.max()) == 0
+  np.testing.assert_array_equal(H.dev_np(d, "ncollision"), od.ncollision)
+  assert_forward_close(od, d)
+  geom_dev, geom_ref = H.dev_np(d, "contact_geom"), od.contact_geom
+  for w in range(33):
+    n = int(od.wcon_n[w])
+    np.testing.assert_array_equal(geom_dev[H.dev_np(d, "wcon")[w, :n]], geom_ref[od.wcon[w, :n]])
+  if bfilter & BF.SPHERE:
+    ncol, nefc = H.dev_np(d, "ncollision").copy(), H.dev_np(d, "nefc").copy()
+    m.opt.broadphase = int(C.BroadphaseType.NXN)
+    mjw.forward(m, d)
+    np.testing.assert_array_equal(H.dev_np(d, "ncollision"), ncol)
+    np.testing.assert_array_equal(H.dev_np(d, "nefc"), nefc)

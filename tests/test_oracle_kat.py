@@ -93,10 +93,11 @@ def run_collision(mjm, qpos, opt=None, nconmax=64, njmax=64, stages=("kinematics
   return om, d
 
 
+@pytest.mark.parametrize("broadphase", [C.BroadphaseType.NXN, C.BroadphaseType.SAP_TILE, C.BroadphaseType.SAP_SEGMENTED])
 @pytest.mark.parametrize("bfilter", FILTERS)
-def test_broadphase_counts(bfilter):
+def test_broadphase_counts(bfilter, broadphase):
   mjm = mjw.load_mjcf_string(BROADPHASE_XML)
-  opt = {"broadphase_filter": int(bfilter)}
+  opt = {"broadphase_filter": int(bfilter), "broadphase": int(broadphase)}
   for key, expected in [(0, 0), (1, 1), (2, 3), (3, 1)]:
     _, d = run_collision(mjm, mjm.key_qpos[key], opt)
     assert int(d.ncollision[0]) == expected, (key, int(bfilter))
