@@ -87,11 +87,157 @@ __device__ __forceinline__ void c_sphere_sphere(V3 p1, float r1, V3 p2, float r2
   pos = p1 + n * (r1 + 0.5f * dist);
 }
 
+__device__ __forceinline__ float safe_divf(float x, float y) { return x / (y != 0.f ? y : MJ_MINVAL); }
+
+// Sphere (geom 1) vs box (geom 2), collision_primitive_core.py:1103-1154.  `br` row-major box rotation.
+__device__ __forceinline__ void c_sphere_box(V3 sp, float r, V3 bp, const float* br, const float* bs, float& dist, V3& pos, V3& nrm) {
+  const V3 d0 = sp - bp;
+  float c[3], q[3], dl[3], nl[3] = {0.f, 0.f, 0.f}, loc[3];
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    c[i] = br[i] * d0.x + br[3 + i] * d0.y + br[6 + i] * d0.z;
+    q[i] = clampf(c[i], -bs[i], bs[i]);
+    dl[i] = q[i] - c[i];
+  }
+  const float len = sqrtf(dl[0] * dl[0] + dl[1] * dl[1] + dl[2] * dl[2]);
+  if (len <= MJ_MINVAL) {  // centre inside the box: nearest face, scanned -x,+x,-y,+y,-z,+z
+    float closest = 2.f * (bs[0] + bs[1] + bs[2]);
+    int k = 0;
+#pragma unroll
+    for (int i = 0; i < 6; i++) {
+      const float fd = fabsf(((i & 1) ? 1.f : -1.f) * bs[i / 2] - c[i / 2]);
+      if (closest > fd) { closest = fd; k = i; }
+    }
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      nl[i] = (i == k / 2) ? ((k & 1) ? -1.f : 1.f) : 0.f;
+      loc[i] = c[i] + nl[i] * (r - closest) * 0.5f;
+    }
+    dist = -closest - r;
+  } else {
+    const float inv = 1.f / len;
+#pragma unroll
+    for (int i = 0; i < 3; i++) { nl[i] = dl[i] * inv; loc[i] = 0.5f * (q[i] + c[i] + nl[i] * r); }
+    dist = len - r;
+  }
+  nrm = V3{br[0] * nl[0] + br[1] * nl[1] + br[2] * nl[2], br[3] * nl[0] + br[4] * nl[1] + br[5] * nl[2], br[6] * nl[0] + br[7] * nl[1] + br[8] * nl[2]};
+  pos = bp + V3{br[0] * loc[0] + br[1] * loc[1] + br[2] * loc[2], br[3] * loc[0] + br[4] * loc[1] + br[5] * loc[2],
+                br[6] * loc[0] + br[7] * loc[1] + br[8] * loc[2]};
+}
+
+// Capsule (geom 1) vs box (geom 2), collision_primitive_core.py:1158-1491: closest feature pair between the capsule
+// segment and the box (a segment end against a face, then the segment against each of the 12 edges), the discrete
+// configuration decides where a second support point along the segment lies, and both points are collided as spheres.
+// Returns the segment parameters t[0], t[1] (in half-lengths from the centre); n = number of points (0..2).
+// Out of line: keeps its register needs out of the humanoid's capsule / sphere / plane paths.
+__device__ __noinline__ int capsule_box_points(V3 cp, V3 caxis, float hl, V3 bp, const float* br, const float* bs, float* t) {
+  const V3 d0 = cp - bp;
+  float pl[3], ax[3], half[3];
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    pl[i] = br[i] * d0.x + br[3 + i] * d0.y + br[6 + i] * d0.z;
+    ax[i] = br[i] * caxis.x + br[3 + i] * caxis.y + br[6 + i] * caxis.z;
+    half[i] = ax[i] * hl;
+  }
+  const int axisdir = (half[0] > 0.f ? 1 : 0) + (half[1] > 0.f ? 2 : 0) + (half[2] > 0.f ? 4 : 0);
+  float best = 1.0e32f, bestseg = -12.f, bestbox = 0.f;
+  int cltype = -4, clface = -12, clcorner = -123, cledge = -123;
+#pragma unroll
+  for (int sg = -1; sg <= 1; sg += 2) {
+    float dd = 0.f;
+    int nout = 0, axout = -1;
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      const float tip = pl[j] + (float)sg * half[j];
+      float cj = tip;
+      if (cj < -bs[j]) { nout++; axout = j; cj = -bs[j]; } else if (cj > bs[j]) { nout++; axout = j; cj = bs[j]; }
+      dd += (cj - tip) * (cj - tip);
+    }
+    if (nout <= 1 && dd < best) { best = dd; bestseg = (float)sg; cltype = -2 + sg; clface = axout; }
+  }
+  const float mc = hl * hl;
+  for (int i = 0; i < 8; i++) {
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      if (i & (1 << j)) continue;
+      float dif[3];
+#pragma unroll
+      for (int k = 0; k < 3; k++) dif[k] = (k == j ? 0.f : ((i >> k) & 1 ? bs[k] : -bs[k])) - pl[k];
+      const float u = -bs[j] * dif[j], v = half[0] * dif[0] + half[1] * dif[1] + half[2] * dif[2];
+      const float ma = bs[j] * bs[j], mb = -bs[j] * half[j], det = ma * mc - mb * mb;
+      if (fabsf(det) < MJ_MINVAL) continue;
+      const float idet = 1.f / det;
+      float x1 = (mc * u - mb * v) * idet, x2 = (ma * v - mb * u) * idet;
+      int s1 = 1, s2 = 1;
+      if (x1 > 1.f) { x1 = 1.f; s1 = 2; x2 = safe_divf(v - mb, mc); }
+      else if (x1 < -1.f) { x1 = -1.f; s1 = 0; x2 = safe_divf(v + mb, mc); }
+      if (x2 > 1.f || x2 < -1.f) {
+        if (x2 > 1.f) { x2 = 1.f; s2 = 2; x1 = safe_divf(u - mb, ma); } else { x2 = -1.f; s2 = 0; x1 = safe_divf(u + mb, ma); }
+        if (x1 > 1.f) { x1 = 1.f; s1 = 2; } else if (x1 < -1.f) { x1 = -1.f; s1 = 0; }
+      }
+      float dd = 0.f;
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        const float e = dif[k] - half[k] * x2 + (k == j ? bs[j] * x1 : 0.f);
+        dd += e * e;
+      }
+      if (dd < best - MJ_MINVAL) {
+        best = dd; bestseg = x2; bestbox = x1;
+        cltype = s1 * 3 + s2;
+        clcorner = i + (1 << j) * (cltype / 6);
+        cledge = j;
+      }
+    }
+  }
+  if (cltype == -4) return 0;
+  float second = -4.f;
+  if (cltype >= 0 && cltype / 3 != 1) {  // a box corner is closest
+    int c1 = axisdir ^ clcorner;
+    if (c1 != 0 && c1 != 7) {
+      float mul = 1.f;
+      if (!(c1 == 1 || c1 == 2 || c1 == 4)) { mul = -1.f; c1 = 7 - c1; }
+      const int a = c1 == 1 ? 0 : (c1 == 2 ? 1 : 2), a1 = (a + 1) % 3, a2 = (a + 2) % 3;
+      if (ax[a] * ax[a] > 0.5f) second = fminf(1.f - mul * bestseg, 2.f * safe_divf(bs[a], fabsf(half[a])));
+      else second = -fminf(1.f + mul * bestseg, 2.f * fminf(safe_divf(bs[a1], fabsf(half[a1])), safe_divf(bs[a2], fabsf(half[a2]))));
+      second *= mul;
+    }
+  } else if (cltype >= 0) {  // the interior of a box edge is closest
+    const int c1 = (axisdir ^ clcorner) & (7 - (1 << cledge));
+    if (c1 == 1 || c1 == 2 || c1 == 4) {
+      const int a = cledge;
+      int a1 = (a + 1) % 3, a2 = (a + 2) % 3;
+      if (fabsf(ax[a1]) > fabsf(ax[a2])) a1 = a2;
+      a2 = 3 - a - a1;
+      float mul;
+      if (c1 & (1 << a2)) { mul = 1.f; second = 1.f - bestseg; } else { mul = -1.f; second = 1.f + bestseg; }
+      second = fminf(2.f * safe_divf(bs[a2], fabsf(half[a2])), second);
+      const float e2 = (((axisdir >> a) & 1) == ((c1 >> a2) & 1)) ? 1.f - bestbox : 1.f + bestbox;
+      second = fminf(bs[a] * safe_divf(e2, fabsf(half[a])), second) * mul;
+    }
+  } else if (clface != -1) {  // a segment end is closest to a face, from outside
+    const float mul = cltype == -3 ? 1.f : -1.f;
+    second = 2.f;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      if (i == clface) continue;
+      const float t1 = pl[i] - half[i] * mul, har = safe_divf(mul, half[i]);
+      float e1 = (bs[i] - t1) * har;
+      if (0.f < e1 && e1 < second) second = e1;
+      e1 = (-bs[i] - t1) * har;
+      if (0.f < e1 && e1 < second) second = e1;
+    }
+    second *= mul;
+  }
+  t[0] = bestseg;
+  t[1] = second + bestseg;
+  return second > -3.f ? 2 : 1;
+}
+
 // Number of candidate contacts of a pair type (collision_primitive.py wrappers).
 __device__ __forceinline__ int pair_ncand(int t1, int t2) {
   if (t1 == GEOM_PLANE) return t2 == GEOM_SPHERE ? 1 : (t2 == GEOM_CAPSULE ? 2 : (t2 == GEOM_BOX ? 8 : 0));
-  if (t1 == GEOM_SPHERE) return (t2 == GEOM_SPHERE || t2 == GEOM_CAPSULE) ? 1 : 0;
-  if (t1 == GEOM_CAPSULE && t2 == GEOM_CAPSULE) return 2;
+  if (t1 == GEOM_SPHERE) return (t2 == GEOM_SPHERE || t2 == GEOM_CAPSULE || t2 == GEOM_BOX) ? 1 : 0;
+  if (t1 == GEOM_CAPSULE) return (t2 == GEOM_CAPSULE || t2 == GEOM_BOX) ? 2 : 0;
   return 0;
 }
 
@@ -131,6 +277,16 @@ __device__ __forceinline__ void pair_contact(const PairGeom& g, const float* r2,
   V3 nrm = V3{1.f, 0.f, 0.f};
   if (g.t1 == GEOM_SPHERE && g.t2 == GEOM_SPHERE) {
     c_sphere_sphere(g.p1, g.s1.x, g.p2, g.s2.x, dist, pos, nrm);
+  } else if (g.t2 == GEOM_BOX) {  // sphere-box :1103, capsule-box :1158 (sphere tests at the support points)
+    const float bs[3] = {g.s2.x, g.s2.y, g.s2.z};
+    V3 centre = g.p1;
+    if (g.t1 == GEOM_CAPSULE) {
+      float t[2];
+      const int n = capsule_box_points(g.p1, g.n1, g.s1.y, g.p2, r2, bs, t);
+      if (k >= n) return;
+      centre = g.p1 + g.n1 * (g.s1.y * t[k]);
+    }
+    c_sphere_box(centre, g.s1.x, g.p2, r2, bs, dist, pos, nrm);
   } else if (g.t1 == GEOM_SPHERE) {  // sphere-capsule, core :147-178
     const V3 a = g.p2 - g.n2 * g.s2.y, ab = g.n2 * (2.0f * g.s2.y);
     const float t = clampf(dot(g.p1 - a, ab) / (dot(ab, ab) + 1e-6f), 0.f, 1.f);

@@ -536,6 +536,144 @@ static void closest_segment_point(real* r, const real* a, const real* b, const r
   for (int i = 0; i < 3; i++) r[i] = a[i] + t * ab[i];
 }
 
+/* collision_primitive_core.py:1103-1154.  Sphere (geom 1) against box (geom 2): the centre is taken into the box
+ * frame and clamped to the box; outside, the contact lies between the clamped point and the deepest sphere point;
+ * inside, the nearest face decides (faces scanned in the order -x,+x,-y,+y,-z,+z, strict improvement). */
+static void c_sphere_box(const real* sp, real r, const real* bp, const real* br, const real* bs, real* dist, real* pos, real* nrm) {
+  real c[3], q[3], dl[3], nl[3] = {0, 0, 0}, loc[3], len;
+  for (int i = 0; i < 3; i++) c[i] = br[i] * (sp[0] - bp[0]) + br[3 + i] * (sp[1] - bp[1]) + br[6 + i] * (sp[2] - bp[2]);
+  for (int i = 0; i < 3; i++) { q[i] = clampr(c[i], -bs[i], bs[i]); dl[i] = q[i] - c[i]; }
+  len = norm3(dl);
+  if (len <= MJ_MINVAL) {
+    real closest = 2.0 * (bs[0] + bs[1] + bs[2]);
+    int k = 0;
+    for (int i = 0; i < 6; i++) {
+      real fd = fabs(((i & 1) ? 1.0 : -1.0) * bs[i / 2] - c[i / 2]);
+      if (closest > fd) { closest = fd; k = i; }
+    }
+    nl[k / 2] = (k & 1) ? -1.0 : 1.0;
+    for (int i = 0; i < 3; i++) loc[i] = c[i] + nl[i] * (r - closest) / 2.0;
+    *dist = -closest - r;
+  } else {
+    for (int i = 0; i < 3; i++) { nl[i] = dl[i] / len; loc[i] = 0.5 * (q[i] + c[i] + nl[i] * r); }
+    *dist = len - r;
+  }
+  mat_vec(nrm, br, nl);
+  mat_vec(pos, br, loc);
+  for (int i = 0; i < 3; i++) pos[i] += bp[i];
+}
+
+/* collision_primitive_core.py:1158-1491 (after MuJoCo C's capsule-box).  Finds the closest feature pair between the
+ * capsule segment and the box (segment end vs face, then segment vs each of the 12 edges), derives from the discrete
+ * configuration where a second support point along the segment lies, and collides a sphere of the capsule's radius
+ * at both segment points with the box.  dist[1] = MJ_MAXVAL when there is no second point. */
+static void c_capsule_box(const real* cp, const real* caxis, real r, real hl, const real* bp, const real* br, const real* bs,
+                          real* dist, real* pos, real* nrm) {
+  real pl[3], ax[3], half[3];
+  for (int i = 0; i < 3; i++) {
+    pl[i] = br[i] * (cp[0] - bp[0]) + br[3 + i] * (cp[1] - bp[1]) + br[6 + i] * (cp[2] - bp[2]);
+    ax[i] = br[i] * caxis[0] + br[3 + i] * caxis[1] + br[6 + i] * caxis[2];
+    half[i] = ax[i] * hl;
+  }
+  const int axisdir = (half[0] > 0.0) + 2 * (half[1] > 0.0) + 4 * (half[2] > 0.0);
+  real best = 1.0e32, bestseg = -12.0, bestbox = 0.0;
+  int cltype = -4, clface = -12, clcorner = -123, cledge = -123;
+  dist[0] = dist[1] = MJ_MAXVAL;
+  memset(pos, 0, 6 * sizeof(real)); memset(nrm, 0, 6 * sizeof(real));
+  for (int sg = -1; sg <= 1; sg += 2) { /* a segment end closest to a face (or inside the box) */
+    real tip[3], dd = 0.0;
+    int nout = 0, axout = -1;
+    for (int j = 0; j < 3; j++) {
+      tip[j] = pl[j] + sg * half[j];
+      real cj = tip[j];
+      if (cj < -bs[j]) { nout++; axout = j; cj = -bs[j]; } else if (cj > bs[j]) { nout++; axout = j; cj = bs[j]; }
+      dd += (cj - tip[j]) * (cj - tip[j]);
+    }
+    if (nout > 1) continue;
+    if (dd < best) { best = dd; bestseg = sg; cltype = -2 + sg; clface = axout; }
+  }
+  for (int i = 0; i < 8; i++) { /* segment against the edge that leaves corner i along axis j */
+    for (int j = 0; j < 3; j++) {
+      if (i & (1 << j)) continue;
+      real e[3] = {(i & 1) ? bs[0] : -bs[0], (i & 2) ? bs[1] : -bs[1], (i & 4) ? bs[2] : -bs[2]}, dif[3];
+      e[j] = 0.0;
+      for (int k = 0; k < 3; k++) dif[k] = e[k] - pl[k];
+      real u = -bs[j] * dif[j], v = dot3(half, dif), ma = bs[j] * bs[j], mb = -bs[j] * half[j], mc = hl * hl;
+      real det = ma * mc - mb * mb;
+      if (fabs(det) < MJ_MINVAL) continue;
+      real x1 = (mc * u - mb * v) / det, x2 = (ma * v - mb * u) / det;
+      int s1 = 1, s2 = 1;
+      if (x1 > 1.0) { x1 = 1.0; s1 = 2; x2 = safe_div(v - mb, mc); }
+      else if (x1 < -1.0) { x1 = -1.0; s1 = 0; x2 = safe_div(v + mb, mc); }
+      if (x2 > 1.0 || x2 < -1.0) {
+        if (x2 > 1.0) { x2 = 1.0; s2 = 2; x1 = safe_div(u - mb, ma); } else { x2 = -1.0; s2 = 0; x1 = safe_div(u + mb, ma); }
+        if (x1 > 1.0) { x1 = 1.0; s1 = 2; } else if (x1 < -1.0) { x1 = -1.0; s1 = 0; }
+      }
+      for (int k = 0; k < 3; k++) dif[k] -= half[k] * x2;
+      dif[j] += bs[j] * x1;
+      real dd = dot3(dif, dif);
+      if (dd < best - MJ_MINVAL) {
+        best = dd; bestseg = x2; bestbox = x1;
+        cltype = s1 * 3 + s2;
+        clcorner = i + (1 << j) * (cltype / 6);
+        cledge = j;
+      }
+    }
+  }
+  if (cltype == -4) return;
+  real second = -4.0;
+  if (cltype >= 0 && cltype / 3 != 1) { /* a box corner is closest */
+    int c1 = axisdir ^ clcorner;
+    if (c1 != 0 && c1 != 7) {
+      int mul = 1;
+      if (!(c1 == 1 || c1 == 2 || c1 == 4)) { mul = -1; c1 = 7 - c1; }
+      int a = c1 == 1 ? 0 : (c1 == 2 ? 1 : 2), a1 = (a + 1) % 3, a2 = (a + 2) % 3;
+      if (ax[a] * ax[a] > 0.5) {
+        real mm = 2.0 * safe_div(bs[a], fabs(half[a]));
+        second = fmin(1.0 - mul * bestseg, mm);
+      } else {
+        real mm = 2.0 * fmin(safe_div(bs[a1], fabs(half[a1])), safe_div(bs[a2], fabs(half[a2])));
+        second = -fmin(1.0 + mul * bestseg, mm);
+      }
+      second *= mul;
+    }
+  } else if (cltype >= 0) { /* the interior of a box edge is closest */
+    int c1 = (axisdir ^ clcorner) & (7 - (1 << cledge));
+    if (c1 == 1 || c1 == 2 || c1 == 4) {
+      int a = cledge, a1 = (a + 1) % 3, a2 = (a + 2) % 3, mul;
+      if (fabs(ax[a1]) > fabs(ax[a2])) a1 = a2;
+      a2 = 3 - a - a1;
+      if (c1 & (1 << a2)) { mul = 1; second = 1.0 - bestseg; } else { mul = -1; second = 1.0 + bestseg; }
+      second = fmin(2.0 * safe_div(bs[a2], fabs(half[a2])), second);
+      real e2 = (((axisdir >> a) & 1) == ((c1 >> a2) & 1)) ? 1.0 - bestbox : 1.0 + bestbox;
+      second = fmin(bs[a] * safe_div(e2, fabs(half[a])), second);
+      second *= mul;
+    }
+  } else if (clface != -1) { /* a segment end is closest to a face, from outside */
+    int mul = cltype == -3 ? 1 : -1;
+    real t1[3];
+    second = 2.0;
+    for (int i = 0; i < 3; i++) t1[i] = pl[i] - half[i] * mul;
+    for (int i = 0; i < 3; i++) {
+      if (i == clface) continue;
+      real har = safe_div((real)mul, half[i]);
+      real e1 = (bs[i] - t1[i]) * har;
+      if (0.0 < e1 && e1 < second) second = e1;
+      e1 = (-bs[i] - t1[i]) * har;
+      if (0.0 < e1 && e1 < second) second = e1;
+    }
+    second *= mul;
+  }
+  for (int k = 0; k < 2; k++) {
+    if (k == 1 && !(second > -3.0)) break;
+    real t = k == 0 ? bestseg : second + bestseg, loc[3], glob[3];
+    for (int i = 0; i < 3; i++) loc[i] = pl[i] + half[i] * t;
+    mat_vec(glob, br, loc);
+    for (int i = 0; i < 3; i++) glob[i] += bp[i];
+    c_sphere_box(glob, r, bp, br, bs, dist + k, pos + 3 * k, nrm + 3 * k);
+  }
+}
+
 /* Computes the contact geometries of one geom pair; returns the number of candidates
  * (collision_primitive.py wrappers :280-1280 + cores).  Candidates with dist >= margin are
  * dropped by the caller (collision_core.py:199-203). */
@@ -597,6 +735,23 @@ static int narrowphase_pair(const OModel* m, const OData* d, int g1, int g2, rea
     make_frame(out[0].frame, n);
     out[0].id = 0;
     return 1;
+  }
+  if (t1 == GEOM_SPHERE && t2 == GEOM_BOX) { /* collision_primitive.py:1047 */
+    real n[3];
+    c_sphere_box(p1, s1[0], p2, r2, s2, &out[0].dist, out[0].pos, n);
+    make_frame(out[0].frame, n);
+    out[0].id = 0;
+    return 1;
+  }
+  if (t1 == GEOM_CAPSULE && t2 == GEOM_BOX) { /* collision_primitive.py:1117 */
+    real dist[2], pos[6], n[6];
+    c_capsule_box(p1, n1, s1[0], s1[1], p2, r2, s2, dist, pos, n);
+    for (int k = 0; k < 2; k++) {
+      out[k].dist = dist[k]; out[k].id = k;
+      memcpy(out[k].pos, pos + 3 * k, 3 * sizeof(real));
+      if (dist[k] < MJ_MAXVAL) make_frame(out[k].frame, n + 3 * k); else memset(out[k].frame, 0, 9 * sizeof(real));
+    }
+    return 2;
   }
   if (t1 == GEOM_CAPSULE && t2 == GEOM_CAPSULE) { /* collision_primitive_core.py:182-308 */
     real ax1[3], ax2[3], dif[3], n[3], v1[3], v2[3], dist, pos[3];

@@ -185,3 +185,60 @@ def test_cg_and_newton_agree(humanoid):
   _, b = H.oracle_data(humanoid, qpos, qvel, ctrl, 24, 64)
   O.run(om, b, "forward", opt={"solver": 1, "iterations": 500, "tolerance": 1e-10})
   np.testing.assert_allclose(a.qacc, b.qacc, rtol=1e-4, atol=1e-4)
+
+
+# ---- box primitives (collision_primitive_core.py:1103 sphere_box, :1158 capsule_box) against sampled geometry ------
+BOX_XML = """
+<mujoco>
+  <worldbody>
+    <body pos="0 0 0"><freejoint/><geom type="box" size=".2 .3 .15" margin="1"/></body>
+    <body pos="1 0 0"><freejoint/><geom type="sphere" size=".1" margin="1"/></body>
+    <body pos="0 1 0"><freejoint/><geom type="capsule" size=".07 .25" margin="1"/></body>
+  </worldbody>
+</mujoco>"""
+
+
+def _box_distance(p, bp, rot, size):
+  c = rot.T @ (p - bp)
+  if np.all(np.abs(c) < size):
+    return -np.min(size - np.abs(c))
+  return np.linalg.norm(np.clip(c, -size, size) - c)
+
+
+def test_sphere_box_and_capsule_box_distances_match_sampled_geometry():
+  from tests.test_oracle_kat import run_collision
+
+  mjm = mjw.load_mjcf_string(BOX_XML)
+  rng = np.random.default_rng(0)
+  nw = 200
+  qpos = np.zeros((nw, 21))
+  for b in range(3):
+    qpos[:, 7 * b : 7 * b + 3] = rng.uniform(-0.45, 0.45, (nw, 3))
+    q = rng.normal(size=(nw, 4))
+    qpos[:, 7 * b + 3 : 7 * b + 7] = q / np.linalg.norm(q, axis=1, keepdims=True)
+  _, d = run_collision(mjm, qpos, nconmax=16)
+  size, ts = np.array([0.2, 0.3, 0.15]), np.linspace(-1, 1, 2001)
+  nsphere = ncap = nsecond = 0
+  for w in range(nw):
+    xpos, xmat = d.geom_xpos[w].reshape(-1, 3), d.geom_xmat[w].reshape(-1, 3, 3)
+    first = None
+    for k in range(int(d.wcon_n[w])):
+      cid = int(d.wcon[w, k])
+      g, dist = tuple(int(x) for x in d.contact_geom[cid]), float(d.contact_dist[cid])
+      frame = d.contact_frame[cid].reshape(3, 3)
+      np.testing.assert_allclose(frame @ frame.T, np.eye(3), atol=1e-9)
+      if g == (1, 0):  # sphere (type 2) sorts before box (type 6)
+        assert abs(_box_distance(xpos[1], xpos[0], xmat[0], size) - 0.1 - dist) < 1e-9
+        nsphere += 1
+      elif g == (2, 0):
+        dd = np.array([_box_distance(xpos[2] + xmat[2][:, 2] * 0.25 * t, xpos[0], xmat[0], size) for t in ts])
+        if int(d.contact_geomcollisionid[cid]) == 0:
+          first = dist
+          if dd.min() > 0:  # segment outside the box: the first contact is the closest approach of the segment
+            assert abs(dd.min() - 0.07 - dist) < 5e-4
+          ncap += 1
+        else:
+          nsecond += 1
+          assert dist >= dd.min() - 0.07 - 1e-9  # no point of the segment is closer than the closest one
+          assert first is not None
+  assert nsphere > 100 and ncap > 100 and nsecond > 20
