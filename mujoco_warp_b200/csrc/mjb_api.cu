@@ -36,6 +36,7 @@ struct MjbModel {
   ModelOffsets mo;
   const unsigned char* blob;
   int blob_bytes;
+  int col_feat;  // CollisionFeature bits the model needs (pair types present in the filtered pair list)
 };
 
 struct MjbData {
@@ -51,7 +52,7 @@ struct MjbData {
   struct GroupCfg {  // launch configuration of one stage-group kernel, resolved on first use
     int ready, wpb, grid, in_smem, scratch_floats;
     size_t smem;
-  } cfg[G_COUNT];
+  } cfg[G_COUNT + COLF_COUNT];  // [G_COUNT + v]: collision variant v > 0
 };
 
 // ---- field-table introspection --------------------------------------------------------------
@@ -137,6 +138,22 @@ extern "C" int mjb_model_create(const int* sizes, int nsizes, const void* blob, 
   }
   m->blob = static_cast<const unsigned char*>(blob);
   m->blob_bytes = (int)nbytes;
+  m->col_feat = 0;
+  if (m->ms.nxn > 0) {  // pair types present in the statically filtered pair list (one small read-back at creation)
+    std::vector<int> pair(2 * (size_t)m->ms.nxn), gtype((size_t)m->ms.ngeom);
+    const unsigned char* db = static_cast<const unsigned char*>(blob);
+    cudaError_t e = cudaMemcpy(pair.data(), db + m->mo.nxn_pair, pair.size() * sizeof(int), cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(gtype.data(), db + m->mo.geom_type, gtype.size() * sizeof(int), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) {
+      delete m;
+      return fail(-10, std::string("mjb_model_create: ") + cudaGetErrorString(e));
+    }
+    for (int p = 0; p < m->ms.nxn; p++) {
+      const int ta = gtype[pair[2 * p]], tb = gtype[pair[2 * p + 1]];
+      const int t1 = ta < tb ? ta : tb, t2 = ta < tb ? tb : ta;
+      if (t2 == GEOM_BOX && t1 != GEOM_PLANE) m->col_feat |= COLF_BOX;
+    }
+  }
   *out = m;
   return 0;
 }
@@ -234,14 +251,20 @@ static int timed_launch(cudaStream_t stream, F&& launch, int group = -1) {
 }
 
 typedef void (*GroupKernel)(const KParams);
-template <int G>
+template <int G, int V = 0>
 static GroupKernel group_kernel(bool in_smem) {
-  return in_smem ? mjb_group_kernel<G, true> : mjb_group_kernel<G, false>;
+  return in_smem ? mjb_group_kernel<G, true, V> : mjb_group_kernel<G, false, V>;
 }
-static GroupKernel group_kernel_of(int g, bool in_smem) {
+static GroupKernel group_kernel_of(int g, bool in_smem, int variant) {
   switch (g) {
     case G_POS: return group_kernel<G_POS>(in_smem);
-    case G_COL: return group_kernel<G_COL>(in_smem);
+    case G_COL:
+      switch (variant) {
+        case 1: return group_kernel<G_COL, 1>(in_smem);
+        case 2: return group_kernel<G_COL, 2>(in_smem);
+        case 3: return group_kernel<G_COL, 3>(in_smem);
+        default: return group_kernel<G_COL, 0>(in_smem);
+      }
     case G_CON: return group_kernel<G_CON>(in_smem);
     case G_VEL: return group_kernel<G_VEL>(in_smem);
     case G_SOL: return group_kernel<G_SOL>(in_smem);
@@ -250,17 +273,19 @@ static GroupKernel group_kernel_of(int g, bool in_smem) {
 }
 
 static int launch_group(int g, const MjbModel* m, MjbData* d, KParams& K, uint32_t stages, cudaStream_t stream) {
-  MjbData::GroupCfg& c = d->cfg[g];
+  // collision: the kernel variant follows the model's pair types and the broadphase option of THIS call
+  const int variant = g == G_COL ? (m->col_feat | (K.o.broadphase != 0 ? COLF_SAP : 0)) : 0;
+  MjbData::GroupCfg& c = d->cfg[variant ? G_COUNT + variant : g];
   if (!c.ready) {
     int wpb = warps_per_block(g == G_SOL ? group_threads(G_SOL) / 32 : 8);
     if (32 * wpb > group_threads(g)) wpb = group_threads(g) / 32;
-    c.scratch_floats = group_scratch_floats(g, m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad, m->ms.ngeom, m->ms.nxn);
+    c.scratch_floats = group_scratch_floats(g, m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad, m->ms.ngeom, m->ms.nxn, variant);
     const size_t scr_bytes = (size_t)wpb * c.scratch_floats * sizeof(float);
     const bool in_smem =
         group_uses_blob(g) && (size_t)m->blob_bytes + 16 + scr_bytes <= (size_t)d->smem_optin && m->blob_bytes <= 96 * 1024;
     const size_t smem = in_smem ? (size_t)m->blob_bytes + 16 + scr_bytes : scr_bytes;
     if (smem > (size_t)d->smem_optin) return fail(-5, "model needs more shared memory than the device offers");
-    GroupKernel k0 = group_kernel_of(g, in_smem);
+    GroupKernel k0 = group_kernel_of(g, in_smem, variant);
     CUDA_OK(cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int occ = 1;
     CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k0, 32 * wpb, smem));
@@ -276,7 +301,7 @@ static int launch_group(int g, const MjbModel* m, MjbData* d, KParams& K, uint32
   }
   K.stages = stages;
   K.scratch_floats = c.scratch_floats;
-  GroupKernel kern = group_kernel_of(g, c.in_smem != 0);
+  GroupKernel kern = group_kernel_of(g, c.in_smem != 0, variant);
   const int grid = c.grid, threads = 32 * c.wpb;
   const size_t smem = c.smem;
   // Programmatic dependent launch: the next group's CTAs may be scheduled (and stage the model blob)

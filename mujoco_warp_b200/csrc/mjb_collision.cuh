@@ -14,6 +14,10 @@
 
 #include "mjb_types.cuh"
 
+// Compile-time variants of the collision kernel (template parameter FEAT): code a model / option set does not need
+// is not compiled into the variant it runs, so it costs the common case neither registers nor instruction cache.
+enum CollisionFeature { COLF_BOX = 1 /* sphere-box, capsule-box pairs present */, COLF_SAP = 2 /* sweep-and-prune broadphase */, COLF_COUNT = 4 };
+
 // collision_driver.py:91-111, 218-271
 __device__ __forceinline__ bool bp_filter(const KParams& K, const unsigned char* mb, int w, int g1, int g2) {
   const float rb1 = MR(geom_rbound)[g1], rb2 = MR(geom_rbound)[g2];
@@ -130,7 +134,7 @@ __device__ __forceinline__ void c_sphere_box(V3 sp, float r, V3 bp, const float*
 // configuration decides where a second support point along the segment lies, and both points are collided as spheres.
 // Returns the segment parameters t[0], t[1] (in half-lengths from the centre); n = number of points (0..2).
 // Out of line: keeps its register needs out of the humanoid's capsule / sphere / plane paths.
-__device__ __noinline__ int capsule_box_points(V3 cp, V3 caxis, float hl, V3 bp, const float* br, const float* bs, float* t) {
+__device__ __forceinline__ int capsule_box_points(V3 cp, V3 caxis, float hl, V3 bp, const float* br, const float* bs, float* t) {
   const V3 d0 = cp - bp;
   float pl[3], ax[3], half[3];
 #pragma unroll
@@ -242,6 +246,7 @@ __device__ __forceinline__ int pair_ncand(int t1, int t2) {
 }
 
 // k-th candidate contact of the pair: distance, position, frame.  `r2` = rotation of geom 2.
+template <int FEAT>
 __device__ __forceinline__ void pair_contact(const PairGeom& g, const float* r2, float margin, int k, float& dist, V3& pos, M3& frame) {
   dist = INFINITY;
   pos = V3{0.f, 0.f, 0.f};
@@ -277,7 +282,7 @@ __device__ __forceinline__ void pair_contact(const PairGeom& g, const float* r2,
   V3 nrm = V3{1.f, 0.f, 0.f};
   if (g.t1 == GEOM_SPHERE && g.t2 == GEOM_SPHERE) {
     c_sphere_sphere(g.p1, g.s1.x, g.p2, g.s2.x, dist, pos, nrm);
-  } else if (g.t2 == GEOM_BOX) {  // sphere-box :1103, capsule-box :1158 (sphere tests at the support points)
+  } else if ((FEAT & COLF_BOX) && g.t2 == GEOM_BOX) {  // sphere-box :1103, capsule-box :1158 (sphere tests at the support points)
     const float bs[3] = {g.s2.x, g.s2.y, g.s2.z};
     V3 centre = g.p1;
     if (g.t1 == GEOM_CAPSULE) {
@@ -380,6 +385,7 @@ __device__ __forceinline__ void contact_params(const KParams& K, const unsigned 
 }
 
 // Narrowphase for up to 32 queued pairs (one lane each); appends contacts to the pool.
+template <int FEAT>
 __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsigned char* mb, int w, int lane, const int* queue, int count,
                                                   int& nw) {
   const bool has = lane < count;
@@ -411,7 +417,7 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
       float dist;
       V3 pos;
       M3 frame;
-      pair_contact(g, r2, cp.margin, k, dist, pos, frame);
+      pair_contact<FEAT>(g, r2, cp.margin, k, dist, pos, frame);
       const bool active = dist < cp.margin;
       if (!((pid0 == -2 || !active) && pid1 == -1)) nact++;
     }
@@ -429,7 +435,7 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
       float dist;
       V3 pos;
       M3 frame;
-      pair_contact(g, r2, cp.margin, k, dist, pos, frame);
+      pair_contact<FEAT>(g, r2, cp.margin, k, dist, pos, frame);
       const bool active = dist < cp.margin;
       if ((pid0 == -2 || !active) && pid1 == -1) continue;
       const int cid = base + slot;
@@ -537,12 +543,13 @@ __device__ __forceinline__ void sap_candidates(const KParams& K, const unsigned 
 }
 
 // collision_driver.collision (collision_driver.py:755).  scratch: collision_scratch_words() ints per warp.
+template <int FEAT>
 __device__ __forceinline__ void s_collision(const KParams& K, const unsigned char* mb, int w, int lane, int* queue) {
   int nw = 0, ncol = 0, qn = 0;
   const bool enabled = K.dsz.naconmax > 0 && !(K.o.disableflags & (DSBL_CONSTRAINT | DSBL_CONTACT));
   if (enabled) {
     const int nxn = K.ms.nxn;
-    const bool sap = uniform_b(K.o.broadphase != 0 && nxn > 0);
+    const bool sap = (FEAT & COLF_SAP) != 0 && nxn > 0;
     unsigned* bits = reinterpret_cast<unsigned*>(queue + 72 + 4 * K.ms.ngeom);
     if (sap) sap_candidates(K, mb, w, lane, queue + 72, bits);
     for (int p0 = 0; p0 < nxn; p0 += 32) {
@@ -555,7 +562,7 @@ __device__ __forceinline__ void s_collision(const KParams& K, const unsigned cha
       ncol += __popc(mask);
       __syncwarp();
       if (qn >= 32) {
-        narrowphase_flush(K, mb, w, lane, queue, 32, nw);
+        narrowphase_flush<FEAT>(K, mb, w, lane, queue, 32, nw);
         __syncwarp();
         const int rem = qn - 32;
         int v = 0;
@@ -566,7 +573,7 @@ __device__ __forceinline__ void s_collision(const KParams& K, const unsigned cha
         __syncwarp();
       }
     }
-    if (qn > 0) narrowphase_flush(K, mb, w, lane, queue, qn, nw);
+    if (qn > 0) narrowphase_flush<FEAT>(K, mb, w, lane, queue, qn, nw);
   }
   if (lane == 0) {
     DW(wcon_n)[0] = min(nw, K.dsz.nwconmax);

@@ -40,13 +40,13 @@ __host__ __device__ inline uint32_t group_mask(int g) {
 }
 
 // per-warp shared-memory scratch (floats) of a group
-__host__ __device__ inline int group_scratch_floats(int g, int nv, int nv_pad, int njmax_pad, int ngeom, int nxn) {
+__host__ __device__ inline int group_scratch_floats(int g, int nv, int nv_pad, int njmax_pad, int ngeom, int nxn, int variant = 0) {
   int n = 0;
   switch (g) {
     case G_POS:
     case G_VEL:
     case G_EUL: n = chol_scratch_floats(nv, nv_pad); break;
-    case G_COL: n = collision_scratch_words(ngeom, nxn); break;
+    case G_COL: n = (variant & COLF_SAP) ? collision_scratch_words(ngeom, nxn) : 72; break;
     case G_CON: n = 0; break;
     case G_SOL: n = solver_scratch_floats(nv, nv_pad, njmax_pad); break;
   }
@@ -90,7 +90,8 @@ __host__ __device__ constexpr int group_min_ctas(int g) {
   return g == G_SOL ? MJB_SOL_MIN_CTAS : g == G_COL ? MJB_COL_MIN_CTAS : g == G_POS ? 4 : g == G_CON ? MJB_CON_MIN_CTAS : 3;
 }
 
-template <int G, bool BLOB_IN_SMEM>
+// V: compile-time variant of the group (collision: CollisionFeature bits; 0 elsewhere)
+template <int G, bool BLOB_IN_SMEM, int V = 0>
 __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group_kernel(const __grid_constant__ KParams K) {
   extern __shared__ __align__(16) unsigned char smem[];
   const unsigned char* mb;
@@ -127,7 +128,7 @@ __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group
       if (st & MJB_STAGE_FACTOR_M) s_factor_m(K, w, lane, scr);
       if (st & MJB_STAGE_TRANSMISSION) s_transmission(K, mb, w, lane);
     } else if constexpr (G == G_COL) {
-      if (K.o.run_collision_detection) s_collision(K, mb, w, lane, reinterpret_cast<int*>(scr));
+      if (K.o.run_collision_detection) s_collision<V>(K, mb, w, lane, reinterpret_cast<int*>(scr));
     } else if constexpr (G == G_CON) {
       s_make_constraint(K, mb, w, lane);
     } else if constexpr (G == G_VEL) {
