@@ -89,8 +89,6 @@ def _check_supported(mjm):
   # features of the reference that this library does not implement yet (scope)
   if is_sparse(mjm):
     raise NotImplementedError("sparse mass matrix / Jacobian (nv > 32 or jacobian=sparse) is not implemented yet.")
-  if int(mjm.opt.cone) == C.ConeType.ELLIPTIC:
-    raise NotImplementedError("elliptic friction cones are not implemented yet.")
   for name in ("ntendon", "nflex", "nmesh", "nhfield"):
     if getattr(mjm, name, 0):
       raise NotImplementedError(f"{name} > 0 is not implemented yet.")

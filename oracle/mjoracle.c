@@ -1073,12 +1073,44 @@ static void o_make_constraint(const OModel* m, const OOpt* o, OData* d, const OD
       real includemargin = glob->contact_includemargin[cid];
       real pos = glob->contact_dist[cid] - includemargin;
       if (!(pos < 0)) continue;
-      int nrow = condim == 1 ? 1 : 2 * (condim - 1);
+      int elliptic = o->cone == 1; /* ConeType.ELLIPTIC */
+      int nrow = condim == 1 ? 1 : (elliptic ? condim : 2 * (condim - 1));
       int g1 = glob->contact_geom[2 * cid], g2 = glob->contact_geom[2 * cid + 1];
       int b1 = m->geom_bodyid[g1], b2 = m->geom_bodyid[g2];
       const real *cpos = glob->contact_pos + 3 * cid, *frame = glob->contact_frame + 9 * cid, *fri = glob->contact_friction + 5 * cid;
       real invw0 = m->body_invweight0[2 * b1] + m->body_invweight0[2 * b2];
       int wb1 = m->body_weldid[b1], wb2 = m->body_weldid[b2];
+      if (elliptic) { /* constraint.py:1940-2206: rows = normal, then one per friction direction, in contact-frame axes */
+        real invw = m->body_invweight0[2 * wb1] + m->body_invweight0[2 * wb2]; /* after the weld mapping (:2049-2050, :2146) */
+        for (int dimid = 0; dimid < nrow; dimid++) {
+          int r = nefc++;
+          if (r >= njmax) { glob->contact_efc_address[cid * nmp + dimid] = -1; continue; }
+          glob->contact_efc_address[cid * nmp + dimid] = r;
+          real* J = d->efc_J + (size_t)r * np;
+          real Jqvel = 0;
+          for (int dof = 0; dof < nv; dof++) {
+            real j1p[3], j1r[3], j2p[3], j2r[3], Jd = 0;
+            jac_dof(m, d, cpos, wb1, dof, j1p, j1r);
+            jac_dof(m, d, cpos, wb2, dof, j2p, j2r);
+            for (int x = 0; x < 3; x++)
+              Jd += dimid < 3 ? frame[3 * dimid + x] * (j2p[x] - j1p[x]) : frame[3 * (dimid - 3) + x] * (j2r[x] - j1r[x]);
+            J[dof] = Jd;
+            Jqvel += Jd * d->qvel[dof];
+          }
+          const real* ref = glob->contact_solref + 2 * cid;
+          real invweight = invw, pos_aref = pos;
+          if (dimid > 0) {
+            const real* srf = glob->contact_solreffriction + 2 * cid;
+            if (srf[0] != 0.0 || srf[1] != 0.0) ref = srf;
+            invweight *= o->impratio_invsqrt * o->impratio_invsqrt;
+            if (dimid > 1) invweight *= fri[0] * fri[0] / (fri[dimid - 1] * fri[dimid - 1]);
+            pos_aref = 0.0;
+          }
+          efc_row(o, d, r, pos_aref, pos, invweight, ref, glob->contact_solimp + 5 * cid, includemargin, Jqvel, 0.0,
+                  condim == 1 ? CT_CONTACT_FRICTIONLESS : CT_CONTACT_ELLIPTIC, cid);
+        }
+        continue;
+      }
       for (int dimid = 0; dimid < nrow; dimid++) {
         int r = nefc++;
         if (r >= njmax) { glob->contact_efc_address[cid * nmp + dimid] = -1; continue; }
@@ -1400,13 +1432,59 @@ typedef struct {
   int nefc, ne, nf;
   real *Jaref, *jv, *grad, *Mgrad, *search, *mv, *H, *L, *prev_grad, *prev_Mgrad;
   real gauss, cost, prev_cost, search_dot, grad_dot;
+  const OData* glob; /* pooled contact arrays (elliptic cones read friction / dim / efc_address) */
+  int nmp, elliptic;
+  real impratio_invsqrt;
 } OSolver;
+
+/* solver.py:263-319 _eval_elliptic: cost, gradient, curvature of one elliptic contact along the search direction.
+ * quad = summed quadratic of its rows; q1 = (u0, v0, uu); q2 = (uv, vv, dm) as prepared at solver.py:986-1050. */
+static pt3 eval_pt_quad(const real* q, real alpha);
+static pt3 eval_elliptic(real mu, const real* quad, const real* q1, const real* q2, real alpha) {
+  pt3 z = {0, 0, 0};
+  real u0 = q1[0], v0 = q1[1], uu = q1[2], uv = q2[0], vv = q2[1], dm = q2[2];
+  real N = u0 + alpha * v0, Tsqr = uu + alpha * (2.0 * uv + alpha * vv);
+  if (Tsqr <= 0.0) return N < 0.0 ? eval_pt_quad(quad, alpha) : z;
+  real T = sqrt(Tsqr);
+  if (N >= mu * T) return z;
+  if (mu * N + T <= 0.0) return eval_pt_quad(quad, alpha);
+  real N1 = v0, T1 = (uv + alpha * vv) / T, T2 = vv / T - (uv + alpha * vv) * T1 / (T * T), e = N - mu * T, e1 = N1 - mu * T1;
+  pt3 r = {0.5 * dm * e * e, dm * e * e1, dm * (e1 * e1 + e * (-mu * T2))};
+  return r;
+}
+/* rows of one elliptic contact: returns dim and fills adr[dim]; 0 if any row is missing (njmax overflow) */
+static int elliptic_rows(const OSolver* s, int conid, int* adr) {
+  int dim = s->glob->contact_dim[conid];
+  for (int j = 0; j < dim; j++) {
+    adr[j] = s->glob->contact_efc_address[conid * s->nmp + j];
+    if (adr[j] < 0) return 0;
+  }
+  return dim;
+}
+/* evaluation of row r of an elliptic contact at alpha (solver.py:602-628, 986-1050): only the primary row contributes */
+static pt3 elliptic_row_eval(const OData* d, const OSolver* s, int r, real alpha) {
+  pt3 z = {0, 0, 0};
+  int conid = d->efc_id[r], adr[6];
+  int dim = elliptic_rows(s, conid, adr);
+  if (!dim || adr[0] != r) return z;
+  const real* fri = s->glob->contact_friction + 5 * conid;
+  real mu = fri[0] * s->impratio_invsqrt, D0 = d->efc_D[r], ja = s->Jaref[r], jv = s->jv[r];
+  real quad[3] = {0.5 * ja * ja * D0, jv * D0 * ja, 0.5 * jv * jv * D0}, q1[3] = {ja * mu, jv * mu, 0}, q2[3] = {0, 0, D0 / (mu * mu * (1.0 + mu * mu))};
+  for (int j = 1; j < dim; j++) {
+    real jaj = s->Jaref[adr[j]], jvj = s->jv[adr[j]], dj = d->efc_D[adr[j]], uj = jaj * fri[j - 1], vj = jvj * fri[j - 1];
+    quad[0] += 0.5 * jaj * dj * jaj; quad[1] += jvj * dj * jaj; quad[2] += 0.5 * jvj * dj * jvj;
+    q1[2] += uj * uj; q2[0] += uj * vj; q2[1] += vj * vj;
+  }
+  return eval_elliptic(mu, quad, q1, q2, alpha);
+}
 
 /* total 1-D cost model at step alpha (sum over rows + Gauss quadratic) */
 static pt3 ls_eval(const OData* d, const OSolver* s, const real* quad_gauss, real alpha) {
   pt3 t = eval_pt_quad(quad_gauss, alpha);
-  for (int r = 0; r < s->nefc; r++)
-    t = pt_add(t, efc_eval_pt(r, alpha, s->ne, s->nf, d->efc_D[r], d->efc_frictionloss[r], s->Jaref[r], s->jv[r]));
+  for (int r = 0; r < s->nefc; r++) {
+    if (s->elliptic && r >= s->ne + s->nf && d->efc_type[r] == CT_CONTACT_ELLIPTIC) t = pt_add(t, elliptic_row_eval(d, s, r, alpha));
+    else t = pt_add(t, efc_eval_pt(r, alpha, s->ne, s->nf, d->efc_D[r], d->efc_frictionloss[r], s->Jaref[r], s->jv[r]));
+  }
   return t;
 }
 
@@ -1427,8 +1505,10 @@ static real o_linesearch(const OModel* m, const OOpt* o, OData* d, OSolver* s) {
     qg[2] += 0.5 * s->search[i] * s->mv[i];
   }
   pt3 p0 = {qg[0], qg[1], 2.0 * qg[2]};
-  for (int r = 0; r < s->nefc; r++)
-    p0 = pt_add(p0, efc_eval_pt(r, 0.0, s->ne, s->nf, d->efc_D[r], d->efc_frictionloss[r], s->Jaref[r], s->jv[r]));
+  for (int r = 0; r < s->nefc; r++) {
+    if (s->elliptic && r >= s->ne + s->nf && d->efc_type[r] == CT_CONTACT_ELLIPTIC) p0 = pt_add(p0, elliptic_row_eval(d, s, r, 0.0));
+    else p0 = pt_add(p0, efc_eval_pt(r, 0.0, s->ne, s->nf, d->efc_D[r], d->efc_frictionloss[r], s->Jaref[r], s->jv[r]));
+  }
   real lo_alpha_in = -safe_div(p0.g, p0.h);
   pt3 lo_in = ls_eval(d, s, qg, lo_alpha_in);
   real alpha;
@@ -1484,9 +1564,29 @@ static void o_update_constraint(const OModel* m, OData* d, OSolver* s) {
       if (ja <= -rf) { d->efc_force[r] = f; st = ST_LINEARNEG; cost += -f * (0.5 * rf + ja); }
       else if (ja >= rf) { d->efc_force[r] = -f; st = ST_LINEARPOS; cost += -f * (0.5 * rf - ja); }
       else { d->efc_force[r] = -D * ja; st = ST_QUADRATIC; cost += 0.5 * D * ja * ja; }
-    } else {
+    } else if (!(s->elliptic && d->efc_type[r] == CT_CONTACT_ELLIPTIC)) {
       if (ja >= 0.0) { d->efc_force[r] = 0; st = ST_SATISFIED; }
       else { d->efc_force[r] = -D * ja; st = ST_QUADRATIC; cost += 0.5 * D * ja * ja; }
+    } else { /* elliptic friction cone contact, solver.py:1886-1943 */
+      int conid = d->efc_id[r], adr[6];
+      int dim = elliptic_rows(s, conid, adr);
+      if (!dim) continue;
+      const real* fri = s->glob->contact_friction + 5 * conid;
+      real mu = fri[0] * s->impratio_invsqrt, N = s->Jaref[adr[0]] * mu, TT = 0, ufr = 0;
+      for (int j = 1; j < dim; j++) {
+        real uj = s->Jaref[adr[j]] * fri[j - 1];
+        TT += uj * uj;
+        if (adr[j] == r) ufr = uj * fri[j - 1];
+      }
+      real T = TT <= 0.0 ? 0.0 : sqrt(TT);
+      if (N >= mu * T || (T <= 0.0 && N >= 0.0)) { d->efc_force[r] = 0; st = ST_SATISFIED; }
+      else if (mu * N + T <= 0.0 || (T <= 0.0 && N < 0.0)) { d->efc_force[r] = -D * ja; st = ST_QUADRATIC; cost += 0.5 * D * ja * ja; }
+      else {
+        real dm = safe_div(d->efc_D[adr[0]], mu * mu * (1.0 + mu * mu)), nmt = N - mu * T, force = -dm * nmt * mu;
+        if (r == adr[0]) { d->efc_force[r] = force; cost += 0.5 * dm * nmt * nmt; }
+        else d->efc_force[r] = -safe_div(force, T) * ufr;
+        st = ST_CONE;
+      }
     }
     d->efc_state[r] = st;
   }
@@ -1525,6 +1625,39 @@ static void o_update_gradient(const OModel* m, const OOpt* o, OData* d, OSolver*
         for (int j = 0; j <= i; j++) s->H[i * nv + j] += D * J[i] * J[j];
       }
     }
+    if (s->elliptic) { /* solver.py:2592-2730 update_gradient_JTCJ_dense: cone Hessian of contacts in the middle zone */
+      for (int k = 0; k < d->wcon_n[0]; k++) {
+        int conid = d->wcon[k], adr[6];
+        int dim = s->glob->contact_dim[conid];
+        if (dim == 1 || !(s->glob->contact_dist[conid] - s->glob->contact_includemargin[conid] < 0.0)) continue;
+        if (!(s->glob->contact_type[conid] & 1)) continue;
+        if (!elliptic_rows(s, conid, adr) || adr[0] >= s->nefc || d->efc_state[adr[0]] != ST_CONE) continue;
+        const real* fri = s->glob->contact_friction + 5 * conid;
+        real mu = fri[0] * s->impratio_invsqrt, mu2 = mu * mu, dm = safe_div(d->efc_D[adr[0]], mu2 * (1.0 + mu2));
+        if (dm == 0.0) continue;
+        real n = s->Jaref[adr[0]] * mu, u[6] = {n, 0, 0, 0, 0, 0}, tt = 0, C[6][6];
+        for (int j = 1; j < dim; j++) { u[j] = s->Jaref[adr[j]] * fri[j - 1]; tt += u[j] * u[j]; }
+        real t = fmax(tt <= 0.0 ? 0.0 : sqrt(tt), MJ_MINVAL), ttt = fmax(t * t * t, MJ_MINVAL);
+        for (int a = 0; a < dim; a++) {
+          for (int b = 0; b < dim; b++) {
+            real h;
+            if (a == 0 && b == 0) h = 1.0;
+            else if (a == 0) h = -safe_div(mu, t) * u[b];
+            else if (b == 0) h = -safe_div(mu, t) * u[a];
+            else { h = mu * safe_div(n, ttt) * u[a] * u[b]; if (a == b) h += mu2 - mu * safe_div(n, t); }
+            C[a][b] = h * dm * (a == 0 ? mu : fri[a - 1]) * (b == 0 ? mu : fri[b - 1]);
+          }
+        }
+        for (int i = 0; i < nv; i++) {
+          for (int j = 0; j <= i; j++) {
+            real h = 0;
+            for (int a = 0; a < dim; a++)
+              for (int b = 0; b < dim; b++) h += C[a][b] * d->efc_J[(size_t)adr[a] * np + i] * d->efc_J[(size_t)adr[b] * np + j];
+            s->H[i * nv + j] += h;
+          }
+        }
+      }
+    }
     chol_factor(s->L, nv, s->H, nv, nv);
     chol_solve(s->Mgrad, s->L, nv, s->grad, nv);
   }
@@ -1541,6 +1674,7 @@ static void o_solve(const OModel* m, const OOpt* o, OData* d, const OData* glob)
   memset(&s, 0, sizeof(s));
   s.nefc = d->nefc[0] < njmax ? d->nefc[0] : njmax;
   s.ne = d->ne[0]; s.nf = d->nf[0];
+  s.glob = glob; s.nmp = m->nmaxpyramid; s.elliptic = o->cone == 1; s.impratio_invsqrt = o->impratio_invsqrt;
   real* ws = (real*)calloc((size_t)(2 * njmax + 8 * nv + 2 * nv * nv + 16), sizeof(real));
   s.Jaref = ws; s.jv = s.Jaref + njmax; s.grad = s.jv + njmax; s.Mgrad = s.grad + nv; s.search = s.Mgrad + nv;
   s.mv = s.search + nv; s.prev_grad = s.mv + nv; s.prev_Mgrad = s.prev_grad + nv; s.H = s.prev_Mgrad + nv; s.L = s.H + nv * nv;
@@ -1767,6 +1901,11 @@ int mjo_run_stages(const int* msizes, const int* const* mint, const double* cons
 
 /* helpers exported for the known-answer tests (reference math_test.py / collision_primitive_core_test.py) */
 void mjo_make_frame(const double* a, double* frame) { make_frame(frame, a); }
+/* test hook: solver.py:263 _eval_elliptic -> (cost, gradient, curvature) */
+void mjo_eval_elliptic(double mu, const double* quad, const double* q1, const double* q2, double alpha, double* out) {
+  pt3 r = eval_elliptic(mu, quad, q1, q2, alpha);
+  out[0] = r.c; out[1] = r.g; out[2] = r.h;
+}
 void mjo_quat_integrate(double* q, const double* v, double dt) { quat_integrate(q, v, dt); }
 void mjo_closest_segment_point(const double* a, const double* b, const double* pt, double* out) { closest_segment_point(out, a, b, pt); }
 void mjo_mul_m(int nv, int nv_pad, const double* qM, const double* vec, double* res) {

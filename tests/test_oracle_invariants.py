@@ -8,6 +8,7 @@ import numpy as np
 import pytest
 
 import mujoco_warp_b200 as mjw
+from mujoco_warp_b200 import constants as C
 from oracle import oracle as O
 from tests import helpers as H
 
@@ -242,3 +243,77 @@ def test_sphere_box_and_capsule_box_distances_match_sampled_geometry():
           assert dist >= dd.min() - 0.07 - 1e-9  # no point of the segment is closer than the closest one
           assert first is not None
   assert nsphere > 100 and ncap > 100 and nsecond > 20
+
+
+# ---- elliptic friction cones (constraint.py:1940, solver.py:263, :1886, :2592) ---------------------------------------
+def test_elliptic_line_cost_derivatives_are_consistent():
+  """_eval_elliptic returns (cost, d cost / d alpha, d2 cost / d alpha2): checked by central differences in every zone."""
+  import ctypes
+
+  lib = O.load()
+  lib.mjo_eval_elliptic.argtypes = [ctypes.c_double] + [ctypes.POINTER(ctypes.c_double)] * 3 + [ctypes.c_double, ctypes.POINTER(ctypes.c_double)]
+  lib.mjo_eval_elliptic.restype = None
+
+  def ev(mu, quad, q1, q2, alpha):
+    out = (ctypes.c_double * 3)()
+    arr = lambda v: (ctypes.c_double * 3)(*v)  # noqa: E731
+    lib.mjo_eval_elliptic(mu, arr(quad), arr(q1), arr(q2), alpha, out)
+    return np.array(out[:])
+
+  rng = np.random.default_rng(0)
+  zones = set()
+  for _ in range(300):
+    mu, D0, D1, D2 = rng.uniform(0.3, 1.5), *rng.uniform(50, 500, 3)
+    fr = np.array([mu, rng.uniform(0.3, 1.5)])
+    ja, jv = rng.normal(0, 1, 3), rng.normal(0, 1, 3)
+    D = np.array([D0, D1, D2])
+    quad = [np.sum(0.5 * ja * ja * D), np.sum(jv * D * ja), np.sum(0.5 * jv * jv * D)]
+    u, v = ja[1:] * fr, jv[1:] * fr
+    q1, q2 = [ja[0] * mu, jv[0] * mu, u @ u], [u @ v, v @ v, D0 / (mu * mu * (1 + mu * mu))]
+    alpha, h = rng.uniform(-0.5, 0.5), 1e-6
+    c0, cp, cm = ev(mu, quad, q1, q2, alpha), ev(mu, quad, q1, q2, alpha + h), ev(mu, quad, q1, q2, alpha - h)
+    N, T = q1[0] + alpha * q1[1], np.sqrt(q1[2] + alpha * (2 * q2[0] + alpha * q2[1]))
+    zone = "top" if N >= mu * T else ("bottom" if mu * N + T <= 0 else "middle")
+    if min(abs(N - mu * T), abs(mu * N + T)) < 1e-3:
+      continue  # finite differences straddle a zone boundary
+    zones.add(zone)
+    assert abs((cp[0] - cm[0]) / (2 * h) - c0[1]) < 1e-5 * (1 + abs(c0[1])), zone
+    assert abs((cp[1] - cm[1]) / (2 * h) - c0[2]) < 1e-4 * (1 + abs(c0[2])), zone
+    if zone == "top":
+      assert not c0.any()
+  assert zones == {"top", "bottom", "middle"}
+
+
+def test_elliptic_solution_lies_in_the_friction_cone(humanoid):
+  """Converged forces of every elliptic contact satisfy f_n >= 0 and sum_j (f_j / mu_j)^2 <= f_n^2, rows per contact are
+  condim (not 2 (condim - 1)), and the stationarity residual M a - qfrc_smooth - J^T f vanishes."""
+  qpos, qvel, ctrl = H.make_states(humanoid, 48, seed=1)
+  qpos[:, 2] -= 0.12
+  om, d = H.oracle_data(humanoid, qpos, qvel, ctrl, 24, 64)
+  O.run(om, d, "forward", opt={"cone": int(C.ConeType.ELLIPTIC)}, nthread=4)
+  _, dp = H.oracle_data(humanoid, qpos, qvel, ctrl, 24, 64)
+  O.run(om, dp, "forward", nthread=4)
+  states = set()
+  for cid in range(int(d.nacon[0])):
+    w, adr, dim = int(d.contact_worldid[cid]), d.contact_efc_address[cid], int(d.contact_dim[cid])
+    if adr[0] < 0:
+      continue
+    assert (np.diff(adr[:dim]) == 1).all() and (adr[dim:] == -1).all()
+    if dim == 1:
+      assert int(d.efc_type[w][adr[0]]) == int(C.ConstraintType.CONTACT_FRICTIONLESS)
+      continue
+    assert (d.efc_type[w][adr[:dim]] == int(C.ConstraintType.CONTACT_ELLIPTIC)).all()
+    f, fri = d.efc_force[w], d.contact_friction[cid]
+    fn, ft = f[adr[0]], np.sqrt(sum((f[adr[j]] / fri[j - 1]) ** 2 for j in range(1, dim)))
+    states.add(int(d.efc_state[w][adr[0]]))
+    assert fn >= -1e-9 and ft <= fn * (1 + 1e-6) + 1e-9
+  assert states == {0, 1, 4}  # satisfied, quadratic (sticking), cone (sliding)
+  nv = humanoid.nv
+  for w in range(48):
+    n = int(d.nefc[w])
+    J = d.efc_J[w].reshape(64, -1)[:n, :nv]
+    res = d.efc_Ma[w] - d.qfrc_smooth[w] - J.T @ d.efc_force[w][:n]
+    assert np.abs(res).max() < 1e-3 * (1 + np.abs(d.qfrc_smooth[w]).max())
+  # the pyramid is a linearisation of the same cone: accelerations stay close
+  assert np.abs(d.qacc - dp.qacc).max() < 0.2 * np.abs(dp.qacc).max()
+  assert int(d.solver_niter.max()) < 30
