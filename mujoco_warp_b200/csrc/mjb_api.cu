@@ -52,7 +52,7 @@ struct MjbData {
   struct GroupCfg {  // launch configuration of one stage-group kernel, resolved on first use
     int ready, wpb, grid, in_smem, scratch_floats;
     size_t smem;
-  } cfg[G_COUNT + COLF_COUNT];  // [G_COUNT + v]: collision variant v > 0
+  } cfg[G_COUNT + COLF_COUNT + 2];  // [G_COUNT + v]: collision variant v > 0; last two: elliptic make_constraint / solve
 };
 
 // ---- field-table introspection --------------------------------------------------------------
@@ -265,17 +265,18 @@ static GroupKernel group_kernel_of(int g, bool in_smem, int variant) {
         case 3: return group_kernel<G_COL, 3>(in_smem);
         default: return group_kernel<G_COL, 0>(in_smem);
       }
-    case G_CON: return group_kernel<G_CON>(in_smem);
+    case G_CON: return variant ? group_kernel<G_CON, 1>(in_smem) : group_kernel<G_CON>(in_smem);
     case G_VEL: return group_kernel<G_VEL>(in_smem);
-    case G_SOL: return group_kernel<G_SOL>(in_smem);
+    case G_SOL: return variant ? group_kernel<G_SOL, 1>(in_smem) : group_kernel<G_SOL>(in_smem);
     default: return group_kernel<G_EUL>(in_smem);
   }
 }
 
 static int launch_group(int g, const MjbModel* m, MjbData* d, KParams& K, uint32_t stages, cudaStream_t stream) {
   // collision: the kernel variant follows the model's pair types and the broadphase option of THIS call
-  const int variant = g == G_COL ? (m->col_feat | (K.o.broadphase != 0 ? COLF_SAP : 0)) : 0;
-  MjbData::GroupCfg& c = d->cfg[variant ? G_COUNT + variant : g];
+  // and make_constraint / solve are compiled once per cone type
+  const int variant = g == G_COL ? (m->col_feat | (K.o.broadphase != 0 ? COLF_SAP : 0)) : ((g == G_CON || g == G_SOL) && K.o.cone == 1) ? 1 : 0;
+  MjbData::GroupCfg& c = d->cfg[!variant ? g : g == G_COL ? G_COUNT + variant : G_COUNT + COLF_COUNT + (g == G_CON ? 0 : 1)];
   if (!c.ready) {
     int wpb = warps_per_block(g == G_SOL ? group_threads(G_SOL) / 32 : 8);
     if (32 * wpb > group_threads(g)) wpb = group_threads(g) / 32;
@@ -325,7 +326,7 @@ static int launch_group(int g, const MjbModel* m, MjbData* d, KParams& K, uint32
 extern "C" int mjb_run_stages(const MjbModel* m, MjbData* d, const MjbOption* opt, uint32_t stages, void* cuda_stream) {
   if (!m || !d || !opt) return fail(-1, "null handle");
   cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
-  if (opt->cone != 0) return fail(-4, "elliptic cones are not implemented");
+  if (opt->cone != 0 && opt->cone != 1) return fail(-4, "unknown cone type");
   if (opt->solver != SOLVER_NEWTON && opt->solver != SOLVER_CG) return fail(-4, "unsupported solver");
   if ((stages & MJB_STAGE_IMPLICIT) && (stages & MJB_STAGE_EULER)) return fail(-4, "euler and implicit stages are exclusive");
   KParams K;

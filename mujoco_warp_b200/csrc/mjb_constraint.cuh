@@ -101,6 +101,8 @@ __device__ __forceinline__ int emit_simple_rows(const KParams& K, int w, int lan
   return nefc + __popc(mask);
 }
 
+// ELL: elliptic friction cones (constraint.py:1940 _contact_elliptic) instead of pyramids (:1669).
+template <bool ELL>
 __device__ __forceinline__ void s_make_constraint(const KParams& K, const unsigned char* mb, int w, int lane) {
   const int nv = K.ms.nv, np = K.ms.nv_pad, njmax = K.dsz.njmax;
   int nefc = 0, ne = 0, nf = 0, nl = 0;
@@ -206,15 +208,17 @@ __device__ __forceinline__ void s_make_constraint(const KParams& K, const unsign
           includemargin = K.d.contact_includemargin[cid];
           pos = K.d.contact_dist[cid] - includemargin;
           if ((K.d.contact_type[cid] & 1) && pos < 0.f) {
-            nrow = condim == 1 ? 1 : 2 * (condim - 1);
-            const int b1 = MI(geom_bodyid)[K.d.contact_geom[2 * cid]], b2 = MI(geom_bodyid)[K.d.contact_geom[2 * cid + 1]];
-            float invweight = MR(body_invweight0)[2 * b1] + MR(body_invweight0)[2 * b2];
-            if (condim > 1) {
-              const float fri0 = K.d.contact_friction[5 * cid];
-              invweight = invweight + fri0 * fri0 * invweight;
-              invweight = invweight * 2.0f * fri0 * fri0 * imp2;
+            nrow = condim == 1 ? 1 : (ELL ? condim : 2 * (condim - 1));
+            if (!ELL) {
+              const int b1 = MI(geom_bodyid)[K.d.contact_geom[2 * cid]], b2 = MI(geom_bodyid)[K.d.contact_geom[2 * cid + 1]];
+              float invweight = MR(body_invweight0)[2 * b1] + MR(body_invweight0)[2 * b2];
+              if (condim > 1) {
+                const float fri0 = K.d.contact_friction[5 * cid];
+                invweight = invweight + fri0 * fri0 * invweight;
+                invweight = invweight * 2.0f * fri0 * fri0 * imp2;
+              }
+              ep = efc_params(K, pos, invweight, K.d.contact_solref + 2 * cid, K.d.contact_solimp + 5 * cid);
             }
-            ep = efc_params(K, pos, invweight, K.d.contact_solref + 2 * cid, K.d.contact_solimp + 5 * cid);
           }
         }
         const int base = nefc + warp_excl_scan(nrow, lane);
@@ -266,7 +270,10 @@ __device__ __forceinline__ void s_make_constraint(const KParams& K, const unsign
               for (int dimid = 0; dimid < cnrow; dimid++) {
                 const int r = row0 + dimid;
                 float Jv = proj[0];
-                if (cdim > 1) {
+                if (ELL) {  // row dimid is the frame axis itself: normal, tangents, then the rotational rows
+#pragma unroll
+                  for (int a = 1; a < 6; a++) Jv = (dimid == a) ? proj[a] : Jv;
+                } else if (cdim > 1) {
                   const int dimid2 = dimid / 2 + 1;
                   float Ji = proj[1];
 #pragma unroll
@@ -282,7 +289,30 @@ __device__ __forceinline__ void s_make_constraint(const KParams& K, const unsign
 #pragma unroll
           for (int a = 0; a < 6; a++)
             if (a < cdim) S[a] = warp_sum(S[a]);
-          if (lane < cnrow && row0 + lane < njmax) {
+          if (ELL && lane < cnrow && row0 + lane < njmax) {  // constraint.py:2146-2206: per-row impedance parameters
+            float vel = S[0];
+#pragma unroll
+            for (int a = 1; a < 6; a++) vel = (lane == a) ? S[a] : vel;
+            float invweight = MR(body_invweight0)[2 * wb1] + MR(body_invweight0)[2 * wb2];  // after the weld mapping (:2049)
+            const float* ref = K.d.contact_solref + 2 * ccid;
+            if (lane > 0) {
+              const float* srf = K.d.contact_solreffriction + 2 * ccid;
+              if (srf[0] != 0.f || srf[1] != 0.f) ref = srf;
+              invweight *= imp2;
+              if (lane > 1) invweight *= fri[0] * fri[0] / (fri[lane - 1] * fri[lane - 1]);
+            }
+            const EfcParams p = efc_params(K, cpos_, invweight, ref, K.d.contact_solimp + 5 * ccid);
+            const float pos_aref = lane == 0 ? cpos_ : 0.f;
+            EfcRow e;
+            e.D = p.D;
+            e.vel = vel;
+            e.aref = -p.ki * pos_aref - p.b * vel;
+            e.pos = pos_aref + cmargin;
+            e.margin = cmargin;
+            e.frictionloss = 0.f;
+            store_row(K, w, row0 + lane, e, cdim == 1 ? CT_CONTACT_FRICTIONLESS : CT_CONTACT_ELLIPTIC, ccid);
+          }
+          if (!ELL && lane < cnrow && row0 + lane < njmax) {
             float vel = S[0];
             if (cdim > 1) {
               const int dimid2 = lane / 2 + 1;

@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group
     } else if constexpr (G == G_COL) {
       if (K.o.run_collision_detection) s_collision<V>(K, mb, w, lane, reinterpret_cast<int*>(scr));
     } else if constexpr (G == G_CON) {
-      s_make_constraint(K, mb, w, lane);
+      s_make_constraint<(V & 1) != 0>(K, mb, w, lane);
     } else if constexpr (G == G_VEL) {
       if (st & MJB_STAGE_ZERO_SENSOR) {
         if (lane < 2) DW(energy)[lane] = 0.f;
@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group
       if (st & MJB_STAGE_FWD_ACTUATION) s_fwd_actuation(K, mb, w, lane);
       if (st & (MJB_STAGE_FWD_ACCELERATION | MJB_STAGE_FWD_ACC_FACTOR)) s_fwd_acceleration(K, mb, w, lane, scr, (st & MJB_STAGE_FWD_ACC_FACTOR) != 0);
     } else if constexpr (G == G_SOL) {
-      s_solve(K, mb, w, lane, scr);
+      s_solve<(V & 1) != 0>(K, mb, w, lane, scr);
     } else {
       s_integrate(K, mb, w, lane, scr, (st & MJB_STAGE_IMPLICIT) != 0);
     }

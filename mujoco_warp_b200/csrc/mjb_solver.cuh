@@ -99,6 +99,106 @@ __device__ __noinline__ void mat_vec(const float* __restrict__ A, int n4, int nr
 }
 __device__ __noinline__ float warp_sum_ol(float v) { return warp_sum(v); }  // out-of-line copy
 
+// ---- elliptic friction cones (template flag ELL; compiled only into the elliptic variant of the kernel) ---------
+// Rows of one contact are contiguous here (make_constraint emits them so): row r0 = normal, r0 + j = friction
+// direction j.  `EllRow` describes the contact a row belongs to.
+struct EllRow {
+  int r0, dim;      // primary row, condim; dim = 0: not a (complete) elliptic contact row
+  const float* fri;  // contact.friction[conid]
+  float mu;          // friction[0] * impratio_invsqrt
+};
+__device__ __forceinline__ EllRow ell_row(const KParams& K, int w, int r, int nefc) {
+  EllRow e{0, 0, nullptr, 0.f};
+  if (DW(efc_type)[r] != CT_CONTACT_ELLIPTIC) return e;
+  const int conid = DW(efc_id)[r];
+  const int r0 = K.d.contact_efc_address[conid * K.ms.nmaxpyramid], dim = K.d.contact_dim[conid];
+  if (r0 < 0 || r0 + dim > nefc) return e;  // rows cut off by njmax: the contact is skipped (solver.py:1897-1908)
+  e.r0 = r0;
+  e.dim = dim;
+  e.fri = K.d.contact_friction + 5 * conid;
+  e.mu = e.fri[0] * K.o.impratio_invsqrt;
+  return e;
+}
+// solver.py:263-319 _eval_elliptic with the sums of :986-1050 folded in: cost, slope, curvature along the search
+// direction of the contact whose primary row is e.r0.
+__device__ __forceinline__ Pt3 ell_eval(const SolverScr& s, const EllRow& e, float alpha) {
+  const float D0 = s.D[e.r0], ja0 = s.Jaref[e.r0], jv0 = s.jv[e.r0], mu = e.mu;
+  float q0 = 0.5f * ja0 * ja0 * D0, q1 = jv0 * D0 * ja0, q2 = 0.5f * jv0 * jv0 * D0;
+  float uu = 0.f, uv = 0.f, vv = 0.f;
+  for (int j = 1; j < e.dim; j++) {
+    const float ja = s.Jaref[e.r0 + j], jv = s.jv[e.r0 + j], dj = s.D[e.r0 + j], f = e.fri[j - 1];
+    q0 += 0.5f * ja * dj * ja;
+    q1 += jv * dj * ja;
+    q2 += 0.5f * jv * dj * jv;
+    const float uj = ja * f, vj = jv * f;
+    uu += uj * uj;
+    uv += uj * vj;
+    vv += vj * vj;
+  }
+  const float N = ja0 * mu + alpha * jv0 * mu, Tsqr = uu + alpha * (2.0f * uv + alpha * vv);
+  const Pt3 zero{0.f, 0.f, 0.f};
+  if (Tsqr <= 0.f) return N < 0.f ? eval_pt_quad(q0, q1, q2, alpha) : zero;
+  const float T = sqrtf(Tsqr);
+  if (N >= mu * T) return zero;
+  if (mu * N + T <= 0.f) return eval_pt_quad(q0, q1, q2, alpha);
+  const float dm = D0 / (mu * mu * (1.0f + mu * mu));
+  const float N1 = jv0 * mu, T1 = (uv + alpha * vv) / T, T2 = vv / T - (uv + alpha * vv) * T1 / (T * T);
+  const float e0 = N - mu * T, e1 = N1 - mu * T1;
+  return Pt3{0.5f * dm * e0 * e0, dm * e0 * e1, dm * (e1 * e1 + e0 * (-mu * T2))};
+}
+// one row's contribution to the line cost at alpha, any row type
+template <bool ELL>
+__device__ __forceinline__ Pt3 row_eval(const KParams& K, int w, const SolverScr& s, int r, int nefc, int ne, int nf, float fl, float alpha) {
+  if (ELL && r >= ne + nf && DW(efc_type)[r] == CT_CONTACT_ELLIPTIC) {
+    const EllRow e = ell_row(K, w, r, nefc);
+    return (e.dim && e.r0 == r) ? ell_eval(s, e, alpha) : Pt3{0.f, 0.f, 0.f};  // only the primary row contributes (:625-628)
+  }
+  return efc_eval_pt(r, alpha, ne, nf, s.D[r], fl, s.Jaref[r], s.jv[r]);
+}
+
+// Cone Hessian (solver.py:2592 update_gradient_JTCJ_dense) added to L (the copy of H about to be factored), for
+// every contact of the world in the middle zone.  With w_a = s_a J_a (s_0 = mu, s_j = friction_j), u_j = Jaref_j
+// friction_j, n = Jaref_0 mu, t = |u|, the reference's condim x condim matrix is
+//   dm [ p p^T + c1 q q^T + c2 sum_j w_j w_j^T ],  q = sum_j u_j w_j,  p = w_0 - (mu / t) q,
+//   c1 = (mu / t^2) (n / t - mu),  c2 = mu (mu - n / t),
+// i.e. rank-one terms; p and q are staged in s.mv / s.x (both free between the constraint update and the solve).
+__device__ __forceinline__ void cone_hessian(const KParams& K, int w, int lane, const SolverScr& s, int nefc) {
+  const int nv = K.ms.nv, np = K.ms.nv_pad, ld = s.ld, ncon = DW(wcon_n)[0];
+  const float* J = DW(efc_J);
+  for (int k = 0; k < ncon; k++) {
+    const int conid = DW(wcon)[k];
+    const int dim = K.d.contact_dim[conid], r0 = K.d.contact_efc_address[conid * K.ms.nmaxpyramid];
+    if (uniform_b(dim == 1 || r0 < 0 || r0 + dim > nefc)) continue;
+    if (uniform_b(DW(efc_state)[r0] != ST_CONE)) continue;
+    const float* fri = K.d.contact_friction + 5 * conid;
+    const float mu = fri[0] * K.o.impratio_invsqrt, mu2 = mu * mu, dm = safe_div(s.D[r0], mu2 * (1.0f + mu2));
+    if (uniform_b(dm == 0.f)) continue;
+    const float n = s.Jaref[r0] * mu;
+    float tt = 0.f;
+    for (int j = 1; j < dim; j++) {
+      const float uj = s.Jaref[r0 + j] * fri[j - 1];
+      tt += uj * uj;
+    }
+    const float t = fmaxf(tt <= 0.f ? 0.f : sqrtf(tt), MJ_MINVAL), ttt = fmaxf(t * t * t, MJ_MINVAL);
+    const float mu_t = safe_div(mu, t), c1 = mu * safe_div(n, ttt) - mu_t * mu_t, c2 = mu2 - mu * safe_div(n, t);
+    for (int i = lane; i < nv; i += 32) {
+      float q = 0.f;
+      for (int j = 1; j < dim; j++) q += s.Jaref[r0 + j] * fri[j - 1] * fri[j - 1] * J[(size_t)(r0 + j) * np + i];
+      s.x[i] = q;
+      s.mv[i] = mu * J[(size_t)r0 * np + i] - mu_t * q;
+    }
+    __syncwarp();
+    for (int e = lane; e < nv * nv; e += 32) {
+      const int i = e / nv, j = e - i * nv;
+      if (j > i) continue;
+      float h = s.mv[i] * s.mv[j] + c1 * s.x[i] * s.x[j];
+      for (int a = 1; a < dim; a++) h += c2 * fri[a - 1] * fri[a - 1] * J[(size_t)(r0 + a) * np + i] * J[(size_t)(r0 + a) * np + j];
+      s.L[i * ld + j] += dm * h;
+    }
+    __syncwarp();
+  }
+}
+
 // H(lower) += sum_r coef[r] * J[r]^T J[r], register tiles of 4 rows x 8 columns per lane over
 // 32x32 blocks (solver.py:2368 JTDAJ and :2055 incremental update in one routine).
 __device__ __forceinline__ void h_accumulate(const KParams& K, int w, int lane, const SolverScr& s, int nefc) {
@@ -186,11 +286,12 @@ __device__ __forceinline__ void h_accumulate(const KParams& K, int w, int lane, 
 }
 
 // solver.py:2154-2219 _update_constraint.  Returns the cost; sets force/state (global), coef.
+template <bool ELL>
 __device__ __forceinline__ void update_constraint(const KParams& K, int w, int lane, const SolverScr& s, int nefc, int ne, int nf, bool first,
-                                                  float& cost, float& gauss, bool& any_change) {
+                                                  float& cost, float& gauss, bool& any_change, bool& any_cone) {
   const int nv = K.ms.nv, np = K.ms.nv_pad;
   float c = 0.f;
-  bool changed = false;
+  bool changed = false, cone = false;
   int* state = DW(efc_state);
   MJB_ROLL
   for (int r = lane; r < nefc; r += 32) {
@@ -204,10 +305,32 @@ __device__ __forceinline__ void update_constraint(const KParams& K, int w, int l
       if (ja <= -rf) { f = fl; st = ST_LINEARNEG; c += -fl * (0.5f * rf + ja); }
       else if (ja >= rf) { f = -fl; st = ST_LINEARPOS; c += -fl * (0.5f * rf - ja); }
       else { f = -D * ja; st = ST_QUADRATIC; c += 0.5f * D * ja * ja; }
-    } else {
+    } else if (!(ELL && DW(efc_type)[r] == CT_CONTACT_ELLIPTIC)) {
       if (ja >= 0.f) { f = 0.f; st = ST_SATISFIED; }
       else { f = -D * ja; st = ST_QUADRATIC; c += 0.5f * D * ja * ja; }
+    } else {  // elliptic friction cone contact, solver.py:1886-1943
+      const EllRow e = ell_row(K, w, r, nefc);
+      if (!e.dim) { f = 0.f; st = ST_SATISFIED; }
+      else {
+        const float mu = e.mu, N = s.Jaref[e.r0] * mu;
+        float TT = 0.f, ufr = 0.f;
+        for (int j = 1; j < e.dim; j++) {
+          const float uj = s.Jaref[e.r0 + j] * e.fri[j - 1];
+          TT += uj * uj;
+          if (e.r0 + j == r) ufr = uj * e.fri[j - 1];
+        }
+        const float T = TT <= 0.f ? 0.f : sqrtf(TT);
+        if (N >= mu * T || (T <= 0.f && N >= 0.f)) { f = 0.f; st = ST_SATISFIED; }
+        else if (mu * N + T <= 0.f || (T <= 0.f && N < 0.f)) { f = -D * ja; st = ST_QUADRATIC; c += 0.5f * D * ja * ja; }
+        else {
+          const float dm = safe_div(s.D[e.r0], mu * mu * (1.0f + mu * mu)), nmt = N - mu * T, force = -dm * nmt * mu;
+          if (r == e.r0) { f = force; c += 0.5f * dm * nmt * nmt; }
+          else f = -safe_div(force, T) * ufr;
+          st = ST_CONE;
+        }
+      }
     }
+    if (ELL) cone |= st == ST_CONE;
     const bool newq = st == ST_QUADRATIC;
     const bool oldq = first ? false : (state[r] == ST_QUADRATIC);
     s.coef[r] = newq == oldq ? 0.f : (newq ? D : -D);
@@ -217,6 +340,7 @@ __device__ __forceinline__ void update_constraint(const KParams& K, int w, int l
     DW(efc_force)[r] = f;
   }
   any_change = __any_sync(FULL, changed);
+  any_cone = ELL ? __any_sync(FULL, cone) : false;
   __syncwarp();
   // qfrc_constraint = J^T force (solver.py:1988): lane = dof; four rows per iteration so that four
   // independent (coalesced) global loads are in flight; groups of rows without force are skipped
@@ -249,17 +373,19 @@ __device__ __forceinline__ void update_constraint(const KParams& K, int w, int l
   __syncwarp();
 }
 
+template <bool ELL>
 __device__ __forceinline__ Pt3 ls_rows(const KParams& K, int w, int lane, const SolverScr& s, int nefc, int ne, int nf, float alpha) {
   Pt3 t = Pt3{0.f, 0.f, 0.f};
   MJB_ROLL
   for (int r = lane; r < nefc; r += 32) {
     const float fl = (r >= ne && r < ne + nf) ? DW(efc_frictionloss)[r] : 0.f;
-    t = t + efc_eval_pt(r, alpha, ne, nf, s.D[r], fl, s.Jaref[r], s.jv[r]);
+    t = t + row_eval<ELL>(K, w, s, r, nefc, ne, nf, fl, alpha);
   }
   return t;
 }
 
 // solver.py:887-1341 linesearch_iterative (pyramidal); updates qacc, Ma, Jaref in scratch.
+template <bool ELL>
 __device__ __forceinline__ void linesearch(const KParams& K, int w, int lane, const SolverScr& s, int nefc, int ne, int nf, float gauss,
                                            float search_dot) {
   const int nv = K.ms.nv, np = K.ms.nv_pad, n4 = np >> 2;
@@ -285,9 +411,9 @@ __device__ __forceinline__ void linesearch(const KParams& K, int w, int lane, co
   q1 = warp_sum(q1);
   q2 = warp_sum(q2);
   const float q0 = gauss;
-  Pt3 p0 = warp_sum(ls_rows(K, w, lane, s, nefc, ne, nf, 0.f)) + Pt3{q0, q1, 2.0f * q2};
+  Pt3 p0 = warp_sum(ls_rows<ELL>(K, w, lane, s, nefc, ne, nf, 0.f)) + Pt3{q0, q1, 2.0f * q2};
   const float lo_alpha_in = -safe_div(p0.g, p0.h);
-  Pt3 lo_in = warp_sum(ls_rows(K, w, lane, s, nefc, ne, nf, lo_alpha_in)) + eval_pt_quad(q0, q1, q2, lo_alpha_in);
+  Pt3 lo_in = warp_sum(ls_rows<ELL>(K, w, lane, s, nefc, ne, nf, lo_alpha_in)) + eval_pt_quad(q0, q1, q2, lo_alpha_in);
   float alpha;
   if (uniform_b(fabsf(lo_in.g) < gtol && lo_in.c < p0.c)) {
     alpha = lo_alpha_in;
@@ -305,6 +431,12 @@ __device__ __forceinline__ void linesearch(const KParams& K, int w, int lane, co
       MJB_ROLL
       for (int r = lane; r < nefc; r += 32) {
         const float fl = (r >= ne && r < ne + nf) ? DW(efc_frictionloss)[r] : 0.f;
+        if (ELL) {
+          a = a + row_eval<true>(K, w, s, r, nefc, ne, nf, fl, lo_next_alpha);
+          b = b + row_eval<true>(K, w, s, r, nefc, ne, nf, fl, hi_next_alpha);
+          c = c + row_eval<true>(K, w, s, r, nefc, ne, nf, fl, mid_alpha);
+          continue;
+        }
         const float D = s.D[r], ja = s.Jaref[r], jv = s.jv[r];
         a = a + efc_eval_pt(r, lo_next_alpha, ne, nf, D, fl, ja, jv);
         b = b + efc_eval_pt(r, hi_next_alpha, ne, nf, D, fl, ja, jv);
@@ -345,7 +477,8 @@ __device__ __forceinline__ void linesearch(const KParams& K, int w, int lane, co
 
 // Newton: factor H, Mgrad = H^-1 grad.  CG: Mgrad = M^-1 grad with the factor held in s.L.
 // The factor is only recomputed when H changed since the last factorisation.
-__device__ __forceinline__ void solve_direction(const KParams& K, int lane, const SolverScr& s, bool refactor) {
+template <bool ELL>
+__device__ __forceinline__ void solve_direction(const KParams& K, int w, int lane, const SolverScr& s, bool refactor, bool cones, int nefc) {
   const int nv = K.ms.nv, ld = s.ld;
   if (refactor) {
     const float4* h4 = reinterpret_cast<const float4*>(s.H);
@@ -353,6 +486,7 @@ __device__ __forceinline__ void solve_direction(const KParams& K, int lane, cons
     MJB_ROLL
     for (int i = lane; i < (nv * ld) >> 2; i += 32) l4[i] = h4[i];
     __syncwarp();
+    if (ELL && cones) cone_hessian(K, w, lane, s, nefc);
     warp_cholesky<!MJB_SOL_COMPACT>(s.L, ld, nv, s.rd, lane);
   }
   MJB_ROLL
@@ -365,6 +499,7 @@ __device__ __forceinline__ void solve_direction(const KParams& K, int lane, cons
 struct SolveState {
   int it, niter, nefc, ne, nf;
   float cost, gauss, prev_cost, search_dot;
+  bool had_cone;  // the current factor contains cone terms (elliptic variant)
 };
 
 // init_context part 1 (solver.py:3257): loads the world into shared memory.  Returns false when there is
@@ -383,6 +518,7 @@ __device__ __forceinline__ bool solve_begin(const KParams& K, int w, int lane, c
   st.nf = uniform_i(DW(nf)[0]);
   st.it = 0;
   st.niter = 0;
+  st.had_cone = false;
   st.cost = st.gauss = st.prev_cost = st.search_dot = 0.f;
   const bool newton = K.o.solver == SOLVER_NEWTON;
   const float* src = (K.o.disableflags & DSBL_WARMSTART) ? DW(qacc_smooth) : DW(qacc_warmstart);
@@ -416,6 +552,7 @@ __device__ __forceinline__ bool solve_begin(const KParams& K, int w, int lane, c
 // One pass.  Pass 0 is the rest of init_context (constraint update, gradient, first search direction);
 // passes 1.. are solver.py:3188 _solver_iteration.  One body keeps a single copy of every routine in
 // the instruction stream.  Returns true when the world is finished.
+template <bool ELL>
 __device__ __forceinline__ bool solve_pass(const KParams& K, int w, int lane, const SolverScr& s, SolveState& st) {
   const int nv = K.ms.nv, np = K.ms.nv_pad;
   const bool newton = K.o.solver == SOLVER_NEWTON;
@@ -423,7 +560,7 @@ __device__ __forceinline__ bool solve_pass(const KParams& K, int w, int lane, co
   float* prev_grad = s.H;  // CG only (H is unused by CG)
   float* prev_Mgrad = s.H + np;
   if (!init) {
-    linesearch(K, w, lane, s, st.nefc, st.ne, st.nf, st.gauss, st.search_dot);
+    linesearch<ELL>(K, w, lane, s, st.nefc, st.ne, st.nf, st.gauss, st.search_dot);
     if (!newton) {
       MJB_ROLL
       for (int i = lane; i < nv; i += 32) { prev_grad[i] = s.grad[i]; prev_Mgrad[i] = s.x[i]; }
@@ -431,8 +568,8 @@ __device__ __forceinline__ bool solve_pass(const KParams& K, int w, int lane, co
     }
     st.prev_cost = st.cost;
   }
-  bool any_change;
-  update_constraint(K, w, lane, s, st.nefc, st.ne, st.nf, init, st.cost, st.gauss, any_change);
+  bool any_change, any_cone;
+  update_constraint<ELL>(K, w, lane, s, st.nefc, st.ne, st.nf, init, st.cost, st.gauss, any_change, any_cone);
   // solver.py:3177 solve_done.  The reference evaluates it after the next search direction has been
   // computed; the direction of a finished world is never used, so it is tested first and the Hessian
   // update, factorisation and solve of the last pass are skipped (outputs are identical).
@@ -449,7 +586,9 @@ __device__ __forceinline__ bool solve_pass(const KParams& K, int w, int lane, co
     return true;
   }
   if (newton && any_change) h_accumulate(K, w, lane, s, st.nefc);
-  solve_direction(K, lane, s, newton && (any_change || init));
+  // the cone part of the Hessian depends on Jaref: refactor whenever a cone is or was in the factor (solver.py:3205-3209)
+  solve_direction<ELL>(K, w, lane, s, newton && (any_change || init || (ELL && (any_cone || st.had_cone))), any_cone, st.nefc);
+  if (ELL) st.had_cone = any_cone;
   float beta = 0.f;
   if (!newton && !init) {  // Polak-Ribiere, solver.py:3081
     float num = 0.f, den = 0.f;
@@ -486,11 +625,12 @@ __device__ __forceinline__ void solve_finish(const KParams& K, int w, int lane, 
 }
 
 // one world, start to finish (used when the solver is fused with other stages)
+template <bool ELL>
 __device__ __forceinline__ void s_solve(const KParams& K, const unsigned char* mb, int w, int lane, float* scr) {
   const SolverScr s = solver_scr(scr, K.ms.nv, K.ms.nv_pad, K.dsz.njmax_pad);
   SolveState st;
   if (!solve_begin(K, w, lane, s, st)) return;
-  while (!solve_pass(K, w, lane, s, st)) {
+  while (!solve_pass<ELL>(K, w, lane, s, st)) {
   }
   solve_finish(K, w, lane, s, st);
 }
@@ -512,7 +652,7 @@ __device__ __forceinline__ void s_solve_cta(const KParams& K, int lane, int warp
       if (!running) w += stride;
     }
     if (!__syncthreads_or(running ? 1 : 0)) break;
-    if (running && solve_pass(K, w, lane, s, st)) {
+    if (running && solve_pass<false>(K, w, lane, s, st)) {
       solve_finish(K, w, lane, s, st);
       running = false;
       w += stride;

@@ -654,5 +654,3 @@ def override_model(m: types.Model, overrides: dict):
       cur.copy_(torch.as_tensor(val, dtype=cur.dtype).reshape(cur.shape))
     else:
       setattr(obj, attr, type(cur)(val) if cur is not None else val)
-  if m.opt.cone == C.ConeType.ELLIPTIC:
-    warnings.warn("elliptic cones are not implemented; results will be pyramidal")

@@ -382,3 +382,29 @@ def test_sphere_box_and_capsule_box_contacts():
     worst = max(worst, err)
   assert nbox > 600
   assert worst < 1e-4, worst
+
+
+@pytest.mark.parametrize("solver", [C.SolverType.NEWTON, C.SolverType.CG])
+def test_elliptic_cones(humanoid, solver):
+  """constraint.py:1940 _contact_elliptic, solver.py:263 / :1886 / :2592: condim rows per contact in contact-frame
+  axes, cone states and forces, the cone term of the Newton Hessian."""
+  qpos, qvel, ctrl = H.make_states(humanoid, 64, seed=31)
+  qpos[:, 2] -= 0.1  # feet into the floor: sticking and sliding contacts
+  opt = {"cone": int(C.ConeType.ELLIPTIC), "solver": int(solver), "iterations": 100}
+  _, od, m, d = run_both(humanoid, qpos, qvel, ctrl, 24, 64, opt=opt)
+  assert int(d.status.max()) == 0
+  assert_forward_close(od, d, tol_solver=5e-2)
+  np.testing.assert_array_equal(H.dev_np(d, "efc_type"), od.efc_type)
+  np.testing.assert_array_equal(H.dev_np(d, "efc_id")[od.efc_type == 7], od.efc_id[od.efc_type == 7])
+  for f in H.EFC_FIELDS:
+    assert H.max_err(H.dev_np(d, f), getattr(od, f)) < 2e-3, f
+  state_dev, state_ref = H.dev_np(d, "efc_state"), od.efc_state
+  rows = np.arange(state_ref.shape[1])[None, :] < od.nefc[:, None]
+  assert (state_ref[rows] == 4).sum() > 20  # cones in the middle zone are exercised
+  assert (state_dev[rows] != state_ref[rows]).mean() < 0.02  # zone boundaries are float-sensitive
+  fscale = 1.0 + np.abs(od.efc_force).max(axis=1, keepdims=True)
+  assert (np.abs(H.dev_np(d, "efc_force") - od.efc_force) / fscale)[rows].max() < 2e-2
+  # and a few steps stay together
+  _, od2, _, d2 = run_both(humanoid, qpos, qvel, ctrl, 24, 64, stage="step", opt=opt, nstep=5)
+  assert H.max_err(H.dev_np(d2, "qpos"), od2.qpos) < 1e-4
+  assert H.max_err(H.dev_np(d2, "qvel"), od2.qvel) < 2e-2

@@ -81,7 +81,6 @@ def test_make_data_rejects_bad_sizes(humanoid, kwargs, msg):
 
 
 UNSUPPORTED = [
-  ('<option cone="elliptic"/>', "elliptic"),
   ('<option jacobian="sparse"/>', "sparse"),
   ('<option solver="PGS"/>', "PGS"),
   ('<option integrator="implicit"/>', "IMPLICIT"),
