@@ -221,6 +221,7 @@ def host_model(mjm) -> SimpleNamespace:
     (C.GeomType.CAPSULE, C.GeomType.CAPSULE),
     (C.GeomType.SPHERE, C.GeomType.BOX),
     (C.GeomType.CAPSULE, C.GeomType.BOX),
+    (C.GeomType.BOX, C.GeomType.BOX),
   }
   gtype = ints["geom_type"]
   for ga, gb in ints["nxn_pair"]:

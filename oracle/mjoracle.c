@@ -536,6 +536,262 @@ static void closest_segment_point(real* r, const real* a, const real* b, const r
   for (int i = 0; i < 3; i++) r[i] = a[i] + t * ab[i];
 }
 
+/* helpers of box_box: 3x3 row-major products and the six face re-orientations (collision_primitive_core.py:616-644:
+ * a signed permutation that turns face `f` of a box (0..2 = +x,+y,+z, 3..5 = -x,-y,-z) into the +z face) */
+static void m3_mul(real* out, const real* a, const real* b) {
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++) out[3 * i + j] = a[3 * i] * b[j] + a[3 * i + 1] * b[3 + j] + a[3 * i + 2] * b[6 + j];
+}
+static void m3_tr(real* out, const real* a) {
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++) out[3 * i + j] = a[3 * j + i];
+}
+static void face_rotation(real* m, int f) {
+  static const signed char tbl[6][3][2] = {/* per row: (column, sign) */
+      {{2, -1}, {1, 1}, {0, 1}}, {{0, 1}, {2, -1}, {1, 1}}, {{0, 1}, {1, 1}, {2, 1}},
+      {{2, 1}, {1, 1}, {0, -1}}, {{0, 1}, {2, 1}, {1, -1}}, {{0, -1}, {1, 1}, {2, -1}}};
+  memset(m, 0, 9 * sizeof(real));
+  for (int i = 0; i < 3; i++) m[3 * i + tbl[f][i][0]] = tbl[f][i][1];
+}
+
+/* collision_primitive_core.py:648-1099 box_box (after MuJoCo C's box-box): separating-axis search over the 6 face
+ * normals and the 9 edge cross products, then clipping in the frame where the reference face is the +z face:
+ * face case -- the incident box's nearest face (or edge) is clipped against the reference rectangle;
+ * edge case -- the nearest face of box 2 is projected along the separating axis and clipped likewise.
+ * Returns the number of contacts (<= 8); all share one normal. */
+static int c_box_box(const real* p1, const real* R1, const real* s1, const real* p2, const real* R2, const real* s2, real margin,
+                     real* dist, real* pos /* [8][3] */, real* nrm) {
+  real R1t[9], R2t[9], rot21[9], rot12[9], a21[9], a12[9], pos21[3], pos12[3], d21[3], d12[3], plen1[3], plen2[3];
+  m3_tr(R1t, R1); m3_tr(R2t, R2);
+  for (int i = 0; i < 3; i++) { d21[i] = p2[i] - p1[i]; d12[i] = p1[i] - p2[i]; }
+  mat_vec(pos21, R1t, d21); mat_vec(pos12, R2t, d12);
+  m3_mul(rot21, R1t, R2); m3_tr(rot12, rot21);
+  for (int i = 0; i < 9; i++) { a21[i] = fabs(rot21[i]); a12[i] = fabs(rot12[i]); }
+  mat_vec(plen2, a21, s2); mat_vec(plen1, a12, s1);
+  real separation = margin + 3.0 * (s1[0] + s2[0]) + 3.0 * (s1[1] + s2[1]) + 3.0 * (s1[2] + s2[2]);
+  int code = -1;
+  for (int i = 0; i < 3; i++) { /* face normals of both boxes */
+    real c1 = -fabs(pos21[i]) + s1[i] + plen2[i], c2 = -fabs(pos12[i]) + s2[i] + plen1[i];
+    if (c1 < -margin || c2 < -margin) return 0;
+    if (c1 < separation) { separation = c1; code = i + 3 * (pos21[i] < 0); }
+    if (c2 < separation) { separation = c2; code = i + 3 * (pos12[i] < 0) + 6; }
+  }
+  real clnorm[3] = {0, 0, 0};
+  int inv = 0, cle1 = 0, cle2 = 0;
+  for (int i = 0; i < 3; i++) { /* edge i of box 1 x edge j of box 2 */
+    for (int j = 0; j < 3; j++) {
+      const real* a = rot12 + 3 * j; /* axis j of box 2 in the frame of box 1 */
+      real cr[3];
+      if (i == 0) { cr[0] = 0; cr[1] = -a[2]; cr[2] = a[1]; }
+      else if (i == 1) { cr[0] = a[2]; cr[1] = 0; cr[2] = -a[0]; }
+      else { cr[0] = -a[1]; cr[1] = a[0]; cr[2] = 0; }
+      real len = norm3(cr);
+      if (len < MJ_MINVAL) continue;
+      for (int k = 0; k < 3; k++) cr[k] /= len;
+      real bd = dot3(pos21, cr), c3 = 0;
+      for (int k = 0; k < 3; k++) {
+        if (k != i) c3 += s1[k] * fabs(cr[k]);
+        if (k != j) c3 += s2[k] * a21[3 * i + 3 - k - j] / len;
+      }
+      c3 -= fabs(bd);
+      if (c3 < -margin) return 0;
+      if (c3 < separation * (1.0 - 1e-12)) {
+        separation = c3;
+        cle1 = cle2 = 0;
+        for (int k = 0; k < 3; k++) {
+          if (k != i && ((cr[k] > 0) ^ (bd < 0))) cle1 += 1 << k;
+          if (k != j && ((rot21[3 * i + 3 - k - j] > 0) ^ (bd < 0) ^ ((k - j + 3) % 3 == 1))) cle2 += 1 << k;
+        }
+        code = 12 + 3 * i + j;
+        memcpy(clnorm, cr, sizeof(cr));
+        inv = bd < 0;
+      }
+    }
+  }
+  if (code == -1) return 0;
+  real pts[8][3], depth[8], rw[9], pw[3], rotmore[9], rmt[9], hz;
+  int n = 0;
+  memset(pts, 0, sizeof(pts));
+  if (code < 12) { /* a face of box `bi` is the reference face; the other box is incident */
+    int bi = code / 6;
+    face_rotation(rotmore, code % 6);
+    real r[9], rt[9], p[3], ss[3], tmp[3];
+    m3_mul(r, rotmore, bi ? rot12 : rot21);
+    mat_vec(p, rotmore, bi ? pos12 : pos21);
+    mat_vec(tmp, rotmore, bi ? s2 : s1);
+    for (int i = 0; i < 3; i++) ss[i] = fabs(tmp[i]);
+    const real* s = bi ? s1 : s2;
+    m3_tr(rt, r);
+    real lx = ss[0], ly = ss[1];
+    hz = ss[2];
+    p[2] -= hz;
+    int clcorner = 0, dirs = 0;
+    for (int i = 0; i < 3; i++) if (r[6 + i] < 0) clcorner += 1 << i;
+    real lp[3] = {p[0], p[1], p[2]}, cn[2][3] = {{0, 0, 0}, {0, 0, 0}};
+    for (int i = 0; i < 3; i++)
+      for (int k = 0; k < 3; k++) lp[k] += rt[3 * i + k] * s[i] * ((clcorner & (1 << i)) ? 1.0 : -1.0);
+    for (int i = 0; i < 3; i++) {
+      if (fabs(r[6 + i]) < 0.5) {
+        for (int k = 0; k < 3; k++) cn[dirs ? 1 : 0][k] = rt[3 * i + k] * s[i] * ((clcorner & (1 << i)) ? -2.0 : 2.0);
+        dirs++;
+      }
+    }
+    for (int i = 0; i < dirs * dirs; i++) { /* incident edges against the sides of the reference rectangle */
+      for (int q = 0; q < 2; q++) {
+        real lav[3], lbv[3];
+        for (int k = 0; k < 3; k++) {
+          lav[k] = lp[k] + (i < 2 ? 0.0 : (i == 2 ? cn[0][k] : cn[1][k]));
+          lbv[k] = (i == 0 || i == 3) ? cn[0][k] : cn[1][k];
+        }
+        if (fabs(lbv[q]) > MJ_MINVAL) {
+          real br = 1.0 / lbv[q];
+          for (int j = -1; j <= 1; j += 2) {
+            real l = ss[q] * j, c1 = (l - lav[q]) * br;
+            if (c1 < 0 || c1 > 1) continue;
+            real c2 = lav[1 - q] + lbv[1 - q] * c1;
+            if (fabs(c2) > ss[1 - q]) continue;
+            if (n < 8) { for (int k = 0; k < 3; k++) pts[n][k] = lav[k] + c1 * lbv[k]; n++; }
+          }
+        }
+      }
+    }
+    if (dirs == 2) { /* corners of the reference rectangle inside the incident face */
+      real ax = cn[0][0], bx = cn[1][0], ay = cn[0][1], by = cn[1][1], C = safe_div(1.0, ax * by - bx * ay);
+      for (int i = 0; i < 4; i++) {
+        real llx = (i / 2) ? lx : -lx, lly = (i % 2) ? ly : -ly, x = llx - lp[0], y = lly - lp[1];
+        real u = (x * by - y * bx) * C, v = (y * ax - x * ay) * C;
+        if (u > 0 && v > 0 && u < 1 && v < 1 && n < 8) {
+          pts[n][0] = llx; pts[n][1] = lly; pts[n][2] = lp[2] + u * cn[0][2] + v * cn[1][2];
+          n++;
+        }
+      }
+    }
+    for (int i = 0; i < (1 << dirs); i++) { /* incident corners inside the reference rectangle */
+      real t[3];
+      for (int k = 0; k < 3; k++) t[k] = lp[k] + (real)(i & 1) * cn[0][k] + (real)((i & 2) != 0) * cn[1][k];
+      if (t[0] > -lx && t[0] < lx && t[1] > -ly && t[1] < ly && n < 8) { memcpy(pts[n], t, sizeof(t)); n++; }
+    }
+    int m = n;
+    n = 0;
+    for (int i = 0; i < m; i++) {
+      if (pts[i][2] > margin) continue;
+      if (i != n) memcpy(pts[n], pts[i], sizeof(pts[i]));
+      depth[n] = pts[n][2];
+      pts[n][2] *= 0.5;
+      n++;
+    }
+    m3_tr(rmt, rotmore);
+    m3_mul(rw, bi ? R2 : R1, rmt);
+    memcpy(pw, bi ? p2 : p1, sizeof(pw));
+    for (int k = 0; k < 3; k++) nrm[k] = (bi ? -1.0 : 1.0) * rw[3 * k + 2];
+  } else { /* edge e1 of box 1 against edge e2 of box 2 */
+    int e1 = (code - 12) / 3, e2 = (code - 12) % 3;
+    int ax1 = 1 - (e2 & 1), ax2 = 2 - (e2 & 2), pax1 = 1 - (e1 & 1), pax2 = 2 - (e1 & 2);
+    if (a21[3 * e1 + ax1] < a21[3 * e1 + ax2]) { int t = ax1; ax1 = ax2; ax2 = t; }
+    if (a12[3 * e2 + pax1] < a12[3 * e2 + pax2]) { int t = pax1; pax1 = pax2; pax2 = t; }
+    (void)pax1;
+    face_rotation(rotmore, (cle1 & (1 << pax2)) ? pax2 : pax2 + 3);
+    m3_tr(rmt, rotmore);
+    real p[3], rn[3], r[9], rt[9], s[3], tmp[3];
+    mat_vec(p, rotmore, pos21); mat_vec(rn, rotmore, clnorm); m3_mul(r, rotmore, rot21); m3_tr(rt, r);
+    mat_vec(tmp, rmt, s1);
+    for (int i = 0; i < 3; i++) s[i] = fabs(tmp[i]);
+    real lx = s[0], ly = s[1];
+    hz = s[2];
+    p[2] -= hz;
+    real sg1 = (cle2 & (1 << ax1)) ? 1.0 : -1.0, sg2 = (cle2 & (1 << ax2)) ? 1.0 : -1.0, pu[4][3];
+    for (int k = 0; k < 3; k++) { /* the face of box 2 nearest to box 1: two edges parallel to e2 */
+      real e = rt[3 * e2 + k] * s2[e2];
+      real q0 = p[k] + rt[3 * ax1 + k] * s2[ax1] * sg1 + rt[3 * ax2 + k] * s2[ax2] * sg2;
+      real q2 = p[k] - rt[3 * ax1 + k] * s2[ax1] * sg1 + rt[3 * ax2 + k] * s2[ax2] * sg2;
+      pts[0][k] = q0 + e; pts[1][k] = q0 - e; pts[2][k] = q2 + e; pts[3][k] = q2 - e;
+    }
+    real alp[3], acn1[3], acn2[3];
+    for (int k = 0; k < 3; k++) { alp[k] = pts[0][k]; acn1[k] = pts[1][k] - pts[0][k]; acn2[k] = pts[2][k] - pts[0][k]; }
+    if (fabs(rn[2]) < MJ_MINVAL) return 0;
+    real sgn = inv ? -1.0 : 1.0, innorm = sgn / rn[2];
+    for (int i = 0; i < 4; i++) { /* project along the separating axis onto the reference plane */
+      memcpy(pu[i], pts[i], sizeof(pts[i]));
+      real sc = pts[i][2] * sgn * innorm;
+      for (int k = 0; k < 3; k++) pts[i][k] -= rn[k] * sc;
+    }
+    real plp[3], pcn1[3], pcn2[3];
+    for (int k = 0; k < 3; k++) { plp[k] = pts[0][k]; pcn1[k] = pts[1][k] - pts[0][k]; pcn2[k] = pts[2][k] - pts[0][k]; }
+    for (int i = 0; i < 4; i++) {
+      for (int q = 0; q < 2; q++) {
+        real la = plp[q] + (i < 2 ? 0.0 : (i == 2 ? pcn1[q] : pcn2[q])), lb = (i == 0 || i == 3) ? pcn1[q] : pcn2[q];
+        real lc = plp[1 - q] + (i < 2 ? 0.0 : (i == 2 ? pcn1[1 - q] : pcn2[1 - q])), ld = (i == 0 || i == 3) ? pcn1[1 - q] : pcn2[1 - q];
+        real lua[3], lub[3];
+        for (int k = 0; k < 3; k++) {
+          lua[k] = alp[k] + (i < 2 ? 0.0 : (i == 2 ? acn1[k] : acn2[k]));
+          lub[k] = (i == 0 || i == 3) ? acn1[k] : acn2[k];
+        }
+        if (fabs(lb) > MJ_MINVAL) {
+          real br = 1.0 / lb;
+          for (int j = -1; j <= 1; j += 2) {
+            if (n == 8) break;
+            real l = s[q] * j, c1 = (l - la) * br;
+            if (c1 < 0 || c1 > 1) continue;
+            real c2 = lc + ld * c1;
+            if (fabs(c2) > s[1 - q]) continue;
+            if ((lua[2] + lub[2] * c1) * innorm > margin) continue;
+            for (int k = 0; k < 3; k++) pts[n][k] = lua[k] * 0.5 + c1 * lub[k] * 0.5;
+            pts[n][q] += 0.5 * l;
+            pts[n][1 - q] += 0.5 * c2;
+            depth[n] = pts[n][2] * innorm * 2.0;
+            n++;
+          }
+        }
+      }
+    }
+    int nl = n;
+    real ax = pcn1[0], bx = pcn2[0], ay = pcn1[1], by = pcn2[1], C = safe_div(1.0, ax * by - bx * ay);
+    for (int i = 0; i < 4; i++) { /* corners of the reference rectangle under the projected face */
+      if (n == 8) break;
+      real llx = (i / 2) ? lx : -lx, lly = (i % 2) ? ly : -ly, x = llx - plp[0], y = lly - plp[1];
+      real u = (x * by - y * bx) * C, v = (y * ax - x * ay) * C;
+      if (nl == 0) { if ((u < 0 || u > 1) && (v < 0 || v > 1)) continue; }
+      else if (u < 0 || v < 0 || u > 1 || v > 1) continue;
+      u = clampr(u, 0.0, 1.0); v = clampr(v, 0.0, 1.0);
+      real w = 1.0 - u - v, vt[3], tc1 = 0, corner[3] = {llx, lly, 0.0};
+      for (int k = 0; k < 3; k++) { vt[k] = pu[0][k] * w + pu[1][k] * u + pu[2][k] * v; tc1 += (corner[k] - vt[k]) * (corner[k] - vt[k]); }
+      if (vt[2] > 0 && tc1 > margin * margin) continue;
+      for (int k = 0; k < 3; k++) pts[n][k] = 0.5 * (corner[k] + vt[k]);
+      depth[n] = sqrt(tc1) * (vt[2] < 0 ? -1.0 : 1.0);
+      n++;
+    }
+    int nf = n;
+    for (int i = 0; i < 4; i++) { /* corners of the face of box 2 over the reference rectangle */
+      if (n >= 8) break;
+      real x = pu[i][0], y = pu[i][1];
+      if (nl == 0 && nf != 0) { if ((x < -lx || x > lx) && (y < -ly || y > ly)) continue; }
+      else if (x < -lx || x > lx || y < -ly || y > ly) continue;
+      real c1 = 0, tp[3] = {pu[i][0], pu[i][1], 0.0};
+      for (int j = 0; j < 2; j++) {
+        if (pu[i][j] < -s[j]) { c1 += (pu[i][j] + s[j]) * (pu[i][j] + s[j]); tp[j] = -s[j] * 0.5; }
+        else if (pu[i][j] > s[j]) { c1 += (pu[i][j] - s[j]) * (pu[i][j] - s[j]); tp[j] = s[j] * 0.5; }
+      }
+      c1 += pu[i][2] * innorm * pu[i][2] * innorm;
+      if (pu[i][2] > 0 && c1 > margin * margin) continue;
+      for (int k = 0; k < 3; k++) pts[n][k] = (tp[k] + pu[i][k]) * 0.5;
+      depth[n] = sqrt(c1) * (pu[i][2] < 0 ? -1.0 : 1.0);
+      n++;
+    }
+    m3_mul(rw, R1, rmt);
+    memcpy(pw, p1, sizeof(pw));
+    real t[3];
+    mat_vec(t, rw, rn);
+    for (int k = 0; k < 3; k++) nrm[k] = sgn * t[k];
+  }
+  for (int i = 0; i < n; i++) {
+    pts[i][2] += hz;
+    mat_vec(pos + 3 * i, rw, pts[i]);
+    for (int k = 0; k < 3; k++) pos[3 * i + k] += pw[k];
+    dist[i] = depth[i];
+  }
+  return n;
+}
+
 /* collision_primitive_core.py:1103-1154.  Sphere (geom 1) against box (geom 2): the centre is taken into the box
  * frame and clamped to the box; outside, the contact lies between the clamped point and the deepest sphere point;
  * inside, the nearest face decides (faces scanned in the order -x,+x,-y,+y,-z,+z, strict improvement). */
@@ -742,6 +998,16 @@ static int narrowphase_pair(const OModel* m, const OData* d, int g1, int g2, rea
     make_frame(out[0].frame, n);
     out[0].id = 0;
     return 1;
+  }
+  if (t1 == GEOM_BOX && t2 == GEOM_BOX) { /* collision_primitive.py:1202 */
+    real dist[8], pos[24], n[3];
+    int nc = c_box_box(p1, r1, s1, p2, r2, s2, margin, dist, pos, n);
+    for (int k = 0; k < 8; k++) {
+      out[k].id = k;
+      if (k < nc) { out[k].dist = dist[k]; memcpy(out[k].pos, pos + 3 * k, 3 * sizeof(real)); make_frame(out[k].frame, n); }
+      else { out[k].dist = MJ_MAXVAL; memset(out[k].pos, 0, 3 * sizeof(real)); memset(out[k].frame, 0, 9 * sizeof(real)); }
+    }
+    return 8;
   }
   if (t1 == GEOM_CAPSULE && t2 == GEOM_BOX) { /* collision_primitive.py:1117 */
     real dist[2], pos[6], n[6];
@@ -1901,6 +2167,31 @@ int mjo_run_stages(const int* msizes, const int* const* mint, const double* cons
 
 /* helpers exported for the known-answer tests (reference math_test.py / collision_primitive_core_test.py) */
 void mjo_make_frame(const double* a, double* frame) { make_frame(frame, a); }
+/* test hook: narrowphase candidates of one geom pair given directly (tests/golden/primitive_core.npz).  geom 1 and 2
+ * are ordered by type as in collision_driver.py:351.  Returns the candidate count; out arrays hold 8 entries. */
+int mjo_narrowphase_pair(int t1, int t2, const double* p1, const double* r1, const double* s1, const double* p2, const double* r2,
+                         const double* s2, double margin, double* dist, double* pos, double* frame) {
+  OModel m;
+  OData d;
+  memset(&m, 0, sizeof(m));
+  memset(&d, 0, sizeof(d));
+  int gtype[2] = {t1, t2};
+  real size[6], xpos[6], xmat[18];
+  memcpy(size, s1, 3 * sizeof(real)); memcpy(size + 3, s2, 3 * sizeof(real));
+  memcpy(xpos, p1, 3 * sizeof(real)); memcpy(xpos + 3, p2, 3 * sizeof(real));
+  memcpy(xmat, r1, 9 * sizeof(real)); memcpy(xmat + 9, r2, 9 * sizeof(real));
+  m.geom_type = gtype; m.geom_size = size;
+  d.geom_xpos = xpos; d.geom_xmat = xmat;
+  OContactGeom out[8];
+  memset(out, 0, sizeof(out));
+  int n = narrowphase_pair(&m, &d, 0, 1, margin, out);
+  for (int k = 0; k < n && k < 8; k++) {
+    dist[k] = out[k].dist;
+    memcpy(pos + 3 * k, out[k].pos, 3 * sizeof(real));
+    memcpy(frame + 9 * k, out[k].frame, 9 * sizeof(real));
+  }
+  return n;
+}
 /* test hook: solver.py:263 _eval_elliptic -> (cost, gradient, curvature) */
 void mjo_eval_elliptic(double mu, const double* quad, const double* q1, const double* q2, double alpha, double* out) {
   pt3 r = eval_elliptic(mu, quad, q1, q2, alpha);
