@@ -151,7 +151,7 @@ extern "C" int mjb_model_create(const int* sizes, int nsizes, const void* blob, 
     for (int p = 0; p < m->ms.nxn; p++) {
       const int ta = gtype[pair[2 * p]], tb = gtype[pair[2 * p + 1]];
       const int t1 = ta < tb ? ta : tb, t2 = ta < tb ? tb : ta;
-      if (t2 == GEOM_BOX && t1 != GEOM_PLANE) m->col_feat |= COLF_BOX;
+      if (t2 == GEOM_BOX && t1 != GEOM_PLANE) m->col_feat |= COLF_BOX;  // sphere-box, capsule-box, box-box
     }
   }
   *out = m;

@@ -237,11 +237,271 @@ __device__ __forceinline__ int capsule_box_points(V3 cp, V3 caxis, float hl, V3 
   return second > -3.f ? 2 : 1;
 }
 
+// ---- box-box (collision_primitive_core.py:648-1099), float restatement of the routine in oracle/mjoracle.c -------
+__device__ __forceinline__ void bb_mat_vec(float* r, const float* m, const float* v) {
+#pragma unroll
+  for (int i = 0; i < 3; i++) r[i] = m[3 * i] * v[0] + m[3 * i + 1] * v[1] + m[3 * i + 2] * v[2];
+}
+__device__ __forceinline__ float bb_dot3(const float* a, const float* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+__device__ __forceinline__ float bb_norm3(const float* a) { return sqrtf(bb_dot3(a, a)); }
+__device__ __forceinline__ void m3_mul(float* out, const float* a, const float* b) {
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) out[3 * i + j] = a[3 * i] * b[j] + a[3 * i + 1] * b[3 + j] + a[3 * i + 2] * b[6 + j];
+}
+__device__ __forceinline__ void m3_tr(float* out, const float* a) {
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) out[3 * i + j] = a[3 * j + i];
+}
+// signed permutation that turns face f (0..2 = +x,+y,+z, 3..5 = -x,-y,-z) into the +z face (:616-644)
+__device__ __forceinline__ void face_rotation(float* m, int f) {
+  const int col[6][3] = {{2, 1, 0}, {0, 2, 1}, {0, 1, 2}, {2, 1, 0}, {0, 2, 1}, {0, 1, 2}};
+  const float sgn[6][3] = {{-1.f, 1.f, 1.f}, {1.f, -1.f, 1.f}, {1.f, 1.f, 1.f}, {1.f, 1.f, -1.f}, {1.f, 1.f, -1.f}, {-1.f, 1.f, -1.f}};
+  for (int i = 0; i < 9; i++) m[i] = 0.f;
+  for (int i = 0; i < 3; i++) m[3 * i + col[f][i]] = sgn[f][i];
+}
+__device__ __noinline__ int c_box_box(const float* p1, const float* R1, const float* s1, const float* p2, const float* R2, const float* s2, float margin,
+                                      float* dist, float* pos, float* nrm) {  // pos: [8][3]
+  float R1t[9], R2t[9], rot21[9], rot12[9], a21[9], a12[9], pos21[3], pos12[3], d21[3], d12[3], plen1[3], plen2[3];
+  m3_tr(R1t, R1); m3_tr(R2t, R2);
+  for (int i = 0; i < 3; i++) { d21[i] = p2[i] - p1[i]; d12[i] = p1[i] - p2[i]; }
+  bb_mat_vec(pos21, R1t, d21); bb_mat_vec(pos12, R2t, d12);
+  m3_mul(rot21, R1t, R2); m3_tr(rot12, rot21);
+  for (int i = 0; i < 9; i++) { a21[i] = fabsf(rot21[i]); a12[i] = fabsf(rot12[i]); }
+  bb_mat_vec(plen2, a21, s2); bb_mat_vec(plen1, a12, s1);
+  float separation = margin + 3.0f * (s1[0] + s2[0]) + 3.0f * (s1[1] + s2[1]) + 3.0f * (s1[2] + s2[2]);
+  int code = -1;
+  for (int i = 0; i < 3; i++) { // face normals of both boxes
+    float c1 = -fabsf(pos21[i]) + s1[i] + plen2[i], c2 = -fabsf(pos12[i]) + s2[i] + plen1[i];
+    if (c1 < -margin || c2 < -margin) return 0;
+    if (c1 < separation) { separation = c1; code = i + 3 * (pos21[i] < 0); }
+    if (c2 < separation) { separation = c2; code = i + 3 * (pos12[i] < 0) + 6; }
+  }
+  float clnorm[3] = {0, 0, 0};
+  int inv = 0, cle1 = 0, cle2 = 0;
+  for (int i = 0; i < 3; i++) { // edge i of box 1 x edge j of box 2
+    for (int j = 0; j < 3; j++) {
+      const float* a = rot12 + 3 * j; // axis j of box 2 in the frame of box 1
+      float cr[3];
+      if (i == 0) { cr[0] = 0; cr[1] = -a[2]; cr[2] = a[1]; }
+      else if (i == 1) { cr[0] = a[2]; cr[1] = 0; cr[2] = -a[0]; }
+      else { cr[0] = -a[1]; cr[1] = a[0]; cr[2] = 0; }
+      float len = bb_norm3(cr);
+      if (len < MJ_MINVAL) continue;
+      for (int k = 0; k < 3; k++) cr[k] /= len;
+      float bd = bb_dot3(pos21, cr), c3 = 0;
+      for (int k = 0; k < 3; k++) {
+        if (k != i) c3 += s1[k] * fabsf(cr[k]);
+        if (k != j) c3 += s2[k] * a21[3 * i + 3 - k - j] / len;
+      }
+      c3 -= fabsf(bd);
+      if (c3 < -margin) return 0;
+      if (c3 < separation * (1.0f - 1e-12f)) {
+        separation = c3;
+        cle1 = cle2 = 0;
+        for (int k = 0; k < 3; k++) {
+          if (k != i && ((cr[k] > 0) ^ (bd < 0))) cle1 += 1 << k;
+          if (k != j && ((rot21[3 * i + 3 - k - j] > 0) ^ (bd < 0) ^ ((k - j + 3) % 3 == 1))) cle2 += 1 << k;
+        }
+        code = 12 + 3 * i + j;
+        clnorm[0] = cr[0]; clnorm[1] = cr[1]; clnorm[2] = cr[2];
+        inv = bd < 0;
+      }
+    }
+  }
+  if (code == -1) return 0;
+  float pts[8][3], depth[8], rw[9], pw[3], rotmore[9], rmt[9], hz;
+  int n = 0;
+  for (int i = 0; i < 8; i++) pts[i][0] = pts[i][1] = pts[i][2] = 0.f;
+  if (code < 12) { // a face of box `bi` is the reference face; the other box is incident
+    int bi = code / 6;
+    face_rotation(rotmore, code % 6);
+    float r[9], rt[9], p[3], ss[3], tmp[3];
+    m3_mul(r, rotmore, bi ? rot12 : rot21);
+    bb_mat_vec(p, rotmore, bi ? pos12 : pos21);
+    bb_mat_vec(tmp, rotmore, bi ? s2 : s1);
+    for (int i = 0; i < 3; i++) ss[i] = fabsf(tmp[i]);
+    const float* s = bi ? s1 : s2;
+    m3_tr(rt, r);
+    float lx = ss[0], ly = ss[1];
+    hz = ss[2];
+    p[2] -= hz;
+    int clcorner = 0, dirs = 0;
+    for (int i = 0; i < 3; i++) if (r[6 + i] < 0) clcorner += 1 << i;
+    float lp[3] = {p[0], p[1], p[2]}, cn[2][3] = {{0, 0, 0}, {0, 0, 0}};
+    for (int i = 0; i < 3; i++)
+      for (int k = 0; k < 3; k++) lp[k] += rt[3 * i + k] * s[i] * ((clcorner & (1 << i)) ? 1.0f : -1.0f);
+    for (int i = 0; i < 3; i++) {
+      if (fabsf(r[6 + i]) < 0.5f) {
+        for (int k = 0; k < 3; k++) cn[dirs ? 1 : 0][k] = rt[3 * i + k] * s[i] * ((clcorner & (1 << i)) ? -2.0f : 2.0f);
+        dirs++;
+      }
+    }
+    for (int i = 0; i < dirs * dirs; i++) { // incident edges against the sides of the reference rectangle
+      for (int q = 0; q < 2; q++) {
+        float lav[3], lbv[3];
+        for (int k = 0; k < 3; k++) {
+          lav[k] = lp[k] + (i < 2 ? 0.0f : (i == 2 ? cn[0][k] : cn[1][k]));
+          lbv[k] = (i == 0 || i == 3) ? cn[0][k] : cn[1][k];
+        }
+        if (fabsf(lbv[q]) > MJ_MINVAL) {
+          float br = 1.0f / lbv[q];
+          for (int j = -1; j <= 1; j += 2) {
+            float l = ss[q] * j, c1 = (l - lav[q]) * br;
+            if (c1 < 0 || c1 > 1) continue;
+            float c2 = lav[1 - q] + lbv[1 - q] * c1;
+            if (fabsf(c2) > ss[1 - q]) continue;
+            if (n < 8) { for (int k = 0; k < 3; k++) pts[n][k] = lav[k] + c1 * lbv[k]; n++; }
+          }
+        }
+      }
+    }
+    if (dirs == 2) { // corners of the reference rectangle inside the incident face
+      float ax = cn[0][0], bx = cn[1][0], ay = cn[0][1], by = cn[1][1], C = safe_divf(1.0f, ax * by - bx * ay);
+      for (int i = 0; i < 4; i++) {
+        float llx = (i / 2) ? lx : -lx, lly = (i % 2) ? ly : -ly, x = llx - lp[0], y = lly - lp[1];
+        float u = (x * by - y * bx) * C, v = (y * ax - x * ay) * C;
+        if (u > 0 && v > 0 && u < 1 && v < 1 && n < 8) {
+          pts[n][0] = llx; pts[n][1] = lly; pts[n][2] = lp[2] + u * cn[0][2] + v * cn[1][2];
+          n++;
+        }
+      }
+    }
+    for (int i = 0; i < (1 << dirs); i++) { // incident corners inside the reference rectangle
+      float t[3];
+      for (int k = 0; k < 3; k++) t[k] = lp[k] + (float)(i & 1) * cn[0][k] + (float)((i & 2) != 0) * cn[1][k];
+      if (t[0] > -lx && t[0] < lx && t[1] > -ly && t[1] < ly && n < 8) { pts[n][0] = t[0]; pts[n][1] = t[1]; pts[n][2] = t[2]; n++; }
+    }
+    int m = n;
+    n = 0;
+    for (int i = 0; i < m; i++) {
+      if (pts[i][2] > margin) continue;
+      if (i != n) { pts[n][0] = pts[i][0]; pts[n][1] = pts[i][1]; pts[n][2] = pts[i][2]; }
+      depth[n] = pts[n][2];
+      pts[n][2] *= 0.5f;
+      n++;
+    }
+    m3_tr(rmt, rotmore);
+    m3_mul(rw, bi ? R2 : R1, rmt);
+    { const float* pp = bi ? p2 : p1; pw[0] = pp[0]; pw[1] = pp[1]; pw[2] = pp[2]; }
+    for (int k = 0; k < 3; k++) nrm[k] = (bi ? -1.0f : 1.0f) * rw[3 * k + 2];
+  } else { // edge e1 of box 1 against edge e2 of box 2
+    int e1 = (code - 12) / 3, e2 = (code - 12) % 3;
+    int ax1 = 1 - (e2 & 1), ax2 = 2 - (e2 & 2), pax1 = 1 - (e1 & 1), pax2 = 2 - (e1 & 2);
+    if (a21[3 * e1 + ax1] < a21[3 * e1 + ax2]) { int t = ax1; ax1 = ax2; ax2 = t; }
+    if (a12[3 * e2 + pax1] < a12[3 * e2 + pax2]) { int t = pax1; pax1 = pax2; pax2 = t; }
+    (void)pax1;
+    face_rotation(rotmore, (cle1 & (1 << pax2)) ? pax2 : pax2 + 3);
+    m3_tr(rmt, rotmore);
+    float p[3], rn[3], r[9], rt[9], s[3], tmp[3];
+    bb_mat_vec(p, rotmore, pos21); bb_mat_vec(rn, rotmore, clnorm); m3_mul(r, rotmore, rot21); m3_tr(rt, r);
+    bb_mat_vec(tmp, rmt, s1);
+    for (int i = 0; i < 3; i++) s[i] = fabsf(tmp[i]);
+    float lx = s[0], ly = s[1];
+    hz = s[2];
+    p[2] -= hz;
+    float sg1 = (cle2 & (1 << ax1)) ? 1.0f : -1.0f, sg2 = (cle2 & (1 << ax2)) ? 1.0f : -1.0f, pu[4][3];
+    for (int k = 0; k < 3; k++) { // the face of box 2 nearest to box 1: two edges parallel to e2
+      float e = rt[3 * e2 + k] * s2[e2];
+      float q0 = p[k] + rt[3 * ax1 + k] * s2[ax1] * sg1 + rt[3 * ax2 + k] * s2[ax2] * sg2;
+      float q2 = p[k] - rt[3 * ax1 + k] * s2[ax1] * sg1 + rt[3 * ax2 + k] * s2[ax2] * sg2;
+      pts[0][k] = q0 + e; pts[1][k] = q0 - e; pts[2][k] = q2 + e; pts[3][k] = q2 - e;
+    }
+    float alp[3], acn1[3], acn2[3];
+    for (int k = 0; k < 3; k++) { alp[k] = pts[0][k]; acn1[k] = pts[1][k] - pts[0][k]; acn2[k] = pts[2][k] - pts[0][k]; }
+    if (fabsf(rn[2]) < MJ_MINVAL) return 0;
+    float sgn = inv ? -1.0f : 1.0f, innorm = sgn / rn[2];
+    for (int i = 0; i < 4; i++) { // project along the separating axis onto the reference plane
+      pu[i][0] = pts[i][0]; pu[i][1] = pts[i][1]; pu[i][2] = pts[i][2];
+      float sc = pts[i][2] * sgn * innorm;
+      for (int k = 0; k < 3; k++) pts[i][k] -= rn[k] * sc;
+    }
+    float plp[3], pcn1[3], pcn2[3];
+    for (int k = 0; k < 3; k++) { plp[k] = pts[0][k]; pcn1[k] = pts[1][k] - pts[0][k]; pcn2[k] = pts[2][k] - pts[0][k]; }
+    for (int i = 0; i < 4; i++) {
+      for (int q = 0; q < 2; q++) {
+        float la = plp[q] + (i < 2 ? 0.0f : (i == 2 ? pcn1[q] : pcn2[q])), lb = (i == 0 || i == 3) ? pcn1[q] : pcn2[q];
+        float lc = plp[1 - q] + (i < 2 ? 0.0f : (i == 2 ? pcn1[1 - q] : pcn2[1 - q])), ld = (i == 0 || i == 3) ? pcn1[1 - q] : pcn2[1 - q];
+        float lua[3], lub[3];
+        for (int k = 0; k < 3; k++) {
+          lua[k] = alp[k] + (i < 2 ? 0.0f : (i == 2 ? acn1[k] : acn2[k]));
+          lub[k] = (i == 0 || i == 3) ? acn1[k] : acn2[k];
+        }
+        if (fabsf(lb) > MJ_MINVAL) {
+          float br = 1.0f / lb;
+          for (int j = -1; j <= 1; j += 2) {
+            if (n == 8) break;
+            float l = s[q] * j, c1 = (l - la) * br;
+            if (c1 < 0 || c1 > 1) continue;
+            float c2 = lc + ld * c1;
+            if (fabsf(c2) > s[1 - q]) continue;
+            if ((lua[2] + lub[2] * c1) * innorm > margin) continue;
+            for (int k = 0; k < 3; k++) pts[n][k] = lua[k] * 0.5f + c1 * lub[k] * 0.5f;
+            pts[n][q] += 0.5f * l;
+            pts[n][1 - q] += 0.5f * c2;
+            depth[n] = pts[n][2] * innorm * 2.0f;
+            n++;
+          }
+        }
+      }
+    }
+    int nl = n;
+    float ax = pcn1[0], bx = pcn2[0], ay = pcn1[1], by = pcn2[1], C = safe_divf(1.0f, ax * by - bx * ay);
+    for (int i = 0; i < 4; i++) { // corners of the reference rectangle under the projected face
+      if (n == 8) break;
+      float llx = (i / 2) ? lx : -lx, lly = (i % 2) ? ly : -ly, x = llx - plp[0], y = lly - plp[1];
+      float u = (x * by - y * bx) * C, v = (y * ax - x * ay) * C;
+      if (nl == 0) { if ((u < 0 || u > 1) && (v < 0 || v > 1)) continue; }
+      else if (u < 0 || v < 0 || u > 1 || v > 1) continue;
+      u = clampf(u, 0.0f, 1.0f); v = clampf(v, 0.0f, 1.0f);
+      float w = 1.0f - u - v, vt[3], tc1 = 0, corner[3] = {llx, lly, 0.0f};
+      for (int k = 0; k < 3; k++) { vt[k] = pu[0][k] * w + pu[1][k] * u + pu[2][k] * v; tc1 += (corner[k] - vt[k]) * (corner[k] - vt[k]); }
+      if (vt[2] > 0 && tc1 > margin * margin) continue;
+      for (int k = 0; k < 3; k++) pts[n][k] = 0.5f * (corner[k] + vt[k]);
+      depth[n] = sqrtf(tc1) * (vt[2] < 0 ? -1.0f : 1.0f);
+      n++;
+    }
+    int nf = n;
+    for (int i = 0; i < 4; i++) { // corners of the face of box 2 over the reference rectangle
+      if (n >= 8) break;
+      float x = pu[i][0], y = pu[i][1];
+      if (nl == 0 && nf != 0) { if ((x < -lx || x > lx) && (y < -ly || y > ly)) continue; }
+      else if (x < -lx || x > lx || y < -ly || y > ly) continue;
+      float c1 = 0, tp[3] = {pu[i][0], pu[i][1], 0.0f};
+      for (int j = 0; j < 2; j++) {
+        if (pu[i][j] < -s[j]) { c1 += (pu[i][j] + s[j]) * (pu[i][j] + s[j]); tp[j] = -s[j] * 0.5f; }
+        else if (pu[i][j] > s[j]) { c1 += (pu[i][j] - s[j]) * (pu[i][j] - s[j]); tp[j] = s[j] * 0.5f; }
+      }
+      c1 += pu[i][2] * innorm * pu[i][2] * innorm;
+      if (pu[i][2] > 0 && c1 > margin * margin) continue;
+      for (int k = 0; k < 3; k++) pts[n][k] = (tp[k] + pu[i][k]) * 0.5f;
+      depth[n] = sqrtf(c1) * (pu[i][2] < 0 ? -1.0f : 1.0f);
+      n++;
+    }
+    m3_mul(rw, R1, rmt);
+    pw[0] = p1[0]; pw[1] = p1[1]; pw[2] = p1[2];
+    float t[3];
+    bb_mat_vec(t, rw, rn);
+    for (int k = 0; k < 3; k++) nrm[k] = sgn * t[k];
+  }
+  for (int i = 0; i < n; i++) {
+    pts[i][2] += hz;
+    bb_mat_vec(pos + 3 * i, rw, pts[i]);
+    for (int k = 0; k < 3; k++) pos[3 * i + k] += pw[k];
+    dist[i] = depth[i];
+  }
+  return n;
+}
+
 // Number of candidate contacts of a pair type (collision_primitive.py wrappers).
 __device__ __forceinline__ int pair_ncand(int t1, int t2) {
   if (t1 == GEOM_PLANE) return t2 == GEOM_SPHERE ? 1 : (t2 == GEOM_CAPSULE ? 2 : (t2 == GEOM_BOX ? 8 : 0));
   if (t1 == GEOM_SPHERE) return (t2 == GEOM_SPHERE || t2 == GEOM_CAPSULE || t2 == GEOM_BOX) ? 1 : 0;
   if (t1 == GEOM_CAPSULE) return (t2 == GEOM_CAPSULE || t2 == GEOM_BOX) ? 2 : 0;
+  if (t1 == GEOM_BOX && t2 == GEOM_BOX) return 8;
   return 0;
 }
 
@@ -393,6 +653,9 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
   PairGeom g;
   ContactParams cp;
   const float* r2 = nullptr;
+  float bdist[(FEAT & COLF_BOX) ? 8 : 1], bpos[(FEAT & COLF_BOX) ? 24 : 1], bnrm[3] = {1.f, 0.f, 0.f};  // box-box results
+  int nbb = 0;
+  bool boxbox = false;
   if (has) {
     const int p = queue[lane];
     const int ga = MI(nxn_pair)[2 * p], gb = MI(nxn_pair)[2 * p + 1];
@@ -413,11 +676,18 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
     g.s2 = ld3(MR(geom_size) + 3 * g2);
     contact_params(K, mb, g1, g2, pid0, cp);
     ncand = pair_ncand(g.t1, g.t2);
+    if ((FEAT & COLF_BOX) && g.t1 == GEOM_BOX && g.t2 == GEOM_BOX) {  // all (<= 8) contacts of the pair in one evaluation
+      const float pa[3] = {g.p1.x, g.p1.y, g.p1.z}, pb[3] = {g.p2.x, g.p2.y, g.p2.z};
+      const float sa[3] = {g.s1.x, g.s1.y, g.s1.z}, sb[3] = {g.s2.x, g.s2.y, g.s2.z};
+      nbb = c_box_box(pa, DW(geom_xmat) + 9 * g1, sa, pb, r2, sb, cp.margin, bdist, bpos, bnrm);
+      boxbox = true;
+    }
     for (int k = 0; k < ncand; k++) {  // pass 1: count (write_contact filter, collision_core.py:199-203)
       float dist;
       V3 pos;
       M3 frame;
-      pair_contact<FEAT>(g, r2, cp.margin, k, dist, pos, frame);
+      if ((FEAT & COLF_BOX) && boxbox) dist = k < nbb ? bdist[k] : INFINITY;
+      else pair_contact<FEAT>(g, r2, cp.margin, k, dist, pos, frame);
       const bool active = dist < cp.margin;
       if (!((pid0 == -2 || !active) && pid1 == -1)) nact++;
     }
@@ -435,7 +705,13 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
       float dist;
       V3 pos;
       M3 frame;
-      pair_contact<FEAT>(g, r2, cp.margin, k, dist, pos, frame);
+      if ((FEAT & COLF_BOX) && boxbox) {
+        dist = k < nbb ? bdist[k] : INFINITY;
+        pos = V3{bpos[3 * (k & 7)], bpos[3 * (k & 7) + 1], bpos[3 * (k & 7) + 2]};
+        frame = make_frame(V3{bnrm[0], bnrm[1], bnrm[2]});
+      } else {
+        pair_contact<FEAT>(g, r2, cp.margin, k, dist, pos, frame);
+      }
       const bool active = dist < cp.margin;
       if ((pid0 == -2 || !active) && pid1 == -1) continue;
       const int cid = base + slot;
