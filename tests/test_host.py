@@ -98,10 +98,10 @@ def test_put_model_rejects_unsupported_features(snippet, msg):
 
 def test_put_model_rejects_unimplemented_geom_pairs():
   xml = """<mujoco><worldbody>
-    <body><freejoint/><geom type="box" size=".1 .1 .1"/></body>
-    <body pos="1 0 0"><freejoint/><geom type="box" size=".1 .1 .1"/></body>
+    <body><freejoint/><geom type="cylinder" size=".1 .1"/></body>
+    <body pos="1 0 0"><freejoint/><geom type="cylinder" size=".1 .1"/></body>
   </worldbody></mujoco>"""
-  with pytest.raises(NotImplementedError, match="BOX"):
+  with pytest.raises(NotImplementedError, match="CYLINDER"):
     mjw.put_model(mjw.load_mjcf_string(xml), device="cpu")
 
 
