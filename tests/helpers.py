@@ -89,3 +89,108 @@ def world_contacts_orc(d, w, name):
   n = int(d.wcon_n[w])
   ids = d.wcon[w, :n]
   return getattr(d, name)[ids]
+
+
+# ----------------------------------------------------------------------------------------------
+# canonical orderings: the reference appends contacts / efc rows through atomic counters, so only the
+# SET of rows per world is defined; these helpers sort both sides the same way before comparing
+# ----------------------------------------------------------------------------------------------
+def _get(obj, name):
+  return np.asarray(obj[name] if isinstance(obj, dict) else getattr(obj, name))
+
+
+def canonical_contacts(obj):
+  """Contacts [0, nacon) sorted by (worldid, geom0, geom1, order of appearance); 'rank' maps conid -> sorted position."""
+  n = int(_get(obj, "nacon").reshape(-1)[0])
+  geom = _get(obj, "contact_geom")[:n].reshape(n, 2)
+  wid = _get(obj, "contact_worldid")[:n].reshape(n)
+  order = np.lexsort((np.arange(n), geom[:, 1], geom[:, 0], wid))
+  out = {"rank": np.empty(n, dtype=np.int64), "order": order}
+  out["rank"][order] = np.arange(n)
+  for f in "dist pos frame includemargin friction solref solreffriction solimp dim geom worldid".split():
+    a = _get(obj, "contact_" + f)[:n]
+    out[f] = a.reshape(n, -1)[order] if n else a.reshape(0, int(np.prod(a.shape[1:])) if a.ndim > 1 else 1)
+  return out
+
+
+def canonical_efc(obj, prefix="efc_"):
+  """Active rows of every world, sorted per world by (type, canonical id), concatenated over worlds."""
+  nefc = _get(obj, "nefc").reshape(-1)
+  types, ids = _get(obj, prefix + "type"), _get(obj, prefix + "id")
+  rank = canonical_contacts(obj)["rank"]
+  fields = {}
+  for f in "J pos margin D vel aref frictionloss force state type".split():
+    try:
+      fields[f] = _get(obj, prefix + f)
+    except (KeyError, AttributeError):
+      pass
+  out = {f: [] for f in fields}
+  out["id"] = []
+  for w, n in enumerate(nefc):
+    n = min(int(n), types.shape[1])
+    t = types[w, :n].astype(np.int64)
+    i = ids[w, :n].astype(np.int64)
+    i = np.where(t >= 5, rank[np.clip(i, 0, max(len(rank) - 1, 0))] if len(rank) else i, i)
+    order = np.lexsort((np.arange(n), i, t))
+    for f, a in fields.items():
+      out[f].append(np.asarray(a[w][:n])[order])
+    out["id"].append(i[order])
+  return {f: (np.concatenate(v) if v else np.zeros(0)) for f, v in out.items()}
+
+
+def oracle_rk4_step(om, od, mjm, opt=None):
+  """reference forward.py:458 rungekutta4 composed on the host from the oracle's forward (the C oracle has no RK4 driver)."""
+  import ctypes
+
+  from oracle import oracle as O
+
+  lib = O.load()
+  dt = (opt or {}).get("timestep", om.opt["timestep"])
+
+  def integrate_pos(q0, v, h):
+    out = q0.copy()
+    for w in range(q0.shape[0]):
+      for j in range(mjm.njnt):
+        jt, qa, da = int(mjm.jnt_type[j]), int(mjm.jnt_qposadr[j]), int(mjm.jnt_dofadr[j])
+        if jt in (0, 1):
+          if jt == 0:
+            out[w, qa : qa + 3] = q0[w, qa : qa + 3] + h * v[w, da : da + 3]
+            qa, da = qa + 3, da + 3
+          quat, om3 = q0[w, qa : qa + 4].copy(), v[w, da : da + 3].copy()
+          lib.mjo_quat_integrate(quat.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), om3.ctypes.data_as(ctypes.POINTER(ctypes.c_double)),
+                                 ctypes.c_double(h))  # fmt: skip
+          out[w, qa : qa + 4] = quat
+        else:
+          out[w, qa] = q0[w, qa] + h * v[w, da]
+    return out
+
+  O.run(om, od, "forward", opt=opt)
+  A, B = [0.5, 0.5, 1.0], [1 / 6, 1 / 3, 1 / 3, 1 / 6]
+  q0, v0, t0 = od.qpos.copy(), od.qvel.copy(), od.time.copy()
+  vrk, ark = B[0] * od.qvel, B[0] * od.qacc
+  for i in range(3):
+    od.qpos[:] = integrate_pos(q0, od.qvel, A[i] * dt)
+    od.qvel[:] = v0 + A[i] * dt * od.qacc
+    O.run(om, od, "forward", opt=opt)
+    vrk += B[i + 1] * od.qvel
+    ark += B[i + 1] * od.qacc
+  od.qvel[:] = v0 + dt * ark
+  od.qpos[:] = integrate_pos(q0, vrk, dt)
+  od.time[:] = t0 + dt
+  od.qacc_warmstart[:] = od.qacc  # forward.py:274 copies d.qacc, which holds the LAST stage's acceleration
+  return od
+
+
+def oracle_steps(om, od, mode, nstep, opt=None, nthread=1):
+  """Runs `forward` or `nstep` steps of the oracle under the given option overrides (integrator-aware)."""
+  from oracle import oracle as O
+
+  integ = int((opt or {}).get("integrator", om.opt["integrator"]))
+  for _ in range(nstep):
+    if mode == "forward":
+      O.run(om, od, "forward", opt=opt, nthread=nthread)
+    elif integ == 1:
+      oracle_rk4_step(om, od, om.mjm, opt)
+    else:
+      O.run(om, od, "step_implicitfast" if integ == 3 else "step", opt=opt, nthread=nthread)
+  return od
