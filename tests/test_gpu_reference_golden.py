@@ -5,8 +5,8 @@ The inputs and expected outputs come from `tests/golden/reference_step.npz` (wri
 Nothing here calls the oracle: this is device vs reference directly.
 
 Bars: counts (ne, nf, nl, nefc, nacon) and row / contact identities (efc_type, contact dim / geom) BIT-EXACT;
-float32 device vs float64 reference with |a-b| / (1 + |b|): smooth dynamics 1e-4 (qacc_smooth, qLD 5e-3), contacts 1e-4,
-constraint rows 2e-3, solver outputs and the integrated state 2e-2 (trajectory qpos 1e-4 / qvel 1e-2 per step; the
+float32 device vs float64 reference with |a-b| / (1 + |b|): smooth dynamics 1e-4 (2e-3 after several steps; qacc_smooth, qLD 5e-3),
+contacts 1e-4, constraint rows 2e-3, solver outputs and the integrated state 2e-2 (CG 5e-2) (trajectory qpos 1e-4 / qvel 1e-2 per step; the
 reference's own tests use 5e-4 / 1e-1 against MuJoCo C for the same groups).
 """
 
@@ -24,22 +24,30 @@ from tests.golden import reference_cases as RC
 pytestmark = pytest.mark.gpu
 
 TOL_SMOOTH, TOL_FACTOR, TOL_CONTACT, TOL_EFC, TOL_SOLVER = 1e-4, 5e-3, 1e-4, 2e-3, 2e-2
+TOL_SMOOTH_MULTISTEP = 2e-3  # after several float32 steps the velocity-dependent fields (qfrc_bias, cvel, ...) see the drifted state
+TOL_SOLVER_CG = 5e-2  # CG stops at `tolerance`, not at the optimum: two runs agree to solver tolerance only
+# stopped after 6 CG iterations, far from converged: the iterates depend on rounding-level linesearch ties (it pins the ORACLE's
+# iterates to the reference's in float64); on the device only the solver-independent fields are compared
+UNCONVERGED = ("humanoid_cg_iter6",)
 FACTOR_FIELDS = ("qacc_smooth", "qLD")
 EXACT = ("efc_type", "efc_id", "contact_dim", "contact_geom")
 
 
-def tol_of(f):
+def tol_of(f, name):
+  c = RC.CASES[name]
   if f in EXACT:
     return 1e-12
   if f in RC.SOLVER_FIELDS or f in ("efc_force", "efc_state", "efc_Ma"):
-    return TOL_SOLVER
+    if name in UNCONVERGED:
+      return float("inf")
+    return TOL_SOLVER_CG if name in RC.LOOSE_SOLVER_CASES else TOL_SOLVER
   if f in FACTOR_FIELDS:
     return TOL_FACTOR
   if f.startswith("efc_"):
     return TOL_EFC
   if f.startswith("contact_"):
     return TOL_CONTACT
-  return TOL_SMOOTH
+  return TOL_SMOOTH_MULTISTEP if c.get("nstep", 1) > 1 else TOL_SMOOTH
 
 
 @pytest.mark.parametrize("name", list(RC.CASES))
@@ -67,6 +75,6 @@ def test_device_matches_reference_execution(name):
     with open(os.path.join(out, f"refgolden_{name}.json"), "w") as fh:
       json.dump({k: float(v) for k, v in report.items()}, fh, indent=1)
   # a world whose active set sits on a float32 tie may gain / lose a row: the counts must be exact on this seeded fixture
-  bad = {f: e for f, e in worst.items() if not e < tol_of(f)}
+  bad = {f: e for f, e in worst.items() if not e < tol_of(f, name)}
   assert not bad, (name, bad)
   assert report["traj_qpos"] < 1e-4 * c.get("nstep", 1) and report["traj_qvel"] < TOL_SOLVER, (name, report["traj_qpos"], report["traj_qvel"])
