@@ -68,10 +68,10 @@
 /* ---- options: re-read on every call (reference users mutate m.opt.* after put_model) -------- */
 #define MJB_OPT_INT_FIELDS(X) \
   X(integrator) X(cone) X(solver) X(iterations) X(ls_iterations) X(disableflags) X(enableflags) \
-  X(broadphase) X(broadphase_filter) X(run_collision_detection)
+  X(broadphase) X(broadphase_filter) X(run_collision_detection) X(ccd_iterations)
 #define MJB_OPT_REAL_FIELDS(X) \
   X(timestep) X(tolerance) X(ls_tolerance) X(gravity_x) X(gravity_y) X(gravity_z) \
-  X(impratio_invsqrt) X(meaninertia)
+  X(impratio_invsqrt) X(meaninertia) X(ccd_tolerance)
 
 /* ---- data sizes ---------------------------------------------------------------------------- */
 #define MJB_DATA_SIZES(X) \

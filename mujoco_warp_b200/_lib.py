@@ -120,9 +120,9 @@ def check(lib, rc: int):
     raise RuntimeError(f"libmjb200 error {rc}: {lib.mjb_last_error().decode()}")
 
 
-_OPT_TENSORS = ("timestep", "tolerance", "ls_tolerance", "gravity", "impratio_invsqrt")
+_OPT_TENSORS = ("timestep", "tolerance", "ls_tolerance", "gravity", "impratio_invsqrt", "ccd_tolerance")
 _OPT_INTS = ("integrator", "cone", "solver", "iterations", "ls_iterations", "disableflags", "enableflags", "broadphase", "broadphase_filter",
-             "run_collision_detection")  # fmt: skip
+             "run_collision_detection", "ccd_iterations")  # fmt: skip
 
 
 def make_option(m) -> MjbOption:
@@ -142,10 +142,11 @@ def make_option(m) -> MjbOption:
     integrator=int(o.integrator), cone=int(o.cone), solver=int(o.solver), iterations=int(o.iterations),
     ls_iterations=int(o.ls_iterations), disableflags=int(o.disableflags), enableflags=int(o.enableflags),
     broadphase=int(o.broadphase), broadphase_filter=int(o.broadphase_filter),
-    run_collision_detection=int(bool(o.run_collision_detection)),
+    run_collision_detection=int(bool(o.run_collision_detection)), ccd_iterations=int(o.ccd_iterations),
     timestep=float(o.timestep.reshape(-1)[0]), tolerance=float(o.tolerance.reshape(-1)[0]),
     ls_tolerance=float(o.ls_tolerance.reshape(-1)[0]), gravity_x=float(g[0]), gravity_y=float(g[1]), gravity_z=float(g[2]),
     impratio_invsqrt=float(o.impratio_invsqrt.reshape(-1)[0]), meaninertia=float(mi.reshape(-1)[0]),
+    ccd_tolerance=float(o.ccd_tolerance.reshape(-1)[0]),
   )  # fmt: skip
   m._opt_cache = (key, opt)
   return opt

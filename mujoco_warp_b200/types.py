@@ -163,9 +163,9 @@ MODEL_REAL_FIELDS = {
 }
 
 OPT_INT_FIELDS = (
-  "integrator cone solver iterations ls_iterations disableflags enableflags broadphase broadphase_filter run_collision_detection"
+  "integrator cone solver iterations ls_iterations disableflags enableflags broadphase broadphase_filter run_collision_detection ccd_iterations"
 ).split()
-OPT_REAL_FIELDS = "timestep tolerance ls_tolerance gravity_x gravity_y gravity_z impratio_invsqrt meaninertia".split()
+OPT_REAL_FIELDS = "timestep tolerance ls_tolerance gravity_x gravity_y gravity_z impratio_invsqrt meaninertia ccd_tolerance".split()
 
 DATA_SIZES = "nworld naconmax njmax njmax_pad nwconmax".split()
 

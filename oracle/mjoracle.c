@@ -4,10 +4,13 @@
  * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load it.
  * The product path (mujoco_warp_b200/) never imports, links or calls anything in oracle/.
  *
- * PARITY UNPINNED against MuJoCo C / Warp: neither `mujoco` nor `warp-lang` is installable in
- * the build container, and the reference stores no golden vectors.  The oracle
- * is pinned instead by (a) the reference's closed-form known-answer tests that need no MuJoCo
- * (tests/test_oracle_known_answers.py), and (b) physics invariants (tests/test_oracle_invariants.py).
+ * PARITY PINNED to outputs of the reference itself: the reference's unmodified source files are executed here in a float64
+ * numpy interpreter of the Warp API (tests/golden/warp_interp.py; `warp-lang` and `mujoco` themselves are not installable),
+ * and the resulting golden vectors are committed: tests/golden/reference_step.npz (put_model -> make_data -> forward / step
+ * on 19 cases, every Data field), primitive_core.npz (pair functions), ccd_pairs.npz (GJK / EPA).  The oracle agrees with
+ * them to <= 1e-9 (tests/test_oracle_reference_golden.py, test_oracle_golden.py, test_oracle_ccd_golden.py).  Also pinned
+ * by the reference's closed-form known-answer tests (tests/test_oracle_kat.py) and physics invariants
+ * (tests/test_oracle_invariants.py).  Not pinned: the MJCF compiler's derived constants (no MuJoCo to compare with).
  *
  * Every function cites the reference file:line (relative to /root/reference/mujoco_warp/_src/)
  * whose algorithm it restates.  Ordering choices where the reference is nondeterministic
@@ -22,6 +25,13 @@
 #include "../include/mjb_fields.h"
 
 typedef double real;
+
+/* convex narrowphase (GJK / EPA): one source, compiled here in float64 and by the CUDA library in float32 */
+#define CCD_REAL double
+#define CCD_FN static inline
+#define CCD_SQRT sqrt
+#define CCD_FABS fabs
+#include "../mujoco_warp_b200/csrc/mjb_ccd_core.h"
 
 #define MJ_MINVAL 1e-15
 #define MJ_MAXVAL 1e10
@@ -933,11 +943,43 @@ static void c_capsule_box(const real* cp, const real* caxis, real r, real hl, co
 /* Computes the contact geometries of one geom pair; returns the number of candidates
  * (collision_primitive.py wrappers :280-1280 + cores).  Candidates with dist >= margin are
  * dropped by the caller (collision_core.py:199-203). */
-static int narrowphase_pair(const OModel* m, const OData* d, int g1, int g2, real margin, OContactGeom* out) {
+/* collision_driver.py:43 MJ_COLLISION_TABLE: pair types routed to the convex (GJK / EPA) narrowphase.  box-box stays on the
+ * primitive here whatever DisableBit.NATIVECCD says (the reference's default sends it to ccd + multicontact, :74, :736). */
+static int is_convex_pair(int t1, int t2) {
+  if (t1 == GEOM_SPHERE || t1 == GEOM_CAPSULE) return t2 == GEOM_ELLIPSOID || (t1 == GEOM_CAPSULE && t2 == GEOM_CYLINDER);
+  if (t1 == GEOM_ELLIPSOID) return t2 == GEOM_ELLIPSOID || t2 == GEOM_CYLINDER || t2 == GEOM_BOX;
+  if (t1 == GEOM_CYLINDER) return t2 == GEOM_CYLINDER || t2 == GEOM_BOX;
+  return 0;
+}
+
+/* collision_convex.py:712 eval_ccd_write_contact (single contact, no collision sensor): returns 1 candidate whose dist is the
+ * surface distance (>= margin when the margin-inflated shapes do not overlap, which write_contact then rejects) */
+static int ccd_pair(const real* p1, const real* r1, const real* s1, int t1, const real* p2, const real* r2, const real* s2, int t2,
+                    real margin, real tolerance, int iterations, OContactGeom* out) {
+  CcdGeom g1, g2;
+  static _Thread_local CcdPolytope pt;
+  CcdGjk res;
+  memcpy(g1.pos, p1, sizeof(g1.pos)); memcpy(g1.rot, r1, sizeof(g1.rot)); memcpy(g1.size, s1, sizeof(g1.size));
+  memcpy(g2.pos, p2, sizeof(g2.pos)); memcpy(g2.rot, r2, sizeof(g2.rot)); memcpy(g2.size, s2, sizeof(g2.size));
+  g1.margin = g2.margin = margin; g1.type = t1; g2.type = t2;
+  if (iterations > CCD_MAX_ITER) iterations = CCD_MAX_ITER;
+  real dist, x1[3], x2[3], n[3];
+  int nc = ccd_run(tolerance, 0.0, iterations, iterations, g1, g2, &pt, &res, &dist, x1, x2);
+  out[0].id = 0;
+  if (nc == 0 || dist >= 0.0) { out[0].dist = MJ_MAXVAL; memset(out[0].pos, 0, sizeof(out[0].pos)); memset(out[0].frame, 0, sizeof(out[0].frame)); return 1; }
+  out[0].dist = dist + margin;
+  for (int i = 0; i < 3; i++) { out[0].pos[i] = 0.5 * (x1[i] + x2[i]); n[i] = x1[i] - x2[i]; }
+  make_frame(out[0].frame, n);
+  return 1;
+}
+
+static int narrowphase_pair(const OModel* m, const OData* d, int g1, int g2, real margin, real ccd_tolerance, int ccd_iterations,
+                            OContactGeom* out) {
   int t1 = m->geom_type[g1], t2 = m->geom_type[g2];
   const real *p1 = d->geom_xpos + 3 * g1, *p2 = d->geom_xpos + 3 * g2, *r1 = d->geom_xmat + 9 * g1, *r2 = d->geom_xmat + 9 * g2;
   const real *s1 = m->geom_size + 3 * g1, *s2 = m->geom_size + 3 * g2;
   real n1[3] = {r1[2], r1[5], r1[8]}, n2[3] = {r2[2], r2[5], r2[8]};
+  if (is_convex_pair(t1, t2)) return ccd_pair(p1, r1, s1, t1, p2, r2, s2, t2, margin, ccd_tolerance, ccd_iterations, out);
   if (t1 == GEOM_PLANE && t2 == GEOM_SPHERE) { /* collision_primitive.py:280 */
     c_plane_sphere(n1, p1, p2, s2[0], &out[0].dist, out[0].pos);
     make_frame(out[0].frame, n1);
@@ -1160,7 +1202,7 @@ static int o_collision(const OModel* m, const OOpt* o, OData* d, const OData* gl
     int condim;
     contact_params(m, g1, g2, pid0, &margin, &gap, &condim, fr, sr, srf, si);
     OContactGeom cg[8];
-    int n = narrowphase_pair(m, d, g1, g2, margin, cg);
+    int n = narrowphase_pair(m, d, g1, g2, margin, o->ccd_tolerance, o->ccd_iterations, cg);
     if (n < 0) { unsupported = 1; continue; }
     for (int k = 0; k < n; k++) { /* write_contact, collision_core.py:160-232 */
       int active = cg[k].dist < margin;
@@ -2184,13 +2226,35 @@ int mjo_narrowphase_pair(int t1, int t2, const double* p1, const double* r1, con
   d.geom_xpos = xpos; d.geom_xmat = xmat;
   OContactGeom out[8];
   memset(out, 0, sizeof(out));
-  int n = narrowphase_pair(&m, &d, 0, 1, margin, out);
+  int n = narrowphase_pair(&m, &d, 0, 1, margin, 1e-6, 35, out);
   for (int k = 0; k < n && k < 8; k++) {
     dist[k] = out[k].dist;
     memcpy(pos + 3 * k, out[k].pos, 3 * sizeof(real));
     memcpy(frame + 9 * k, out[k].frame, 9 * sizeof(real));
   }
   return n;
+}
+/* test hook: collision_gjk.py:2200 ccd on one geom pair (tests/golden/ccd_pairs.npz); returns ncollision */
+static _Thread_local CcdPolytope g_dbg_pt;
+/* test hook: the polytope left behind by the last mjo_ccd call of this thread */
+int mjo_ccd_polytope(double* vert, int* face, double* norm2, int* nvert) {
+  memcpy(vert, g_dbg_pt.vert, sizeof(g_dbg_pt.vert));
+  memcpy(face, g_dbg_pt.face, sizeof(g_dbg_pt.face));
+  memcpy(norm2, g_dbg_pt.face_norm2, sizeof(g_dbg_pt.face_norm2));
+  *nvert = g_dbg_pt.nvert;
+  return g_dbg_pt.nface;
+}
+int mjo_ccd(int t1, int t2, const double* p1, const double* r1, const double* s1, const double* p2, const double* r2, const double* s2,
+            double margin, double cutoff, double tolerance, int iterations, double* dist, double* x1, double* x2) {
+  CcdGeom g1, g2;
+#define pt g_dbg_pt
+  CcdGjk res;
+  memcpy(g1.pos, p1, sizeof(g1.pos)); memcpy(g1.rot, r1, sizeof(g1.rot)); memcpy(g1.size, s1, sizeof(g1.size));
+  memcpy(g2.pos, p2, sizeof(g2.pos)); memcpy(g2.rot, r2, sizeof(g2.rot)); memcpy(g2.size, s2, sizeof(g2.size));
+  g1.margin = g2.margin = margin; g1.type = t1; g2.type = t2;
+  x1[0] = x1[1] = x1[2] = x2[0] = x2[1] = x2[2] = 0.0;
+  return ccd_run(tolerance, cutoff, iterations, iterations, g1, g2, &pt, &res, dist, x1, x2);
+#undef pt
 }
 /* test hook: solver.py:263 _eval_elliptic -> (cost, gradient, curvature) */
 void mjo_eval_elliptic(double mu, const double* quad, const double* q1, const double* q2, double alpha, double* out) {

@@ -31,6 +31,8 @@ import types as _types
 
 import numpy as np
 
+_F = np.float64  # scalars are numpy float64: IEEE semantics (x / 0 = inf, 0 / 0 = nan) like the compiled kernels, no Python exceptions
+
 # ------------------------------------------------------------------------------------------------
 # integers with C semantics
 # ------------------------------------------------------------------------------------------------
@@ -90,13 +92,16 @@ class wrange:
 
 
 def _wint_ctor(x=0):
-  return wint(_math.trunc(x)) if not isinstance(x, (str, bytes)) else wint(int(x))
+  if isinstance(x, (bool, np.bool_, str, bytes)):
+    return wint(int(x))
+  return wint(_math.trunc(x))
 
 
 def patch_module(mod):
   """Rebinds `int` and `range` inside a reference kernel module to the C-semantics versions."""
   mod.int = _IntMeta
   mod.range = wrange
+  mod.float = _F
 
 
 class _IntType(type):
@@ -119,7 +124,7 @@ class _IntMeta(metaclass=_IntType):
 def _scalar(v, isint):
   if isint:
     return wint(int(v))
-  return float(v)
+  return _F(v)
 
 
 class _Arr(np.ndarray):
@@ -262,7 +267,7 @@ def _wrap(v, isint=False):
     return bool(v)
   if isint or isinstance(v, (int, np.integer)):
     return wint(int(v))
-  return float(v)
+  return _F(v)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -353,7 +358,7 @@ class warray:
       return bool(v)
     if self._a.dtype.kind in "iu":
       return wint(int(v))
-    return float(v)
+    return _F(v)
 
   def __getitem__(self, idx):
     if not isinstance(idx, tuple):
@@ -491,10 +496,34 @@ def _kernel(f=None, **kw):
   return lambda g: Kernel(g)
 
 
+def _copy_struct(o):
+  """Warp passes structs to functions BY VALUE (reference collision_gjk.py:2226 relies on it: ccd() shrinks its Geom arguments
+  and returns without restoring them).  Arrays inside a struct stay shared, vectors are copied."""
+  c = type(o).__new__(type(o))
+  for k, v in o.__dict__.items():
+    if isinstance(v, _Arr):
+      v = v.copy().view(type(v))
+    elif getattr(type(v), "_wp_struct", False):
+      v = _copy_struct(v)
+    c.__dict__[k] = v
+  return c
+
+
 def _func(f=None, **kw):
+  def wrap(g):
+    import functools
+
+    @functools.wraps(g)
+    def call(*args, **kwargs):
+      if any(getattr(type(a), "_wp_struct", False) for a in args):
+        args = tuple(_copy_struct(a) if getattr(type(a), "_wp_struct", False) else a for a in args)
+      return g(*args, **kwargs)
+
+    return call
+
   if f is not None and callable(f):
-    return f
-  return lambda g: g
+    return wrap(f)
+  return wrap
 
 
 def _func_native(snippet=None, **kw):
@@ -582,7 +611,7 @@ class Tile(np.ndarray):
       return wint(int(r))
     if isinstance(r, np.bool_):
       return bool(r)
-    return float(r)
+    return _F(r)
 
   def __setitem__(self, idx, val):
     np.ndarray.__setitem__(self.view(np.ndarray), idx, val)
@@ -771,7 +800,7 @@ def _minmax(fn, pyfn):
     if np.ndim(a) == 0 and np.ndim(b) == 0:
       if _is_intlike(a) and _is_intlike(b):
         return wint(pyfn(int(a), int(b)))
-      return float(fn(float(a), float(b)))  # numpy propagates NaN like fmin/fmax do not; inputs are finite
+      return _F(fn(_F(a), _F(b)))  # numpy propagates NaN like fmin/fmax do not; inputs are finite
     return _wrap(fn(np.asarray(a), np.asarray(b)), _is_intlike(np.asarray(a)) and _is_intlike(np.asarray(b)))
 
   return f
@@ -785,7 +814,7 @@ def _normalize(v):
 def _f1(fn):
   def f(v):
     with np.errstate(all="ignore"):
-      return _wrap(fn(np.asarray(v, dtype=np.float64))) if np.ndim(v) else float(fn(float(v)))
+      return _wrap(fn(np.asarray(v, dtype=np.float64))) if np.ndim(v) else _F(fn(_F(v)))
 
   return f
 
@@ -793,7 +822,7 @@ def _f1(fn):
 def _abs(v):
   if np.ndim(v):
     return _wrap(np.abs(np.asarray(v)), _is_intlike(np.asarray(v)))
-  return wint(abs(int(v))) if _is_intlike(v) else float(abs(v))
+  return wint(abs(int(v))) if _is_intlike(v) else _F(abs(v))
 
 
 def _where(c, a, b):
@@ -878,7 +907,7 @@ def build():
   wp.set_module_options = lambda *a, **k: None
   wp.init = lambda *a, **k: None
   wp.config = _types.SimpleNamespace(enable_mathdx_gemm=False, quiet=True, verbose=False)
-  wp.float32 = wp.float64 = wp.float = float
+  wp.float32 = wp.float64 = wp.float = _F
 
   class _I32(metaclass=_IntType):
     _wp_int = True
@@ -910,17 +939,17 @@ def build():
   wp.sqrt = _f1(np.sqrt)
   wp.sin, wp.cos, wp.tan = _f1(np.sin), _f1(np.cos), _f1(np.tan)
   wp.asin, wp.acos, wp.atan = _f1(np.arcsin), _f1(np.arccos), _f1(np.arctan)
-  wp.atan2 = lambda a, b: float(np.arctan2(a, b))
+  wp.atan2 = lambda a, b: _F(np.arctan2(a, b))
   wp.exp, wp.log = _f1(np.exp), _f1(np.log)
-  wp.ceil, wp.floor, wp.round = _f1(np.ceil), _f1(np.floor), (lambda v: float(np.sign(v) * np.floor(abs(v) + 0.5)))
-  wp.pow = lambda a, b: float(np.power(float(a), float(b)))
-  wp.sign = lambda v: -1.0 if v < 0 else 1.0
+  wp.ceil, wp.floor, wp.round = _f1(np.ceil), _f1(np.floor), (lambda v: _F(np.sign(v) * np.floor(abs(v) + 0.5)))
+  wp.pow = lambda a, b: _F(np.power(float(a), float(b)))
+  wp.sign = lambda v: _wrap(np.where(np.asarray(v) < 0, -1.0, 1.0)) if np.ndim(v) else (_F(-1.0) if v < 0 else _F(1.0))
   wp.min, wp.max = _minmax(np.minimum, min), _minmax(np.maximum, max)
   wp.clamp = lambda v, lo, hi: _wrap(np.clip(v, lo, hi), _is_intlike(v) and _is_intlike(lo))
-  wp.dot = lambda a, b: float(np.dot(np.asarray(a), np.asarray(b)))
+  wp.dot = lambda a, b: _F(np.dot(np.asarray(a), np.asarray(b)))
   wp.cross = lambda a, b: _wrap(np.cross(np.asarray(a), np.asarray(b)))
-  wp.length = lambda v: float(np.sqrt(np.dot(np.asarray(v), np.asarray(v))))
-  wp.length_sq = lambda v: float(np.dot(np.asarray(v), np.asarray(v)))
+  wp.length = lambda v: _F(np.sqrt(np.dot(np.asarray(v), np.asarray(v))))
+  wp.length_sq = lambda v: _F(np.dot(np.asarray(v), np.asarray(v)))
   wp.norm_l2 = wp.length
   wp.normalize = _normalize
   wp.transpose = lambda m: _wrap(np.asarray(m).T.copy())
@@ -928,8 +957,8 @@ def build():
   wp.cw_div = lambda a, b: _wrap(np.asarray(a) / np.asarray(b))
   wp.outer = lambda a, b: _wrap(np.outer(a, b))
   wp.diag = lambda v: _wrap(np.diag(np.asarray(v)))
-  wp.trace = lambda m: float(np.trace(np.asarray(m)))
-  wp.determinant = lambda m: float(np.linalg.det(np.asarray(m)))
+  wp.trace = lambda m: _F(np.trace(np.asarray(m)))
+  wp.determinant = lambda m: _F(np.linalg.det(np.asarray(m)))
   wp.inverse = lambda m: _wrap(np.linalg.inv(np.asarray(m)))
   wp.identity = lambda n, dtype=float: _wrap(np.eye(n))
   wp.matrix_from_rows = lambda *rows: _wrap(np.stack([np.asarray(r, dtype=np.float64) for r in rows]))
@@ -1000,6 +1029,7 @@ def install():
   if "warp" in sys.modules and not getattr(sys.modules["warp"], "_is_shim", False):
     raise RuntimeError("a real warp is importable: use it instead of the interpreter")
   wp = build()
+  np.seterr(all="ignore")
   sys.modules["warp"] = wp
   sys.modules["warp.types"] = wp.types
   sys.modules["warp.utils"] = wp.utils

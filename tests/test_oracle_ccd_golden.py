@@ -1,0 +1,59 @@
+"""Oracle GJK / EPA (the float64 build of csrc/mjb_ccd_core.h) vs golden vectors produced by executing the REFERENCE's own
+`ccd` (/root/reference/mujoco_warp/_src/collision_gjk.py:2200, run under tests/golden/warp_interp.py by
+tests/golden/make_ccd_golden.py): 540 seeded pairs over all 15 type combinations of sphere / capsule / ellipsoid / cylinder
+/ box -- separated (early-out and distance mode), shallow and deep penetrations, with and without margin.
+
+ncollision must be equal and dist agree to 1e-8 on every pair (both sides float64).  Witness points x1, x2 agree to 1e-7
+except on a few pairs per type: (a) a stopping test that falls within rounding of its threshold costs one EPA iteration and
+moves the witness by < the ccd tolerance (seen: <= 2.2e-6); (b) exact ties -- e.g. in a deep sphere-cylinder penetration the
+reference zeroes the cylinder's radius (collision_gjk.py:2259 writes size2 = 0 back into a non-sphere geom2), the initial
+polytope's face normal is then exactly perpendicular to the remaining segment and `sign(0 +- 1e-17)` picks the support
+point (collision_gjk.py:137).  Both outcomes have the same depth; at most 3 such pairs per type are tolerated."""
+
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ccd_pairs.npz")
+NAMES = {2: "sphere", 3: "capsule", 4: "ellipsoid", 5: "cylinder", 6: "box"}
+TYPES = [2, 3, 4, 5, 6]
+PAIRS = [(a, b) for i, a in enumerate(TYPES) for b in TYPES[i:]]
+
+
+def run_pair(lib, g, i):
+  dp = ctypes.POINTER(ctypes.c_double)
+  keep = [np.ascontiguousarray(g[k][i], dtype=np.float64) for k in ("p1", "r1", "s1", "p2", "r2", "s2")]
+  dist = ctypes.c_double(0.0)
+  x1, x2 = (ctypes.c_double * 3)(), (ctypes.c_double * 3)()
+  n = lib.mjo_ccd(int(g["t1"][i]), int(g["t2"][i]), *[a.ctypes.data_as(dp) for a in keep], ctypes.c_double(float(g["margin"][i])),
+                  ctypes.c_double(float(g["cutoff"][i])), ctypes.c_double(1e-6), 35, ctypes.byref(dist), x1, x2)  # fmt: skip
+  return n, dist.value, np.array(x1[:]), np.array(x2[:])
+
+
+@pytest.mark.parametrize("pair", PAIRS, ids=lambda p: f"{NAMES[p[0]]}-{NAMES[p[1]]}")
+def test_ccd_matches_reference_execution(pair):
+  lib = O.load()
+  lib.mjo_ccd.restype = ctypes.c_int
+  with np.load(GOLDEN) as z:
+    g = {k: z[k] for k in z.files}
+  idx = np.nonzero((g["t1"] == pair[0]) & (g["t2"] == pair[1]))[0]
+  assert len(idx) >= 30
+  loose = npen = 0
+  for i in idx:
+    n, dist, x1, x2 = run_pair(lib, g, i)
+    assert n == int(g["ncollision"][i]), (pair, i)
+    if g["dist"][i] > 1e29:
+      assert dist > 1e29, (pair, i, dist)
+      continue
+    npen += g["dist"][i] < 0
+    assert abs(dist - g["dist"][i]) < 1e-8, (pair, i, dist, g["dist"][i])
+    err = max(np.abs(x1 - g["x1"][i]).max(), np.abs(x2 - g["x2"][i]).max())
+    if err > 1e-7:
+      loose += 1
+      assert err < 5e-2, (pair, i, err)
+  assert loose <= 3, (pair, loose)
+  assert npen >= 5, (pair, npen)
