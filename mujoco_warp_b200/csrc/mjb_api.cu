@@ -152,6 +152,7 @@ extern "C" int mjb_model_create(const int* sizes, int nsizes, const void* blob, 
       const int ta = gtype[pair[2 * p]], tb = gtype[pair[2 * p + 1]];
       const int t1 = ta < tb ? ta : tb, t2 = ta < tb ? tb : ta;
       if (t2 == GEOM_BOX && t1 != GEOM_PLANE) m->col_feat |= COLF_BOX;  // sphere-box, capsule-box, box-box
+      if (t1 == GEOM_ELLIPSOID || t1 == GEOM_CYLINDER || t2 == GEOM_ELLIPSOID || t2 == GEOM_CYLINDER) m->col_feat |= COLF_CONVEX;
     }
   }
   *out = m;
@@ -263,6 +264,7 @@ static GroupKernel group_kernel_of(int g, bool in_smem, int variant) {
         case 1: return group_kernel<G_COL, 1>(in_smem);
         case 2: return group_kernel<G_COL, 2>(in_smem);
         case 3: return group_kernel<G_COL, 3>(in_smem);
+        case 7: return group_kernel<G_COL, 7>(in_smem);  // models with ellipsoid / cylinder geoms run the all-features variant
         default: return group_kernel<G_COL, 0>(in_smem);
       }
     case G_CON: return variant ? group_kernel<G_CON, 1>(in_smem) : group_kernel<G_CON>(in_smem);
@@ -275,7 +277,7 @@ static GroupKernel group_kernel_of(int g, bool in_smem, int variant) {
 static int launch_group(int g, const MjbModel* m, MjbData* d, KParams& K, uint32_t stages, cudaStream_t stream) {
   // collision: the kernel variant follows the model's pair types and the broadphase option of THIS call
   // and make_constraint / solve are compiled once per cone type
-  const int variant = g == G_COL ? (m->col_feat | (K.o.broadphase != 0 ? COLF_SAP : 0)) : ((g == G_CON || g == G_SOL) && K.o.cone == 1) ? 1 : 0;
+  const int variant = g == G_COL ? ((m->col_feat & COLF_CONVEX) ? COLF_COUNT - 1 : (m->col_feat | (K.o.broadphase != 0 ? COLF_SAP : 0))) : ((g == G_CON || g == G_SOL) && K.o.cone == 1) ? 1 : 0;
   MjbData::GroupCfg& c = d->cfg[!variant ? g : g == G_COL ? G_COUNT + variant : G_COUNT + COLF_COUNT + (g == G_CON ? 0 : 1)];
   if (!c.ready) {
     int wpb = warps_per_block(g == G_SOL ? group_threads(G_SOL) / 32 : 8);

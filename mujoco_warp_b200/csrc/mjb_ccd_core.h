@@ -10,11 +10,16 @@
  * agreement alone proves nothing about it: what pins it is tests/golden/ccd_pairs.npz, produced by executing the
  * reference's own `ccd` (tests/golden/make_ccd_golden.py).
  *
- * The includer defines:  CCD_REAL (float | double),  CCD_FN (function qualifiers),  CCD_SQRT / CCD_FABS.
+ * The includer defines:  CCD_REAL (float | double),  CCD_FN (qualifiers of the small helpers),  CCD_FN_NOINLINE (qualifiers of
+ * the large routines: kept out of line on the device, where inlining the S3D -> S2D -> S1D recursion into every caller multiplies
+ * the code size),  CCD_SQRT / CCD_FABS.
  */
 #ifndef MJB_CCD_CORE_H_
 #define MJB_CCD_CORE_H_
 
+#ifndef CCD_FN_NOINLINE
+#define CCD_FN_NOINLINE CCD_FN
+#endif
 typedef CCD_REAL creal;
 #define CR(x) ((creal)(x))
 
@@ -79,7 +84,7 @@ CCD_FN void ccd_rot_t(creal* r, const creal* m, const creal* v) {
 }
 
 /* collision_gjk.py:98 support: furthest point of a geom along `dir`; returns the vertex index (boxes) or -1 */
-CCD_FN int ccd_support(const CcdGeom* g, const creal* dir, creal* point) {
+CCD_FN_NOINLINE int ccd_support(const CcdGeom* g, const creal* dir, creal* point) {
   int vertex_index = -1;
   if (g->type == CCD_GEOM_SPHERE) {
     creal s = g->size[0] + CR(0.5) * g->margin;
@@ -130,7 +135,7 @@ CCD_FN void ccd_project_origin_line(creal* r, const creal* v1, const creal* v2) 
 }
 
 /* :287 returns 1 on failure */
-CCD_FN int ccd_project_origin_plane(creal* r, const creal* v1, const creal* v2, const creal* v3) {
+CCD_FN_NOINLINE int ccd_project_origin_plane(creal* r, const creal* v1, const creal* v2, const creal* v3) {
   creal d21[3], d31[3], d32[3], n[3], nv, nn;
   ccd_sub(d21, v2, v1); ccd_sub(d31, v3, v1); ccd_sub(d32, v3, v2);
   r[0] = r[1] = r[2] = CR(0.0);
@@ -163,7 +168,7 @@ CCD_FN void ccd_S1D(creal* out, const creal* s1, const creal* s2) {
 }
 
 /* :395 */
-CCD_FN void ccd_S2D(creal* out, const creal* s1, const creal* s2, const creal* s3) {
+CCD_FN_NOINLINE void ccd_S2D(creal* out, const creal* s1, const creal* s2, const creal* s3) {
   creal po[3];
   if (ccd_project_origin_plane(po, s1, s2, s3)) {
     creal v[2];
@@ -209,7 +214,7 @@ CCD_FN void ccd_S2D(creal* out, const creal* s1, const creal* s2, const creal* s
 }
 
 /* :319 */
-CCD_FN void ccd_S3D(creal* out, const creal* s1, const creal* s2, const creal* s3, const creal* s4) {
+CCD_FN_NOINLINE void ccd_S3D(creal* out, const creal* s1, const creal* s2, const creal* s3, const creal* s4) {
   creal C41 = -ccd_det3(s2, s3, s4), C42 = ccd_det3(s1, s3, s4), C43 = -ccd_det3(s1, s2, s4), C44 = ccd_det3(s1, s2, s3);
   creal m_det = C41 + C42 + C43 + C44;
   int comp1 = ccd_same_sign(m_det, C41), comp2 = ccd_same_sign(m_det, C42), comp3 = ccd_same_sign(m_det, C43), comp4 = ccd_same_sign(m_det, C44);
@@ -261,7 +266,7 @@ CCD_FN void ccd_linear_combine(creal* v, int n, const creal* c, creal mat[4][3])
 }
 
 /* :563 gjk.  x1_0 / x2_0: initial guess (geom centres). */
-CCD_FN void ccd_gjk(CcdGjk* res, creal tolerance, int iterations, const CcdGeom* g1, const CcdGeom* g2, const creal* x1_0,
+CCD_FN_NOINLINE void ccd_gjk(CcdGjk* res, creal tolerance, int iterations, const CcdGeom* g1, const CcdGeom* g2, const creal* x1_0,
                     const creal* x2_0, creal cutoff, int is_discrete) {
   creal cutoff2 = cutoff * cutoff, tol2 = tolerance * tolerance, epsilon = is_discrete ? CR(0.0) : CR(0.5) * tol2;
   creal coord[4] = {CR(0.0), CR(0.0), CR(0.0), CR(0.0)}, xk[3], xnorm_old = CCD_FLOAT_MAX;
@@ -326,7 +331,7 @@ CCD_FN int ccd_test_tetra(const creal* p0, const creal* p1, const creal* p2, con
 }
 
 /* :702 */
-CCD_FN void ccd_tri_affine_coord(creal* out, const creal* v1, const creal* v2, const creal* v3, const creal* p) {
+CCD_FN_NOINLINE void ccd_tri_affine_coord(creal* out, const creal* v1, const creal* v2, const creal* v3, const creal* p) {
   creal M14 = v2[1] * v3[2] - v2[2] * v3[1] - v1[1] * v3[2] + v1[2] * v3[1] + v1[1] * v2[2] - v1[2] * v2[1];
   creal M24 = v2[0] * v3[2] - v2[2] * v3[0] - v1[0] * v3[2] + v1[2] * v3[0] + v1[0] * v2[2] - v1[2] * v2[0];
   creal M34 = v2[0] * v3[1] - v2[1] * v3[0] - v1[0] * v3[1] + v1[1] * v3[0] + v1[0] * v2[1] - v1[1] * v2[0];
@@ -352,7 +357,7 @@ CCD_FN int ccd_tri_point_intersect(const creal* v1, const creal* v2, const creal
 }
 
 /* :195 */
-CCD_FN creal ccd_attach_face(CcdPolytope* pt, int idx, int v1, int v2, int v3) {
+CCD_FN_NOINLINE creal ccd_attach_face(CcdPolytope* pt, int idx, int v1, int v2, int v3) {
   if (pt->nface == pt->maxface) return CR(0.0);
   creal p1[3], p2[3], p3[3], r[3];
   ccd_sub(p1, pt->vert[2 * v1], pt->vert[2 * v1 + 1]);
@@ -408,7 +413,7 @@ CCD_FN void ccd_load_simplex(CcdPolytope* pt, const CcdGjk* r, int n) {
 }
 
 /* :937 polytope from a 1-simplex.  On status -1 `r` is replaced by a 2-simplex (the caller continues with _polytope3). */
-CCD_FN void ccd_polytope2(CcdPolytope* pt, CcdGjk* r, const CcdGeom* g1, const CcdGeom* g2) {
+CCD_FN_NOINLINE void ccd_polytope2(CcdPolytope* pt, CcdGjk* r, const CcdGeom* g1, const CcdGeom* g2) {
   creal diff[3], value = CCD_FLOAT_MAX, e[3] = {CR(0.0), CR(0.0), CR(0.0)}, d1[3], d2[3], d3[3], R[9];
   creal s0[3], s1[3];
   int index = 0;
@@ -447,7 +452,7 @@ CCD_FN void ccd_polytope2(CcdPolytope* pt, CcdGjk* r, const CcdGeom* g1, const C
 }
 
 /* :1027 polytope from a 2-simplex */
-CCD_FN void ccd_polytope3(CcdPolytope* pt, const CcdGjk* r, const CcdGeom* g1, const CcdGeom* g2) {
+CCD_FN_NOINLINE void ccd_polytope3(CcdPolytope* pt, const CcdGjk* r, const CcdGeom* g1, const CcdGeom* g2) {
   creal a[3], b[3], n[3], nn[3], v1[3], v2[3], v3[3], v4[3], v5[3];
   ccd_copy(v1, r->simplex[0]); ccd_copy(v2, r->simplex[1]); ccd_copy(v3, r->simplex[2]);
   ccd_sub(a, v2, v1); ccd_sub(b, v3, v1); ccd_cross(n, a, b);
@@ -468,7 +473,7 @@ CCD_FN void ccd_polytope3(CcdPolytope* pt, const CcdGjk* r, const CcdGeom* g1, c
 }
 
 /* :1115 polytope from a 3-simplex */
-CCD_FN void ccd_polytope4(CcdPolytope* pt, CcdGjk* r) {
+CCD_FN_NOINLINE void ccd_polytope4(CcdPolytope* pt, CcdGjk* r) {
   ccd_load_simplex(pt, r, 4);
   const int f[4][3] = {{0, 1, 2}, {0, 3, 1}, {0, 2, 3}, {3, 2, 1}};
   for (int k = 0; k < 4; k++) {
@@ -499,7 +504,7 @@ CCD_FN int ccd_add_edge(CcdPolytope* pt, int e1, int e2) {
 }
 
 /* :1202 _epa + :863 _epa_witness.  Returns the face index (-1: no contact) and dist / x1 / x2. */
-CCD_FN int ccd_epa(creal tolerance, int iterations, CcdPolytope* pt, const CcdGeom* g1, const CcdGeom* g2, int is_discrete, creal* dist,
+CCD_FN_NOINLINE int ccd_epa(creal tolerance, int iterations, CcdPolytope* pt, const CcdGeom* g1, const CcdGeom* g2, int is_discrete, creal* dist,
                    creal* x1, creal* x2) {
   creal upper = CCD_FLOAT_MAX, upper2 = CCD_FLOAT_MAX, epsilon = is_discrete ? CR(1e-15) : tolerance;
   int idx = -1, pidx = -1, nvalid = pt->nface;
@@ -579,7 +584,7 @@ CCD_FN int ccd_epa(creal tolerance, int iterations, CcdPolytope* pt, const CcdGe
 
 /* :2200 ccd.  g1 / g2 are taken by value (the routine shrinks spheres / capsules to points / segments).  `pt` is scratch.
  * Returns the number of contacts (0 or 1); dist is relative to the margin-inflated shapes as in the reference. */
-CCD_FN int ccd_run(creal tolerance, creal cutoff, int gjk_iterations, int epa_iterations, CcdGeom g1, CcdGeom g2, CcdPolytope* pt,
+CCD_FN_NOINLINE int ccd_run(creal tolerance, creal cutoff, int gjk_iterations, int epa_iterations, CcdGeom g1, CcdGeom g2, CcdPolytope* pt,
                    CcdGjk* res, creal* dist, creal* x1, creal* x2) {
   creal full1 = CR(0.0), full2 = CR(0.0), size1 = CR(0.0), size2 = CR(0.0), x_1[3], x_2[3];
   int is_discrete = (g1.type == CCD_GEOM_BOX && g2.type == CCD_GEOM_BOX) && (g1.margin == CR(0.0) && g2.margin == CR(0.0));

@@ -16,7 +16,54 @@
 
 // Compile-time variants of the collision kernel (template parameter FEAT): code a model / option set does not need
 // is not compiled into the variant it runs, so it costs the common case neither registers nor instruction cache.
-enum CollisionFeature { COLF_BOX = 1 /* sphere-box, capsule-box pairs present */, COLF_SAP = 2 /* sweep-and-prune broadphase */, COLF_COUNT = 4 };
+enum CollisionFeature {
+  COLF_BOX = 1 /* sphere-box, capsule-box, box-box pairs present */,
+  COLF_SAP = 2 /* sweep-and-prune broadphase */,
+  COLF_CONVEX = 4 /* ellipsoid / cylinder geoms: their primitive pairs and the GJK / EPA pairs */,
+  COLF_COUNT = 8
+};
+
+// Convex narrowphase core (GJK + EPA, reference collision_gjk.py), float32 device build of the shared C source
+#define CCD_REAL float
+#define CCD_FN static __device__ __forceinline__
+#define CCD_FN_NOINLINE static __device__ __noinline__
+#define CCD_SQRT sqrtf
+#define CCD_FABS fabsf
+#include "mjb_ccd_core.h"
+
+// collision_driver.py:43 MJ_COLLISION_TABLE: pair types of CollisionType.CONVEX among the implemented geom types
+// (box-box stays on the primitive, the reference's NATIVECCD-disabled route, :736)
+__device__ __forceinline__ bool is_convex_pair(int t1, int t2) {
+  if (t1 == GEOM_SPHERE || t1 == GEOM_CAPSULE) return t2 == GEOM_ELLIPSOID || (t1 == GEOM_CAPSULE && t2 == GEOM_CYLINDER);
+  if (t1 == GEOM_ELLIPSOID) return t2 == GEOM_ELLIPSOID || t2 == GEOM_CYLINDER || t2 == GEOM_BOX;
+  if (t1 == GEOM_CYLINDER) return t2 == GEOM_CYLINDER || t2 == GEOM_BOX;
+  return false;
+}
+
+// collision_convex.py:712 eval_ccd_write_contact for one pair (single contact, no collision sensor): returns the number of
+// contacts (0 / 1); dist is the surface distance, pos the midpoint of the witness points, nrm = x1 - x2 (unnormalised).
+__device__ __noinline__ int c_ccd_pair(const float* p1, const float* r1, const float* s1, int t1, const float* p2, const float* r2,
+                                       const float* s2, int t2, float margin, float tolerance, int iterations, float* dist, float* pos,
+                                       float* nrm) {
+  CcdGeom g1, g2;
+  CcdPolytope pt;  // ~5 kB of local memory per thread
+  CcdGjk res;
+#pragma unroll
+  for (int i = 0; i < 3; i++) { g1.pos[i] = p1[i]; g2.pos[i] = p2[i]; g1.size[i] = s1[i]; g2.size[i] = s2[i]; }
+#pragma unroll
+  for (int i = 0; i < 9; i++) { g1.rot[i] = r1[i]; g2.rot[i] = r2[i]; }
+  g1.margin = g2.margin = margin;
+  g1.type = t1;
+  g2.type = t2;
+  if (iterations > CCD_MAX_ITER) iterations = CCD_MAX_ITER;
+  float d, x1[3], x2[3];
+  const int nc = ccd_run(tolerance, 0.f, iterations, iterations, g1, g2, &pt, &res, &d, x1, x2);
+  if (nc == 0 || d >= 0.f) return 0;
+  *dist = d + margin;
+#pragma unroll
+  for (int i = 0; i < 3; i++) { pos[i] = 0.5f * (x1[i] + x2[i]); nrm[i] = x1[i] - x2[i]; }
+  return 1;
+}
 
 // collision_driver.py:91-111, 218-271
 __device__ __forceinline__ bool bp_filter(const KParams& K, const unsigned char* mb, int w, int g1, int g2) {
@@ -498,8 +545,9 @@ __device__ __noinline__ int c_box_box(const float* p1, const float* R1, const fl
 
 // Number of candidate contacts of a pair type (collision_primitive.py wrappers).
 __device__ __forceinline__ int pair_ncand(int t1, int t2) {
-  if (t1 == GEOM_PLANE) return t2 == GEOM_SPHERE ? 1 : (t2 == GEOM_CAPSULE ? 2 : (t2 == GEOM_BOX ? 8 : 0));
-  if (t1 == GEOM_SPHERE) return (t2 == GEOM_SPHERE || t2 == GEOM_CAPSULE || t2 == GEOM_BOX) ? 1 : 0;
+  if (t1 == GEOM_PLANE) return t2 == GEOM_SPHERE || t2 == GEOM_ELLIPSOID ? 1 : (t2 == GEOM_CAPSULE ? 2 : (t2 == GEOM_BOX ? 8 : (t2 == GEOM_CYLINDER ? 4 : 0)));
+  if (is_convex_pair(t1, t2)) return 1;
+  if (t1 == GEOM_SPHERE) return (t2 == GEOM_SPHERE || t2 == GEOM_CAPSULE || t2 == GEOM_BOX || t2 == GEOM_CYLINDER) ? 1 : 0;
   if (t1 == GEOM_CAPSULE) return (t2 == GEOM_CAPSULE || t2 == GEOM_BOX) ? 2 : 0;
   if (t1 == GEOM_BOX && t2 == GEOM_BOX) return 8;
   return 0;
@@ -529,6 +577,39 @@ __device__ __forceinline__ void pair_contact(const PairGeom& g, const float* r2,
       const V3 e = g.p2 + g.n2 * (k == 0 ? g.s2.y : -g.s2.y);
       dist = dot(e - g.p1, n) - g.s2.x;
       pos = e - n * (g.s2.x + 0.5f * dist);
+    } else if ((FEAT & COLF_CONVEX) && g.t2 == GEOM_ELLIPSOID) {  // core :365-392
+      V3 ld = V3{(r2[0] * n.x + r2[3] * n.y + r2[6] * n.z) * g.s2.x, (r2[1] * n.x + r2[4] * n.y + r2[7] * n.z) * g.s2.y,
+                 (r2[2] * n.x + r2[5] * n.y + r2[8] * n.z) * g.s2.z};
+      const float nn = norm(ld);
+      ld = nn > 0.f ? ld * (-1.0f / nn) : V3{0.f, 0.f, 0.f};
+      const V3 loc = V3{ld.x * g.s2.x, ld.y * g.s2.y, ld.z * g.s2.z};
+      const V3 pe = g.p2 + V3{r2[0] * loc.x + r2[1] * loc.y + r2[2] * loc.z, r2[3] * loc.x + r2[4] * loc.y + r2[5] * loc.z,
+                              r2[6] * loc.x + r2[7] * loc.y + r2[8] * loc.z};
+      dist = dot(n, pe - g.p1);
+      pos = pe - n * (dist * 0.5f);
+      frame = make_frame(n);
+    } else if ((FEAT & COLF_CONVEX) && g.t2 == GEOM_CYLINDER) {  // core :519-612
+      V3 axis = g.n2;
+      float prjaxis = dot(n, axis);
+      if (prjaxis > 0.f) { axis = axis * -1.0f; prjaxis = -prjaxis; }
+      const float dist0 = dot(g.p2 - g.p1, n), radius = g.s2.x, hh = g.s2.y;
+      V3 vec = axis * prjaxis - n;
+      const float len_sqr = dot(vec, vec);
+      vec = len_sqr >= 1e-12f ? vec * safe_divf(radius, sqrtf(len_sqr)) : V3{radius, 0.f, 0.f};
+      const float prjvec = dot(vec, n);
+      axis = axis * hh;
+      prjaxis *= hh;
+      if (k < 2) {
+        dist = dist0 + (k == 0 ? prjaxis : -prjaxis) + prjvec;
+        pos = g.p2 + vec + (k == 0 ? axis : axis * -1.0f) - n * (dist * 0.5f);
+      } else {
+        dist = dist0 + prjaxis - prjvec * 0.5f;
+        V3 vec1 = cross(vec, axis);
+        const float nv1 = norm(vec1);
+        vec1 = nv1 > 0.f ? vec1 * (radius * sqrtf(3.0f) * 0.5f / nv1) : V3{0.f, 0.f, 0.f};
+        pos = g.p2 + (k == 2 ? vec1 : vec1 * -1.0f) + axis - vec * 0.5f - n * (dist * 0.5f);
+      }
+      frame = make_frame(n);
     } else {  // plane-box, core :396-443
       const V3 corner = V3{(k & 1) ? g.s2.x : -g.s2.x, (k & 2) ? g.s2.y : -g.s2.y, (k & 4) ? g.s2.z : -g.s2.z};
       const V3 cw = V3{r2[0] * corner.x + r2[1] * corner.y + r2[2] * corner.z, r2[3] * corner.x + r2[4] * corner.y + r2[5] * corner.z,
@@ -552,6 +633,28 @@ __device__ __forceinline__ void pair_contact(const PairGeom& g, const float* r2,
       centre = g.p1 + g.n1 * (g.s1.y * t[k]);
     }
     c_sphere_box(centre, g.s1.x, g.p2, r2, bs, dist, pos, nrm);
+  } else if ((FEAT & COLF_CONVEX) && g.t1 == GEOM_SPHERE && g.t2 == GEOM_CYLINDER) {  // core :447-515
+    const V3 vec = g.p1 - g.p2;
+    const float x = dot(vec, g.n2);
+    const V3 aproj = g.n2 * x, pproj = vec - aproj;
+    const float psq = dot(pproj, pproj);
+    bool side = fabsf(x) < g.s2.y, cap = psq < g.s2.x * g.s2.x;
+    if (side && cap) {
+      if (g.s2.y - fabsf(x) < g.s2.x - sqrtf(psq)) side = false;
+      else cap = false;
+    }
+    if (side) {
+      c_sphere_sphere(g.p1, g.s1.x, g.p2 + aproj, g.s2.x, dist, pos, nrm);
+    } else if (cap) {
+      const float sg = x > 0.f ? 1.f : -1.f;
+      const V3 pn = g.n2 * sg, pc = g.p2 + pn * g.s2.y;
+      dist = dot(g.p1 - pc, pn) - g.s1.x;
+      pos = g.p1 - pn * (g.s1.x + 0.5f * dist);
+      nrm = pn * -1.0f;
+    } else {
+      const float inv = safe_divf(1.0f, sqrtf(psq)), sg = x < 0.f ? -1.f : 1.f;
+      c_sphere_sphere(g.p1, g.s1.x, g.p2 + g.n2 * (sg * g.s2.y) + pproj * (g.s2.x * inv), 0.f, dist, pos, nrm);
+    }
   } else if (g.t1 == GEOM_SPHERE) {  // sphere-capsule, core :147-178
     const V3 a = g.p2 - g.n2 * g.s2.y, ab = g.n2 * (2.0f * g.s2.y);
     const float t = clampf(dot(g.p1 - a, ab) / (dot(ab, ab) + 1e-6f), 0.f, 1.f);
@@ -653,7 +756,7 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
   PairGeom g;
   ContactParams cp;
   const float* r2 = nullptr;
-  float bdist[(FEAT & COLF_BOX) ? 8 : 1], bpos[(FEAT & COLF_BOX) ? 24 : 1], bnrm[3] = {1.f, 0.f, 0.f};  // box-box results
+  float bdist[(FEAT & COLF_BOX) ? 8 : 1], bpos[(FEAT & COLF_BOX) ? 24 : 3], bnrm[3] = {1.f, 0.f, 0.f};  // box-box results
   int nbb = 0;
   bool boxbox = false;
   if (has) {
@@ -682,11 +785,17 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
       nbb = c_box_box(pa, DW(geom_xmat) + 9 * g1, sa, pb, r2, sb, cp.margin, bdist, bpos, bnrm);
       boxbox = true;
     }
+    if ((FEAT & COLF_CONVEX) && is_convex_pair(g.t1, g.t2)) {  // GJK / EPA once per pair; the two passes below read the result
+      const float pa[3] = {g.p1.x, g.p1.y, g.p1.z}, pb[3] = {g.p2.x, g.p2.y, g.p2.z};
+      const float sa[3] = {g.s1.x, g.s1.y, g.s1.z}, sb[3] = {g.s2.x, g.s2.y, g.s2.z};
+      nbb = c_ccd_pair(pa, DW(geom_xmat) + 9 * g1, sa, g.t1, pb, r2, sb, g.t2, cp.margin, K.o.ccd_tolerance, K.o.ccd_iterations, bdist, bpos, bnrm);
+      boxbox = true;
+    }
     for (int k = 0; k < ncand; k++) {  // pass 1: count (write_contact filter, collision_core.py:199-203)
       float dist;
       V3 pos;
       M3 frame;
-      if ((FEAT & COLF_BOX) && boxbox) dist = k < nbb ? bdist[k] : INFINITY;
+      if ((FEAT & (COLF_BOX | COLF_CONVEX)) && boxbox) dist = k < nbb ? bdist[k] : INFINITY;
       else pair_contact<FEAT>(g, r2, cp.margin, k, dist, pos, frame);
       const bool active = dist < cp.margin;
       if (!((pid0 == -2 || !active) && pid1 == -1)) nact++;
@@ -705,7 +814,7 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
       float dist;
       V3 pos;
       M3 frame;
-      if ((FEAT & COLF_BOX) && boxbox) {
+      if ((FEAT & (COLF_BOX | COLF_CONVEX)) && boxbox) {
         dist = k < nbb ? bdist[k] : INFINITY;
         pos = V3{bpos[3 * (k & 7)], bpos[3 * (k & 7) + 1], bpos[3 * (k & 7) + 2]};
         frame = make_frame(V3{bnrm[0], bnrm[1], bnrm[2]});

@@ -211,7 +211,7 @@ def host_model(mjm) -> SimpleNamespace:
   lookup[include] = np.arange(nxn, dtype=i32)
   ints["nxn_lookup"] = lookup
 
-  # supported narrowphase pair types (primitive analytic functions only in this round)
+  # supported narrowphase pair types: analytic primitives + GJK / EPA for ellipsoid / cylinder pairs (no meshes / hfields yet)
   supported = {
     (C.GeomType.PLANE, C.GeomType.SPHERE),
     (C.GeomType.PLANE, C.GeomType.CAPSULE),
@@ -222,6 +222,18 @@ def host_model(mjm) -> SimpleNamespace:
     (C.GeomType.SPHERE, C.GeomType.BOX),
     (C.GeomType.CAPSULE, C.GeomType.BOX),
     (C.GeomType.BOX, C.GeomType.BOX),
+    (C.GeomType.PLANE, C.GeomType.ELLIPSOID),
+    (C.GeomType.PLANE, C.GeomType.CYLINDER),
+    (C.GeomType.SPHERE, C.GeomType.CYLINDER),
+    # convex narrowphase (GJK / EPA, reference collision_driver.py:43 MJ_COLLISION_TABLE entries of type CONVEX)
+    (C.GeomType.SPHERE, C.GeomType.ELLIPSOID),
+    (C.GeomType.CAPSULE, C.GeomType.ELLIPSOID),
+    (C.GeomType.CAPSULE, C.GeomType.CYLINDER),
+    (C.GeomType.ELLIPSOID, C.GeomType.ELLIPSOID),
+    (C.GeomType.ELLIPSOID, C.GeomType.CYLINDER),
+    (C.GeomType.ELLIPSOID, C.GeomType.BOX),
+    (C.GeomType.CYLINDER, C.GeomType.CYLINDER),
+    (C.GeomType.CYLINDER, C.GeomType.BOX),
   }
   gtype = ints["geom_type"]
   for ga, gb in ints["nxn_pair"]:

@@ -1018,6 +1018,67 @@ static int narrowphase_pair(const OModel* m, const OData* d, int g1, int g2, rea
     }
     return 8;
   }
+  if (t1 == GEOM_PLANE && t2 == GEOM_ELLIPSOID) { /* collision_primitive_core.py:365-392 */
+    real ld[3], sup[3], loc[3], w[3], nn;
+    for (int i = 0; i < 3; i++) ld[i] = (r2[i] * n1[0] + r2[3 + i] * n1[1] + r2[6 + i] * n1[2]) * s2[i];
+    nn = norm3(ld);
+    for (int i = 0; i < 3; i++) { sup[i] = nn > 0.0 ? -ld[i] / nn : 0.0; loc[i] = sup[i] * s2[i]; }
+    mat_vec(w, r2, loc);
+    real pe[3] = {p2[0] + w[0], p2[1] + w[1], p2[2] + w[2]}, dif[3] = {pe[0] - p1[0], pe[1] - p1[1], pe[2] - p1[2]};
+    out[0].dist = dot3(n1, dif);
+    for (int i = 0; i < 3; i++) out[0].pos[i] = pe[i] - n1[i] * out[0].dist * 0.5;
+    make_frame(out[0].frame, n1);
+    out[0].id = 0;
+    return 1;
+  }
+  if (t1 == GEOM_PLANE && t2 == GEOM_CYLINDER) { /* collision_primitive_core.py:519-612 */
+    real axis[3] = {n2[0], n2[1], n2[2]}, prjaxis = dot3(n1, n2), dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]}, vec[3], vec1[3];
+    if (prjaxis > 0) { for (int i = 0; i < 3; i++) axis[i] = -axis[i]; prjaxis = -prjaxis; }
+    real dist0 = dot3(dif, n1), len_sqr, prjvec, radius = s2[0], hh = s2[1];
+    for (int i = 0; i < 3; i++) vec[i] = axis[i] * prjaxis - n1[i];
+    len_sqr = dot3(vec, vec);
+    if (len_sqr >= 1e-12) { real sc = safe_div(radius, sqrt(len_sqr)); for (int i = 0; i < 3; i++) vec[i] *= sc; }
+    else { vec[0] = radius; vec[1] = 0; vec[2] = 0; }
+    prjvec = dot3(vec, n1);
+    for (int i = 0; i < 3; i++) axis[i] *= hh;
+    prjaxis *= hh;
+    real d1 = dist0 + prjaxis + prjvec, d2 = dist0 - prjaxis + prjvec, d3 = dist0 + prjaxis - prjvec * 0.5, nv1;
+    cross3(vec1, vec, axis);
+    nv1 = norm3(vec1);
+    for (int i = 0; i < 3; i++) vec1[i] = (nv1 > 0.0 ? vec1[i] / nv1 : 0.0) * (radius * sqrt(3.0) * 0.5);
+    for (int i = 0; i < 3; i++) {
+      out[0].pos[i] = p2[i] + vec[i] + axis[i] - n1[i] * (d1 * 0.5);
+      out[1].pos[i] = p2[i] + vec[i] - axis[i] - n1[i] * (d2 * 0.5);
+      out[2].pos[i] = p2[i] + vec1[i] + axis[i] - vec[i] * 0.5 - n1[i] * (d3 * 0.5);
+      out[3].pos[i] = p2[i] - vec1[i] + axis[i] - vec[i] * 0.5 - n1[i] * (d3 * 0.5);
+    }
+    out[0].dist = d1; out[1].dist = d2; out[2].dist = d3; out[3].dist = d3;
+    for (int k = 0; k < 4; k++) { make_frame(out[k].frame, n1); out[k].id = k; }
+    return 4;
+  }
+  if (t1 == GEOM_SPHERE && t2 == GEOM_CYLINDER) { /* collision_primitive_core.py:447-515 */
+    real vec[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]}, x = dot3(vec, n2), aproj[3], pproj[3], n[3], psq;
+    for (int i = 0; i < 3; i++) { aproj[i] = n2[i] * x; pproj[i] = vec[i] - aproj[i]; }
+    psq = dot3(pproj, pproj);
+    int side = fabs(x) < s2[1], cap = psq < s2[0] * s2[0];
+    if (side && cap) { if (s2[1] - fabs(x) < s2[0] - sqrt(psq)) side = 0; else cap = 0; }
+    if (side) {
+      real tgt[3] = {p2[0] + aproj[0], p2[1] + aproj[1], p2[2] + aproj[2]};
+      c_sphere_sphere(p1, s1[0], tgt, s2[0], &out[0].dist, out[0].pos, n);
+    } else if (cap) {
+      real sg = x > 0.0 ? 1.0 : -1.0, pc[3], pn[3];
+      for (int i = 0; i < 3; i++) { pc[i] = p2[i] + sg * n2[i] * s2[1]; pn[i] = sg * n2[i]; }
+      c_plane_sphere(pn, pc, p1, s1[0], &out[0].dist, out[0].pos);
+      for (int i = 0; i < 3; i++) n[i] = -pn[i];
+    } else {
+      real inv = safe_div(1.0, sqrt(psq)), sg = x < 0.0 ? -1.0 : 1.0, corner[3];
+      for (int i = 0; i < 3; i++) corner[i] = p2[i] + n2[i] * (sg * s2[1]) + pproj[i] * (s2[0] * inv);
+      c_sphere_sphere(p1, s1[0], corner, 0.0, &out[0].dist, out[0].pos, n);
+    }
+    make_frame(out[0].frame, n);
+    out[0].id = 0;
+    return 1;
+  }
   if (t1 == GEOM_SPHERE && t2 == GEOM_SPHERE) { /* collision_primitive.py:352 */
     real n[3];
     c_sphere_sphere(p1, s1[0], p2, s2[0], &out[0].dist, out[0].pos, n);

@@ -45,4 +45,17 @@ BOX_PAIRS_XML = """
   </worldbody>
 </mujoco>"""
 
-XML = dict(SMALL_MODELS, box_pairs=BOX_PAIRS_XML)
+# every pair type of the convex (GJK / EPA) narrowphase plus the ellipsoid / cylinder primitives (collision_driver.py:43)
+CONVEX_PAIRS_XML = """
+<mujoco>
+  <worldbody>
+    <geom type="plane" size="5 5 .01" pos="0 0 -0.45"/>
+    <body pos="0 0 0"><freejoint/><geom type="ellipsoid" size=".2 .3 .15"/></body>
+    <body pos="1 0 0"><freejoint/><geom type="cylinder" size=".15 .25"/></body>
+    <body pos="0 1 0"><freejoint/><geom type="sphere" size=".18"/><geom type="ellipsoid" size=".12 .1 .3" pos=".35 0 0" margin=".01"/></body>
+    <body pos="1 1 0"><freejoint/><geom type="capsule" size=".1 .25"/><geom type="cylinder" size=".2 .1" pos="0 .4 0" euler="30 20 0"/></body>
+    <body pos="2 1 0"><freejoint/><geom type="box" size=".25 .15 .2"/></body>
+  </worldbody>
+</mujoco>"""
+
+XML = dict(SMALL_MODELS, box_pairs=BOX_PAIRS_XML, convex_pairs=CONVEX_PAIRS_XML)
