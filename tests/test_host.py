@@ -96,13 +96,21 @@ def test_put_model_rejects_unsupported_features(snippet, msg):
     mjw.put_model(mjm, device="cpu")
 
 
-def test_put_model_rejects_unimplemented_geom_pairs():
+def test_mesh_geoms_are_rejected_and_every_primitive_pair_is_accepted():
+  """Meshes / height fields need assets the MJCF-lite compiler does not load yet: rejected up front, like the reference
+  rejects what it does not implement (io.py:100-144).  All pairs of plane / sphere / capsule / ellipsoid / cylinder / box
+  have a narrowphase (primitive or GJK / EPA)."""
   xml = """<mujoco><worldbody>
-    <body><freejoint/><geom type="cylinder" size=".1 .1"/></body>
-    <body pos="1 0 0"><freejoint/><geom type="cylinder" size=".1 .1"/></body>
+    <body><freejoint/><geom type="mesh" mesh="m"/></body>
+    <body pos="1 0 0"><freejoint/><geom type="sphere" size=".1"/></body>
   </worldbody></mujoco>"""
-  with pytest.raises(NotImplementedError, match="CYLINDER"):
-    mjw.put_model(mjw.load_mjcf_string(xml), device="cpu")
+  with pytest.raises(NotImplementedError, match="mesh"):
+    mjw.load_mjcf_string(xml)
+  geoms = ['type="sphere" size=".1"', 'type="capsule" size=".1 .2"', 'type="ellipsoid" size=".1 .2 .3"', 'type="cylinder" size=".1 .2"',
+           'type="box" size=".1 .2 .3"']  # fmt: skip
+  bodies = "".join(f'<body pos="{i} 0 1"><joint type="slide"/><geom {g}/></body>' for i, g in enumerate(geoms))
+  m = mjw.put_model(mjw.load_mjcf_string(f'<mujoco><worldbody><geom type="plane" size="1 1 .1"/>{bodies}</worldbody></mujoco>'), device="cpu")
+  assert m.sizes["nxn"] == 15
 
 
 def test_device_is_mandatory_for_compute(humanoid):
