@@ -4,8 +4,9 @@ Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl refere
 import this module.  It may import the product's host tables (mujoco_warp_b200.io.host_model,
 types) to share field names and shapes; the product never imports it.
 
-Parity status: UNPINNED against MuJoCo C / Warp (neither is installable here); see the header
-of mjoracle.c and DESIGN.md.
+Parity status: PINNED to outputs of the reference itself (its unmodified sources executed here in a
+float64 numpy interpreter of Warp, golden vectors under tests/golden/); see the header of mjoracle.c
+and DESIGN.md section 4.
 """
 
 from __future__ import annotations

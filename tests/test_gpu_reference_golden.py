@@ -29,16 +29,24 @@ TOL_SOLVER_CG = 5e-2  # CG stops at `tolerance`, not at the optimum: two runs ag
 # stopped after 6 CG iterations, far from converged: the iterates depend on rounding-level linesearch ties (it pins the ORACLE's
 # iterates to the reference's in float64); on the device only the solver-independent fields are compared
 UNCONVERGED = ("humanoid_cg_iter6",)
+# GJK / EPA case: the penetration DEPTH converges to opt.ccd_tolerance (device vs reference 1.6e-6), but on smooth shapes the
+# witness direction is only determined to ~sqrt(tolerance / radius) -- a float32 EPA and a float64 EPA stop on different faces
+# of the polytope.  Measured on B200: contact_pos 4.5e-4, contact_frame 5.8e-3, efc_J 9.5e-3.  The bodies of this fixture
+# are dropped on top of each other (penetrations up to 0.3), so the solver outputs amplify those normals and are not compared.
+CASE_TOL = {"convex_pairs_collision": {"contact_pos": 2e-3, "contact_frame": 2e-2, "efc_J": 3e-2, "efc_aref": 5e-3, "efc_D": 1e-3}}
+CASE_SKIP_SOLVER = ("convex_pairs_collision",)
 FACTOR_FIELDS = ("qacc_smooth", "qLD")
 EXACT = ("efc_type", "efc_id", "contact_dim", "contact_geom")
 
 
 def tol_of(f, name):
   c = RC.CASES[name]
+  if f in CASE_TOL.get(name, {}):
+    return CASE_TOL[name][f]
   if f in EXACT:
     return 1e-12
   if f in RC.SOLVER_FIELDS or f in ("efc_force", "efc_state", "efc_Ma"):
-    if name in UNCONVERGED:
+    if name in UNCONVERGED or name in CASE_SKIP_SOLVER:
       return float("inf")
     return TOL_SOLVER_CG if name in RC.LOOSE_SOLVER_CASES else TOL_SOLVER
   if f in FACTOR_FIELDS:
