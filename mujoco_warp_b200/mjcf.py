@@ -736,7 +736,20 @@ def _finalize(root, comp, defaults, opt, bodies, joints, geoms, sites, basedir) 
   for i, g in enumerate(geoms):
     gt = _GEOM_TYPES[g.get("type", "sphere")]
     if gt in (C.GeomType.MESH, C.GeomType.HFIELD):
-      raise NotImplementedError(f"geom type {g.get('type')} requires mesh/hfield assets (not supported by mjcf lite yet)")
+      # Mesh assets are not loaded.  A mesh geom that can never collide (contype = conaffinity = 0) on a body with an explicit
+      # <inertial> contributes nothing to the step path: it is kept (geom ids stay MuJoCo's) as a massless, sizeless geom whose
+      # frame is the XML frame (MuJoCo would re-centre it on the mesh's inertial frame: only geom_xpos / geom_xmat of that
+      # visual geom differ).  Anything else needs the asset.
+      inert_ok = bodies[g["_body"]]["inertial"] is not None
+      if gt == C.GeomType.HFIELD or int(g.get("contype", 1)) != 0 or int(g.get("conaffinity", 1)) != 0 or not inert_ok:
+        raise NotImplementedError(f"geom type {g.get('type')} requires mesh/hfield assets (not supported by mjcf lite yet)")
+      m.geom_type[i] = gt
+      m.geom_contype[i] = m.geom_conaffinity[i] = 0
+      m.geom_pos[i], m.geom_quat[i] = _vec(g.get("pos"), 3, [0, 0, 0]), _orientation(g, comp)
+      for key, arr, cast in (("group", m.geom_group, int), ("condim", m.geom_condim, int), ("priority", m.geom_priority, int)):
+        if key in g:
+          arr[i] = cast(g[key])
+      continue
     m.geom_type[i] = gt
     size = np.zeros(3)
     sv = _vec(g.get("size"))

@@ -70,6 +70,16 @@ def _box_pair_states(mjm, nworld, seed):
   return qpos, np.zeros((nworld, mjm.nv)), np.zeros((nworld, mjm.nu))
 
 
+def _panda_states(mjm, nworld, seed):
+  """Joint angles a little beyond the joint ranges (active limits), velocities, controls beyond ctrlrange (clamping)."""
+  rng = np.random.default_rng(seed)
+  lo, hi = np.asarray(mjm.jnt_range)[:, 0], np.asarray(mjm.jnt_range)[:, 1]
+  qpos = lo - 0.03 * (hi - lo) + rng.uniform(0, 1, (nworld, mjm.nq)) * 1.06 * (hi - lo)
+  clo, chi = np.asarray(mjm.actuator_ctrlrange)[:, 0], np.asarray(mjm.actuator_ctrlrange)[:, 1]
+  ctrl = clo - 0.1 * (chi - clo) + rng.uniform(0, 1, (nworld, mjm.nu)) * 1.2 * (chi - clo)
+  return qpos, rng.uniform(-0.5, 0.5, (nworld, mjm.nv)), ctrl
+
+
 # case name -> (model key, state fn, nworld, seed, opt overrides, mode, nstep, nconmax, njmax)
 CASES = {
   "humanoid_forward": dict(model="humanoid", nworld=4, seed=3, sink=0.05, mode="forward"),
@@ -94,6 +104,10 @@ CASES = {
   "no_constraints_no_actuators": dict(model="no_constraints_no_actuators", nworld=2, seed=5, mode="step", nstep=3, nconmax=32),
   # box-box goes through the primitive only with NATIVECCD disabled (collision_driver.py:736); margins need it too (io.py:389)
   "box_pairs_collision": dict(model="box_pairs", nworld=24, seed=3, mode="forward", nconmax=32, njmax=160, states="box_pairs", disable=["NATIVECCD"]),
+  # benchmarks/franka_emika_panda (BASELINE config 3): implicitfast, joint equality, position / general actuators with force
+  # and ctrl clamps, active joint limits, plane-box and plane-capsule contacts; mesh geoms are visual-only (contype 0)
+  "panda_step3": dict(model="panda", nworld=10, seed=50, mode="step", nstep=3, nconmax=8, njmax=40, states="panda"),
+  "panda_deep_forward": dict(model="panda", nworld=10, seed=43, mode="forward", nconmax=8, njmax=80, states="panda"),
   "convex_pairs_collision": dict(model="convex_pairs", nworld=12, seed=4, mode="forward", nconmax=48, njmax=200, states="box_pairs"),
 }
 
@@ -101,6 +115,8 @@ CASES = {
 def load_model(key):
   if key == "humanoid":
     return mjw.load_mjcf(H.HUMANOID)
+  if key == "panda":
+    return mjw.load_mjcf(os.path.join(ROOT, "benchmarks", "franka_emika_panda", "scene.xml"))
   return mjw.load_mjcf_string(TM.XML[key])
 
 
@@ -114,6 +130,8 @@ def case_inputs(name):
   kind = c.get("states", "humanoid" if c["model"] == "humanoid" else "small")
   if kind == "humanoid":
     qpos, qvel, ctrl = _states(mjm, c["nworld"], c["seed"], c.get("sink", 0.0))
+  elif kind == "panda":
+    qpos, qvel, ctrl = _panda_states(mjm, c["nworld"], c["seed"])
   elif kind == "box_pairs":
     qpos, qvel, ctrl = _box_pair_states(mjm, c["nworld"], c["seed"])
   else:
