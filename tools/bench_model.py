@@ -1,0 +1,60 @@
+"""Device-resident env-steps/s of `mjw.step` on a secondary benchmark config (not the bench.py headline line).
+
+  python tools/bench_model.py panda [nworld] [nconmax] [njmax] [nstep]
+
+panda: benchmarks/franka_emika_panda/scene.xml (reference benchmarks/config.txt:22: nworld 32768, nconmax 1, njmax 5;
+BASELINE.json config 3 quotes nworld 8192).  Initial state qpos0, controls = OU noise around 0 like the benchmark loop
+(reference benchmark.py:42), CUDA-graph step, CUDA-event timing after warm-up.
+"""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+import mujoco_warp_b200 as mjw
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+MODELS = {"panda": ("benchmarks/franka_emika_panda/scene.xml", 32768, 1, 5), "humanoid": ("benchmarks/humanoid/humanoid.xml", 8192, 24, 64)}
+
+
+def main():
+  name = sys.argv[1] if len(sys.argv) > 1 else "panda"
+  path, nworld, nconmax, njmax = MODELS[name]
+  args = [int(a) for a in sys.argv[2:]]
+  nworld, nconmax, njmax = (args + [nworld, nconmax, njmax][len(args):])[:3] if len(args) < 3 else args[:3]
+  nstep = args[3] if len(args) > 3 else 200
+  mjm = mjw.load_mjcf(os.path.join(ROOT, path))
+  m = mjw.put_model(mjm)
+  d = mjw.make_data(mjm, nworld=nworld, nconmax=nconmax, njmax=njmax)
+  if mjm.nkey:
+    d.qpos.copy_(torch.tensor(mjm.key_qpos[0], dtype=torch.float32, device="cuda").expand(nworld, -1))
+  for i in range(20):
+    mjw.ctrl_noise(m, d, i)
+    mjw.step(m, d)
+  torch.cuda.synchronize()
+  g = torch.cuda.CUDAGraph()
+  s = torch.cuda.Stream()
+  with torch.cuda.stream(s):
+    mjw.step(m, d)
+    with torch.cuda.graph(g, stream=s):
+      mjw.step(m, d)
+  torch.cuda.synchronize()
+  e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+  for _ in range(10):
+    g.replay()
+  e0.record()
+  for i in range(nstep):
+    g.replay()
+  e1.record()
+  e1.synchronize()
+  ms = e0.elapsed_time(e1) / nstep
+  out = {"model": path, "nworld": nworld, "nconmax": nconmax, "njmax": njmax, "steps": nstep, "ms_per_step": ms,
+         "env_steps_per_s": nworld / ms * 1e3, "mean_nefc": float(d.nefc.float().mean()), "mean_niter": float(d.solver_niter.float().mean()),
+         "nan_worlds": int(torch.isnan(d.qpos).any(dim=1).sum()), "status_bits": int(d.status.max())}  # fmt: skip
+  print(json.dumps(out))
+
+
+if __name__ == "__main__":
+  main()
