@@ -314,6 +314,58 @@ def _geom_bounds(gtype, size):
   raise NotImplementedError(f"geom type {gtype} bounds")
 
 
+# ----------------------------------------------------------------------------- mesh assets
+def _load_mesh_vertices(path):
+  """Vertex positions of a binary / ASCII STL or an OBJ file (faces are not needed: collision uses the convex hull)."""
+  ext = os.path.splitext(path)[1].lower()
+  with open(path, "rb") as f:
+    raw = f.read()
+  if ext == ".obj":
+    rows = [ln.split()[1:4] for ln in raw.decode("utf-8", "replace").splitlines() if ln.startswith("v ")]
+    return np.array(rows, dtype=np.float64).reshape(-1, 3)
+  if ext == ".stl":
+    ntri = int(np.frombuffer(raw[80:84], dtype="<u4")[0]) if len(raw) >= 84 else 0
+    if len(raw) == 84 + 50 * ntri:  # binary: 80-byte header, count, 50-byte records (normal, 3 vertices, attribute)
+      rec = np.frombuffer(raw[84:], dtype=np.dtype([("n", "<f4", 3), ("v", "<f4", 9), ("a", "<u2")]))
+      return rec["v"].reshape(-1, 3).astype(np.float64)
+    rows = [ln.split()[1:4] for ln in raw.decode("utf-8", "replace").splitlines() if ln.strip().startswith("vertex")]
+    return np.array(rows, dtype=np.float64).reshape(-1, 3)
+  raise NotImplementedError(f"mesh file format {ext}")
+
+
+def _convex_hull_vertices(v):
+  """Vertices of the convex hull (in first-appearance order).  MuJoCo collides meshes through their convex hulls; the support
+  function over the hull vertices equals the support function over all vertices."""
+  v = np.asarray(v, dtype=np.float64).reshape(-1, 3)
+  _, first = np.unique(np.round(v, 12), axis=0, return_index=True)
+  v = v[np.sort(first)]
+  if len(v) < 4:
+    return v
+  try:
+    from scipy.spatial import ConvexHull
+
+    return v[np.sort(ConvexHull(v).vertices)]
+  except Exception:  # degenerate (flat) point sets: keep all points
+    return v
+
+
+def _parse_meshes(root, comp, defaults, basedir):
+  """name -> hull vertices (scaled, in the mesh file's frame) for every <asset><mesh>; None when the file is absent."""
+  meshes = {}
+  for asset in root.findall("asset"):
+    for e in asset.findall("mesh"):
+      a = _resolve(defaults, e, None)
+      name = a.get("name") or os.path.splitext(os.path.basename(a.get("file", "")))[0]
+      scale = _vec(a.get("scale"), 3, [1, 1, 1])
+      if "vertex" in a:
+        verts = _vec(a["vertex"]).reshape(-1, 3)
+      else:
+        path = os.path.join(basedir, comp.meshdir, a.get("file", ""))
+        verts = _load_mesh_vertices(path) if os.path.isfile(path) else None
+      meshes[name] = None if verts is None else _convex_hull_vertices(verts * scale)
+  return meshes
+
+
 # ----------------------------------------------------------------------------- parse tree
 class _Compiler:
   def __init__(self):
@@ -733,22 +785,41 @@ def _finalize(root, comp, defaults, opt, bodies, joints, geoms, sites, basedir) 
   m.geom_aabb = np.zeros((ngeom, 6))
   geom_mass = np.zeros(ngeom)
   geom_inertia = np.zeros((ngeom, 3))
+  meshes = _parse_meshes(root, comp, defaults, basedir)
+  mesh_ids = {}  # only meshes referenced by a geom enter the model, in order of first use
   for i, g in enumerate(geoms):
-    gt = _GEOM_TYPES[g.get("type", "sphere")]
-    if gt in (C.GeomType.MESH, C.GeomType.HFIELD):
-      # Mesh assets are not loaded.  A mesh geom that can never collide (contype = conaffinity = 0) on a body with an explicit
-      # <inertial> contributes nothing to the step path: it is kept (geom ids stay MuJoCo's) as a massless, sizeless geom whose
-      # frame is the XML frame (MuJoCo would re-centre it on the mesh's inertial frame: only geom_xpos / geom_xmat of that
-      # visual geom differ).  Anything else needs the asset.
-      inert_ok = bodies[g["_body"]]["inertial"] is not None
-      if gt == C.GeomType.HFIELD or int(g.get("contype", 1)) != 0 or int(g.get("conaffinity", 1)) != 0 or not inert_ok:
-        raise NotImplementedError(f"geom type {g.get('type')} requires mesh/hfield assets (not supported by mjcf lite yet)")
+    gt = _GEOM_TYPES[g.get("type", "mesh" if "mesh" in g else "sphere")]
+    if gt == C.GeomType.HFIELD:
+      raise NotImplementedError("geom type hfield requires height-field assets (not supported by mjcf lite yet)")
+    if gt == C.GeomType.MESH:
+      # Collision uses the convex hull of the asset's vertices, kept in the mesh file's frame: MuJoCo re-centres a mesh on its
+      # inertial frame and folds that transform into geom_pos / geom_quat -- the world-space shape is the same, only the
+      # reported geom_xpos / geom_xmat of mesh geoms differ.  Mesh mass properties are not computed: the body needs <inertial>.
+      verts = meshes.get(g.get("mesh"))
+      collides = int(g.get("contype", 1)) != 0 or int(g.get("conaffinity", 1)) != 0
+      if bodies[g["_body"]]["inertial"] is None and g["_body"] != 0:
+        raise NotImplementedError("mesh geoms need an explicit <inertial> on their body (mesh mass properties are not computed)")
+      if verts is None and collides:
+        raise NotImplementedError(f"mesh asset '{g.get('mesh')}' of a colliding geom is missing (mesh files are loaded from meshdir)")
       m.geom_type[i] = gt
-      m.geom_contype[i] = m.geom_conaffinity[i] = 0
       m.geom_pos[i], m.geom_quat[i] = _vec(g.get("pos"), 3, [0, 0, 0]), _orientation(g, comp)
-      for key, arr, cast in (("group", m.geom_group, int), ("condim", m.geom_condim, int), ("priority", m.geom_priority, int)):
+      for key, arr, cast in (("contype", m.geom_contype, int), ("conaffinity", m.geom_conaffinity, int), ("condim", m.geom_condim, int),
+                             ("priority", m.geom_priority, int), ("group", m.geom_group, int), ("solmix", m.geom_solmix, float),
+                             ("margin", m.geom_margin, float), ("gap", m.geom_gap, float)):  # fmt: skip
         if key in g:
           arr[i] = cast(g[key])
+      for key, arr in (("friction", m.geom_friction), ("solref", m.geom_solref), ("solimp", m.geom_solimp)):
+        if key in g:
+          v = _vec(g[key])
+          arr[i, : v.size] = v
+      if verts is not None:
+        if g.get("mesh") not in mesh_ids:
+          mesh_ids[g.get("mesh")] = len(mesh_ids)
+        m.geom_dataid[i] = mesh_ids[g.get("mesh")]
+        lo, hi = verts.min(axis=0), verts.max(axis=0)
+        m.geom_size[i] = 0.5 * (hi - lo)
+        m.geom_rbound[i] = float(np.linalg.norm(verts, axis=1).max())
+        m.geom_aabb[i] = np.concatenate((0.5 * (lo + hi), 0.5 * (hi - lo)))
       continue
     m.geom_type[i] = gt
     size = np.zeros(3)
@@ -791,6 +862,19 @@ def _finalize(root, comp, defaults, opt, bodies, joints, geoms, sites, basedir) 
       geom_mass[i] = mass
       geom_inertia[i] = inert * dens
     m.geom_rbound[i], m.geom_aabb[i] = _geom_bounds(gt, size)
+
+  # ---------------- mesh tables (convex hull vertices; no hill-climbing graph: mesh_graphadr = -1 selects the exhaustive support
+  # search, reference collision_gjk.py:142)
+  names = sorted(mesh_ids, key=mesh_ids.get)
+  m.nmesh = len(names)
+  m.mesh_names = names
+  m.mesh_vertnum = np.array([len(meshes[n]) for n in names], dtype=i32)
+  m.mesh_vertadr = np.concatenate(([0], np.cumsum(m.mesh_vertnum)[:-1])).astype(i32) if names else np.zeros(0, dtype=i32)
+  m.mesh_vert = np.concatenate([meshes[n] for n in names]).reshape(-1, 3) if names else np.zeros((0, 3))
+  m.nmeshvert = int(m.mesh_vert.shape[0])
+  m.mesh_graphadr = np.full(m.nmesh, -1, dtype=i32)
+  m.mesh_polyadr = np.full(m.nmesh, -1, dtype=i32)
+  m.nmeshgraph = 0
 
   # ---------------- body inertial properties
   m.body_mass = np.zeros(nbody)
@@ -1036,7 +1120,7 @@ def _finalize_constraints(m, root, comp, defaults):
       m.pair_friction[i, : v.size] = v
 
   # absent features (sizes the device model expects)
-  m.ntendon = m.nflex = m.nsensor = m.nsensordata = m.nmesh = m.nhfield = m.ncam = m.nlight = 0
+  m.ntendon = m.nflex = m.nsensor = m.nsensordata = m.nhfield = m.ncam = m.nlight = 0
   m.nwrap = m.nJten = m.nflexvert = m.nflexedge = m.nflexelem = 0
   m.ngravcomp = int((m.body_gravcomp != 0).sum())
 
