@@ -28,7 +28,8 @@
   X(neqjnt)     /* joint equalities (reference io.py:447) */ \
   X(nJmom)      /* actuator moment non-zeros */ \
   X(nmaxcondim) X(nmaxpyramid) X(ngravcomp) X(is_sparse) X(nM) X(ntree) \
-  X(ngeompair)  /* ngeom (ngeom - 1) / 2: entries of the upper-triangular pair table (SAP broadphase) */
+  X(ngeompair)  /* ngeom (ngeom - 1) / 2: entries of the upper-triangular pair table (SAP broadphase) */ \
+  X(nmesh) X(nmeshvert) /* convex-hull vertex tables of mesh geoms (reference types.py Model.mesh_vert*) */
 
 /* ---- model int arrays ---------------------------------------------------------------------- */
 #define MJB_MODEL_INT_FIELDS(X) \
@@ -47,7 +48,8 @@
   X(actuator_trntype) X(actuator_trnid) X(actuator_dyntype) X(actuator_gaintype) \
   X(actuator_biastype) X(actuator_actadr) X(actuator_actnum) X(actuator_ctrllimited) \
   X(actuator_forcelimited) X(actuator_actlimited) X(actuator_actearly) \
-  X(eq_type) X(eq_obj1id) X(eq_obj2id) X(eq_jnt_adr)
+  X(eq_type) X(eq_obj1id) X(eq_obj2id) X(eq_jnt_adr) \
+  X(geom_dataid) X(mesh_vertadr) X(mesh_vertnum)
 
 /* ---- model real arrays --------------------------------------------------------------------- */
 #define MJB_MODEL_REAL_FIELDS(X) \
@@ -63,7 +65,8 @@
   X(pair_solref) X(pair_solreffriction) X(pair_solimp) X(pair_margin) X(pair_gap) X(pair_friction) \
   X(actuator_dynprm) X(actuator_gainprm) X(actuator_biasprm) X(actuator_ctrlrange) \
   X(actuator_forcerange) X(actuator_actrange) X(actuator_gear) \
-  X(eq_solref) X(eq_solimp) X(eq_data)
+  X(eq_solref) X(eq_solimp) X(eq_data) \
+  X(mesh_vert)
 
 /* ---- options: re-read on every call (reference users mutate m.opt.* after put_model) -------- */
 #define MJB_OPT_INT_FIELDS(X) \

@@ -152,7 +152,7 @@ extern "C" int mjb_model_create(const int* sizes, int nsizes, const void* blob, 
       const int ta = gtype[pair[2 * p]], tb = gtype[pair[2 * p + 1]];
       const int t1 = ta < tb ? ta : tb, t2 = ta < tb ? tb : ta;
       if (t2 == GEOM_BOX && t1 != GEOM_PLANE) m->col_feat |= COLF_BOX;  // sphere-box, capsule-box, box-box
-      if (t1 == GEOM_ELLIPSOID || t1 == GEOM_CYLINDER || t2 == GEOM_ELLIPSOID || t2 == GEOM_CYLINDER) m->col_feat |= COLF_CONVEX;
+      if (t1 == GEOM_ELLIPSOID || t1 == GEOM_CYLINDER || t1 == GEOM_MESH || t2 == GEOM_ELLIPSOID || t2 == GEOM_CYLINDER || t2 == GEOM_MESH) m->col_feat |= COLF_CONVEX;
     }
   }
   *out = m;

@@ -1,9 +1,10 @@
-/* mjb_ccd_core.h -- convex narrowphase: GJK distance + EPA penetration for sphere / capsule / ellipsoid / cylinder / box.
+/* mjb_ccd_core.h -- convex narrowphase: GJK distance + EPA penetration for sphere / capsule / ellipsoid / cylinder / box /
+ * convex mesh (hull vertices, exhaustive support search).
  *
  * Restates reference mujoco_warp/_src/collision_gjk.py: support :98, _attach_face :195, _epa_support :217, _subdistance
  * :253 (_S3D :319, _S2D :395, _S1D :540), gjk :563, _polytope2 :937, _polytope3 :1027, _polytope4 :1115, _epa :1202,
  * _epa_witness :863, _inflate :2153, ccd :2200 (itself a restatement of MuJoCo C engine_collision_gjk.c).
- * Mesh and height-field support functions and the multi-contact face clipping (:1930) are not included.
+ * The hill-climbing mesh support (mesh_graph), height fields and the multi-contact face clipping (:1930) are not included.
  *
  * Plain C (no C++), compiled TWICE from this one source: in float32 as __device__ code by mjb_collision.cuh (the product
  * path) and in float64 by oracle/mjoracle.c (the CPU checker).  Because the two builds share this text, device-vs-oracle
@@ -21,6 +22,9 @@
 #define CCD_FN_NOINLINE CCD_FN
 #endif
 typedef CCD_REAL creal;
+#ifndef CCD_VERT_REAL
+#define CCD_VERT_REAL CCD_REAL /* element type of the mesh vertex table */
+#endif
 #define CR(x) ((creal)(x))
 
 #define CCD_GEOM_SPHERE 2
@@ -28,6 +32,7 @@ typedef CCD_REAL creal;
 #define CCD_GEOM_ELLIPSOID 4
 #define CCD_GEOM_CYLINDER 5
 #define CCD_GEOM_BOX 6
+#define CCD_GEOM_MESH 7
 
 #define CCD_FLOAT_MAX CR(1e30)
 #define CCD_MINVAL CR(1e-15)
@@ -40,6 +45,8 @@ typedef CCD_REAL creal;
 typedef struct {
   creal pos[3], rot[9], size[3], margin;
   int type;
+  const CCD_VERT_REAL* vert; /* mesh: hull vertices in the geom frame (the model's mesh_vert + 3 * mesh_vertadr), nvert of them */
+  int nvert;
 } CcdGeom;
 
 typedef struct {
@@ -83,9 +90,11 @@ CCD_FN void ccd_rot_t(creal* r, const creal* m, const creal* v) {
   r[0] = x; r[1] = y; r[2] = z;
 }
 
-/* collision_gjk.py:98 support: furthest point of a geom along `dir`; returns the vertex index (boxes) or -1 */
-CCD_FN_NOINLINE int ccd_support(const CcdGeom* g, const creal* dir, creal* point) {
-  int vertex_index = -1;
+/* collision_gjk.py:98 support: furthest point of a geom along `dir`; returns the vertex index (boxes, meshes) or -1.
+ * *cached: in = the mesh vertex found by the previous call of this search (geom.index, -1 = none), out = this call's. */
+CCD_FN_NOINLINE int ccd_support(const CcdGeom* g, const creal* dir, creal* point, int* cached) {
+  int vertex_index = -1, cache_in = *cached;
+  *cached = -1;
   if (g->type == CCD_GEOM_SPHERE) {
     creal s = g->size[0] + CR(0.5) * g->margin;
     for (int i = 0; i < 3; i++) point[i] = g->pos[i] + s * dir[i];
@@ -112,6 +121,20 @@ CCD_FN_NOINLINE int ccd_support(const CcdGeom* g, const creal* dir, creal* point
       res[0] = ld[0] * scl; res[1] = ld[1] * scl;
     }
     res[2] = ccd_sign(ld[2]) * g->size[1];
+  } else if (g->type == CCD_GEOM_MESH) { /* :140-154 exhaustive search (graphadr == -1); ties keep the cached vertex, then the first */
+    creal max_dist = CR(-1e30);
+    int best = -1;
+    if (cache_in > -1) {
+      best = cache_in;
+      max_dist = (creal)g->vert[3 * cache_in] * ld[0] + (creal)g->vert[3 * cache_in + 1] * ld[1] + (creal)g->vert[3 * cache_in + 2] * ld[2];
+    }
+    for (int i = 0; i < g->nvert; i++) {
+      creal d = (creal)g->vert[3 * i] * ld[0] + (creal)g->vert[3 * i + 1] * ld[1] + (creal)g->vert[3 * i + 2] * ld[2];
+      if (d > max_dist) { max_dist = d; best = i; }
+    }
+    if (best > -1) { res[0] = (creal)g->vert[3 * best]; res[1] = (creal)g->vert[3 * best + 1]; res[2] = (creal)g->vert[3 * best + 2]; }
+    *cached = best;
+    vertex_index = best;
   }
   ccd_rot(point, g->rot, res);
   for (int i = 0; i < 3; i++) point[i] += g->pos[i];
@@ -275,14 +298,15 @@ CCD_FN_NOINLINE void ccd_gjk(CcdGjk* res, creal tolerance, int iterations, const
     res->index1[k] = res->index2[k] = 0;
     for (int i = 0; i < 3; i++) res->simplex[k][i] = res->simplex1[k][i] = res->simplex2[k][i] = CR(0.0);
   }
+  int cache1 = -1, cache2 = -1; /* geom.index: lives in gjk's by-value copies of the geoms (:602, :608) */
   ccd_sub(xk, x1_0, x2_0);
   for (int it = 0; it < iterations; it++) {
     creal xnorm = ccd_dot(xk, xk);
     if (xnorm < tol2 || CCD_FABS(xnorm_old - xnorm) < tol2) break;
     xnorm_old = xnorm;
     creal inv = CR(1.0) / CCD_SQRT(xnorm), dneg[3] = {xk[0] * inv, xk[1] * inv, xk[2] * inv}, dpos[3] = {-dneg[0], -dneg[1], -dneg[2]};
-    res->index1[n] = ccd_support(g1, dpos, res->simplex1[n]);
-    res->index2[n] = ccd_support(g2, dneg, res->simplex2[n]);
+    res->index1[n] = ccd_support(g1, dpos, res->simplex1[n], &cache1);
+    res->index2[n] = ccd_support(g2, dneg, res->simplex2[n], &cache2);
     ccd_sub(res->simplex[n], res->simplex1[n], res->simplex2[n]);
     if (cutoff == CR(0.0)) {
       if (ccd_dot(xk, res->simplex[n]) > CR(0.0)) { res->dim = 0; res->dist = CCD_FLOAT_MAX; return; }
@@ -371,10 +395,10 @@ CCD_FN_NOINLINE creal ccd_attach_face(CcdPolytope* pt, int idx, int v1, int v2, 
 }
 
 /* :217 */
-CCD_FN void ccd_epa_support(CcdPolytope* pt, int idx, const CcdGeom* g1, const CcdGeom* g2, const creal* dir) {
+CCD_FN void ccd_epa_support(CcdPolytope* pt, int idx, const CcdGeom* g1, const CcdGeom* g2, const creal* dir, int* cache1, int* cache2) {
   creal nd[3] = {-dir[0], -dir[1], -dir[2]};
-  pt->vert_index[2 * idx] = ccd_support(g1, dir, pt->vert[2 * idx]);
-  pt->vert_index[2 * idx + 1] = ccd_support(g2, nd, pt->vert[2 * idx + 1]);
+  pt->vert_index[2 * idx] = ccd_support(g1, dir, pt->vert[2 * idx], cache1);
+  pt->vert_index[2 * idx + 1] = ccd_support(g2, nd, pt->vert[2 * idx + 1], cache2);
 }
 
 /* :762 */
@@ -434,9 +458,9 @@ CCD_FN_NOINLINE void ccd_polytope2(CcdPolytope* pt, CcdGjk* r, const CcdGeom* g1
   ccd_load_simplex(pt, r, 2);
   creal n1 = ccd_norm(d1), n2 = ccd_norm(d2), n3 = ccd_norm(d3);
   for (int i = 0; i < 3; i++) { d1[i] /= n1; d2[i] /= n2; d3[i] /= n3; }
-  ccd_epa_support(pt, 2, g1, g2, d1);
-  ccd_epa_support(pt, 3, g1, g2, d2);
-  ccd_epa_support(pt, 4, g1, g2, d3);
+  { int c1 = -1, c2 = -1; ccd_epa_support(pt, 2, g1, g2, d1, &c1, &c2); }
+  { int c1 = -1, c2 = -1; ccd_epa_support(pt, 3, g1, g2, d2, &c1, &c2); }
+  { int c1 = -1, c2 = -1; ccd_epa_support(pt, 4, g1, g2, d3, &c1, &c2); }
   const int f[6][3] = {{0, 2, 3}, {0, 4, 2}, {0, 3, 4}, {1, 3, 2}, {1, 2, 4}, {1, 4, 3}};
   for (int k = 0; k < 6; k++) {
     if (ccd_attach_face(pt, k, f[k][0], f[k][1], f[k][2]) < CCD_MIN_DIST) {
@@ -459,8 +483,8 @@ CCD_FN_NOINLINE void ccd_polytope3(CcdPolytope* pt, const CcdGjk* r, const CcdGe
   if (ccd_norm(n) < CCD_MINVAL) { pt->status = 2; return; }
   ccd_load_simplex(pt, r, 3);
   nn[0] = -n[0]; nn[1] = -n[1]; nn[2] = -n[2];
-  ccd_epa_support(pt, 3, g1, g2, nn);
-  ccd_epa_support(pt, 4, g1, g2, n);
+  { int c1 = -1, c2 = -1; ccd_epa_support(pt, 3, g1, g2, nn, &c1, &c2); }
+  { int c1 = -1, c2 = -1; ccd_epa_support(pt, 4, g1, g2, n, &c1, &c2); }
   ccd_sub(v4, pt->vert[6], pt->vert[7]);
   ccd_sub(v5, pt->vert[8], pt->vert[9]);
   if (ccd_tri_point_intersect(v1, v2, v3, v4)) { pt->status = 3; return; }
@@ -507,7 +531,7 @@ CCD_FN int ccd_add_edge(CcdPolytope* pt, int e1, int e2) {
 CCD_FN_NOINLINE int ccd_epa(creal tolerance, int iterations, CcdPolytope* pt, const CcdGeom* g1, const CcdGeom* g2, int is_discrete, creal* dist,
                    creal* x1, creal* x2) {
   creal upper = CCD_FLOAT_MAX, upper2 = CCD_FLOAT_MAX, epsilon = is_discrete ? CR(1e-15) : tolerance;
-  int idx = -1, pidx = -1, nvalid = pt->nface;
+  int idx = -1, pidx = -1, nvalid = pt->nface, cache1 = -1, cache2 = -1;
   if (iterations > 1000) iterations = 1000;
   for (int it = 0; it < iterations; it++) {
     pidx = idx;
@@ -519,7 +543,7 @@ CCD_FN_NOINLINE int ccd_epa(creal tolerance, int iterations, CcdPolytope* pt, co
     if (lower2 <= CR(0.0)) break;
     creal lower = CCD_SQRT(lower2), dir[3] = {pt->face_pr[idx][0] / lower, pt->face_pr[idx][1] / lower, pt->face_pr[idx][2] / lower}, w[3];
     int wi = pt->nvert;
-    ccd_epa_support(pt, wi, g1, g2, dir);
+    ccd_epa_support(pt, wi, g1, g2, dir, &cache1, &cache2); /* :1248-1251: geom.index follows the last support */
     ccd_sub(w, pt->vert[2 * wi], pt->vert[2 * wi + 1]);
     pt->nvert++;
     creal upper_k = ccd_dot(dir, w);
@@ -587,7 +611,8 @@ CCD_FN_NOINLINE int ccd_epa(creal tolerance, int iterations, CcdPolytope* pt, co
 CCD_FN_NOINLINE int ccd_run(creal tolerance, creal cutoff, int gjk_iterations, int epa_iterations, CcdGeom g1, CcdGeom g2, CcdPolytope* pt,
                    CcdGjk* res, creal* dist, creal* x1, creal* x2) {
   creal full1 = CR(0.0), full2 = CR(0.0), size1 = CR(0.0), size2 = CR(0.0), x_1[3], x_2[3];
-  int is_discrete = (g1.type == CCD_GEOM_BOX && g2.type == CCD_GEOM_BOX) && (g1.margin == CR(0.0) && g2.margin == CR(0.0));
+  int is_discrete = ((g1.type == CCD_GEOM_BOX || g1.type == CCD_GEOM_MESH) && (g2.type == CCD_GEOM_BOX || g2.type == CCD_GEOM_MESH)) &&
+                    (g1.margin == CR(0.0) && g2.margin == CR(0.0)); /* :91 _discrete_geoms */
   ccd_copy(x_1, g1.pos); ccd_copy(x_2, g2.pos);
   if (g1.type == CCD_GEOM_SPHERE || g1.type == CCD_GEOM_CAPSULE) {
     size1 = g1.size[0]; full1 = size1 + CR(0.5) * g1.margin; g1.margin = CR(0.0); g1.size[0] = CR(0.0);

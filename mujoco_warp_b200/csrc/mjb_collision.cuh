@@ -39,12 +39,13 @@ __device__ __forceinline__ bool is_convex_pair(int t1, int t2) {
   if (t1 == GEOM_CYLINDER) return t2 == GEOM_CYLINDER || t2 == GEOM_BOX;
   return false;
 }
+__device__ __forceinline__ bool is_ccd_pair(int t1, int t2) { return (t2 == GEOM_MESH && t1 >= GEOM_SPHERE) || is_convex_pair(t1, t2); }
 
 // collision_convex.py:712 eval_ccd_write_contact for one pair (single contact, no collision sensor): returns the number of
 // contacts (0 / 1); dist is the surface distance, pos the midpoint of the witness points, nrm = x1 - x2 (unnormalised).
-__device__ __noinline__ int c_ccd_pair(const float* p1, const float* r1, const float* s1, int t1, const float* p2, const float* r2,
-                                       const float* s2, int t2, float margin, float tolerance, int iterations, float* dist, float* pos,
-                                       float* nrm) {
+__device__ __noinline__ int c_ccd_pair(const float* p1, const float* r1, const float* s1, int t1, const float* v1, int nv1, const float* p2,
+                                       const float* r2, const float* s2, int t2, const float* v2, int nv2, float margin, float tolerance,
+                                       int iterations, float* dist, float* pos, float* nrm) {
   CcdGeom g1, g2;
   CcdPolytope pt;  // ~5 kB of local memory per thread
   CcdGjk res;
@@ -55,6 +56,8 @@ __device__ __noinline__ int c_ccd_pair(const float* p1, const float* r1, const f
   g1.margin = g2.margin = margin;
   g1.type = t1;
   g2.type = t2;
+  g1.vert = v1; g1.nvert = nv1;
+  g2.vert = v2; g2.nvert = nv2;
   if (iterations > CCD_MAX_ITER) iterations = CCD_MAX_ITER;
   float d, x1[3], x2[3];
   const int nc = ccd_run(tolerance, 0.f, iterations, iterations, g1, g2, &pt, &res, &d, x1, x2);
@@ -63,6 +66,67 @@ __device__ __noinline__ int c_ccd_pair(const float* p1, const float* r1, const f
 #pragma unroll
   for (int i = 0; i < 3; i++) { pos[i] = 0.5f * (x1[i] + x2[i]); nrm[i] = x1[i] - x2[i]; }
   return 1;
+}
+
+// collision_primitive.py:52-277 plane_convex, exhaustive branch (meshes carry no hill-climbing graph here): up to 4 contacts at the
+// deepest vertex a, the in-threshold vertex b furthest from a, c furthest from the line ab, d furthest from the edges ac / bc.
+__device__ __noinline__ int c_plane_mesh(const float* p1, const float* n1, const float* p2, const float* r2, const float* vert, int nvert,
+                                         float* dist, float* pos) {
+  const float HUGE_V = 1e6f;
+  float pl[3], n[3];
+  const float dp[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    pl[i] = r2[i] * dp[0] + r2[3 + i] * dp[1] + r2[6 + i] * dp[2];
+    n[i] = r2[i] * n1[0] + r2[3 + i] * n1[1] + r2[6 + i] * n1[2];
+  }
+  int idx[4] = {-1, -1, -1, -1};
+  float max_support = -HUGE_V, a[3] = {0.f, 0.f, 0.f}, b[3] = {0.f, 0.f, 0.f}, c[3] = {0.f, 0.f, 0.f};
+  auto support = [&](int i) {
+    return (pl[0] - vert[3 * i]) * n[0] + (pl[1] - vert[3 * i + 1]) * n[1] + (pl[2] - vert[3 * i + 2]) * n[2];
+  };
+    for (int i = 0; i < nvert; i++) {
+    const float sp = support(i);
+    if (sp > max_support) { max_support = sp; idx[0] = i; a[0] = vert[3 * i]; a[1] = vert[3 * i + 1]; a[2] = vert[3 * i + 2]; }
+  }
+  if (max_support < 0.f) return 0;
+  const float threshold = max_support - 1e-3f;
+  float bd = -HUGE_V, cd = -HUGE_V, dd = -HUGE_V;
+  for (int i = 0; i < nvert; i++) {
+    const float mask = support(i) > threshold ? 0.f : -HUGE_V;
+    const float t0 = a[0] - vert[3 * i], t1 = a[1] - vert[3 * i + 1], t2 = a[2] - vert[3 * i + 2];
+    const float d = t0 * t0 + t1 * t1 + t2 * t2 + mask;
+    if (d > bd) { idx[1] = i; bd = d; b[0] = vert[3 * i]; b[1] = vert[3 * i + 1]; b[2] = vert[3 * i + 2]; }
+  }
+  const V3 nn{n[0], n[1], n[2]};
+  const V3 ab = cross(nn, V3{a[0] - b[0], a[1] - b[1], a[2] - b[2]});
+  for (int i = 0; i < nvert; i++) {
+    const float mask = support(i) > threshold ? 0.f : -HUGE_V;
+    const V3 ap{a[0] - vert[3 * i], a[1] - vert[3 * i + 1], a[2] - vert[3 * i + 2]};
+    const float d = fabsf(dot(ap, ab)) + mask;
+    if (d > cd) { idx[2] = i; cd = d; c[0] = vert[3 * i]; c[1] = vert[3 * i + 1]; c[2] = vert[3 * i + 2]; }
+  }
+  const V3 ac = cross(nn, V3{a[0] - c[0], a[1] - c[1], a[2] - c[2]}), bc = cross(nn, V3{b[0] - c[0], b[1] - c[1], b[2] - c[2]});
+  for (int i = 0; i < nvert; i++) {
+    const float mask = support(i) > threshold ? 0.f : -HUGE_V;
+    const V3 ap{a[0] - vert[3 * i], a[1] - vert[3 * i + 1], a[2] - vert[3 * i + 2]};
+    const V3 bp{b[0] - vert[3 * i], b[1] - vert[3 * i + 1], b[2] - vert[3 * i + 2]};
+    const float d = (fabsf(dot(ap, ac)) + mask) + (fabsf(dot(bp, bc)) + mask);
+    if (d > dd) { idx[3] = i; dd = d; }
+  }
+  int count = 0;
+  for (int i = 3; i >= 0; i--) {  // :258-275 one contact per index that appears once among idx[0..i]
+    int rep = 0;
+    for (int j = 0; j <= i; j++) rep += idx[j] == idx[i];
+    if (rep != 1) continue;
+    const float* v = vert + 3 * idx[i];
+    const float d = -support(idx[i]);
+    dist[count] = d;
+#pragma unroll
+    for (int k = 0; k < 3; k++) pos[3 * count + k] = p2[k] + r2[3 * k] * v[0] + r2[3 * k + 1] * v[1] + r2[3 * k + 2] * v[2] - 0.5f * d * n1[k];
+    count++;
+  }
+  return count;
 }
 
 // collision_driver.py:91-111, 218-271
@@ -545,8 +609,8 @@ __device__ __noinline__ int c_box_box(const float* p1, const float* R1, const fl
 
 // Number of candidate contacts of a pair type (collision_primitive.py wrappers).
 __device__ __forceinline__ int pair_ncand(int t1, int t2) {
-  if (t1 == GEOM_PLANE) return t2 == GEOM_SPHERE || t2 == GEOM_ELLIPSOID ? 1 : (t2 == GEOM_CAPSULE ? 2 : (t2 == GEOM_BOX ? 8 : (t2 == GEOM_CYLINDER ? 4 : 0)));
-  if (is_convex_pair(t1, t2)) return 1;
+  if (t1 == GEOM_PLANE) return t2 == GEOM_SPHERE || t2 == GEOM_ELLIPSOID ? 1 : (t2 == GEOM_CAPSULE ? 2 : (t2 == GEOM_BOX ? 8 : (t2 == GEOM_CYLINDER || t2 == GEOM_MESH ? 4 : 0)));
+  if (is_ccd_pair(t1, t2)) return 1;
   if (t1 == GEOM_SPHERE) return (t2 == GEOM_SPHERE || t2 == GEOM_CAPSULE || t2 == GEOM_BOX || t2 == GEOM_CYLINDER) ? 1 : 0;
   if (t1 == GEOM_CAPSULE) return (t2 == GEOM_CAPSULE || t2 == GEOM_BOX) ? 2 : 0;
   if (t1 == GEOM_BOX && t2 == GEOM_BOX) return 8;
@@ -785,10 +849,22 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
       nbb = c_box_box(pa, DW(geom_xmat) + 9 * g1, sa, pb, r2, sb, cp.margin, bdist, bpos, bnrm);
       boxbox = true;
     }
-    if ((FEAT & COLF_CONVEX) && is_convex_pair(g.t1, g.t2)) {  // GJK / EPA once per pair; the two passes below read the result
+    if ((FEAT & COLF_CONVEX) && is_ccd_pair(g.t1, g.t2)) {  // GJK / EPA once per pair; the two passes below read the result
       const float pa[3] = {g.p1.x, g.p1.y, g.p1.z}, pb[3] = {g.p2.x, g.p2.y, g.p2.z};
       const float sa[3] = {g.s1.x, g.s1.y, g.s1.z}, sb[3] = {g.s2.x, g.s2.y, g.s2.z};
-      nbb = c_ccd_pair(pa, DW(geom_xmat) + 9 * g1, sa, g.t1, pb, r2, sb, g.t2, cp.margin, K.o.ccd_tolerance, K.o.ccd_iterations, bdist, bpos, bnrm);
+      const float *v1 = nullptr, *v2 = nullptr;
+      int nv1 = 0, nv2 = 0;
+      if (g.t1 == GEOM_MESH) { const int id = MI(geom_dataid)[g1]; v1 = MR(mesh_vert) + 3 * MI(mesh_vertadr)[id]; nv1 = MI(mesh_vertnum)[id]; }
+      if (g.t2 == GEOM_MESH) { const int id = MI(geom_dataid)[g2]; v2 = MR(mesh_vert) + 3 * MI(mesh_vertadr)[id]; nv2 = MI(mesh_vertnum)[id]; }
+      nbb = c_ccd_pair(pa, DW(geom_xmat) + 9 * g1, sa, g.t1, v1, nv1, pb, r2, sb, g.t2, v2, nv2, cp.margin, K.o.ccd_tolerance,
+                       K.o.ccd_iterations, bdist, bpos, bnrm);
+      boxbox = true;
+    }
+    if ((FEAT & COLF_CONVEX) && g.t1 == GEOM_PLANE && g.t2 == GEOM_MESH) {
+      const float pa[3] = {g.p1.x, g.p1.y, g.p1.z}, pb[3] = {g.p2.x, g.p2.y, g.p2.z};
+      const int id = MI(geom_dataid)[g2];
+      bnrm[0] = g.n1.x; bnrm[1] = g.n1.y; bnrm[2] = g.n1.z;
+      nbb = c_plane_mesh(pa, bnrm, pb, r2, MR(mesh_vert) + 3 * MI(mesh_vertadr)[id], MI(mesh_vertnum)[id], bdist, bpos);
       boxbox = true;
     }
     for (int k = 0; k < ncand; k++) {  // pass 1: count (write_contact filter, collision_core.py:199-203)

@@ -89,7 +89,7 @@ def _check_supported(mjm):
   # features of the reference that this library does not implement yet (scope)
   if is_sparse(mjm):
     raise NotImplementedError("sparse mass matrix / Jacobian (nv > 32 or jacobian=sparse) is not implemented yet.")
-  for name in ("ntendon", "nflex", "nmesh", "nhfield"):
+  for name in ("ntendon", "nflex", "nhfield"):
     if getattr(mjm, name, 0):
       raise NotImplementedError(f"{name} > 0 is not implemented yet.")
   for t in np.asarray(mjm.actuator_trntype):
@@ -129,8 +129,15 @@ def host_model(mjm) -> SimpleNamespace:
     "actuator_forcelimited actuator_actlimited actuator_actearly eq_type eq_obj1id eq_obj2id"
   ).split():
     ints[name] = A(name, i32)
+  # mesh tables (absent on models without mesh assets)
+  nmesh = int(getattr(mjm, "nmesh", 0))
+  ints["geom_dataid"] = A("geom_dataid", i32) if hasattr(mjm, "geom_dataid") else np.full(ngeom, -1, dtype=i32)
+  ints["mesh_vertadr"] = A("mesh_vertadr", i32) if nmesh else np.zeros(0, dtype=i32)
+  ints["mesh_vertnum"] = A("mesh_vertnum", i32) if nmesh else np.zeros(0, dtype=i32)
   for name in types.MODEL_REAL_FIELDS:
-    if name == "actuator_gear":
+    if name == "mesh_vert":
+      reals[name] = A(name, f64).reshape(-1, 3) if nmesh else np.zeros((0, 3))
+    elif name == "actuator_gear":
       reals[name] = A(name, f64).reshape(nu, 6)
     else:
       reals[name] = A(name, f64)
@@ -211,7 +218,7 @@ def host_model(mjm) -> SimpleNamespace:
   lookup[include] = np.arange(nxn, dtype=i32)
   ints["nxn_lookup"] = lookup
 
-  # supported narrowphase pair types: analytic primitives + GJK / EPA for ellipsoid / cylinder pairs (no meshes / hfields yet)
+  # supported narrowphase pair types: analytic primitives + GJK / EPA for ellipsoid / cylinder / mesh pairs (no hfields yet)
   supported = {
     (C.GeomType.PLANE, C.GeomType.SPHERE),
     (C.GeomType.PLANE, C.GeomType.CAPSULE),
@@ -234,6 +241,14 @@ def host_model(mjm) -> SimpleNamespace:
     (C.GeomType.ELLIPSOID, C.GeomType.BOX),
     (C.GeomType.CYLINDER, C.GeomType.CYLINDER),
     (C.GeomType.CYLINDER, C.GeomType.BOX),
+    # convex-hull meshes: plane_convex (exhaustive vertex search) and GJK / EPA with the exhaustive support function
+    (C.GeomType.PLANE, C.GeomType.MESH),
+    (C.GeomType.SPHERE, C.GeomType.MESH),
+    (C.GeomType.CAPSULE, C.GeomType.MESH),
+    (C.GeomType.ELLIPSOID, C.GeomType.MESH),
+    (C.GeomType.CYLINDER, C.GeomType.MESH),
+    (C.GeomType.BOX, C.GeomType.MESH),
+    (C.GeomType.MESH, C.GeomType.MESH),
   }
   gtype = ints["geom_type"]
   for ga, gb in ints["nxn_pair"]:
@@ -258,7 +273,7 @@ def host_model(mjm) -> SimpleNamespace:
     nfrictiondof=int(ints["dof_friction_adr"].size), neqjnt=int(ints["eq_jnt_adr"].size), nJmom=nJmom,
     nmaxcondim=nmaxcondim, nmaxpyramid=int(max(1, 2 * (nmaxcondim - 1))),
     ngravcomp=int((reals["body_gravcomp"] != 0).sum()), is_sparse=int(sparse), nM=int(getattr(mjm, "nM", 0)),
-    ntree=int(getattr(mjm, "ntree", 0)), ngeompair=int(len(geom1)),
+    ntree=int(getattr(mjm, "ntree", 0)), ngeompair=int(len(geom1)), nmesh=nmesh, nmeshvert=int(reals["mesh_vert"].shape[0]),
   )  # fmt: skip
   extra = dict(
     nsensordata=int(getattr(mjm, "nsensordata", 0)), ncam=int(getattr(mjm, "ncam", 0)), nlight=int(getattr(mjm, "nlight", 0)),

@@ -50,7 +50,7 @@ TILE_SIZE_JTDAJ_DENSE = 16  # reference types.py:35
 # ----------------------------------------------------------------------------------------------
 MODEL_SIZES = (
   "nq nv nu na nbody njnt ngeom nsite nmocap neq npair nxn nlevel nv_pad nlimit nlimitball "
-  "nfrictiondof neqjnt nJmom nmaxcondim nmaxpyramid ngravcomp is_sparse nM ntree ngeompair"
+  "nfrictiondof neqjnt nJmom nmaxcondim nmaxpyramid ngravcomp is_sparse nM ntree ngeompair nmesh nmeshvert"
 ).split()
 
 MODEL_INT_FIELDS = {
@@ -102,6 +102,9 @@ MODEL_INT_FIELDS = {
   "eq_obj1id": ("neq",),
   "eq_obj2id": ("neq",),
   "eq_jnt_adr": ("neqjnt",),
+  "geom_dataid": ("ngeom",),
+  "mesh_vertadr": ("nmesh",),
+  "mesh_vertnum": ("nmesh",),
 }
 
 # reference batches these over a leading `*` dimension (1 or nworld); here always 1
@@ -160,6 +163,7 @@ MODEL_REAL_FIELDS = {
   "eq_solref": ("neq", 2),
   "eq_solimp": ("neq", 5),
   "eq_data": ("neq", 11),
+  "mesh_vert": ("nmeshvert", 3),
 }
 
 OPT_INT_FIELDS = (

@@ -951,12 +951,14 @@ static int is_convex_pair(int t1, int t2) {
   if (t1 == GEOM_CYLINDER) return t2 == GEOM_CYLINDER || t2 == GEOM_BOX;
   return 0;
 }
+static int is_convex_pair_mesh(int t1, int t2) { return (t2 == GEOM_MESH && t1 >= GEOM_SPHERE) || is_convex_pair(t1, t2); }
 
 /* collision_convex.py:712 eval_ccd_write_contact (single contact, no collision sensor): returns 1 candidate whose dist is the
  * surface distance (>= margin when the margin-inflated shapes do not overlap, which write_contact then rejects) */
-static int ccd_pair(const real* p1, const real* r1, const real* s1, int t1, const real* p2, const real* r2, const real* s2, int t2,
-                    real margin, real tolerance, int iterations, OContactGeom* out) {
+static int ccd_pair(const real* p1, const real* r1, const real* s1, int t1, const real* v1, int nv1, const real* p2, const real* r2,
+                    const real* s2, int t2, const real* v2, int nv2, real margin, real tolerance, int iterations, OContactGeom* out) {
   CcdGeom g1, g2;
+  g1.vert = v1; g1.nvert = nv1; g2.vert = v2; g2.nvert = nv2;
   static _Thread_local CcdPolytope pt;
   CcdGjk res;
   memcpy(g1.pos, p1, sizeof(g1.pos)); memcpy(g1.rot, r1, sizeof(g1.rot)); memcpy(g1.size, s1, sizeof(g1.size));
@@ -979,7 +981,62 @@ static int narrowphase_pair(const OModel* m, const OData* d, int g1, int g2, rea
   const real *p1 = d->geom_xpos + 3 * g1, *p2 = d->geom_xpos + 3 * g2, *r1 = d->geom_xmat + 9 * g1, *r2 = d->geom_xmat + 9 * g2;
   const real *s1 = m->geom_size + 3 * g1, *s2 = m->geom_size + 3 * g2;
   real n1[3] = {r1[2], r1[5], r1[8]}, n2[3] = {r2[2], r2[5], r2[8]};
-  if (is_convex_pair(t1, t2)) return ccd_pair(p1, r1, s1, t1, p2, r2, s2, t2, margin, ccd_tolerance, ccd_iterations, out);
+  if (is_convex_pair_mesh(t1, t2)) {
+    const real *v1 = 0, *v2 = 0;
+    int nv1 = 0, nv2 = 0;
+    if (t1 == GEOM_MESH) { int id = m->geom_dataid[g1]; v1 = m->mesh_vert + 3 * m->mesh_vertadr[id]; nv1 = m->mesh_vertnum[id]; }
+    if (t2 == GEOM_MESH) { int id = m->geom_dataid[g2]; v2 = m->mesh_vert + 3 * m->mesh_vertadr[id]; nv2 = m->mesh_vertnum[id]; }
+    return ccd_pair(p1, r1, s1, t1, v1, nv1, p2, r2, s2, t2, v2, nv2, margin, ccd_tolerance, ccd_iterations, out);
+  }
+  if (t1 == GEOM_PLANE && t2 == GEOM_MESH) { /* collision_primitive.py:52-277 plane_convex, exhaustive branch (no mesh graph) */
+    int id = m->geom_dataid[g2], nvert = m->mesh_vertnum[id], idx[4] = {-1, -1, -1, -1};
+    const real* vert = m->mesh_vert + 3 * m->mesh_vertadr[id];
+    real dp[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]}, pl[3], n[3], HUGE_V = 1e6;
+    for (int i = 0; i < 3; i++) { pl[i] = r2[i] * dp[0] + r2[3 + i] * dp[1] + r2[6 + i] * dp[2]; n[i] = r2[i] * n1[0] + r2[3 + i] * n1[1] + r2[6 + i] * n1[2]; }
+    for (int k = 0; k < 4; k++) { out[k].dist = MJ_MAXVAL; memset(out[k].pos, 0, sizeof(out[k].pos)); make_frame(out[k].frame, n1); out[k].id = k; }
+#define SUPPORT(i) ((pl[0] - vert[3 * (i)]) * n[0] + (pl[1] - vert[3 * (i) + 1]) * n[1] + (pl[2] - vert[3 * (i) + 2]) * n[2])
+    real max_support = -HUGE_V, a[3] = {0, 0, 0}, b[3] = {0, 0, 0}, c[3] = {0, 0, 0};
+    for (int i = 0; i < nvert; i++) { real sp = SUPPORT(i); if (sp > max_support) { max_support = sp; idx[0] = i; memcpy(a, vert + 3 * i, sizeof(a)); } }
+    if (max_support < 0) return 4;
+    real threshold = max_support - 1e-3, bd = -HUGE_V, cd = -HUGE_V, dd = -HUGE_V, ab[3], ac[3], bc[3], t[3];
+    for (int i = 0; i < nvert; i++) {
+      real mask = SUPPORT(i) > threshold ? 0.0 : -HUGE_V, d;
+      for (int j = 0; j < 3; j++) t[j] = a[j] - vert[3 * i + j];
+      d = dot3(t, t) + mask;
+      if (d > bd) { idx[1] = i; bd = d; memcpy(b, vert + 3 * i, sizeof(b)); }
+    }
+    for (int j = 0; j < 3; j++) t[j] = a[j] - b[j];
+    cross3(ab, n, t);
+    for (int i = 0; i < nvert; i++) {
+      real mask = SUPPORT(i) > threshold ? 0.0 : -HUGE_V, d;
+      for (int j = 0; j < 3; j++) t[j] = a[j] - vert[3 * i + j];
+      d = fabs(dot3(t, ab)) + mask;
+      if (d > cd) { idx[2] = i; cd = d; memcpy(c, vert + 3 * i, sizeof(c)); }
+    }
+    for (int j = 0; j < 3; j++) t[j] = a[j] - c[j];
+    cross3(ac, n, t);
+    for (int j = 0; j < 3; j++) t[j] = b[j] - c[j];
+    cross3(bc, n, t);
+    for (int i = 0; i < nvert; i++) {
+      real mask = SUPPORT(i) > threshold ? 0.0 : -HUGE_V, ap[3], bp[3], d;
+      for (int j = 0; j < 3; j++) { ap[j] = a[j] - vert[3 * i + j]; bp[j] = b[j] - vert[3 * i + j]; }
+      d = fabs(dot3(ap, ac)) + mask + fabs(dot3(bp, bc)) + mask;
+      if (d > dd) { idx[3] = i; dd = d; }
+    }
+    int count = 0;
+    for (int i = 3; i >= 0; i--) { /* :258-275 contacts from the indices that appear once among idx[0..i] */
+      int rep = 0;
+      for (int j = 0; j <= i; j++) rep += idx[j] == idx[i];
+      if (rep != 1) continue;
+      real w[3], dist = -SUPPORT(idx[i]);
+      mat_vec(w, r2, vert + 3 * idx[i]);
+      out[count].dist = dist;
+      for (int j = 0; j < 3; j++) out[count].pos[j] = p2[j] + w[j] - 0.5 * dist * n1[j];
+      count++;
+    }
+#undef SUPPORT
+    return 4;
+  }
   if (t1 == GEOM_PLANE && t2 == GEOM_SPHERE) { /* collision_primitive.py:280 */
     c_plane_sphere(n1, p1, p2, s2[0], &out[0].dist, out[0].pos);
     make_frame(out[0].frame, n1);
@@ -2305,17 +2362,23 @@ int mjo_ccd_polytope(double* vert, int* face, double* norm2, int* nvert) {
   *nvert = g_dbg_pt.nvert;
   return g_dbg_pt.nface;
 }
-int mjo_ccd(int t1, int t2, const double* p1, const double* r1, const double* s1, const double* p2, const double* r2, const double* s2,
-            double margin, double cutoff, double tolerance, int iterations, double* dist, double* x1, double* x2) {
+int mjo_ccd_mesh(int t1, int t2, const double* p1, const double* r1, const double* s1, const double* v1, int nv1, const double* p2,
+                 const double* r2, const double* s2, const double* v2, int nv2, double margin, double cutoff, double tolerance, int iterations,
+                 double* dist, double* x1, double* x2) {
   CcdGeom g1, g2;
 #define pt g_dbg_pt
   CcdGjk res;
   memcpy(g1.pos, p1, sizeof(g1.pos)); memcpy(g1.rot, r1, sizeof(g1.rot)); memcpy(g1.size, s1, sizeof(g1.size));
   memcpy(g2.pos, p2, sizeof(g2.pos)); memcpy(g2.rot, r2, sizeof(g2.rot)); memcpy(g2.size, s2, sizeof(g2.size));
   g1.margin = g2.margin = margin; g1.type = t1; g2.type = t2;
+  g1.vert = v1; g1.nvert = nv1; g2.vert = v2; g2.nvert = nv2;
   x1[0] = x1[1] = x1[2] = x2[0] = x2[1] = x2[2] = 0.0;
   return ccd_run(tolerance, cutoff, iterations, iterations, g1, g2, &pt, &res, dist, x1, x2);
 #undef pt
+}
+int mjo_ccd(int t1, int t2, const double* p1, const double* r1, const double* s1, const double* p2, const double* r2, const double* s2,
+            double margin, double cutoff, double tolerance, int iterations, double* dist, double* x1, double* x2) {
+  return mjo_ccd_mesh(t1, t2, p1, r1, s1, 0, 0, p2, r2, s2, 0, 0, margin, cutoff, tolerance, iterations, dist, x1, x2);
 }
 /* test hook: solver.py:263 _eval_elliptic -> (cost, gradient, curvature) */
 void mjo_eval_elliptic(double mu, const double* quad, const double* q1, const double* q2, double alpha, double* out) {

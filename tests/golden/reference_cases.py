@@ -109,6 +109,7 @@ CASES = {
   "panda_step3": dict(model="panda", nworld=10, seed=50, mode="step", nstep=3, nconmax=8, njmax=40, states="panda"),
   "panda_deep_forward": dict(model="panda", nworld=10, seed=43, mode="forward", nconmax=8, njmax=80, states="panda"),
   "convex_pairs_collision": dict(model="convex_pairs", nworld=12, seed=4, mode="forward", nconmax=48, njmax=200, states="box_pairs"),
+  "mesh_pairs_collision": dict(model="mesh_pairs", nworld=12, seed=9, mode="forward", nconmax=48, njmax=200, states="box_pairs"),
 }
 
 
@@ -214,7 +215,7 @@ SOLVER_FIELDS = "qfrc_constraint qacc qacc_warmstart efc_force efc_state efc_Ma 
 LOOSE_SOLVER_CASES = ("humanoid_cg", "humanoid_elliptic_cg")
 # GJK / EPA stop on opt.ccd_tolerance (1e-6): two float64 evaluation orders may differ by one EPA iteration (witness points
 # move by < the tolerance; tests/test_oracle_ccd_golden.py quantifies it pair by pair)
-CASE_TOL = {"convex_pairs_collision": 5e-6}
+CASE_TOL = {"convex_pairs_collision": 5e-6, "mesh_pairs_collision": 5e-6}
 
 
 def load_golden(name):

@@ -58,4 +58,24 @@ CONVEX_PAIRS_XML = """
   </worldbody>
 </mujoco>"""
 
-XML = dict(SMALL_MODELS, box_pairs=BOX_PAIRS_XML, convex_pairs=CONVEX_PAIRS_XML)
+# convex-hull meshes given inline (no asset files): an irregular 14-vertex hull and a tetrahedron, against each other, the plane and
+# every primitive type (plane_convex + GJK / EPA with the exhaustive mesh support function)
+MESH_PAIRS_XML = """
+<mujoco>
+  <asset>
+    <mesh name="rock" vertex="0.001 0.143 -0.197 -0.147 -0.060 -0.196 0.010 0.178 -0.098 -0.146 0.092 0.101 0.026 -0.180 -0.009 0.099 -0.153 -0.078
+      -0.157 -0.085 -0.183 -0.039 -0.168 0.054 0.014 -0.014 -0.275 -0.198 -0.014 0.050 -0.179 -0.045 -0.137 -0.112 0.118 -0.134
+      -0.006 0.138 -0.137 -0.159 0.126 0.109 0.2 0.05 0.1 0.05 0.02 0.28"/>
+    <mesh name="tetra" vertex="0 0 0.3  0.28 0 -0.1  -0.14 0.24 -0.1  -0.14 -0.24 -0.1"/>
+  </asset>
+  <worldbody>
+    <geom type="plane" size="5 5 .01" pos="0 0 -0.45"/>
+    <body pos="0 0 0"><inertial pos="0 0 0" mass="1" diaginertia=".02 .02 .02"/><freejoint/><geom type="mesh" mesh="rock"/></body>
+    <body pos="1 0 0"><inertial pos="0 0 0" mass=".5" diaginertia=".01 .01 .01"/><freejoint/><geom type="mesh" mesh="tetra" margin=".01"/></body>
+    <body pos="0 1 0"><freejoint/><geom type="sphere" size=".18"/><geom type="ellipsoid" size=".12 .1 .3" pos=".35 0 0"/></body>
+    <body pos="1 1 0"><freejoint/><geom type="capsule" size=".1 .25"/><geom type="cylinder" size=".2 .1" pos="0 .4 0" euler="30 20 0"/></body>
+    <body pos="2 1 0"><freejoint/><geom type="box" size=".25 .15 .2"/></body>
+  </worldbody>
+</mujoco>"""
+
+XML = dict(SMALL_MODELS, box_pairs=BOX_PAIRS_XML, convex_pairs=CONVEX_PAIRS_XML, mesh_pairs=MESH_PAIRS_XML)

@@ -33,8 +33,9 @@ UNCONVERGED = ("humanoid_cg_iter6",)
 # witness direction is only determined to ~sqrt(tolerance / radius) -- a float32 EPA and a float64 EPA stop on different faces
 # of the polytope.  Measured on B200: contact_pos 4.5e-4, contact_frame 5.8e-3, efc_J 9.5e-3.  The bodies of this fixture
 # are dropped on top of each other (penetrations up to 0.3), so the solver outputs amplify those normals and are not compared.
-CASE_TOL = {"convex_pairs_collision": {"contact_pos": 2e-3, "contact_frame": 2e-2, "efc_J": 3e-2, "efc_aref": 5e-3, "efc_D": 1e-3}}
-CASE_SKIP_SOLVER = ("convex_pairs_collision",)
+_CCD_TOL = {"contact_pos": 2e-3, "contact_frame": 2e-2, "efc_J": 3e-2, "efc_aref": 5e-3, "efc_D": 1e-3}
+CASE_TOL = {"convex_pairs_collision": _CCD_TOL, "mesh_pairs_collision": _CCD_TOL}
+CASE_SKIP_SOLVER = ("convex_pairs_collision", "mesh_pairs_collision")
 FACTOR_FIELDS = ("qacc_smooth", "qLD")
 EXACT = ("efc_type", "efc_id", "contact_dim", "contact_geom")
 

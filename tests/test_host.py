@@ -96,10 +96,10 @@ def test_put_model_rejects_unsupported_features(snippet, msg):
     mjw.put_model(mjm, device="cpu")
 
 
-def test_mesh_geoms_are_rejected_and_every_primitive_pair_is_accepted():
-  """Meshes / height fields need assets the MJCF-lite compiler does not load yet: rejected up front, like the reference
-  rejects what it does not implement (io.py:100-144).  All pairs of plane / sphere / capsule / ellipsoid / cylinder / box
-  have a narrowphase (primitive or GJK / EPA)."""
+def test_mesh_geoms_without_assets_are_rejected_and_every_pair_is_accepted():
+  """A colliding mesh geom needs its asset (hull vertices) and its body an explicit <inertial>: rejected up front, like the
+  reference rejects what it does not implement (io.py:100-144).  All pairs of plane / sphere / capsule / ellipsoid /
+  cylinder / box / mesh have a narrowphase (primitive or GJK / EPA)."""
   xml = """<mujoco><worldbody>
     <body><freejoint/><geom type="mesh" mesh="m"/></body>
     <body pos="1 0 0"><freejoint/><geom type="sphere" size=".1"/></body>
@@ -107,10 +107,45 @@ def test_mesh_geoms_are_rejected_and_every_primitive_pair_is_accepted():
   with pytest.raises(NotImplementedError, match="mesh"):
     mjw.load_mjcf_string(xml)
   geoms = ['type="sphere" size=".1"', 'type="capsule" size=".1 .2"', 'type="ellipsoid" size=".1 .2 .3"', 'type="cylinder" size=".1 .2"',
-           'type="box" size=".1 .2 .3"']  # fmt: skip
-  bodies = "".join(f'<body pos="{i} 0 1"><joint type="slide"/><geom {g}/></body>' for i, g in enumerate(geoms))
-  m = mjw.put_model(mjw.load_mjcf_string(f'<mujoco><worldbody><geom type="plane" size="1 1 .1"/>{bodies}</worldbody></mujoco>'), device="cpu")
-  assert m.sizes["nxn"] == 15
+           'type="box" size=".1 .2 .3"', 'type="mesh" mesh="t"']  # fmt: skip
+  inertial = '<inertial pos="0 0 0" mass="1" diaginertia=".1 .1 .1"/>'
+  bodies = "".join(f'<body pos="{i} 0 1">{inertial}<joint type="slide"/><geom {g}/></body>' for i, g in enumerate(geoms))
+  asset = '<asset><mesh name="t" vertex="0 0 0 1 0 0 0 1 0 0 0 1 .1 .1 .1"/></asset>'
+  mjm = mjw.load_mjcf_string(f'<mujoco>{asset}<worldbody><geom type="plane" size="1 1 .1"/>{bodies}</worldbody></mujoco>')
+  assert mjm.nmesh == 1 and mjm.mesh_vertnum.tolist() == [4]  # the interior point is not a hull vertex
+  m = mjw.put_model(mjm, device="cpu")
+  assert m.sizes["nxn"] == 21 and m.sizes["nmesh"] == 1 and m.sizes["nmeshvert"] == 4
+  np.testing.assert_allclose(m.mesh_vert.numpy().reshape(-1, 3), mjm.mesh_vert, rtol=1e-6)
+  assert int(m.geom_dataid[6]) == 0 and int(m.geom_dataid[1]) == -1
+
+
+def test_mesh_files_stl_and_obj_load_as_convex_hull_vertices(tmp_path):
+  """Binary STL, ASCII STL and OBJ assets: vertices deduplicated to their convex hull, `scale` applied, bounds from the hull."""
+  import struct
+
+  cube = np.array([[x, y, z] for x in (-1, 1) for y in (-1, 1) for z in (-1, 1)], dtype=np.float64)
+  faces = [(0, 1, 3), (0, 3, 2), (4, 6, 7), (4, 7, 5), (0, 4, 5), (0, 5, 1), (2, 3, 7), (2, 7, 6), (0, 2, 6), (0, 6, 4), (1, 5, 7), (1, 7, 3)]
+  with open(tmp_path / "cube.stl", "wb") as f:
+    f.write(b"\0" * 80 + struct.pack("<I", len(faces)))
+    for tri in faces:
+      f.write(struct.pack("<12fH", 0, 0, 0, *cube[list(tri)].ravel(), 0))
+  with open(tmp_path / "cube_ascii.stl", "w") as f:
+    f.write("solid cube\n")
+    for tri in faces:
+      f.write(" facet normal 0 0 0\n  outer loop\n" + "".join(f"   vertex {v[0]} {v[1]} {v[2]}\n" for v in cube[list(tri)]) + "  endloop\n endfacet\n")
+    f.write("endsolid cube\n")
+  with open(tmp_path / "cube.obj", "w") as f:
+    f.write("# cube with an interior point\n" + "".join(f"v {v[0]} {v[1]} {v[2]}\n" for v in np.vstack([cube, [[0, 0, 0]]])))
+    f.write("".join(f"f {a + 1} {b + 1} {c + 1}\n" for a, b, c in faces))
+  for fname in ("cube.stl", "cube_ascii.stl", "cube.obj"):
+    xml = f"""<mujoco><compiler meshdir="{tmp_path}"/><asset><mesh name="c" file="{fname}" scale=".1 .2 .3"/></asset><worldbody>
+      <body><inertial pos="0 0 0" mass="1" diaginertia=".1 .1 .1"/><freejoint/><geom type="mesh" mesh="c"/></body></worldbody></mujoco>"""
+    mjm = mjw.load_mjcf_string(xml)
+    assert mjm.mesh_vertnum.tolist() == [8], fname
+    got = mjm.mesh_vert[np.lexsort(mjm.mesh_vert.T[::-1])]
+    want = cube * [0.1, 0.2, 0.3]
+    np.testing.assert_allclose(got, want[np.lexsort(want.T[::-1])], atol=1e-7, err_msg=fname)
+    np.testing.assert_allclose(mjm.geom_rbound[0], np.linalg.norm([0.1, 0.2, 0.3]), rtol=1e-6)
 
 
 def test_device_is_mandatory_for_compute(humanoid):

@@ -57,3 +57,40 @@ def test_ccd_matches_reference_execution(pair):
       assert err < 5e-2, (pair, i, err)
   assert loose <= 3, (pair, loose)
   assert npen >= 5, (pair, npen)
+
+
+GOLDEN_MESH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ccd_mesh_pairs.npz")
+
+
+@pytest.mark.parametrize("t1", TYPES + [7], ids=lambda t: f"{NAMES.get(t, 'mesh')}-mesh")
+def test_ccd_mesh_matches_reference_execution(t1):
+  """Convex-hull meshes (4-20 vertices, exhaustive support search with the cached start vertex, collision_gjk.py:140-154)
+  against every other convex type: 30 pairs each from the reference's `ccd` (make_ccd_golden.py --mesh)."""
+  lib = O.load()
+  lib.mjo_ccd_mesh.restype = ctypes.c_int
+  dp = ctypes.POINTER(ctypes.c_double)
+  with np.load(GOLDEN_MESH) as z:
+    g = {k: z[k] for k in z.files}
+  idx = np.nonzero(g["t1"] == t1)[0]
+  assert len(idx) >= 30
+  loose = npen = 0
+  for i in idx:
+    keep = {k: np.ascontiguousarray(g[k][i], dtype=np.float64) for k in ("p1", "r1", "s1", "v1", "p2", "r2", "s2", "v2")}
+    P = lambda k: keep[k].ctypes.data_as(dp)  # noqa: E731
+    dist = ctypes.c_double(0.0)
+    x1, x2 = (ctypes.c_double * 3)(), (ctypes.c_double * 3)()
+    n = lib.mjo_ccd_mesh(int(t1), 7, P("p1"), P("r1"), P("s1"), P("v1"), int(g["nv1"][i]), P("p2"), P("r2"), P("s2"), P("v2"), int(g["nv2"][i]),
+                         ctypes.c_double(float(g["margin"][i])), ctypes.c_double(float(g["cutoff"][i])), ctypes.c_double(1e-6), 35,
+                         ctypes.byref(dist), x1, x2)  # fmt: skip
+    assert n == int(g["ncollision"][i]), (t1, i)
+    if g["dist"][i] > 1e29:
+      assert dist.value > 1e29, (t1, i, dist.value)
+      continue
+    npen += g["dist"][i] < 0
+    assert abs(dist.value - g["dist"][i]) < 1e-8, (t1, i, dist.value, g["dist"][i])
+    err = max(np.abs(np.array(x1[:]) - g["x1"][i]).max(), np.abs(np.array(x2[:]) - g["x2"][i]).max())
+    if err > 1e-7:
+      loose += 1
+      assert err < 5e-2, (t1, i, err)
+  assert loose <= 3, (t1, loose)
+  assert npen >= 5, (t1, npen)
