@@ -94,3 +94,52 @@ def test_ccd_mesh_matches_reference_execution(t1):
       assert err < 5e-2, (t1, i, err)
   assert loose <= 3, (t1, loose)
   assert npen >= 5, (t1, npen)
+
+
+def _build_f32():
+  """Host build of the FLOAT32 instantiation of csrc/mjb_ccd_core.h (tests/csrc/ccd_f32.c): the arithmetic of the CUDA kernel."""
+  import subprocess
+  import tempfile
+
+  here = os.path.dirname(os.path.abspath(__file__))
+  out = os.path.join(tempfile.gettempdir(), f"libmjb_ccd_f32_{os.getuid()}.so")
+  src = os.path.join(here, "csrc", "ccd_f32.c")
+  core = os.path.join(here, "..", "mujoco_warp_b200", "csrc", "mjb_ccd_core.h")
+  if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(src), os.path.getmtime(core)):
+    subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-o", out, src, "-lm"], check=True)
+  lib = ctypes.CDLL(out)
+  lib.ccd32.restype = ctypes.c_int
+  return lib
+
+
+@pytest.mark.parametrize("golden", ["ccd_pairs.npz", "ccd_mesh_pairs.npz"])
+def test_float32_build_of_the_device_ccd_core_against_reference_execution(golden):
+  """The device runs the same source in float32.  Against the reference's float64 execution: the collision decision is equal
+  on every pair; the depth agrees to ~1e-6 (the ccd tolerance) typically, but EPA on smooth shapes in float32 can stop on a
+  sliver face of the polytope whose normal is rounding-limited: worst seen 1.1e-4 (sphere-ellipsoid, depth 0.089).  These
+  bounds are what tests/test_gpu_reference_golden.py allows the CUDA path on the GJK / EPA fixtures."""
+  lib = _build_f32()
+  dp = ctypes.POINTER(ctypes.c_double)
+  with np.load(os.path.join(os.path.dirname(GOLDEN), golden)) as z:
+    g = {k: z[k] for k in z.files}
+  mesh = "v1" in g
+  errs = []
+  for i in range(len(g["dist"])):
+    keep = {k: np.ascontiguousarray(g[k][i], dtype=np.float64) for k in ("p1", "r1", "s1", "p2", "r2", "s2")}
+    v1 = np.ascontiguousarray(g["v1"][i], dtype=np.float64) if mesh else np.zeros(3)
+    v2 = np.ascontiguousarray(g["v2"][i], dtype=np.float64) if mesh else np.zeros(3)
+    P = lambda a: a.ctypes.data_as(dp)  # noqa: E731
+    dist = ctypes.c_double(0.0)
+    x1, x2 = (ctypes.c_double * 3)(), (ctypes.c_double * 3)()
+    n = lib.ccd32(int(g["t1"][i]), int(g["t2"][i]), P(keep["p1"]), P(keep["r1"]), P(keep["s1"]), P(v1), int(g["nv1"][i]) if mesh else 0,
+                  P(keep["p2"]), P(keep["r2"]), P(keep["s2"]), P(v2), int(g["nv2"][i]) if mesh else 0, ctypes.c_double(float(g["margin"][i])),
+                  ctypes.c_double(float(g["cutoff"][i])), ctypes.c_double(1e-6), 35, ctypes.byref(dist), x1, x2)  # fmt: skip
+    assert n == int(g["ncollision"][i]), (golden, i)
+    if g["dist"][i] > 1e29:
+      assert dist.value > 1e29, (golden, i)
+      continue
+    errs.append(abs(dist.value - g["dist"][i]))
+  errs = np.array(errs)
+  assert errs.max() < 3e-4, errs.max()
+  assert np.percentile(errs, 90) < 5e-6, np.percentile(errs, 90)
+  assert np.median(errs) < 2e-7, np.median(errs)
