@@ -106,6 +106,38 @@ int mjb_status(MjbData* d, uint32_t* host_flags, void* cuda_stream);
 int mjb_ctrl_noise(const MjbModel* m, MjbData* d, const MjbOption* opt, const float* ctrl_center,
                    int step, float ctrlnoisestd, float ctrlnoiserate, void* cuda_stream);
 
+/* ---- the callers either side of `step` (RL loops): state packing, masked reset, contact forces ----
+ * State signature bits = the reference's `State` enum (types.py:598-637 = MuJoCo mjtState):
+ * time, qpos, qvel, act, qacc_warmstart, ctrl, qfrc_applied, xfrc_applied, eq_active, mocap_pos, mocap_quat. */
+#define MJB_STATE_TIME (1 << 0)
+#define MJB_STATE_QPOS (1 << 1)
+#define MJB_STATE_QVEL (1 << 2)
+#define MJB_STATE_ACT (1 << 3)
+#define MJB_STATE_WARMSTART (1 << 4)
+#define MJB_STATE_CTRL (1 << 5)
+#define MJB_STATE_QFRC_APPLIED (1 << 6)
+#define MJB_STATE_XFRC_APPLIED (1 << 7)
+#define MJB_STATE_EQ_ACTIVE (1 << 8)
+#define MJB_STATE_MOCAP_POS (1 << 9)
+#define MJB_STATE_MOCAP_QUAT (1 << 10)
+#define MJB_STATE_USERDATA (1 << 11) /* accepted, carries no data (unsupported in the reference too, types.py:638) */
+#define MJB_STATE_PLUGIN (1 << 12)   /* accepted, carries no data */
+#define MJB_NSTATE 13
+/* Floats per world of the state selected by `sig` (mj_stateSize), or < 0 on an invalid signature. */
+int mjb_state_size(const MjbModel* m, const MjbData* d, int sig);
+/* support.get_state / set_state (reference support.py:572 / :711): packs / unpacks the selected components between Data and
+ * `state` (device, nworld rows of `ld` >= state size floats).  `active` is a device array of nworld bytes (non-zero = copy
+ * that world) or NULL for every world. */
+int mjb_get_state(const MjbModel* m, MjbData* d, float* state, int ld, int sig, const uint8_t* active, void* cuda_stream);
+int mjb_set_state(const MjbModel* m, MjbData* d, const float* state, int ld, int sig, const uint8_t* active, void* cuda_stream);
+/* io.reset_data (reference io.py:1458): default state for the worlds whose byte in `reset` (device, nworld bytes; NULL = all)
+ * is non-zero, their contacts cleared in place.  No host synchronisation, graph capturable. */
+int mjb_reset_data(const MjbModel* m, MjbData* d, const uint8_t* reset, void* cuda_stream);
+/* support.contact_force (reference support.py:354): 6D force:torque of `n` contacts (device ids) in the contact frame, or
+ * rotated into the world frame; `cone` = Option.cone; `force` = n x 6 floats (device).  Rows of ids >= nacon are not written. */
+int mjb_contact_force(const MjbModel* m, MjbData* d, int cone, const int* contact_ids, int n, int to_world_frame, float* force,
+                      void* cuda_stream);
+
 /* Number of kernel launches issued by this library since load (for bench.py's gpu_launches). */
 long long mjb_launch_count(void);
 /* Duration bookkeeping for bench.py: records CUDA events around every stage launch when enabled

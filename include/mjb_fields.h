@@ -33,7 +33,7 @@
 
 /* ---- model int arrays ---------------------------------------------------------------------- */
 #define MJB_MODEL_INT_FIELDS(X) \
-  X(body_parentid) X(body_rootid) X(body_weldid) X(body_mocapid) X(body_jntnum) X(body_jntadr) \
+  X(body_parentid) X(body_rootid) X(body_weldid) X(body_mocapid) X(eq_active0) X(body_jntnum) X(body_jntadr) \
   X(body_dofnum) X(body_dofadr) \
   X(body_subtreeend) /* one past the last body of the (pre-order contiguous) subtree */ \
   X(body_tree) X(body_tree_adr) \

@@ -22,6 +22,7 @@ from .constants import IntegratorType as IntegratorType
 from .constants import JacobianType as JacobianType
 from .constants import JointType as JointType
 from .constants import SolverType as SolverType
+from .constants import State as State
 from .constants import TrnType as TrnType
 from .forward import collision as collision
 from .forward import com_pos as com_pos
@@ -55,6 +56,10 @@ from .io import put_model as put_model
 from .io import reset_data as reset_data
 from .mjcf import load_mjcf as load_mjcf
 from .mjcf import load_mjcf_string as load_mjcf_string
+from .support import contact_force as contact_force
+from .support import get_state as get_state
+from .support import set_state as set_state
+from .support import state_size as state_size
 from .types import Constraint as Constraint
 from .types import Contact as Contact
 from .types import Data as Data

@@ -29,20 +29,48 @@ _lock = threading.Lock()
 _lib = None
 
 
+def _includes(path, seen=None):
+  """Project headers a source file includes, transitively (csrc/ and include/ only)."""
+  import re
+
+  seen = set() if seen is None else seen
+  with open(path) as fh:
+    for name in re.findall(r'^\s*#\s*include\s+"([^"]+)"', fh.read(), flags=re.M):
+      for base in (os.path.dirname(path), CSRC, INCLUDE):
+        cand = os.path.normpath(os.path.join(base, name))
+        if os.path.isfile(cand) and cand not in seen:
+          seen.add(cand)
+          _includes(cand, seen)
+          break
+  return seen
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
-  """Compiles csrc/*.cu into csrc/libmjb200.so for sm_100a (works without a GPU)."""
+  """Compiles csrc/*.cu into csrc/libmjb200.so for sm_100a (works without a GPU).
+
+  One object per translation unit under csrc/_obj/, rebuilt only when the unit or a header it includes changed: the step
+  pipeline (mjb_api.cu, minutes) is not recompiled for an edit of the light units."""
   srcs = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith(".cu")]
-  deps = srcs + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
-  deps += [os.path.join(INCLUDE, f) for f in os.listdir(INCLUDE)]
-  if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(p) for p in deps):
-    return LIB_PATH
-  cmd = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xptxas", "-v" if verbose else "-O3",
-         "-shared", "-Xcompiler", "-fPIC", "-I", INCLUDE, "-I", CSRC, "-o", LIB_PATH] + srcs  # fmt: skip
-  res = subprocess.run(cmd, capture_output=True, text=True)
-  if res.returncode != 0:
-    raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
-  if verbose:
-    print(res.stderr)
+  objdir = os.path.join(CSRC, "_obj")
+  os.makedirs(objdir, exist_ok=True)
+  objs, relink = [], force or not os.path.exists(LIB_PATH)
+  common = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xptxas", "-v" if verbose else "-O3",
+            "-Xcompiler", "-fPIC", "-I", INCLUDE, "-I", CSRC]  # fmt: skip
+  for src in srcs:
+    obj = os.path.join(objdir, os.path.splitext(os.path.basename(src))[0] + ".o")
+    deps = [src] + sorted(_includes(src))
+    if force or not os.path.exists(obj) or any(os.path.getmtime(obj) < os.path.getmtime(p) for p in deps):
+      res = subprocess.run(["nvcc"] + common + ["-c", src, "-o", obj], capture_output=True, text=True)
+      if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+      if verbose:
+        print(res.stderr)
+      relink = True
+    objs.append(obj)
+  if relink or any(os.path.getmtime(LIB_PATH) < os.path.getmtime(o) for o in objs):
+    res = subprocess.run(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB_PATH] + objs, capture_output=True, text=True)
+    if res.returncode != 0:
+      raise RuntimeError("nvcc link failed:\n" + res.stdout + res.stderr)
   return LIB_PATH
 
 
@@ -83,6 +111,16 @@ def load():
     lib.mjb_mul_m.argtypes = [vp, vp, vp, vp, vp]
     lib.mjb_ctrl_noise.restype = ctypes.c_int
     lib.mjb_ctrl_noise.argtypes = [vp, vp, ctypes.POINTER(MjbOption), vp, ctypes.c_int, ctypes.c_float, ctypes.c_float, vp]
+    lib.mjb_state_size.restype = ctypes.c_int
+    lib.mjb_state_size.argtypes = [vp, vp, ctypes.c_int]
+    for name in ("mjb_get_state", "mjb_set_state"):
+      fn = getattr(lib, name)
+      fn.restype = ctypes.c_int
+      fn.argtypes = [vp, vp, vp, ctypes.c_int, ctypes.c_int, vp, vp]
+    lib.mjb_reset_data.restype = ctypes.c_int
+    lib.mjb_reset_data.argtypes = [vp, vp, vp, vp]
+    lib.mjb_contact_force.restype = ctypes.c_int
+    lib.mjb_contact_force.argtypes = [vp, vp, ctypes.c_int, vp, ctypes.c_int, ctypes.c_int, vp, vp]
     lib.mjb_launch_count.restype = ctypes.c_longlong
     lib.mjb_timing_enable.argtypes = [ctypes.c_int]
     lib.mjb_timing_ms.restype = ctypes.c_double

@@ -162,6 +162,28 @@ class BroadphaseFilter(enum.IntFlag):
   OBB = 8
 
 
+class State(enum.IntEnum):
+  """State component bitflags (reference types.py:598-637 = MuJoCo mjtState)."""
+
+  TIME = 1 << 0
+  QPOS = 1 << 1
+  QVEL = 1 << 2
+  ACT = 1 << 3
+  WARMSTART = 1 << 4
+  CTRL = 1 << 5
+  QFRC_APPLIED = 1 << 6
+  XFRC_APPLIED = 1 << 7
+  EQ_ACTIVE = 1 << 8
+  MOCAP_POS = 1 << 9
+  MOCAP_QUAT = 1 << 10
+  NSTATE = 13
+  PHYSICS = (1 << 1) | (1 << 2) | (1 << 3)
+  FULLPHYSICS = (1 << 0) | (1 << 1) | (1 << 2) | (1 << 3) | (1 << 12)
+  USER = (1 << 5) | (1 << 6) | (1 << 7) | (1 << 8) | (1 << 9) | (1 << 10) | (1 << 11)
+  INTEGRATION = (1 << 13) - 1
+  # unsupported (carry no data): USERDATA = 1 << 11, PLUGIN = 1 << 12
+
+
 class ContactType(enum.IntFlag):
   CONSTRAINT = 1
   SENSOR = 2

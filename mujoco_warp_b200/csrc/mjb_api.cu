@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "mjb200.h"
+#include "mjb_internal.h"
 #include "mjb_kernels.cuh"
 
 static thread_local std::string g_err;
@@ -219,6 +220,16 @@ static void fill_params(KParams& K, const MjbModel* m, const MjbData* d, const M
   K.scratch_floats = d->scratch_floats;
   K.stages = stages;
 }
+
+int mjb_internal_params(const MjbModel* m, const MjbData* d, KParams* K) {
+  if (!m || !d || !K) return fail(-1, "null handle");
+  MjbOption o;
+  memset(&o, 0, sizeof(o));
+  fill_params(*K, m, d, &o, 0);
+  return 0;
+}
+int mjb_internal_fail(int code, const char* msg) { return fail(code, msg); }
+void mjb_internal_count_launch(void) { g_launches++; }
 
 // warps (= worlds in flight) per CTA; MJB_WARPS_PER_BLOCK overrides the per-group default
 static int warps_per_block(int dflt) {

@@ -129,6 +129,7 @@ def host_model(mjm) -> SimpleNamespace:
     "actuator_forcelimited actuator_actlimited actuator_actearly eq_type eq_obj1id eq_obj2id"
   ).split():
     ints[name] = A(name, i32)
+  ints["eq_active0"] = np.asarray(getattr(mjm, "eq_active0", np.ones(int(getattr(mjm, "neq", 0)), dtype=bool))).astype(i32).reshape(-1)
   # mesh tables (absent on models without mesh assets)
   nmesh = int(getattr(mjm, "nmesh", 0))
   ints["geom_dataid"] = A("geom_dataid", i32) if hasattr(mjm, "geom_dataid") else np.full(ngeom, -1, dtype=i32)
@@ -636,35 +637,32 @@ def get_data_into(result, mjm, d: types.Data, world_id: int = 0):
 
 
 def reset_data(m: types.Model, d: types.Data, reset=None):
-  """Resets (a masked subset of) worlds to the default state (reference io.py:1458).
+  """Clears data and sets defaults, optionally per world (reference io.py:1458).
+
+  One pass through the C ABI (mjb_reset_data: a contact-pool kernel and a per-world kernel), asynchronous on the current
+  stream and graph capturable -- the mask stays on the device.  Like the reference it resets the state (qpos = qpos0, qvel, act,
+  ctrl, qacc, qacc_warmstart, applied forces, eq_active, mocap poses, time, energy), the constraint counts, qM and the
+  contacts of the reset worlds; derived fields are recomputed by the next `forward` / `step`.
 
   Args:
     reset: optional bool tensor / array of shape (nworld,); None resets every world.
   """
-  dev = d.device
-  if reset is None:
-    mask = torch.ones(d.nworld, dtype=torch.bool, device=dev)
-  else:
-    mask = torch.as_tensor(reset, device=dev).to(torch.bool)
-  if not bool(mask.any()):
-    return
-  idx = mask.nonzero(as_tuple=True)[0]
-  for name in list(types.DATA_REAL_FIELDS) + list(types.DATA_INT_FIELDS):
-    shape = types.DATA_REAL_FIELDS.get(name) or types.DATA_INT_FIELDS.get(name)
-    if shape[0] != "nworld" or name in ("geom_xpos", "geom_xmat", "xpos", "xquat", "xmat", "xipos", "ximat", "moment_rownnz", "moment_rowadr", "moment_colind", "eq_active", "mocap_pos", "mocap_quat"):
-      continue
-    d.field(name)[idx] = 0
-  d.qpos[idx] = m.qpos0[0].unsqueeze(0).expand(idx.numel(), -1)
-  nmocap = m.sizes["nmocap"]
-  if nmocap:
-    hm = m._host
-    mocap_body = np.nonzero(hm.ints["body_mocapid"] >= 0)[0]
-    order = torch.from_numpy(mocap_body[np.argsort(hm.ints["body_mocapid"][mocap_body])]).to(dev)
-    d.mocap_pos[idx] = m.body_pos[0][order].unsqueeze(0).expand(idx.numel(), -1, -1)
-    d.mocap_quat[idx] = m.body_quat[0][order].unsqueeze(0).expand(idx.numel(), -1, -1)
-  if bool(mask.all()):
-    d.nacon.zero_()
-    d.ncollision.zero_()
+  import ctypes
+
+  from . import forward as _fw
+
+  lib = _lib.load()
+  if d.qpos.device.type != "cuda":
+    raise RuntimeError("reset_data runs on the CUDA device only: there is no CPU fallback")
+  _fw._ensure_bound(m, d)
+  ptr, mask = ctypes.c_void_p(0), None
+  if reset is not None:
+    mask = torch.as_tensor(reset, device=d.qpos.device)
+    if mask.shape != (d.nworld,):
+      raise ValueError(f"reset must have shape ({d.nworld},), got {tuple(mask.shape)}")
+    mask = (mask.view(torch.uint8) if mask.dtype == torch.bool else (mask != 0).view(torch.uint8)).contiguous()
+    ptr = ctypes.c_void_p(mask.data_ptr())
+  _lib.check(lib, lib.mjb_reset_data(m._handle, d._handle, ptr, _lib.stream_ptr()))
 
 
 def override_model(m: types.Model, overrides: dict):

@@ -58,6 +58,7 @@ MODEL_INT_FIELDS = {
   "body_rootid": ("nbody",),
   "body_weldid": ("nbody",),
   "body_mocapid": ("nbody",),
+  "eq_active0": ("neq",),
   "body_jntnum": ("nbody",),
   "body_jntadr": ("nbody",),
   "body_dofnum": ("nbody",),

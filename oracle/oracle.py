@@ -133,3 +133,101 @@ def check_tables():
       got.append(s.decode())
       i += 1
     assert got == list(names), (kind, set(got) ^ set(names))
+
+
+# ---- callers either side of `step` (test checker for mjb_get_state / mjb_set_state / mjb_reset_data / mjb_contact_force) ----
+_STATE_FIELDS = ("time", "qpos", "qvel", "act", "qacc_warmstart", "ctrl", "qfrc_applied", "xfrc_applied", "eq_active", "mocap_pos", "mocap_quat")
+
+
+def _state_segments(d, sig):
+  """[(field, column offset, width)] of the packed state row: MuJoCo mj_getState order = the bit order of the reference's
+  `State` enum (types.py:598-637), the layout support.py:572-708 writes (see mujoco_warp_b200/support.py on its two slips)."""
+  segs, adr = [], 0
+  for bit, name in enumerate(_STATE_FIELDS):
+    if sig & (1 << bit):
+      width = int(np.prod(getattr(d, name).shape[1:], dtype=np.int64))
+      segs.append((name, adr, width))
+      adr += width
+  return segs, adr
+
+
+def get_state(om, d, sig, active=None, state=None):
+  """support.py:572 get_state -> (nworld, nstate) float64; rows of inactive worlds keep the values of `state` (zeros if None)."""
+  segs, n = _state_segments(d, int(sig))
+  out = np.zeros((d.nworld, n)) if state is None else state
+  rows = np.ones(d.nworld, dtype=bool) if active is None else np.asarray(active, dtype=bool)
+  for name, adr, width in segs:
+    out[rows, adr : adr + width] = getattr(d, name).reshape(d.nworld, -1)[rows].astype(np.float64)
+  return out
+
+
+def set_state(om, d, state, sig, active=None):
+  """support.py:711 set_state."""
+  segs, _ = _state_segments(d, int(sig))
+  rows = np.ones(d.nworld, dtype=bool) if active is None else np.asarray(active, dtype=bool)
+  for name, adr, width in segs:
+    f = getattr(d, name)
+    v = np.asarray(state)[:, adr : adr + width]
+    f.reshape(d.nworld, -1)[rows] = (v != 0).astype(f.dtype)[rows] if name == "eq_active" else v[rows]
+
+
+def reset_data(om, d, reset=None):
+  """io.py:1458-1640 reset_data: contacts of the reset worlds cleared in place, then the per-world defaults."""
+  rows = np.ones(d.nworld, dtype=bool) if reset is None else np.asarray(reset, dtype=bool)
+  hm, nacon = om.hm, int(d.nacon.reshape(-1)[0])
+  wid = d.contact_worldid[:nacon]
+  clear = np.nonzero((wid < 0) | rows[np.clip(wid, 0, d.nworld - 1)])[0]  # :1622-1626
+  for name in ("dist", "pos", "frame", "includemargin", "friction", "solref", "solreffriction", "solimp", "dim", "geom", "worldid", "type", "geomcollisionid"):
+    getattr(d, "contact_" + name)[clear] = 0
+  d.contact_efc_address[clear] = -1
+  for name in ("xfrc_applied", "qM", "solver_niter", "ne", "nf", "nl", "nefc", "time", "energy", "qvel", "qacc_warmstart", "qfrc_applied", "qacc", "ctrl"):
+    getattr(d, name)[rows] = 0
+  if rows[0]:
+    d.nacon.reshape(-1)[0] = 0  # :1525 only a reset of world 0 zeroes the pooled counter
+  d.qpos[rows] = hm.reals["qpos0"].reshape(-1)
+  k = min(om.sizes["nu"], om.sizes["na"])  # :1541-1545
+  d.act[rows, :k] = 0
+  d.act_dot[rows, :k] = 0
+  if om.sizes["neq"]:
+    d.eq_active[rows] = hm.ints["eq_active0"]
+  for b, mid in enumerate(hm.ints["body_mocapid"]):
+    if mid >= 0:
+      d.mocap_pos.reshape(d.nworld, -1, 3)[rows, mid] = hm.reals["body_pos"].reshape(-1, 3)[b]
+      d.mocap_quat.reshape(d.nworld, -1, 4)[rows, mid] = hm.reals["body_quat"].reshape(-1, 4)[b]
+
+
+def contact_force(om, d, contact_ids, to_world_frame, cone=None, force=None):
+  """support.py:354 contact_force (kernel :317, contact_force_fn :263, _decode_pyramid :239) -> (n, 6)."""
+  cone = int(om.opt["cone"]) if cone is None else int(cone)
+  ids = np.asarray(contact_ids).reshape(-1)
+  out = np.zeros((len(ids), 6)) if force is None else force
+  nacon, njmax = int(d.nacon.reshape(-1)[0]), int(d.sizes["njmax"])
+  adr_all = d.contact_efc_address.reshape(len(d.contact_dim), -1)
+  for t, c in enumerate(ids):
+    if c >= nacon:
+      continue  # :331 row left untouched
+    f = np.zeros(6)
+    if c >= 0:
+      w, condim, adr0 = int(d.contact_worldid[c]), int(d.contact_dim[c]), int(adr_all[c, 0])
+      frc = d.efc_force[w]
+      if adr0 >= 0:
+        if cone == 0:
+          if condim == 1:
+            f[0] = frc[adr0]
+          else:
+            for i in range(condim - 1):
+              a = adr0 + 2 * i
+              d1 = frc[a] if a < njmax else 0.0
+              d2 = frc[a + 1] if a + 1 < njmax else 0.0
+              f[0] += d1 + d2
+              f[i + 1] = (d1 - d2) * d.contact_friction[c, i]
+        else:
+          for i in range(min(condim, adr_all.shape[1])):
+            a = int(adr_all[c, i])
+            if 0 <= a < njmax:
+              f[i] = frc[a]
+      if to_world_frame:
+        fr = d.contact_frame[c].reshape(3, 3)
+        f = np.concatenate([f[:3] @ fr, f[3:] @ fr])
+    out[t] = f
+  return out

@@ -50,8 +50,15 @@ _ENUMS = {
                              mjCNSTRSTATE_CONE=4),
   "mjtStage": dict(mjSTAGE_NONE=0, mjSTAGE_POS=1, mjSTAGE_VEL=2, mjSTAGE_ACC=3),
   "mjtDataType": dict(mjDATATYPE_REAL=0, mjDATATYPE_POSITIVE=1, mjDATATYPE_AXIS=2, mjDATATYPE_QUATERNION=3),
+  "mjtState": dict(
+    mjSTATE_TIME=1 << 0, mjSTATE_QPOS=1 << 1, mjSTATE_QVEL=1 << 2, mjSTATE_ACT=1 << 3, mjSTATE_WARMSTART=1 << 4, mjSTATE_CTRL=1 << 5,
+    mjSTATE_QFRC_APPLIED=1 << 6, mjSTATE_XFRC_APPLIED=1 << 7, mjSTATE_EQ_ACTIVE=1 << 8, mjSTATE_MOCAP_POS=1 << 9, mjSTATE_MOCAP_QUAT=1 << 10,
+    mjSTATE_USERDATA=1 << 11, mjSTATE_PLUGIN=1 << 12, mjNSTATE=13, mjSTATE_PHYSICS=(1 << 1) | (1 << 2) | (1 << 3),
+    mjSTATE_FULLPHYSICS=(1 << 0) | (1 << 1) | (1 << 2) | (1 << 3) | (1 << 12),
+    mjSTATE_USER=(1 << 5) | (1 << 6) | (1 << 7) | (1 << 8) | (1 << 9) | (1 << 10) | (1 << 11), mjSTATE_INTEGRATION=(1 << 13) - 1,
+  ),
 }
-_AUTO_BITS = {"mjtState"}
+_AUTO_BITS = set()
 
 
 class _Enum:

@@ -368,6 +368,9 @@ class warray:
       for k, i in enumerate(idx):
         if not (0 <= i < self.shape[k]):
           raise IndexError(f"index {tuple(int(j) for j in idx)} out of bounds for array of shape {self.shape}")
+      dt = self.dtype
+      if isinstance(dt, type) and issubclass(dt, _Arr) and _store_through(sys._getframe(1)):
+        return self._a[tuple(int(i) for i in idx)].view(dt)  # `a[i, j][k] = v` writes the array element in Warp
       return self._elem(self._a[tuple(int(i) for i in idx)])
     if len(idx) > self.ndim:
       raise IndexError("too many indices")
@@ -534,6 +537,28 @@ def _func_native(snippet=None, **kw):
     return noop
 
   return deco
+
+
+_STORE_THROUGH = {}
+
+
+def _store_through(f):
+  """True when the subscript being evaluated in frame `f` is the target of a nested element store `a[i, j][k] = v`
+  (bytecode: BINARY_SUBSCR, simple loads of k, STORE_SUBSCR): Warp writes the array element, a copy would lose the write."""
+  key = (f.f_code, f.f_lasti)
+  r = _STORE_THROUGH.get(key)
+  if r is None:
+    ins = list(dis.get_instructions(f.f_code))
+    r = False
+    for k, i in enumerate(ins):
+      if i.offset <= f.f_lasti and (k + 1 == len(ins) or ins[k + 1].offset > f.f_lasti):
+        j = k + 1
+        while j < len(ins) and ins[j].opname in ("LOAD_FAST", "LOAD_CONST", "LOAD_DEREF", "LOAD_GLOBAL", "LOAD_FAST_CHECK"):
+          j += 1
+        r = i.opname == "BINARY_SUBSCR" and j > k + 1 and j < len(ins) and ins[j].opname == "STORE_SUBSCR"
+        break
+    _STORE_THROUGH[key] = r
+  return r
 
 
 def _tid():

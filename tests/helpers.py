@@ -194,3 +194,25 @@ def oracle_steps(om, od, mode, nstep, opt=None, nthread=1):
     else:
       O.run(om, od, "step_implicitfast" if integ == 3 else "step", opt=opt, nthread=nthread)
   return od
+
+
+# ---- support golden (tests/golden/support_golden.npz: outputs of the reference's get_state / set_state / contact_force / reset_data)
+SUPPORT_NPZ = os.path.join(ROOT, "tests", "golden", "support_golden.npz")
+SUPPORT_CASES = {"humanoid_pyramidal": "humanoid_step5", "humanoid_elliptic": "humanoid_elliptic_newton", "equality": "equality_friction_limits",
+                 "box_spheres_pyramidal": "box_and_spheres_on_plane", "box_spheres_elliptic": "box_and_spheres_on_plane"}  # fmt: skip
+SUPPORT_STATE_FIELDS = "time qpos qvel act qacc_warmstart ctrl qfrc_applied xfrc_applied eq_active mocap_pos mocap_quat".split()
+SUPPORT_RESET_FIELDS = SUPPORT_STATE_FIELDS + "qacc act_dot energy qM solver_niter ne nf nl nefc nacon".split()
+SUPPORT_CONTACT_FIELDS = ["contact_" + f for f in "dist pos frame includemargin friction solref solreffriction solimp dim geom efc_address worldid type geomcollisionid".split()]
+
+
+def load_support_case(name):
+  with np.load(SUPPORT_NPZ) as z:
+    pre = name + "/"
+    return {k[len(pre):]: z[k] for k in z.files if k.startswith(pre)}
+
+
+def support_fill(rec, prefix, fields, assign):
+  """Calls assign(field, array) for every `prefix + field` entry of a support golden record."""
+  for f in fields:
+    if prefix + f in rec:
+      assign(f, rec[prefix + f])

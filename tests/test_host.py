@@ -177,21 +177,12 @@ def test_put_data_tiles_host_state_and_get_data_into_reads_it_back(humanoid):
   assert out.qvel.dtype == np.float64 and out.nefc == 0 and out.ncon == 0
 
 
-def test_reset_data_masked(humanoid):
+def test_reset_data_needs_the_device(humanoid):
+  """reset_data is a CUDA kernel behind the C ABI (mjb_reset_data); like `step` it has no CPU path (tests/test_gpu_support.py)."""
   m = mjw.put_model(humanoid, device="cpu")
   d = mjw.make_data(humanoid, nworld=4, nconmax=24, njmax=64, device="cpu")
-  d.qpos.add_(0.5)
-  d.qvel.fill_(2.0)
-  d.qacc_warmstart.fill_(3.0)
-  d.time.fill_(9.0)
-  mjw.reset_data(m, d, reset=np.array([True, False, True, False]))
-  for w in (0, 2):
-    np.testing.assert_allclose(d.qpos[w].numpy(), np.asarray(humanoid.qpos0), rtol=1e-6)
-    assert float(d.qvel[w].abs().max()) == 0 and float(d.time[w]) == 0 and float(d.qacc_warmstart[w].abs().max()) == 0
-  for w in (1, 3):
-    assert float(d.qvel[w, 0]) == 2.0 and float(d.time[w]) == 9.0
-  mjw.reset_data(m, d)
-  assert float(d.qvel.abs().max()) == 0
+  with pytest.raises(RuntimeError, match="no CPU fallback"):
+    mjw.reset_data(m, d, reset=np.array([True, False, True, False]))
 
 
 def test_override_model_accepts_reference_style_keys(humanoid):
