@@ -649,12 +649,12 @@ def reset_data(m: types.Model, d: types.Data, reset=None):
   """
   import ctypes
 
-  from . import forward as _fw
+  from .forward import _ensure_bound
 
   lib = _lib.load()
   if d.qpos.device.type != "cuda":
     raise RuntimeError("reset_data runs on the CUDA device only: there is no CPU fallback")
-  _fw._ensure_bound(m, d)
+  _ensure_bound(m, d)
   ptr, mask = ctypes.c_void_p(0), None
   if reset is not None:
     mask = torch.as_tensor(reset, device=d.qpos.device)
