@@ -108,6 +108,11 @@ CASES = {
   # and ctrl clamps, active joint limits, plane-box and plane-capsule contacts; mesh geoms are visual-only (contype 0)
   "panda_step3": dict(model="panda", nworld=10, seed=50, mode="step", nstep=3, nconmax=8, njmax=40, states="panda"),
   "panda_deep_forward": dict(model="panda", nworld=10, seed=43, mode="forward", nconmax=8, njmax=80, states="panda"),
+  # BASELINE config 4 (benchmarks/apptronik_apollo/scene_flat.xml: nv 25, frictionloss on every joint, position actuators with force
+  # ranges, capsule / box feet on the plane, eulerdamp disabled, timestep 5 ms).  Its box geoms carry a margin, which the reference
+  # only accepts with NATIVECCD disabled (io.py:386-395): box-box then runs the box_box primitive.
+  "apollo_forward": dict(model="apollo", nworld=4, seed=31, sink=0.04, mode="forward", nconmax=16, njmax=96, states="humanoid", disable=["NATIVECCD"]),
+  "apollo_step3": dict(model="apollo", nworld=3, seed=32, sink=0.03, mode="step", nstep=3, nconmax=16, njmax=64, states="humanoid", disable=["NATIVECCD"]),
   "convex_pairs_collision": dict(model="convex_pairs", nworld=12, seed=4, mode="forward", nconmax=48, njmax=200, states="box_pairs"),
   "mesh_pairs_collision": dict(model="mesh_pairs", nworld=12, seed=9, mode="forward", nconmax=48, njmax=200, states="box_pairs"),
 }
@@ -116,6 +121,8 @@ CASES = {
 def load_model(key):
   if key == "humanoid":
     return mjw.load_mjcf(H.HUMANOID)
+  if key == "apollo":
+    return mjw.load_mjcf(os.path.join(ROOT, "benchmarks", "apptronik_apollo", "scene_flat.xml"))
   if key == "panda":
     return mjw.load_mjcf(os.path.join(ROOT, "benchmarks", "franka_emika_panda", "scene.xml"))
   return mjw.load_mjcf_string(TM.XML[key])

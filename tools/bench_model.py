@@ -16,7 +16,8 @@ import torch
 import mujoco_warp_b200 as mjw
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-MODELS = {"panda": ("benchmarks/franka_emika_panda/scene.xml", 32768, 1, 5), "humanoid": ("benchmarks/humanoid/humanoid.xml", 8192, 24, 64)}
+MODELS = {"panda": ("benchmarks/franka_emika_panda/scene.xml", 32768, 1, 5), "humanoid": ("benchmarks/humanoid/humanoid.xml", 8192, 24, 64),
+          "apollo": ("benchmarks/apptronik_apollo/scene_flat.xml", 8192, 16, 64)}  # reference benchmarks/config.txt:17
 
 
 def main():
@@ -30,8 +31,12 @@ def main():
   d = mjw.make_data(mjm, nworld=nworld, nconmax=nconmax, njmax=njmax)
   if mjm.nkey:
     d.qpos.copy_(torch.tensor(mjm.key_qpos[0], dtype=torch.float32, device="cuda").expand(nworld, -1))
+  center = None
+  if mjm.nkey and getattr(mjm, "key_ctrl", None) is not None and mjm.nu:  # noise centred on the keyframe controls (testspeed.py:286)
+    center = torch.tensor(mjm.key_ctrl[0], dtype=torch.float32, device="cuda").expand(nworld, -1).contiguous()
+    d.ctrl.copy_(center)
   for i in range(20):
-    mjw.ctrl_noise(m, d, i)
+    mjw.ctrl_noise(m, d, i, ctrl_center=center)
     mjw.step(m, d)
   torch.cuda.synchronize()
   g = torch.cuda.CUDAGraph()
