@@ -10,6 +10,7 @@ import ctypes
 import os
 import subprocess
 import threading
+import time
 
 import torch
 
@@ -60,9 +61,11 @@ def build(force: bool = False, verbose: bool = False) -> str:
     obj = os.path.join(objdir, os.path.splitext(os.path.basename(src))[0] + ".o")
     deps = [src] + sorted(_includes(src))
     if force or not os.path.exists(obj) or any(os.path.getmtime(obj) < os.path.getmtime(p) for p in deps):
+      started = time.time()
       res = subprocess.run(["nvcc"] + common + ["-c", src, "-o", obj], capture_output=True, text=True)
       if res.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+      os.utime(obj, (started, started))  # a header edited while the unit compiled must trigger the next rebuild
       if verbose:
         print(res.stderr)
       relink = True

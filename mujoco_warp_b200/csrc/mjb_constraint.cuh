@@ -101,6 +101,100 @@ __device__ __forceinline__ int emit_simple_rows(const KParams& K, int w, int lan
   return nefc + __popc(mask);
 }
 
+// constraint.py:125-364 _equality_connect and :793-1108 _equality_weld (between bodies, dense Jacobian): one equality at a
+// time (they are few), lane = dof for the 3 / 6 Jacobian rows, lanes 0..5 finish the rows.  Returns the new nefc.
+__device__ __noinline__ int emit_connect_weld(const KParams& K, const unsigned char* mb, int w, int lane, int nefc, int& ne) {
+  const int nv = K.ms.nv, np = K.ms.nv_pad, njmax = K.dsz.njmax;
+  const float* qvel = DW(qvel);
+  const float* scom = DW(subtree_com);
+  const float* cdof = DW(cdof);
+  for (int k = 0; k < K.ms.neqconnect + K.ms.neqweld; k++) {
+    const bool weld = k >= K.ms.neqconnect;
+    const int eq = weld ? MI(eq_wld_adr)[k - K.ms.neqconnect] : MI(eq_connect_adr)[k];
+    if (DW(eq_active)[eq] == 0) continue;  // warp-uniform
+    const int nrow = weld ? 6 : 3, r0 = nefc;
+    ne += nrow;
+    nefc += nrow;
+    if (r0 >= njmax - nrow) continue;  // :186 / :855 (sic)
+    const float* data = MR(eq_data) + 11 * eq;
+    int b1 = MI(eq_obj1id)[eq], b2 = MI(eq_obj2id)[eq];
+    const bool site = K.ms.nsite > 0 && MI(eq_objtype)[eq] == 6;  // mjOBJ_SITE: the site frames are constrained (:203-208, :868-877)
+    const float torquescale = weld ? data[10] : 0.f;
+    V3 pos1, pos2;
+    Q4 quat{1.f, 0.f, 0.f, 0.f}, quat1{1.f, 0.f, 0.f, 0.f};
+    if (site) {
+      const int s1 = b1, s2 = b2;
+      pos1 = ld3(DW(site_xpos) + 3 * s1);
+      pos2 = ld3(DW(site_xpos) + 3 * s2);
+      b1 = MI(site_bodyid)[s1];
+      b2 = MI(site_bodyid)[s2];
+      if (weld) {
+        quat = mul_quat(ld4(DW(xquat) + 4 * b1), ld4(MR(site_quat) + 4 * s1));
+        const Q4 q2 = mul_quat(ld4(DW(xquat) + 4 * b2), ld4(MR(site_quat) + 4 * s2));
+        quat1 = Q4{q2.w, -q2.x, -q2.y, -q2.z};
+      }
+    } else {
+      // connect: anchor1 = data[0:3] in body1, data[3:6] in body2.  weld: data[3:6] in body1, data[0:3] in body2.
+      pos1 = ld3(DW(xpos) + 3 * b1) + mat_vec(ldm3(DW(xmat) + 9 * b1), ld3(data + (weld ? 3 : 0)));
+      pos2 = ld3(DW(xpos) + 3 * b2) + mat_vec(ldm3(DW(xmat) + 9 * b2), ld3(data + (weld ? 0 : 3)));
+      if (weld) {
+        quat = mul_quat(ld4(DW(xquat) + 4 * b1), ld4(data + 6));
+        const Q4 q2 = ld4(DW(xquat) + 4 * b2);
+        quat1 = Q4{q2.w, -q2.x, -q2.y, -q2.z};
+      }
+    }
+    const V3 cpos = pos1 - pos2;
+    const V3 off1 = pos1 - ld3(scom + 3 * MI(body_rootid)[b1]), off2 = pos2 - ld3(scom + 3 * MI(body_rootid)[b2]);
+    float S[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int d0 = 0; d0 < np; d0 += 32) {
+      const int dof = d0 + lane;
+      float J[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (dof < nv) {  // support.jac_dof (support.py:397): zero unless the dof's body is an ancestor-or-self of the body
+        const int db = MI(dof_bodyid)[dof], dend = MI(body_subtreeend)[db];
+        const bool in1 = db <= b1 && b1 < dend, in2 = db <= b2 && b2 < dend;
+        const S6 cd = ld6(cdof + 6 * dof);
+        const V3 ang = top(cd), lin = bot(cd), zero{0.f, 0.f, 0.f};
+        const V3 jp = (in1 ? lin + cross(ang, off1) : zero) - (in2 ? lin + cross(ang, off2) : zero);
+        J[0] = jp.x; J[1] = jp.y; J[2] = jp.z;
+        if (weld) {
+          const V3 dr = ((in1 ? ang : zero) - (in2 ? ang : zero)) * torquescale;
+          const Q4 qa{-quat1.x * dr.x - quat1.y * dr.y - quat1.z * dr.z, quat1.w * dr.x + quat1.y * dr.z - quat1.z * dr.y,
+                      quat1.w * dr.y + quat1.z * dr.x - quat1.x * dr.z, quat1.w * dr.z + quat1.x * dr.y - quat1.y * dr.x};  // math.py:34
+          const Q4 qb = mul_quat(qa, quat);
+          J[3] = 0.5f * qb.x; J[4] = 0.5f * qb.y; J[5] = 0.5f * qb.z;
+        }
+        const float qv = qvel[dof];
+#pragma unroll
+        for (int a = 0; a < 6; a++) S[a] += J[a] * qv;
+      }
+      if (dof < np) {
+#pragma unroll
+        for (int a = 0; a < 6; a++)
+          if (a < nrow) DW(efc_J)[(size_t)(r0 + a) * np + dof] = J[a];
+      }
+    }
+#pragma unroll
+    for (int a = 0; a < 6; a++) S[a] = warp_sum(S[a]);
+    V3 crot{0.f, 0.f, 0.f};
+    if (weld) {
+      const Q4 cq = mul_quat(quat1, quat);
+      crot = V3{cq.x, cq.y, cq.z} * torquescale;
+    }
+    const float pos_imp = weld ? sqrtf(dot(cpos, cpos) + dot(crot, crot)) : norm(cpos);
+    if (lane < nrow) {
+      const float err[6] = {cpos.x, cpos.y, cpos.z, crot.x, crot.y, crot.z};
+      float e_pos = err[0], e_vel = S[0];
+#pragma unroll
+      for (int a = 1; a < 6; a++) { e_pos = (lane == a) ? err[a] : e_pos; e_vel = (lane == a) ? S[a] : e_vel; }
+      const int comp = lane < 3 ? 0 : 1;  // translational / rotational inverse weight
+      const float invweight = MR(body_invweight0)[2 * b1 + comp] + MR(body_invweight0)[2 * b2 + comp];
+      const EfcRow e = efc_row(K, e_pos, pos_imp, invweight, MR(eq_solref) + 2 * eq, MR(eq_solimp) + 5 * eq, 0.f, e_vel, 0.f);
+      store_row(K, w, r0 + lane, e, CT_EQUALITY, eq);
+    }
+  }
+  return nefc;
+}
+
 // ELL: elliptic friction cones (constraint.py:1940 _contact_elliptic) instead of pyramids (:1669).
 template <bool ELL>
 __device__ __forceinline__ void s_make_constraint(const KParams& K, const unsigned char* mb, int w, int lane) {
@@ -110,8 +204,9 @@ __device__ __forceinline__ void s_make_constraint(const KParams& K, const unsign
   const float* qvel = DW(qvel);
   const int dsbl = K.o.disableflags;
   if (!(dsbl & DSBL_CONSTRAINT)) {
-    if (!(dsbl & DSBL_EQUALITY)) {  // constraint.py:368-497
-      for (int k0 = 0; k0 < K.ms.neqjnt; k0 += 32) {
+    if (!(dsbl & DSBL_EQUALITY)) {
+      if (K.ms.neqconnect + K.ms.neqweld > 0) nefc = emit_connect_weld(K, mb, w, lane, nefc, ne);
+      for (int k0 = 0; k0 < K.ms.neqjnt; k0 += 32) {  // constraint.py:368-497
         const int k = k0 + lane;
         bool active = false;
         EfcRow e = {};

@@ -132,10 +132,13 @@ __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group
     } else if constexpr (G == G_CON) {
       s_make_constraint<(V & 1) != 0>(K, mb, w, lane);
     } else if constexpr (G == G_VEL) {
+      const bool energy = (st & MJB_STAGE_ZERO_SENSOR) && (K.o.enableflags & 2);  // EnableBit.ENERGY (forward.py:975)
       if (st & MJB_STAGE_ZERO_SENSOR) {
-        if (lane < 2) DW(energy)[lane] = 0.f;
+        if (energy) s_energy_pos(K, mb, w, lane);
+        else if (lane < 2) DW(energy)[lane] = 0.f;
       }
       if (st & MJB_STAGE_FWD_VELOCITY) s_fwd_velocity(K, mb, w, lane);
+      if (energy && (st & MJB_STAGE_FWD_VELOCITY)) s_energy_vel(K, w, lane);
       if (st & MJB_STAGE_FWD_ACTUATION) s_fwd_actuation(K, mb, w, lane);
       if (st & (MJB_STAGE_FWD_ACCELERATION | MJB_STAGE_FWD_ACC_FACTOR)) s_fwd_acceleration(K, mb, w, lane, scr, (st & MJB_STAGE_FWD_ACC_FACTOR) != 0);
     } else if constexpr (G == G_SOL) {

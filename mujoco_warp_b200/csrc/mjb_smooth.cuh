@@ -717,6 +717,24 @@ __device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned 
       DW(qfrc_passive)[da + i] = sp[i] + dm;
     }
   }
+  // passive.py:246-272 _gravity_force + :536-565: gravity compensation through the CoM Jacobian (support.jac_dof), lane = dof
+  if (K.ms.ngravcomp && !(K.o.disableflags & DSBL_GRAVITY) && !(dsbl_spring && dsbl_damper)) {
+    __syncwarp();
+    const V3 g{K.o.gravity_x, K.o.gravity_y, K.o.gravity_z};
+    for (int dof = lane; dof < K.ms.nv; dof += 32) {
+      const int db = MI(dof_bodyid)[dof], dend = MI(body_subtreeend)[db];
+      const S6 cd = ld6(DW(cdof) + 6 * dof);
+      float q = 0.f;
+      for (int b = db; b < dend; b++) {  // bodies the dof moves: its own body's subtree
+        const float gc = MR(body_gravcomp)[b];
+        if (gc == 0.f) continue;
+        const V3 off = ld3(DW(xipos) + 3 * b) - ld3(DW(subtree_com) + 3 * MI(body_rootid)[b]);
+        q += dot(bot(cd) + cross(top(cd), off), g * (-MR(body_mass)[b] * gc));
+      }
+      DW(qfrc_gravcomp)[dof] = q;
+      if (!MI(jnt_actgravcomp)[MI(dof_jntid)[dof]]) DW(qfrc_passive)[dof] += q;
+    }
+  }
   // com_vel + cacc, level-synchronous (cacc needs cdof_dot of the same body only)
   if (lane < 6) {
     cvel[lane] = 0.f;
@@ -1010,4 +1028,53 @@ __device__ __forceinline__ void s_integrate(const KParams& K, const unsigned cha
     if (st) DW(status)[0] |= st;
   }
   __syncwarp();
+}
+
+// sensor.energy_pos (sensor.py:2854): potential energy = -sum_b m_b g . xipos_b + joint springs (:2704-2812); energy[1] = 0.
+__device__ __noinline__ void s_energy_pos(const KParams& K, const unsigned char* mb, int w, int lane) {
+  float e = 0.f;
+  if (!(K.o.disableflags & DSBL_GRAVITY)) {
+    const V3 g{K.o.gravity_x, K.o.gravity_y, K.o.gravity_z};
+    for (int b = 1 + lane; b < K.ms.nbody; b += 32) e -= MR(body_mass)[b] * dot(g, ld3(DW(xipos) + 3 * b));
+  }
+  if (!(K.o.disableflags & DSBL_SPRING)) {
+    const float* qpos = DW(qpos);
+    for (int j = lane; j < K.ms.njnt; j += 32) {
+      const float k = MR(jnt_stiffness)[j];
+      if (k == 0.f) continue;
+      const int qa = MI(jnt_qposadr)[j], t = MI(jnt_type)[j];
+      const float* qs = MR(qpos_spring) + qa;
+      if (t == JNT_FREE || t == JNT_BALL) {
+        float s = 0.f;
+        int qo = 0;
+        if (t == JNT_FREE) {
+          const V3 d0 = ld3(qpos + qa) - ld3(qs);
+          s = dot(d0, d0);
+          qo = 3;
+        }
+        const V3 dif = quat_sub(normalize(ld4(qpos + qa + qo)), ld4(qs + qo));
+        e += 0.5f * k * (s + dot(dif, dif));
+      } else {
+        const float dq = qpos[qa] - qs[0];
+        e += 0.5f * k * dq * dq;
+      }
+    }
+  }
+  e = warp_sum(e);
+  if (lane == 0) { DW(energy)[0] = e; DW(energy)[1] = 0.f; }
+}
+
+// sensor.energy_vel (sensor.py:2922): kinetic energy = 0.5 qvel^T M qvel (dense qM)
+__device__ __noinline__ void s_energy_vel(const KParams& K, int w, int lane) {
+  const int nv = K.ms.nv, np = K.ms.nv_pad;
+  const float* qvel = DW(qvel);
+  float e = 0.f;
+  for (int i = lane; i < nv; i += 32) {
+    const float* row = DW(qM) + (size_t)i * np;
+    float s = 0.f;
+    for (int j = 0; j < nv; j++) s += row[j] * qvel[j];
+    e += qvel[i] * s;
+  }
+  e = warp_sum(e);
+  if (lane == 0) DW(energy)[1] = 0.5f * e;
 }

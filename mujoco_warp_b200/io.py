@@ -95,14 +95,14 @@ def _check_supported(mjm):
   for t in np.asarray(mjm.actuator_trntype):
     if int(t) not in (C.TrnType.JOINT, C.TrnType.JOINTINPARENT):
       raise NotImplementedError("only joint / jointinparent actuator transmissions are implemented.")
-  for t in np.asarray(mjm.eq_type):
-    if int(t) != C.EqType.JOINT:
-      raise NotImplementedError("only joint equality constraints are implemented.")
+  for i, t in enumerate(np.asarray(mjm.eq_type)):
+    if int(t) not in (C.EqType.JOINT, C.EqType.CONNECT, C.EqType.WELD):
+      raise NotImplementedError("only connect / weld / joint equality constraints are implemented.")
+    if int(t) != C.EqType.JOINT and int(np.asarray(getattr(mjm, "eq_objtype", np.ones(mjm.neq)))[i]) not in (1, 6):
+      raise NotImplementedError("connect / weld equality constraints are implemented between bodies or sites only.")
   for arr, bad in ((mjm.actuator_dyntype, (C.DynType.MUSCLE, C.DynType.USER)), (mjm.actuator_gaintype, (C.GainType.MUSCLE, C.GainType.USER)), (mjm.actuator_biastype, (C.BiasType.MUSCLE, C.BiasType.USER))):
     if np.isin(np.asarray(arr), [int(b) for b in bad]).any():
       raise NotImplementedError("muscle / user actuators are not implemented.")
-  if (np.asarray(mjm.body_gravcomp) != 0).any():
-    raise NotImplementedError("gravity compensation is not implemented yet.")
   if float(mjm.opt.density) > 0 or float(mjm.opt.viscosity) > 0 or np.asarray(mjm.opt.wind).any():
     raise NotImplementedError("fluid forces are not implemented yet.")
 
@@ -182,7 +182,10 @@ def host_model(mjm) -> SimpleNamespace:
   if ints["jnt_limited_ball_adr"].size:
     raise NotImplementedError("ball joint limits are not implemented yet.")
   ints["dof_friction_adr"] = np.nonzero(reals["dof_frictionloss"] > 0)[0].astype(i32)
+  ints["eq_objtype"] = np.asarray(getattr(mjm, "eq_objtype", np.ones(int(mjm.neq)))).astype(i32).reshape(-1)  # mjtObj: 1 body, 3 joint, 6 site
   ints["eq_jnt_adr"] = np.nonzero(ints["eq_type"] == C.EqType.JOINT)[0].astype(i32)
+  ints["eq_connect_adr"] = np.nonzero(ints["eq_type"] == C.EqType.CONNECT)[0].astype(i32)  # reference io.py:445-446
+  ints["eq_wld_adr"] = np.nonzero(ints["eq_type"] == C.EqType.WELD)[0].astype(i32)
 
   # static geoms: attached to the world and not descended from a mocap body (smooth.py:195)
   bodyid = ints["geom_bodyid"]
@@ -271,7 +274,8 @@ def host_model(mjm) -> SimpleNamespace:
     nq=int(mjm.nq), nv=nv, nu=nu, na=int(mjm.na), nbody=nbody, njnt=njnt, ngeom=ngeom, nsite=int(mjm.nsite),
     nmocap=int(mjm.nmocap), neq=int(mjm.neq), npair=npair, nxn=nxn, nlevel=nlevel, nv_pad=nv_pad,
     nlimit=int(ints["jnt_limited_adr"].size), nlimitball=int(ints["jnt_limited_ball_adr"].size),
-    nfrictiondof=int(ints["dof_friction_adr"].size), neqjnt=int(ints["eq_jnt_adr"].size), nJmom=nJmom,
+    nfrictiondof=int(ints["dof_friction_adr"].size), neqjnt=int(ints["eq_jnt_adr"].size), neqconnect=int(ints["eq_connect_adr"].size),
+    neqweld=int(ints["eq_wld_adr"].size), nJmom=nJmom,
     nmaxcondim=nmaxcondim, nmaxpyramid=int(max(1, 2 * (nmaxcondim - 1))),
     ngravcomp=int((reals["body_gravcomp"] != 0).sum()), is_sparse=int(sparse), nM=int(getattr(mjm, "nM", 0)),
     ntree=int(getattr(mjm, "ntree", 0)), ngeompair=int(len(geom1)), nmesh=nmesh, nmeshvert=int(reals["mesh_vert"].shape[0]),

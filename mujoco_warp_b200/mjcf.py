@@ -1068,6 +1068,23 @@ def _finalize_constraints(m, root, comp, defaults):
         m.eq_obj2id[i] = m.jnt_names.index(a["joint2"])
       pc = _vec(a.get("polycoef"), None, [0, 1, 0, 0, 0])
       m.eq_data[i, : pc.size] = pc
+    elif tag in ("connect", "weld"):
+      # body1 / body2 (world when absent); the qpos0-dependent half of eq_data is filled by _set_const like mj_setConst does
+      m.eq_type[i] = C.EqType.CONNECT if tag == "connect" else C.EqType.WELD
+      if "site1" in a:  # the site poses define the constraint frames (reference constraint.py:203-208, :868-877); eq_data is unused
+        m.eq_objtype[i] = 6  # mjOBJ_SITE
+        m.eq_obj1id[i] = m.site_names.index(a["site1"])
+        m.eq_obj2id[i] = m.site_names.index(a["site2"])
+      else:
+        m.eq_objtype[i] = 1  # mjOBJ_BODY
+        m.eq_obj1id[i] = m.body_names.index(a["body1"])
+        m.eq_obj2id[i] = m.body_names.index(a["body2"]) if "body2" in a else 0
+      m.eq_data[i, :3] = _vec(a.get("anchor"), 3, [0, 0, 0])
+      if tag == "weld":
+        rel = _vec(a.get("relpose"), 7, [0, 1, 0, 0, 0, 0, 0])
+        if np.any(rel[3:] != 0):
+          raise NotImplementedError("weld with an explicit relpose quaternion is not supported by mjcf lite yet")
+        m.eq_data[i, 10] = float(a.get("torquescale", 1.0))
     else:
       raise NotImplementedError(f"equality <{tag}> is not supported by mjcf lite yet")
 
@@ -1281,6 +1298,20 @@ def _set_const(m):
     elif rot < mjMINVAL and tr > mjMINVAL:
       rot = tr
     m.body_invweight0[b] = [tr, rot]
+  # connect / weld: anchors and relative pose at qpos0 (MuJoCo engine_setconst.c set0)
+  k = aux.kin
+  for i in range(m.neq):
+    b1, b2 = int(m.eq_obj1id[i]), int(m.eq_obj2id[i])
+    if m.eq_objtype[i] != 1:
+      continue
+    if m.eq_type[i] == C.EqType.CONNECT:  # data[0:3] anchor in body1, data[3:6] the same point in body2
+      world = k.xpos[b1] + k.xmat[b1] @ m.eq_data[i, :3]
+      m.eq_data[i, 3:6] = k.xmat[b2].T @ (world - k.xpos[b2])
+    elif m.eq_type[i] == C.EqType.WELD:  # data[0:3] anchor in body2, data[3:6] the same point in body1, data[6:10] = q1^-1 q2
+      world = k.xpos[b2] + k.xmat[b2] @ m.eq_data[i, :3]
+      m.eq_data[i, 3:6] = k.xmat[b1].T @ (world - k.xpos[b1])
+      q1 = k.xquat[b1] * np.array([1.0, -1.0, -1.0, -1.0])
+      m.eq_data[i, 6:10] = quat_mul(q1, k.xquat[b2])
   # actuator_acc0 = |M^-1 moment| for joint transmissions
   for i in range(m.nu):
     j = m.actuator_trnid[i, 0]

@@ -50,7 +50,7 @@ TILE_SIZE_JTDAJ_DENSE = 16  # reference types.py:35
 # ----------------------------------------------------------------------------------------------
 MODEL_SIZES = (
   "nq nv nu na nbody njnt ngeom nsite nmocap neq npair nxn nlevel nv_pad nlimit nlimitball "
-  "nfrictiondof neqjnt nJmom nmaxcondim nmaxpyramid ngravcomp is_sparse nM ntree ngeompair nmesh nmeshvert"
+  "nfrictiondof neqjnt nJmom nmaxcondim nmaxpyramid ngravcomp is_sparse nM ntree ngeompair nmesh nmeshvert neqconnect neqweld"
 ).split()
 
 MODEL_INT_FIELDS = {
@@ -102,7 +102,10 @@ MODEL_INT_FIELDS = {
   "eq_type": ("neq",),
   "eq_obj1id": ("neq",),
   "eq_obj2id": ("neq",),
+  "eq_objtype": ("neq",),
   "eq_jnt_adr": ("neqjnt",),
+  "eq_connect_adr": ("neqconnect",),
+  "eq_wld_adr": ("neqweld",),
   "geom_dataid": ("ngeom",),
   "mesh_vertadr": ("nmesh",),
   "mesh_vertnum": ("nmesh",),

@@ -44,6 +44,8 @@ enum { GEOM_PLANE = 0, GEOM_HFIELD, GEOM_SPHERE, GEOM_CAPSULE, GEOM_ELLIPSOID, G
 enum { DSBL_CONSTRAINT = 1, DSBL_EQUALITY = 2, DSBL_FRICTIONLOSS = 4, DSBL_LIMIT = 8, DSBL_CONTACT = 16,
        DSBL_SPRING = 32, DSBL_DAMPER = 64, DSBL_GRAVITY = 128, DSBL_CLAMPCTRL = 256, DSBL_WARMSTART = 512,
        DSBL_ACTUATION = 2048, DSBL_REFSAFE = 4096, DSBL_EULERDAMP = 32768 };
+enum { ENBL_ENERGY = 2 };
+enum { OBJ_BODY = 1, OBJ_SITE = 6 }; /* mjtObj values of eq_objtype */ /* types.py EnableBit.ENERGY */
 enum { CT_EQUALITY = 0, CT_FRICTION_DOF = 1, CT_LIMIT_JOINT = 3, CT_CONTACT_FRICTIONLESS = 5,
        CT_CONTACT_PYRAMIDAL = 6, CT_CONTACT_ELLIPTIC = 7 };
 enum { ST_SATISFIED = 0, ST_QUADRATIC = 1, ST_LINEARNEG = 2, ST_LINEARPOS = 3, ST_CONE = 4 };
@@ -1422,13 +1424,148 @@ static void jac_dof(const OModel* m, const OData* d, const real* point, int body
   for (int i = 0; i < 3; i++) { jacp[i] = cd[3 + i] + c[i]; jacr[i] = cd[i]; }
 }
 
+/* sensor.py:2854 energy_pos: potential energy = -sum m g.xipos + joint springs (:2704-2812) */
+static void o_energy_pos(const OModel* m, const OOpt* o, OData* d) {
+  real e = 0;
+  if (!(o->disableflags & DSBL_GRAVITY)) {
+    real g[3] = {o->gravity_x, o->gravity_y, o->gravity_z};
+    for (int b = 1; b < m->nbody; b++) e -= m->body_mass[b] * dot3(g, d->xipos + 3 * b);
+  }
+  if (!(o->disableflags & DSBL_SPRING)) {
+    for (int j = 0; j < m->njnt; j++) {
+      real k = m->jnt_stiffness[j];
+      if (k == 0.0) continue;
+      int pa = m->jnt_qposadr[j], t = m->jnt_type[j];
+      const real *q = d->qpos + pa, *qs = m->qpos_spring + pa;
+      if (t == JNT_FREE || t == JNT_BALL) {
+        real s = 0, quat[4], dif[3];
+        int qo = 0;
+        if (t == JNT_FREE) { for (int i = 0; i < 3; i++) s += (q[i] - qs[i]) * (q[i] - qs[i]); qo = 3; }
+        memcpy(quat, q + qo, sizeof(quat));
+        normalize4(quat);
+        quat_sub(dif, quat, qs + qo);
+        e += 0.5 * k * (s + dot3(dif, dif));
+      } else {
+        e += 0.5 * k * (q[0] - qs[0]) * (q[0] - qs[0]);
+      }
+    }
+  }
+  d->energy[0] = e;
+  d->energy[1] = 0;
+}
+/* sensor.py:2922 energy_vel: kinetic energy = 0.5 qvel^T M qvel */
+static void o_energy_vel(const OModel* m, OData* d) {
+  real e = 0;
+  for (int i = 0; i < m->nv; i++) {
+    real s = 0;
+    for (int j = 0; j < m->nv; j++) s += d->qM[i * m->nv_pad + j] * d->qvel[j];
+    e += d->qvel[i] * s;
+  }
+  d->energy[1] = 0.5 * e;
+}
+
 static void o_make_constraint(const OModel* m, const OOpt* o, OData* d, const OData* glob) {
   int nv = m->nv, np = m->nv_pad, njmax = glob->njmax, nefc = 0;
   d->ne[0] = d->nf[0] = d->nl[0] = d->nefc[0] = 0;
   if (o->disableflags & DSBL_CONSTRAINT) return;
   real ts = o->timestep;
   (void)ts;
-  if (!(o->disableflags & DSBL_EQUALITY)) { /* constraint.py:368-497 joint equality */
+  if (!(o->disableflags & DSBL_EQUALITY)) {
+    for (int k = 0; k < m->neqconnect; k++) { /* constraint.py:125-364 connect (bodies) */
+      int eq = m->eq_connect_adr[k];
+      if (!d->eq_active[eq]) continue;
+      d->ne[0] += 3;
+      int r = nefc;
+      nefc += 3;
+      if (r >= njmax - 3) continue; /* :186 (sic) */
+      const real* data = m->eq_data + 11 * eq;
+      int b1 = m->eq_obj1id[eq], b2 = m->eq_obj2id[eq];
+      real pos1[3], pos2[3], pos[3], Jqvel[3] = {0, 0, 0}, t[3];
+      if (m->nsite > 0 && m->eq_objtype[eq] == OBJ_SITE) { /* :203-208 */
+        memcpy(pos1, d->site_xpos + 3 * b1, sizeof(pos1));
+        memcpy(pos2, d->site_xpos + 3 * b2, sizeof(pos2));
+        b1 = m->site_bodyid[b1];
+        b2 = m->site_bodyid[b2];
+      } else {
+        mat_vec(t, d->xmat + 9 * b1, data);
+        for (int i = 0; i < 3; i++) pos1[i] = d->xpos[3 * b1 + i] + t[i];
+        mat_vec(t, d->xmat + 9 * b2, data + 3);
+        for (int i = 0; i < 3; i++) pos2[i] = d->xpos[3 * b2 + i] + t[i];
+      }
+      for (int i = 0; i < 3; i++) pos[i] = pos1[i] - pos2[i];
+      for (int dof = 0; dof < nv; dof++) {
+        real jp1[3], jp2[3], jr[3];
+        jac_dof(m, d, pos1, b1, dof, jp1, jr);
+        jac_dof(m, d, pos2, b2, dof, jp2, jr);
+        for (int i = 0; i < 3; i++) {
+          d->efc_J[(size_t)(r + i) * np + dof] = jp1[i] - jp2[i];
+          Jqvel[i] += (jp1[i] - jp2[i]) * d->qvel[dof];
+        }
+      }
+      real invweight = m->body_invweight0[2 * b1] + m->body_invweight0[2 * b2], pos_imp = norm3(pos);
+      for (int i = 0; i < 3; i++)
+        efc_row(o, d, r + i, pos[i], pos_imp, invweight, m->eq_solref + 2 * eq, m->eq_solimp + 5 * eq, 0.0, Jqvel[i], 0.0, CT_EQUALITY, eq);
+    }
+    for (int k = 0; k < m->neqweld; k++) { /* constraint.py:793-1108 weld (bodies) */
+      int eq = m->eq_wld_adr[k];
+      if (!d->eq_active[eq]) continue;
+      d->ne[0] += 6;
+      int r = nefc;
+      nefc += 6;
+      if (r >= njmax - 6) continue; /* :855 (sic) */
+      const real* data = m->eq_data + 11 * eq;
+      int b1 = m->eq_obj1id[eq], b2 = m->eq_obj2id[eq];
+      real torquescale = data[10], pos1[3], pos2[3], cpos[3], t[3], quat[4], quat1[4], Jqp[3] = {0, 0, 0}, Jqr[3] = {0, 0, 0};
+      if (m->nsite > 0 && m->eq_objtype[eq] == OBJ_SITE) { /* :868-877: the site frames are welded */
+        int s1 = b1, s2 = b2;
+        real q2[4];
+        memcpy(pos1, d->site_xpos + 3 * s1, sizeof(pos1));
+        memcpy(pos2, d->site_xpos + 3 * s2, sizeof(pos2));
+        b1 = m->site_bodyid[s1];
+        b2 = m->site_bodyid[s2];
+        mul_quat(quat, d->xquat + 4 * b1, m->site_quat + 4 * s1);
+        mul_quat(q2, d->xquat + 4 * b2, m->site_quat + 4 * s2);
+        quat1[0] = q2[0];
+        for (int i = 1; i < 4; i++) quat1[i] = -q2[i];
+      } else {
+        mat_vec(t, d->xmat + 9 * b1, data + 3); /* anchor2 = data[3:6] lives in body1 */
+        for (int i = 0; i < 3; i++) pos1[i] = d->xpos[3 * b1 + i] + t[i];
+        mat_vec(t, d->xmat + 9 * b2, data);
+        for (int i = 0; i < 3; i++) pos2[i] = d->xpos[3 * b2 + i] + t[i];
+        mul_quat(quat, d->xquat + 4 * b1, data + 6);
+        quat1[0] = d->xquat[4 * b2];
+        for (int i = 1; i < 4; i++) quat1[i] = -d->xquat[4 * b2 + i];
+      }
+      for (int i = 0; i < 3; i++) cpos[i] = pos1[i] - pos2[i];
+      for (int dof = 0; dof < nv; dof++) {
+        real jp1[3], jp2[3], jr1[3], jr2[3], dr[3], qa[4], qb[4];
+        jac_dof(m, d, pos1, b1, dof, jp1, jr1);
+        jac_dof(m, d, pos2, b2, dof, jp2, jr2);
+        for (int i = 0; i < 3; i++) dr[i] = (jr1[i] - jr2[i]) * torquescale;
+        qa[0] = -quat1[1] * dr[0] - quat1[2] * dr[1] - quat1[3] * dr[2]; /* math.py:34 quat_mul_axis */
+        qa[1] = quat1[0] * dr[0] + quat1[2] * dr[2] - quat1[3] * dr[1];
+        qa[2] = quat1[0] * dr[1] + quat1[3] * dr[0] - quat1[1] * dr[2];
+        qa[3] = quat1[0] * dr[2] + quat1[1] * dr[1] - quat1[2] * dr[0];
+        mul_quat(qb, qa, quat);
+        for (int i = 0; i < 3; i++) {
+          real jp = jp1[i] - jp2[i], jr = 0.5 * qb[1 + i];
+          d->efc_J[(size_t)(r + i) * np + dof] = jp;
+          d->efc_J[(size_t)(r + 3 + i) * np + dof] = jr;
+          Jqp[i] += jp * d->qvel[dof];
+          Jqr[i] += jr * d->qvel[dof];
+        }
+      }
+      real crotq[4], crot[3];
+      mul_quat(crotq, quat1, quat);
+      for (int i = 0; i < 3; i++) crot[i] = crotq[1 + i] * torquescale;
+      real pos_imp = sqrt(dot3(cpos, cpos) + dot3(crot, crot));
+      real iw_t = m->body_invweight0[2 * b1] + m->body_invweight0[2 * b2], iw_r = m->body_invweight0[2 * b1 + 1] + m->body_invweight0[2 * b2 + 1];
+      for (int i = 0; i < 3; i++) {
+        efc_row(o, d, r + i, cpos[i], pos_imp, iw_t, m->eq_solref + 2 * eq, m->eq_solimp + 5 * eq, 0.0, Jqp[i], 0.0, CT_EQUALITY, eq);
+        efc_row(o, d, r + 3 + i, crot[i], pos_imp, iw_r, m->eq_solref + 2 * eq, m->eq_solimp + 5 * eq, 0.0, Jqr[i], 0.0, CT_EQUALITY, eq);
+      }
+    }
+    /* constraint.py:368-497 joint equality */
     for (int k = 0; k < m->neqjnt; k++) {
       int eq = m->eq_jnt_adr[k];
       if (!d->eq_active[eq]) continue;
@@ -1690,7 +1827,25 @@ static void o_fwd_velocity(const OModel* m, const OOpt* o, OData* d) {
       if (hd) for (int i = 0; i < n; i++) d->qfrc_damper[da + i] = -c * d->qvel[da + i];
     }
   }
-  for (int i = 0; i < nv; i++) d->qfrc_passive[i] = (dsbl_spring && dsbl_damper) ? 0.0 : d->qfrc_spring[i] + d->qfrc_damper[i];
+  /* passive.py:246-272 _gravity_force: gravity compensation of bodies with gravcomp != 0, through the Jacobian of their CoM */
+  int gravcomp = m->ngravcomp && !(o->disableflags & DSBL_GRAVITY) && !(dsbl_spring && dsbl_damper);
+  if (gravcomp) {
+    for (int b = 1; b < m->nbody; b++) {
+      real gc = m->body_gravcomp[b];
+      if (gc == 0.0) continue;
+      real force[3] = {-o->gravity_x * m->body_mass[b] * gc, -o->gravity_y * m->body_mass[b] * gc, -o->gravity_z * m->body_mass[b] * gc};
+      for (int dof = 0; dof < nv; dof++) {
+        real jp[3], jr[3];
+        jac_dof(m, d, d->xipos + 3 * b, b, dof, jp, jr);
+        d->qfrc_gravcomp[dof] += dot3(jp, force);
+      }
+    }
+  }
+  for (int i = 0; i < nv; i++) { /* passive.py:536-565 */
+    real q = (dsbl_spring && dsbl_damper) ? 0.0 : d->qfrc_spring[i] + d->qfrc_damper[i];
+    if (gravcomp && !m->jnt_actgravcomp[m->dof_jntid[i]]) q += d->qfrc_gravcomp[i];
+    d->qfrc_passive[i] = q;
+  }
   /* rne (flg_acc = False) */
   for (int i = 0; i < 6; i++) d->cacc[i] = 0;
   if (!(o->disableflags & DSBL_GRAVITY)) { d->cacc[3] = -o->gravity_x; d->cacc[4] = -o->gravity_y; d->cacc[5] = -o->gravity_z; }
@@ -2313,8 +2468,12 @@ int mjo_run_stages(const int* msizes, const int* const* mint, const double* cons
       if (o_collision(&m, &o, &v, &d, w) < 0) rc = -3;
     if (stages & MJB_STAGE_MAKE_CONSTRAINT) o_make_constraint(&m, &o, &v, &d);
     if (stages & MJB_STAGE_TRANSMISSION) o_transmission(&m, &v);
-    if (stages & MJB_STAGE_ZERO_SENSOR) { v.energy[0] = v.energy[1] = 0; }
+    if (stages & MJB_STAGE_ZERO_SENSOR) { /* forward.py:978-984: sensordata / energy zeroing, energy_pos when enabled */
+      v.energy[0] = v.energy[1] = 0;
+      if (o.enableflags & ENBL_ENERGY) o_energy_pos(&m, &o, &v);
+    }
     if (stages & MJB_STAGE_FWD_VELOCITY) o_fwd_velocity(&m, &o, &v);
+    if ((stages & MJB_STAGE_ZERO_SENSOR) && (stages & MJB_STAGE_FWD_VELOCITY) && (o.enableflags & ENBL_ENERGY)) o_energy_vel(&m, &v); /* :989-991 */
     if (stages & MJB_STAGE_FWD_ACTUATION) o_fwd_actuation(&m, &o, &v);
     if (stages & MJB_STAGE_FWD_ACCELERATION) o_fwd_acceleration(&m, &v, 0);
     if (stages & MJB_STAGE_FWD_ACC_FACTOR) o_fwd_acceleration(&m, &v, 1);

@@ -45,6 +45,8 @@ def run_reference(name):
     setattr(m.opt, k, v)
   for flag in c.get("disable", []):
     m.opt.disableflags |= int(getattr(types_mod.DisableBit, flag))
+  for flag in c.get("enable", []):
+    m.opt.enableflags |= int(getattr(types_mod.EnableBit, flag))
   R.set_state(d, qpos, qvel, ctrl)
   out = {"in_qpos": qpos, "in_qvel": qvel, "in_ctrl": ctrl}
   fn = ref.forward if c["mode"] == "forward" else ref.step

@@ -25,8 +25,8 @@ NPZ = os.path.join(HERE, "reference_step.npz")
 
 REAL_FIELDS = (
   "xpos xquat xmat xipos ximat xanchor xaxis geom_xpos geom_xmat subtree_com cinert cdof crb qM qLD actuator_length actuator_moment "
-  "actuator_velocity cvel cdof_dot qfrc_spring qfrc_damper qfrc_passive qfrc_bias actuator_force qfrc_actuator qfrc_smooth qacc_smooth "
-  "cacc cfrc_int qfrc_constraint qacc qacc_warmstart qpos qvel act act_dot time"
+  "actuator_velocity cvel cdof_dot qfrc_spring qfrc_damper qfrc_gravcomp qfrc_passive qfrc_bias actuator_force qfrc_actuator qfrc_smooth qacc_smooth "
+  "cacc cfrc_int qfrc_constraint qacc qacc_warmstart qpos qvel act act_dot time energy"
 ).split()
 EFC_REAL = "J pos margin D vel aref frictionloss force Ma".split()
 EFC_INT = "type id state".split()
@@ -108,6 +108,14 @@ CASES = {
   # and ctrl clamps, active joint limits, plane-box and plane-capsule contacts; mesh geoms are visual-only (contype 0)
   "panda_step3": dict(model="panda", nworld=10, seed=50, mode="step", nstep=3, nconmax=8, njmax=40, states="panda"),
   "panda_deep_forward": dict(model="panda", nworld=10, seed=43, mode="forward", nconmax=8, njmax=80, states="panda"),
+  # EnableBit.ENERGY: potential (gravity + joint springs, free / ball / hinge / slide) and kinetic energy (sensor.py:2854, :2922)
+  "humanoid_energy_step2": dict(model="humanoid", nworld=3, seed=71, mode="step", nstep=2, enable=["ENERGY"]),
+  "springs_energy_forward": dict(model="springs", nworld=4, seed=72, mode="forward", enable=["ENERGY"]),
+  "gravcomp_step3": dict(model="gravcomp", nworld=4, seed=81, mode="step", nstep=3),
+  "site_equalities_step3": dict(model="site_equalities", nworld=4, seed=91, mode="step", nstep=3, njmax=32),
+  "connect_weld_forward": dict(model="connect_weld", nworld=5, seed=61, mode="forward", njmax=48),
+  "connect_weld_step4": dict(model="connect_weld", nworld=4, seed=62, mode="step", nstep=4, njmax=48),
+  "connect_weld_njmax_overflow": dict(model="connect_weld", nworld=2, seed=63, mode="forward", njmax=16),
   # BASELINE config 4 (benchmarks/apptronik_apollo/scene_flat.xml: nv 25, frictionloss on every joint, position actuators with force
   # ranges, capsule / box feet on the plane, eulerdamp disabled, timestep 5 ms).  Its box geoms carry a margin, which the reference
   # only accepts with NATIVECCD disabled (io.py:386-395): box-box then runs the box_box primitive.
@@ -173,6 +181,10 @@ def run_oracle(name):
   for flag in c.get("disable", []):
     flags |= int(getattr(C.DisableBit, flag))
   opt["disableflags"] = flags
+  eflags = int(om.opt["enableflags"])
+  for flag in c.get("enable", []):
+    eflags |= int(getattr(C.EnableBit, flag))
+  opt["enableflags"] = eflags
   H.oracle_steps(om, od, c["mode"], c.get("nstep", 1), opt)
   return od
 
@@ -189,7 +201,7 @@ def compare(name, ref_out, od, verbose=True):
       if verbose:
         print("   count mismatch", f, a, b)
   for f in REAL_FIELDS:
-    if not hasattr(od, f):
+    if not hasattr(od, f) or f not in ref_out:  # fields added to the list after a case was recorded
       continue
     r, o = _shape_like(ref_out[f], getattr(od, f))
     if f == "cfrc_int":  # the reference never clears the world body's entry (smooth.py:1199 skips body 0, :1233 adds into it)
@@ -243,6 +255,10 @@ def case_opt(name):
   for flag in c.get("disable", []):
     flags |= int(getattr(C.DisableBit, flag))
   opt["disableflags"] = flags
+  eflags = int(mjm.opt.enableflags)
+  for flag in c.get("enable", []):
+    eflags |= int(getattr(C.EnableBit, flag))
+  opt["enableflags"] = eflags
   return opt
 
 

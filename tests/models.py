@@ -24,6 +24,72 @@ SMALL_MODELS = {
         <body pos="0.5 0.15 0.1"><freejoint/><geom type="sphere" size=".08" condim="1"/></body>
       </worldbody>
     </mujoco>""",
+  # connect (loop closure between two chains, and a body pinned to the world), weld (two free bodies; one body welded to the world
+  # with a torquescale and an anchor), an inactive weld, next to a joint equality
+  "connect_weld": """
+    <mujoco><option timestep="0.002"/>
+      <worldbody>
+        <body name="l1" pos="0 0 1"><joint name="a" type="hinge" axis="0 1 0" damping="0.05"/><geom type="capsule" size=".03 .2" fromto="0 0 0 .4 0 0"/>
+          <body name="l2" pos=".4 0 0"><joint name="b" type="hinge" axis="0 1 0"/><geom type="capsule" size=".03 .2" fromto="0 0 0 .3 0 -.2"/></body>
+        </body>
+        <body name="r1" pos=".7 0 1"><joint name="c" type="ball"/><geom type="capsule" size=".03 .1" fromto="0 0 0 0 0 -.2"/></body>
+        <body name="f1" pos="0 1 1"><freejoint/><geom type="box" size=".1 .05 .08"/></body>
+        <body name="f2" pos=".3 1 1.1" euler="10 20 30"><freejoint/><geom type="sphere" size=".07"/></body>
+        <body name="f3" pos="0 -1 1" euler="0 45 0"><freejoint/><geom type="ellipsoid" size=".1 .06 .04"/></body>
+        <body name="p1" pos="1.5 0 1"><joint name="d" type="slide" axis="0 0 1"/><joint name="e" type="hinge" axis="1 0 0"/><geom type="sphere" size=".05"/></body>
+      </worldbody>
+      <equality>
+        <connect body1="l2" body2="r1" anchor=".3 0 -.2"/>
+        <weld body1="f1" body2="f2" solref="0.01 1"/>
+        <connect body1="p1" anchor="0 .1 0" solimp="0.8 0.9 0.01 0.5 2"/>
+        <weld body1="f3" torquescale="0.5" anchor=".05 0 .02"/>
+        <weld body1="f2" body2="f3" active="false"/>
+        <joint joint1="d" joint2="e" polycoef="0 0.2 0 0 0"/>
+      </equality>
+      <actuator><motor joint="a" gear="3"/><motor joint="e" gear="1"/></actuator>
+    </mujoco>""",
+  # joint springs of every joint type (potential energy, passive forces), springref away from qpos0
+  "springs": """
+    <mujoco><option timestep="0.002"/>
+      <worldbody>
+        <body pos="0 0 1"><joint type="free" stiffness="2"/><geom type="box" size=".1 .1 .1"/></body>
+        <body pos="1 0 1"><joint type="ball" stiffness="3" damping="0.1"/><geom type="capsule" size=".05 .2" fromto="0 0 0 .3 0 0"/>
+          <body pos=".3 0 0"><joint type="hinge" axis="0 1 0" stiffness="5" springref="20"/><geom type="capsule" size=".04 .2" fromto="0 0 0 .3 0 0"/>
+            <body pos=".3 0 0"><joint type="slide" axis="1 0 0" stiffness="40" springref="0.05"/><geom type="sphere" size=".06"/></body></body>
+        </body>
+      </worldbody>
+    </mujoco>""",
+  # gravity compensation: fully and partially compensated bodies, a joint whose compensation is routed through the actuator
+  # channel (actuatorgravcomp, forward.py:806-829), a free body that floats
+  "gravcomp": """
+    <mujoco><option timestep="0.002"/>
+      <worldbody>
+        <body pos="0 0 1" gravcomp="1"><joint name="a" type="hinge" axis="0 1 0" damping="0.2"/><geom type="capsule" size=".04 .2" fromto="0 0 0 .4 0 0"/>
+          <body pos=".4 0 0" gravcomp="0.5"><joint name="b" type="hinge" axis="0 1 0" actuatorgravcomp="true" actuatorfrclimited="true" actuatorfrcrange="-2 2"/>
+            <geom type="capsule" size=".03 .2" fromto="0 0 0 .3 0 .1"/>
+            <body pos=".3 0 .1"><joint name="c" type="ball"/><geom type="box" size=".05 .04 .03" pos=".05 0 0"/></body></body>
+        </body>
+        <body pos="0 1 1" gravcomp="1"><freejoint/><geom type="sphere" size=".1"/></body>
+      </worldbody>
+      <actuator><motor joint="b" gear="1.5"/><motor joint="a"/></actuator>
+    </mujoco>""",
+  # connect / weld defined between sites (the site frames, not eq_data, give the anchors and the relative orientation)
+  "site_equalities": """
+    <mujoco><option timestep="0.002"/>
+      <worldbody>
+        <site name="w0" pos=".2 0 1.2" euler="0 0 20"/>
+        <body pos="0 0 1"><joint type="hinge" axis="0 1 0"/><geom type="capsule" size=".03 .2" fromto="0 0 0 .4 0 0"/><site name="a1" pos=".4 0 .05"/>
+          <body pos=".4 0 0"><joint type="ball"/><geom type="capsule" size=".03 .1" fromto="0 0 0 .2 0 0"/><site name="a2" pos=".2 0 0" euler="10 0 0"/></body></body>
+        <body pos=".7 0 1"><freejoint/><geom type="box" size=".05 .05 .05"/><site name="b1" pos="-.1 0 0" euler="0 15 0"/><site name="b2" pos="0 .1 0"/></body>
+        <body pos="0 1 1"><freejoint/><geom type="sphere" size=".06"/><site name="c1" pos="0 0 .1" euler="5 5 5"/></body>
+      </worldbody>
+      <equality>
+        <connect site1="a2" site2="b1"/>
+        <weld site1="c1" site2="w0" torquescale="0.8"/>
+        <connect site1="b2" site2="a1" active="false"/>
+        <weld site1="b2" site2="c1" solref="0.03 1"/>
+      </equality>
+    </mujoco>""",
   "no_constraints_no_actuators": """
     <mujoco><worldbody>
       <body pos="0 0 1"><joint type="ball"/><geom type="capsule" size=".05 .2"/>

@@ -203,3 +203,30 @@ def test_field_tables_cover_every_dataclass_field():
   assert {"J", "pos", "margin", "D", "vel", "aref", "frictionloss", "force", "state", "type", "id"} <= {
     f.name for f in dataclasses.fields(types.Constraint)
   }
+
+
+def test_connect_and_weld_equalities_compile_their_qpos0_data():
+  """MJCF-lite fills the qpos0-dependent half of eq_data like mj_setConst: connect stores the anchor in both body frames, weld the
+  anchor in both frames plus the relative orientation q1^-1 q2; site-based equalities reference site ids (mjOBJ_SITE = 6)."""
+  from tests import models as TM
+
+  mjm = mjw.load_mjcf_string(TM.SMALL_MODELS["connect_weld"])
+  assert mjm.eq_type.tolist() == [0, 1, 0, 1, 1, 2] and mjm.eq_objtype.tolist() == [1, 1, 1, 1, 1, 3]
+  assert mjm.eq_active0.tolist() == [True, True, True, True, False, True]
+  k = mjw.mjcf.host_kinematics(mjm, mjm.qpos0)
+  for i in range(mjm.neq):
+    b1, b2, data = int(mjm.eq_obj1id[i]), int(mjm.eq_obj2id[i]), mjm.eq_data[i]
+    if mjm.eq_type[i] == 0:  # the two anchors are the same world point at qpos0
+      np.testing.assert_allclose(k.xpos[b1] + k.xmat[b1] @ data[:3], k.xpos[b2] + k.xmat[b2] @ data[3:6], atol=1e-12)
+    elif mjm.eq_type[i] == 1:
+      np.testing.assert_allclose(k.xpos[b1] + k.xmat[b1] @ data[3:6], k.xpos[b2] + k.xmat[b2] @ data[:3], atol=1e-12)
+      np.testing.assert_allclose(mjw.mjcf.quat_mul(k.xquat[b1], data[6:10]), k.xquat[b2], atol=1e-12)
+  assert mjm.eq_data[3, 10] == 0.5 and mjm.eq_data[1, 10] == 1.0
+  m = mjw.put_model(mjm, device="cpu")
+  assert m.sizes["neqconnect"] == 2 and m.sizes["neqweld"] == 3 and m.sizes["neqjnt"] == 1
+  assert m.eq_connect_adr.tolist() == [0, 2] and m.eq_wld_adr.tolist() == [1, 3, 4]
+  sites = mjw.load_mjcf_string(TM.SMALL_MODELS["site_equalities"])
+  assert sites.eq_objtype.tolist() == [6, 6, 6, 6] and sites.eq_obj1id.tolist() == [sites.site_names.index(n) for n in ("a2", "c1", "b2", "b2")]
+  with pytest.raises(NotImplementedError, match="relpose"):
+    mjw.load_mjcf_string('<mujoco><worldbody><body name="a"><freejoint/><geom size=".1"/></body></worldbody>'
+                         '<equality><weld body1="a" relpose="0 0 0 1 0 0 0"/></equality></mujoco>')

@@ -317,3 +317,46 @@ def test_elliptic_solution_lies_in_the_friction_cone(humanoid):
   # the pyramid is a linearisation of the same cone: accelerations stay close
   assert np.abs(d.qacc - dp.qacc).max() < 0.2 * np.abs(dp.qacc).max()
   assert int(d.solver_niter.max()) < 30
+
+
+def test_connect_and_weld_equalities_hold_the_bodies_together():
+  """Constraint-level property of the connect / weld rows (constraint.py:125, :793): efc_pos is the world-space error of the
+  anchors (and of the relative orientation), zero at qpos0 by construction of eq_data (mj_setConst), efc_J is its derivative
+  (finite differences through the kinematics), and over 0.6 s of gravity the welded / pinned bodies stay where the equalities hold
+  them (a free body would have dropped 1.8 m)."""
+  from tests import models as TM
+
+  mjm = mjw.load_mjcf_string(TM.SMALL_MODELS["connect_weld"])
+  om = O.OracleModel(mjm)
+  d = O.make_data(om, nworld=1, njmax=48)
+  O.run(om, d, "forward")
+  ne = int(d.ne[0])
+  assert ne == 3 + 6 + 3 + 6 + 1  # the inactive weld emits no rows
+  assert np.abs(d.efc_pos[0, :ne]).max() < 1e-12
+  # derivative check on the hinge / ball / slide coordinates (quaternion coordinates are left alone)
+  rng = np.random.default_rng(3)
+  q0 = np.array(d.qpos[0])
+  hinge = [int(mjm.jnt_qposadr[j]) for j in range(mjm.njnt) if int(mjm.jnt_type[j]) in (2, 3)]
+  dofs = [int(mjm.jnt_dofadr[j]) for j in range(mjm.njnt) if int(mjm.jnt_type[j]) in (2, 3)]
+  q0[hinge] += rng.uniform(-0.2, 0.2, len(hinge))
+  d.qpos[0] = q0
+  O.run(om, d, "forward")
+  J, pos0 = np.array(d.efc_J[0, :ne, : mjm.nv]), np.array(d.efc_pos[0, :ne])
+  eps = 1e-6
+  for qa, da in zip(hinge, dofs):
+    d.qpos[0] = q0
+    d.qpos[0, qa] += eps
+    O.run(om, d, "forward")
+    fd = (np.array(d.efc_pos[0, :ne]) - pos0) / eps
+    rows = slice(0, 18)  # connect / weld rows: their positional rows are exact derivatives; weld rotation rows to first order
+    assert np.abs(fd[rows] - J[rows, da]).max() < 2e-2 * (1 + np.abs(J[rows, da]).max()), (qa, np.abs(fd[rows] - J[rows, da]).max())
+  d.qpos[0] = q0
+  d.qvel[:] = 0
+  O.run(om, d, "forward")
+  for _ in range(300):
+    O.run(om, d, "step")
+  O.run(om, d, "forward")
+  assert np.abs(d.efc_pos[0, : int(d.ne[0])]).max() < 0.3
+  f1, f2, p1 = (mjm.body_names.index(n) for n in ("f1", "f2", "p1"))
+  assert abs(d.xpos[0, p1, 2] - 1.0) < 0.2  # pinned to the world
+  assert d.xpos[0, f1, 2] < -0.5 and abs(np.linalg.norm(d.xpos[0, f1] - d.xpos[0, f2]) - np.linalg.norm([0.3, 0.0, 0.1])) < 0.02  # fall together
