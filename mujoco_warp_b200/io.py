@@ -591,6 +591,18 @@ def put_data(
   """
   d = make_data(mjm, nworld, nconmax, nccdmax, njmax, njmax_nnz, naconmax, naccdmax, device=device, m=None)
   dev = d.device
+  # The reference runs MuJoCo's mj_kinematics on the host data first (io.py:1108), which normalises the quaternions of qpos in
+  # place -- an all-zero quaternion (keyframes of benchmarks/aloha_pot) becomes the identity (mju_normalize4).
+  if hasattr(mjd, "qpos"):
+    q = np.asarray(mjd.qpos, dtype=np.float64)
+    for j in range(int(mjm.njnt)):
+      jt, qa = int(mjm.jnt_type[j]), int(mjm.jnt_qposadr[j])
+      if jt in (C.JointType.FREE, C.JointType.BALL):
+        qa += 3 if jt == C.JointType.FREE else 0
+        n = float(np.linalg.norm(q[qa : qa + 4]))
+        q[qa : qa + 4] = [1.0, 0.0, 0.0, 0.0] if n < 1e-15 else q[qa : qa + 4] / n
+    if isinstance(mjd.qpos, np.ndarray):
+      mjd.qpos[...] = q
   for name in _STATE_FIELDS:
     if hasattr(mjd, name):
       src = np.asarray(getattr(mjd, name), dtype=np.float32)

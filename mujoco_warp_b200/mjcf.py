@@ -349,6 +349,31 @@ def _convex_hull_vertices(v):
     return v
 
 
+def _hull_mass_properties(verts):
+  """(volume, centre of mass, 3x3 inertia about the centre of mass) of the convex hull of `verts` at unit density: signed
+  tetrahedra between the origin and the outward-oriented hull triangles.  For a convex mesh this is what MuJoCo's mesh
+  compiler integrates over the faces; a non-convex mesh is treated as its hull (MuJoCo's `inertia="convex"`)."""
+  from scipy.spatial import ConvexHull
+
+  v = np.asarray(verts, dtype=np.float64).reshape(-1, 3)
+  hull = ConvexHull(v)
+  vol, first, second = 0.0, np.zeros(3), np.zeros((3, 3))
+  canon = (np.eye(3) + np.ones((3, 3))) / 120.0  # integral of x x^T over the unit tetrahedron with a vertex at the origin
+  for tri, eq in zip(hull.simplices, hull.equations):
+    a, b, c = v[tri]
+    if np.dot(np.cross(b - a, c - a), eq[:3]) < 0:  # orient outward
+      b, c = c, b
+    A = np.stack([a, b, c], axis=1)
+    det = np.linalg.det(A)  # 6 x signed volume
+    vol += det / 6.0
+    first += det * (a + b + c) / 24.0
+    second += det * (A @ canon @ A.T)
+  com = first / vol
+  cov = second - vol * np.outer(com, com)  # second moment about the centre of mass
+  inertia = np.trace(cov) * np.eye(3) - cov
+  return float(vol), com, inertia
+
+
 def _parse_meshes(root, comp, defaults, basedir):
   """name -> hull vertices (scaled, in the mesh file's frame) for every <asset><mesh>; None when the file is absent."""
   meshes = {}
@@ -785,6 +810,8 @@ def _finalize(root, comp, defaults, opt, bodies, joints, geoms, sites, basedir) 
   m.geom_aabb = np.zeros((ngeom, 6))
   geom_mass = np.zeros(ngeom)
   geom_inertia = np.zeros((ngeom, 3))
+  geom_mesh_com = np.zeros((ngeom, 3))  # mesh geoms: centre of mass in the geom (= mesh file) frame and the full tensor about it
+  geom_mesh_inertia = np.zeros((ngeom, 3, 3))
   meshes = _parse_meshes(root, comp, defaults, basedir)
   mesh_ids = {}  # only meshes referenced by a geom enter the model, in order of first use
   for i, g in enumerate(geoms):
@@ -797,8 +824,6 @@ def _finalize(root, comp, defaults, opt, bodies, joints, geoms, sites, basedir) 
       # reported geom_xpos / geom_xmat of mesh geoms differ.  Mesh mass properties are not computed: the body needs <inertial>.
       verts = meshes.get(g.get("mesh"))
       collides = int(g.get("contype", 1)) != 0 or int(g.get("conaffinity", 1)) != 0
-      if bodies[g["_body"]]["inertial"] is None and g["_body"] != 0:
-        raise NotImplementedError("mesh geoms need an explicit <inertial> on their body (mesh mass properties are not computed)")
       if verts is None and collides:
         raise NotImplementedError(f"mesh asset '{g.get('mesh')}' of a colliding geom is missing (mesh files are loaded from meshdir)")
       m.geom_type[i] = gt
@@ -820,6 +845,13 @@ def _finalize(root, comp, defaults, opt, bodies, joints, geoms, sites, basedir) 
         m.geom_size[i] = 0.5 * (hi - lo)
         m.geom_rbound[i] = float(np.linalg.norm(verts, axis=1).max())
         m.geom_aabb[i] = np.concatenate((0.5 * (lo + hi), 0.5 * (hi - lo)))
+        if bodies[g["_body"]]["inertial"] is None and g["_body"] != 0 and len(verts) >= 4:
+          vol, com, inert = _hull_mass_properties(verts)
+          dens = float(g["mass"]) / max(vol, mjMINVAL) if "mass" in g else float(g.get("density", 1000.0))
+          geom_mass[i] = dens * vol
+          geom_mesh_com[i], geom_mesh_inertia[i] = com, inert * dens
+      elif bodies[g["_body"]]["inertial"] is None and g["_body"] != 0 and comp.inertiagrouprange[0] <= m.geom_group[i] <= comp.inertiagrouprange[1]:
+        raise NotImplementedError(f"mesh asset '{g.get('mesh')}' is missing and its body has no <inertial>: the body's mass properties cannot be computed")
       continue
     m.geom_type[i] = gt
     size = np.zeros(3)
@@ -892,20 +924,23 @@ def _finalize(root, comp, defaults, opt, bodies, joints, geoms, sites, basedir) 
     sel = [
       g for g in bodies[b]["geom"] if comp.inertiagrouprange[0] <= m.geom_group[g] <= comp.inertiagrouprange[1] and geom_mass[g] > 0
     ]
-    if len(sel) == 1:
+    has_mesh = any(m.geom_type[g] == C.GeomType.MESH for g in sel)
+    if len(sel) == 1 and not has_mesh:
       g = sel[0]
       m.body_mass[b] = geom_mass[g]
       m.body_inertia[b] = geom_inertia[g]
       m.body_ipos[b] = m.geom_pos[g]
       m.body_iquat[b] = m.geom_quat[g]
-    elif len(sel) > 1:
+    elif len(sel) >= 1:
       mass = geom_mass[sel].sum()
-      com = (geom_mass[sel, None] * m.geom_pos[sel]).sum(axis=0) / mass
+      gcom = {g: m.geom_pos[g] + quat_to_mat(m.geom_quat[g]) @ geom_mesh_com[g] for g in sel}  # geom centre of mass in the body frame
+      com = sum(geom_mass[g] * gcom[g] for g in sel) / mass
       tot = np.zeros((3, 3))
       for g in sel:
         R = quat_to_mat(m.geom_quat[g])
-        d = m.geom_pos[g] - com
-        tot += R @ np.diag(geom_inertia[g]) @ R.T + geom_mass[g] * (np.dot(d, d) * np.eye(3) - np.outer(d, d))
+        d = gcom[g] - com
+        local = geom_mesh_inertia[g] if m.geom_type[g] == C.GeomType.MESH else np.diag(geom_inertia[g])
+        tot += R @ local @ R.T + geom_mass[g] * (np.dot(d, d) * np.eye(3) - np.outer(d, d))
       ev, q = eig3(tot)
       m.body_mass[b] = mass
       m.body_inertia[b] = ev

@@ -70,6 +70,24 @@ def _box_pair_states(mjm, nworld, seed):
   return qpos, np.zeros((nworld, mjm.nv)), np.zeros((nworld, mjm.nu))
 
 
+def _aloha_states(mjm, nworld, seed):
+  """Keyframe lift_pot0 / lift_pot4 (arms at the pot; the keyframes hold an all-zero pot quaternion, which MuJoCo's
+  mj_kinematics turns into the identity for the reference's put_data; here a slightly tilted one) plus small joint noise."""
+  rng = np.random.default_rng(seed)
+  keys = [i for i, n in enumerate(mjm.key_names) if n.startswith("lift_pot")]
+  qpos = np.stack([np.asarray(mjm.key_qpos[keys[(4 * w) % len(keys)]], dtype=np.float64) for w in range(nworld)])
+  ctrl = np.stack([np.asarray(mjm.key_ctrl[keys[(4 * w) % len(keys)]], dtype=np.float64) for w in range(nworld)])
+  for j in range(mjm.njnt):
+    jt, qa = int(mjm.jnt_type[j]), int(mjm.jnt_qposadr[j])
+    if jt == 0:
+      quat = np.array([1.0, 0.013, -0.021, 0.005]) + rng.normal(0, 0.004, (nworld, 4))  # slightly tilted: a pot standing exactly flat on
+      qpos[:, qa + 3 : qa + 7] = quat / np.linalg.norm(quat, axis=1, keepdims=True)  # the table has no unique witness point (EPA tie)
+      qpos[:, qa + 2] -= rng.uniform(0.0, 0.012, nworld)  # the pot a little into the table: box-mesh contacts
+    elif jt == 3:
+      qpos[:, qa] += rng.uniform(-0.02, 0.02, nworld)
+  return qpos, rng.uniform(-0.05, 0.05, (nworld, mjm.nv)), ctrl
+
+
 def _panda_states(mjm, nworld, seed):
   """Joint angles a little beyond the joint ranges (active limits), velocities, controls beyond ctrlrange (clamping)."""
   rng = np.random.default_rng(seed)
@@ -113,6 +131,8 @@ CASES = {
   "springs_energy_forward": dict(model="springs", nworld=4, seed=72, mode="forward", enable=["ENERGY"]),
   "gravcomp_step3": dict(model="gravcomp", nworld=4, seed=81, mode="step", nstep=3),
   "site_equalities_step3": dict(model="site_equalities", nworld=4, seed=91, mode="step", nstep=3, njmax=32),
+  # BASELINE config 5 (benchmarks/aloha_pot: 133 convex-hull meshes up to 1159 vertices, 9154 candidate geom pairs, elliptic cones)
+  "aloha_pot_forward": dict(model="aloha", nworld=2, seed=95, mode="forward", nconmax=24, njmax=128, states="aloha"),
   "connect_weld_forward": dict(model="connect_weld", nworld=5, seed=61, mode="forward", njmax=48),
   "connect_weld_step4": dict(model="connect_weld", nworld=4, seed=62, mode="step", nstep=4, njmax=48),
   "connect_weld_njmax_overflow": dict(model="connect_weld", nworld=2, seed=63, mode="forward", njmax=16),
@@ -129,6 +149,8 @@ CASES = {
 def load_model(key):
   if key == "humanoid":
     return mjw.load_mjcf(H.HUMANOID)
+  if key == "aloha":
+    return mjw.load_mjcf(os.path.join(ROOT, "benchmarks", "aloha_pot", "scene.xml"))
   if key == "apollo":
     return mjw.load_mjcf(os.path.join(ROOT, "benchmarks", "apptronik_apollo", "scene_flat.xml"))
   if key == "panda":
@@ -148,6 +170,8 @@ def case_inputs(name):
     qpos, qvel, ctrl = _states(mjm, c["nworld"], c["seed"], c.get("sink", 0.0))
   elif kind == "panda":
     qpos, qvel, ctrl = _panda_states(mjm, c["nworld"], c["seed"])
+  elif kind == "aloha":
+    qpos, qvel, ctrl = _aloha_states(mjm, c["nworld"], c["seed"])
   elif kind == "box_pairs":
     qpos, qvel, ctrl = _box_pair_states(mjm, c["nworld"], c["seed"])
   else:

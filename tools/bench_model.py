@@ -17,7 +17,26 @@ import mujoco_warp_b200 as mjw
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 MODELS = {"panda": ("benchmarks/franka_emika_panda/scene.xml", 32768, 1, 5), "humanoid": ("benchmarks/humanoid/humanoid.xml", 8192, 24, 64),
-          "apollo": ("benchmarks/apptronik_apollo/scene_flat.xml", 8192, 16, 64)}  # reference benchmarks/config.txt:17
+          "apollo": ("benchmarks/apptronik_apollo/scene_flat.xml", 8192, 16, 64),  # reference benchmarks/config.txt:17
+          "aloha": ("benchmarks/aloha_pot/scene.xml", 8192, 24, 128)}  # config.txt:15, replay = keyframes lift_pot*
+REPLAY = {"aloha": "lift_pot"}
+
+
+def make_trajectory(mjm, keys):
+  """Control trajectory through the keyframes `keys` by linear interpolation (reference io.py:2603 make_trajectory)."""
+  import numpy as np
+
+  ctrls, prev, prev_time, time = [], np.zeros(mjm.nu), 0.0, 0.0
+  for k in keys:
+    ck, ct = np.asarray(mjm.key_ctrl[k], dtype=np.float64), float(mjm.key_time[k])
+    while time < ct:
+      frac = (time - prev_time) / (ct - prev_time)
+      ctrls.append(prev * (1 - frac) + ck * frac)
+      time += float(mjm.opt.timestep)
+    ctrls.append(ck)
+    time += float(mjm.opt.timestep)
+    prev, prev_time = ck, time
+  return np.array(ctrls)
 
 
 def main():
@@ -28,15 +47,25 @@ def main():
   nstep = args[3] if len(args) > 3 else 200
   mjm = mjw.load_mjcf(os.path.join(ROOT, path))
   m = mjw.put_model(mjm)
-  d = mjw.make_data(mjm, nworld=nworld, nconmax=nconmax, njmax=njmax)
-  if mjm.nkey:
-    d.qpos.copy_(torch.tensor(mjm.key_qpos[0], dtype=torch.float32, device="cuda").expand(nworld, -1))
+  traj = None
+  if name in REPLAY:  # testspeed.py:277-282: state of the first matching keyframe, controls replayed along the keyframe sequence
+    keys = [i for i, n in enumerate(mjm.key_names) if n.startswith(REPLAY[name])]
+    hd = mjw.make_host_data(mjm)
+    hd.qpos[:] = mjm.key_qpos[keys[0]]
+    hd.ctrl[:] = mjm.key_ctrl[keys[0]]
+    d = mjw.put_data(mjm, hd, nworld=nworld, nconmax=nconmax, njmax=njmax)
+    traj = torch.tensor(make_trajectory(mjm, keys), dtype=torch.float32, device="cuda")
+  else:
+    d = mjw.make_data(mjm, nworld=nworld, nconmax=nconmax, njmax=njmax)
+    if mjm.nkey:
+      d.qpos.copy_(torch.tensor(mjm.key_qpos[0], dtype=torch.float32, device="cuda").expand(nworld, -1))
   center = None
-  if mjm.nkey and getattr(mjm, "key_ctrl", None) is not None and mjm.nu:  # noise centred on the keyframe controls (testspeed.py:286)
+  if traj is None and mjm.nkey and getattr(mjm, "key_ctrl", None) is not None and mjm.nu:  # noise centred on the keyframe controls (testspeed.py:286)
     center = torch.tensor(mjm.key_ctrl[0], dtype=torch.float32, device="cuda").expand(nworld, -1).contiguous()
     d.ctrl.copy_(center)
   for i in range(20):
-    mjw.ctrl_noise(m, d, i, ctrl_center=center)
+    if traj is None:
+      mjw.ctrl_noise(m, d, i, ctrl_center=center)
     mjw.step(m, d)
   torch.cuda.synchronize()
   g = torch.cuda.CUDAGraph()
@@ -49,14 +78,26 @@ def main():
   e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
   for _ in range(10):
     g.replay()
-  e0.record()
-  for i in range(nstep):
-    g.replay()
-  e1.record()
-  e1.synchronize()
-  ms = e0.elapsed_time(e1) / nstep
+  if traj is None:
+    e0.record()
+    for i in range(nstep):
+      g.replay()
+    e1.record()
+    e1.synchronize()
+    ms = e0.elapsed_time(e1) / nstep
+  else:  # controls of step i set before it, outside the timed region (benchmark.py:139-169 times each step on its own)
+    ms = 0.0
+    with torch.cuda.stream(s):
+      for i in range(nstep):
+        d.ctrl.copy_(traj[min(20 + i, traj.shape[0] - 1)].expand(nworld, -1))
+        e0.record(s)
+        g.replay()
+        e1.record(s)
+        e1.synchronize()
+        ms += e0.elapsed_time(e1)
+    ms /= nstep
   out = {"model": path, "nworld": nworld, "nconmax": nconmax, "njmax": njmax, "steps": nstep, "ms_per_step": ms,
-         "env_steps_per_s": nworld / ms * 1e3, "mean_nefc": float(d.nefc.float().mean()), "mean_niter": float(d.solver_niter.float().mean()),
+         "env_steps_per_s": nworld / ms * 1e3, "mean_nefc": float(d.nefc.float().mean()), "mean_niter": float(d.solver_niter.float().mean()), "mean_ncon": float(d.nacon[0]) / nworld,
          "nan_worlds": int(torch.isnan(d.qpos).any(dim=1).sum()), "status_bits": int(d.status.max())}  # fmt: skip
   print(json.dumps(out))
 
