@@ -29,7 +29,7 @@
   X(nJmom)      /* actuator moment non-zeros */ \
   X(nmaxcondim) X(nmaxpyramid) X(ngravcomp) X(is_sparse) X(nM) X(ntree) \
   X(ngeompair)  /* ngeom (ngeom - 1) / 2: entries of the upper-triangular pair table (SAP broadphase) */ \
-  X(nmesh) X(nmeshvert) /* convex-hull vertex tables of mesh geoms (reference types.py Model.mesh_vert*) */ \
+  X(nmesh) X(nmeshvert) X(nmeshgraph) /* convex-hull vertex tables of mesh geoms (reference types.py Model.mesh_vert*) */ \
   X(neqconnect) X(neqweld) /* connect / weld equalities (reference io.py:445-448 eq_connect_adr, eq_wld_adr) */
 
 /* ---- model int arrays ---------------------------------------------------------------------- */
@@ -50,7 +50,7 @@
   X(actuator_biastype) X(actuator_actadr) X(actuator_actnum) X(actuator_ctrllimited) \
   X(actuator_forcelimited) X(actuator_actlimited) X(actuator_actearly) \
   X(eq_type) X(eq_obj1id) X(eq_obj2id) X(eq_objtype) X(eq_jnt_adr) X(eq_connect_adr) X(eq_wld_adr) \
-  X(geom_dataid) X(mesh_vertadr) X(mesh_vertnum)
+  X(geom_dataid) X(mesh_vertadr) X(mesh_vertnum) X(mesh_graphadr) X(mesh_graph)
 
 /* ---- model real arrays --------------------------------------------------------------------- */
 #define MJB_MODEL_REAL_FIELDS(X) \

@@ -47,6 +47,7 @@ typedef struct {
   int type;
   const CCD_VERT_REAL* vert; /* mesh: hull vertices in the geom frame (the model's mesh_vert + 3 * mesh_vertadr), nvert of them */
   int nvert;
+  const int* graph; /* mesh: MuJoCo-layout convex graph of the hull (mesh_graph + mesh_graphadr), or NULL: exhaustive support search */
 } CcdGeom;
 
 typedef struct {
@@ -121,6 +122,26 @@ CCD_FN_NOINLINE int ccd_support(const CcdGeom* g, const creal* dir, creal* point
       res[0] = ld[0] * scl; res[1] = ld[1] * scl;
     }
     res[2] = ccd_sign(ld[2]) * g->size[1];
+  } else if (g->type == CCD_GEOM_MESH && g->graph && g->nvert >= 10) { /* :153-176 hill climbing over the hull's edge graph */
+    const int* graph = g->graph;
+    const int numvert = graph[0];
+    const int *vert_edgeadr = graph + 2, *vert_globalid = graph + 2 + numvert, *edge_localid = graph + 2 + 2 * numvert;
+    creal max_dist = CR(-1e30);
+    int prev = -1, imax = cache_in > -1 ? cache_in : 0;
+    while (imax != prev) { /* the start vertex itself is not evaluated (max_dist starts at FLOAT_MIN), as in the reference */
+      prev = imax;
+      int i = vert_edgeadr[imax], subidx = edge_localid[i];
+      while (subidx >= 0) {
+        const int idx = vert_globalid[subidx];
+        creal d = ld[0] * (creal)g->vert[3 * idx] + ld[1] * (creal)g->vert[3 * idx + 1] + ld[2] * (creal)g->vert[3 * idx + 2];
+        if (d > max_dist) { imax = subidx; max_dist = d; }
+        i++;
+        subidx = edge_localid[i];
+      }
+    }
+    *cached = imax;
+    vertex_index = vert_globalid[imax];
+    res[0] = (creal)g->vert[3 * vertex_index]; res[1] = (creal)g->vert[3 * vertex_index + 1]; res[2] = (creal)g->vert[3 * vertex_index + 2];
   } else if (g->type == CCD_GEOM_MESH) { /* :140-154 exhaustive search (graphadr == -1); ties keep the cached vertex, then the first */
     creal max_dist = CR(-1e30);
     int best = -1;

@@ -43,9 +43,9 @@ __device__ __forceinline__ bool is_ccd_pair(int t1, int t2) { return (t2 == GEOM
 
 // collision_convex.py:712 eval_ccd_write_contact for one pair (single contact, no collision sensor): returns the number of
 // contacts (0 / 1); dist is the surface distance, pos the midpoint of the witness points, nrm = x1 - x2 (unnormalised).
-__device__ __noinline__ int c_ccd_pair(const float* p1, const float* r1, const float* s1, int t1, const float* v1, int nv1, const float* p2,
-                                       const float* r2, const float* s2, int t2, const float* v2, int nv2, float margin, float tolerance,
-                                       int iterations, float* dist, float* pos, float* nrm) {
+__device__ __noinline__ int c_ccd_pair(const float* p1, const float* r1, const float* s1, int t1, const float* v1, int nv1, const int* gr1,
+                                       const float* p2, const float* r2, const float* s2, int t2, const float* v2, int nv2, const int* gr2,
+                                       float margin, float tolerance, int iterations, float* dist, float* pos, float* nrm) {
   CcdGeom g1, g2;
   CcdPolytope pt;  // ~5 kB of local memory per thread
   CcdGjk res;
@@ -56,8 +56,8 @@ __device__ __noinline__ int c_ccd_pair(const float* p1, const float* r1, const f
   g1.margin = g2.margin = margin;
   g1.type = t1;
   g2.type = t2;
-  g1.vert = v1; g1.nvert = nv1;
-  g2.vert = v2; g2.nvert = nv2;
+  g1.vert = v1; g1.nvert = nv1; g1.graph = gr1;
+  g2.vert = v2; g2.nvert = nv2; g2.graph = gr2;
   if (iterations > CCD_MAX_ITER) iterations = CCD_MAX_ITER;
   float d, x1[3], x2[3];
   const int nc = ccd_run(tolerance, 0.f, iterations, iterations, g1, g2, &pt, &res, &d, x1, x2);
@@ -68,10 +68,10 @@ __device__ __noinline__ int c_ccd_pair(const float* p1, const float* r1, const f
   return 1;
 }
 
-// collision_primitive.py:52-277 plane_convex, exhaustive branch (meshes carry no hill-climbing graph here): up to 4 contacts at the
+// collision_primitive.py:52-277 plane_convex (hill climbing over the mesh graph for >= 10 vertices, else exhaustive): up to 4 contacts at the
 // deepest vertex a, the in-threshold vertex b furthest from a, c furthest from the line ab, d furthest from the edges ac / bc.
 __device__ __noinline__ int c_plane_mesh(const float* p1, const float* n1, const float* p2, const float* r2, const float* vert, int nvert,
-                                         float* dist, float* pos) {
+                                         const int* graph, float* dist, float* pos) {
   const float HUGE_V = 1e6f;
   float pl[3], n[3];
   const float dp[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
@@ -85,7 +85,54 @@ __device__ __noinline__ int c_plane_mesh(const float* p1, const float* n1, const
   auto support = [&](int i) {
     return (pl[0] - vert[3 * i]) * n[0] + (pl[1] - vert[3 * i + 1]) * n[1] + (pl[2] - vert[3 * i + 2]) * n[2];
   };
-    for (int i = 0; i < nvert; i++) {
+  const V3 nn{n[0], n[1], n[2]};
+  bool climbed = false;
+  if (graph && nvert >= 10) {  // collision_primitive.py:140-255: the same four searches by hill climbing over the hull's edge graph
+    climbed = true;
+    const int numvert = graph[0];
+    const int *vert_edgeadr = graph + 2, *vert_globalid = graph + 2 + numvert, *edge_localid = graph + 2 + 2 * numvert;
+    int imax = 0;
+    float threshold = 0.f, best = -HUGE_V;
+    V3 ab{0.f, 0.f, 0.f}, ac = ab, bc = ab;
+    for (int phase = 0; phase < 5; phase++) {  // 0: deepest vertex, 1: a (deepest above the threshold), 2: b, 3: c, 4: d
+      if (phase > 0) best = -HUGE_V;
+      for (;;) {
+        const int prev = imax;
+        int i = vert_edgeadr[imax];
+        while (edge_localid[i] >= 0) {
+          const int subidx = edge_localid[i], vi = vert_globalid[subidx];
+          const float sp = support(vi), mask = sp > threshold ? 0.f : -HUGE_V;
+          const V3 ap{a[0] - vert[3 * vi], a[1] - vert[3 * vi + 1], a[2] - vert[3 * vi + 2]};
+          float val;
+          if (phase == 0) val = sp;
+          else if (phase == 1) val = sp > threshold ? sp : -HUGE_V;
+          else if (phase == 2) val = dot(ap, ap) + mask;
+          else if (phase == 3) val = fabsf(dot(ap, ab)) + mask;
+          else {
+            const V3 bp{b[0] - vert[3 * vi], b[1] - vert[3 * vi + 1], b[2] - vert[3 * vi + 2]};
+            val = (fabsf(dot(ap, ac)) + mask) + (fabsf(dot(bp, bc)) + mask);
+          }
+          if (val > best) { best = val; imax = subidx; }
+          i++;
+        }
+        if (imax == prev) break;
+      }
+      const int gi = vert_globalid[imax];
+      const float* v = vert + 3 * gi;
+      if (phase == 0) { max_support = best; threshold = fmaxf(0.f, max_support - 1e-3f); }
+      else if (phase == 1) { idx[0] = gi; a[0] = v[0]; a[1] = v[1]; a[2] = v[2]; }
+      else if (phase == 2) {
+        idx[1] = gi; b[0] = v[0]; b[1] = v[1]; b[2] = v[2];
+        ab = cross(nn, V3{a[0] - b[0], a[1] - b[1], a[2] - b[2]});
+      } else if (phase == 3) {
+        idx[2] = gi; c[0] = v[0]; c[1] = v[1]; c[2] = v[2];
+        ac = cross(nn, V3{a[0] - c[0], a[1] - c[1], a[2] - c[2]});
+        bc = cross(nn, V3{b[0] - c[0], b[1] - c[1], b[2] - c[2]});
+      } else idx[3] = gi;
+    }
+  }
+  if (!climbed) {
+  for (int i = 0; i < nvert; i++) {
     const float sp = support(i);
     if (sp > max_support) { max_support = sp; idx[0] = i; a[0] = vert[3 * i]; a[1] = vert[3 * i + 1]; a[2] = vert[3 * i + 2]; }
   }
@@ -98,7 +145,6 @@ __device__ __noinline__ int c_plane_mesh(const float* p1, const float* n1, const
     const float d = t0 * t0 + t1 * t1 + t2 * t2 + mask;
     if (d > bd) { idx[1] = i; bd = d; b[0] = vert[3 * i]; b[1] = vert[3 * i + 1]; b[2] = vert[3 * i + 2]; }
   }
-  const V3 nn{n[0], n[1], n[2]};
   const V3 ab = cross(nn, V3{a[0] - b[0], a[1] - b[1], a[2] - b[2]});
   for (int i = 0; i < nvert; i++) {
     const float mask = support(i) > threshold ? 0.f : -HUGE_V;
@@ -114,6 +160,7 @@ __device__ __noinline__ int c_plane_mesh(const float* p1, const float* n1, const
     const float d = (fabsf(dot(ap, ac)) + mask) + (fabsf(dot(bp, bc)) + mask);
     if (d > dd) { idx[3] = i; dd = d; }
   }
+  }  // exhaustive search
   int count = 0;
   for (int i = 3; i >= 0; i--) {  // :258-275 one contact per index that appears once among idx[0..i]
     int rep = 0;
@@ -853,10 +900,21 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
       const float pa[3] = {g.p1.x, g.p1.y, g.p1.z}, pb[3] = {g.p2.x, g.p2.y, g.p2.z};
       const float sa[3] = {g.s1.x, g.s1.y, g.s1.z}, sb[3] = {g.s2.x, g.s2.y, g.s2.z};
       const float *v1 = nullptr, *v2 = nullptr;
+      const int *gr1 = nullptr, *gr2 = nullptr;
       int nv1 = 0, nv2 = 0;
-      if (g.t1 == GEOM_MESH) { const int id = MI(geom_dataid)[g1]; v1 = MR(mesh_vert) + 3 * MI(mesh_vertadr)[id]; nv1 = MI(mesh_vertnum)[id]; }
-      if (g.t2 == GEOM_MESH) { const int id = MI(geom_dataid)[g2]; v2 = MR(mesh_vert) + 3 * MI(mesh_vertadr)[id]; nv2 = MI(mesh_vertnum)[id]; }
-      nbb = c_ccd_pair(pa, DW(geom_xmat) + 9 * g1, sa, g.t1, v1, nv1, pb, r2, sb, g.t2, v2, nv2, cp.margin, K.o.ccd_tolerance,
+      if (g.t1 == GEOM_MESH) {
+        const int id = MI(geom_dataid)[g1];
+        v1 = MR(mesh_vert) + 3 * MI(mesh_vertadr)[id];
+        nv1 = MI(mesh_vertnum)[id];
+        if (MI(mesh_graphadr)[id] >= 0) gr1 = MI(mesh_graph) + MI(mesh_graphadr)[id];
+      }
+      if (g.t2 == GEOM_MESH) {
+        const int id = MI(geom_dataid)[g2];
+        v2 = MR(mesh_vert) + 3 * MI(mesh_vertadr)[id];
+        nv2 = MI(mesh_vertnum)[id];
+        if (MI(mesh_graphadr)[id] >= 0) gr2 = MI(mesh_graph) + MI(mesh_graphadr)[id];
+      }
+      nbb = c_ccd_pair(pa, DW(geom_xmat) + 9 * g1, sa, g.t1, v1, nv1, gr1, pb, r2, sb, g.t2, v2, nv2, gr2, cp.margin, K.o.ccd_tolerance,
                        K.o.ccd_iterations, bdist, bpos, bnrm);
       boxbox = true;
     }
@@ -864,7 +922,8 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
       const float pa[3] = {g.p1.x, g.p1.y, g.p1.z}, pb[3] = {g.p2.x, g.p2.y, g.p2.z};
       const int id = MI(geom_dataid)[g2];
       bnrm[0] = g.n1.x; bnrm[1] = g.n1.y; bnrm[2] = g.n1.z;
-      nbb = c_plane_mesh(pa, bnrm, pb, r2, MR(mesh_vert) + 3 * MI(mesh_vertadr)[id], MI(mesh_vertnum)[id], bdist, bpos);
+      nbb = c_plane_mesh(pa, bnrm, pb, r2, MR(mesh_vert) + 3 * MI(mesh_vertadr)[id], MI(mesh_vertnum)[id],
+                         MI(mesh_graphadr)[id] >= 0 ? MI(mesh_graph) + MI(mesh_graphadr)[id] : nullptr, bdist, bpos);
       boxbox = true;
     }
     for (int k = 0; k < ncand; k++) {  // pass 1: count (write_contact filter, collision_core.py:199-203)

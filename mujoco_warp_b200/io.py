@@ -135,6 +135,8 @@ def host_model(mjm) -> SimpleNamespace:
   ints["geom_dataid"] = A("geom_dataid", i32) if hasattr(mjm, "geom_dataid") else np.full(ngeom, -1, dtype=i32)
   ints["mesh_vertadr"] = A("mesh_vertadr", i32) if nmesh else np.zeros(0, dtype=i32)
   ints["mesh_vertnum"] = A("mesh_vertnum", i32) if nmesh else np.zeros(0, dtype=i32)
+  ints["mesh_graphadr"] = A("mesh_graphadr", i32) if nmesh and hasattr(mjm, "mesh_graphadr") else np.full(nmesh, -1, dtype=i32)
+  ints["mesh_graph"] = A("mesh_graph", i32).reshape(-1) if nmesh and hasattr(mjm, "mesh_graph") else np.zeros(0, dtype=i32)
   for name in types.MODEL_REAL_FIELDS:
     if name == "mesh_vert":
       reals[name] = A(name, f64).reshape(-1, 3) if nmesh else np.zeros((0, 3))
@@ -278,7 +280,7 @@ def host_model(mjm) -> SimpleNamespace:
     neqweld=int(ints["eq_wld_adr"].size), nJmom=nJmom,
     nmaxcondim=nmaxcondim, nmaxpyramid=int(max(1, 2 * (nmaxcondim - 1))),
     ngravcomp=int((reals["body_gravcomp"] != 0).sum()), is_sparse=int(sparse), nM=int(getattr(mjm, "nM", 0)),
-    ntree=int(getattr(mjm, "ntree", 0)), ngeompair=int(len(geom1)), nmesh=nmesh, nmeshvert=int(reals["mesh_vert"].shape[0]),
+    ntree=int(getattr(mjm, "ntree", 0)), ngeompair=int(len(geom1)), nmesh=nmesh, nmeshvert=int(reals["mesh_vert"].shape[0]), nmeshgraph=int(ints["mesh_graph"].size),
   )  # fmt: skip
   extra = dict(
     nsensordata=int(getattr(mjm, "nsensordata", 0)), ncam=int(getattr(mjm, "ncam", 0)), nlight=int(getattr(mjm, "nlight", 0)),

@@ -349,6 +349,34 @@ def _convex_hull_vertices(v):
     return v
 
 
+def _hull_graph(verts):
+  """MuJoCo-layout convex graph of hull vertices `verts` (already reduced to the hull); None for degenerate sets."""
+  v = np.asarray(verts, dtype=np.float64).reshape(-1, 3)
+  if len(v) < 4:
+    return None
+  try:
+    from scipy.spatial import ConvexHull
+
+    hull = ConvexHull(v)
+  except Exception:
+    return None
+  if len(hull.vertices) != len(v):  # a vertex inside a facet: not every point is a graph node; keep the exhaustive search
+    return None
+  nvert, nface = len(v), len(hull.simplices)
+  nbr = [[] for _ in range(nvert)]
+  for a, b, c in hull.simplices:
+    for x, y in ((a, b), (b, c), (c, a), (b, a), (c, b), (a, c)):
+      if y not in nbr[x]:
+        nbr[x].append(int(y))
+  edgeadr, edges = [], []
+  for i in range(nvert):
+    edgeadr.append(len(edges))
+    edges.extend(sorted(nbr[i]))
+    edges.append(-1)
+  edges += [-1] * (nvert + 3 * nface - len(edges))  # MuJoCo sizes the block as numvert + 3 numface
+  return np.concatenate(([nvert, nface], edgeadr, np.arange(nvert), edges, np.asarray(hull.simplices).reshape(-1))).astype(np.int32)
+
+
 def _hull_mass_properties(verts):
   """(volume, centre of mass, 3x3 inertia about the centre of mass) of the convex hull of `verts` at unit density: signed
   tetrahedra between the origin and the outward-oriented hull triangles.  For a convex mesh this is what MuJoCo's mesh
@@ -904,9 +932,19 @@ def _finalize(root, comp, defaults, opt, bodies, joints, geoms, sites, basedir) 
   m.mesh_vertadr = np.concatenate(([0], np.cumsum(m.mesh_vertnum)[:-1])).astype(i32) if names else np.zeros(0, dtype=i32)
   m.mesh_vert = np.concatenate([meshes[n] for n in names]).reshape(-1, 3) if names else np.zeros((0, 3))
   m.nmeshvert = int(m.mesh_vert.shape[0])
-  m.mesh_graphadr = np.full(m.nmesh, -1, dtype=i32)
+  # hill-climbing graph of each hull in MuJoCo's mesh_graph layout (the reference's support functions read it, collision_gjk.py:153-176,
+  # collision_primitive.py:141-146): numvert, numface, vert_edgeadr[numvert], vert_globalid[numvert],
+  # edge_localid[numvert + 3 numface] (neighbour lists, each closed by -1), face_globalid[3 numface]
+  graphs, adr = [], []
+  for n in names:
+    g = _hull_graph(meshes[n])
+    adr.append(-1 if g is None else sum(len(x) for x in graphs))
+    if g is not None:
+      graphs.append(g)
+  m.mesh_graphadr = np.array(adr, dtype=i32).reshape(m.nmesh)
+  m.mesh_graph = np.concatenate(graphs).astype(i32) if graphs else np.zeros(0, dtype=i32)
+  m.nmeshgraph = int(m.mesh_graph.size)
   m.mesh_polyadr = np.full(m.nmesh, -1, dtype=i32)
-  m.nmeshgraph = 0
 
   # ---------------- body inertial properties
   m.body_mass = np.zeros(nbody)

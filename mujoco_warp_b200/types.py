@@ -50,7 +50,7 @@ TILE_SIZE_JTDAJ_DENSE = 16  # reference types.py:35
 # ----------------------------------------------------------------------------------------------
 MODEL_SIZES = (
   "nq nv nu na nbody njnt ngeom nsite nmocap neq npair nxn nlevel nv_pad nlimit nlimitball "
-  "nfrictiondof neqjnt nJmom nmaxcondim nmaxpyramid ngravcomp is_sparse nM ntree ngeompair nmesh nmeshvert neqconnect neqweld"
+  "nfrictiondof neqjnt nJmom nmaxcondim nmaxpyramid ngravcomp is_sparse nM ntree ngeompair nmesh nmeshvert nmeshgraph neqconnect neqweld"
 ).split()
 
 MODEL_INT_FIELDS = {
@@ -109,6 +109,8 @@ MODEL_INT_FIELDS = {
   "geom_dataid": ("ngeom",),
   "mesh_vertadr": ("nmesh",),
   "mesh_vertnum": ("nmesh",),
+  "mesh_graphadr": ("nmesh",),
+  "mesh_graph": ("nmeshgraph",),
 }
 
 # reference batches these over a leading `*` dimension (1 or nworld); here always 1

@@ -957,10 +957,12 @@ static int is_convex_pair_mesh(int t1, int t2) { return (t2 == GEOM_MESH && t1 >
 
 /* collision_convex.py:712 eval_ccd_write_contact (single contact, no collision sensor): returns 1 candidate whose dist is the
  * surface distance (>= margin when the margin-inflated shapes do not overlap, which write_contact then rejects) */
-static int ccd_pair(const real* p1, const real* r1, const real* s1, int t1, const real* v1, int nv1, const real* p2, const real* r2,
-                    const real* s2, int t2, const real* v2, int nv2, real margin, real tolerance, int iterations, OContactGeom* out) {
+static int ccd_pair(const real* p1, const real* r1, const real* s1, int t1, const real* v1, int nv1, const int* gr1, const real* p2,
+                    const real* r2, const real* s2, int t2, const real* v2, int nv2, const int* gr2, real margin, real tolerance,
+                    int iterations, OContactGeom* out) {
   CcdGeom g1, g2;
   g1.vert = v1; g1.nvert = nv1; g2.vert = v2; g2.nvert = nv2;
+  g1.graph = gr1; g2.graph = gr2;
   static _Thread_local CcdPolytope pt;
   CcdGjk res;
   memcpy(g1.pos, p1, sizeof(g1.pos)); memcpy(g1.rot, r1, sizeof(g1.rot)); memcpy(g1.size, s1, sizeof(g1.size));
@@ -985,10 +987,21 @@ static int narrowphase_pair(const OModel* m, const OData* d, int g1, int g2, rea
   real n1[3] = {r1[2], r1[5], r1[8]}, n2[3] = {r2[2], r2[5], r2[8]};
   if (is_convex_pair_mesh(t1, t2)) {
     const real *v1 = 0, *v2 = 0;
+    const int *gr1 = 0, *gr2 = 0;
     int nv1 = 0, nv2 = 0;
-    if (t1 == GEOM_MESH) { int id = m->geom_dataid[g1]; v1 = m->mesh_vert + 3 * m->mesh_vertadr[id]; nv1 = m->mesh_vertnum[id]; }
-    if (t2 == GEOM_MESH) { int id = m->geom_dataid[g2]; v2 = m->mesh_vert + 3 * m->mesh_vertadr[id]; nv2 = m->mesh_vertnum[id]; }
-    return ccd_pair(p1, r1, s1, t1, v1, nv1, p2, r2, s2, t2, v2, nv2, margin, ccd_tolerance, ccd_iterations, out);
+    if (t1 == GEOM_MESH) {
+      int id = m->geom_dataid[g1];
+      v1 = m->mesh_vert + 3 * m->mesh_vertadr[id];
+      nv1 = m->mesh_vertnum[id];
+      if (m->mesh_graphadr[id] >= 0) gr1 = m->mesh_graph + m->mesh_graphadr[id];
+    }
+    if (t2 == GEOM_MESH) {
+      int id = m->geom_dataid[g2];
+      v2 = m->mesh_vert + 3 * m->mesh_vertadr[id];
+      nv2 = m->mesh_vertnum[id];
+      if (m->mesh_graphadr[id] >= 0) gr2 = m->mesh_graph + m->mesh_graphadr[id];
+    }
+    return ccd_pair(p1, r1, s1, t1, v1, nv1, gr1, p2, r2, s2, t2, v2, nv2, gr2, margin, ccd_tolerance, ccd_iterations, out);
   }
   if (t1 == GEOM_PLANE && t2 == GEOM_MESH) { /* collision_primitive.py:52-277 plane_convex, exhaustive branch (no mesh graph) */
     int id = m->geom_dataid[g2], nvert = m->mesh_vertnum[id], idx[4] = {-1, -1, -1, -1};
@@ -998,6 +1011,50 @@ static int narrowphase_pair(const OModel* m, const OData* d, int g1, int g2, rea
     for (int k = 0; k < 4; k++) { out[k].dist = MJ_MAXVAL; memset(out[k].pos, 0, sizeof(out[k].pos)); make_frame(out[k].frame, n1); out[k].id = k; }
 #define SUPPORT(i) ((pl[0] - vert[3 * (i)]) * n[0] + (pl[1] - vert[3 * (i) + 1]) * n[1] + (pl[2] - vert[3 * (i) + 2]) * n[2])
     real max_support = -HUGE_V, a[3] = {0, 0, 0}, b[3] = {0, 0, 0}, c[3] = {0, 0, 0};
+    if (m->mesh_graphadr[id] >= 0 && nvert >= 10) { /* collision_primitive.py:140-255: the same four searches by hill climbing */
+      const int* graph = m->mesh_graph + m->mesh_graphadr[id];
+      const int numvert = graph[0], *vert_edgeadr = graph + 2, *vert_globalid = graph + 2 + numvert, *edge_localid = graph + 2 + 2 * numvert;
+      int imax = 0;
+      real threshold = 0, best = -HUGE_V, ab[3] = {0, 0, 0}, ac[3] = {0, 0, 0}, bc[3] = {0, 0, 0}, t[3];
+      for (int phase = 0; phase < 5; phase++) { /* 0: deepest vertex, 1: a (deepest above threshold), 2: b, 3: c, 4: d */
+        if (phase > 0) best = -HUGE_V;
+        for (;;) {
+          int prev = imax, i = vert_edgeadr[imax];
+          while (edge_localid[i] >= 0) {
+            int subidx = edge_localid[i], vi = vert_globalid[subidx];
+            real sp = SUPPORT(vi), mask = sp > threshold ? 0.0 : -HUGE_V, val;
+            const real* v = vert + 3 * vi;
+            if (phase == 0) val = sp;
+            else if (phase == 1) val = sp > threshold ? sp : -HUGE_V;
+            else if (phase == 2) { for (int j = 0; j < 3; j++) t[j] = a[j] - v[j]; val = dot3(t, t) + mask; }
+            else if (phase == 3) { for (int j = 0; j < 3; j++) t[j] = a[j] - v[j]; val = fabs(dot3(t, ab)) + mask; }
+            else {
+              real bp[3];
+              for (int j = 0; j < 3; j++) { t[j] = a[j] - v[j]; bp[j] = b[j] - v[j]; }
+              val = (fabs(dot3(t, ac)) + mask) + (fabs(dot3(bp, bc)) + mask);
+            }
+            if (val > best) { best = val; imax = subidx; }
+            i++;
+          }
+          if (imax == prev) break;
+        }
+        int gi = vert_globalid[imax];
+        if (phase == 0) { max_support = best; threshold = fmax(0.0, max_support - 1e-3); }
+        else if (phase == 1) { idx[0] = gi; memcpy(a, vert + 3 * gi, sizeof(a)); }
+        else if (phase == 2) {
+          idx[1] = gi; memcpy(b, vert + 3 * gi, sizeof(b));
+          for (int j = 0; j < 3; j++) t[j] = a[j] - b[j];
+          cross3(ab, n, t);
+        } else if (phase == 3) {
+          idx[2] = gi; memcpy(c, vert + 3 * gi, sizeof(c));
+          for (int j = 0; j < 3; j++) t[j] = a[j] - c[j];
+          cross3(ac, n, t);
+          for (int j = 0; j < 3; j++) t[j] = b[j] - c[j];
+          cross3(bc, n, t);
+        } else idx[3] = gi;
+      }
+      goto plane_mesh_collect;
+    }
     for (int i = 0; i < nvert; i++) { real sp = SUPPORT(i); if (sp > max_support) { max_support = sp; idx[0] = i; memcpy(a, vert + 3 * i, sizeof(a)); } }
     if (max_support < 0) return 4;
     real threshold = max_support - 1e-3, bd = -HUGE_V, cd = -HUGE_V, dd = -HUGE_V, ab[3], ac[3], bc[3], t[3];
@@ -1025,6 +1082,7 @@ static int narrowphase_pair(const OModel* m, const OData* d, int g1, int g2, rea
       d = fabs(dot3(ap, ac)) + mask + fabs(dot3(bp, bc)) + mask;
       if (d > dd) { idx[3] = i; dd = d; }
     }
+  plane_mesh_collect:;
     int count = 0;
     for (int i = 3; i >= 0; i--) { /* :258-275 contacts from the indices that appear once among idx[0..i] */
       int rep = 0;
@@ -2531,6 +2589,7 @@ int mjo_ccd_mesh(int t1, int t2, const double* p1, const double* r1, const doubl
   memcpy(g2.pos, p2, sizeof(g2.pos)); memcpy(g2.rot, r2, sizeof(g2.rot)); memcpy(g2.size, s2, sizeof(g2.size));
   g1.margin = g2.margin = margin; g1.type = t1; g2.type = t2;
   g1.vert = v1; g1.nvert = nv1; g2.vert = v2; g2.nvert = nv2;
+  g1.graph = g2.graph = 0;
   x1[0] = x1[1] = x1[2] = x2[0] = x2[1] = x2[2] = 0.0;
   return ccd_run(tolerance, cutoff, iterations, iterations, g1, g2, &pt, &res, dist, x1, x2);
 #undef pt

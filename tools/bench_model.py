@@ -96,7 +96,18 @@ def main():
         e1.synchronize()
         ms += e0.elapsed_time(e1)
     ms /= nstep
-  out = {"model": path, "nworld": nworld, "nconmax": nconmax, "njmax": njmax, "steps": nstep, "ms_per_step": ms,
+  # per stage-group kernel time (CUDA events around every launch of 20 eager steps)
+  from mujoco_warp_b200 import _lib
+  lib = _lib.load()
+  lib.mjb_timing_reset()
+  lib.mjb_timing_enable(1)
+  for _ in range(20):
+    mjw.step(m, d)
+  torch.cuda.synchronize()
+  groups = {lib.mjb_group_name(g).decode(): round(lib.mjb_timing_group_ms(g) / 20, 4) for g in range(lib.mjb_group_count())}
+  lib.mjb_timing_enable(0)
+  lib.mjb_timing_reset()
+  out = {"groups_ms": groups, "model": path, "nworld": nworld, "nconmax": nconmax, "njmax": njmax, "steps": nstep, "ms_per_step": ms,
          "env_steps_per_s": nworld / ms * 1e3, "mean_nefc": float(d.nefc.float().mean()), "mean_niter": float(d.solver_niter.float().mean()), "mean_ncon": float(d.nacon[0]) / nworld,
          "nan_worlds": int(torch.isnan(d.qpos).any(dim=1).sum()), "status_bits": int(d.status.max())}  # fmt: skip
   print(json.dumps(out))
