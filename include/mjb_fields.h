@@ -30,7 +30,7 @@
   X(nmaxcondim) X(nmaxpyramid) X(ngravcomp) X(is_sparse) X(nM) X(ntree) \
   X(ngeompair)  /* ngeom (ngeom - 1) / 2: entries of the upper-triangular pair table (SAP broadphase) */ \
   X(nmesh) X(nmeshvert) X(nmeshgraph) /* convex-hull vertex tables of mesh geoms (reference types.py Model.mesh_vert*) */ \
-  X(neqconnect) X(neqweld) /* connect / weld equalities (reference io.py:445-448 eq_connect_adr, eq_wld_adr) */
+  X(neqconnect) X(neqweld) X(blob_hot_bytes) /* connect / weld equalities (reference io.py:445-448 eq_connect_adr, eq_wld_adr) */
 
 /* ---- model int arrays ---------------------------------------------------------------------- */
 #define MJB_MODEL_INT_FIELDS(X) \

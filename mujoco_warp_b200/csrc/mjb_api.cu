@@ -37,6 +37,7 @@ struct MjbModel {
   ModelOffsets mo;
   const unsigned char* blob;
   int blob_bytes;
+  int blob_hot;  // bytes of the prefix the kernels stage in shared memory (= blob_bytes unless the model carries large cold tables)
   int col_feat;  // CollisionFeature bits the model needs (pair types present in the filtered pair list)
 };
 
@@ -139,6 +140,7 @@ extern "C" int mjb_model_create(const int* sizes, int nsizes, const void* blob, 
   }
   m->blob = static_cast<const unsigned char*>(blob);
   m->blob_bytes = (int)nbytes;
+  m->blob_hot = (m->ms.blob_hot_bytes > 0 && m->ms.blob_hot_bytes < (int)nbytes) ? m->ms.blob_hot_bytes : (int)nbytes;
   m->col_feat = 0;
   if (m->ms.nxn > 0) {  // pair types present in the statically filtered pair list (one small read-back at creation)
     std::vector<int> pair(2 * (size_t)m->ms.nxn), gtype((size_t)m->ms.ngeom);
@@ -216,7 +218,8 @@ static void fill_params(KParams& K, const MjbModel* m, const MjbData* d, const M
   static_assert(sizeof(OptView) == sizeof(MjbOption), "option struct mismatch");
   memcpy(&K.o, opt, sizeof(OptView));
   K.blob = m->blob;
-  K.blob_bytes = m->blob_bytes;
+  K.blob_bytes = m->blob_hot;
+  K.cold_global = m->blob_hot < m->blob_bytes;
   K.scratch_floats = d->scratch_floats;
   K.stages = stages;
 }
@@ -296,8 +299,8 @@ static int launch_group(int g, const MjbModel* m, MjbData* d, KParams& K, uint32
     c.scratch_floats = group_scratch_floats(g, m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad, m->ms.ngeom, m->ms.nxn, variant);
     const size_t scr_bytes = (size_t)wpb * c.scratch_floats * sizeof(float);
     const bool in_smem =
-        group_uses_blob(g) && (size_t)m->blob_bytes + 16 + scr_bytes <= (size_t)d->smem_optin && m->blob_bytes <= 96 * 1024;
-    const size_t smem = in_smem ? (size_t)m->blob_bytes + 16 + scr_bytes : scr_bytes;
+        group_uses_blob(g) && (size_t)m->blob_hot + 16 + scr_bytes <= (size_t)d->smem_optin && m->blob_hot <= 96 * 1024;
+    const size_t smem = in_smem ? (size_t)m->blob_hot + 16 + scr_bytes : scr_bytes;
     if (smem > (size_t)d->smem_optin) return fail(-5, "model needs more shared memory than the device offers");
     GroupKernel k0 = group_kernel_of(g, in_smem, variant);
     CUDA_OK(cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

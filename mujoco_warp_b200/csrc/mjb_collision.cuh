@@ -872,9 +872,9 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
   bool boxbox = false;
   if (has) {
     const int p = queue[lane];
-    const int ga = MI(nxn_pair)[2 * p], gb = MI(nxn_pair)[2 * p + 1];
-    pid0 = MI(nxn_pairid)[2 * p];
-    pid1 = MI(nxn_pairid)[2 * p + 1];
+    const int ga = MIC(nxn_pair)[2 * p], gb = MIC(nxn_pair)[2 * p + 1];
+    pid0 = MIC(nxn_pairid)[2 * p];
+    pid1 = MIC(nxn_pairid)[2 * p + 1];
     const bool swap = MI(geom_type)[ga] > MI(geom_type)[gb];  // collision_driver.py:351
     g1 = swap ? gb : ga;
     g2 = swap ? ga : gb;
@@ -904,15 +904,15 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
       int nv1 = 0, nv2 = 0;
       if (g.t1 == GEOM_MESH) {
         const int id = MI(geom_dataid)[g1];
-        v1 = MR(mesh_vert) + 3 * MI(mesh_vertadr)[id];
+        v1 = MRC(mesh_vert) + 3 * MI(mesh_vertadr)[id];
         nv1 = MI(mesh_vertnum)[id];
-        if (MI(mesh_graphadr)[id] >= 0) gr1 = MI(mesh_graph) + MI(mesh_graphadr)[id];
+        if (MI(mesh_graphadr)[id] >= 0) gr1 = MIC(mesh_graph) + MI(mesh_graphadr)[id];
       }
       if (g.t2 == GEOM_MESH) {
         const int id = MI(geom_dataid)[g2];
-        v2 = MR(mesh_vert) + 3 * MI(mesh_vertadr)[id];
+        v2 = MRC(mesh_vert) + 3 * MI(mesh_vertadr)[id];
         nv2 = MI(mesh_vertnum)[id];
-        if (MI(mesh_graphadr)[id] >= 0) gr2 = MI(mesh_graph) + MI(mesh_graphadr)[id];
+        if (MI(mesh_graphadr)[id] >= 0) gr2 = MIC(mesh_graph) + MI(mesh_graphadr)[id];
       }
       nbb = c_ccd_pair(pa, DW(geom_xmat) + 9 * g1, sa, g.t1, v1, nv1, gr1, pb, r2, sb, g.t2, v2, nv2, gr2, cp.margin, K.o.ccd_tolerance,
                        K.o.ccd_iterations, bdist, bpos, bnrm);
@@ -922,8 +922,8 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
       const float pa[3] = {g.p1.x, g.p1.y, g.p1.z}, pb[3] = {g.p2.x, g.p2.y, g.p2.z};
       const int id = MI(geom_dataid)[g2];
       bnrm[0] = g.n1.x; bnrm[1] = g.n1.y; bnrm[2] = g.n1.z;
-      nbb = c_plane_mesh(pa, bnrm, pb, r2, MR(mesh_vert) + 3 * MI(mesh_vertadr)[id], MI(mesh_vertnum)[id],
-                         MI(mesh_graphadr)[id] >= 0 ? MI(mesh_graph) + MI(mesh_graphadr)[id] : nullptr, bdist, bpos);
+      nbb = c_plane_mesh(pa, bnrm, pb, r2, MRC(mesh_vert) + 3 * MI(mesh_vertadr)[id], MI(mesh_vertnum)[id],
+                         MI(mesh_graphadr)[id] >= 0 ? MIC(mesh_graph) + MI(mesh_graphadr)[id] : nullptr, bdist, bpos);
       boxbox = true;
     }
     for (int k = 0; k < ncand; k++) {  // pass 1: count (write_contact filter, collision_core.py:199-203)
@@ -1056,7 +1056,7 @@ __device__ __forceinline__ void sap_candidates(const KParams& K, const unsigned 
     const int i = hi, j = i + 1 + k - (i > 0 ? cum[i - 1] : 0);
     int a = order[i], b = order[j];
     if (b < a) { const int t = a; a = b; b = t; }
-    const int p = MI(nxn_lookup)[(a * (2 * ng - a - 3)) / 2 + b - 1];
+    const int p = MIC(nxn_lookup)[(a * (2 * ng - a - 3)) / 2 + b - 1];
     if (p >= 0) atomicOr(bits + (p >> 5), 1u << (p & 31));
   }
   __syncwarp();
@@ -1075,7 +1075,7 @@ __device__ __forceinline__ void s_collision(const KParams& K, const unsigned cha
     for (int p0 = 0; p0 < nxn; p0 += 32) {
       const int p = p0 + lane;
       bool pass = false;
-      if (p < nxn && (!sap || (bits[p >> 5] >> (p & 31) & 1u))) pass = bp_filter(K, mb, w, MI(nxn_pair)[2 * p], MI(nxn_pair)[2 * p + 1]) || MI(nxn_pairid)[2 * p + 1] >= 0;
+      if (p < nxn && (!sap || (bits[p >> 5] >> (p & 31) & 1u))) pass = bp_filter(K, mb, w, MIC(nxn_pair)[2 * p], MIC(nxn_pair)[2 * p + 1]) || MIC(nxn_pairid)[2 * p + 1] >= 0;
       const unsigned mask = __ballot_sync(FULL, pass);
       if (pass) queue[qn + __popc(mask & ((1u << lane) - 1u))] = p;
       qn += __popc(mask);

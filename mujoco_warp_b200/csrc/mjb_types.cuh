@@ -81,7 +81,8 @@ struct KParams {
   DataStrides st;
   OptView o;
   const unsigned char* blob;  // global copy of the model blob
-  int blob_bytes;             // multiple of 16
+  int blob_bytes;             // staged prefix of the blob (multiple of 16): everything, or the hot tables of a large model
+  int cold_global;            // 1: the cold tables (pair lists, mesh vertices / graphs) stay in global memory behind the staged prefix
   int scratch_floats;         // per-warp shared-memory scratch
   uint32_t stages;
   // optional extra operands for the small utility kernels
@@ -92,6 +93,9 @@ struct KParams {
 // model accessors: `mb` is the base of the model blob (shared memory inside the main kernel)
 #define MI(name) (reinterpret_cast<const int*>(mb + K.mo.name))
 #define MR(name) (reinterpret_cast<const float*>(mb + K.mo.name))
+// cold tables (large, streamed or rarely touched): read through `mb` when the whole blob is staged, else from the global copy
+#define MIC(name) (reinterpret_cast<const int*>((K.cold_global ? K.blob : mb) + K.mo.name))
+#define MRC(name) (reinterpret_cast<const float*>((K.cold_global ? K.blob : mb) + K.mo.name))
 // per-world data pointer
 #define DW(name) (K.d.name + (size_t)w * (size_t)K.st.name)
 

@@ -61,6 +61,9 @@ def _default_njmax(mjm, mjd=None) -> int:
   return int(valid_sizes[np.searchsorted(valid_sizes, njmax)])
 
 
+_BLOB_SMEM_LIMIT = 96 * 1024  # bytes of model tables the stage-group kernels keep in shared memory (mjb_api.cu)
+
+
 def _check_supported(mjm):
   """Feature gating with the reference's exception types (reference io.py:90-144)."""
   for field, enum_cls in (
@@ -280,7 +283,7 @@ def host_model(mjm) -> SimpleNamespace:
     neqweld=int(ints["eq_wld_adr"].size), nJmom=nJmom,
     nmaxcondim=nmaxcondim, nmaxpyramid=int(max(1, 2 * (nmaxcondim - 1))),
     ngravcomp=int((reals["body_gravcomp"] != 0).sum()), is_sparse=int(sparse), nM=int(getattr(mjm, "nM", 0)),
-    ntree=int(getattr(mjm, "ntree", 0)), ngeompair=int(len(geom1)), nmesh=nmesh, nmeshvert=int(reals["mesh_vert"].shape[0]), nmeshgraph=int(ints["mesh_graph"].size),
+    ntree=int(getattr(mjm, "ntree", 0)), ngeompair=int(len(geom1)), nmesh=nmesh, nmeshvert=int(reals["mesh_vert"].shape[0]), nmeshgraph=int(ints["mesh_graph"].size), blob_hot_bytes=0,
   )  # fmt: skip
   extra = dict(
     nsensordata=int(getattr(mjm, "nsensordata", 0)), ncam=int(getattr(mjm, "ncam", 0)), nlight=int(getattr(mjm, "nlight", 0)),
@@ -369,12 +372,18 @@ def put_model(mjm, device=None) -> types.Model:
 
   # pack the blob
   int_names, real_names = list(types.MODEL_INT_FIELDS), list(types.MODEL_REAL_FIELDS)
-  offsets, off = {}, 0
-  for name in int_names + real_names:
+  # hot tables first, then the large / streamed ones (pair lists, mesh vertices and graphs): when the whole blob does not fit the
+  # kernels' shared-memory budget they stage the hot prefix only and read the cold tables from global memory (mjb_types.cuh MIC / MRC)
+  cold = ("nxn_pair", "nxn_pairid", "nxn_lookup", "mesh_graph", "mesh_vert")
+  offsets, off, hot_bytes = {}, 0, 0
+  for name in [n for n in int_names + real_names if n not in cold] + list(cold):
     arr = hm.ints[name] if name in hm.ints else hm.reals[name]
+    if name == cold[0]:
+      hot_bytes = off
     offsets[name] = off
     off += (arr.size * 4 + 15) // 16 * 16
   nbytes = max(off, 16)
+  m.sizes["blob_hot_bytes"] = hot_bytes if nbytes > _BLOB_SMEM_LIMIT else 0  # 0: stage everything
   host = np.zeros(nbytes, dtype=np.uint8)
   for name in int_names:
     a = hm.ints[name].astype(np.int32).ravel()

@@ -50,7 +50,7 @@ TILE_SIZE_JTDAJ_DENSE = 16  # reference types.py:35
 # ----------------------------------------------------------------------------------------------
 MODEL_SIZES = (
   "nq nv nu na nbody njnt ngeom nsite nmocap neq npair nxn nlevel nv_pad nlimit nlimitball "
-  "nfrictiondof neqjnt nJmom nmaxcondim nmaxpyramid ngravcomp is_sparse nM ntree ngeompair nmesh nmeshvert nmeshgraph neqconnect neqweld"
+  "nfrictiondof neqjnt nJmom nmaxcondim nmaxpyramid ngravcomp is_sparse nM ntree ngeompair nmesh nmeshvert nmeshgraph neqconnect neqweld blob_hot_bytes"
 ).split()
 
 MODEL_INT_FIELDS = {
