@@ -1069,7 +1069,8 @@ __device__ __forceinline__ void s_collision(const KParams& K, const unsigned cha
   const bool enabled = K.dsz.naconmax > 0 && !(K.o.disableflags & (DSBL_CONSTRAINT | DSBL_CONTACT));
   if (enabled) {
     const int nxn = K.ms.nxn;
-    const bool sap = (FEAT & COLF_SAP) != 0 && nxn > 0;
+    // the all-features variant (convex models) carries the sweep-and-prune code but runs it only when the option asks for it
+    const bool sap = (FEAT & COLF_SAP) != 0 && nxn > 0 && K.o.broadphase != 0;
     unsigned* bits = reinterpret_cast<unsigned*>(queue + 72 + 4 * K.ms.ngeom);
     if (sap) sap_candidates(K, mb, w, lane, queue + 72, bits);
     for (int p0 = 0; p0 < nxn; p0 += 32) {
