@@ -4,8 +4,8 @@
  * The reference exposes this path only as Python functions over Warp arrays
  * (reference mujoco_warp/__init__.py:25-112); there is no FFI in the reference to bind to, so
  * each entry point below names the Python function it replaces.  All functions are
- * asynchronous on the given CUDA stream, allocate nothing, never synchronise the device and are
- * CUDA-graph capturable.  Pointers are *borrowed* device pointers owned by the caller
+ * asynchronous on the given CUDA stream, never synchronise the device (mjb_status excepted) and,
+ * once mjb_prepare() has run, allocate nothing and are CUDA-graph capturable.  Pointers are *borrowed* device pointers owned by the caller
  * (PyTorch in the bundled host layer).  No torch / C++ types cross this boundary.
  *
  * Return value: 0 on success, negative on error (see mjb_last_error()).
@@ -58,8 +58,9 @@ int mjb_data_bind(const MjbModel* m, const int* sizes, int nsizes, int* const* i
                   float* const* real_ptrs, int nreal, MjbData** out);
 void mjb_data_destroy(MjbData* d);
 
-/* Runs the pipeline stages selected by `stages` (MJB_STAGE_* bits) in pipeline order in ONE
- * kernel launch, one warp per world.  Every per-stage reference function f(m, d)
+/* Runs the pipeline stages selected by `stages` (MJB_STAGE_* bits) in pipeline order: one kernel
+ * launch per stage group touched (smooth_position, collision, make_constraint, smooth_velocity,
+ * solve, euler -- six for a whole step), one warp per world.  Every per-stage reference function f(m, d)
  * (kinematics, com_pos, crb, factor_m, collision, make_constraint, transmission,
  * fwd_velocity, fwd_actuation, fwd_acceleration, solve, euler, implicit; reference
  * __init__.py:25-112) maps to one bit. */
@@ -71,6 +72,16 @@ int mjb_step(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_str
 int mjb_forward(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
 int mjb_step1(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
 int mjb_step2(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+
+/* forward.rungekutta4 (reference forward.py:458): the RK4 integrator, called after `forward` like the reference's; mjb_step runs
+ * forward + this when opt->integrator is RK4.  The six temporaries the reference allocates on every call (forward.py:465-475) live in
+ * a scratch buffer of mjb_rk_scratch_floats() floats owned by the MjbData handle: cudaMalloc'ed by mjb_prepare(), or by the first call. */
+int mjb_rungekutta4(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+long long mjb_rk_scratch_floats(const MjbModel* m, const MjbData* d);
+/* No reference counterpart (the reference JIT-compiles and sizes its launches lazily inside the first call, warp_util.py cache_kernel):
+ * does everything a first call would do lazily for the kernel variants `opt` selects -- function attributes, occupancy queries, the
+ * Runge-Kutta scratch -- so that the next step / forward / stage call can be captured into a CUDA graph. */
+int mjb_prepare(const MjbModel* m, MjbData* d, const MjbOption* opt);
 
 /* smooth.solve_m (reference smooth.py:2848): x = M^-1 y using d.qLD; x, y are (nworld, nv). */
 int mjb_solve_m(const MjbModel* m, MjbData* d, float* x, const float* y, void* cuda_stream);

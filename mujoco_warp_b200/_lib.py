@@ -102,10 +102,14 @@ def load():
     lib.mjb_data_bind.restype = ctypes.c_int
     lib.mjb_data_bind.argtypes = [vp, ip, ctypes.c_int, ctypes.POINTER(vp), ctypes.c_int, ctypes.POINTER(vp), ctypes.c_int, ctypes.POINTER(vp)]
     lib.mjb_data_destroy.argtypes = [vp]
-    for name in ("mjb_step", "mjb_forward", "mjb_step1", "mjb_step2"):
+    for name in ("mjb_step", "mjb_forward", "mjb_step1", "mjb_step2", "mjb_rungekutta4"):
       fn = getattr(lib, name)
       fn.restype = ctypes.c_int
       fn.argtypes = [vp, vp, ctypes.POINTER(MjbOption), vp]
+    lib.mjb_prepare.restype = ctypes.c_int
+    lib.mjb_prepare.argtypes = [vp, vp, ctypes.POINTER(MjbOption)]
+    lib.mjb_rk_scratch_floats.restype = ctypes.c_longlong
+    lib.mjb_rk_scratch_floats.argtypes = [vp, vp]
     lib.mjb_run_stages.restype = ctypes.c_int
     lib.mjb_run_stages.argtypes = [vp, vp, ctypes.POINTER(MjbOption), ctypes.c_uint32, vp]
     lib.mjb_solve_m.restype = ctypes.c_int
@@ -174,6 +178,11 @@ def make_option(m) -> MjbOption:
   per-step host path)."""
   o = m.opt
   mi = m.stat.meaninertia
+  for n in _OPT_TENSORS:  # the reference indexes these as [worldid % shape[0]]; here one value serves all worlds
+    if getattr(o, n).numel() != (3 if n == "gravity" else 1):
+      raise NotImplementedError(f"per-world Option.{n} (shape {tuple(getattr(o, n).shape)}) is not implemented: the kernels take one value for all worlds")
+  if mi.numel() != 1:
+    raise NotImplementedError("per-world stat.meaninertia is not implemented")
   key = tuple(getattr(o, n) for n in _OPT_INTS) + tuple(x for n in _OPT_TENSORS for x in (id(getattr(o, n)), getattr(o, n)._version)) + (id(mi), mi._version)
   cached = getattr(m, "_opt_cache", None)
   if cached is not None and cached[0] == key:
@@ -209,12 +218,16 @@ def data_ptr_signature(d):
 
 def data_bind(lib, m, d):
   int_names, real_names = list(types.DATA_INT_FIELDS), list(types.DATA_REAL_FIELDS)
-  for n in int_names:
-    t = d.field(n)
-    assert t.dtype == torch.int32 and t.is_contiguous() and t.device == m.device, n
-  for n in real_names:
-    t = d.field(n)
-    assert t.dtype == torch.float32 and t.is_contiguous() and t.device == m.device, n
+  sizes_all = dict(m.sizes)
+  sizes_all.update(d._sizes)
+  for names, dtype in ((int_names, torch.int32), (real_names, torch.float32)):
+    for n in names:
+      t = d.field(n)
+      if t.dtype != dtype or not t.is_contiguous() or t.device != m.device:
+        raise ValueError(f"Data.{n}: expected a contiguous {dtype} tensor on {m.device}, got {t.dtype} on {t.device} (contiguous={t.is_contiguous()})")
+      want = types.data_field_numel(n, sizes_all)
+      if want is not None and t.numel() != want:
+        raise ValueError(f"Data.{n}: expected {want} elements for this model / nworld, got shape {tuple(t.shape)}")
   sizes = (ctypes.c_int * len(types.DATA_SIZES))(*[int(d._sizes[n]) for n in types.DATA_SIZES])
   ip = (ctypes.c_void_p * len(int_names))(*[d.field(n).data_ptr() for n in int_names])
   rp = (ctypes.c_void_p * len(real_names))(*[d.field(n).data_ptr() for n in real_names])

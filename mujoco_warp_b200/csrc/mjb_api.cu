@@ -4,6 +4,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -13,8 +14,8 @@
 #include "mjb_kernels.cuh"
 
 static thread_local std::string g_err;
-static long long g_launches = 0;
-static int g_timing = 0;
+static std::atomic<long long> g_launches{0};
+static std::atomic<int> g_timing{0};
 struct TimedLaunch {
   cudaEvent_t first, second;
   int group;  // StageGroup, or -1 for the utility kernels
@@ -50,6 +51,8 @@ struct MjbData {
   int device;
   int nsm;
   int smem_optin;
+  float* rk_scratch;  // Runge-Kutta temporaries (reference forward.py:465-475 allocates them per call): cudaMalloc'ed by mjb_prepare / on first use
+  size_t rk_floats;
   // launch configuration of the pipeline kernel, resolved on the first launch
   struct GroupCfg {  // launch configuration of one stage-group kernel, resolved on first use
     int ready, wpb, grid, in_smem, scratch_floats;
@@ -165,6 +168,7 @@ extern "C" void mjb_model_destroy(MjbModel* m) { delete m; }
 
 extern "C" int mjb_data_bind(const MjbModel* m, const int* sizes, int nsizes, int* const* int_ptrs, int nint, float* const* real_ptrs,
                              int nreal, MjbData** out) {
+  if (!m || !sizes || !int_ptrs || !real_ptrs || !out) return fail(-1, "mjb_data_bind: null argument");
   if (nsizes != mjb_field_count(5) || nint != mjb_field_count(6) || nreal != mjb_field_count(7))
     return fail(-1, "mjb_data_bind: field table size mismatch");
   MjbData* d = new MjbData();
@@ -193,7 +197,29 @@ extern "C" int mjb_data_bind(const MjbModel* m, const int* sizes, int nsizes, in
     MJB_DATA_REAL_FIELDS(X)
 #undef X
   }
+  {  // a field with elements must come with a pointer (empty fields -- na == 0, nmocap == 0 ... -- may be null)
+    const char* missing = nullptr;
+#define X(n, c) if (!d->d.n && !missing && (((#c)[0] == '0' && (#c)[1] == 0) ? d->dsz.naconmax > 0 : ((c) > 0 && d->dsz.nworld > 0))) missing = #n;
+    {
+#define Y(n) const int n = m->ms.n; (void)n;
+      MJB_MODEL_SIZES(Y)
+#undef Y
+#define Y(n) const int n = d->dsz.n; (void)n;
+      MJB_DATA_SIZES(Y)
+#undef Y
+      MJB_DATA_INT_FIELDS(X)
+      MJB_DATA_REAL_FIELDS(X)
+    }
+#undef X
+    if (missing) {
+      const std::string name = missing;
+      delete d;
+      return fail(-2, "mjb_data_bind: null pointer for field " + name);
+    }
+  }
   d->scratch_floats = chol_scratch_floats(m->ms.nv, m->ms.nv_pad);
+  d->rk_scratch = nullptr;
+  d->rk_floats = 0;
   memset(d->cfg, 0, sizeof(d->cfg));
   cudaError_t e = cudaGetDevice(&d->device);
   if (e != cudaSuccess) {
@@ -205,7 +231,25 @@ extern "C" int mjb_data_bind(const MjbModel* m, const int* sizes, int nsizes, in
   *out = d;
   return 0;
 }
-extern "C" void mjb_data_destroy(MjbData* d) { delete d; }
+extern "C" void mjb_data_destroy(MjbData* d) {
+  if (d && d->rk_scratch) cudaFree(d->rk_scratch);
+  delete d;
+}
+
+float* mjb_internal_rk_scratch(MjbData* d, size_t floats) {
+  if (d->rk_floats >= floats && d->rk_scratch) return d->rk_scratch;
+  if (d->rk_scratch) cudaFree(d->rk_scratch);
+  d->rk_scratch = nullptr;
+  d->rk_floats = 0;
+  cudaError_t e = cudaMalloc(&d->rk_scratch, floats * sizeof(float));
+  if (e != cudaSuccess) {
+    d->rk_scratch = nullptr;
+    fail(-10, std::string("cudaMalloc of the Runge-Kutta scratch: ") + cudaGetErrorString(e));
+    return nullptr;
+  }
+  d->rk_floats = floats;
+  return d->rk_scratch;
+}
 
 // ---- launches -------------------------------------------------------------------------------
 static void fill_params(KParams& K, const MjbModel* m, const MjbData* d, const MjbOption* opt, uint32_t stages) {
@@ -233,6 +277,7 @@ int mjb_internal_params(const MjbModel* m, const MjbData* d, KParams* K) {
 }
 int mjb_internal_fail(int code, const char* msg) { return fail(code, msg); }
 void mjb_internal_count_launch(void) { g_launches++; }
+int mjb_internal_nworld(const MjbData* d) { return d->dsz.nworld; }
 
 // warps (= worlds in flight) per CTA; MJB_WARPS_PER_BLOCK overrides the per-group default
 static int warps_per_block(int dflt) {
@@ -246,20 +291,21 @@ static int warps_per_block(int dflt) {
 }
 
 template <typename F>
-static int timed_launch(cudaStream_t stream, F&& launch, int group = -1) {
+static int timed_launch(cudaStream_t stream, F&& launch, int group = -1, bool count = true) {
   cudaEvent_t e0 = nullptr, e1 = nullptr;
-  if (g_timing) {
+  const bool timing = count && g_timing.load() != 0;
+  if (timing) {
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
     cudaEventRecord(e0, stream);
   }
   launch();
-  if (g_timing) {
+  if (timing) {
     cudaEventRecord(e1, stream);
     std::lock_guard<std::mutex> lk(g_mu);
     g_events.push_back(TimedLaunch{e0, e1, group});
   }
-  g_launches++;
+  if (count) g_launches++;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(-11, std::string("kernel launch: ") + cudaGetErrorString(e));
   return 0;
@@ -288,34 +334,51 @@ static GroupKernel group_kernel_of(int g, bool in_smem, int variant) {
   }
 }
 
+// kernel variant of a group under the given options: collision follows the model's pair types and the broadphase option of THIS
+// call; make_constraint / solve are compiled once per cone type
+static int group_variant(int g, const MjbModel* m, int broadphase, int cone) {
+  if (g == G_COL) return (m->col_feat & COLF_CONVEX) ? COLF_COUNT - 1 : (m->col_feat | (broadphase != 0 ? COLF_SAP : 0));
+  return ((g == G_CON || g == G_SOL) && cone == 1) ? 1 : 0;
+}
+static MjbData::GroupCfg& group_cfg(MjbData* d, int g, int variant) {
+  return d->cfg[!variant ? g : g == G_COL ? G_COUNT + variant : G_COUNT + COLF_COUNT + (g == G_CON ? 0 : 1)];
+}
+// resolves (once) the launch configuration of a group kernel: CTA width, shared memory, resident grid.  Sets function attributes and
+// queries occupancy, so it must not run under stream capture: mjb_prepare() calls it ahead of time.
+static int resolve_cfg(int g, int variant, const MjbModel* m, MjbData* d) {
+  MjbData::GroupCfg& c = group_cfg(d, g, variant);
+  if (c.ready) return 0;
+  int wpb = warps_per_block(g == G_SOL ? group_threads(G_SOL) / 32 : 8);
+  if (32 * wpb > group_threads(g)) wpb = group_threads(g) / 32;
+  c.scratch_floats = group_scratch_floats(g, m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad, m->ms.ngeom, m->ms.nxn, variant);
+  const size_t scr_bytes = (size_t)wpb * c.scratch_floats * sizeof(float);
+  const bool in_smem =
+      group_uses_blob(g) && (size_t)m->blob_hot + 16 + scr_bytes <= (size_t)d->smem_optin && m->blob_hot <= 96 * 1024;
+  const size_t smem = in_smem ? (size_t)m->blob_hot + 16 + scr_bytes : scr_bytes;
+  if (smem > (size_t)d->smem_optin) return fail(-5, "model needs more shared memory than the device offers");
+  GroupKernel k0 = group_kernel_of(g, in_smem, variant);
+  CUDA_OK(cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 1;
+  CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k0, 32 * wpb, smem));
+  if (occ < 1) occ = 1;
+  int grid = (d->dsz.nworld + wpb - 1) / wpb;
+  const int maxgrid = d->nsm * occ;
+  if (grid > maxgrid) grid = maxgrid;
+  c.wpb = wpb;
+  c.grid = grid;
+  c.in_smem = in_smem;
+  c.smem = smem;
+  c.ready = 1;
+  return 0;
+}
+
 static int launch_group(int g, const MjbModel* m, MjbData* d, KParams& K, uint32_t stages, cudaStream_t stream) {
-  // collision: the kernel variant follows the model's pair types and the broadphase option of THIS call
-  // and make_constraint / solve are compiled once per cone type
-  const int variant = g == G_COL ? ((m->col_feat & COLF_CONVEX) ? COLF_COUNT - 1 : (m->col_feat | (K.o.broadphase != 0 ? COLF_SAP : 0))) : ((g == G_CON || g == G_SOL) && K.o.cone == 1) ? 1 : 0;
-  MjbData::GroupCfg& c = d->cfg[!variant ? g : g == G_COL ? G_COUNT + variant : G_COUNT + COLF_COUNT + (g == G_CON ? 0 : 1)];
-  if (!c.ready) {
-    int wpb = warps_per_block(g == G_SOL ? group_threads(G_SOL) / 32 : 8);
-    if (32 * wpb > group_threads(g)) wpb = group_threads(g) / 32;
-    c.scratch_floats = group_scratch_floats(g, m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad, m->ms.ngeom, m->ms.nxn, variant);
-    const size_t scr_bytes = (size_t)wpb * c.scratch_floats * sizeof(float);
-    const bool in_smem =
-        group_uses_blob(g) && (size_t)m->blob_hot + 16 + scr_bytes <= (size_t)d->smem_optin && m->blob_hot <= 96 * 1024;
-    const size_t smem = in_smem ? (size_t)m->blob_hot + 16 + scr_bytes : scr_bytes;
-    if (smem > (size_t)d->smem_optin) return fail(-5, "model needs more shared memory than the device offers");
-    GroupKernel k0 = group_kernel_of(g, in_smem, variant);
-    CUDA_OK(cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int occ = 1;
-    CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k0, 32 * wpb, smem));
-    if (occ < 1) occ = 1;
-    int grid = (d->dsz.nworld + wpb - 1) / wpb;
-    const int maxgrid = d->nsm * occ;
-    if (grid > maxgrid) grid = maxgrid;
-    c.wpb = wpb;
-    c.grid = grid;
-    c.in_smem = in_smem;
-    c.smem = smem;
-    c.ready = 1;
+  const int variant = group_variant(g, m, K.o.broadphase, K.o.cone);
+  {
+    const int rc = resolve_cfg(g, variant, m, d);
+    if (rc) return rc;
   }
+  MjbData::GroupCfg& c = group_cfg(d, g, variant);
   K.stages = stages;
   K.scratch_floats = c.scratch_floats;
   GroupKernel kern = group_kernel_of(g, c.in_smem != 0, variant);
@@ -371,8 +434,26 @@ extern "C" int mjb_forward(const MjbModel* m, MjbData* d, const MjbOption* opt, 
 extern "C" int mjb_step(const MjbModel* m, MjbData* d, const MjbOption* opt, void* s) {
   if (!opt) return fail(-1, "null option");
   const uint32_t integ = integrator_stage(opt);
-  if (!integ) return fail(-4, "integrator not implemented (RK4 is driven from the host layer)");
+  if (opt->integrator == 1) {  // forward.py:1013-1016: forward, then rungekutta4
+    const int rc = mjb_run_stages(m, d, opt, MJB_STAGES_FORWARD, s);
+    return rc ? rc : mjb_rungekutta4(m, d, opt, s);
+  }
+  if (!integ) return fail(-4, "integrator not implemented");
   return mjb_run_stages(m, d, opt, MJB_STAGES_FORWARD | integ, s);
+}
+
+// Everything a first call would otherwise do lazily (function attributes, occupancy queries, the Runge-Kutta scratch allocation),
+// for the kernel variants `opt` selects: after it, step / forward / every stage entry can be captured into a CUDA graph.
+extern "C" int mjb_prepare(const MjbModel* m, MjbData* d, const MjbOption* opt) {
+  if (!m || !d || !opt) return fail(-1, "null handle");
+  for (int g = 0; g < G_COUNT; g++) {
+    const int rc = resolve_cfg(g, group_variant(g, m, opt->broadphase, opt->cone), m, d);
+    if (rc) return rc;
+  }
+  const size_t smem = (size_t)warps_per_block(4) * d->scratch_floats * sizeof(float);
+  CUDA_OK(cudaFuncSetAttribute(mjb_solve_m_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (opt->integrator == 1 && !mjb_internal_rk_scratch(d, (size_t)mjb_rk_scratch_floats(m, d))) return -10;
+  return 0;
 }
 extern "C" int mjb_step1(const MjbModel* m, MjbData* d, const MjbOption* opt, void* s) {
   return mjb_run_stages(m, d, opt, MJB_STAGES_FWD_POSITION | MJB_STAGE_FACTOR_M | MJB_STAGE_ZERO_SENSOR | MJB_STAGE_FWD_VELOCITY, s);
@@ -461,15 +542,11 @@ extern "C" int mjb_ctrl_noise(const MjbModel* m, MjbData* d, const MjbOption* op
   fill_params(K, m, d, opt, 0);
   const int n = d->dsz.nworld * m->ms.nu;
   if (n == 0) return 0;
-  const int timing = g_timing;
-  g_timing = 0;  // not part of the step
-  int rc = timed_launch(stream, [&] { mjb_ctrl_noise_kernel<<<(n + 255) / 256, 256, 0, stream>>>(K, ctrl_center, step, ctrlnoisestd, ctrlnoiserate); });
-  g_timing = timing;
-  g_launches--;
-  return rc;
+  // not part of the step: neither timed nor counted
+  return timed_launch(stream, [&] { mjb_ctrl_noise_kernel<<<(n + 255) / 256, 256, 0, stream>>>(K, ctrl_center, step, ctrlnoisestd, ctrlnoiserate); }, -1, false);
 }
 
-extern "C" long long mjb_launch_count(void) { return g_launches; }
+extern "C" long long mjb_launch_count(void) { return g_launches.load(); }
 extern "C" void mjb_timing_enable(int on) { g_timing = on; }
 extern "C" void mjb_timing_reset(void) {
   std::lock_guard<std::mutex> lk(g_mu);

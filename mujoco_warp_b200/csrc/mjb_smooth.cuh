@@ -807,21 +807,6 @@ __device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned 
   __syncwarp();
 }
 
-// support.next_act (support.py:38-64)
-__device__ __forceinline__ float next_act(float dt, int dyntype, const float* dynprm, const float* actrange, float act, float act_dot,
-                                          float scale, bool clamp) {
-  if (dyntype == 3) {
-    const float tau = fmaxf(MJ_MINVAL, dynprm[0]);
-    act = act + scale * act_dot * tau * (1.0f - expf(-dt / tau));
-  } else if (dyntype == 5) {
-    return act;
-  } else {
-    act = act + scale * act_dot * dt;
-  }
-  if (clamp) act = clampf(act, actrange[0], actrange[1]);
-  return act;
-}
-
 // forward.fwd_actuation (forward.py:617-927), no muscles / tendons
 __device__ __forceinline__ void s_fwd_actuation(const KParams& K, const unsigned char* mb, int w, int lane) {
   const int nv = K.ms.nv, nu = K.ms.nu;

@@ -248,6 +248,21 @@ __device__ __forceinline__ Q4 quat_integrate(Q4 q, V3 v, float dt) {
 }
 __device__ __forceinline__ float safe_div(float x, float y) { return x / (y != 0.f ? y : MJ_MINVAL); }
 __device__ __forceinline__ float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+// support.next_act (support.py:38-64)
+__device__ __forceinline__ float next_act(float dt, int dyntype, const float* dynprm, const float* actrange, float act, float act_dot,
+                                          float scale, bool clamp) {
+  if (dyntype == 3) {
+    const float tau = fmaxf(MJ_MINVAL, dynprm[0]);
+    act = act + scale * act_dot * tau * (1.0f - expf(-dt / tau));
+  } else if (dyntype == 5) {
+    return act;
+  } else {
+    act = act + scale * act_dot * dt;
+  }
+  if (clamp) act = clampf(act, actrange[0], actrange[1]);
+  return act;
+}
+
 // math.py:203, 247: frame rows (a, b, c)
 __device__ __forceinline__ M3 make_frame(V3 a) {
   a = normalize(a);

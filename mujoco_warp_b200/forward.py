@@ -5,9 +5,9 @@ forward, :1004 step, :1022 step1, :1050 step2, :514 fwd_position, :593 fwd_veloc
 :837 fwd_actuation, :950 fwd_acceleration, :327 euler, :458 rungekutta4; smooth.py:358
 kinematics, :602 com_pos, :889 crb, :1104 factor_m, :2848 solve_m, :2605 transmission;
 collision_driver.py:755 collision; constraint.py:2210 make_constraint; solver.py:3297 solve;
-support.py:133 mul_m).  Each call is ONE kernel launch through the C ABI (mjb_run_stages with
-the stage bits of the requested function); nothing is computed on the host and there is no
-fallback path.
+support.py:133 mul_m).  Each call goes through the C ABI (mjb_run_stages with the stage bits of the
+requested function: one kernel launch per stage group touched, six for a whole step); nothing is
+computed on the host and there is no fallback path.
 """
 
 from __future__ import annotations
@@ -48,6 +48,16 @@ def _ensure_bound(m: types.Model, d: types.Data):
     _io.bind(m, d)
   else:
     d._bound_epoch = types._EPOCH[0]
+
+
+def prepare(m: types.Model, d: types.Data):
+  """Resolves launch configurations and library-owned scratch for the current `m.opt` ahead of time (mjb_prepare), so that the next
+  call can be captured into a CUDA graph.  `_ensure_bound` calls it on every (re)bind; call it again after changing
+  `m.opt.cone / broadphase / integrator` if the next call is to be captured."""
+  lib = _lib.load()
+  _ensure_bound(m, d)
+  opt = _lib.make_option(m)
+  _lib.check(lib, lib.mjb_prepare(m._handle, d._handle, ctypes.byref(opt)))
 
 
 def _run(m: types.Model, d: types.Data, stages: int):
@@ -133,80 +143,25 @@ def forward(m, d):
 
 
 def rungekutta4(m, d):
-  """RK4 integrator (reference forward.py:458): three extra `forward` calls on perturbed states."""
-  A = [0.5, 0.5, 1.0]
-  B = [1.0 / 6.0, 1.0 / 3.0, 1.0 / 3.0, 1.0 / 6.0]
-  dt = float(m.opt.timestep.reshape(-1)[0])
-  qpos_t0, qvel_t0 = d.qpos.clone(), d.qvel.clone()
-  qvel_rk, qacc_rk = B[0] * d.qvel, B[0] * d.qacc
-  has_act = m.sizes["na"] > 0
-  if has_act:
-    act_t0, act_dot_rk = d.act.clone(), B[0] * d.act_dot
-  for i in range(3):
-    a, b = A[i], B[i + 1]
-    _rk_integrate_pos(m, d, qpos_t0, d.qvel, a * dt)
-    d.qvel.copy_(qvel_t0 + a * dt * d.qacc)
-    if has_act:
-      d.act.copy_(act_t0 + a * dt * d.act_dot)
-    forward(m, d)
-    qvel_rk += b * d.qvel
-    qacc_rk += b * d.qacc
-    if has_act:
-      act_dot_rk += b * d.act_dot
-  d.qpos.copy_(qpos_t0)
-  d.qvel.copy_(qvel_t0)
-  if has_act:
-    d.act.copy_(act_t0)
-    d.act_dot.copy_(act_dot_rk)
-    d.act.add_(dt * d.act_dot)
-  d.qvel.add_(dt * qacc_rk)
-  _rk_integrate_pos(m, d, d.qpos.clone(), qvel_rk, dt)
-  d.time.add_(dt)
-  d.qacc_warmstart.copy_(d.qacc)
+  """RK4 integrator (reference forward.py:458), called after `forward` like the reference's.
 
-
-def _rk_integrate_pos(m, d, qpos0, qvel, h):
-  """qpos <- integrate(qpos0, qvel, h) with quaternion joints (reference forward.py:52-112), torch ops."""
-  hm = m._host
-  out = qpos0.clone()
-  for j in range(hm.sizes["njnt"]):
-    jt = int(hm.ints["jnt_type"][j])
-    qa, da = int(hm.ints["jnt_qposadr"][j]), int(hm.ints["jnt_dofadr"][j])
-    if jt in (C.JointType.FREE, C.JointType.BALL):
-      if jt == C.JointType.FREE:
-        out[:, qa : qa + 3] = qpos0[:, qa : qa + 3] + h * qvel[:, da : da + 3]
-        qa, da = qa + 3, da + 3
-      q = torch.nn.functional.normalize(qpos0[:, qa : qa + 4], dim=1)
-      v = qvel[:, da : da + 3]
-      n = v.norm(dim=1, keepdim=True)
-      ax = torch.where(n > 0, v / n.clamp_min(1e-30), torch.zeros_like(v))
-      ang = 0.5 * h * n
-      qr = torch.cat([torch.cos(ang), ax * torch.sin(ang)], dim=1)
-      w0, x0, y0, z0 = q.unbind(1)
-      w1, x1, y1, z1 = qr.unbind(1)
-      res = torch.stack(
-        [w0 * w1 - x0 * x1 - y0 * y1 - z0 * z1, w0 * x1 + x0 * w1 + y0 * z1 - z0 * y1, w0 * y1 - x0 * z1 + y0 * w1 + z0 * x1, w0 * z1 + x0 * y1 - y0 * x1 + z0 * w1],
-        dim=1,
-      )
-      out[:, qa : qa + 4] = torch.nn.functional.normalize(res, dim=1)
-    else:
-      out[:, qa] = qpos0[:, qa] + h * qvel[:, da]
-  d.qpos.copy_(out)
+  Native: four small save / accumulate / perturb / advance launches around three `forward` passes (csrc/mjb_rk4.cu); activations go
+  through the device `next_act` (filterexact dynamics, actrange clamp on the final advance)."""
+  lib = _lib.load()
+  _ensure_bound(m, d)
+  opt = _lib.make_option(m)
+  _lib.check(lib, lib.mjb_rungekutta4(m._handle, d._handle, ctypes.byref(opt), _lib.stream_ptr()))
 
 
 def step(m, d):
   """Advances the simulation by one timestep (reference forward.py:1004)."""
   integrator = int(m.opt.integrator)
-  if integrator in (C.IntegratorType.EULER, C.IntegratorType.IMPLICITFAST):
-    lib = _lib.load()
-    _ensure_bound(m, d)
-    opt = _lib.make_option(m)
-    _lib.check(lib, lib.mjb_step(m._handle, d._handle, ctypes.byref(opt), _lib.stream_ptr()))
-  elif integrator == C.IntegratorType.RK4:
-    forward(m, d)
-    rungekutta4(m, d)
-  else:
+  if integrator not in (C.IntegratorType.EULER, C.IntegratorType.RK4, C.IntegratorType.IMPLICITFAST):
     raise NotImplementedError(f"integrator {integrator} not implemented.")
+  lib = _lib.load()
+  _ensure_bound(m, d)
+  opt = _lib.make_option(m)
+  _lib.check(lib, lib.mjb_step(m._handle, d._handle, ctypes.byref(opt), _lib.stream_ptr()))
 
 
 def step1(m, d):

@@ -8,6 +8,7 @@ mujoco_warp/_src/io.py:77 put_model, :859 make_data, :1016 put_data, :1243 get_d
 
 from __future__ import annotations
 
+import ctypes
 import dataclasses
 import warnings
 from types import SimpleNamespace
@@ -410,6 +411,7 @@ def put_model(mjm, device=None) -> types.Model:
   if dev.type == "cuda":
     lib = _lib.load()
     m._handle = _lib.model_create(lib, m, int_names, real_names)
+  m._frozen = True  # blob fields can no longer be re-assigned (types.Model.__setattr__)
   return m
 
 
@@ -550,6 +552,8 @@ def bind(m: types.Model, d: types.Data):
   if d._handle is not None:
     _lib.data_destroy(lib, d._handle)
   d._handle = _lib.data_bind(lib, m, d)
+  opt = _lib.make_option(m)
+  _lib.check(lib, lib.mjb_prepare(m._handle, d._handle, ctypes.byref(opt)))  # first-call work done here: the next call is graph-capturable
   d._model = m
   d._bound_ptrs = _lib.data_ptr_signature(d)
   d._bound_epoch = types._EPOCH[0]  # set last: the assignments above bump the epoch
@@ -674,8 +678,6 @@ def reset_data(m: types.Model, d: types.Data, reset=None):
   Args:
     reset: optional bool tensor / array of shape (nworld,); None resets every world.
   """
-  import ctypes
-
   from .forward import _ensure_bound
 
   lib = _lib.load()

@@ -307,6 +307,21 @@ def resolve_shape(shape, sizes) -> tuple:
   return tuple(out)
 
 
+def data_field_numel(name: str, sizes) -> Optional[int]:
+  """Element count of an ABI data field for the given model + data sizes, or None if a symbol of its shape is unknown."""
+  shape = DATA_INT_FIELDS.get(name) or DATA_REAL_FIELDS.get(name)
+  if shape is None:
+    return None
+  try:
+    dims = resolve_shape(shape, sizes)
+  except KeyError:
+    return None
+  n = 1
+  for x in dims:
+    n *= x
+  return n
+
+
 # ----------------------------------------------------------------------------------------------
 # dataclasses
 # ----------------------------------------------------------------------------------------------
@@ -393,6 +408,17 @@ class Model:
     if name in sizes:
       return sizes[name]
     raise AttributeError(name)
+
+  def __setattr__(self, name, value):
+    # The kernels read the blob, not this object's attributes: re-assigning a blob field after put_model (the reference's
+    # domain-randomisation idiom `m.geom_friction = <(nworld, ngeom, 3) array>`, indexed there as [worldid % shape[0]]) would be
+    # silently ignored.  Edit in place (`m.geom_friction[0, g] = ...`, `m.dof_damping.copy_(x)`) instead.
+    if self.__dict__.get("_frozen") and (name in MODEL_INT_FIELDS or name in MODEL_REAL_FIELDS):
+      raise NotImplementedError(
+        f"Model.{name} is a view into the packed device model: assign in place (m.{name}[...] = value / m.{name}.copy_(value)). "
+        "Per-world (nworld-batched) model fields are not implemented."
+      )
+    object.__setattr__(self, name, value)
 
 
 # Bumped whenever a tensor attribute of any Data / Contact / Constraint object is (re)assigned; lets the

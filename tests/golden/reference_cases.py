@@ -111,6 +111,9 @@ CASES = {
   "humanoid_elliptic_cg": dict(model="humanoid", nworld=2, seed=32, sink=0.1, mode="forward", opt=dict(cone=1, solver=1)),
   "humanoid_implicitfast": dict(model="humanoid", nworld=2, seed=7, sink=0.03, mode="step", nstep=3, opt=dict(integrator=3)),
   "humanoid_rk4": dict(model="humanoid", nworld=2, seed=8, sink=0.03, mode="step", nstep=2, opt=dict(integrator=1)),
+  # RK4 with stateful actuators (filterexact + actrange clamp, integrator, filter, actearly): next_act in the stage perturbation
+  # (unclamped) and the final advance (clamped), forward.py:355-400, :213-274
+  "rk4_actuators_step4": dict(model="rk4_actuators", nworld=4, seed=17, mode="step", nstep=4, nconmax=16, njmax=32, opt=dict(integrator=1)),
   "humanoid_sap_tile": dict(model="humanoid", nworld=2, seed=9, sink=0.05, mode="forward", opt=dict(broadphase=1)),
   "humanoid_sap_segmented": dict(model="humanoid", nworld=2, seed=9, sink=0.05, mode="forward", opt=dict(broadphase=2)),
   "humanoid_no_eulerdamp_refsafe": dict(model="humanoid", nworld=2, seed=12, sink=0.03, mode="step", nstep=2, disable=["EULERDAMP", "REFSAFE"]),

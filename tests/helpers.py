@@ -164,16 +164,41 @@ def oracle_rk4_step(om, od, mjm, opt=None):
           out[w, qa] = q0[w, qa] + h * v[w, da]
     return out
 
+  def next_act(act0, act_dot, scale, clamp):  # support.py:38-64 over every actuator with activations
+    out = act0.copy()
+    for u in range(mjm.nu):
+      a0, n = int(mjm.actuator_actadr[u]), int(mjm.actuator_actnum[u])
+      if a0 < 0:
+        continue
+      dyn = int(mjm.actuator_dyntype[u])
+      for j in range(a0, a0 + n):
+        if dyn == 3:
+          tau = max(1e-15, float(mjm.actuator_dynprm[u][0]))
+          out[:, j] = act0[:, j] + scale * act_dot[:, j] * tau * (1.0 - np.exp(-dt / tau))
+        elif dyn == 5:
+          continue
+        else:
+          out[:, j] = act0[:, j] + scale * act_dot[:, j] * dt
+        if clamp and bool(mjm.actuator_actlimited[u]):
+          out[:, j] = np.clip(out[:, j], mjm.actuator_actrange[u][0], mjm.actuator_actrange[u][1])
+    return out
+
   O.run(om, od, "forward", opt=opt)
   A, B = [0.5, 0.5, 1.0], [1 / 6, 1 / 3, 1 / 3, 1 / 6]
-  q0, v0, t0 = od.qpos.copy(), od.qvel.copy(), od.time.copy()
-  vrk, ark = B[0] * od.qvel, B[0] * od.qacc
+  q0, v0, t0, a0 = od.qpos.copy(), od.qvel.copy(), od.time.copy(), od.act.copy()
+  vrk, ark, drk = B[0] * od.qvel, B[0] * od.qacc, B[0] * od.act_dot
   for i in range(3):
     od.qpos[:] = integrate_pos(q0, od.qvel, A[i] * dt)
     od.qvel[:] = v0 + A[i] * dt * od.qacc
+    if mjm.na:
+      od.act[:] = next_act(a0, od.act_dot, A[i], False)
     O.run(om, od, "forward", opt=opt)
     vrk += B[i + 1] * od.qvel
     ark += B[i + 1] * od.qacc
+    drk += B[i + 1] * od.act_dot
+  if mjm.na:
+    od.act_dot[:] = drk
+    od.act[:] = next_act(a0, drk, 1.0, True)
   od.qvel[:] = v0 + dt * ark
   od.qpos[:] = integrate_pos(q0, vrk, dt)
   od.time[:] = t0 + dt

@@ -99,6 +99,28 @@ SMALL_MODELS = {
 }
 
 
+# Runge-Kutta with stateful actuators: filterexact + activation clamp, integrator with a clamp that binds, plain filter, actearly;
+# free / ball / hinge / slide joints for the position integration (forward.py:52-112, :130-167, support.py:38-64)
+SMALL_MODELS["rk4_actuators"] = """
+    <mujoco><option timestep="0.004"/>
+      <worldbody>
+        <geom type="plane" size="5 5 .01"/>
+        <body pos="0 0 1"><joint name="a" type="hinge" axis="0 1 0" damping="0.1"/><geom type="capsule" size=".05 .2" fromto="0 0 0 .4 0 0"/>
+          <body pos=".4 0 0"><joint name="b" type="hinge" axis="0 1 0" stiffness="2"/><geom type="capsule" size=".04 .2" fromto="0 0 0 .3 0 0"/>
+            <body pos=".3 0 0"><joint name="c" type="ball" damping="0.05"/><geom type="capsule" size=".03 .1" fromto="0 0 0 .2 0 0"/></body></body>
+        </body>
+        <body pos="0 1 1"><joint name="s" type="slide" axis="0 0 1" damping="1"/><geom type="sphere" size=".1"/></body>
+        <body pos="1 1 0.5" euler="10 20 30"><freejoint/><geom type="box" size=".1 .08 .05"/></body>
+      </worldbody>
+      <actuator>
+        <general joint="a" dyntype="filterexact" dynprm="0.03" gainprm="4" actlimited="true" actrange="-0.25 0.25"/>
+        <general joint="b" dyntype="integrator" gainprm="2" actlimited="true" actrange="-0.004 0.004"/>
+        <general joint="s" dyntype="filter" dynprm="0.02" gainprm="30" biastype="affine" biasprm="0 -30 -1"/>
+        <general joint="b" dyntype="filterexact" dynprm="0.01" gainprm="1.5" actearly="true"/>
+        <motor joint="a" gear="0.5"/>
+      </actuator>
+    </mujoco>"""
+
 BOX_PAIRS_XML = """
 <mujoco>
   <worldbody>

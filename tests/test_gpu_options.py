@@ -379,3 +379,49 @@ def test_elliptic_cones(humanoid, solver):
   newton = solver == C.SolverType.NEWTON  # CG stops on its (looser) improvement criterion: float32 / float64 runs part earlier
   assert H.max_err(H.dev_np(d2, "qpos"), od2.qpos) < (1e-4 if newton else 1e-3)
   assert H.max_err(H.dev_np(d2, "qvel"), od2.qvel) < (2e-2 if newton else 1e-1)
+
+
+def test_rk4_is_native_and_graph_capturable(humanoid):
+  """mjb_step with integrator RK4: forward + mjb_rungekutta4 (csrc/mjb_rk4.cu) -- 4 x 5 stage-group launches + 4 RK launches, no
+  torch kernels, no host synchronisation, and a CUDA-graph replay equals the eager step bit for bit."""
+  from mujoco_warp_b200 import _lib
+
+  lib = _lib.load()
+  qpos, qvel, ctrl = H.make_states(humanoid, 16, seed=23)
+  m, a = H.device_data(mjw, humanoid, qpos, qvel, ctrl, 24, 64)
+  _, b = H.device_data(mjw, humanoid, qpos, qvel, ctrl, 24, 64)
+  m.opt.integrator = int(C.IntegratorType.RK4)
+  mjw.prepare(m, a)  # the RK scratch is allocated here, not inside a capture
+  mjw.prepare(m, b)
+  n0 = lib.mjb_launch_count()
+  with torch.profiler.profile(activities=[torch.profiler.ProfilerActivity.CUDA]) as prof:
+    mjw.step(m, a)
+    torch.cuda.synchronize()
+  assert lib.mjb_launch_count() - n0 == 4 * 5 + 4  # forward = five stage groups (no integrator group)
+  names = [e.key for e in prof.key_averages() if e.device_type == torch.autograd.DeviceType.CUDA]
+  foreign = [n for n in names if "mjb_" not in n and "memset" not in n.lower()]
+  assert not foreign, foreign
+  mjw.step(m, a)
+  s = torch.cuda.Stream()
+  with torch.cuda.stream(s):
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=s):
+      mjw.step(m, b)
+    g.replay()
+    g.replay()
+  torch.cuda.synchronize()
+  for f in ["qpos", "qvel", "qacc", "qacc_warmstart", "time"]:
+    assert torch.equal(a.field(f), b.field(f)), f
+
+
+def test_rk4_public_function_after_forward_equals_step(humanoid):
+  """forward(m, d); rungekutta4(m, d) == step(m, d) with integrator RK4 (forward.py:1013-1016)."""
+  qpos, qvel, ctrl = H.make_states(humanoid, 8, seed=29)
+  m, a = H.device_data(mjw, humanoid, qpos, qvel, ctrl, 24, 64)
+  _, b = H.device_data(mjw, humanoid, qpos, qvel, ctrl, 24, 64)
+  m.opt.integrator = int(C.IntegratorType.RK4)
+  mjw.step(m, a)
+  mjw.forward(m, b)
+  mjw.rungekutta4(m, b)
+  for f in ["qpos", "qvel", "qacc", "time"]:
+    assert torch.equal(a.field(f), b.field(f)), f

@@ -250,3 +250,31 @@ def test_connect_and_weld_equalities_compile_their_qpos0_data():
   with pytest.raises(NotImplementedError, match="relpose"):
     mjw.load_mjcf_string('<mujoco><worldbody><body name="a"><freejoint/><geom size=".1"/></body></worldbody>'
                          '<equality><weld body1="a" relpose="0 0 0 1 0 0 0"/></equality></mujoco>')
+
+
+def test_blob_fields_cannot_be_rebound_and_batched_options_are_rejected(humanoid):
+  """The kernels read the packed blob and one option value for all worlds: the reference's per-world randomisation idiom
+  (`m.geom_friction = <(nworld, ...)>`, `m.opt.timestep = <(nworld,)>`, indexed there as [worldid % shape[0]]) must fail loudly."""
+  from mujoco_warp_b200 import _lib
+
+  m = mjw.put_model(humanoid, device="cpu")
+  with pytest.raises(NotImplementedError, match="in place"):
+    m.geom_friction = torch.zeros(8, humanoid.ngeom, 3)
+  with pytest.raises(NotImplementedError, match="in place"):
+    m.dof_damping = m.dof_damping.clone()
+  m.geom_friction[0, 1, 0] = 0.5  # in-place edits stay legal and land in the blob
+  off = m._offsets["geom_friction"]
+  assert float(m._blob[off + 12 : off + 16].view(torch.float32)[0]) == 0.5
+  assert _lib.make_option(m).timestep == pytest.approx(float(m.opt.timestep[0]))
+  m.opt.timestep = torch.full((8,), 0.002)
+  with pytest.raises(NotImplementedError, match="per-world Option.timestep"):
+    _lib.make_option(m)
+
+
+def test_data_field_numel_matches_make_data(humanoid):
+  d = mjw.make_data(humanoid, nworld=3, nconmax=24, njmax=64, device="cpu")
+  m = mjw.put_model(humanoid, device="cpu")
+  sizes = dict(m.sizes)
+  sizes.update(d._sizes)
+  for n in list(types.DATA_INT_FIELDS) + list(types.DATA_REAL_FIELDS):
+    assert types.data_field_numel(n, sizes) == d.field(n).numel(), n
