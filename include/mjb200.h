@@ -83,6 +83,20 @@ long long mjb_rk_scratch_floats(const MjbModel* m, const MjbData* d);
  * Runge-Kutta scratch -- so that the next step / forward / stage call can be captured into a CUDA graph. */
 int mjb_prepare(const MjbModel* m, MjbData* d, const MjbOption* opt);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc (code under
+ * CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same integrator as mjb_rungekutta4 -- same inputs, same
+ * outputs, called after `forward` -- but its scratch is a file-scope `static __device__` array of MJB_RK_STATIC_MAX_FLOATS floats
+ * (4 MiB; every GPU that loads the library holds it until the process exits) instead of the cudaMalloc'ed buffer of the MjbData
+ * handle.  It calls no cudaMalloc / cudaFree / allocating library routine.  Returns -6 with a clear mjb_last_error() when
+ * nworld x round_up4(nq + 3 nv + 2 na) exceeds the maximum (humanoid: 112 floats per world, i.e. up to 9362 worlds).
+ * Every call on a device shares the one array: it keeps the previous call's contents (stage 0 overwrites every word a call
+ * reads, so nothing needs clearing), and two calls that overlap on the same GPU (different streams, or different MjbData) RACE --
+ * serialise them.  One resolve of the array's device address per device (cudaGetSymbolAddress) happens on the first call with
+ * that device current; run the kernels' own first-call set-up with mjb_prepare() before capturing. */
+#define MJB_RK_STATIC_MAX_FLOATS (1 << 20)
+int mjb_rungekutta4_static(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+long long mjb_rk_static_max_floats(void);
+
 /* smooth.solve_m (reference smooth.py:2848): x = M^-1 y using d.qLD; x, y are (nworld, nv). */
 int mjb_solve_m(const MjbModel* m, MjbData* d, float* x, const float* y, void* cuda_stream);
 /* support.mul_m (reference support.py:133): res = qM @ vec; (nworld, nv). */

@@ -102,12 +102,13 @@ def load():
     lib.mjb_data_bind.restype = ctypes.c_int
     lib.mjb_data_bind.argtypes = [vp, ip, ctypes.c_int, ctypes.POINTER(vp), ctypes.c_int, ctypes.POINTER(vp), ctypes.c_int, ctypes.POINTER(vp)]
     lib.mjb_data_destroy.argtypes = [vp]
-    for name in ("mjb_step", "mjb_forward", "mjb_step1", "mjb_step2", "mjb_rungekutta4"):
+    for name in ("mjb_step", "mjb_forward", "mjb_step1", "mjb_step2", "mjb_rungekutta4", "mjb_rungekutta4_static"):
       fn = getattr(lib, name)
       fn.restype = ctypes.c_int
       fn.argtypes = [vp, vp, ctypes.POINTER(MjbOption), vp]
     lib.mjb_prepare.restype = ctypes.c_int
     lib.mjb_prepare.argtypes = [vp, vp, ctypes.POINTER(MjbOption)]
+    lib.mjb_rk_static_max_floats.restype = ctypes.c_longlong
     lib.mjb_rk_scratch_floats.restype = ctypes.c_longlong
     lib.mjb_rk_scratch_floats.argtypes = [vp, vp]
     lib.mjb_run_stages.restype = ctypes.c_int

@@ -8,6 +8,8 @@
 //     qpos_t0 (nq) | qvel_t0 (nv) | qvel_rk (nv) | qacc_rk (nv) | act_t0 (na) | act_dot_rk (na)
 // Nothing is computed on the host, nothing synchronises, and the whole step is CUDA-graph capturable once the scratch exists
 // (mjb_prepare, or the first call).
+//
+// mjb_rungekutta4_static is the same integrator for callers that must not allocate: its scratch is a file-scope device array.
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -160,5 +162,47 @@ extern "C" int mjb_rungekutta4(const MjbModel* m, MjbData* d, const MjbOption* o
   if (n < 0) return -1;
   float* scr = mjb_internal_rk_scratch(d, n > 0 ? (size_t)n : 1);  // allocates on the first call only (mjb_prepare does it ahead of a capture)
   if (!scr) return -10;
+  return rk_run(m, d, opt, scr, static_cast<cudaStream_t>(s));
+}
+
+// ---- allocation-free variant -----------------------------------------------------------------------------------------------------
+// Scratch of mjb_rungekutta4_static: resident on every GPU that loads the library until the process exits.
+static __device__ __align__(256) float g_rk_static_scratch[MJB_RK_STATIC_MAX_FLOATS];
+
+// Device address of g_rk_static_scratch on the CURRENT device (in host code the array's name is only a handle for the runtime,
+// not an address a kernel can use), resolved once per device.
+static int rk_static_address(float** out) {
+  enum { MAX_DEVICES = 64 };
+  static std::mutex mu;
+  static float* ptr[MAX_DEVICES] = {nullptr};
+  int dev = -1;
+  CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= MAX_DEVICES) return mjb_internal_fail(-2, "mjb_rungekutta4_static: device ordinal out of range");
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptr[dev]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_rk_static_scratch);
+    if (e != cudaSuccess || !p)
+      return mjb_internal_fail(-10, (std::string("cudaGetSymbolAddress(g_rk_static_scratch): ") + cudaGetErrorString(e)).c_str());
+    ptr[dev] = static_cast<float*>(p);
+  }
+  *out = ptr[dev];
+  return 0;
+}
+
+extern "C" long long mjb_rk_static_max_floats(void) { return (long long)MJB_RK_STATIC_MAX_FLOATS; }
+
+extern "C" int mjb_rungekutta4_static(const MjbModel* m, MjbData* d, const MjbOption* opt, void* s) {
+  if (!m || !d || !opt) return mjb_internal_fail(-1, "null handle");
+  const long long n = mjb_rk_scratch_floats(m, d);
+  if (n < 0) return -1;
+  if (n > (long long)MJB_RK_STATIC_MAX_FLOATS)
+    return mjb_internal_fail(-6, ("mjb_rungekutta4_static: nworld x (nq + 3 nv + 2 na) = " + std::to_string(n) + " floats exceeds the static scratch of " +
+                                  std::to_string((long long)MJB_RK_STATIC_MAX_FLOATS) + " floats (MJB_RK_STATIC_MAX_FLOATS); use mjb_rungekutta4")
+                                     .c_str());
+  float* scr = nullptr;
+  const int rc = rk_static_address(&scr);
+  if (rc) return rc;
+  // nothing to clear: stage 0 overwrites every scratch word this call reads
   return rk_run(m, d, opt, scr, static_cast<cudaStream_t>(s));
 }
