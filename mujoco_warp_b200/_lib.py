@@ -46,6 +46,18 @@ def _includes(path, seen=None):
   return seen
 
 
+def _deps(src):
+  """Project headers `src` really includes (the preprocessor decides: the stage-group units see only their own stage headers through
+  `MJB_UNIT_GROUP`), falling back to the textual scan if the preprocessor run fails."""
+  cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
+  res = subprocess.run(["g++", "-MM", "-x", "c++", "-std=c++17", "-D__CUDACC__", "-I", INCLUDE, "-I", CSRC, "-I", cuda_inc, src],
+                       capture_output=True, text=True)  # fmt: skip
+  if res.returncode != 0:
+    return sorted(_includes(src))
+  names = res.stdout.replace("\\\n", " ").split(":", 1)[1].split()
+  return sorted(os.path.normpath(n) for n in names if os.path.normpath(n) != os.path.normpath(src))
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
   """Compiles csrc/*.cu into csrc/libmjb200.so for sm_100a (works without a GPU).
 
@@ -57,19 +69,31 @@ def build(force: bool = False, verbose: bool = False) -> str:
   objs, relink = [], force or not os.path.exists(LIB_PATH)
   common = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xptxas", "-v" if verbose else "-O3",
             "-Xcompiler", "-fPIC", "-I", INCLUDE, "-I", CSRC]  # fmt: skip
+  jobs = []
   for src in srcs:
     obj = os.path.join(objdir, os.path.splitext(os.path.basename(src))[0] + ".o")
-    deps = [src] + sorted(_includes(src))
+    deps = [src] + (_deps(src) if os.path.exists(obj) and not force else [])
     if force or not os.path.exists(obj) or any(os.path.getmtime(obj) < os.path.getmtime(p) for p in deps):
-      started = time.time()
-      res = subprocess.run(["nvcc"] + common + ["-c", src, "-o", obj], capture_output=True, text=True)
-      if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
-      os.utime(obj, (started, started))  # a header edited while the unit compiled must trigger the next rebuild
-      if verbose:
-        print(res.stderr)
-      relink = True
+      jobs.append((src, obj))
     objs.append(obj)
+
+  def compile_one(job):
+    src, obj = job
+    started = time.time()
+    res = subprocess.run(["nvcc"] + common + ["-c", src, "-o", obj], capture_output=True, text=True)
+    if res.returncode != 0:
+      raise RuntimeError(f"nvcc failed on {os.path.basename(src)}:\n" + res.stdout + res.stderr)
+    os.utime(obj, (started, started))  # a header edited while the unit compiled must trigger the next rebuild
+    return res.stderr
+
+  if jobs:  # the stage-group kernels are separate units (mjb_g_*.cu): compile them side by side
+    from concurrent.futures import ThreadPoolExecutor
+
+    with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 1)) as pool:
+      for log in pool.map(compile_one, jobs):
+        if verbose:
+          print(log)
+    relink = True
   if relink or any(os.path.getmtime(LIB_PATH) < os.path.getmtime(o) for o in objs):
     res = subprocess.run(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB_PATH] + objs, capture_output=True, text=True)
     if res.returncode != 0:

@@ -11,6 +11,7 @@
 
 #include "mjb200.h"
 #include "mjb_internal.h"
+#include "mjb_groups.h"
 #include "mjb_kernels.cuh"
 
 static thread_local std::string g_err;
@@ -311,26 +312,15 @@ static int timed_launch(cudaStream_t stream, F&& launch, int group = -1, bool co
   return 0;
 }
 
-typedef void (*GroupKernel)(const KParams);
-template <int G, int V = 0>
-static GroupKernel group_kernel(bool in_smem) {
-  return in_smem ? mjb_group_kernel<G, true, V> : mjb_group_kernel<G, false, V>;
-}
+// the stage-group kernels are instantiated in their own translation units (mjb_g_*.cu), compiled in parallel
 static GroupKernel group_kernel_of(int g, bool in_smem, int variant) {
   switch (g) {
-    case G_POS: return group_kernel<G_POS>(in_smem);
-    case G_COL:
-      switch (variant) {
-        case 1: return group_kernel<G_COL, 1>(in_smem);
-        case 2: return group_kernel<G_COL, 2>(in_smem);
-        case 3: return group_kernel<G_COL, 3>(in_smem);
-        case 7: return group_kernel<G_COL, 7>(in_smem);  // models with ellipsoid / cylinder geoms run the all-features variant
-        default: return group_kernel<G_COL, 0>(in_smem);
-      }
-    case G_CON: return variant ? group_kernel<G_CON, 1>(in_smem) : group_kernel<G_CON>(in_smem);
-    case G_VEL: return group_kernel<G_VEL>(in_smem);
-    case G_SOL: return variant ? group_kernel<G_SOL, 1>(in_smem) : group_kernel<G_SOL>(in_smem);
-    default: return group_kernel<G_EUL>(in_smem);
+    case G_POS: return mjb_gk_pos(in_smem);
+    case G_COL: return variant == COLF_COUNT - 1 ? mjb_gk_col_convex(in_smem) : mjb_gk_col(in_smem, variant);
+    case G_CON: return mjb_gk_con(in_smem, variant);
+    case G_VEL: return mjb_gk_vel(in_smem);
+    case G_SOL: return mjb_gk_sol(in_smem, variant);
+    default: return mjb_gk_eul(in_smem);
   }
 }
 
@@ -451,7 +441,7 @@ extern "C" int mjb_prepare(const MjbModel* m, MjbData* d, const MjbOption* opt) 
     if (rc) return rc;
   }
   const size_t smem = (size_t)warps_per_block(4) * d->scratch_floats * sizeof(float);
-  CUDA_OK(cudaFuncSetAttribute(mjb_solve_m_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CUDA_OK(mjb_util_solve_m_smem(smem));
   if (opt->integrator == 1 && !mjb_internal_rk_scratch(d, (size_t)mjb_rk_scratch_floats(m, d))) return -10;
   return 0;
 }
@@ -514,10 +504,10 @@ extern "C" int mjb_solve_m(const MjbModel* m, MjbData* d, float* x, const float*
   K.y = y;
   const int wpb = warps_per_block(4);
   const size_t smem = (size_t)wpb * d->scratch_floats * sizeof(float);
-  CUDA_OK(cudaFuncSetAttribute(mjb_solve_m_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CUDA_OK(mjb_util_solve_m_smem(smem));
   int grid = (d->dsz.nworld + wpb - 1) / wpb;
   if (grid > d->nsm * 8) grid = d->nsm * 8;
-  return timed_launch(stream, [&] { mjb_solve_m_kernel<<<grid, 32 * wpb, smem, stream>>>(K); });
+  return timed_launch(stream, [&] { mjb_util_solve_m(K, grid, 32 * wpb, smem, stream); });
 }
 
 extern "C" int mjb_mul_m(const MjbModel* m, MjbData* d, float* res, const float* vec, void* s) {
@@ -531,7 +521,7 @@ extern "C" int mjb_mul_m(const MjbModel* m, MjbData* d, float* res, const float*
   K.y = vec;
   const int n = d->dsz.nworld * m->ms.nv;
   if (n == 0) return 0;
-  return timed_launch(stream, [&] { mjb_mul_m_kernel<<<(n + 255) / 256, 256, 0, stream>>>(K); });
+  return timed_launch(stream, [&] { mjb_util_mul_m(K, (n + 255) / 256, stream); });
 }
 
 extern "C" int mjb_ctrl_noise(const MjbModel* m, MjbData* d, const MjbOption* opt, const float* ctrl_center, int step, float ctrlnoisestd,
@@ -543,7 +533,7 @@ extern "C" int mjb_ctrl_noise(const MjbModel* m, MjbData* d, const MjbOption* op
   const int n = d->dsz.nworld * m->ms.nu;
   if (n == 0) return 0;
   // not part of the step: neither timed nor counted
-  return timed_launch(stream, [&] { mjb_ctrl_noise_kernel<<<(n + 255) / 256, 256, 0, stream>>>(K, ctrl_center, step, ctrlnoisestd, ctrlnoiserate); }, -1, false);
+  return timed_launch(stream, [&] { mjb_util_ctrl_noise(K, (n + 255) / 256, ctrl_center, step, ctrlnoisestd, ctrlnoiserate, stream); }, -1, false);
 }
 
 extern "C" long long mjb_launch_count(void) { return g_launches.load(); }

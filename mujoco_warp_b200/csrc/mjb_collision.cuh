@@ -43,7 +43,7 @@ __device__ __forceinline__ bool is_ccd_pair(int t1, int t2) { return (t2 == GEOM
 
 // collision_convex.py:712 eval_ccd_write_contact for one pair (single contact, no collision sensor): returns the number of
 // contacts (0 / 1); dist is the surface distance, pos the midpoint of the witness points, nrm = x1 - x2 (unnormalised).
-__device__ __noinline__ int c_ccd_pair(const float* p1, const float* r1, const float* s1, int t1, const float* v1, int nv1, const int* gr1,
+static __device__ __noinline__ int c_ccd_pair(const float* p1, const float* r1, const float* s1, int t1, const float* v1, int nv1, const int* gr1,
                                        const float* p2, const float* r2, const float* s2, int t2, const float* v2, int nv2, const int* gr2,
                                        float margin, float tolerance, int iterations, float* dist, float* pos, float* nrm) {
   CcdGeom g1, g2;
@@ -70,7 +70,7 @@ __device__ __noinline__ int c_ccd_pair(const float* p1, const float* r1, const f
 
 // collision_primitive.py:52-277 plane_convex (hill climbing over the mesh graph for >= 10 vertices, else exhaustive): up to 4 contacts at the
 // deepest vertex a, the in-threshold vertex b furthest from a, c furthest from the line ab, d furthest from the edges ac / bc.
-__device__ __noinline__ int c_plane_mesh(const float* p1, const float* n1, const float* p2, const float* r2, const float* vert, int nvert,
+static __device__ __noinline__ int c_plane_mesh(const float* p1, const float* n1, const float* p2, const float* r2, const float* vert, int nvert,
                                          const int* graph, float* dist, float* pos) {
   const float HUGE_V = 1e6f;
   float pl[3], n[3];
@@ -421,7 +421,7 @@ __device__ __forceinline__ void face_rotation(float* m, int f) {
   for (int i = 0; i < 9; i++) m[i] = 0.f;
   for (int i = 0; i < 3; i++) m[3 * i + col[f][i]] = sgn[f][i];
 }
-__device__ __noinline__ int c_box_box(const float* p1, const float* R1, const float* s1, const float* p2, const float* R2, const float* s2, float margin,
+static __device__ __noinline__ int c_box_box(const float* p1, const float* R1, const float* s1, const float* p2, const float* R2, const float* s2, float margin,
                                       float* dist, float* pos, float* nrm) {  // pos: [8][3]
   float R1t[9], R2t[9], rot21[9], rot12[9], a21[9], a12[9], pos21[3], pos12[3], d21[3], d12[3], plen1[3], plen2[3];
   m3_tr(R1t, R1); m3_tr(R2t, R2);

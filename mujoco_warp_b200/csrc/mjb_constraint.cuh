@@ -103,7 +103,7 @@ __device__ __forceinline__ int emit_simple_rows(const KParams& K, int w, int lan
 
 // constraint.py:125-364 _equality_connect and :793-1108 _equality_weld (between bodies, dense Jacobian): one equality at a
 // time (they are few), lane = dof for the 3 / 6 Jacobian rows, lanes 0..5 finish the rows.  Returns the new nefc.
-__device__ __noinline__ int emit_connect_weld(const KParams& K, const unsigned char* mb, int w, int lane, int nefc, int& ne) {
+static __device__ __noinline__ int emit_connect_weld(const KParams& K, const unsigned char* mb, int w, int lane, int nefc, int& ne) {
   const int nv = K.ms.nv, np = K.ms.nv_pad, njmax = K.dsz.njmax;
   const float* qvel = DW(qvel);
   const float* scom = DW(subtree_com);

@@ -1,10 +1,26 @@
 // mjb_kernels.cuh -- the persistent one-warp-per-world pipeline kernel and small utility kernels.
 #pragma once
 
+// A translation unit that instantiates ONE stage group defines MJB_UNIT_GROUP (0 smooth_position, 1 collision, 2 make_constraint,
+// 3 smooth_velocity, 4 solve, 5 euler) before including this header and then sees only the stage headers that group needs, so an
+// edit of one stage recompiles one unit.  Host code (mjb_api.cu) leaves it undefined and sees everything.
+#ifdef MJB_UNIT_GROUP
+#define MJB_UNIT_IS(g) (MJB_UNIT_GROUP == (g))
+#else
+#define MJB_UNIT_IS(g) 1
+#endif
+#if MJB_UNIT_IS(1)
 #include "mjb_collision.cuh"
+#endif
+#if MJB_UNIT_IS(2)
 #include "mjb_constraint.cuh"
+#endif
+#if MJB_UNIT_IS(0) || MJB_UNIT_IS(3) || MJB_UNIT_IS(5) || MJB_UNIT_IS(4)
 #include "mjb_smooth.cuh"
+#endif
+#if MJB_UNIT_IS(4)
 #include "mjb_solver.cuh"
+#endif
 #include "mjb_types.cuh"
 
 // The step is issued as one launch per stage GROUP.  Every group is its own kernel instantiation:
@@ -39,6 +55,7 @@ __host__ __device__ inline uint32_t group_mask(int g) {
   return 0;
 }
 
+#ifndef MJB_UNIT_GROUP
 // per-warp shared-memory scratch (floats) of a group
 __host__ __device__ inline int group_scratch_floats(int g, int nv, int nv_pad, int njmax_pad, int ngeom, int nxn, int variant = 0) {
   int n = 0;
@@ -52,6 +69,7 @@ __host__ __device__ inline int group_scratch_floats(int g, int nv, int nv_pad, i
   }
   return (n + 3) & ~3;
 }
+#endif
 __host__ __device__ inline bool group_uses_blob(int g) { return g != G_SOL; }
 
 // Stages the model blob into shared memory with one TMA bulk copy (cp.async.bulk, completion on
@@ -114,24 +132,34 @@ __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group
   const int lane = threadIdx.x & 31, warp = __shfl_sync(FULL, threadIdx.x >> 5, 0), wpb = blockDim.x >> 5;
   float* scr = scr_base + (size_t)warp * K.scratch_floats;
   const uint32_t st = K.stages;
-#if MJB_SOL_SYNC
+#if MJB_SOL_SYNC && MJB_UNIT_IS(4)
   if constexpr (G == G_SOL) {
     s_solve_cta(K, lane, warp, wpb, scr);
     return;
   }
 #endif
   for (int w = blockIdx.x * wpb + warp; w < K.dsz.nworld; w += gridDim.x * wpb) {
+#if MJB_UNIT_IS(0)
     if constexpr (G == G_POS) {
       if (st & MJB_STAGE_KINEMATICS) s_kinematics(K, mb, w, lane);
       if (st & MJB_STAGE_COM_POS) s_com_pos(K, mb, w, lane);
       if (st & MJB_STAGE_CRB) s_crb(K, mb, w, lane);
       if (st & MJB_STAGE_FACTOR_M) s_factor_m(K, w, lane, scr);
       if (st & MJB_STAGE_TRANSMISSION) s_transmission(K, mb, w, lane);
-    } else if constexpr (G == G_COL) {
+    }
+#endif
+#if MJB_UNIT_IS(1)
+    if constexpr (G == G_COL) {
       if (K.o.run_collision_detection) s_collision<V>(K, mb, w, lane, reinterpret_cast<int*>(scr));
-    } else if constexpr (G == G_CON) {
+    }
+#endif
+#if MJB_UNIT_IS(2)
+    if constexpr (G == G_CON) {
       s_make_constraint<(V & 1) != 0>(K, mb, w, lane);
-    } else if constexpr (G == G_VEL) {
+    }
+#endif
+#if MJB_UNIT_IS(3)
+    if constexpr (G == G_VEL) {
       const bool energy = (st & MJB_STAGE_ZERO_SENSOR) && (K.o.enableflags & 2);  // EnableBit.ENERGY (forward.py:975)
       if (st & MJB_STAGE_ZERO_SENSOR) {
         if (energy) s_energy_pos(K, mb, w, lane);
@@ -141,82 +169,17 @@ __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group
       if (energy && (st & MJB_STAGE_FWD_VELOCITY)) s_energy_vel(K, w, lane);
       if (st & MJB_STAGE_FWD_ACTUATION) s_fwd_actuation(K, mb, w, lane);
       if (st & (MJB_STAGE_FWD_ACCELERATION | MJB_STAGE_FWD_ACC_FACTOR)) s_fwd_acceleration(K, mb, w, lane, scr, (st & MJB_STAGE_FWD_ACC_FACTOR) != 0);
-    } else if constexpr (G == G_SOL) {
+    }
+#endif
+#if MJB_UNIT_IS(4)
+    if constexpr (G == G_SOL) {
       s_solve<(V & 1) != 0>(K, mb, w, lane, scr);
-    } else {
+    }
+#endif
+#if MJB_UNIT_IS(5)
+    if constexpr (G == G_EUL) {
       s_integrate(K, mb, w, lane, scr, (st & MJB_STAGE_IMPLICIT) != 0);
     }
+#endif
   }
-}
-
-// smooth.solve_m (smooth.py:2848): x = (L L^T)^-1 y with L = d.qLD
-__global__ void __launch_bounds__(256) mjb_solve_m_kernel(const __grid_constant__ KParams K) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-  float* scr = reinterpret_cast<float*>(smem) + (size_t)warp * K.scratch_floats;
-  const int nv = K.ms.nv;
-  const CholScr c = chol_scr(scr, nv, K.ms.nv_pad);
-  const int ld = c.ld;
-  float* x = c.x;
-  for (int w = blockIdx.x * wpb + warp; w < K.dsz.nworld; w += gridDim.x * wpb) {
-    load_rows(scr, ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
-    chol_rdiag(scr, ld, nv, c.rd, lane);
-    for (int i = lane; i < nv; i += 32) x[i] = K.y[(size_t)w * nv + i];
-    __syncwarp();
-    warp_chol_solve<false>(scr, ld, nv, c.rd, x, lane);
-    for (int i = lane; i < nv; i += 32) K.x[(size_t)w * nv + i] = x[i];
-    __syncwarp();
-  }
-}
-
-// support.mul_m dense (support.py:105-129)
-__global__ void mjb_mul_m_kernel(const __grid_constant__ KParams K) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  const int nv = K.ms.nv, np = K.ms.nv_pad;
-  if (t >= K.dsz.nworld * nv) return;
-  const int w = t / nv, i = t - w * nv;
-  const float* row = DW(qM) + (size_t)i * np;
-  const float* v = K.y + (size_t)w * nv;
-  float s = 0.f;
-  for (int j = 0; j < nv; j++) s += row[j] * v[j];
-  K.x[(size_t)w * nv + i] = s;
-}
-
-// util_misc.halton (util_misc.py:60-73)
-__device__ __forceinline__ float halton(int index, int base) {
-  int n0 = index;
-  const float b = (float)base;
-  float f = 1.0f / b, hn = 0.f;
-  while (n0 > 0) {
-    const int n1 = n0 / base;
-    const int r = n0 - n1 * base;
-    hn += f * (float)r;
-    f /= b;
-    n0 = n1;
-  }
-  return hn;
-}
-
-// benchmark.ctrl_noise (benchmark.py:42-83)
-__global__ void mjb_ctrl_noise_kernel(const __grid_constant__ KParams K, const float* ctrl_center, int step, float ctrlnoisestd,
-                                      float ctrlnoiserate) {
-  const unsigned char* mb = K.blob;
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  const int nu = K.ms.nu;
-  if (t >= K.dsz.nworld * nu) return;
-  const int w = t / nu, a = t - w * nu;
-  const float rate = expf(-K.o.timestep / ctrlnoiserate);
-  const float scale = ctrlnoisestd * sqrtf(1.0f - rate * rate);
-  float midpoint = 0.f, halfrange = 1.f;
-  const float lo = MR(actuator_ctrlrange)[2 * a], hi = MR(actuator_ctrlrange)[2 * a + 1];
-  const bool limited = MI(actuator_ctrllimited)[a] != 0;
-  if (limited) {
-    midpoint = 0.5f * (hi + lo);
-    halfrange = 0.5f * (hi - lo);
-  }
-  if (ctrl_center != nullptr) midpoint = ctrl_center[a];
-  float ctrl = rate * DW(ctrl)[a] + (1.0f - rate) * midpoint;
-  ctrl += scale * halfrange * (2.0f * halton((step + 1) * (w + 1), a + 2) - 1.0f);
-  if (limited) ctrl = clampf(ctrl, lo, hi);
-  DW(ctrl)[a] = ctrl;
 }

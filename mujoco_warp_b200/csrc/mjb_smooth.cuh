@@ -274,7 +274,7 @@ __device__ __forceinline__ float chol_row_dot(const float* ri, const float* rj, 
   for (int k = j4 << 2; k < j; k++) s -= ri[k] * rj[k];
   return s;
 }
-__device__ __noinline__ void warp_cholesky_smem(float* A, int ld, int n, int lane) {
+static __device__ __noinline__ void warp_cholesky_smem(float* A, int ld, int n, int lane) {
   const int i0 = lane, i1 = lane + 32;
   for (int j = 0; j < n; j++) {
     const float* rj = A + j * ld;
@@ -290,7 +290,7 @@ __device__ __noinline__ void warp_cholesky_smem(float* A, int ld, int n, int lan
 }
 
 // x <- (L L^T)^-1 x with L in shared memory, x in shared memory (n <= 64).
-__device__ __noinline__ void warp_chol_solve_smem(const float* L, int ld, int n, float* x, int lane) {
+static __device__ __noinline__ void warp_chol_solve_smem(const float* L, int ld, int n, float* x, int lane) {
   const int i0 = lane, i1 = lane + 32;
   float x0 = i0 < n ? x[i0] : 0.f, x1 = i1 < n ? x[i1] : 0.f;
   const float d0 = i0 < n ? 1.0f / L[i0 * ld + i0] : 1.f, d1 = i1 < n ? 1.0f / L[i1 * ld + i1] : 1.f;
@@ -332,7 +332,7 @@ __device__ __noinline__ void warp_chol_solve_smem(const float* L, int ld, int n,
 // lane with shuffles and subtracted from the trailing rows (n^2/2 shuffle+FMA pairs, no shared-memory
 // traffic besides one 128-bit row load and store per lane).
 template <int N>
-__device__ __noinline__ void warp_cholesky_reg(float* A, int ld, int n, int lane) {
+static __device__ __noinline__ void warp_cholesky_reg(float* A, int ld, int n, int lane) {
   float r[N];
   const bool in = lane < n;
   const float4* row4 = reinterpret_cast<const float4*>(A + (in ? lane : 0) * ld);
@@ -363,7 +363,7 @@ __device__ __noinline__ void warp_cholesky_reg(float* A, int ld, int n, int lane
 }
 
 template <int N>
-__device__ __noinline__ void warp_chol_solve_reg(const float* L, int ld, int n, float* x, int lane) {
+static __device__ __noinline__ void warp_chol_solve_reg(const float* L, int ld, int n, float* x, int lane) {
   float r[N], c[N];  // r = row `lane` of L left of the diagonal, c = column `lane` of L below it
   const bool in = lane < n;
   const int i = in ? lane : 0;
@@ -393,7 +393,7 @@ __device__ __noinline__ void warp_chol_solve_reg(const float* L, int ld, int n, 
 
 __device__ __forceinline__ float dot4(const float4 a, const float4 b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
 
-__device__ __noinline__ void warp_cholesky_blk(float* A, int ld, int n, float* rdiag, int lane) {
+static __device__ __noinline__ void warp_cholesky_blk(float* A, int ld, int n, float* rdiag, int lane) {
   const int nb = (n + 3) >> 2;
   #pragma unroll 1
   for (int J = 0; J < nb; J++) {
@@ -485,7 +485,7 @@ __device__ __forceinline__ void chol_rdiag(const float* L, int ld, int n, float*
 // x <- (L L^T)^-1 x with L and x in shared memory (x padded to a multiple of 4 entries).
 // Blocked substitution: the 4x4 diagonal systems are solved redundantly by all lanes, the
 // off-diagonal part is one strip (forward: 128-bit row load, backward: four column loads) per lane.
-__device__ __noinline__ void warp_chol_solve_blk(const float* L, int ld, int n, const float* rdiag, float* x, int lane) {
+static __device__ __noinline__ void warp_chol_solve_blk(const float* L, int ld, int n, const float* rdiag, float* x, int lane) {
   const int nb = (n + 3) >> 2;
   float4* x4 = reinterpret_cast<float4*>(x);
   #pragma unroll 1
@@ -572,7 +572,7 @@ __device__ __forceinline__ void warp_chol_solve(const float* L, int ld, int n, c
 // copies the n leading rows of a global matrix (ld_src) into shared memory (ld); rows are copied
 // whole (the Cholesky only reads the lower triangle).  Optional diagonal shift.
 #if MJB_SOL_COMPACT
-__device__ __noinline__
+static __device__ __noinline__
 #else
 __device__ __forceinline__
 #endif
@@ -1016,7 +1016,7 @@ __device__ __forceinline__ void s_integrate(const KParams& K, const unsigned cha
 }
 
 // sensor.energy_pos (sensor.py:2854): potential energy = -sum_b m_b g . xipos_b + joint springs (:2704-2812); energy[1] = 0.
-__device__ __noinline__ void s_energy_pos(const KParams& K, const unsigned char* mb, int w, int lane) {
+static __device__ __noinline__ void s_energy_pos(const KParams& K, const unsigned char* mb, int w, int lane) {
   float e = 0.f;
   if (!(K.o.disableflags & DSBL_GRAVITY)) {
     const V3 g{K.o.gravity_x, K.o.gravity_y, K.o.gravity_z};
@@ -1050,7 +1050,7 @@ __device__ __noinline__ void s_energy_pos(const KParams& K, const unsigned char*
 }
 
 // sensor.energy_vel (sensor.py:2922): kinetic energy = 0.5 qvel^T M qvel (dense qM)
-__device__ __noinline__ void s_energy_vel(const KParams& K, int w, int lane) {
+static __device__ __noinline__ void s_energy_vel(const KParams& K, int w, int lane) {
   const int nv = K.ms.nv, np = K.ms.nv_pad;
   const float* qvel = DW(qvel);
   float e = 0.f;

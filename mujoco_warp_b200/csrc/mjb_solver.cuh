@@ -27,7 +27,7 @@ struct Pt3 {
 __device__ __forceinline__ Pt3 operator+(Pt3 a, Pt3 b) { return Pt3{a.c + b.c, a.g + b.g, a.h + b.h}; }
 // one out-of-line copy of the three interleaved reductions (the line search calls it in many places)
 #if MJB_SOL_COMPACT
-__device__ __noinline__
+static __device__ __noinline__
 #else
 __device__ __forceinline__
 #endif
@@ -90,14 +90,14 @@ __device__ __forceinline__ float row_dot(const float* __restrict__ row, const fl
 // out[r] = A[r, :] . vec - sub[r] for r < nrows (A row-major in global memory, rows of 4*n4 floats, 16-byte
 // aligned; vec in shared memory).  One out-of-line copy serves J qacc, M qacc, M p and J p: the solver kernel
 // is instruction-fetch bound when its hot code outgrows the 32 kB instruction cache.
-__device__ __noinline__ void mat_vec(const float* __restrict__ A, int n4, int nrows, const float* vec, float* out, const float* sub, int lane) {
+static __device__ __noinline__ void mat_vec(const float* __restrict__ A, int n4, int nrows, const float* vec, float* out, const float* sub, int lane) {
 #pragma unroll 1
   for (int r = lane; r < nrows; r += 32) {
     const float s = row_dot(A + (size_t)r * (4 * n4), vec, n4);
     out[r] = sub ? s - sub[r] : s;
   }
 }
-__device__ __noinline__ float warp_sum_ol(float v) { return warp_sum(v); }  // out-of-line copy
+static __device__ __noinline__ float warp_sum_ol(float v) { return warp_sum(v); }  // out-of-line copy
 
 // ---- elliptic friction cones (template flag ELL; compiled only into the elliptic variant of the kernel) ---------
 // Rows of one contact are contiguous here (make_constraint emits them so): row r0 = normal, r0 + j = friction
