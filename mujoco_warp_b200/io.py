@@ -694,6 +694,34 @@ def reset_data(m: types.Model, d: types.Data, reset=None):
   _lib.check(lib, lib.mjb_reset_data(m._handle, d._handle, ptr, _lib.stream_ptr()))
 
 
+def find_keys(mjm, keyname_prefix: str) -> list:
+  """Keyframe ids whose name starts with `keyname_prefix` (reference io.py:2591)."""
+  return [i for i, n in enumerate(mjm.key_names) if n.startswith(keyname_prefix)]
+
+
+def make_trajectory(mjm, keys) -> np.ndarray:
+  """Control trajectory through the keyframes `keys`, linearly interpolated at the model timestep (reference io.py:2603)."""
+  ctrls = []
+  prev_ctrl_key = np.zeros(mjm.nu, dtype=np.float64)
+  prev_time, time = 0.0, 0.0
+  dt = float(mjm.opt.timestep)
+  for key in keys:
+    ctrl_key, ctrl_time = np.asarray(mjm.key_ctrl[key], dtype=np.float64), float(mjm.key_time[key])
+    if not ctrls and ctrl_time != 0.0:
+      raise ValueError("first keyframe must have time 0.0")
+    elif ctrls and ctrl_time <= prev_time:
+      raise ValueError("keyframes must be in time order")
+    while time < ctrl_time:
+      frac = (time - prev_time) / (ctrl_time - prev_time)
+      ctrls.append(prev_ctrl_key * (1 - frac) + ctrl_key * frac)
+      time += dt
+    ctrls.append(ctrl_key)
+    time += dt
+    prev_ctrl_key = ctrl_key
+    prev_time = time
+  return np.array(ctrls)
+
+
 def override_model(m: types.Model, overrides: dict):
   """Subset of reference io.py:2498 override_model: `{"opt.solver": "cg", "opt.iterations": 5, ...}`."""
   enums = {

@@ -185,7 +185,8 @@ static inline void quat_integrate(real* q, const real* v, real dt) {
   normalize4(q);
 }
 static inline real safe_div(real x, real y) { return x / (y != 0.0 ? y : MJ_MINVAL); }
-static inline real clampr(real x, real lo, real hi) { return x < lo ? lo : (x > hi ? hi : x); }
+/* wp.clamp(x, lo, hi) = min(max(lo, x), hi): when lo > hi (a mixed solimp with dmin > dmax, constraint.py:108) the result is hi */
+static inline real clampr(real x, real lo, real hi) { const real t = x < lo ? lo : x; return t > hi ? hi : t; }
 /* math.py:203,247 make_frame: rows (a, b, c) */
 static void make_frame(real* f, const real* a_in) {
   real a[3] = {a_in[0], a_in[1], a_in[2]}, b[3], c[3];

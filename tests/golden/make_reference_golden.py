@@ -51,7 +51,10 @@ def run_reference(name):
   out = {"in_qpos": qpos, "in_qvel": qvel, "in_ctrl": ctrl}
   fn = ref.forward if c["mode"] == "forward" else ref.step
   traj_qpos, traj_qvel = [], []
-  for _ in range(c.get("nstep", 1)):
+  ctrl_traj = RC.case_ctrl_traj(name, mjm)
+  for t in range(c.get("nstep", 1)):
+    if ctrl_traj is not None:
+      d.ctrl.numpy()[...] = ctrl_traj[t]
     fn(m, d)
     traj_qpos.append(np.array(d.qpos.numpy()))
     traj_qvel.append(np.array(d.qvel.numpy()))

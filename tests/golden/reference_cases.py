@@ -88,6 +88,27 @@ def _aloha_states(mjm, nworld, seed):
   return qpos, rng.uniform(-0.05, 0.05, (nworld, mjm.nv)), ctrl
 
 
+def _aloha_replay_states(mjm, nworld, seed):
+  """Keyframe lift_pot0 exactly as testspeed --replay starts (qvel 0; the keyframe's all-zero pot quaternion becomes the identity,
+  as mj_kinematics does for the reference's put_data) then tilted by a fraction of a degree: a pot standing exactly flat on the
+  table has no unique EPA witness point)."""
+  rng = np.random.default_rng(seed)
+  k0 = [i for i, n in enumerate(mjm.key_names) if n.startswith("lift_pot")][0]
+  qpos = np.repeat(np.asarray(mjm.key_qpos[k0], dtype=np.float64)[None], nworld, axis=0)
+  ctrl = np.repeat(np.asarray(mjm.key_ctrl[k0], dtype=np.float64)[None], nworld, axis=0)
+  for j in range(mjm.njnt):
+    if int(mjm.jnt_type[j]) == 0:
+      qa = int(mjm.jnt_qposadr[j])
+      quat = np.array([1.0, 0.0, 0.0, 0.0]) + rng.normal(0, 0.004, (nworld, 4))
+      qpos[:, qa + 3 : qa + 7] = quat / np.linalg.norm(quat, axis=1, keepdims=True)
+  # the keyframe holds the lid joint EXACTLY on its lower limit (q = 0, range 0 .. 0.06) with zero load: whether `q - lo < 0` makes
+  # a limit row is then decided by rounding noise (1e-24), in the reference as much as here.  Start it a millimetre open instead.
+  lid = [j for j in range(mjm.njnt) if int(mjm.jnt_type[j]) in (2, 3) and tuple(np.asarray(mjm.jnt_range[j])) == (0.0, 0.06)]
+  for j in lid:
+    qpos[:, int(mjm.jnt_qposadr[j])] = 0.001 + 0.0005 * np.arange(nworld)
+  return qpos, np.zeros((nworld, mjm.nv)), ctrl
+
+
 def _panda_states(mjm, nworld, seed):
   """Joint angles a little beyond the joint ranges (active limits), velocities, controls beyond ctrlrange (clamping)."""
   rng = np.random.default_rng(seed)
@@ -136,6 +157,11 @@ CASES = {
   "site_equalities_step3": dict(model="site_equalities", nworld=4, seed=91, mode="step", nstep=3, njmax=32),
   # BASELINE config 5 (benchmarks/aloha_pot: 133 convex-hull meshes up to 1159 vertices, 9154 candidate geom pairs, elliptic cones)
   "aloha_pot_forward": dict(model="aloha", nworld=2, seed=95, mode="forward", nconmax=24, njmax=128, states="aloha"),
+  # config 5 beyond one forward: three Newton / elliptic steps, the CG solver, and the first 20 steps of the benchmark's own
+  # `lift_pot` keyframe replay (testspeed.py --replay; io.py:2603 make_trajectory) with the control trajectory applied per step
+  "aloha_pot_step3": dict(model="aloha", nworld=2, seed=96, mode="step", nstep=3, nconmax=24, njmax=128, states="aloha"),
+  "aloha_pot_cg_forward": dict(model="aloha", nworld=2, seed=97, mode="forward", nconmax=24, njmax=128, states="aloha", opt=dict(solver=1)),
+  "aloha_lift_pot_replay20": dict(model="aloha", nworld=2, seed=98, mode="step", nstep=20, nconmax=24, njmax=128, states="aloha_replay", replay="lift_pot"),
   "connect_weld_forward": dict(model="connect_weld", nworld=5, seed=61, mode="forward", njmax=48),
   "connect_weld_step4": dict(model="connect_weld", nworld=4, seed=62, mode="step", nstep=4, njmax=48),
   "connect_weld_njmax_overflow": dict(model="connect_weld", nworld=2, seed=63, mode="forward", njmax=16),
@@ -175,11 +201,21 @@ def case_inputs(name):
     qpos, qvel, ctrl = _panda_states(mjm, c["nworld"], c["seed"])
   elif kind == "aloha":
     qpos, qvel, ctrl = _aloha_states(mjm, c["nworld"], c["seed"])
+  elif kind == "aloha_replay":
+    qpos, qvel, ctrl = _aloha_replay_states(mjm, c["nworld"], c["seed"])
   elif kind == "box_pairs":
     qpos, qvel, ctrl = _box_pair_states(mjm, c["nworld"], c["seed"])
   else:
     qpos, qvel, ctrl = _small_states(mjm, c["nworld"], c["seed"])
   return mjm, qpos, qvel, ctrl
+
+
+def case_ctrl_traj(name, mjm):
+  """(nstep, nu) control trajectory of a keyframe-replay case (reference io.py:2591 find_keys + :2603 make_trajectory), else None."""
+  c = CASES[name]
+  if "replay" not in c:
+    return None
+  return mjw.make_trajectory(mjm, mjw.find_keys(mjm, c["replay"]))[: c.get("nstep", 1)]
 
 
 def _shape_like(r, o):
@@ -212,7 +248,13 @@ def run_oracle(name):
   for flag in c.get("enable", []):
     eflags |= int(getattr(C.EnableBit, flag))
   opt["enableflags"] = eflags
-  H.oracle_steps(om, od, c["mode"], c.get("nstep", 1), opt)
+  traj = case_ctrl_traj(name, mjm)
+  if traj is None:
+    H.oracle_steps(om, od, c["mode"], c.get("nstep", 1), opt)
+  else:
+    for t in range(c.get("nstep", 1)):
+      od.ctrl[:] = traj[t]
+      H.oracle_steps(om, od, c["mode"], 1, opt)
   return od
 
 
@@ -258,7 +300,7 @@ def compare(name, ref_out, od, verbose=True):
 SOLVER_FIELDS = "qfrc_constraint qacc qacc_warmstart efc_force efc_state efc_Ma qpos qvel act act_dot".split()
 # cases whose solver does not run to the quadratic-convergence regime: the iterates depend on rounding-level ties in
 # the linesearch (see the note at CASES["humanoid_cg_iter6"]), only the converged solution is comparable, to solver tolerance
-LOOSE_SOLVER_CASES = ("humanoid_cg", "humanoid_elliptic_cg")
+LOOSE_SOLVER_CASES = ("humanoid_cg", "humanoid_elliptic_cg", "aloha_pot_cg_forward")
 # GJK / EPA stop on opt.ccd_tolerance (1e-6): two float64 evaluation orders may differ by one EPA iteration (witness points
 # move by < the tolerance; tests/test_oracle_ccd_golden.py quantifies it pair by pair)
 CASE_TOL = {"convex_pairs_collision": 5e-6, "mesh_pairs_collision": 5e-6}

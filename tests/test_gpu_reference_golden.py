@@ -37,7 +37,11 @@ UNCONVERGED = ("humanoid_cg_iter6",)
 # against 720 reference pairs: median 1e-7, worst 1.1e-4); measured on B200, mesh fixture: contact_dist 3.9e-4, efc_aref 2.6e-2
 # (aref = -k * imp * pos with k ~ 2500: a 1e-5 depth error is a 2.5e-2 aref error).
 _CCD_TOL = {"contact_dist": 1e-3, "efc_pos": 1e-3, "contact_pos": 2e-3, "contact_frame": 2e-2, "efc_J": 3e-2, "efc_aref": 8e-2, "efc_D": 1e-3}
-CASE_TOL = {"convex_pairs_collision": _CCD_TOL, "mesh_pairs_collision": _CCD_TOL}
+# aloha_pot (config 5): mesh contacts through the float32 GJK / EPA; polyhedral hulls pin the normal far better than the smooth shapes above
+# (measured on B200: contact_frame <= 2.8e-4, everything else inside the generic tolerances, solver outputs INCLUDED)
+_ALOHA_TOL = {"contact_frame": 1e-3}
+CASE_TOL = {"convex_pairs_collision": _CCD_TOL, "mesh_pairs_collision": _CCD_TOL, "aloha_pot_forward": _ALOHA_TOL, "aloha_pot_step3": _ALOHA_TOL,
+            "aloha_pot_cg_forward": _ALOHA_TOL, "aloha_lift_pot_replay20": _ALOHA_TOL}  # fmt: skip
 CASE_SKIP_SOLVER = ("convex_pairs_collision", "mesh_pairs_collision")
 FACTOR_FIELDS = ("qacc_smooth", "qLD")
 EXACT = ("efc_type", "efc_id", "contact_dim", "contact_geom")
@@ -72,7 +76,10 @@ def test_device_matches_reference_execution(name):
   for k, v in RC.case_opt(name).items():
     setattr(m.opt, k, v)
   traj_q, traj_v = [], []
-  for _ in range(c.get("nstep", 1)):
+  ctrl_traj = RC.case_ctrl_traj(name, mjm)
+  for t in range(c.get("nstep", 1)):
+    if ctrl_traj is not None:
+      d.ctrl.copy_(torch.from_numpy(np.broadcast_to(ctrl_traj[t], (c["nworld"], mjm.nu)).astype(np.float32)))
     (mjw.forward if c["mode"] == "forward" else mjw.step)(m, d)
     traj_q.append(H.dev_np(d, "qpos").copy())
     traj_v.append(H.dev_np(d, "qvel").copy())

@@ -28,7 +28,10 @@ def test_oracle_matches_reference_execution(name):
   np.testing.assert_array_equal(RC.case_inputs(name)[1], g["in_qpos"])  # the fixture's inputs are the seeded ones
   om, od = H.oracle_data(mjm, g["in_qpos"], g["in_qvel"], g["in_ctrl"], c.get("nconmax", 24), c.get("njmax", 64))
   traj = []
-  for _ in range(c.get("nstep", 1)):
+  ctrl_traj = RC.case_ctrl_traj(name, mjm)
+  for t in range(c.get("nstep", 1)):
+    if ctrl_traj is not None:
+      od.ctrl[:] = ctrl_traj[t]
     H.oracle_steps(om, od, c["mode"], 1, RC.case_opt(name))
     traj.append(od.qpos.copy())
   worst = RC.compare(name, g, od, verbose=False)

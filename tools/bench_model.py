@@ -22,21 +22,7 @@ MODELS = {"panda": ("benchmarks/franka_emika_panda/scene.xml", 32768, 1, 5), "hu
 REPLAY = {"aloha": "lift_pot"}
 
 
-def make_trajectory(mjm, keys):
-  """Control trajectory through the keyframes `keys` by linear interpolation (reference io.py:2603 make_trajectory)."""
-  import numpy as np
-
-  ctrls, prev, prev_time, time = [], np.zeros(mjm.nu), 0.0, 0.0
-  for k in keys:
-    ck, ct = np.asarray(mjm.key_ctrl[k], dtype=np.float64), float(mjm.key_time[k])
-    while time < ct:
-      frac = (time - prev_time) / (ct - prev_time)
-      ctrls.append(prev * (1 - frac) + ck * frac)
-      time += float(mjm.opt.timestep)
-    ctrls.append(ck)
-    time += float(mjm.opt.timestep)
-    prev, prev_time = ck, time
-  return np.array(ctrls)
+make_trajectory = mjw.make_trajectory  # reference io.py:2603
 
 
 def main():
