@@ -52,6 +52,7 @@ struct MjbData {
   int device;
   int nsm;
   int smem_optin;
+  int* queue;         // G_COUNT dynamic world counters (one per stage group), zeroed at the start of every mjb_run_stages
   float* rk_scratch;  // Runge-Kutta temporaries (reference forward.py:465-475 allocates them per call): cudaMalloc'ed by mjb_prepare / on first use
   size_t rk_floats;
   // launch configuration of the pipeline kernel, resolved on the first launch
@@ -221,6 +222,7 @@ extern "C" int mjb_data_bind(const MjbModel* m, const int* sizes, int nsizes, in
   d->scratch_floats = chol_scratch_floats(m->ms.nv, m->ms.nv_pad);
   d->rk_scratch = nullptr;
   d->rk_floats = 0;
+  d->queue = nullptr;
   memset(d->cfg, 0, sizeof(d->cfg));
   cudaError_t e = cudaGetDevice(&d->device);
   if (e != cudaSuccess) {
@@ -229,11 +231,20 @@ extern "C" int mjb_data_bind(const MjbModel* m, const int* sizes, int nsizes, in
   }
   cudaDeviceGetAttribute(&d->nsm, cudaDevAttrMultiProcessorCount, d->device);
   cudaDeviceGetAttribute(&d->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, d->device);
+  static const int dynamic = getenv("MJB_DYNAMIC_WORLDS") ? atoi(getenv("MJB_DYNAMIC_WORLDS")) : 1;
+  if (dynamic) {
+    e = cudaMalloc(&d->queue, G_COUNT * sizeof(int));
+    if (e != cudaSuccess) {
+      delete d;
+      return fail(-10, std::string("cudaMalloc of the world queue: ") + cudaGetErrorString(e));
+    }
+  }
   *out = d;
   return 0;
 }
 extern "C" void mjb_data_destroy(MjbData* d) {
   if (d && d->rk_scratch) cudaFree(d->rk_scratch);
+  if (d && d->queue) cudaFree(d->queue);
   delete d;
 }
 
@@ -267,6 +278,7 @@ static void fill_params(KParams& K, const MjbModel* m, const MjbData* d, const M
   K.cold_global = m->blob_hot < m->blob_bytes;
   K.scratch_floats = d->scratch_floats;
   K.stages = stages;
+  K.queue = d->queue;
 }
 
 int mjb_internal_params(const MjbModel* m, const MjbData* d, KParams* K) {
@@ -404,6 +416,7 @@ extern "C" int mjb_run_stages(const MjbModel* m, MjbData* d, const MjbOption* op
     CUDA_OK(cudaMemsetAsync(d->d.nacon, 0, sizeof(int), stream));
     CUDA_OK(cudaMemsetAsync(d->d.ncollision, 0, sizeof(int), stream));
   }
+  if (d->queue) CUDA_OK(cudaMemsetAsync(d->queue, 0, G_COUNT * sizeof(int), stream));
   for (int g = 0; g < G_COUNT; g++) {
     const uint32_t gs = stages & group_mask(g);
     if (!gs) continue;

@@ -138,7 +138,12 @@ __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group
     return;
   }
 #endif
-  for (int w = blockIdx.x * wpb + warp; w < K.dsz.nworld; w += gridDim.x * wpb) {
+  // Worlds are handed out dynamically: every warp starts on world (CTA, warp) and fetches its next world from a per-launch counter.
+  // Per-world time varies (contacts, solver iterations), and nworld is rarely a multiple of the resident warps: with a static
+  // stride the slowest warp decides (8192 worlds on 2960 resident solver warps = 2 or 3 worlds per warp).
+  const int nresident = gridDim.x * wpb;
+  for (int w = blockIdx.x * wpb + warp; w < K.dsz.nworld;
+       w = K.queue ? uniform_i(lane == 0 ? nresident + atomicAdd(K.queue + G, 1) : 0) : w + nresident) {
 #if MJB_UNIT_IS(0)
     if constexpr (G == G_POS) {
       if (st & MJB_STAGE_KINEMATICS) s_kinematics(K, mb, w, lane);

@@ -85,6 +85,7 @@ struct KParams {
   int cold_global;            // 1: the cold tables (pair lists, mesh vertices / graphs) stay in global memory behind the staged prefix
   int scratch_floats;         // per-warp shared-memory scratch
   uint32_t stages;
+  int* queue;  // dynamic world queue of this launch (zeroed by the host before the group kernels run), or null: static striding
   // optional extra operands for the small utility kernels
   float* x;
   const float* y;
