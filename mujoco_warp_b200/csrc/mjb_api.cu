@@ -350,10 +350,11 @@ static MjbData::GroupCfg& group_cfg(MjbData* d, int g, int variant) {
 static int resolve_cfg(int g, int variant, const MjbModel* m, MjbData* d) {
   MjbData::GroupCfg& c = group_cfg(d, g, variant);
   if (c.ready) return 0;
-  int wpb = warps_per_block(g == G_SOL ? group_threads(G_SOL) / 32 : 8);
+  const int wpw = 32 / group_lw(g);  // worlds per warp
+  int wpb = warps_per_block(g == G_SOL ? group_threads(G_SOL) / 32 : wpw > 1 ? 4 : 8);
   if (32 * wpb > group_threads(g)) wpb = group_threads(g) / 32;
   c.scratch_floats = group_scratch_floats(g, m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad, m->ms.ngeom, m->ms.nxn, variant);
-  const size_t scr_bytes = (size_t)wpb * c.scratch_floats * sizeof(float);
+  const size_t scr_bytes = (size_t)wpb * wpw * c.scratch_floats * sizeof(float);
   const bool in_smem =
       group_uses_blob(g) && (size_t)m->blob_hot + 16 + scr_bytes <= (size_t)d->smem_optin && m->blob_hot <= 96 * 1024;
   const size_t smem = in_smem ? (size_t)m->blob_hot + 16 + scr_bytes : scr_bytes;
@@ -363,7 +364,7 @@ static int resolve_cfg(int g, int variant, const MjbModel* m, MjbData* d) {
   int occ = 1;
   CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k0, 32 * wpb, smem));
   if (occ < 1) occ = 1;
-  int grid = (d->dsz.nworld + wpb - 1) / wpb;
+  int grid = (d->dsz.nworld + wpb * wpw - 1) / (wpb * wpw);
   const int maxgrid = d->nsm * occ;
   if (grid > maxgrid) grid = maxgrid;
   c.wpb = wpb;

@@ -22,6 +22,9 @@
 #include "mjb_solver.cuh"
 #endif
 #include "mjb_types.cuh"
+#ifndef MJB_LW
+#define MJB_LW 32
+#endif
 
 // The step is issued as one launch per stage GROUP.  Every group is its own kernel instantiation:
 // compact code (the instruction cache holds it while warps drift apart), its own register budget
@@ -71,6 +74,8 @@ __host__ __device__ inline int group_scratch_floats(int g, int nv, int nv_pad, i
 }
 #endif
 __host__ __device__ inline bool group_uses_blob(int g) { return g != G_SOL; }
+// lanes per world of a group's kernel (worlds per warp = 32 / lanes)
+__host__ __device__ constexpr int group_lw(int g) { return (g == G_POS || g == G_VEL || g == G_EUL) ? MJB_SMOOTH_LW : 32; }
 
 // Stages the model blob into shared memory with one TMA bulk copy (cp.async.bulk, completion on
 // an mbarrier).  All threads of the CTA wait on the barrier's phase 0.
@@ -129,8 +134,12 @@ __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group
   asm volatile("griddepcontrol.wait;" ::: "memory");
   // broadcast from lane 0 so that the compiler can treat the warp index (and every loop / branch
   // that depends on it) as warp-uniform
-  const int lane = threadIdx.x & 31, warp = __shfl_sync(FULL, threadIdx.x >> 5, 0), wpb = blockDim.x >> 5;
-  float* scr = scr_base + (size_t)warp * K.scratch_floats;
+  // A warp carries WPW = 32 / LW worlds (LW lanes each); `lane` is the lane inside the world's group.
+  constexpr int LW = group_lw(G), WPW = 32 / LW;
+  static_assert(LW == 32 || LW == MJB_LW, "a sub-warp group kernel must be compiled with MJB_LW = its lane count");
+  const int lane32 = threadIdx.x & 31, lane = lane32 % LW, grp = lane32 / LW;
+  const int warp = __shfl_sync(FULL, threadIdx.x >> 5, 0), wpb = blockDim.x >> 5;
+  float* scr = scr_base + (size_t)(warp * WPW + grp) * K.scratch_floats;
   const uint32_t st = K.stages;
 #if MJB_SOL_SYNC && MJB_UNIT_IS(4)
   if constexpr (G == G_SOL) {
@@ -141,9 +150,11 @@ __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group
   // Worlds are handed out dynamically: every warp starts on world (CTA, warp) and fetches its next world from a per-launch counter.
   // Per-world time varies (contacts, solver iterations), and nworld is rarely a multiple of the resident warps: with a static
   // stride the slowest warp decides (8192 worlds on 2960 resident solver warps = 2 or 3 worlds per warp).
-  const int nresident = gridDim.x * wpb;
-  for (int w = blockIdx.x * wpb + warp; w < K.dsz.nworld;
-       w = K.queue ? uniform_i(lane == 0 ? nresident + atomicAdd(K.queue + G, 1) : 0) : w + nresident) {
+  // (Units of WPW consecutive worlds; the groups of a last, partial unit repeat its last world -- same inputs, same stores.)
+  const int nresident = gridDim.x * wpb, nunit = (K.dsz.nworld + WPW - 1) / WPW;
+  for (int u = blockIdx.x * wpb + warp; u < nunit;
+       u = K.queue ? uniform_i(lane32 == 0 ? nresident + atomicAdd(K.queue + G, 1) : 0) : u + nresident) {
+    const int w = min(u * WPW + grp, K.dsz.nworld - 1);
 #if MJB_UNIT_IS(0)
     if constexpr (G == G_POS) {
       if (st & MJB_STAGE_KINEMATICS) s_kinematics(K, mb, w, lane);

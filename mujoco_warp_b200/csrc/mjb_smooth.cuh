@@ -14,6 +14,25 @@
 
 #include "mjb_types.cuh"
 
+// Lanes per world of the stage functions in this header.  32: one warp per world.  8 / 16: a warp carries 4 / 2 worlds, `lane` is
+// the lane inside the world's group and every loop strides by MJB_LW.  The tree recursions keep 2-3 lanes busy per level whatever
+// the group width, so narrower groups execute several worlds for the price of one; control flow in these stages depends on the
+// model only, so the groups of a warp stay convergent and __syncwarp() keeps its full mask.  Set per translation unit.
+// Measured on B200 (humanoid, 8192 worlds, 7 warps per CTA so that all worlds are resident in one wave): 8 lanes per world
+// smooth_position 69 -> 80 us, smooth_velocity 111 -> 95 us, euler 20 -> 18 us.  The stages are chains of dependent global-memory
+// round trips (parent poses, subtree sums, ancestor walks); with a quarter of the warps in flight those latencies are no longer
+// hidden, which cancels the saved instructions.  The default therefore stays at one warp per world (MJB_SMOOTH_LW = 32).
+#ifndef MJB_LW
+#define MJB_LW 32
+#endif
+static_assert(MJB_LW == 32 || MJB_LW == 16 || MJB_LW == 8, "lanes per world: 8, 16 or 32");
+// sum over the lanes of a world's group
+__device__ __forceinline__ float lw_sum(float v) {
+#pragma unroll
+  for (int o = MJB_LW / 2; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  return v;
+}
+
 // ---------------------------------------------------------------------------------------------
 // smooth.kinematics (smooth.py:45-224)
 // ---------------------------------------------------------------------------------------------
@@ -27,7 +46,7 @@ __device__ __forceinline__ void s_kinematics(const KParams& K, const unsigned ch
   const int* tree_adr = MI(body_tree_adr);
   for (int lv = 1; lv < K.ms.nlevel; lv++) {
     const int a1 = tree_adr[lv + 1];
-    for (int i = tree_adr[lv] + lane; i < a1; i += 32) {
+    for (int i = tree_adr[lv] + lane; i < a1; i += MJB_LW) {
       const int b = tree[i];
       const int pid = MI(body_parentid)[b];
       int jadr = MI(body_jntadr)[b];
@@ -84,21 +103,21 @@ __device__ __forceinline__ void s_kinematics(const KParams& K, const unsigned ch
     __syncwarp();
   }
   // body matrices and inertial frames (smooth.py:147-173)
-  for (int b = lane; b < K.ms.nbody; b += 32) {
+  for (int b = lane; b < K.ms.nbody; b += MJB_LW) {
     const Q4 q = ld4(xquat_o + 4 * b);
     stm3(DW(xmat) + 9 * b, quat_to_mat(q));
     st3(DW(xipos) + 3 * b, ld3(xpos_o + 3 * b) + rot_vec_quat(ld3(MR(body_ipos) + 3 * b), q));
     stm3(DW(ximat) + 9 * b, quat_to_mat(mul_quat(q, ld4(MR(body_iquat) + 4 * b))));
   }
   // geoms (smooth.py:177-203); static world geoms keep their make_data pose
-  for (int g = lane; g < K.ms.ngeom; g += 32) {
+  for (int g = lane; g < K.ms.ngeom; g += MJB_LW) {
     if (MI(geom_static)[g]) continue;
     const int b = MI(geom_bodyid)[g];
     const Q4 q = ld4(xquat_o + 4 * b);
     st3(DW(geom_xpos) + 3 * g, ld3(xpos_o + 3 * b) + rot_vec_quat(ld3(MR(geom_pos) + 3 * g), q));
     stm3(DW(geom_xmat) + 9 * g, quat_to_mat(mul_quat(q, ld4(MR(geom_quat) + 4 * g))));
   }
-  for (int s = lane; s < K.ms.nsite; s += 32) {  // smooth.py:207-224
+  for (int s = lane; s < K.ms.nsite; s += MJB_LW) {  // smooth.py:207-224
     const int b = MI(site_bodyid)[s];
     const Q4 q = ld4(xquat_o + 4 * b);
     st3(DW(site_xpos) + 3 * s, ld3(xpos_o + 3 * b) + rot_vec_quat(ld3(MR(site_pos) + 3 * s), q));
@@ -114,7 +133,7 @@ __device__ __forceinline__ void s_com_pos(const KParams& K, const unsigned char*
   const float* xipos = DW(xipos);
   float* scom = DW(subtree_com);
   const int nb = K.ms.nbody;
-  for (int b = lane; b < nb; b += 32) {  // subtree = id range [b, end)
+  for (int b = lane; b < nb; b += MJB_LW) {  // subtree = id range [b, end)
     const int end = MI(body_subtreeend)[b];
     V3 acc = V3{0.f, 0.f, 0.f};
     for (int c = b; c < end; c++) acc = acc + ld3(xipos + 3 * c) * MR(body_mass)[c];
@@ -123,7 +142,7 @@ __device__ __forceinline__ void s_com_pos(const KParams& K, const unsigned char*
     st3(scom + 3 * b, acc);
   }
   __syncwarp();
-  for (int b = lane; b < nb; b += 32) {  // smooth.py:511-553 (mju_inertCom)
+  for (int b = lane; b < nb; b += MJB_LW) {  // smooth.py:511-553 (mju_inertCom)
     const M3 mat = ldm3(DW(ximat) + 9 * b);
     const V3 inert = ld3(MR(body_inertia) + 3 * b);
     const float mass = MR(body_mass)[b];
@@ -148,7 +167,7 @@ __device__ __forceinline__ void s_com_pos(const KParams& K, const unsigned char*
     res[8] = mass * dif.z;
     res[9] = mass;
   }
-  for (int j = lane; j < K.ms.njnt; j += 32) {  // smooth.py:557-598
+  for (int j = lane; j < K.ms.njnt; j += MJB_LW) {  // smooth.py:557-598
     const int b = MI(jnt_bodyid)[j];
     const int jt = MI(jnt_type)[j];
     float* res = DW(cdof) + 6 * MI(jnt_dofadr)[j];
@@ -184,7 +203,7 @@ __device__ __forceinline__ void s_crb(const KParams& K, const unsigned char* mb,
   const int nb = K.ms.nbody, nv = K.ms.nv, np = K.ms.nv_pad;
   const float* cinert = DW(cinert);
   float* crb = DW(crb);
-  for (int b = lane; b < nb; b += 32) {
+  for (int b = lane; b < nb; b += MJB_LW) {
     // reference accumulates children into parents except into the world body (smooth.py:820)
     const int end = b == 0 ? 1 : MI(body_subtreeend)[b];
     float acc[10];
@@ -201,11 +220,11 @@ __device__ __forceinline__ void s_crb(const KParams& K, const unsigned char* mb,
   {
     float4* q4 = reinterpret_cast<float4*>(qM);
     const int n4 = (np * np) >> 2;
-    for (int i = lane; i < n4; i += 32) q4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = lane; i < n4; i += MJB_LW) q4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   __syncwarp();
   const float* cdof = DW(cdof);
-  for (int i = lane; i < nv; i += 32) {  // smooth.py:856-885
+  for (int i = lane; i < nv; i += MJB_LW) {  // smooth.py:856-885
     const S6 ci = ld6(cdof + 6 * i);
     const S6 buf = inert_vec(crb + 10 * MI(dof_bodyid)[i], ci);
     qM[i * np + i] = MR(dof_armature)[i] + dot6(ci, buf);
@@ -406,7 +425,7 @@ static __device__ __noinline__ void warp_cholesky_blk(float* A, int ld, int n, f
     const float4* p2 = reinterpret_cast<const float4*>(A + r2 * ld);
     const float4* p3 = reinterpret_cast<const float4*>(A + r3 * ld);
     #pragma unroll 1
-    for (int i = lane; i < n; i += 32) {
+    for (int i = lane; i < n; i += MJB_LW) {
       if (i < c0) continue;
       float4* own = reinterpret_cast<float4*>(A + i * ld);
       float4 acc = own[J];
@@ -433,7 +452,7 @@ static __device__ __noinline__ void warp_cholesky_blk(float* A, int ld, int n, f
     if (lane == 0) reinterpret_cast<float4*>(rdiag)[J] = make_float4(i0, i1, i2, i3);  // 1 / L_jj
     __syncwarp();
     #pragma unroll 1
-    for (int i = lane; i < n; i += 32) {
+    for (int i = lane; i < n; i += MJB_LW) {
       if (i < c0) continue;
       float4* own = reinterpret_cast<float4*>(A + i * ld);
       const float4 a = own[J];
@@ -478,7 +497,7 @@ __device__ __forceinline__ DiagBlock load_diag_block(const float* L, int ld, int
 
 // reciprocal diagonal of a factor that was loaded rather than computed here (padding entries are 1)
 __device__ __forceinline__ void chol_rdiag(const float* L, int ld, int n, float* rdiag, int lane) {
-  for (int i = lane; i < ((n + 3) & ~3); i += 32) rdiag[i] = i < n ? 1.0f / L[i * ld + i] : 1.0f;
+  for (int i = lane; i < ((n + 3) & ~3); i += MJB_LW) rdiag[i] = i < n ? 1.0f / L[i * ld + i] : 1.0f;
   __syncwarp();
 }
 
@@ -489,7 +508,7 @@ static __device__ __noinline__ void warp_chol_solve_blk(const float* L, int ld, 
   const int nb = (n + 3) >> 2;
   float4* x4 = reinterpret_cast<float4*>(x);
   #pragma unroll 1
-  for (int i = n + lane; i < 4 * nb; i += 32) x[i] = 0.f;
+  for (int i = n + lane; i < 4 * nb; i += MJB_LW) x[i] = 0.f;
   __syncwarp();
   #pragma unroll 1
   for (int J = 0; J < nb; J++) {  // forward: L y = b
@@ -503,7 +522,7 @@ static __device__ __noinline__ void warp_chol_solve_blk(const float* L, int ld, 
     __syncwarp();
     if (lane == 0) x4[J] = y;
     #pragma unroll 1
-    for (int i = 4 * J + 4 + lane; i < n; i += 32) x[i] -= dot4(reinterpret_cast<const float4*>(L + i * ld)[J], y);
+    for (int i = 4 * J + 4 + lane; i < n; i += MJB_LW) x[i] -= dot4(reinterpret_cast<const float4*>(L + i * ld)[J], y);
     __syncwarp();
   }
   #pragma unroll 1
@@ -524,7 +543,7 @@ static __device__ __noinline__ void warp_chol_solve_blk(const float* L, int ld, 
     const float* q3 = L + min(c0 + 3, n - 1) * ld;
     // rows past n have z == 0 there (identity padding), so the aliased loads contribute nothing
     #pragma unroll 1
-    for (int i = lane; i < c0; i += 32) x[i] -= q0[i] * z.x + q1[i] * z.y + q2[i] * z.z + q3[i] * z.w;
+    for (int i = lane; i < c0; i += MJB_LW) x[i] -= q0[i] * z.x + q1[i] * z.y + q2[i] * z.z + q3[i] * z.w;
     __syncwarp();
   }
 }
@@ -586,21 +605,21 @@ void load_rows(float* A, int ld, const float* src, int ld_src, int n, int lane, 
     if (c4 <= 8) {  // rows of <= 32 floats: 4 rows per pass, lane = (row % 4, float4 column)
       const int q = lane & 7;
 #pragma unroll 2
-      for (int i = lane >> 3; i < n; i += 4)
+      for (int i = lane >> 3; i < n; i += MJB_LW / 8)
         if (q < c4) a4[i * ld4 + q] = s4[i * c4 + q];
     } else {
 #pragma unroll 1
       for (int i = 0; i < n; i++)
-        for (int q = lane; q < c4; q += 32) a4[i * ld4 + q] = s4[i * c4 + q];
+        for (int q = lane; q < c4; q += MJB_LW) a4[i * ld4 + q] = s4[i * c4 + q];
     }
   } else {
 #pragma unroll 1
     for (int i = 0; i < n; i++)
-      for (int j = lane; j < ld_src; j += 32) A[i * ld + j] = src[i * ld_src + j];
+      for (int j = lane; j < ld_src; j += MJB_LW) A[i * ld + j] = src[i * ld_src + j];
   }
   __syncwarp();
   if (diag_add != nullptr) {
-    for (int i = lane; i < n; i += 32) A[i * ld + i] += diag_scale * diag_add[i];
+    for (int i = lane; i < n; i += MJB_LW) A[i * ld + i] += diag_scale * diag_add[i];
     __syncwarp();
   }
 }
@@ -609,13 +628,13 @@ void load_rows(float* A, int ld, const float* src, int ld_src, int n, int lane, 
 __device__ __forceinline__ void store_qLD(const KParams& K, int w, int lane, const float* L, int ld) {
   const int nv = K.ms.nv;
   float* qLD = DW(qLD);
-  if (nv <= 32) {
+  if (MJB_LW == 32 && nv <= 32) {
 #pragma unroll 4
     for (int i = 0; i < nv; i++)
       if (lane < nv) qLD[i * nv + lane] = (lane <= i) ? L[i * ld + lane] : 0.f;
   } else {
     for (int i = 0; i < nv; i++)
-      for (int j = lane; j < nv; j += 32) qLD[i * nv + j] = (j <= i) ? L[i * ld + j] : 0.f;
+      for (int j = lane; j < nv; j += MJB_LW) qLD[i * nv + j] = (j <= i) ? L[i * ld + j] : 0.f;
   }
 }
 
@@ -635,7 +654,7 @@ __device__ __forceinline__ void s_factor_m(const KParams& K, int w, int lane, fl
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void s_transmission(const KParams& K, const unsigned char* mb, int w, int lane) {
   const float* qpos = DW(qpos);
-  for (int a = lane; a < K.ms.nu; a += 32) {
+  for (int a = lane; a < K.ms.nu; a += MJB_LW) {
     const int j = MI(actuator_trnid)[2 * a];
     const int jt = MI(jnt_type)[j], qa = MI(jnt_qposadr)[j];
     const int trn = MI(actuator_trntype)[a];
@@ -680,7 +699,7 @@ __device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned 
   const int* tree = MI(body_tree);
   const int* tree_adr = MI(body_tree_adr);
 
-  for (int a = lane; a < K.ms.nu; a += 32) {
+  for (int a = lane; a < K.ms.nu; a += MJB_LW) {
     const int adr = DW(moment_rowadr)[a], nnz = DW(moment_rownnz)[a];
     float v = 0.f;
     for (int i = 0; i < nnz; i++) v += DW(actuator_moment)[adr + i] * qvel[DW(moment_colind)[adr + i]];
@@ -688,7 +707,7 @@ __device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned 
   }
   // passive forces: lane per joint
   const int dsbl_spring = K.o.disableflags & DSBL_SPRING, dsbl_damper = K.o.disableflags & DSBL_DAMPER;
-  for (int j = lane; j < K.ms.njnt; j += 32) {
+  for (int j = lane; j < K.ms.njnt; j += MJB_LW) {
     const int da = MI(jnt_dofadr)[j], qa = MI(jnt_qposadr)[j], jt = MI(jnt_type)[j];
     const float k = MR(jnt_stiffness)[j], c = MR(dof_damping)[da];
     const bool hs = k != 0.f && !dsbl_spring, hd = c != 0.f && !dsbl_damper;
@@ -721,7 +740,7 @@ __device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned 
   if (K.ms.ngravcomp && !(K.o.disableflags & DSBL_GRAVITY) && !(dsbl_spring && dsbl_damper)) {
     __syncwarp();
     const V3 g{K.o.gravity_x, K.o.gravity_y, K.o.gravity_z};
-    for (int dof = lane; dof < K.ms.nv; dof += 32) {
+    for (int dof = lane; dof < K.ms.nv; dof += MJB_LW) {
       const int db = MI(dof_bodyid)[dof], dend = MI(body_subtreeend)[db];
       const S6 cd = ld6(DW(cdof) + 6 * dof);
       float q = 0.f;
@@ -745,7 +764,7 @@ __device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned 
   __syncwarp();
   for (int lv = 1; lv < K.ms.nlevel; lv++) {
     const int a1 = tree_adr[lv + 1];
-    for (int i = tree_adr[lv] + lane; i < a1; i += 32) {
+    for (int i = tree_adr[lv] + lane; i < a1; i += MJB_LW) {
       const int b = tree[i], pid = MI(body_parentid)[b];
       S6 v = ld6(cvel + 6 * pid);
       S6 acc = ld6(cacc + 6 * pid);
@@ -795,15 +814,15 @@ __device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned 
     __syncwarp();
   }
   // cfrc_int[b] = sum of the own forces over the subtree (smooth.py:1219-1240 without atomics)
-  for (int b = lane; b < nb; b += 32) {
+  for (int b = lane; b < nb; b += MJB_LW) {
     const int end = MI(body_subtreeend)[b];
     S6 acc = S6{{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
     for (int c = (b == 0 ? 1 : b); c < end; c++) axpy6(acc, 1.0f, ld6(DW(cfrc_ext) + 6 * c));
     st6(cfrc + 6 * b, acc);
   }
   __syncwarp();
-  for (int b = lane; b < nb; b += 32) st6(DW(cfrc_ext) + 6 * b, S6{{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}});
-  for (int i = lane; i < nv; i += 32) DW(qfrc_bias)[i] = dot6(ld6(cdof + 6 * i), ld6(cfrc + 6 * MI(dof_bodyid)[i]));
+  for (int b = lane; b < nb; b += MJB_LW) st6(DW(cfrc_ext) + 6 * b, S6{{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}});
+  for (int i = lane; i < nv; i += MJB_LW) DW(qfrc_bias)[i] = dot6(ld6(cdof + 6 * i), ld6(cfrc + 6 * MI(dof_bodyid)[i]));
   __syncwarp();
 }
 
@@ -811,12 +830,12 @@ __device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned 
 __device__ __forceinline__ void s_fwd_actuation(const KParams& K, const unsigned char* mb, int w, int lane) {
   const int nv = K.ms.nv, nu = K.ms.nu;
   if (!nu || (K.o.disableflags & DSBL_ACTUATION)) {
-    for (int i = lane; i < K.ms.na; i += 32) DW(act_dot)[i] = 0.f;
-    for (int i = lane; i < nv; i += 32) DW(qfrc_actuator)[i] = 0.f;
+    for (int i = lane; i < K.ms.na; i += MJB_LW) DW(act_dot)[i] = 0.f;
+    for (int i = lane; i < nv; i += MJB_LW) DW(qfrc_actuator)[i] = 0.f;
     __syncwarp();
     return;
   }
-  for (int u = lane; u < nu; u += 32) {
+  for (int u = lane; u < nu; u += MJB_LW) {
     float ctrl = DW(ctrl)[u];
     if (MI(actuator_ctrllimited)[u] && !(K.o.disableflags & DSBL_CLAMPCTRL))
       ctrl = clampf(ctrl, MR(actuator_ctrlrange)[2 * u], MR(actuator_ctrlrange)[2 * u + 1]);
@@ -852,10 +871,10 @@ __device__ __forceinline__ void s_fwd_actuation(const KParams& K, const unsigned
   // qfrc_actuator = moment^T force (forward.py:783), deterministic and without atomics: lane u holds the
   // k-th entry (column, moment * force) of actuator u's moment row; the entries are broadcast one by one
   // and the lane that owns the dof adds them up
-  for (int i = lane; i < ((nv + 31) & ~31); i += 32) {
+  for (int i = lane; i < ((nv + MJB_LW - 1) & ~(MJB_LW - 1)); i += MJB_LW) {
     float q = 0.f;
-    for (int u0 = 0; u0 < nu; u0 += 32) {
-      const int u = u0 + lane, cnt = min(32, nu - u0);
+    for (int u0 = 0; u0 < nu; u0 += MJB_LW) {
+      const int u = u0 + lane, cnt = min(MJB_LW, nu - u0);
       int adr = 0, nnz = 0;
       float force = 0.f;
       if (u < nu) {
@@ -865,13 +884,13 @@ __device__ __forceinline__ void s_fwd_actuation(const KParams& K, const unsigned
       }
       int maxnnz = nnz;
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) maxnnz = max(maxnnz, __shfl_xor_sync(FULL, maxnnz, o));
+      for (int o = MJB_LW / 2; o > 0; o >>= 1) maxnnz = max(maxnnz, __shfl_xor_sync(FULL, maxnnz, o));
       for (int k = 0; k < maxnnz; k++) {
         const int col = k < nnz ? DW(moment_colind)[adr + k] : -1;
         const float val = k < nnz ? DW(actuator_moment)[adr + k] * force : 0.f;
         for (int uu = 0; uu < cnt; uu++) {
-          const int c = __shfl_sync(FULL, col, uu);
-          const float v = __shfl_sync(FULL, val, uu);
+          const int c = __shfl_sync(FULL, col, uu, MJB_LW);
+          const float v = __shfl_sync(FULL, val, uu, MJB_LW);
           if (c == i) q += v;
         }
       }
@@ -891,7 +910,7 @@ __device__ __forceinline__ void s_fwd_acceleration(const KParams& K, const unsig
   const CholScr s = chol_scr(scr, nv, K.ms.nv_pad);
   float* x = s.x;
   const float* xfrc = DW(xfrc_applied);
-  for (int i = lane; i < nv; i += 32) {
+  for (int i = lane; i < nv; i += MJB_LW) {
     float q = DW(qfrc_passive)[i] - DW(qfrc_bias)[i] + DW(qfrc_actuator)[i] + DW(qfrc_applied)[i];
     const S6 cd = ld6(DW(cdof) + 6 * i);
     const int db = MI(dof_bodyid)[i], end = MI(body_subtreeend)[db];
@@ -915,7 +934,7 @@ __device__ __forceinline__ void s_fwd_acceleration(const KParams& K, const unsig
   }
   __syncwarp();
   warp_chol_solve<false>(s.L, s.ld, nv, s.rd, x, lane);
-  for (int i = lane; i < nv; i += 32) DW(qacc_smooth)[i] = x[i];
+  for (int i = lane; i < nv; i += MJB_LW) DW(qacc_smooth)[i] = x[i];
   __syncwarp();
 }
 
@@ -962,9 +981,9 @@ __device__ __forceinline__ void s_integrate(const KParams& K, const unsigned cha
     if (implicit && K.ms.nu > 0 && !(dsbl & DSBL_ACTUATION)) {
       for (int u = 0; u < K.ms.nu; u++) {  // rows are short (one entry for joint transmissions)
         const float vel = act_vel_deriv(K, mb, w, u);
-        if (vel == 0.f) continue;
+        if (MJB_LW == 32 && vel == 0.f) continue;  // world-dependent (ctrl): only a full-warp world may skip the __syncwarp below
         const int adr = DW(moment_rowadr)[u], nnz = DW(moment_rownnz)[u];
-        for (int idx = lane; idx < nnz * nnz; idx += 32) {
+        for (int idx = lane; idx < nnz * nnz; idx += MJB_LW) {
           const int a = idx / nnz, b = idx - a * nnz;
           s.L[DW(moment_colind)[adr + a] * s.ld + DW(moment_colind)[adr + b]] -= dt * DW(actuator_moment)[adr + a] * DW(actuator_moment)[adr + b] * vel;
         }
@@ -972,14 +991,14 @@ __device__ __forceinline__ void s_integrate(const KParams& K, const unsigned cha
       }
     }
     warp_cholesky<false>(s.L, s.ld, nv, s.rd, lane);
-    for (int i = lane; i < nv; i += 32) x[i] = DW(efc_Ma)[i];
+    for (int i = lane; i < nv; i += MJB_LW) x[i] = DW(efc_Ma)[i];
     __syncwarp();
     warp_chol_solve<false>(s.L, s.ld, nv, s.rd, x, lane);
   } else {
-    for (int i = lane; i < nv; i += 32) x[i] = DW(qacc)[i];
+    for (int i = lane; i < nv; i += MJB_LW) x[i] = DW(qacc)[i];
     __syncwarp();
   }
-  for (int u = lane; u < K.ms.nu; u += 32) {
+  for (int u = lane; u < K.ms.nu; u += MJB_LW) {
     const int a0 = MI(actuator_actadr)[u];
     if (a0 < 0) continue;
     for (int j = a0; j < a0 + MI(actuator_actnum)[u]; j++)
@@ -988,12 +1007,12 @@ __device__ __forceinline__ void s_integrate(const KParams& K, const unsigned cha
   }
   float* qvel = DW(qvel);
   float* qpos = DW(qpos);
-  for (int i = lane; i < nv; i += 32) {
+  for (int i = lane; i < nv; i += MJB_LW) {
     qvel[i] += x[i] * dt;
     DW(qacc_warmstart)[i] = DW(qacc)[i];
   }
   __syncwarp();
-  for (int j = lane; j < K.ms.njnt; j += 32) {  // forward.py:52-112
+  for (int j = lane; j < K.ms.njnt; j += MJB_LW) {  // forward.py:52-112
     const int qa = MI(jnt_qposadr)[j], da = MI(jnt_dofadr)[j], jt = MI(jnt_type)[j];
     if (jt == JNT_FREE) {
       qpos[qa] += dt * qvel[da];
@@ -1020,11 +1039,11 @@ static __device__ __noinline__ void s_energy_pos(const KParams& K, const unsigne
   float e = 0.f;
   if (!(K.o.disableflags & DSBL_GRAVITY)) {
     const V3 g{K.o.gravity_x, K.o.gravity_y, K.o.gravity_z};
-    for (int b = 1 + lane; b < K.ms.nbody; b += 32) e -= MR(body_mass)[b] * dot(g, ld3(DW(xipos) + 3 * b));
+    for (int b = 1 + lane; b < K.ms.nbody; b += MJB_LW) e -= MR(body_mass)[b] * dot(g, ld3(DW(xipos) + 3 * b));
   }
   if (!(K.o.disableflags & DSBL_SPRING)) {
     const float* qpos = DW(qpos);
-    for (int j = lane; j < K.ms.njnt; j += 32) {
+    for (int j = lane; j < K.ms.njnt; j += MJB_LW) {
       const float k = MR(jnt_stiffness)[j];
       if (k == 0.f) continue;
       const int qa = MI(jnt_qposadr)[j], t = MI(jnt_type)[j];
@@ -1045,7 +1064,7 @@ static __device__ __noinline__ void s_energy_pos(const KParams& K, const unsigne
       }
     }
   }
-  e = warp_sum(e);
+  e = lw_sum(e);
   if (lane == 0) { DW(energy)[0] = e; DW(energy)[1] = 0.f; }
 }
 
@@ -1054,12 +1073,12 @@ static __device__ __noinline__ void s_energy_vel(const KParams& K, int w, int la
   const int nv = K.ms.nv, np = K.ms.nv_pad;
   const float* qvel = DW(qvel);
   float e = 0.f;
-  for (int i = lane; i < nv; i += 32) {
+  for (int i = lane; i < nv; i += MJB_LW) {
     const float* row = DW(qM) + (size_t)i * np;
     float s = 0.f;
     for (int j = 0; j < nv; j++) s += row[j] * qvel[j];
     e += qvel[i] * s;
   }
-  e = warp_sum(e);
+  e = lw_sum(e);
   if (lane == 0) DW(energy)[1] = 0.5f * e;
 }

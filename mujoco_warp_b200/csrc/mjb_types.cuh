@@ -14,6 +14,11 @@
 
 #include "mjb_fields.h"
 
+// lanes per world of the smooth-dynamics stage groups (smooth_position, smooth_velocity, euler): see MJB_LW in mjb_smooth.cuh
+#ifndef MJB_SMOOTH_LW
+#define MJB_SMOOTH_LW 32
+#endif
+
 #define MJ_MINVAL 1e-15f
 #define MJ_MAXVAL 1e10f
 #define MJ_MINIMP 1e-4f
