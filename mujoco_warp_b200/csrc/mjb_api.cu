@@ -413,11 +413,22 @@ extern "C" int mjb_run_stages(const MjbModel* m, MjbData* d, const MjbOption* op
   if ((stages & MJB_STAGE_IMPLICIT) && (stages & MJB_STAGE_EULER)) return fail(-4, "euler and implicit stages are exclusive");
   KParams K;
   fill_params(K, m, d, opt, stages);
-  if ((stages & MJB_STAGE_COLLISION) && opt->run_collision_detection) {  // collision_driver.py:779
-    CUDA_OK(cudaMemsetAsync(d->d.nacon, 0, sizeof(int), stream));
-    CUDA_OK(cudaMemsetAsync(d->d.ncollision, 0, sizeof(int), stream));
+  // One small kernel clears the contact counters (collision_driver.py:779) and the world queues.  Deliberately not memset nodes:
+  // those run on a copy engine, where they queue behind the caller's host <-> device transfers and stall the step (measured).
+  {
+    const bool col = (stages & MJB_STAGE_COLLISION) && opt->run_collision_detection;
+    static const int memsets = getenv("MJB_CLEAR_MEMSET") ? atoi(getenv("MJB_CLEAR_MEMSET")) : 0;
+    if (memsets) {
+      if (col) {
+        CUDA_OK(cudaMemsetAsync(d->d.nacon, 0, sizeof(int), stream));
+        CUDA_OK(cudaMemsetAsync(d->d.ncollision, 0, sizeof(int), stream));
+      }
+      if (d->queue) CUDA_OK(cudaMemsetAsync(d->queue, 0, G_COUNT * sizeof(int), stream));
+    } else if (col || d->queue) {
+      const int rc = timed_launch(stream, [&] { mjb_util_clear(col ? d->d.nacon : nullptr, col ? d->d.ncollision : nullptr, d->queue, G_COUNT, stream); }, -1, false);
+      if (rc) return rc;
+    }
   }
-  if (d->queue) CUDA_OK(cudaMemsetAsync(d->queue, 0, G_COUNT * sizeof(int), stream));
   for (int g = 0; g < G_COUNT; g++) {
     const uint32_t gs = stages & group_mask(g);
     if (!gs) continue;

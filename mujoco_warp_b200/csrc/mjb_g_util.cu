@@ -85,3 +85,11 @@ void mjb_util_ctrl_noise(const KParams& K, int grid, const float* ctrl_center, i
                          cudaStream_t stream) {
   mjb_ctrl_noise_kernel<<<grid, 256, 0, stream>>>(K, ctrl_center, step, ctrlnoisestd, ctrlnoiserate);
 }
+
+__global__ void mjb_clear_kernel(int* a, int* b, int* q, int nq) {
+  const int t = threadIdx.x;
+  if (t == 0 && a) *a = 0;
+  if (t == 1 && b) *b = 0;
+  if (q && t < nq) q[t] = 0;
+}
+void mjb_util_clear(int* a, int* b, int* q, int nq, cudaStream_t stream) { mjb_clear_kernel<<<1, 32, 0, stream>>>(a, b, q, nq); }

@@ -18,3 +18,5 @@ cudaError_t mjb_util_solve_m_smem(size_t smem);
 void mjb_util_solve_m(const KParams& K, int grid, int threads, size_t smem, cudaStream_t stream);
 void mjb_util_mul_m(const KParams& K, int grid, cudaStream_t stream);
 void mjb_util_ctrl_noise(const KParams& K, int grid, const float* ctrl_center, int step, float ctrlnoisestd, float ctrlnoiserate, cudaStream_t stream);
+// zeroes *a, *b (either may be null) and q[0..nq) (q may be null): the per-call counters of mjb_run_stages
+void mjb_util_clear(int* a, int* b, int* q, int nq, cudaStream_t stream);

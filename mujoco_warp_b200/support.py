@@ -52,8 +52,11 @@ def _state_call(fn_name, m, d, state, sig, active):
   n = state_size(m, d, sig)
   if not (torch.is_tensor(state) and state.dtype == torch.float32 and state.dim() == 2 and state.stride(1) == 1):
     raise ValueError("state must be a float32 tensor of shape (nworld, >= state size) with contiguous rows")
-  if state.shape[0] != d.nworld or state.shape[1] < n or state.device != d.qpos.device:
-    raise ValueError(f"state must have shape ({d.nworld}, >= {n}) on {d.qpos.device}, got {tuple(state.shape)} on {state.device}")
+  # a pinned host tensor is device-accessible (mapped, unified addressing): the kernel then reads / writes host memory directly
+  # over PCIe, which saves the staging buffer and the DMA copy of an observation / action exchange with the host
+  on_device = state.device == d.qpos.device or (state.device.type == "cpu" and state.is_pinned())
+  if state.shape[0] != d.nworld or state.shape[1] < n or not on_device:
+    raise ValueError(f"state must have shape ({d.nworld}, >= {n}) on {d.qpos.device} (or in pinned host memory), got {tuple(state.shape)} on {state.device}")
   lib = _lib.load()
   _ensure_bound(m, d)
   keep = []

@@ -1,88 +1,81 @@
-"""Variants of the end-to-end loop (host ctrl -> H2D -> step -> D2H obs) timed against each other on one GPU."""
+"""Where the end-to-end loop of bench.py loses time against the device-resident replay: variants of the loop on one GPU.
+Finding (round 2): none of the transfer variants matters (a 0.69 MB upload is 30 us and overlaps); the 25 % "gap" of the round-1
+loop was its WORKLOAD -- it uploaded uncorrelated +-0.1 controls, which agitate the humanoids and cost solver iterations, while the
+device-resident loop applies the benchmark's small Ornstein-Uhlenbeck noise.  This probe still uploads the agitating controls, so
+every variant that uploads shows the slower step; bench.py now uploads frames of the OU process.
+  python tools/e2e_probe.py [nsteps]"""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
+import bench
 import mujoco_warp_b200 as mjw
-from tests import helpers as H
 
-nworld, Ke = 8192, 200
-mjm = mjw.load_mjcf(H.HUMANOID)
-m = mjw.put_model(mjm)
-hd = mjw.make_host_data(mjm); hd.qpos[:] = mjm.key_qpos[0]
-d = mjw.put_data(mjm, hd, nworld=nworld, nconmax=24, njmax=64, m=m)
-nu, nq, nv = m.nu, m.nq, m.nv
-stream = torch.cuda.Stream(); copy_stream = torch.cuda.Stream()
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 200
+w = bench.Workload("humanoid", 8192)
+m, d, stream = w.m, w.d, w.stream
+nu, nq, nv, nworld = m.nu, m.nq, m.nv, 8192
 with torch.cuda.stream(stream):
-  for i in range(30):
-    mjw.ctrl_noise(m, d, i); mjw.step(m, d)
-stream.synchronize()
-
-
-def run(depth, fused_graph):
-  NB = depth
-  h_ctrl = [torch.empty((nworld, nu), dtype=torch.float32).pin_memory().uniform_(-0.1, 0.1) for _ in range(NB)]
-  h_obs = [torch.empty((nworld, nq + nv), dtype=torch.float32).pin_memory() for _ in range(NB)]
-  d_stage = [torch.empty_like(d.ctrl) for _ in range(NB)]
-  d_obs = [torch.empty((nworld, nq + nv), dtype=torch.float32, device="cuda") for _ in range(NB)]
-  ev_ctrl = [torch.cuda.Event() for _ in range(NB)]; ev_step = [torch.cuda.Event() for _ in range(NB)]; ev_obs = [torch.cuda.Event() for _ in range(NB)]
+  w.run(10); w.capture(); w.run(250); stream.synchronize()
+  h_ctrl = [torch.empty((nworld, nu)).uniform_(-0.1, 0.1).pin_memory() for _ in range(2)]
+  h_obs = [torch.empty((nworld, nq + nv)).pin_memory() for _ in range(2)]
+  stage = [torch.empty_like(d.ctrl) for _ in range(2)]
+  d_obs = [torch.empty((nworld, nq + nv), device="cuda") for _ in range(2)]
+  sig = int(mjw.State.QPOS) | int(mjw.State.QVEL)
   graphs = []
-  with torch.cuda.stream(stream):
-    if fused_graph:
-      for b in range(NB):
-        g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g, stream=stream):
-          d.ctrl.copy_(d_stage[b]); mjw.step(m, d); d_obs[b][:, :nq].copy_(d.qpos); d_obs[b][:, nq:].copy_(d.qvel)
-        graphs.append(g)
-    else:
-      g = torch.cuda.CUDAGraph()
-      with torch.cuda.graph(g, stream=stream):
-        mjw.step(m, d)
-      graphs = [g] * NB
-  torch.cuda.synchronize()
+  for b in range(2):
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=stream):
+      mjw.set_state(m, d, stage[b], int(mjw.State.CTRL)); mjw.step(m, d); mjw.get_state(m, d, d_obs[b], sig)
+    graphs.append(g)
+  copy = torch.cuda.Stream()
+  evc = [torch.cuda.Event() for _ in range(2)]; evs = [torch.cuda.Event() for _ in range(2)]; evo = [torch.cuda.Event() for _ in range(2)]
 
-  def upload(k):
-    b = k % NB
-    with torch.cuda.stream(copy_stream):
-      d_stage[b].copy_(h_ctrl[b], non_blocking=True); ev_ctrl[b].record(copy_stream)
-
-  def step(k):
-    b = k % NB
-    upload(k + 1)
-    with torch.cuda.stream(stream):
-      stream.wait_event(ev_ctrl[b])
-      if fused_graph:
-        graphs[b].replay()
-      else:
-        d.ctrl.copy_(d_stage[b], non_blocking=True); graphs[b].replay()
-        d_obs[b][:, :nq].copy_(d.qpos, non_blocking=True); d_obs[b][:, nq:].copy_(d.qvel, non_blocking=True)
-      ev_step[b].record(stream)
-    with torch.cuda.stream(copy_stream):
-      copy_stream.wait_event(ev_step[b]); h_obs[b].copy_(d_obs[b], non_blocking=True); ev_obs[b].record(copy_stream)
-    lag = depth - 1
-    if k >= lag:
-      ev_obs[(k - lag) % NB].synchronize()
-
-  def loop(n):
-    upload(0)
+  def loop(h2d, d2h, hostsync, same_stream=False):
+    torch.cuda.synchronize(); t0 = time.perf_counter()
     for k in range(n):
-      step(k)
+      b = k & 1
+      if h2d:
+        if same_stream:
+          stage[b].copy_(h_ctrl[b], non_blocking=True)
+        else:
+          with torch.cuda.stream(copy):
+            stage[b].copy_(h_ctrl[b], non_blocking=True); evc[b].record(copy)
+          stream.wait_event(evc[b])
+      graphs[b].replay()
+      if d2h:
+        if same_stream:
+          h_obs[b].copy_(d_obs[b], non_blocking=True); evo[b].record(stream)
+        else:
+          evs[b].record(stream)
+          with torch.cuda.stream(copy):
+            copy.wait_event(evs[b]); h_obs[b].copy_(d_obs[b], non_blocking=True); evo[b].record(copy)
+        if hostsync and k > 0:
+          evo[(k - 1) & 1].synchronize()
     torch.cuda.synchronize()
+    return nworld * n / (time.perf_counter() - t0) / 1e6
 
-  loop(6)
-  torch.cuda.synchronize(); t0 = time.perf_counter(); loop(Ke); dt = time.perf_counter() - t0
-  return nworld * Ke / dt / 1e6, dt / Ke * 1e3
+  # zero-copy: the graph's set_state / get_state kernels address the pinned host buffers directly
+  zg = []
+  for b in range(2):
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=stream):
+      mjw.set_state(m, d, h_ctrl[b], int(mjw.State.CTRL)); mjw.step(m, d); mjw.get_state(m, d, h_obs[b], sig)
+    zg.append(g)
 
+  def zloop(hostsync):
+    torch.cuda.synchronize(); t0 = time.perf_counter()
+    for k in range(n):
+      b = k & 1
+      zg[b].replay(); evo[b].record(stream)
+      if hostsync and k > 0:
+        evo[(k - 1) & 1].synchronize()
+    torch.cuda.synchronize()
+    return nworld * n / (time.perf_counter() - t0) / 1e6
 
-for depth in (2, 3):
-  for fused in (False, True):
-    v, ms = run(depth, fused)
-    print(f"depth {depth} fused_graph {fused}: {v:.2f} M env-steps/s  {ms:.3f} ms/step", flush=True)
-# device-only reference
-g = torch.cuda.CUDAGraph()
-with torch.cuda.stream(stream):
-  with torch.cuda.graph(g, stream=stream):
-    mjw.step(m, d)
-  torch.cuda.synchronize(); t0 = time.perf_counter()
-  for _ in range(Ke): g.replay()
-  torch.cuda.synchronize(); dt = time.perf_counter() - t0
-print(f"device-only graph replay: {nworld * Ke / dt / 1e6:.2f} M  {dt / Ke * 1e3:.3f} ms/step")
+  for hs in (0, 1):
+    zloop(hs); print("zero-copy hostsync=%d   %.2f M env-steps/s" % (hs, zloop(hs)))
+  h_obs[0].zero_(); zg[0].replay(); torch.cuda.synchronize()
+  print("obs check", float((h_obs[0][:, :nq] - d.qpos.cpu()).abs().max()), float(h_obs[0].abs().max()))
+  for name, args in [("graph only", (0, 0, 0)), ("h2d", (1, 0, 0)), ("d2h nosync", (0, 1, 0)), ("h2d+d2h nosync", (1, 1, 0)), ("full (bench)", (1, 1, 1)),
+                     ("full same-stream", (1, 1, 1, True))]:
+    loop(*args); print("%-20s %.2f M env-steps/s" % (name, loop(*args)))
