@@ -163,6 +163,7 @@ extern "C" int mjb_model_create(const int* sizes, int nsizes, const void* blob, 
       if (t1 == GEOM_ELLIPSOID || t1 == GEOM_CYLINDER || t1 == GEOM_MESH || t2 == GEOM_ELLIPSOID || t2 == GEOM_CYLINDER || t2 == GEOM_MESH) m->col_feat |= COLF_CONVEX;
     }
   }
+  if (m->ms.ngrouppair > 0) m->col_feat |= COLF_SAP;  // the two-level broadphase lives in the variants that carry the sweep-and-prune workspace
   *out = m;
   return 0;
 }
@@ -353,7 +354,7 @@ static int resolve_cfg(int g, int variant, const MjbModel* m, MjbData* d) {
   const int wpw = 32 / group_lw(g);  // worlds per warp
   int wpb = warps_per_block(g == G_SOL ? group_threads(G_SOL) / 32 : wpw > 1 ? 4 : 8);
   if (32 * wpb > group_threads(g)) wpb = group_threads(g) / 32;
-  c.scratch_floats = group_scratch_floats(g, m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad, m->ms.ngeom, m->ms.nxn, variant);
+  c.scratch_floats = group_scratch_floats(g, m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad, m->ms.ngeom, m->ms.nxn, variant, m->ms.ngroup);
   const size_t scr_bytes = (size_t)wpb * wpw * c.scratch_floats * sizeof(float);
   const bool in_smem =
       group_uses_blob(g) && (size_t)m->blob_hot + 16 + scr_bytes <= (size_t)d->smem_optin && m->blob_hot <= 96 * 1024;

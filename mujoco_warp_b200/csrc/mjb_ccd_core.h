@@ -48,6 +48,7 @@ typedef struct {
   const CCD_VERT_REAL* vert; /* mesh: hull vertices in the geom frame (the model's mesh_vert + 3 * mesh_vertadr), nvert of them */
   int nvert;
   const int* graph; /* mesh: MuJoCo-layout convex graph of the hull (mesh_graph + mesh_graphadr), or NULL: exhaustive support search */
+  int coop;         /* device build only: 1 = every lane of the warp runs THIS pair, mesh support = lane-parallel search (CCD_COOP_MESH_SUPPORT) */
 } CcdGeom;
 
 typedef struct {
@@ -122,6 +123,13 @@ CCD_FN_NOINLINE int ccd_support(const CcdGeom* g, const creal* dir, creal* point
       res[0] = ld[0] * scl; res[1] = ld[1] * scl;
     }
     res[2] = ccd_sign(ld[2]) * g->size[1];
+#ifdef CCD_COOP_MESH_SUPPORT
+  } else if (g->type == CCD_GEOM_MESH && g->coop) { /* the hull vertex of largest projection, searched by all lanes together */
+    const int best = CCD_COOP_MESH_SUPPORT(g->vert, g->nvert, ld);
+    res[0] = (creal)g->vert[3 * best]; res[1] = (creal)g->vert[3 * best + 1]; res[2] = (creal)g->vert[3 * best + 2];
+    *cached = best;
+    vertex_index = best;
+#endif
   } else if (g->type == CCD_GEOM_MESH && g->graph && g->nvert >= 10) { /* :153-176 hill climbing over the hull's edge graph */
     const int* graph = g->graph;
     const int numvert = graph[0];

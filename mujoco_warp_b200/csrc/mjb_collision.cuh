@@ -29,7 +29,31 @@ enum CollisionFeature {
 #define CCD_FN_NOINLINE static __device__ __noinline__
 #define CCD_SQRT sqrtf
 #define CCD_FABS fabsf
+// Warp-cooperative mesh support (product path only; the oracle keeps the reference's hill climbing, collision_gjk.py:153-176):
+// when all 32 lanes run GJK / EPA on the SAME pair, the support vertex of a hull is the arg max of <vertex, dir> over ALL its
+// vertices, lanes striding over the (coalesced) vertex table, instead of a serial walk over the hull's edge graph whose every
+// step is a dependent global-memory round trip.  Same vertex as the hill climb on a convex hull (ties: lowest index).
+__device__ __forceinline__ int ccd_coop_mesh_support(const float* vert, int nvert, const float* ld) {
+  const int lane = threadIdx.x & 31;
+  float best = -3.0e38f;
+  int ibest = 0x7fffffff;
+#pragma unroll 4
+  for (int i = lane; i < nvert; i += 32) {
+    const float d = vert[3 * i] * ld[0] + vert[3 * i + 1] * ld[1] + vert[3 * i + 2] * ld[2];
+    if (d > best) { best = d; ibest = i; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, ibest, o);
+    if (ob > best || (ob == best && oi < ibest)) { best = ob; ibest = oi; }
+  }
+  return ibest;
+}
+#define CCD_COOP_MESH_SUPPORT ccd_coop_mesh_support
 #include "mjb_ccd_core.h"
+// words of one EPA polytope, padded to 16 bytes (the warp-cooperative mesh pairs keep theirs in shared memory)
+#define CCD_POLY_WORDS ((int)((sizeof(CcdPolytope) + 15) / 16 * 4))
 
 // collision_driver.py:43 MJ_COLLISION_TABLE: pair types of CollisionType.CONVEX among the implemented geom types
 // (box-box stays on the primitive, the reference's NATIVECCD-disabled route, :736)
@@ -45,9 +69,14 @@ __device__ __forceinline__ bool is_ccd_pair(int t1, int t2) { return (t2 == GEOM
 // contacts (0 / 1); dist is the surface distance, pos the midpoint of the witness points, nrm = x1 - x2 (unnormalised).
 static __device__ __noinline__ int c_ccd_pair(const float* p1, const float* r1, const float* s1, int t1, const float* v1, int nv1, const int* gr1,
                                        const float* p2, const float* r2, const float* s2, int t2, const float* v2, int nv2, const int* gr2,
-                                       float margin, float tolerance, int iterations, float* dist, float* pos, float* nrm) {
+                                       float margin, float tolerance, int iterations, float* dist, float* pos, float* nrm, int coop,
+                                       CcdPolytope* shared_pt) {
   CcdGeom g1, g2;
-  CcdPolytope pt;  // ~5 kB of local memory per thread
+  g1.coop = g2.coop = coop;
+  // ~5 kB of local memory per thread; the warp-cooperative path passes ONE polytope in shared memory instead (every lane computes
+  // and stores the same values), which takes the EPA's face / vertex tables off the local-memory path
+  CcdPolytope pt_local;
+  CcdPolytope& pt = shared_pt ? *shared_pt : pt_local;
   CcdGjk res;
 #pragma unroll
   for (int i = 0; i < 3; i++) { g1.pos[i] = p1[i]; g2.pos[i] = p2[i]; g1.size[i] = s1[i]; g2.size[i] = s2[i]; }
@@ -869,7 +898,7 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
   const float* r2 = nullptr;
   float bdist[(FEAT & COLF_BOX) ? 8 : 1], bpos[(FEAT & COLF_BOX) ? 24 : 3], bnrm[3] = {1.f, 0.f, 0.f};  // box-box results
   int nbb = 0;
-  bool boxbox = false;
+  bool boxbox = false, mesh_ccd = false;
   if (has) {
     const int p = queue[lane];
     const int ga = MIC(nxn_pair)[2 * p], gb = MIC(nxn_pair)[2 * p + 1];
@@ -896,7 +925,9 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
       nbb = c_box_box(pa, DW(geom_xmat) + 9 * g1, sa, pb, r2, sb, cp.margin, bdist, bpos, bnrm);
       boxbox = true;
     }
-    if ((FEAT & COLF_CONVEX) && is_ccd_pair(g.t1, g.t2)) {  // GJK / EPA once per pair; the two passes below read the result
+    if ((FEAT & COLF_CONVEX) && g.t2 == GEOM_MESH && is_ccd_pair(g.t1, g.t2)) {
+      mesh_ccd = true;  // evaluated below by the whole warp, one pair at a time
+    } else if ((FEAT & COLF_CONVEX) && is_ccd_pair(g.t1, g.t2)) {  // GJK / EPA once per pair; the two passes below read the result
       const float pa[3] = {g.p1.x, g.p1.y, g.p1.z}, pb[3] = {g.p2.x, g.p2.y, g.p2.z};
       const float sa[3] = {g.s1.x, g.s1.y, g.s1.z}, sb[3] = {g.s2.x, g.s2.y, g.s2.z};
       const float *v1 = nullptr, *v2 = nullptr;
@@ -915,7 +946,7 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
         if (MI(mesh_graphadr)[id] >= 0) gr2 = MIC(mesh_graph) + MI(mesh_graphadr)[id];
       }
       nbb = c_ccd_pair(pa, DW(geom_xmat) + 9 * g1, sa, g.t1, v1, nv1, gr1, pb, r2, sb, g.t2, v2, nv2, gr2, cp.margin, K.o.ccd_tolerance,
-                       K.o.ccd_iterations, bdist, bpos, bnrm);
+                       K.o.ccd_iterations, bdist, bpos, bnrm, 0, nullptr);
       boxbox = true;
     }
     if ((FEAT & COLF_CONVEX) && g.t1 == GEOM_PLANE && g.t2 == GEOM_MESH) {
@@ -926,6 +957,51 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
                          MI(mesh_graphadr)[id] >= 0 ? MIC(mesh_graph) + MI(mesh_graphadr)[id] : nullptr, bdist, bpos);
       boxbox = true;
     }
+  }
+  if (FEAT & COLF_CONVEX) {
+    // Pairs with a mesh: GJK / EPA by the WHOLE warp, one pair at a time.  Every lane runs the same (warp-uniform) iteration on the
+    // same pair and the hull support function searches all vertices with the lanes in parallel (ccd_coop_mesh_support): a mesh
+    // pair costs ~50 support calls on hulls of up to ~1200 vertices, and one lane walking the hull's edge graph through global
+    // memory for each of them is what made this stage 80 % of the aloha_pot step.
+    unsigned todo = __ballot_sync(FULL, has && mesh_ccd);
+    while (todo) {  // warp-uniform
+      const int src = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const int p = queue[src];
+      const int ga = MIC(nxn_pair)[2 * p], gb = MIC(nxn_pair)[2 * p + 1];
+      const bool swap = MI(geom_type)[ga] > MI(geom_type)[gb];
+      const int u1 = swap ? gb : ga, u2 = swap ? ga : gb;
+      const int ut1 = MI(geom_type)[u1];
+      const float* v1 = nullptr;
+      const int* gr1 = nullptr;
+      int nv1 = 0;
+      if (ut1 == GEOM_MESH) {
+        const int id = MI(geom_dataid)[u1];
+        v1 = MRC(mesh_vert) + 3 * MI(mesh_vertadr)[id];
+        nv1 = MI(mesh_vertnum)[id];
+        if (MI(mesh_graphadr)[id] >= 0) gr1 = MIC(mesh_graph) + MI(mesh_graphadr)[id];
+      }
+      const int id2 = MI(geom_dataid)[u2];
+      const float* v2 = MRC(mesh_vert) + 3 * MI(mesh_vertadr)[id2];
+      const int* gr2 = MI(mesh_graphadr)[id2] >= 0 ? MIC(mesh_graph) + MI(mesh_graphadr)[id2] : nullptr;
+      ContactParams ucp;
+      contact_params(K, mb, u1, u2, MIC(nxn_pairid)[2 * p], ucp);
+      float tdist = 0.f, tpos[3] = {0.f, 0.f, 0.f}, tnrm[3] = {1.f, 0.f, 0.f};
+      const int n = c_ccd_pair(DW(geom_xpos) + 3 * u1, DW(geom_xmat) + 9 * u1, MR(geom_size) + 3 * u1, ut1, v1, nv1, gr1, DW(geom_xpos) + 3 * u2,
+                               DW(geom_xmat) + 9 * u2, MR(geom_size) + 3 * u2, GEOM_MESH, v2, MI(mesh_vertnum)[id2], gr2, ucp.margin,
+                               K.o.ccd_tolerance, K.o.ccd_iterations, &tdist, tpos, tnrm, 1,
+                               reinterpret_cast<CcdPolytope*>(const_cast<int*>(queue) + K.scratch_floats - 64 - CCD_POLY_WORDS));
+      if (lane == src) {
+        nbb = n;
+        boxbox = true;
+        bdist[0] = tdist;
+#pragma unroll
+        for (int i = 0; i < 3; i++) { bpos[i] = tpos[i]; bnrm[i] = tnrm[i]; }
+      }
+      __syncwarp();
+    }
+  }
+  if (has) {
     for (int k = 0; k < ncand; k++) {  // pass 1: count (write_contact filter, collision_core.py:199-203)
       float dist;
       V3 pos;
@@ -995,7 +1071,12 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
 
 // Per-warp shared scratch of the collision stage, in 32-bit words: the pair queue (64 + 8), then the
 // sweep-and-prune workspace (lower, upper, order, range prefix: 4 ngeom words; candidate bit set).
-__host__ __device__ inline int collision_scratch_words(int ngeom, int nxn) { return 72 + 4 * ngeom + (nxn + 31) / 32 + 1; }
+// The two-level broadphase (ngroup > 0) uses the sweep-and-prune workspace for the geoms' world spheres and 4 ngroup more words for
+// the groups' (the candidate bit set, unused on that path, follows and is simply large enough).
+__host__ __device__ inline int collision_scratch_words(int ngeom, int nxn, int ngroup = 0, bool convex = false) {
+  // ... + alignment + [the polytope of the warp-cooperative convex pairs] + the 64-entry candidate queue at the very end
+  return ((72 + 4 * ngeom + 4 * ngroup + (nxn + 31) / 32 + 1 + 3) & ~3) + (convex ? CCD_POLY_WORDS : 0) + 64;
+}
 
 // Sweep-and-prune candidate set (collision_driver.py:554 sap_broadphase).  The reference projects the bounding
 // spheres on a fixed direction (:573), sorts per world by the lower end (tile sort or segmented sort, :458/:617),
@@ -1073,10 +1154,10 @@ __device__ __forceinline__ void s_collision(const KParams& K, const unsigned cha
     const bool sap = (FEAT & COLF_SAP) != 0 && nxn > 0 && K.o.broadphase != 0;
     unsigned* bits = reinterpret_cast<unsigned*>(queue + 72 + 4 * K.ms.ngeom);
     if (sap) sap_candidates(K, mb, w, lane, queue + 72, bits);
-    for (int p0 = 0; p0 < nxn; p0 += 32) {
-      const int p = p0 + lane;
+    // one chunk of up to 32 pairs: lane = pair, broadphase filter, ballot-compacted append to the queue, narrowphase when 32 wait
+    auto chunk = [&](int p, bool valid) {
       bool pass = false;
-      if (p < nxn && (!sap || (bits[p >> 5] >> (p & 31) & 1u))) pass = bp_filter(K, mb, w, MIC(nxn_pair)[2 * p], MIC(nxn_pair)[2 * p + 1]) || MIC(nxn_pairid)[2 * p + 1] >= 0;
+      if (valid && (!sap || (bits[p >> 5] >> (p & 31) & 1u))) pass = bp_filter(K, mb, w, MIC(nxn_pair)[2 * p], MIC(nxn_pair)[2 * p + 1]) || MIC(nxn_pairid)[2 * p + 1] >= 0;
       const unsigned mask = __ballot_sync(FULL, pass);
       if (pass) queue[qn + __popc(mask & ((1u << lane) - 1u))] = p;
       qn += __popc(mask);
@@ -1093,6 +1174,87 @@ __device__ __forceinline__ void s_collision(const KParams& K, const unsigned cha
         qn = rem;
         __syncwarp();
       }
+    };
+    const int ngp = K.ms.ngrouppair;
+    if ((FEAT & COLF_SAP) != 0 && ngp > 0 && !sap) {
+      // Two-level broadphase (large pair lists, io.py host_model): bounding spheres of the geom groups in the world frame, lanes
+      // over group pairs, then the geom pairs of the surviving group pairs only.  Conservative w.r.t. the per-pair sphere filter.
+      float4* gg = reinterpret_cast<float4*>(queue + 72);  // the sweep-and-prune workspace is free on this path
+      float4* gs = gg + K.ms.ngeom;
+      int* cand = queue + K.scratch_floats - 64;  // pairs that passed the cheap sphere test, waiting for the full filter
+      int cn = 0;
+      const bool sphere = (K.o.broadphase_filter & BF_SPHERE) != 0;
+      // world bounding spheres of the geoms: the quantities of bp_filter's sphere test, |p1 - p2| <= rbound1 + rbound2 + margins
+      for (int g = lane; g < K.ms.ngeom; g += 32) {
+        const V3 pw = ld3(DW(geom_xpos) + 3 * g);
+        const float rb = MR(geom_rbound)[g];
+        gg[g] = make_float4(pw.x, pw.y, pw.z, (rb == 0.f || !sphere) ? -1.f : rb + MR(geom_margin)[g]);  // < 0: no sphere test
+      }
+      for (int g = lane; g < K.ms.ngroup; g += 32) {
+        const int b = MI(group_bodyid)[g];
+        const float* c = MR(group_sphere) + 4 * g;
+        const V3 pw = ld3(DW(xpos) + 3 * b) + mat_vec(ldm3(DW(xmat) + 9 * b), ld3(c));
+        gs[g] = make_float4(pw.x, pw.y, pw.z, c[3]);
+      }
+      __syncwarp();
+      // stage 1 (cheap, shared memory only): sphere test per pair; survivors are compacted and go to `chunk` 32 at a time
+      auto feed = [&](int p, bool valid) {
+        bool near = false;
+        if (valid) {
+          const float4 a = gg[MIC(nxn_pair)[2 * p]], b = gg[MIC(nxn_pair)[2 * p + 1]];
+          const float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z, bound = a.w + b.w;
+          near = a.w < 0.f || b.w < 0.f || dx * dx + dy * dy + dz * dz <= bound * bound || MIC(nxn_pairid)[2 * p + 1] >= 0;
+        }
+        const unsigned mask = __ballot_sync(FULL, near);
+        if (near) cand[cn + __popc(mask & ((1u << lane) - 1u))] = p;
+        cn += __popc(mask);
+        __syncwarp();
+        if (cn >= 32) {
+          chunk(cand[lane], true);
+          const int rem = cn - 32;
+          int v = 0;
+          if (lane < rem) v = cand[32 + lane];
+          __syncwarp();
+          if (lane < rem) cand[lane] = v;
+          cn = rem;
+          __syncwarp();
+        }
+      };
+      for (int gp0 = 0; gp0 < ngp; gp0 += 32) {
+        const int gp = gp0 + lane;
+        bool live = false;
+        int adr = 0, len = 0;
+        if (gp < ngp) {
+          live = !sphere || MI(grouppair_always)[gp] != 0;
+          if (!live) {
+            const float4 a = gs[MI(grouppair)[2 * gp]], b = gs[MI(grouppair)[2 * gp + 1]];
+            const float dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z, bound = a.w + b.w;
+            live = dx * dx + dy * dy + dz * dz <= bound * bound;
+          }
+          if (live) {
+            adr = MI(grouppair_adr)[gp];
+            len = MI(grouppair_adr)[gp + 1] - adr;
+          }
+        }
+        // the geom pairs of this batch's live group pairs, flattened: lane k takes the k-th pair of the concatenated ranges
+        const int excl = warp_excl_scan(len, lane);
+        const int total = __shfl_sync(FULL, excl + len, 31);
+        for (int k0 = 0; k0 < total; k0 += 32) {
+          const int k = k0 + lane;
+          int owner = 0;  // the last lane whose range starts at or before k (ranges are contiguous in k, empty ones share a start)
+#pragma unroll
+          for (int step = 16; step > 0; step >>= 1) {
+            const int probe = owner + step;
+            const int start = __shfl_sync(FULL, excl, probe & 31);
+            if (probe < 32 && start <= k) owner = probe;
+          }
+          const int oadr = __shfl_sync(FULL, adr, owner), oexcl = __shfl_sync(FULL, excl, owner);
+          feed(oadr + k - oexcl, k < total);
+        }
+      }
+      if (cn > 0) chunk(lane < cn ? cand[lane] : 0, lane < cn);
+    } else {
+      for (int p0 = 0; p0 < nxn; p0 += 32) chunk(p0 + lane, p0 + lane < nxn);
     }
     if (qn > 0) narrowphase_flush<FEAT>(K, mb, w, lane, queue, qn, nw);
   }

@@ -60,13 +60,13 @@ __host__ __device__ inline uint32_t group_mask(int g) {
 
 #ifndef MJB_UNIT_GROUP
 // per-warp shared-memory scratch (floats) of a group
-__host__ __device__ inline int group_scratch_floats(int g, int nv, int nv_pad, int njmax_pad, int ngeom, int nxn, int variant = 0) {
+__host__ __device__ inline int group_scratch_floats(int g, int nv, int nv_pad, int njmax_pad, int ngeom, int nxn, int variant = 0, int ngroup = 0) {
   int n = 0;
   switch (g) {
     case G_POS:
     case G_VEL:
     case G_EUL: n = chol_scratch_floats(nv, nv_pad); break;
-    case G_COL: n = (variant & COLF_SAP) ? collision_scratch_words(ngeom, nxn) : 72; break;
+    case G_COL: n = (variant & COLF_SAP) ? collision_scratch_words(ngeom, nxn, ngroup, (variant & COLF_CONVEX) != 0) : 72; break;
     case G_CON: n = 0; break;
     case G_SOL: n = solver_scratch_floats(nv, nv_pad, njmax_pad); break;
   }

@@ -62,6 +62,7 @@ def _default_njmax(mjm, mjd=None) -> int:
   return int(valid_sizes[np.searchsorted(valid_sizes, njmax)])
 
 
+_GROUP_BROADPHASE_MIN_PAIRS = 1024  # filtered geom pairs from which the two-level (group sphere, then geom pair) broadphase is used
 _BLOB_SMEM_LIMIT = 96 * 1024  # bytes of model tables the stage-group kernels keep in shared memory (mjb_api.cu)
 
 
@@ -146,6 +147,8 @@ def host_model(mjm) -> SimpleNamespace:
       reals[name] = A(name, f64).reshape(-1, 3) if nmesh else np.zeros((0, 3))
     elif name == "actuator_gear":
       reals[name] = A(name, f64).reshape(nu, 6)
+    elif name == "group_sphere":
+      continue  # derived below (two-level broadphase)
     else:
       reals[name] = A(name, f64)
 
@@ -228,6 +231,61 @@ def host_model(mjm) -> SimpleNamespace:
   lookup[include] = np.arange(nxn, dtype=i32)
   ints["nxn_lookup"] = lookup
 
+  # Two-level broadphase for large pair lists (aloha_pot: 9154 filtered pairs, of which a handful are ever close): geoms are grouped
+  # (all geoms of a moving body; every world geom alone), each group gets a bounding sphere in its body's frame that contains the
+  # members' bounding spheres with their margins, and the pair list is sorted by group pair.  The collision kernel tests the
+  # group spheres first and walks the geom pairs of the surviving group pairs only.  The test is conservative with respect to
+  # the reference's per-pair sphere filter (collision_driver.py:91-111), so the set of pairs that pass -- and ncollision -- is
+  # unchanged; only the order of the pair list (hence of a world's contacts, arbitrary in the reference) differs.
+  ngroup = ngrouppair = 0
+  grp_body, grp_sphere = np.zeros(0, dtype=i32), np.zeros((0, 4))
+  grp_pair, grp_adr, grp_always = np.zeros((0, 2), dtype=i32), np.zeros(1, dtype=i32), np.zeros(0, dtype=i32)
+  if nxn >= _GROUP_BROADPHASE_MIN_PAIRS:
+    geom_group = np.zeros(ngeom, dtype=np.int64)
+    members = []
+    by_body = {}
+    for g in range(ngeom):
+      b = int(bodyid[g])
+      if b == 0:
+        geom_group[g] = len(members)
+        members.append([g])
+      else:
+        if b not in by_body:
+          by_body[b] = len(members)
+          members.append([])
+        geom_group[g] = by_body[b]
+        members[by_body[b]].append(g)
+    ngroup = len(members)
+    grp_body = np.array([int(bodyid[mm[0]]) for mm in members], dtype=i32)
+    grp_sphere = np.zeros((ngroup, 4))
+    has_plane = np.zeros(ngroup, dtype=bool)
+    gpos, grb, gmargin = reals["geom_pos"], reals["geom_rbound"], reals["geom_margin"]
+    for k, mm in enumerate(members):
+      c = gpos[mm].mean(axis=0)
+      r = max(float(np.linalg.norm(gpos[g] - c)) + float(grb[g]) + float(gmargin[g]) for g in mm)
+      grp_sphere[k] = [c[0], c[1], c[2], r * (1.0 + 1e-4) + 1e-6]  # slack: the device evaluates both tests in float32
+      has_plane[k] = any(float(grb[g]) == 0.0 for g in mm)
+    pr = ints["nxn_pair"]
+    ga, gb = geom_group[pr[:, 0]], geom_group[pr[:, 1]]
+    lo, hi = np.minimum(ga, gb), np.maximum(ga, gb)
+    order = np.lexsort((np.arange(nxn), hi, lo))
+    ints["nxn_pair"] = np.ascontiguousarray(pr[order])
+    ints["nxn_pairid"] = np.ascontiguousarray(ints["nxn_pairid"][order])
+    inv = np.empty(nxn, dtype=i32)
+    inv[order] = np.arange(nxn, dtype=i32)
+    lookup[include] = inv
+    ints["nxn_lookup"] = lookup
+    key = (lo[order] * ngroup + hi[order]).astype(np.int64)
+    starts = np.concatenate(([0], np.nonzero(np.diff(key))[0] + 1)).astype(i32)
+    ngrouppair = int(starts.size)
+    grp_adr = np.concatenate((starts, [nxn])).astype(i32)
+    grp_pair = np.stack((lo[order][starts], hi[order][starts]), axis=1).astype(i32)
+    sensor = ints["nxn_pairid"][:, 1] >= 0
+    grp_always = np.array(
+      [int(has_plane[a] or has_plane[b] or sensor[grp_adr[k] : grp_adr[k + 1]].any()) for k, (a, b) in enumerate(grp_pair)], dtype=i32)
+  ints["group_bodyid"], ints["grouppair"], ints["grouppair_adr"], ints["grouppair_always"] = grp_body, grp_pair, grp_adr, grp_always
+  reals["group_sphere"] = grp_sphere
+
   # supported narrowphase pair types: analytic primitives + GJK / EPA for ellipsoid / cylinder / mesh pairs (no hfields yet)
   supported = {
     (C.GeomType.PLANE, C.GeomType.SPHERE),
@@ -285,6 +343,7 @@ def host_model(mjm) -> SimpleNamespace:
     nmaxcondim=nmaxcondim, nmaxpyramid=int(max(1, 2 * (nmaxcondim - 1))),
     ngravcomp=int((reals["body_gravcomp"] != 0).sum()), is_sparse=int(sparse), nM=int(getattr(mjm, "nM", 0)),
     ntree=int(getattr(mjm, "ntree", 0)), ngeompair=int(len(geom1)), nmesh=nmesh, nmeshvert=int(reals["mesh_vert"].shape[0]), nmeshgraph=int(ints["mesh_graph"].size), blob_hot_bytes=0,
+    ngroup=ngroup, ngrouppair=ngrouppair,
   )  # fmt: skip
   extra = dict(
     nsensordata=int(getattr(mjm, "nsensordata", 0)), ncam=int(getattr(mjm, "ncam", 0)), nlight=int(getattr(mjm, "nlight", 0)),
