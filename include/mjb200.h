@@ -116,6 +116,14 @@ int mjb_transmission(const MjbModel* m, MjbData* d, const MjbOption* opt, void* 
 int mjb_fwd_position(const MjbModel* m, MjbData* d, const MjbOption* opt, int factorize, void* cuda_stream);
 int mjb_fwd_velocity(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
 int mjb_fwd_actuation(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+/* sub-functions of fwd_velocity / forward that the reference exports on their own: smooth.py:2015 com_vel (cvel, cdof_dot),
+ * passive.py:729 passive (qfrc_spring / damper / gravcomp / passive), smooth.py:1259 rne (cacc, cfrc_int, qfrc_bias),
+ * sensor.py:2854 energy_pos / :2922 energy_vel (d.energy[:, 0] / [:, 1]) */
+int mjb_com_vel(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_passive(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_rne(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_energy_pos(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
+int mjb_energy_vel(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
 int mjb_fwd_acceleration(const MjbModel* m, MjbData* d, const MjbOption* opt, int factorize, void* cuda_stream);
 int mjb_solve(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);
 int mjb_euler(const MjbModel* m, MjbData* d, const MjbOption* opt, void* cuda_stream);

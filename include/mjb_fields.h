@@ -137,6 +137,12 @@
 #define MJB_STAGE_EULER            (1u << 12) /* forward.euler       forward.py:327 */
 #define MJB_STAGE_IMPLICIT         (1u << 13) /* forward.implicit    forward.py:495 */
 #define MJB_STAGE_ZERO_SENSOR      (1u << 14) /* d.sensordata.zero_(), d.energy.zero_() :978,:984 */
+/* sub-functions of fwd_velocity / forward that the reference also exports on their own (mujoco_warp/__init__.py:25-112) */
+#define MJB_STAGE_COM_VEL          (1u << 15) /* smooth.com_vel      smooth.py:2015 */
+#define MJB_STAGE_PASSIVE          (1u << 16) /* passive.passive     passive.py:729 */
+#define MJB_STAGE_RNE              (1u << 17) /* smooth.rne          smooth.py:1259 */
+#define MJB_STAGE_ENERGY_POS       (1u << 18) /* sensor.energy_pos   sensor.py:2854 */
+#define MJB_STAGE_ENERGY_VEL       (1u << 19) /* sensor.energy_vel   sensor.py:2922 */
 
 #define MJB_STAGES_FWD_POSITION (MJB_STAGE_KINEMATICS | MJB_STAGE_COM_POS | MJB_STAGE_CRB | \
   MJB_STAGE_COLLISION | MJB_STAGE_MAKE_CONSTRAINT | MJB_STAGE_TRANSMISSION)

@@ -192,7 +192,7 @@ def check(lib, rc: int):
 
 _OPT_TENSORS = ("timestep", "tolerance", "ls_tolerance", "gravity", "impratio_invsqrt", "ccd_tolerance")
 _OPT_INTS = ("integrator", "cone", "solver", "iterations", "ls_iterations", "disableflags", "enableflags", "broadphase", "broadphase_filter",
-             "run_collision_detection", "ccd_iterations")  # fmt: skip
+             "run_collision_detection", "ccd_iterations", "ls_parallel")  # fmt: skip
 
 
 def make_option(m) -> MjbOption:
@@ -208,6 +208,8 @@ def make_option(m) -> MjbOption:
       raise NotImplementedError(f"per-world Option.{n} (shape {tuple(getattr(o, n).shape)}) is not implemented: the kernels take one value for all worlds")
   if mi.numel() != 1:
     raise NotImplementedError("per-world stat.meaninertia is not implemented")
+  if bool(o.ls_parallel):  # reference solver.py:331-566: N step sizes evaluated at once; the in-kernel search here is the iterative one
+    raise NotImplementedError("opt.ls_parallel (parallel linesearch) is not implemented: use the iterative linesearch (ls_parallel=False)")
   key = tuple(getattr(o, n) for n in _OPT_INTS) + tuple(x for n in _OPT_TENSORS for x in (id(getattr(o, n)), getattr(o, n)._version)) + (id(mi), mi._version)
   cached = getattr(m, "_opt_cache", None)
   if cached is not None and cached[0] == key:

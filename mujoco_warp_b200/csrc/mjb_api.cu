@@ -493,6 +493,11 @@ MJB_STAGE_ENTRY(make_constraint, MJB_STAGE_MAKE_CONSTRAINT)
 MJB_STAGE_ENTRY(transmission, MJB_STAGE_TRANSMISSION)
 MJB_STAGE_ENTRY(fwd_velocity, MJB_STAGE_FWD_VELOCITY)
 MJB_STAGE_ENTRY(fwd_actuation, MJB_STAGE_FWD_ACTUATION)
+MJB_STAGE_ENTRY(com_vel, MJB_STAGE_COM_VEL)
+MJB_STAGE_ENTRY(passive, MJB_STAGE_PASSIVE)
+MJB_STAGE_ENTRY(rne, MJB_STAGE_RNE)
+MJB_STAGE_ENTRY(energy_pos, MJB_STAGE_ENERGY_POS)
+MJB_STAGE_ENTRY(energy_vel, MJB_STAGE_ENERGY_VEL)
 MJB_STAGE_ENTRY(solve, MJB_STAGE_SOLVE)
 MJB_STAGE_ENTRY(euler, MJB_STAGE_EULER)
 MJB_STAGE_ENTRY(implicit, MJB_STAGE_IMPLICIT)

@@ -284,6 +284,43 @@ __device__ __forceinline__ void s_make_constraint(const KParams& K, const unsign
         nl += n2 - nefc;
         nefc = n2;
       }
+      // ball joints (constraint.py:1422 _limit_ball): the rotation angle against max(range), J = -axis on the joint's three dofs
+      for (int k0 = 0; k0 < K.ms.nlimitball; k0 += 32) {
+        const int k = k0 + lane;
+        bool active = false;
+        EfcRow e = {};
+        int j = 0, da = 0;
+        V3 axis{0.f, 0.f, 0.f};
+        if (k < K.ms.nlimitball) {
+          j = MI(jnt_limited_ball_adr)[k];
+          const V3 aa = quat_to_vel(normalize(ld4(qpos + MI(jnt_qposadr)[j])));
+          const float angle = norm(aa), mg = MR(jnt_margin)[j];
+          axis = angle == 0.f ? aa : aa * (1.0f / angle);  // math.py:261 normalize_with_norm
+          const float pos = fmaxf(MR(jnt_range)[2 * j], MR(jnt_range)[2 * j + 1]) - angle - mg;
+          active = pos < 0.f;
+          if (active) {
+            da = MI(jnt_dofadr)[j];
+            const float jqvel = -axis.x * qvel[da] - axis.y * qvel[da + 1] - axis.z * qvel[da + 2];
+            e = efc_row(K, pos, pos, MR(dof_invweight0)[da], MR(jnt_solref) + 2 * j, MR(jnt_solimp) + 5 * j, mg, jqvel, 0.f);
+          }
+        }
+        const unsigned mask = __ballot_sync(FULL, active);
+        const int r = nefc + __popc(mask & ((1u << lane) - 1u));
+        if (active && r < K.dsz.njmax) store_row(K, w, r, e, CT_LIMIT_JOINT, j);
+        unsigned mm = mask;
+        while (mm) {
+          const int src = __ffs(mm) - 1;
+          mm &= mm - 1;
+          const int rr = __shfl_sync(FULL, r, src), dd = __shfl_sync(FULL, da, src);
+          const float ax = __shfl_sync(FULL, axis.x, src), ay = __shfl_sync(FULL, axis.y, src), az = __shfl_sync(FULL, axis.z, src);
+          if (rr < K.dsz.njmax) {
+            float* J = DW(efc_J) + (size_t)rr * K.ms.nv_pad;
+            for (int c = lane; c < K.ms.nv_pad; c += 32) J[c] = c == dd ? -ax : (c == dd + 1 ? -ay : (c == dd + 2 ? -az : 0.f));
+          }
+        }
+        nl += __popc(mask);
+        nefc += __popc(mask);
+      }
     }
     if (!(dsbl & DSBL_CONTACT)) {  // constraint.py:1669-1936, pyramidal cones
       const int ncon = DW(wcon_n)[0], nmp = K.ms.nmaxpyramid;

@@ -51,7 +51,9 @@ __host__ __device__ inline uint32_t group_mask(int g) {
     case G_POS: return MJB_STAGE_KINEMATICS | MJB_STAGE_COM_POS | MJB_STAGE_CRB | MJB_STAGE_FACTOR_M | MJB_STAGE_TRANSMISSION;
     case G_COL: return MJB_STAGE_COLLISION;
     case G_CON: return MJB_STAGE_MAKE_CONSTRAINT;
-    case G_VEL: return MJB_STAGE_ZERO_SENSOR | MJB_STAGE_FWD_VELOCITY | MJB_STAGE_FWD_ACTUATION | MJB_STAGE_FWD_ACCELERATION | MJB_STAGE_FWD_ACC_FACTOR;
+    case G_VEL:
+      return MJB_STAGE_ZERO_SENSOR | MJB_STAGE_FWD_VELOCITY | MJB_STAGE_FWD_ACTUATION | MJB_STAGE_FWD_ACCELERATION | MJB_STAGE_FWD_ACC_FACTOR |
+             MJB_STAGE_COM_VEL | MJB_STAGE_PASSIVE | MJB_STAGE_RNE | MJB_STAGE_ENERGY_POS | MJB_STAGE_ENERGY_VEL;
     case G_SOL: return MJB_STAGE_SOLVE;
     case G_EUL: return MJB_STAGE_EULER | MJB_STAGE_IMPLICIT;
   }
@@ -181,8 +183,12 @@ __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group
         if (energy) s_energy_pos(K, mb, w, lane);
         else if (lane < 2) DW(energy)[lane] = 0.f;
       }
-      if (st & MJB_STAGE_FWD_VELOCITY) s_fwd_velocity(K, mb, w, lane);
-      if (energy && (st & MJB_STAGE_FWD_VELOCITY)) s_energy_vel(K, w, lane);
+      if (st & MJB_STAGE_ENERGY_POS) s_energy_pos(K, mb, w, lane);
+      const int parts = (st & MJB_STAGE_FWD_VELOCITY) ? FV_ALL
+                                                      : ((st & MJB_STAGE_COM_VEL) ? FV_COMVEL : 0) | ((st & MJB_STAGE_PASSIVE) ? FV_PASSIVE : 0) |
+                                                            ((st & MJB_STAGE_RNE) ? FV_RNE : 0);
+      if (parts) s_fwd_velocity(K, mb, w, lane, parts);
+      if ((energy && (st & MJB_STAGE_FWD_VELOCITY)) || (st & MJB_STAGE_ENERGY_VEL)) s_energy_vel(K, w, lane);
       if (st & MJB_STAGE_FWD_ACTUATION) s_fwd_actuation(K, mb, w, lane);
       if (st & (MJB_STAGE_FWD_ACCELERATION | MJB_STAGE_FWD_ACC_FACTOR)) s_fwd_acceleration(K, mb, w, lane, scr, (st & MJB_STAGE_FWD_ACC_FACTOR) != 0);
     }

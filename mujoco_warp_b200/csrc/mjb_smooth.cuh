@@ -687,7 +687,12 @@ __device__ __forceinline__ void s_transmission(const KParams& K, const unsigned 
 // forward.fwd_velocity (forward.py:593): actuator_velocity (:541), com_vel (smooth.py:1936-2038),
 // passive spring/damper (passive.py:71-180, 536-565), rne (smooth.py:1113-1274)
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned char* mb, int w, int lane) {
+// `parts` selects the reference's sub-functions, which are public stage functions too: FV_ACTVEL actuator_velocity (forward.py:541),
+// FV_PASSIVE passive.passive (passive.py:729), FV_COMVEL smooth.com_vel (smooth.py:2015: cvel, cdof_dot), FV_RNE smooth.rne
+// (smooth.py:1259: cacc, cfrc_int, qfrc_bias).  com_vel and rne share one walk down the tree; run alone, each recomputes the
+// velocities on the way and stores only its own outputs.
+enum { FV_ACTVEL = 1, FV_PASSIVE = 2, FV_COMVEL = 4, FV_RNE = 8, FV_ALL = 15 };
+__device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned char* mb, int w, int lane, int parts = FV_ALL) {
   const int nb = K.ms.nbody, nv = K.ms.nv;
   const float* qvel = DW(qvel);
   const float* qpos = DW(qpos);
@@ -699,7 +704,7 @@ __device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned 
   const int* tree = MI(body_tree);
   const int* tree_adr = MI(body_tree_adr);
 
-  for (int a = lane; a < K.ms.nu; a += MJB_LW) {
+  for (int a = lane; a < ((parts & FV_ACTVEL) ? K.ms.nu : 0); a += MJB_LW) {
     const int adr = DW(moment_rowadr)[a], nnz = DW(moment_rownnz)[a];
     float v = 0.f;
     for (int i = 0; i < nnz; i++) v += DW(actuator_moment)[adr + i] * qvel[DW(moment_colind)[adr + i]];
@@ -707,7 +712,7 @@ __device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned 
   }
   // passive forces: lane per joint
   const int dsbl_spring = K.o.disableflags & DSBL_SPRING, dsbl_damper = K.o.disableflags & DSBL_DAMPER;
-  for (int j = lane; j < K.ms.njnt; j += MJB_LW) {
+  for (int j = lane; j < ((parts & FV_PASSIVE) ? K.ms.njnt : 0); j += MJB_LW) {
     const int da = MI(jnt_dofadr)[j], qa = MI(jnt_qposadr)[j], jt = MI(jnt_type)[j];
     const float k = MR(jnt_stiffness)[j], c = MR(dof_damping)[da];
     const bool hs = k != 0.f && !dsbl_spring, hd = c != 0.f && !dsbl_damper;
@@ -737,7 +742,7 @@ __device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned 
     }
   }
   // passive.py:246-272 _gravity_force + :536-565: gravity compensation through the CoM Jacobian (support.jac_dof), lane = dof
-  if (K.ms.ngravcomp && !(K.o.disableflags & DSBL_GRAVITY) && !(dsbl_spring && dsbl_damper)) {
+  if ((parts & FV_PASSIVE) && K.ms.ngravcomp && !(K.o.disableflags & DSBL_GRAVITY) && !(dsbl_spring && dsbl_damper)) {
     __syncwarp();
     const V3 g{K.o.gravity_x, K.o.gravity_y, K.o.gravity_z};
     for (int dof = lane; dof < K.ms.nv; dof += MJB_LW) {
@@ -754,7 +759,16 @@ __device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned 
       if (!MI(jnt_actgravcomp)[MI(dof_jntid)[dof]]) DW(qfrc_passive)[dof] += q;
     }
   }
-  // com_vel + cacc, level-synchronous (cacc needs cdof_dot of the same body only)
+  if (!(parts & (FV_COMVEL | FV_RNE))) {
+    __syncwarp();
+    return;
+  }
+  // com_vel + cacc, level-synchronous (cacc needs cdof_dot of the same body only).  Run alone, com_vel keeps its running velocities
+  // in cvel and rne its accelerations in cacc; the other quantity of the walk then travels through the scratch rows of cfrc_ext
+  // (bodies x 6, rewritten to zero at the end) so that neither touches the other's outputs.
+  const bool do_cv = (parts & FV_COMVEL) != 0, do_rne = (parts & FV_RNE) != 0;
+  if (!do_cv) cvel = DW(cfrc_int);  // rne alone: velocities are staged in cfrc_int (defined by rne itself, after the walk)
+  if (!do_rne) cacc = DW(cfrc_ext);  // com_vel alone: the accelerations of the walk are not an output
   if (lane < 6) {
     cvel[lane] = 0.f;
     float g = 0.f;
@@ -803,26 +817,29 @@ __device__ __forceinline__ void s_fwd_velocity(const KParams& K, const unsigned 
       }
       st6(cvel + 6 * b, v);
       st6(cacc + 6 * b, acc);
-      // body force (smooth.py:1188-1209), own contribution; subtree sums follow
-      const float* ci = DW(cinert) + 10 * b;
-      S6 f = inert_vec(ci, acc);
-      const S6 u = motion_cross_force(v, inert_vec(ci, v));
+      if (do_rne) {  // body force (smooth.py:1188-1209), own contribution; subtree sums follow
+        const float* ci = DW(cinert) + 10 * b;
+        S6 f = inert_vec(ci, acc);
+        const S6 u = motion_cross_force(v, inert_vec(ci, v));
 #pragma unroll
-      for (int k = 0; k < 6; k++) f.v[k] += u.v[k];
-      st6(DW(cfrc_ext) + 6 * b, f);  // staging: cfrc_ext is rewritten to zero below
+        for (int k = 0; k < 6; k++) f.v[k] += u.v[k];
+        st6(DW(cfrc_ext) + 6 * b, f);  // staging: cfrc_ext is rewritten to zero below
+      }
     }
     __syncwarp();
   }
-  // cfrc_int[b] = sum of the own forces over the subtree (smooth.py:1219-1240 without atomics)
-  for (int b = lane; b < nb; b += MJB_LW) {
-    const int end = MI(body_subtreeend)[b];
-    S6 acc = S6{{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
-    for (int c = (b == 0 ? 1 : b); c < end; c++) axpy6(acc, 1.0f, ld6(DW(cfrc_ext) + 6 * c));
-    st6(cfrc + 6 * b, acc);
+  if (do_rne) {  // cfrc_int[b] = sum of the own forces over the subtree (smooth.py:1219-1240 without atomics)
+    for (int b = lane; b < nb; b += MJB_LW) {
+      const int end = MI(body_subtreeend)[b];
+      S6 acc = S6{{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}};
+      for (int c = (b == 0 ? 1 : b); c < end; c++) axpy6(acc, 1.0f, ld6(DW(cfrc_ext) + 6 * c));
+      st6(cfrc + 6 * b, acc);
+    }
+    __syncwarp();
   }
-  __syncwarp();
   for (int b = lane; b < nb; b += MJB_LW) st6(DW(cfrc_ext) + 6 * b, S6{{0.f, 0.f, 0.f, 0.f, 0.f, 0.f}});
-  for (int i = lane; i < nv; i += MJB_LW) DW(qfrc_bias)[i] = dot6(ld6(cdof + 6 * i), ld6(cfrc + 6 * MI(dof_bodyid)[i]));
+  if (do_rne)
+    for (int i = lane; i < nv; i += MJB_LW) DW(qfrc_bias)[i] = dot6(ld6(cdof + 6 * i), ld6(cfrc + 6 * MI(dof_bodyid)[i]));
   __syncwarp();
 }
 

@@ -36,6 +36,11 @@ STAGE_SOLVE = 1 << 11
 STAGE_EULER = 1 << 12
 STAGE_IMPLICIT = 1 << 13
 STAGE_ZERO_SENSOR = 1 << 14
+STAGE_COM_VEL = 1 << 15
+STAGE_PASSIVE = 1 << 16
+STAGE_RNE = 1 << 17
+STAGE_ENERGY_POS = 1 << 18
+STAGE_ENERGY_VEL = 1 << 19
 STAGES_FWD_POSITION = STAGE_KINEMATICS | STAGE_COM_POS | STAGE_CRB | STAGE_COLLISION | STAGE_MAKE_CONSTRAINT | STAGE_TRANSMISSION
 STAGES_FORWARD = STAGES_FWD_POSITION | STAGE_ZERO_SENSOR | STAGE_FWD_VELOCITY | STAGE_FWD_ACTUATION | STAGE_FWD_ACC_FACTOR | STAGE_SOLVE
 
@@ -110,6 +115,31 @@ def fwd_position(m, d, factorize: bool = True):
 def fwd_velocity(m, d):
   """Velocity-dependent computations (reference forward.py:593)."""
   _run(m, d, STAGE_FWD_VELOCITY)
+
+
+def com_vel(m, d):
+  """Body velocities in the com frame and the time derivatives of the motion axes (reference smooth.py:2015)."""
+  _run(m, d, STAGE_COM_VEL)
+
+
+def passive(m, d):
+  """Passive forces: joint springs, dampers, gravity compensation (reference passive.py:729)."""
+  _run(m, d, STAGE_PASSIVE)
+
+
+def rne(m, d):
+  """Recursive Newton-Euler bias forces: cacc, cfrc_int, qfrc_bias (reference smooth.py:1259)."""
+  _run(m, d, STAGE_RNE)
+
+
+def energy_pos(m, d):
+  """Potential energy into d.energy[:, 0] (reference sensor.py:2854)."""
+  _run(m, d, STAGE_ENERGY_POS)
+
+
+def energy_vel(m, d):
+  """Kinetic energy into d.energy[:, 1] (reference sensor.py:2922)."""
+  _run(m, d, STAGE_ENERGY_VEL)
 
 
 def fwd_actuation(m, d):

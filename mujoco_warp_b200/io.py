@@ -188,8 +188,6 @@ def host_model(mjm) -> SimpleNamespace:
   limited = np.asarray(mjm.jnt_limited).astype(bool)
   ints["jnt_limited_adr"] = np.nonzero(limited & np.isin(jnt_type, (C.JointType.SLIDE, C.JointType.HINGE)))[0].astype(i32)
   ints["jnt_limited_ball_adr"] = np.nonzero(limited & (jnt_type == C.JointType.BALL))[0].astype(i32)
-  if ints["jnt_limited_ball_adr"].size:
-    raise NotImplementedError("ball joint limits are not implemented yet.")
   ints["dof_friction_adr"] = np.nonzero(reals["dof_frictionloss"] > 0)[0].astype(i32)
   ints["eq_objtype"] = np.asarray(getattr(mjm, "eq_objtype", np.ones(int(mjm.neq)))).astype(i32).reshape(-1)  # mjtObj: 1 body, 3 joint, 6 site
   ints["eq_jnt_adr"] = np.nonzero(ints["eq_type"] == C.EqType.JOINT)[0].astype(i32)

@@ -1685,6 +1685,26 @@ static void o_make_constraint(const OModel* m, const OOpt* o, OData* d, const OD
       efc_row(o, d, r, pos, pos, m->dof_invweight0[da], m->jnt_solref + 2 * j, m->jnt_solimp + 5 * j, mg, Jv * d->qvel[da], 0.0,
               CT_LIMIT_JOINT, j);
     }
+    for (int k = 0; k < m->nlimitball; k++) { /* constraint.py:1422-1545 _limit_ball */
+      int j = m->jnt_limited_ball_adr[k];
+      real q[4], aa[3], axis[3] = {0, 0, 0};
+      for (int i = 0; i < 4; i++) q[i] = d->qpos[m->jnt_qposadr[j] + i];
+      normalize4(q);
+      quat_to_vel(aa, q);
+      real angle = sqrt(aa[0] * aa[0] + aa[1] * aa[1] + aa[2] * aa[2]), mg = m->jnt_margin[j];
+      for (int i = 0; i < 3; i++) axis[i] = angle == 0 ? aa[i] : aa[i] / angle; /* math.py:261 normalize_with_norm */
+      real pos = fmax(m->jnt_range[2 * j], m->jnt_range[2 * j + 1]) - angle - mg;
+      if (!(pos < 0)) continue;
+      d->nl[0]++;
+      int r = nefc++;
+      if (r >= njmax) continue;
+      int da = m->jnt_dofadr[j];
+      real* J = d->efc_J + (size_t)r * np;
+      for (int i = 0; i < nv; i++) J[i] = 0;
+      real jqvel = 0;
+      for (int i = 0; i < 3; i++) { J[da + i] = -axis[i]; jqvel -= axis[i] * d->qvel[da + i]; }
+      efc_row(o, d, r, pos, pos, m->dof_invweight0[da], m->jnt_solref + 2 * j, m->jnt_solimp + 5 * j, mg, jqvel, 0.0, CT_LIMIT_JOINT, j);
+    }
   }
   if (!(o->disableflags & DSBL_CONTACT)) { /* constraint.py:1669-1936 pyramidal */
     int nmp = m->nmaxpyramid;

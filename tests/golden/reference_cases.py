@@ -135,6 +135,7 @@ CASES = {
   # RK4 with stateful actuators (filterexact + actrange clamp, integrator, filter, actearly): next_act in the stage perturbation
   # (unclamped) and the final advance (clamped), forward.py:355-400, :213-274
   "rk4_actuators_step4": dict(model="rk4_actuators", nworld=4, seed=17, mode="step", nstep=4, nconmax=16, njmax=32, opt=dict(integrator=1)),
+  "ball_limits_step3": dict(model="ball_limits", nworld=6, seed=23, mode="step", nstep=3, nconmax=8, njmax=16),
   "humanoid_sap_tile": dict(model="humanoid", nworld=2, seed=9, sink=0.05, mode="forward", opt=dict(broadphase=1)),
   "humanoid_sap_segmented": dict(model="humanoid", nworld=2, seed=9, sink=0.05, mode="forward", opt=dict(broadphase=2)),
   "humanoid_no_eulerdamp_refsafe": dict(model="humanoid", nworld=2, seed=12, sink=0.03, mode="step", nstep=2, disable=["EULERDAMP", "REFSAFE"]),

@@ -121,6 +121,19 @@ SMALL_MODELS["rk4_actuators"] = """
       </actuator>
     </mujoco>"""
 
+# limited ball joints (constraint.py:1422 _limit_ball): one well past its range, one inside, one with a margin that activates it
+SMALL_MODELS["ball_limits"] = """
+    <mujoco><option timestep="0.002"/>
+      <worldbody>
+        <body pos="0 0 1"><joint name="a" type="ball" limited="true" range="0 20" damping="0.05"/><geom type="capsule" size=".04 .2" fromto="0 0 0 .4 0 0"/>
+          <body pos=".4 0 0"><joint name="b" type="ball" limited="true" range="0 60"/><geom type="capsule" size=".03 .15" fromto="0 0 0 .3 0 0"/>
+            <body pos=".3 0 0"><joint name="c" type="hinge" axis="0 1 0" limited="true" range="-10 10"/><geom type="sphere" size=".05" pos=".1 0 0"/></body></body>
+        </body>
+        <body pos="0 1 1"><joint name="d" type="ball" limited="true" range="0 25" margin="0.2" solreflimit="0.01 1" solimplimit="0.8 0.9 0.01"/><geom type="box" size=".1 .05 .03" pos=".1 0 0"/></body>
+      </worldbody>
+      <actuator><motor joint="c" gear="1"/></actuator>
+    </mujoco>"""
+
 BOX_PAIRS_XML = """
 <mujoco>
   <worldbody>

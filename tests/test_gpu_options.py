@@ -425,3 +425,26 @@ def test_rk4_public_function_after_forward_equals_step(humanoid):
   mjw.rungekutta4(m, b)
   for f in ["qpos", "qvel", "qacc", "time"]:
     assert torch.equal(a.field(f), b.field(f)), f
+
+
+def test_sub_stage_functions_reproduce_fwd_velocity(humanoid):
+  """com_vel / passive / rne / energy_pos / energy_vel are public stage functions of the reference too (mujoco_warp/__init__.py): run on
+  their own, each writes exactly the outputs it defines with the values `forward` gives them."""
+  qpos, qvel, ctrl = H.make_states(humanoid, 8, seed=31)
+  m, a = H.device_data(mjw, humanoid, qpos, qvel, ctrl, 24, 64)
+  _, b = H.device_data(mjw, humanoid, qpos, qvel, ctrl, 24, 64)
+  m.opt.enableflags = int(m.opt.enableflags) | int(C.EnableBit.ENERGY)
+  mjw.forward(m, a)
+  mjw.fwd_position(m, b)
+  outs = {"com_vel": ["cvel", "cdof_dot"], "passive": ["qfrc_spring", "qfrc_damper", "qfrc_passive"], "rne": ["cacc", "cfrc_int", "qfrc_bias"]}
+  for fn in ("rne", "passive", "com_vel"):  # any order: each recomputes what it needs from qpos / qvel and the position stage
+    for f in outs[fn]:
+      b.field(f).fill_(7.0)
+    getattr(mjw, fn)(m, b)
+    for f in outs[fn]:
+      assert torch.equal(a.field(f), b.field(f)), (fn, f)
+  assert torch.all(b.cfrc_ext == 0)
+  mjw.energy_pos(m, b)
+  mjw.energy_vel(m, b)
+  torch.testing.assert_close(a.energy, b.energy, rtol=1e-6, atol=1e-6)
+  assert float(b.energy[:, 1].min()) > 0
