@@ -35,7 +35,7 @@ SETTLE_STEPS = 250  # untimed steps between the keyframe start and every timed w
 CONFIGS = {
   "humanoid": dict(path="benchmarks/humanoid/humanoid.xml", nworld=8192, nconmax=24, njmax=64, replay=None),
   "panda": dict(path="benchmarks/franka_emika_panda/scene.xml", nworld=8192, nconmax=1, njmax=5, replay=None),
-  "apollo_flat": dict(path="benchmarks/apptronik_apollo/scene_flat.xml", nworld=4096, nconmax=16, njmax=64, replay=None,
+  "apollo_flat": dict(path="benchmarks/apptronik_apollo/scene_flat.xml", nworld=4096, nconmax=16, njmax=64, replay=None, disable=("NATIVECCD",),
                       note="box-box pairs carry a margin: the reference's put_model only accepts this scene with DisableBit.NATIVECCD "
                            "(io.py:386-395), i.e. box-box through the box_box primitive, which is the route timed here"),
   "aloha_pot": dict(path="benchmarks/aloha_pot/scene.xml", nworld=4096, nconmax=24, njmax=128, replay="lift_pot"),
@@ -173,6 +173,8 @@ def load_config(name):
 
   cfg = CONFIGS[name]
   mjm = mjw.load_mjcf(os.path.join(ROOT, cfg["path"]))
+  for flag in cfg.get("disable", ()):
+    mjm.opt.disableflags |= int(getattr(mjw.DisableBit, flag))
   keys = mjw.find_keys(mjm, cfg["replay"]) if cfg["replay"] else ([0] if mjm.nkey else [])
   return cfg, mjm, keys
 

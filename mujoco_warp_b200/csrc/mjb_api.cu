@@ -41,6 +41,7 @@ struct MjbModel {
   int blob_bytes;
   int blob_hot;  // bytes of the prefix the kernels stage in shared memory (= blob_bytes unless the model carries large cold tables)
   int col_feat;  // CollisionFeature bits the model needs (pair types present in the filtered pair list)
+  int has_boxbox;  // box-box pairs present: they run GJK / EPA + multi-contact (the convex variant) unless DisableBit.NATIVECCD
 };
 
 struct MjbData {
@@ -147,6 +148,7 @@ extern "C" int mjb_model_create(const int* sizes, int nsizes, const void* blob, 
   m->blob_bytes = (int)nbytes;
   m->blob_hot = (m->ms.blob_hot_bytes > 0 && m->ms.blob_hot_bytes < (int)nbytes) ? m->ms.blob_hot_bytes : (int)nbytes;
   m->col_feat = 0;
+  m->has_boxbox = 0;
   if (m->ms.nxn > 0) {  // pair types present in the statically filtered pair list (one small read-back at creation)
     std::vector<int> pair(2 * (size_t)m->ms.nxn), gtype((size_t)m->ms.ngeom);
     const unsigned char* db = static_cast<const unsigned char*>(blob);
@@ -160,6 +162,7 @@ extern "C" int mjb_model_create(const int* sizes, int nsizes, const void* blob, 
       const int ta = gtype[pair[2 * p]], tb = gtype[pair[2 * p + 1]];
       const int t1 = ta < tb ? ta : tb, t2 = ta < tb ? tb : ta;
       if (t2 == GEOM_BOX && t1 != GEOM_PLANE) m->col_feat |= COLF_BOX;  // sphere-box, capsule-box, box-box
+      if (t1 == GEOM_BOX && t2 == GEOM_BOX) m->has_boxbox = 1;
       if (t1 == GEOM_ELLIPSOID || t1 == GEOM_CYLINDER || t1 == GEOM_MESH || t2 == GEOM_ELLIPSOID || t2 == GEOM_CYLINDER || t2 == GEOM_MESH) m->col_feat |= COLF_CONVEX;
     }
   }
@@ -339,8 +342,11 @@ static GroupKernel group_kernel_of(int g, bool in_smem, int variant) {
 
 // kernel variant of a group under the given options: collision follows the model's pair types and the broadphase option of THIS
 // call; make_constraint / solve are compiled once per cone type
-static int group_variant(int g, const MjbModel* m, int broadphase, int cone) {
-  if (g == G_COL) return (m->col_feat & COLF_CONVEX) ? COLF_COUNT - 1 : (m->col_feat | (broadphase != 0 ? COLF_SAP : 0));
+static int group_variant(int g, const MjbModel* m, int broadphase, int cone, int disableflags) {
+  if (g == G_COL) {
+    const bool convex = (m->col_feat & COLF_CONVEX) || (m->has_boxbox && !(disableflags & DSBL_NATIVECCD));
+    return convex ? COLF_COUNT - 1 : (m->col_feat | (broadphase != 0 ? COLF_SAP : 0));
+  }
   return ((g == G_CON || g == G_SOL) && cone == 1) ? 1 : 0;
 }
 static MjbData::GroupCfg& group_cfg(MjbData* d, int g, int variant) {
@@ -377,7 +383,7 @@ static int resolve_cfg(int g, int variant, const MjbModel* m, MjbData* d) {
 }
 
 static int launch_group(int g, const MjbModel* m, MjbData* d, KParams& K, uint32_t stages, cudaStream_t stream) {
-  const int variant = group_variant(g, m, K.o.broadphase, K.o.cone);
+  const int variant = group_variant(g, m, K.o.broadphase, K.o.cone, K.o.disableflags);
   {
     const int rc = resolve_cfg(g, variant, m, d);
     if (rc) return rc;
@@ -463,7 +469,7 @@ extern "C" int mjb_step(const MjbModel* m, MjbData* d, const MjbOption* opt, voi
 extern "C" int mjb_prepare(const MjbModel* m, MjbData* d, const MjbOption* opt) {
   if (!m || !d || !opt) return fail(-1, "null handle");
   for (int g = 0; g < G_COUNT; g++) {
-    const int rc = resolve_cfg(g, group_variant(g, m, opt->broadphase, opt->cone), m, d);
+    const int rc = resolve_cfg(g, group_variant(g, m, opt->broadphase, opt->cone, opt->disableflags), m, d);
     if (rc) return rc;
   }
   const size_t smem = (size_t)warps_per_block(4) * d->scratch_floats * sizeof(float);

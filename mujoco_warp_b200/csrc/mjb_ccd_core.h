@@ -638,7 +638,8 @@ CCD_FN_NOINLINE int ccd_epa(creal tolerance, int iterations, CcdPolytope* pt, co
 /* :2200 ccd.  g1 / g2 are taken by value (the routine shrinks spheres / capsules to points / segments).  `pt` is scratch.
  * Returns the number of contacts (0 or 1); dist is relative to the margin-inflated shapes as in the reference. */
 CCD_FN_NOINLINE int ccd_run(creal tolerance, creal cutoff, int gjk_iterations, int epa_iterations, CcdGeom g1, CcdGeom g2, CcdPolytope* pt,
-                   CcdGjk* res, creal* dist, creal* x1, creal* x2) {
+                   CcdGjk* res, creal* dist, creal* x1, creal* x2, int* multiccd_idx) {
+  *multiccd_idx = -1; /* the EPA face the contact was found on, when multi-contact recovery applies (:2336-2343) */
   creal full1 = CR(0.0), full2 = CR(0.0), size1 = CR(0.0), size2 = CR(0.0), x_1[3], x_2[3];
   int is_discrete = ((g1.type == CCD_GEOM_BOX || g1.type == CCD_GEOM_MESH) && (g2.type == CCD_GEOM_BOX || g2.type == CCD_GEOM_MESH)) &&
                     (g1.margin == CR(0.0) && g2.margin == CR(0.0)); /* :91 _discrete_geoms */
@@ -686,7 +687,282 @@ CCD_FN_NOINLINE int ccd_run(creal tolerance, creal cutoff, int gjk_iterations, i
   if (pt->status) { *dist = res->dist; ccd_copy(x1, res->x1); ccd_copy(x2, res->x2); return 1; }
   int idx = ccd_epa(tolerance, epa_iterations, pt, &g1, &g2, is_discrete, dist, x1, x2);
   if (idx == -1) { *dist = CCD_FLOAT_MAX; return 0; }
+  /* multicontact: not with a margin, boxes and meshes only */
+  if (g1.margin == CR(0.0) && g2.margin == CR(0.0) && (g1.type == CCD_GEOM_BOX || g1.type == CCD_GEOM_MESH) &&
+      (g2.type == CCD_GEOM_BOX || g2.type == CCD_GEOM_MESH))
+    *multiccd_idx = idx;
   return 1;
+}
+
+/* ---- multi-contact recovery by face clipping (collision_gjk.py:1332-2150), boxes --------------------------------------------------
+ * The reference also clips mesh polygons (_mesh_normals :1460, _mesh_edge_normals :1530, _mesh_face :1766); those need MuJoCo's
+ * mesh_poly* tables, which the MJCF-lite compiler does not build: pairs with a mesh keep their single EPA contact. */
+#define CCD_FACE_TOL CR(0.99999872000027307) /* cos(0.0016) */
+#define CCD_EDGE_TOL CR(0.0015999993173334207) /* sin(0.0016) */
+#define CCD_INTERSECT_TOL CR(0.0000003)
+
+typedef struct {
+  creal polygon[8][3], clipped[8][3], pnormal[4][3], pdist[4]; /* polygon buffers: 2 * max sides (collision_convex.py:1158) */
+  creal n1[3][3], n2[3][3], endvert[3][3], face1[4][3], face2[4][3];
+  int idx1[3], idx2[3];
+} CcdMulti;
+
+CCD_FN void ccd_matvec(creal* r, const creal* m, creal x, creal y, creal z) {
+  r[0] = m[0] * x + m[1] * y + m[2] * z; r[1] = m[3] * x + m[4] * y + m[5] * z; r[2] = m[6] * x + m[7] * y + m[8] * z;
+}
+CCD_FN void ccd_normalize(creal* v) {
+  creal n = ccd_norm(v);
+  if (n > CR(0.0)) { v[0] /= n; v[1] /= n; v[2] /= n; } else { v[0] = v[1] = v[2] = CR(0.0); }
+}
+/* :1332 */
+CCD_FN creal ccd_area4(const creal* a, const creal* b, const creal* c, const creal* d) {
+  creal ad[3], db[3], bc[3], ca[3], c1[3], c2[3];
+  ccd_sub(ad, a, d); ccd_sub(db, d, b); ccd_sub(bc, b, c); ccd_sub(ca, c, a);
+  ccd_cross(c1, ad, db); ccd_cross(c2, bc, ca);
+  c1[0] += c2[0]; c1[1] += c2[1]; c1[2] += c2[2];
+  return CR(0.5) * ccd_norm(c1);
+}
+/* :1338 quadrilateral of maximum area in a convex polygon (npolygon > 4) */
+CCD_FN void ccd_polygon_quad(int* res, creal (*poly)[3], int np) {
+  int b = 1, c = 2, d = 3;
+  res[0] = 0; res[1] = b; res[2] = c; res[3] = d;
+  creal m = ccd_area4(poly[0], poly[b], poly[c], poly[d]);
+  for (int a = 0; a < np; a++) {
+    for (;;) {
+      creal m_next = ccd_area4(poly[a], poly[b], poly[c], poly[(d + 1) % np]);
+      if (m_next <= m) break;
+      m = m_next; d = (d + 1) % np;
+      res[0] = a; res[1] = b; res[2] = c; res[3] = d;
+      for (;;) {
+        m_next = ccd_area4(poly[a], poly[b], poly[(c + 1) % np], poly[d]);
+        if (m_next <= m) break;
+        m = m_next; c = (c + 1) % np;
+        res[0] = a; res[1] = b; res[2] = c; res[3] = d;
+      }
+      for (;;) {
+        m_next = ccd_area4(poly[a], poly[(b + 1) % np], poly[c], poly[d]);
+        if (m_next <= m) break;
+        m = m_next; b = (b + 1) % np;
+        res[0] = a; res[1] = b; res[2] = c; res[3] = d;
+      }
+    }
+    if (b == a) {
+      b = (b + 1) % np;
+      if (c == b) {
+        c = (c + 1) % np;
+        if (d == c) d = (d + 1) % np;
+      }
+    }
+  }
+}
+/* :1378 dimension (1, 2, 3) of the feature of geom `offset` spanned by an EPA face; vertices reordered if necessary */
+CCD_FN int ccd_feature_dim(const int* face, const CcdPolytope* pt, int offset, int* findex, creal (*fvert)[3]) {
+  int v1i = pt->vert_index[2 * face[0] + offset], v2i = pt->vert_index[2 * face[1] + offset], v3i = pt->vert_index[2 * face[2] + offset];
+  findex[0] = v1i; findex[1] = v2i; findex[2] = v3i;
+  for (int k = 0; k < 3; k++) ccd_copy(fvert[k], pt->vert[2 * face[k] + offset]);
+  if (v1i != v2i) return (v3i == v1i || v3i == v2i) ? 2 : 3;
+  findex[1] = v3i;
+  ccd_copy(fvert[1], pt->vert[2 * face[2] + offset]);
+  return v1i != v3i ? 2 : 1;
+}
+
+/* :1578 the box face (if any) whose normal is within FACE_TOL of n (world frame) */
+CCD_FN int ccd_box_normals2(const creal* mat, const creal* n, creal (*normal)[3], int* index) {
+  const creal fn[6][3] = {{1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};
+  creal ln[3];
+  ccd_rot_t(ln, mat, n);
+  ccd_normalize(ln);
+  for (int i = 0; i < 6; i++) {
+    if (ln[0] * fn[i][0] + ln[1] * fn[i][1] + ln[2] * fn[i][2] > CCD_FACE_TOL) {
+      ccd_matvec(normal[0], mat, fn[i][0], fn[i][1], fn[i][2]);
+      index[0] = i;
+      return 1;
+    }
+  }
+  return 0;
+}
+/* :1611 possible face normals of a box given up to 3 of its vertices (vertex index bits: x 1, y 2, z 4) */
+CCD_FN int ccd_box_normals(int fdim, const int* fi, const creal* mat, const creal* dir, creal (*normal)[3], int* index) {
+  const int v1 = fi[0], v2 = fi[1], v3 = fi[2];
+  if (fdim == 3) {
+    int c = 0;
+    creal x = (creal)(((v1 & 1) && (v2 & 1) && (v3 & 1)) ? 1 : 0) - (creal)((!(v1 & 1) && !(v2 & 1) && !(v3 & 1)) ? 1 : 0);
+    creal y = (creal)(((v1 & 2) && (v2 & 2) && (v3 & 2)) ? 1 : 0) - (creal)((!(v1 & 2) && !(v2 & 2) && !(v3 & 2)) ? 1 : 0);
+    creal z = (creal)(((v1 & 4) && (v2 & 4) && (v3 & 4)) ? 1 : 0) - (creal)((!(v1 & 4) && !(v2 & 4) && !(v3 & 4)) ? 1 : 0);
+    ccd_matvec(normal[0], mat, x, y, z);
+    creal sgn = x + y + z;
+    if (x != CR(0.0)) index[c++] = 0;
+    if (y != CR(0.0)) index[c++] = 2;
+    if (z != CR(0.0)) index[c++] = 4;
+    if (sgn == CR(-1.0)) index[0] = index[0] + 1;
+    if (c == 1) return 1;
+    return ccd_box_normals2(mat, dir, normal, index);
+  }
+  if (fdim == 2) {
+    int c = 0;
+    creal x = (creal)(((v1 & 1) && (v2 & 1)) ? 1 : 0) - (creal)((!(v1 & 1) && !(v2 & 1)) ? 1 : 0);
+    creal y = (creal)(((v1 & 2) && (v2 & 2)) ? 1 : 0) - (creal)((!(v1 & 2) && !(v2 & 2)) ? 1 : 0);
+    creal z = (creal)(((v1 & 4) && (v2 & 4)) ? 1 : 0) - (creal)((!(v1 & 4) && !(v2 & 4)) ? 1 : 0);
+    if (x != CR(0.0)) { ccd_matvec(normal[c], mat, x, CR(0.0), CR(0.0)); index[c] = x > CR(0.0) ? 0 : 1; c++; }
+    if (y != CR(0.0)) { ccd_matvec(normal[c], mat, CR(0.0), y, CR(0.0)); index[c] = y > CR(0.0) ? 2 : 3; c++; }
+    if (z != CR(0.0)) { ccd_matvec(normal[c], mat, CR(0.0), CR(0.0), z); index[c] = z > CR(0.0) ? 4 : 5; c++; }
+    if (c == 1 || c == 2) return c; /* 1: the edge is a face diagonal, 2: an external edge of the box */
+    return ccd_box_normals2(mat, dir, normal, index);
+  }
+  if (fdim == 1) {
+    creal x = (v1 & 1) ? CR(1.0) : CR(-1.0), y = (v1 & 2) ? CR(1.0) : CR(-1.0), z = (v1 & 4) ? CR(1.0) : CR(-1.0);
+    ccd_matvec(normal[0], mat, x, CR(0.0), CR(0.0));
+    ccd_matvec(normal[1], mat, CR(0.0), y, CR(0.0));
+    ccd_matvec(normal[2], mat, CR(0.0), CR(0.0), z);
+    index[0] = x > CR(0.0) ? 0 : 1; index[1] = y > CR(0.0) ? 2 : 3; index[2] = z > CR(0.0) ? 4 : 5;
+    return 3;
+  }
+  return 0;
+}
+/* :1685 edge directions of a box for edge collisions */
+CCD_FN int ccd_box_edge_normals(int dim, const CcdGeom* g, const creal* v1, const creal* v2, int v1i, creal (*normal)[3], creal (*endvert)[3]) {
+  if (dim == 2) {
+    ccd_copy(endvert[0], v2);
+    ccd_sub(normal[0], v2, v1);
+    ccd_normalize(normal[0]);
+    return 1;
+  }
+  if (dim == 1) { /* the three vertices adjacent to v1 */
+    creal x = (v1i & 1) ? g->size[0] : -g->size[0], y = (v1i & 2) ? g->size[1] : -g->size[1], z = (v1i & 4) ? g->size[2] : -g->size[2];
+    const creal c[3][3] = {{-x, y, z}, {x, -y, z}, {x, y, -z}};
+    for (int k = 0; k < 3; k++) {
+      ccd_matvec(endvert[k], g->rot, c[k][0], c[k][1], c[k][2]);
+      for (int i = 0; i < 3; i++) endvert[k][i] += g->pos[i];
+      ccd_sub(normal[k], endvert[k], v1);
+      ccd_normalize(normal[k]);
+    }
+    return 3;
+  }
+  return 0;
+}
+/* :1723 corners of box face idx (0 +x, 1 -x, 2 +y, 3 -y, 4 +z, 5 -z) in world coordinates */
+CCD_FN int ccd_box_face(const CcdGeom* g, int idx, creal (*face)[3]) {
+  static const signed char sg[6][4][3] = {
+      {{1, 1, 1}, {1, 1, -1}, {1, -1, -1}, {1, -1, 1}},     {{-1, 1, -1}, {-1, 1, 1}, {-1, -1, 1}, {-1, -1, -1}},
+      {{-1, 1, -1}, {1, 1, -1}, {1, 1, 1}, {-1, 1, 1}},     {{-1, -1, 1}, {1, -1, 1}, {1, -1, -1}, {-1, -1, -1}},
+      {{-1, 1, 1}, {1, 1, 1}, {1, -1, 1}, {-1, -1, 1}},     {{1, 1, -1}, {-1, 1, -1}, {-1, -1, -1}, {1, -1, -1}}};
+  if (idx < 0 || idx > 5) return 0;
+  for (int k = 0; k < 4; k++) {
+    ccd_matvec(face[k], g->rot, sg[idx][k][0] * g->size[0], sg[idx][k][1] * g->size[1], sg[idx][k][2] * g->size[2]);
+    for (int i = 0; i < 3; i++) face[k][i] += g->pos[i];
+  }
+  return 4;
+}
+
+/* :1816 clips polygon face2 against the edges of face1 (normal n); up to 4 witness pairs (w2 on the clipped polygon, w1 = w2 - dir) */
+CCD_FN int ccd_polygon_clip(CcdMulti* mc, creal (*face1)[3], int nface1, creal (*face2)[3], int nface2, const creal* n, const creal* dir,
+                            creal (*w1)[3], creal (*w2)[3]) {
+  if (nface1 < 3) return 0; /* the clipping face needs to be at least a triangle */
+  for (int i = 0; i < nface1; i++) { /* :1791 _plane_normal of every edge */
+    const creal *a = face1[i], *b = face1[(i + 1) % nface1];
+    creal ba[3];
+    ccd_sub(ba, b, a);
+    ccd_cross(mc->pnormal[i], ba, n);
+    mc->pdist[i] = ccd_dot(mc->pnormal[i], a);
+  }
+  creal (*poly)[3] = mc->polygon, (*clip)[3] = mc->clipped;
+  int npoly = nface2, nclip = 0;
+  for (int i = 0; i < nface2; i++) ccd_copy(poly[i], face2[i]);
+  for (int e = 0; e < nface1; e++) {
+    for (int i = 0; i < npoly; i++) {
+      const creal *P = poly[i], *Q = poly[(i + 1) % npoly];
+      creal pa[3], qa[3];
+      ccd_sub(pa, P, face1[e]); ccd_sub(qa, Q, face1[e]);
+      const int in1 = ccd_dot(pa, mc->pnormal[e]) > CR(-1e-10), in2 = ccd_dot(qa, mc->pnormal[e]) > CR(-1e-10); /* :1798 _halfspace */
+      if (!in1 && !in2) continue;
+      if (in1 && in2) { ccd_copy(clip[nclip++], Q); continue; }
+      creal qp[3];
+      ccd_sub(qp, Q, P);
+      const creal dt = ccd_dot(mc->pnormal[e], qp); /* :1803 _plane_intersect */
+      const creal t = CCD_FABS(dt) < CR(1e-10) ? CCD_FLOAT_MAX : (mc->pdist[e] - ccd_dot(mc->pnormal[e], P)) / dt;
+      if (t > -CCD_INTERSECT_TOL && t < CR(1.0) + CCD_INTERSECT_TOL) {
+        const creal tc = t < CR(0.0) ? CR(0.0) : (t > CR(1.0) ? CR(1.0) : t);
+        for (int k = 0; k < 3; k++) clip[nclip][k] = P[k] + tc * qp[k];
+        nclip++;
+      }
+      if (in2) ccd_copy(clip[nclip++], Q);
+    }
+    creal (*tmp)[3] = poly; poly = clip; clip = tmp;
+    npoly = nclip; nclip = 0;
+  }
+  if (npoly < 1) return 0;
+  if (npoly > 4) {
+    int quad[4];
+    ccd_polygon_quad(quad, poly, npoly);
+    for (int i = 0; i < 4; i++) { ccd_copy(w2[i], poly[quad[i]]); ccd_sub(w1[i], w2[i], dir); }
+    return 4;
+  }
+  for (int i = 0; i < npoly; i++) { ccd_copy(w2[i], poly[i]); ccd_sub(w1[i], w2[i], dir); }
+  return npoly;
+}
+
+/* :1930 multicontact for a box-box pair: recovers up to 4 contacts from the EPA face `epa_face` by clipping the boxes' matching
+ * faces (or an edge against a face).  w1[0] / w2[0] hold the EPA witness points on entry.  Returns the number of contacts. */
+CCD_FN_NOINLINE int ccd_multicontact_box(CcdMulti* mc, const CcdPolytope* pt, int epa_face, const CcdGeom* g1, const CcdGeom* g2,
+                                         creal (*w1)[3], creal (*w2)[3]) {
+  const int face[3] = {epa_face & 0x3FF, (epa_face >> 10) & 0x3FF, (epa_face >> 20) & 0x3FF};
+  int fi1[3], fi2[3];
+  creal fv1[3][3], fv2[3][3], dir[3], dirn[3];
+  int nface1 = ccd_feature_dim(face, pt, 0, fi1, fv1), nface2 = ccd_feature_dim(face, pt, 1, fi2, fv2);
+  ccd_sub(dir, w2[0], w1[0]);
+  dirn[0] = -dir[0]; dirn[1] = -dir[1]; dirn[2] = -dir[2];
+  int nn1 = ccd_box_normals(nface1, fi1, g1->rot, dirn, mc->n1, mc->idx1);
+  int nn2 = ccd_box_normals(nface2, fi2, g2->rot, dir, mc->n2, mc->idx2);
+  int edge1 = 0, edge2 = 0, ri = 0, rj = 0, found = 0;
+  for (int i = 0; i < nn1 && !found; i++) /* :1404 _aligned_faces */
+    for (int j = 0; j < nn2; j++)
+      if (ccd_dot(mc->n1[i], mc->n2[j]) < -CCD_FACE_TOL) { ri = i; rj = j; found = 1; break; }
+  if (!found) {
+    if (nface1 < 3 && nface1 <= nface2) { /* edge (or vertex) of geom 1 against a face of geom 2 */
+      nn1 = ccd_box_edge_normals(nface1, g1, fv1[0], fv1[1], fi1[0], mc->n1, mc->endvert);
+      for (int i = 0; i < nn2 && !found; i++) /* :1418 _aligned_face_edge(edge = n1, face = n2) */
+        for (int j = 0; j < nn1; j++)
+          if (CCD_FABS(ccd_dot(mc->n1[j], mc->n2[i])) < CCD_EDGE_TOL) { ri = j; rj = i; found = 1; break; }
+      if (!found) return 1;
+      edge1 = 1;
+    } else if (nface2 < 3) { /* face of geom 1 against an edge of geom 2 */
+      nn2 = ccd_box_edge_normals(nface2, g2, fv2[0], fv2[1], fi2[0], mc->n2, mc->endvert);
+      for (int i = 0; i < nn1 && !found; i++)
+        for (int j = 0; j < nn2; j++)
+          if (CCD_FABS(ccd_dot(mc->n2[j], mc->n1[i])) < CCD_EDGE_TOL) { ri = j; rj = i; found = 1; break; }
+      if (!found) return 1;
+      edge2 = 1;
+    } else {
+      return 1;
+    }
+  }
+  const int i = ri, j = rj;
+  if (edge1) { /* :1913 _set_edge */
+    ccd_copy(mc->face1[0], pt->vert[2 * face[0]]);
+    ccd_copy(mc->face1[1], mc->endvert[i]);
+    nface1 = 2;
+  } else {
+    nface1 = ccd_box_face(g1, edge2 ? mc->idx1[j] : mc->idx1[i], mc->face1);
+  }
+  if (edge2) {
+    ccd_copy(mc->face2[0], pt->vert[2 * face[0] + 1]);
+    ccd_copy(mc->face2[1], mc->endvert[i]);
+    nface2 = 2;
+  } else {
+    nface2 = ccd_box_face(g2, mc->idx2[j], mc->face2);
+  }
+  const creal nd = ccd_norm(dir);
+  creal approx[3];
+  if (edge1) {
+    for (int k = 0; k < 3; k++) approx[k] = nd * mc->n2[j][k];
+    return ccd_polygon_clip(mc, mc->face2, nface2, mc->face1, nface1, mc->n2[j], approx, w1, w2);
+  }
+  if (edge2) {
+    for (int k = 0; k < 3; k++) approx[k] = -nd * mc->n1[j][k];
+    return ccd_polygon_clip(mc, mc->face1, nface1, mc->face2, nface2, mc->n1[j], approx, w1, w2);
+  }
+  for (int k = 0; k < 3; k++) approx[k] = nd * mc->n2[j][k];
+  return ccd_polygon_clip(mc, mc->face1, nface1, mc->face2, nface2, mc->n1[i], approx, w1, w2);
 }
 
 #endif /* MJB_CCD_CORE_H_ */

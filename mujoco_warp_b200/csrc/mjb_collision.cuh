@@ -63,7 +63,10 @@ __device__ __forceinline__ bool is_convex_pair(int t1, int t2) {
   if (t1 == GEOM_CYLINDER) return t2 == GEOM_CYLINDER || t2 == GEOM_BOX;
   return false;
 }
-__device__ __forceinline__ bool is_ccd_pair(int t1, int t2) { return (t2 == GEOM_MESH && t1 >= GEOM_SPHERE) || is_convex_pair(t1, t2); }
+// nativeccd: box-box goes through GJK / EPA + multi-contact unless DisableBit.NATIVECCD (collision_driver.py:74, :736)
+__device__ __forceinline__ bool is_ccd_pair(int t1, int t2, bool nativeccd = false) {
+  return (t2 == GEOM_MESH && t1 >= GEOM_SPHERE) || is_convex_pair(t1, t2) || (nativeccd && t1 == GEOM_BOX && t2 == GEOM_BOX);
+}
 
 // collision_convex.py:712 eval_ccd_write_contact for one pair (single contact, no collision sensor): returns the number of
 // contacts (0 / 1); dist is the surface distance, pos the midpoint of the witness points, nrm = x1 - x2 (unnormalised).
@@ -89,11 +92,27 @@ static __device__ __noinline__ int c_ccd_pair(const float* p1, const float* r1, 
   g2.vert = v2; g2.nvert = nv2; g2.graph = gr2;
   if (iterations > CCD_MAX_ITER) iterations = CCD_MAX_ITER;
   float d, x1[3], x2[3];
-  const int nc = ccd_run(tolerance, 0.f, iterations, iterations, g1, g2, &pt, &res, &d, x1, x2);
+  int face_idx = -1;
+  const int nc = ccd_run(tolerance, 0.f, iterations, iterations, g1, g2, &pt, &res, &d, x1, x2, &face_idx);
   if (nc == 0 || d >= 0.f) return 0;
+#pragma unroll
+  for (int i = 0; i < 3; i++) nrm[i] = x1[i] - x2[i];
+  if (t1 == GEOM_BOX && t2 == GEOM_BOX && face_idx > -1) {  // collision_convex.py:809-846: up to 4 contacts by face clipping
+    CcdMulti mc;
+    float w1[4][3], w2[4][3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) { w1[0][i] = x1[i]; w2[0][i] = x2[i]; }
+    const int n = ccd_multicontact_box(&mc, &pt, pt.face[face_idx], &g1, &g2, w1, w2);
+    for (int k = 0; k < n; k++) {
+      dist[k] = d + margin;
+      for (int i = 0; i < 3; i++) pos[3 * k + i] = 0.5f * (w1[k][i] + w2[k][i]);
+    }
+    for (int i = 0; i < 3; i++) nrm[i] = w1[0][i] - w2[0][i];
+    return n;
+  }
   *dist = d + margin;
 #pragma unroll
-  for (int i = 0; i < 3; i++) { pos[i] = 0.5f * (x1[i] + x2[i]); nrm[i] = x1[i] - x2[i]; }
+  for (int i = 0; i < 3; i++) pos[i] = 0.5f * (x1[i] + x2[i]);
   return 1;
 }
 
@@ -919,7 +938,8 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
     g.s2 = ld3(MR(geom_size) + 3 * g2);
     contact_params(K, mb, g1, g2, pid0, cp);
     ncand = pair_ncand(g.t1, g.t2);
-    if ((FEAT & COLF_BOX) && g.t1 == GEOM_BOX && g.t2 == GEOM_BOX) {  // all (<= 8) contacts of the pair in one evaluation
+    const bool nativeccd = (FEAT & COLF_CONVEX) && !(K.o.disableflags & DSBL_NATIVECCD);
+    if ((FEAT & COLF_BOX) && g.t1 == GEOM_BOX && g.t2 == GEOM_BOX && !nativeccd) {  // all (<= 8) contacts of the pair in one evaluation
       const float pa[3] = {g.p1.x, g.p1.y, g.p1.z}, pb[3] = {g.p2.x, g.p2.y, g.p2.z};
       const float sa[3] = {g.s1.x, g.s1.y, g.s1.z}, sb[3] = {g.s2.x, g.s2.y, g.s2.z};
       nbb = c_box_box(pa, DW(geom_xmat) + 9 * g1, sa, pb, r2, sb, cp.margin, bdist, bpos, bnrm);
@@ -927,7 +947,7 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
     }
     if ((FEAT & COLF_CONVEX) && g.t2 == GEOM_MESH && is_ccd_pair(g.t1, g.t2)) {
       mesh_ccd = true;  // evaluated below by the whole warp, one pair at a time
-    } else if ((FEAT & COLF_CONVEX) && is_ccd_pair(g.t1, g.t2)) {  // GJK / EPA once per pair; the two passes below read the result
+    } else if ((FEAT & COLF_CONVEX) && is_ccd_pair(g.t1, g.t2, nativeccd)) {  // GJK / EPA once per pair; the two passes below read the result
       const float pa[3] = {g.p1.x, g.p1.y, g.p1.z}, pb[3] = {g.p2.x, g.p2.y, g.p2.z};
       const float sa[3] = {g.s1.x, g.s1.y, g.s1.z}, sb[3] = {g.s2.x, g.s2.y, g.s2.z};
       const float *v1 = nullptr, *v2 = nullptr;

@@ -229,6 +229,15 @@ def host_model(mjm) -> SimpleNamespace:
   lookup[include] = np.arange(nxn, dtype=i32)
   ints["nxn_lookup"] = lookup
 
+  # box-box runs GJK / EPA + multi-contact unless DisableBit.NATIVECCD; multi-contact does not support margins (reference io.py:372-403)
+  if not (int(mjm.opt.disableflags) & C.DisableBit.NATIVECCD):
+    gt_, gm_ = ints["geom_type"], reals["geom_margin"]
+    for (ga, gb), (pid, _) in zip(ints["nxn_pair"], ints["nxn_pairid"]):
+      if int(gt_[ga]) == C.GeomType.BOX and int(gt_[gb]) == C.GeomType.BOX:
+        margin = float(reals["pair_margin"][pid]) if pid >= 0 else max(float(gm_[ga]), float(gm_[gb]))
+        if margin:
+          raise NotImplementedError(f"geom pair ({ga}, {gb}) has non-zero margin with NATIVECCD enabled. Set margin to 0 or disable NATIVECCD.")
+
   # Two-level broadphase for large pair lists (aloha_pot: 9154 filtered pairs, of which a handful are ever close): geoms are grouped
   # (all geoms of a moving body; every world geom alone), each group gets a bounding sphere in its body's frame that contains the
   # members' bounding spheres with their margins, and the pair list is sorted by group pair.  The collision kernel tests the

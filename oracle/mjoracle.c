@@ -43,7 +43,7 @@ enum { JNT_FREE = 0, JNT_BALL = 1, JNT_SLIDE = 2, JNT_HINGE = 3 };
 enum { GEOM_PLANE = 0, GEOM_HFIELD, GEOM_SPHERE, GEOM_CAPSULE, GEOM_ELLIPSOID, GEOM_CYLINDER, GEOM_BOX, GEOM_MESH };
 enum { DSBL_CONSTRAINT = 1, DSBL_EQUALITY = 2, DSBL_FRICTIONLOSS = 4, DSBL_LIMIT = 8, DSBL_CONTACT = 16,
        DSBL_SPRING = 32, DSBL_DAMPER = 64, DSBL_GRAVITY = 128, DSBL_CLAMPCTRL = 256, DSBL_WARMSTART = 512,
-       DSBL_ACTUATION = 2048, DSBL_REFSAFE = 4096, DSBL_EULERDAMP = 32768 };
+       DSBL_ACTUATION = 2048, DSBL_REFSAFE = 4096, DSBL_EULERDAMP = 32768, DSBL_NATIVECCD = 131072 };
 enum { ENBL_ENERGY = 2 };
 enum { OBJ_BODY = 1, OBJ_SITE = 6 }; /* mjtObj values of eq_objtype */ /* types.py EnableBit.ENERGY */
 enum { CT_EQUALITY = 0, CT_FRICTION_DOF = 1, CT_LIMIT_JOINT = 3, CT_CONTACT_FRICTIONLESS = 5,
@@ -947,7 +947,7 @@ static void c_capsule_box(const real* cp, const real* caxis, real r, real hl, co
  * (collision_primitive.py wrappers :280-1280 + cores).  Candidates with dist >= margin are
  * dropped by the caller (collision_core.py:199-203). */
 /* collision_driver.py:43 MJ_COLLISION_TABLE: pair types routed to the convex (GJK / EPA) narrowphase.  box-box stays on the
- * primitive here whatever DisableBit.NATIVECCD says (the reference's default sends it to ccd + multicontact, :74, :736). */
+ * primitive only under DisableBit.NATIVECCD (the reference's default sends it to ccd + multicontact, :74, :736; see narrowphase_pair). */
 static int is_convex_pair(int t1, int t2) {
   if (t1 == GEOM_SPHERE || t1 == GEOM_CAPSULE) return t2 == GEOM_ELLIPSOID || (t1 == GEOM_CAPSULE && t2 == GEOM_CYLINDER);
   if (t1 == GEOM_ELLIPSOID) return t2 == GEOM_ELLIPSOID || t2 == GEOM_CYLINDER || t2 == GEOM_BOX;
@@ -971,22 +971,35 @@ static int ccd_pair(const real* p1, const real* r1, const real* s1, int t1, cons
   g1.margin = g2.margin = margin; g1.type = t1; g2.type = t2;
   if (iterations > CCD_MAX_ITER) iterations = CCD_MAX_ITER;
   real dist, x1[3], x2[3], n[3];
-  int nc = ccd_run(tolerance, 0.0, iterations, iterations, g1, g2, &pt, &res, &dist, x1, x2);
-  out[0].id = 0;
-  if (nc == 0 || dist >= 0.0) { out[0].dist = MJ_MAXVAL; memset(out[0].pos, 0, sizeof(out[0].pos)); memset(out[0].frame, 0, sizeof(out[0].frame)); return 1; }
-  out[0].dist = dist + margin;
-  for (int i = 0; i < 3; i++) { out[0].pos[i] = 0.5 * (x1[i] + x2[i]); n[i] = x1[i] - x2[i]; }
-  make_frame(out[0].frame, n);
-  return 1;
+  int face_idx = -1;
+  int nc = ccd_run(tolerance, 0.0, iterations, iterations, g1, g2, &pt, &res, &dist, x1, x2, &face_idx);
+  const int ncand = (t1 == GEOM_BOX && t2 == GEOM_BOX) ? 4 : 1; /* box-box: up to 4 contacts by face clipping (collision_gjk.py:1930) */
+  for (int k = 0; k < ncand; k++) { out[k].id = k; out[k].dist = MJ_MAXVAL; memset(out[k].pos, 0, sizeof(out[k].pos)); memset(out[k].frame, 0, sizeof(out[k].frame)); }
+  if (nc == 0 || dist >= 0.0) return ncand;
+  real w1[4][3], w2[4][3];
+  memcpy(w1[0], x1, sizeof(x1)); memcpy(w2[0], x2, sizeof(x2));
+  int ncon = 1;
+  if (ncand == 4 && face_idx > -1) { /* collision_convex.py:809-846 */
+    static _Thread_local CcdMulti mc;
+    ncon = ccd_multicontact_box(&mc, &pt, pt.face[face_idx], &g1, &g2, w1, w2);
+  }
+  for (int i = 0; i < 3; i++) n[i] = w1[0][i] - w2[0][i];
+  for (int k = 0; k < ncon; k++) {
+    out[k].dist = dist + margin;
+    for (int i = 0; i < 3; i++) out[k].pos[i] = 0.5 * (w1[k][i] + w2[k][i]);
+    make_frame(out[k].frame, n);
+  }
+  return ncand;
 }
 
 static int narrowphase_pair(const OModel* m, const OData* d, int g1, int g2, real margin, real ccd_tolerance, int ccd_iterations,
-                            OContactGeom* out) {
+                            int nativeccd, OContactGeom* out) {
   int t1 = m->geom_type[g1], t2 = m->geom_type[g2];
   const real *p1 = d->geom_xpos + 3 * g1, *p2 = d->geom_xpos + 3 * g2, *r1 = d->geom_xmat + 9 * g1, *r2 = d->geom_xmat + 9 * g2;
   const real *s1 = m->geom_size + 3 * g1, *s2 = m->geom_size + 3 * g2;
   real n1[3] = {r1[2], r1[5], r1[8]}, n2[3] = {r2[2], r2[5], r2[8]};
-  if (is_convex_pair_mesh(t1, t2)) {
+  /* collision_driver.py:74, :736: box-box goes through ccd + multicontact unless DisableBit.NATIVECCD */
+  if (is_convex_pair_mesh(t1, t2) || (nativeccd && t1 == GEOM_BOX && t2 == GEOM_BOX)) {
     const real *v1 = 0, *v2 = 0;
     const int *gr1 = 0, *gr2 = 0;
     int nv1 = 0, nv2 = 0;
@@ -1381,7 +1394,7 @@ static int o_collision(const OModel* m, const OOpt* o, OData* d, const OData* gl
     int condim;
     contact_params(m, g1, g2, pid0, &margin, &gap, &condim, fr, sr, srf, si);
     OContactGeom cg[8];
-    int n = narrowphase_pair(m, d, g1, g2, margin, o->ccd_tolerance, o->ccd_iterations, cg);
+    int n = narrowphase_pair(m, d, g1, g2, margin, o->ccd_tolerance, o->ccd_iterations, !(o->disableflags & DSBL_NATIVECCD), cg);
     if (n < 0) { unsupported = 1; continue; }
     for (int k = 0; k < n; k++) { /* write_contact, collision_core.py:160-232 */
       int active = cg[k].dist < margin;
@@ -2582,7 +2595,7 @@ int mjo_narrowphase_pair(int t1, int t2, const double* p1, const double* r1, con
   d.geom_xpos = xpos; d.geom_xmat = xmat;
   OContactGeom out[8];
   memset(out, 0, sizeof(out));
-  int n = narrowphase_pair(&m, &d, 0, 1, margin, 1e-6, 35, out);
+  int n = narrowphase_pair(&m, &d, 0, 1, margin, 1e-6, 35, 0, out);
   for (int k = 0; k < n && k < 8; k++) {
     dist[k] = out[k].dist;
     memcpy(pos + 3 * k, out[k].pos, 3 * sizeof(real));
@@ -2612,7 +2625,8 @@ int mjo_ccd_mesh(int t1, int t2, const double* p1, const double* r1, const doubl
   g1.vert = v1; g1.nvert = nv1; g2.vert = v2; g2.nvert = nv2;
   g1.graph = g2.graph = 0;
   x1[0] = x1[1] = x1[2] = x2[0] = x2[1] = x2[2] = 0.0;
-  return ccd_run(tolerance, cutoff, iterations, iterations, g1, g2, &pt, &res, dist, x1, x2);
+  int face_idx;
+  return ccd_run(tolerance, cutoff, iterations, iterations, g1, g2, &pt, &res, dist, x1, x2, &face_idx);
 #undef pt
 }
 int mjo_ccd(int t1, int t2, const double* p1, const double* r1, const double* s1, const double* p2, const double* r2, const double* s2,

@@ -26,7 +26,8 @@ int ccd32(int t1, int t2, const double* p1, const double* r1, const double* s1, 
   g1.margin = g2.margin = (float)margin; g1.type = t1; g2.type = t2;
   g1.vert = fv1; g1.nvert = nv1; g2.vert = fv2; g2.nvert = nv2;
   g1.graph = g2.graph = 0;
-  int n = ccd_run((float)tolerance, (float)cutoff, iterations, iterations, g1, g2, &pt, &res, &d, a, b);
+  int face_idx;
+  int n = ccd_run((float)tolerance, (float)cutoff, iterations, iterations, g1, g2, &pt, &res, &d, a, b, &face_idx);
   *dist = d;
   for (int i = 0; i < 3; i++) { x1[i] = a[i]; x2[i] = b[i]; }
   return n;

@@ -34,6 +34,66 @@ KERNEL_MODULES = (
 _ref = None
 
 
+class _KernelBoolOps(__import__("ast").NodeTransformer):
+  """Inside @wp.func / @wp.kernel bodies, `a and b` / `a or b` yield a bool in Warp (the operands are converted), whereas Python
+  returns one of the operands: `float((v1 & 4) and (v2 & 4))` is 1.0 in Warp and 4.0 in Python (collision_gjk.py:1630-1650 relies on
+  it).  Wraps the operands of boolean operators in bool() -- only inside device functions; host code keeps Python semantics
+  (`qvel or d.qvel`)."""
+
+  def __init__(self):
+    self.depth = 0
+
+  @staticmethod
+  def _is_device(node):
+    import ast
+
+    for d in node.decorator_list:
+      f = d.func if isinstance(d, ast.Call) else d
+      if isinstance(f, ast.Attribute) and isinstance(f.value, ast.Name) and f.value.id == "wp" and f.attr in ("func", "kernel"):
+        return True
+    return False
+
+  def visit_FunctionDef(self, node):
+    dev = self._is_device(node)
+    self.depth += dev
+    self.generic_visit(node)
+    self.depth -= dev
+    return node
+
+  def visit_BoolOp(self, node):
+    import ast
+
+    self.generic_visit(node)
+    if self.depth > 0:
+      node.values = [ast.Call(func=ast.Name(id="bool", ctx=ast.Load()), args=[v], keywords=[]) for v in node.values]
+    return node
+
+
+def _install_source_transform():
+  """Import hook: modules of the reference package are compiled from their (unmodified) source files through _KernelBoolOps."""
+  import ast
+  import importlib.abc
+  import importlib.machinery
+
+  class Loader(importlib.machinery.SourceFileLoader):
+    def source_to_code(self, data, path, *, _optimize=-1):
+      tree = ast.parse(data, filename=path)
+      tree = ast.fix_missing_locations(_KernelBoolOps().visit(tree))
+      return compile(tree, path, "exec", dont_inherit=True, optimize=_optimize)
+
+  class Finder(importlib.abc.MetaPathFinder):
+    def find_spec(self, name, path, target=None):
+      if not (name == "mujoco_warp" or name.startswith("mujoco_warp.")):
+        return None
+      spec = importlib.machinery.PathFinder.find_spec(name, path)
+      if spec is not None and isinstance(spec.loader, importlib.machinery.SourceFileLoader):
+        spec.loader = Loader(spec.loader.name, spec.loader.path)
+      return spec
+
+  if not any(type(f).__name__ == "Finder" and f.__module__ == __name__ for f in sys.meta_path):
+    sys.meta_path.insert(0, Finder())
+
+
 def load_reference():
   """Imports /root/reference/mujoco_warp under the interpreter; returns (wp, mujoco_warp module)."""
   global _ref
@@ -42,6 +102,7 @@ def load_reference():
   wp = warp_interp.install()
   mujoco_stub.install()
   sys.dont_write_bytecode = True
+  _install_source_transform()
   if REFERENCE not in sys.path:
     sys.path.insert(0, REFERENCE)
   import importlib

@@ -70,6 +70,70 @@ def _box_pair_states(mjm, nworld, seed):
   return qpos, np.zeros((nworld, mjm.nv)), np.zeros((nworld, mjm.nu))
 
 
+def _box_stack_states(mjm, nworld, seed):
+  """Box pairs in face-face, edge-face and corner contact with small penetrations: boxes laid on top of / beside box 0 with yaw
+  (flat faces: 4 clipped contacts), tilted about an edge (2 contacts) or standing on a corner (1 contact), plus a random world."""
+  rng = np.random.default_rng(seed)
+  qpos = np.zeros((nworld, mjm.nq))
+  sizes = np.asarray(mjm.geom_size)[1:]  # the plane is geom 0
+
+  def quat(axis, ang):
+    axis = np.asarray(axis, dtype=float) / np.linalg.norm(axis)
+    return np.concatenate(([np.cos(ang / 2)], np.sin(ang / 2) * axis))
+
+  def qmul(a, b):
+    return np.array([a[0]*b[0]-a[1]*b[1]-a[2]*b[2]-a[3]*b[3], a[0]*b[1]+a[1]*b[0]+a[2]*b[3]-a[3]*b[2],
+                     a[0]*b[2]-a[1]*b[3]+a[2]*b[0]+a[3]*b[1], a[0]*b[3]+a[1]*b[2]-a[2]*b[1]+a[3]*b[0]])  # fmt: skip
+
+  for w in range(nworld):
+    far = np.array([[0, 0, 0], [3, 0, 0], [0, 3, 0], [3, 3, 0], [6, 3, 0]], dtype=float)
+    q = np.tile([1.0, 0, 0, 0], (5, 1))
+    pos = far.copy()
+    q[0] = quat([0.3, -0.2, 1.0], 0.2 * w)  # the base box, slightly rotated
+    kind = w % 4
+    pen = 0.004 + 0.003 * rng.uniform()
+    for b in (1, 2):
+      s = sizes[b]
+      yaw = quat([0, 0, 1], rng.uniform(0.2, 1.2))
+      off = np.array([rng.uniform(-0.1, 0.1), rng.uniform(-0.1, 0.1), 0.0])
+      if kind == 0 or (kind == 3 and b == 1):  # flat on top of box 0 (b = 1) / flat below it (b = 2)
+        sign = 1.0 if b == 1 else -1.0
+        local_q, h = yaw, s[2]
+      elif kind == 1:  # tilted about an edge: the lower edge touches the top face
+        tilt = quat([1, 0, 0], 0.5)
+        local_q, h = qmul(yaw, tilt), abs(np.cos(0.5)) * s[2] + abs(np.sin(0.5)) * s[1]
+        sign = 1.0 if b == 1 else -1.0
+      else:  # standing on a corner
+        tilt = qmul(quat([1, 0, 0], 0.6), quat([0, 1, 0], 0.5))
+        local_q = qmul(yaw, tilt)
+        Rl = _quat_to_mat(local_q)
+        h = float(np.abs(Rl[2] * s).sum())
+        sign = 1.0 if b == 1 else -1.0
+      if sign < 0:
+        local_q = qmul(quat([1, 0, 0], np.pi), local_q)
+      local_p = off + np.array([0, 0, sign * (sizes[0][2] + h - pen)])
+      R0m = _quat_to_mat(q[0])
+      pos[b] = R0m @ local_p
+      q[b] = qmul(q[0], local_q)
+    if kind == 3:  # boxes 3 and 4 in a random overlapping pose
+      pos[3] = [3, 3, 0]
+      pos[4] = pos[3] + rng.uniform(-0.12, 0.12, 3)
+      for b in (3, 4):
+        v = rng.normal(size=4)
+        q[b] = v / np.linalg.norm(v)
+    for b in range(5):
+      qpos[w, 7 * b : 7 * b + 3] = pos[b]
+      qpos[w, 7 * b + 3 : 7 * b + 7] = q[b] / np.linalg.norm(q[b])
+  return qpos, np.zeros((nworld, mjm.nv)), np.zeros((nworld, mjm.nu))
+
+
+def _quat_to_mat(q):
+  w, x, y, z = q / np.linalg.norm(q)
+  return np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)],
+                   [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                   [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]])  # fmt: skip
+
+
 def _aloha_states(mjm, nworld, seed):
   """Keyframe lift_pot0 / lift_pot4 (arms at the pot; the keyframes hold an all-zero pot quaternion, which MuJoCo's
   mj_kinematics turns into the identity for the reference's put_data; here a slightly tilted one) plus small joint noise."""
@@ -171,6 +235,8 @@ CASES = {
   # only accepts with NATIVECCD disabled (io.py:386-395): box-box then runs the box_box primitive.
   "apollo_forward": dict(model="apollo", nworld=4, seed=31, sink=0.04, mode="forward", nconmax=16, njmax=96, states="humanoid", disable=["NATIVECCD"]),
   "apollo_step3": dict(model="apollo", nworld=3, seed=32, sink=0.03, mode="step", nstep=3, nconmax=16, njmax=64, states="humanoid", disable=["NATIVECCD"]),
+  # box-box on the reference's DEFAULT route: GJK / EPA + multi-contact face clipping (flat faces 4 contacts, edge 2, corner 1)
+  "box_stack_multicontact": dict(model="box_stack", nworld=12, seed=6, mode="forward", nconmax=32, njmax=160, states="box_stack"),
   "convex_pairs_collision": dict(model="convex_pairs", nworld=12, seed=4, mode="forward", nconmax=48, njmax=200, states="box_pairs"),
   "mesh_pairs_collision": dict(model="mesh_pairs", nworld=12, seed=9, mode="forward", nconmax=48, njmax=200, states="box_pairs"),
 }
@@ -188,13 +254,20 @@ def load_model(key):
   return mjw.load_mjcf_string(TM.XML[key])
 
 
-def case_inputs(name):
-  c = CASES[name]
-  mjm = load_model(c["model"])
+def load_case_model(name):
+  """The case's host model with its disable flags set on the model itself: put_model validates against them (io.py:373)."""
   from mujoco_warp_b200 import constants as C
 
-  for flag in c.get("disable", []):  # on the host model too: the reference's put_model validates against them (io.py:373)
+  c = CASES[name]
+  mjm = load_model(c["model"])
+  for flag in c.get("disable", []):
     mjm.opt.disableflags |= int(getattr(C.DisableBit, flag))
+  return mjm
+
+
+def case_inputs(name):
+  c = CASES[name]
+  mjm = load_case_model(name)
   kind = c.get("states", "humanoid" if c["model"] == "humanoid" else "small")
   if kind == "humanoid":
     qpos, qvel, ctrl = _states(mjm, c["nworld"], c["seed"], c.get("sink", 0.0))
@@ -206,6 +279,8 @@ def case_inputs(name):
     qpos, qvel, ctrl = _aloha_replay_states(mjm, c["nworld"], c["seed"])
   elif kind == "box_pairs":
     qpos, qvel, ctrl = _box_pair_states(mjm, c["nworld"], c["seed"])
+  elif kind == "box_stack":
+    qpos, qvel, ctrl = _box_stack_states(mjm, c["nworld"], c["seed"])
   else:
     qpos, qvel, ctrl = _small_states(mjm, c["nworld"], c["seed"])
   return mjm, qpos, qvel, ctrl

@@ -146,6 +146,20 @@ BOX_PAIRS_XML = """
   </worldbody>
 </mujoco>"""
 
+# zero-margin boxes: box-box through GJK / EPA + multi-contact face clipping, the reference's default route (collision_driver.py:74,
+# :736, collision_gjk.py:1930); five free boxes of different proportions
+BOX_STACK_XML = """
+<mujoco>
+  <worldbody>
+    <geom type="plane" size="5 5 .01" pos="0 0 -1"/>
+    <body pos="0 0 0"><freejoint/><geom type="box" size=".3 .3 .1"/></body>
+    <body pos="1 0 0"><freejoint/><geom type="box" size=".15 .2 .1"/></body>
+    <body pos="0 1 0"><freejoint/><geom type="box" size=".1 .1 .25"/></body>
+    <body pos="1 1 0"><freejoint/><geom type="box" size=".2 .05 .15"/></body>
+    <body pos="2 1 0"><freejoint/><geom type="box" size=".12 .12 .12"/></body>
+  </worldbody>
+</mujoco>"""
+
 # every pair type of the convex (GJK / EPA) narrowphase plus the ellipsoid / cylinder primitives (collision_driver.py:43)
 CONVEX_PAIRS_XML = """
 <mujoco>
@@ -179,4 +193,4 @@ MESH_PAIRS_XML = """
   </worldbody>
 </mujoco>"""
 
-XML = dict(SMALL_MODELS, box_pairs=BOX_PAIRS_XML, convex_pairs=CONVEX_PAIRS_XML, mesh_pairs=MESH_PAIRS_XML)
+XML = dict(SMALL_MODELS, box_pairs=BOX_PAIRS_XML, box_stack=BOX_STACK_XML, convex_pairs=CONVEX_PAIRS_XML, mesh_pairs=MESH_PAIRS_XML)

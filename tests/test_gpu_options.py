@@ -315,6 +315,7 @@ def test_sphere_box_capsule_box_and_box_box_contacts():
   from oracle import oracle as O
 
   mjm = mjw.load_mjcf_string(BOX_PAIRS_XML)
+  mjm.opt.disableflags |= int(C.DisableBit.NATIVECCD)  # the box_box primitive is the NATIVECCD-disabled route; margins need it too (io.py:386)
   rng = np.random.default_rng(3)
   nw = 512
   qpos = np.zeros((nw, 35))

@@ -24,7 +24,7 @@ def test_oracle_matches_reference_execution(name):
   c = RC.CASES[name]
   g = RC.load_golden(name)
   assert g, f"case {name} missing from reference_step.npz: run tests/golden/make_reference_golden.py"
-  mjm = RC.load_model(c["model"])
+  mjm = RC.load_case_model(name)
   np.testing.assert_array_equal(RC.case_inputs(name)[1], g["in_qpos"])  # the fixture's inputs are the seeded ones
   om, od = H.oracle_data(mjm, g["in_qpos"], g["in_qvel"], g["in_ctrl"], c.get("nconmax", 24), c.get("njmax", 64))
   traj = []

@@ -32,6 +32,8 @@ def main():
   nworld, nconmax, njmax = (args + [nworld, nconmax, njmax][len(args):])[:3] if len(args) < 3 else args[:3]
   nstep = args[3] if len(args) > 3 else 200
   mjm = mjw.load_mjcf(os.path.join(ROOT, path))
+  if name == "apollo":  # box-box margins: the reference accepts the scene only with NATIVECCD disabled (io.py:386-395)
+    mjm.opt.disableflags |= int(mjw.DisableBit.NATIVECCD)
   m = mjw.put_model(mjm)
   traj = None
   if name in REPLAY:  # testspeed.py:277-282: state of the first matching keyframe, controls replayed along the keyframe sequence
