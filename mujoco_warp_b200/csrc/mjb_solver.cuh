@@ -285,6 +285,86 @@ __device__ __forceinline__ void h_accumulate(const KParams& K, int w, int lane, 
   __syncwarp();
 }
 
+// The same update on the tensor cores: H(lower) += A B with A[m][k] = coef[k] J[k][m] (16 x 8 tiles) and B[k][n] = J[k][n] (8 x 8),
+// mma.sync m16n8k8 TF32 with the 3xTF32 split (a = a_hi + a_lo, products hi*hi + hi*lo + lo*hi, FP32 accumulate), which keeps the
+// result at FP32 accuracy (relative error ~2^-21; plain TF32 would be 2^-11).  One 16-row band of H at a time, its <= 8 column
+// tiles of the lower triangle accumulate in registers over the constraint rows, eight rows per step.  Fragment layout (PTX ISA,
+// m16n8k8 .tf32): g = lane / 4, t = lane % 4; a0..3 = A[g | g+8][t | t+4], b0..1 = B[t | t+4][g], c0..3 = C[g | g+8][2t | 2t+1].
+// Measured on B200 (humanoid, 8192 worlds, steady state, nefc ~ 46 x nv 27): the tensor-core version runs the solve kernel in
+// 260.8 us against 232.9 us for the FP32 FMA register tiles below (profiles/r2_tensor_core_experiment.md): at these sizes the
+// fragment gathers, the six conversions per operand pair of the 3xTF32 split and the dependent accumulator chain of mma.sync cost
+// more than the 2 x 46 x 28 x 28 / 2 FMAs they replace.  It stays in the source behind MJB_SOL_MMA = 1; the default is FMA.
+#ifndef MJB_SOL_MMA
+#define MJB_SOL_MMA 0
+#endif
+__device__ __forceinline__ void tf32_split(float x, uint32_t& hi, uint32_t& lo) {
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
+  const float r = x - __uint_as_float(hi);
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void h_accumulate_mma(const KParams& K, int w, int lane, const SolverScr& s, int nefc) {
+  const int nv = K.ms.nv, np = K.ms.nv_pad, ld = s.ld;
+  const float* J = DW(efc_J);
+  const int g = lane >> 2, t = lane & 3;
+  const int nmt = (nv + 15) >> 4, ntile = (nv + 7) >> 3;
+  MJB_ROLL
+  for (int mt = 0; mt < nmt; mt++) {
+    const int m0 = 16 * mt, nnt = min(2 * mt + 2, ntile);  // column tiles of this band that touch the lower triangle
+    float acc[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; i++) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.f;
+    const bool ra = m0 + g < np, rb = m0 + g + 8 < np;
+    MJB_ROLL
+    for (int k0 = 0; k0 < nefc; k0 += 8) {
+      const int ka = k0 + t, kb = k0 + t + 4;
+      const float ca = ka < nefc ? s.coef[ka] : 0.f, cb = kb < nefc ? s.coef[kb] : 0.f;
+      if (!__any_sync(FULL, ca != 0.f || cb != 0.f)) continue;  // warp-uniform: no row of this step changed state
+      const float* Ja = J + (size_t)min(ka, nefc - 1) * np;
+      const float* Jb = J + (size_t)min(kb, nefc - 1) * np;
+      uint32_t ah[4], al[4];
+      tf32_split(ra ? ca * Ja[m0 + g] : 0.f, ah[0], al[0]);
+      tf32_split(rb ? ca * Ja[m0 + g + 8] : 0.f, ah[1], al[1]);
+      tf32_split(ra ? cb * Jb[m0 + g] : 0.f, ah[2], al[2]);
+      tf32_split(rb ? cb * Jb[m0 + g + 8] : 0.f, ah[3], al[3]);
+#pragma unroll
+      for (int nt = 0; nt < 8; nt++) {
+        if (nt < nnt) {
+          const int n = 8 * nt + g;
+          uint32_t bh0, bl0, bh1, bl1;
+          tf32_split((n < np && ka < nefc) ? Ja[n] : 0.f, bh0, bl0);
+          tf32_split((n < np && kb < nefc) ? Jb[n] : 0.f, bh1, bl1);
+          mma_tf32(acc[nt], al, bh0, bh1);
+          mma_tf32(acc[nt], ah, bl0, bl1);
+          mma_tf32(acc[nt], ah, bh0, bh1);
+        }
+      }
+    }
+#pragma unroll
+    for (int nt = 0; nt < 8; nt++) {
+      if (nt < nnt) {
+        const int c = 8 * nt + 2 * t;
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const int r = m0 + g + 8 * h;
+          if (r < nv && c < np) {  // whole tiles: elements above the diagonal receive their (symmetric) values too
+            float2* p = reinterpret_cast<float2*>(s.H + r * ld + c);
+            float2 v = *p;
+            v.x += acc[nt][2 * h];
+            v.y += acc[nt][2 * h + 1];
+            *p = v;
+          }
+        }
+      }
+    }
+  }
+  __syncwarp();
+}
+
 // solver.py:2154-2219 _update_constraint.  Returns the cost; sets force/state (global), coef.
 template <bool ELL>
 __device__ __forceinline__ void update_constraint(const KParams& K, int w, int lane, const SolverScr& s, int nefc, int ne, int nf, bool first,
@@ -585,7 +665,11 @@ __device__ __forceinline__ bool solve_pass(const KParams& K, int w, int lane, co
   } else if (K.o.iterations <= 0) {
     return true;
   }
+#if MJB_SOL_MMA
+  if (newton && any_change) h_accumulate_mma(K, w, lane, s, st.nefc);
+#else
   if (newton && any_change) h_accumulate(K, w, lane, s, st.nefc);
+#endif
   // the cone part of the Hessian depends on Jaref: refactor whenever a cone is or was in the factor (solver.py:3205-3209)
   solve_direction<ELL>(K, w, lane, s, newton && (any_change || init || (ELL && (any_cone || st.had_cone))), any_cone, st.nefc);
   if (ELL) st.had_cone = any_cone;
