@@ -31,6 +31,7 @@
   X(ngeompair)  /* ngeom (ngeom - 1) / 2: entries of the upper-triangular pair table (SAP broadphase) */ \
   X(nmesh) X(nmeshvert) X(nmeshgraph) /* convex-hull vertex tables of mesh geoms (reference types.py Model.mesh_vert*) */ \
   X(neqconnect) X(neqweld) X(blob_hot_bytes) /* connect / weld equalities (reference io.py:445-448 eq_connect_adr, eq_wld_adr) */ \
+  X(nhfield) X(nhfielddata) /* height fields (reference types.py:1046-1050) */ \
   X(ngroup) X(ngrouppair) /* two-level broadphase of large pair lists: geom groups (a body; each world geom alone) and group pairs */
 
 /* ---- model int arrays ---------------------------------------------------------------------- */
@@ -52,6 +53,7 @@
   X(actuator_forcelimited) X(actuator_actlimited) X(actuator_actearly) \
   X(eq_type) X(eq_obj1id) X(eq_obj2id) X(eq_objtype) X(eq_jnt_adr) X(eq_connect_adr) X(eq_wld_adr) \
   X(geom_dataid) X(mesh_vertadr) X(mesh_vertnum) X(mesh_graphadr) X(mesh_graph) \
+  X(hfield_nrow) X(hfield_ncol) X(hfield_adr) \
   X(group_bodyid) /* body whose frame carries the group's bounding sphere */ \
   X(grouppair)    /* (group, group) of every group pair that owns filtered geom pairs; nxn_pair is sorted by group pair */ \
   X(grouppair_adr) /* ngrouppair + 1: range of nxn_pair rows of each group pair */ \
@@ -73,6 +75,8 @@
   X(actuator_forcerange) X(actuator_actrange) X(actuator_gear) \
   X(eq_solref) X(eq_solimp) X(eq_data) \
   X(mesh_vert) \
+  X(hfield_size) /* nhfield x 4: x, y, z_top, z_bottom */ \
+  X(hfield_data) /* nhfielddata: elevations in [0, 1], row major, rows along +y */ \
   X(group_sphere) /* ngroup x 4: centre (body frame) and radius of a sphere around the group's geoms, margins included */
 
 /* ---- options: re-read on every call (reference users mutate m.opt.* after put_model) -------- */

@@ -164,6 +164,7 @@ extern "C" int mjb_model_create(const int* sizes, int nsizes, const void* blob, 
       if (t2 == GEOM_BOX && t1 != GEOM_PLANE) m->col_feat |= COLF_BOX;  // sphere-box, capsule-box, box-box
       if (t1 == GEOM_BOX && t2 == GEOM_BOX) m->has_boxbox = 1;
       if (t1 == GEOM_ELLIPSOID || t1 == GEOM_CYLINDER || t1 == GEOM_MESH || t2 == GEOM_ELLIPSOID || t2 == GEOM_CYLINDER || t2 == GEOM_MESH) m->col_feat |= COLF_CONVEX;
+      if (t1 == GEOM_HFIELD) m->col_feat |= COLF_CONVEX;  // height fields run the per-prism GJK / EPA
     }
   }
   if (m->ms.ngrouppair > 0) m->col_feat |= COLF_SAP;  // the two-level broadphase lives in the variants that carry the sweep-and-prune workspace

@@ -27,6 +27,7 @@ typedef CCD_REAL creal;
 #endif
 #define CR(x) ((creal)(x))
 
+#define CCD_GEOM_HFIELD 1 /* one prism of a height field (collision_convex.py:158 ccd_hfield_kernel), in the field's frame */
 #define CCD_GEOM_SPHERE 2
 #define CCD_GEOM_CAPSULE 3
 #define CCD_GEOM_ELLIPSOID 4
@@ -48,6 +49,7 @@ typedef struct {
   const CCD_VERT_REAL* vert; /* mesh: hull vertices in the geom frame (the model's mesh_vert + 3 * mesh_vertadr), nvert of them */
   int nvert;
   const int* graph; /* mesh: MuJoCo-layout convex graph of the hull (mesh_graph + mesh_graphadr), or NULL: exhaustive support search */
+  creal prism[6][3]; /* CCD_GEOM_HFIELD: bottom triangle 0-2, top triangle 3-5 */
   int coop;         /* device build only: 1 = every lane of the warp runs THIS pair, mesh support = lane-parallel search (CCD_COOP_MESH_SUPPORT) */
 } CcdGeom;
 
@@ -101,6 +103,16 @@ CCD_FN_NOINLINE int ccd_support(const CcdGeom* g, const creal* dir, creal* point
     creal s = g->size[0] + CR(0.5) * g->margin;
     for (int i = 0; i < 3; i++) point[i] = g->pos[i] + s * dir[i];
     return -1;
+  }
+  if (g->type == CCD_GEOM_HFIELD) { /* :178-188: the prism vertex of largest projection; identity pose */
+    creal max_dist = CR(-1e30);
+    for (int i = 0; i < 6; i++) {
+      creal d = ccd_dot(g->prism[i], dir);
+      if (d > max_dist) { max_dist = d; ccd_copy(point, g->prism[i]); }
+    }
+    if (g->margin > CR(0.0))
+      for (int i = 0; i < 3; i++) point[i] += dir[i] * (CR(0.5) * g->margin);
+    return dir[2] < CR(0.0) ? -2 : -3;
   }
   creal ld[3], res[3] = {CR(0.0), CR(0.0), CR(0.0)};
   ccd_rot_t(ld, g->rot, dir);
@@ -327,6 +339,7 @@ CCD_FN_NOINLINE void ccd_gjk(CcdGjk* res, creal tolerance, int iterations, const
     res->index1[k] = res->index2[k] = 0;
     for (int i = 0; i < 3; i++) res->simplex[k][i] = res->simplex1[k][i] = res->simplex2[k][i] = CR(0.0);
   }
+  for (int i = 0; i < 3; i++) res->x1[i] = res->x2[i] = CR(0.0); /* a fresh GJKResult: early exits leave the witness points at zero */
   int cache1 = -1, cache2 = -1; /* geom.index: lives in gjk's by-value copies of the geoms (:602, :608) */
   ccd_sub(xk, x1_0, x2_0);
   for (int it = 0; it < iterations; it++) {
@@ -369,6 +382,13 @@ CCD_FN_NOINLINE void ccd_gjk(CcdGjk* res, creal tolerance, int iterations, const
   else { ccd_linear_combine(res->x1, n, coord, res->simplex1); ccd_linear_combine(res->x2, n, coord, res->simplex2); }
   res->dist = ccd_norm(xk);
   res->dim = n;
+#ifdef CCD_DEBUG_PRINT
+  if (g1->type == CCD_GEOM_HFIELD && g2->type == CCD_GEOM_MESH) {
+    CCD_DEBUG_PRINT("ORAGJK dim %d dist %.6f i1 [%d %d %d %d] i2 [%d %d %d %d] s2", n, (double)res->dist, res->index1[0], res->index1[1], res->index1[2], res->index1[3], res->index2[0], res->index2[1], res->index2[2], res->index2[3]);
+    for (int k = 0; k < 4; k++) CCD_DEBUG_PRINT(" [%.4f %.4f %.4f]", (double)res->simplex2[k][0], (double)res->simplex2[k][1], (double)res->simplex2[k][2]);
+    CCD_DEBUG_PRINT("\n");
+  }
+#endif
 }
 
 /* :689 */
@@ -556,6 +576,26 @@ CCD_FN int ccd_add_edge(CcdPolytope* pt, int e1, int e2) {
   return n + 1;
 }
 
+/* :886-921 and :2160-2185: witness points against the TOP triangle of a height-field prism when the simplex / face touches more than
+ * one of its sides.  x2 is the point found on geom 2; returns x1 on the prism and dist = -|x1 - x2|. */
+CCD_FN creal ccd_hfield_witness(const CcdGeom* g1, creal* x1, const creal* x2) {
+  const creal *a = g1->prism[3], *b = g1->prism[4], *c = g1->prism[5];
+  creal co[3];
+  ccd_tri_affine_coord(co, a, b, c, x2);
+  if (co[0] > CR(0.0) && co[1] > CR(0.0) && co[2] > CR(0.0)) {
+    for (int i = 0; i < 3; i++) x1[i] = co[0] * a[i] + co[1] * b[i] + co[2] * c[i];
+  } else {
+    const creal* p = c;
+    if (co[1] > CR(0.0)) p = b;
+    if (co[0] > CR(0.0)) p = a;
+    const creal h = x2[2] - p[2]; /* dot(x2 - p, n) with n = (0, 0, 1) */
+    x1[0] = x2[0]; x1[1] = x2[1]; x1[2] = x2[2] - h;
+  }
+  creal d[3];
+  ccd_sub(d, x1, x2);
+  return -ccd_norm(d);
+}
+
 /* :1202 _epa + :863 _epa_witness.  Returns the face index (-1: no contact) and dist / x1 / x2. */
 CCD_FN_NOINLINE int ccd_epa(creal tolerance, int iterations, CcdPolytope* pt, const CcdGeom* g1, const CcdGeom* g2, int is_discrete, creal* dist,
                    creal* x1, creal* x2) {
@@ -578,6 +618,13 @@ CCD_FN_NOINLINE int ccd_epa(creal tolerance, int iterations, CcdPolytope* pt, co
     creal upper_k = ccd_dot(dir, w);
     if (upper_k < upper) { upper = upper_k; upper2 = upper * upper; }
     if (upper - lower < epsilon) break;
+#ifdef CCD_DEBUG_PRINT
+    if (g1->type == CCD_GEOM_HFIELD && g2->type == CCD_GEOM_MESH) {
+      CCD_DEBUG_PRINT("  EPA it %d idx %d wi %d disc %d idx(wi) %d %d prev:", it, idx, wi, is_discrete, pt->vert_index[2 * wi], pt->vert_index[2 * wi + 1]);
+      for (int i = 0; i < wi; i++) CCD_DEBUG_PRINT(" (%d %d)", pt->vert_index[2 * i], pt->vert_index[2 * i + 1]);
+      CCD_DEBUG_PRINT(" upper-lower %.3e\n", (double)(upper - lower));
+    }
+#endif
     if (is_discrete) {
       int found = 0;
       for (int i = 0; i < pt->nvert - 1; i++)
@@ -628,6 +675,31 @@ CCD_FN_NOINLINE int ccd_epa(creal tolerance, int iterations, CcdPolytope* pt, co
       x1[i] = pt->vert[2 * f0][i] * l[0] + pt->vert[2 * f1][i] * l[1] + pt->vert[2 * f2][i] * l[2];
     }
     *dist = -CCD_SQRT(pt->face_norm2[idx]);
+    {
+      const int i1 = pt->vert_index[2 * f0], i2 = pt->vert_index[2 * f1], i3 = pt->vert_index[2 * f2];
+#ifdef CCD_DEBUG_PRINT
+      if (g1->type == CCD_GEOM_HFIELD && g2->type == CCD_GEOM_MESH) CCD_DEBUG_PRINT("ORAWIT face_idx %d face (%d %d %d) i [%d %d %d] nvert %d nface %d dist %.6f\n", idx, f0, f1, f2, i1, i2, i3, pt->nvert, pt->nface, (double)*dist);
+#endif
+      if (g1->type == CCD_GEOM_HFIELD && (i1 != i2 || i1 != i3)) { /* :886-921 correct the witness points for height fields */
+        CcdGeom t = *g2;
+        creal sp[3], dirn[3];
+        int cache = -1;
+        if (g2->type == CCD_GEOM_CAPSULE || g2->type == CCD_GEOM_SPHERE) {
+          const creal radius = g2->size[0], margin = g2->margin;
+          t.margin = CR(0.0);
+          t.size[0] = CR(0.0);
+          ccd_support(&t, x2, sp, &cache); /* the reference passes x2 itself as the direction here */
+          x2[0] = sp[0]; x2[1] = sp[1]; x2[2] = sp[2] - (CR(0.5) * margin + radius);
+        } else {
+          ccd_copy(dirn, x2);
+          creal n = ccd_norm(dirn);
+          if (n > CR(0.0)) { dirn[0] /= n; dirn[1] /= n; dirn[2] /= n; } else { dirn[0] = dirn[1] = dirn[2] = CR(0.0); }
+          ccd_support(&t, dirn, sp, &cache);
+          ccd_copy(x2, sp);
+        }
+        *dist = ccd_hfield_witness(g1, x1, x2);
+      }
+    }
     return idx;
   }
   *dist = CR(0.0);
@@ -641,7 +713,8 @@ CCD_FN_NOINLINE int ccd_run(creal tolerance, creal cutoff, int gjk_iterations, i
                    CcdGjk* res, creal* dist, creal* x1, creal* x2, int* multiccd_idx) {
   *multiccd_idx = -1; /* the EPA face the contact was found on, when multi-contact recovery applies (:2336-2343) */
   creal full1 = CR(0.0), full2 = CR(0.0), size1 = CR(0.0), size2 = CR(0.0), x_1[3], x_2[3];
-  int is_discrete = ((g1.type == CCD_GEOM_BOX || g1.type == CCD_GEOM_MESH) && (g2.type == CCD_GEOM_BOX || g2.type == CCD_GEOM_MESH)) &&
+  int is_discrete = ((g1.type == CCD_GEOM_BOX || g1.type == CCD_GEOM_MESH || g1.type == CCD_GEOM_HFIELD) &&
+                     (g2.type == CCD_GEOM_BOX || g2.type == CCD_GEOM_MESH || g2.type == CCD_GEOM_HFIELD)) &&
                     (g1.margin == CR(0.0) && g2.margin == CR(0.0)); /* :91 _discrete_geoms */
   ccd_copy(x_1, g1.pos); ccd_copy(x_2, g2.pos);
   if (g1.type == CCD_GEOM_SPHERE || g1.type == CCD_GEOM_CAPSULE) {
@@ -657,6 +730,19 @@ CCD_FN_NOINLINE int ccd_run(creal tolerance, creal cutoff, int gjk_iterations, i
       ccd_copy(x1, res->x1); ccd_copy(x2, res->x2);
       if (res->dist == CCD_FLOAT_MAX) { *dist = res->dist; return 1; }
       /* :2153 _inflate */
+      if (g1.type == CCD_GEOM_HFIELD) { /* :2160-2185 the simplex touches a side of the prism: witness against its top triangle */
+        int is_side = 0;
+        for (int i = 0; i < res->dim; i++)
+          if (res->index1[i] != res->index1[0]) { is_side = 1; break; }
+        if (is_side) {
+          creal sp[3];
+          int cache = -1;
+          ccd_support(&g2, x2, sp, &cache);
+          x2[0] = sp[0]; x2[1] = sp[1]; x2[2] = sp[2] - full2;
+          *dist = ccd_hfield_witness(&g1, x1, x2);
+          return 1;
+        }
+      }
       creal n[3], nn;
       ccd_sub(n, x2, x1);
       nn = ccd_norm(n);

@@ -116,6 +116,139 @@ static __device__ __noinline__ int c_ccd_pair(const float* p1, const float* r1, 
   return 1;
 }
 
+// collision_convex.py:56 _hfield_filter + :158 ccd_hfield_kernel: a convex geom against a height field.  The geom is brought into the
+// field's frame, the grid cells under its bounding box are walked, every cell contributes two triangular prisms (bottom at
+// -z_bottom, top at the elevations + margin) that run GJK / EPA against the geom, and up to four of the resulting contacts are kept:
+// the deepest, the one furthest from it, the one furthest from their line, the one furthest from the other triangle edge.  Every
+// contact carries its own normal.  One lane per pair (the prisms are walked serially).
+#define MJB_MAXCONPAIR 50
+static __device__ __noinline__ void c_hfield_pair(const KParams& K, const unsigned char* mb, int w, int g1, int g2, float margin, float* dist4,
+                                                  float* pos12, float* nrm12) {
+  for (int k = 0; k < 4; k++) dist4[k] = INFINITY;
+  const int hid = MI(geom_dataid)[g1];
+  const float* size1 = MR(hfield_size) + 4 * hid;
+  const float *pos1 = DW(geom_xpos) + 3 * g1, *mat1 = DW(geom_xmat) + 9 * g1, *pos2 = DW(geom_xpos) + 3 * g2, *mat2 = DW(geom_xmat) + 9 * g2;
+  const float dp[3] = {pos2[0] - pos1[0], pos2[1] - pos1[1], pos2[2] - pos1[2]};
+  float pos[3];
+  for (int i = 0; i < 3; i++) pos[i] = mat1[i] * dp[0] + mat1[3 + i] * dp[1] + mat1[6 + i] * dp[2];
+  const float r2 = MR(geom_rbound)[g2], fm = MR(geom_margin)[g1] + MR(geom_margin)[g2];
+  for (int i = 0; i < 2; i++)
+    if (size1[i] < pos[i] - r2 - fm || -size1[i] > pos[i] + r2 + fm) return;
+  if (size1[2] < pos[2] - r2 - fm) return;
+  if (-size1[3] > pos[2] + r2 + fm) return;
+  CcdGeom ga, gb;
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++) gb.rot[3 * i + j] = mat1[i] * mat2[j] + mat1[3 + i] * mat2[3 + j] + mat1[6 + i] * mat2[6 + j];
+  for (int i = 0; i < 3; i++) { gb.pos[i] = pos[i]; gb.size[i] = MR(geom_size)[3 * g2 + i]; ga.size[i] = 0.f; }
+  gb.margin = 0.f;
+  gb.type = MI(geom_type)[g2];
+  gb.vert = nullptr; gb.nvert = 0; gb.graph = nullptr; gb.coop = 0;
+  ga.vert = nullptr; ga.nvert = 0; ga.graph = nullptr; ga.coop = 0;
+  if (gb.type == GEOM_MESH) {
+    const int id = MI(geom_dataid)[g2];
+    gb.vert = MRC(mesh_vert) + 3 * MI(mesh_vertadr)[id];
+    gb.nvert = MI(mesh_vertnum)[id];
+    gb.graph = MI(mesh_graphadr)[id] >= 0 ? MIC(mesh_graph) + MI(mesh_graphadr)[id] : nullptr;
+  }
+  float ext[6];  // xmax xmin ymax ymin zmax zmin by support queries
+  for (int a = 0; a < 3; a++)
+    for (int sgn = 0; sgn < 2; sgn++) {
+      float dir[3] = {0.f, 0.f, 0.f}, pnt[3];
+      int cache = -1;
+      dir[a] = sgn ? -1.f : 1.f;
+      ccd_support(&gb, dir, pnt, &cache);
+      ext[2 * a + sgn] = pnt[a];
+    }
+  const float xmax = ext[0], xmin = ext[1], ymax = ext[2], ymin = ext[3], zmax = ext[4], zmin = ext[5];
+  if (xmin - fm > size1[0] || xmax + fm < -size1[0] || ymin - fm > size1[1] || ymax + fm < -size1[1] || zmin - fm > size1[2] || zmax + fm < -size1[3])
+    return;
+  ga.type = GEOM_HFIELD;
+  ga.margin = 0.f;
+  for (int i = 0; i < 9; i++) ga.rot[i] = (i == 0 || i == 4 || i == 8) ? 1.f : 0.f;
+  const int nrow = MI(hfield_nrow)[hid], ncol = MI(hfield_ncol)[hid], adr = MI(hfield_adr)[hid];
+  const float* hdata = MRC(hfield_data) + adr;
+  const float x_scale = 0.5f * (float)(ncol - 1) / size1[0], y_scale = 0.5f * (float)(nrow - 1) / size1[1];
+  const int cmin = max(0, (int)floorf((xmin + size1[0]) * x_scale)), cmax = min(ncol - 1, (int)ceilf((xmax + size1[0]) * x_scale));
+  const int rmin = max(0, (int)floorf((ymin + size1[1]) * y_scale)), rmax = min(nrow - 1, (int)ceilf((ymax + size1[1]) * y_scale));
+  const float dx = 2.0f * size1[0] / (float)(ncol - 1), dy = 2.0f * size1[1] / (float)(nrow - 1);
+  float prism[6][3];
+  for (int i = 0; i < 6; i++) prism[i][0] = prism[i][1] = prism[i][2] = 0.f;
+  prism[0][2] = prism[1][2] = prism[2][2] = -size1[3];
+  float cdist[MJB_MAXCONPAIR], cpos[MJB_MAXCONPAIR][3], cnrm[MJB_MAXCONPAIR][3];
+  float min_dist = MJ_MAXVAL;
+  int min_id = -1, count = 0;
+  gb.margin = margin;
+  CcdPolytope pt;
+  CcdGjk res;
+  int iterations = K.o.ccd_iterations;
+  if (iterations > CCD_MAX_ITER) iterations = CCD_MAX_ITER;
+  auto add_vert = [&](int cc, int rr) {
+    const float x = dx * (float)cc - size1[0], y = dy * (float)rr - size1[1], z = hdata[rr * ncol + cc] * size1[2] + margin;
+    for (int k = 0; k < 3; k++) { prism[0][k] = prism[1][k]; prism[1][k] = prism[2][k]; prism[3][k] = prism[4][k]; prism[4][k] = prism[5][k]; }
+    prism[2][0] = x; prism[5][0] = x; prism[2][1] = y; prism[5][1] = y; prism[5][2] = z;
+  };
+  for (int r = rmin; r < rmax; r++) {
+    add_vert(cmin, r + 1);
+    add_vert(cmin, r);
+    for (int c = cmin + 1; c <= cmax; c++) {
+      for (int i = 0; i < 2; i++) {
+        if (count >= MJB_MAXCONPAIR) continue;  // the reference reports an overflow and skips (without advancing the prism)
+        add_vert(c, r + (i == 0 ? 1 : 0));
+        if (prism[3][2] < zmin && prism[4][2] < zmin && prism[5][2] < zmin) continue;
+        for (int k = 0; k < 6; k++) { ga.prism[k][0] = prism[k][0]; ga.prism[k][1] = prism[k][1]; ga.prism[k][2] = prism[k][2]; }
+        for (int k = 0; k < 3; k++) ga.pos[k] = (prism[0][k] + prism[1][k] + prism[2][k] + prism[3][k] + prism[4][k] + prism[5][k]) * (1.0f / 6.0f);
+        float d, w1[3], w2[3];
+        int face_idx;
+        const int nc = ccd_run(K.o.ccd_tolerance, 0.f, iterations, iterations, ga, gb, &pt, &res, &d, w1, w2, &face_idx);
+        if (nc == 0) continue;
+        cdist[count] = d;
+        const V3 pl{0.5f * (w1[0] + w2[0]), 0.5f * (w1[1] + w2[1]), 0.5f * (w1[2] + w2[2])};
+        const M3 fr = make_frame(V3{w1[0] - w2[0], w1[1] - w2[1], w1[2] - w2[2]});
+        const M3 m1 = ldm3(mat1);
+        const V3 pg = mat_vec(m1, pl) + ld3(pos1), ng = mat_vec(m1, V3{fr.m[0], fr.m[1], fr.m[2]});
+        st3(cpos[count], pg);
+        st3(cnrm[count], ng);
+        if (d < min_dist) { min_dist = d; min_id = count; }
+        count++;
+      }
+    }
+  }
+  if (min_id < 0) return;
+  const V3 min_pos = ld3(cpos[min_id]), min_normal = ld3(cnrm[min_id]);
+  auto put = [&](int k, int id) {
+    dist4[k] = cdist[id];
+    for (int i = 0; i < 3; i++) { pos12[3 * k + i] = cpos[id][i]; nrm12[3 * k + i] = cnrm[id][i]; }
+  };
+  put(0, min_id);
+  const float MIN_NEXT = 1.0e-3f;
+  int id1 = -1, id2 = -1, id3 = -1;
+  float dist1 = -MJ_MAXVAL, dist12 = -MJ_MAXVAL, dist3 = -MJ_MAXVAL;
+  for (int i = 0; i < count; i++) {
+    if (i == min_id) continue;
+    const float dd = norm(ld3(cpos[i]) - min_pos);
+    if (dd > dist1) { id1 = i; dist1 = dd; }
+  }
+  if (id1 == -1 || (0.f < dist1 && dist1 < MIN_NEXT)) return;
+  put(1, id1);
+  const V3 p1 = ld3(cpos[id1]), d_min1 = cross(min_normal, min_pos - p1);
+  for (int i = 0; i < count; i++) {
+    if (i == min_id || i == id1) continue;
+    const float dd = fabsf(dot(ld3(cpos[i]) - min_pos, d_min1));
+    if (dd > dist12) { id2 = i; dist12 = dd; }
+  }
+  if (id2 == -1 || (0.f < dist12 && dist12 < MIN_NEXT)) return;
+  put(2, id2);
+  const V3 p2 = ld3(cpos[id2]), vec_min2 = cross(min_normal, min_pos - p2), vec_12 = cross(min_normal, p1 - p2);
+  for (int i = 0; i < count; i++) {
+    if (i == min_id || i == id1 || i == id2) continue;
+    const V3 hp = ld3(cpos[i]);
+    const float dd = fabsf(dot(hp - min_pos, vec_min2)) + fabsf(dot(p1 - hp, vec_12));
+    if (dd > dist3) { id3 = i; dist3 = dd; }
+  }
+  if (id3 == -1 || (0.f < dist3 && dist3 < MIN_NEXT)) return;
+  put(3, id3);
+}
+
 // collision_primitive.py:52-277 plane_convex (hill climbing over the mesh graph for >= 10 vertices, else exhaustive): up to 4 contacts at the
 // deepest vertex a, the in-threshold vertex b furthest from a, c furthest from the line ab, d furthest from the edges ac / bc.
 static __device__ __noinline__ int c_plane_mesh(const float* p1, const float* n1, const float* p2, const float* r2, const float* vert, int nvert,
@@ -704,6 +837,7 @@ static __device__ __noinline__ int c_box_box(const float* p1, const float* R1, c
 
 // Number of candidate contacts of a pair type (collision_primitive.py wrappers).
 __device__ __forceinline__ int pair_ncand(int t1, int t2) {
+  if (t1 == GEOM_HFIELD) return 4;
   if (t1 == GEOM_PLANE) return t2 == GEOM_SPHERE || t2 == GEOM_ELLIPSOID ? 1 : (t2 == GEOM_CAPSULE ? 2 : (t2 == GEOM_BOX ? 8 : (t2 == GEOM_CYLINDER || t2 == GEOM_MESH ? 4 : 0)));
   if (is_ccd_pair(t1, t2)) return 1;
   if (t1 == GEOM_SPHERE) return (t2 == GEOM_SPHERE || t2 == GEOM_CAPSULE || t2 == GEOM_BOX || t2 == GEOM_CYLINDER) ? 1 : 0;
@@ -916,6 +1050,8 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
   ContactParams cp;
   const float* r2 = nullptr;
   float bdist[(FEAT & COLF_BOX) ? 8 : 1], bpos[(FEAT & COLF_BOX) ? 24 : 3], bnrm[3] = {1.f, 0.f, 0.f};  // box-box results
+  float hnrm[(FEAT & COLF_CONVEX) ? 12 : 1];  // height-field contacts carry one normal each
+  bool pernormal = false;
   int nbb = 0;
   bool boxbox = false, mesh_ccd = false;
   if (has) {
@@ -945,7 +1081,12 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
       nbb = c_box_box(pa, DW(geom_xmat) + 9 * g1, sa, pb, r2, sb, cp.margin, bdist, bpos, bnrm);
       boxbox = true;
     }
-    if ((FEAT & COLF_CONVEX) && g.t2 == GEOM_MESH && is_ccd_pair(g.t1, g.t2)) {
+    if ((FEAT & COLF_CONVEX) && (FEAT & COLF_BOX) && g.t1 == GEOM_HFIELD) {
+      c_hfield_pair(K, mb, w, g1, g2, cp.margin, bdist, bpos, hnrm);
+      nbb = 4;
+      boxbox = true;
+      pernormal = true;
+    } else if ((FEAT & COLF_CONVEX) && g.t2 == GEOM_MESH && is_ccd_pair(g.t1, g.t2)) {
       mesh_ccd = true;  // evaluated below by the whole warp, one pair at a time
     } else if ((FEAT & COLF_CONVEX) && is_ccd_pair(g.t1, g.t2, nativeccd)) {  // GJK / EPA once per pair; the two passes below read the result
       const float pa[3] = {g.p1.x, g.p1.y, g.p1.z}, pb[3] = {g.p2.x, g.p2.y, g.p2.z};
@@ -1048,7 +1189,8 @@ __device__ __forceinline__ void narrowphase_flush(const KParams& K, const unsign
       if ((FEAT & (COLF_BOX | COLF_CONVEX)) && boxbox) {
         dist = k < nbb ? bdist[k] : INFINITY;
         pos = V3{bpos[3 * (k & 7)], bpos[3 * (k & 7) + 1], bpos[3 * (k & 7) + 2]};
-        frame = make_frame(V3{bnrm[0], bnrm[1], bnrm[2]});
+        if ((FEAT & COLF_CONVEX) && pernormal) frame = make_frame(V3{hnrm[3 * (k & 3)], hnrm[3 * (k & 3) + 1], hnrm[3 * (k & 3) + 2]});
+        else frame = make_frame(V3{bnrm[0], bnrm[1], bnrm[2]});
       } else {
         pair_contact<FEAT>(g, r2, cp.margin, k, dist, pos, frame);
       }

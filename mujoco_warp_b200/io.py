@@ -94,7 +94,7 @@ def _check_supported(mjm):
   # features of the reference that this library does not implement yet (scope)
   if is_sparse(mjm):
     raise NotImplementedError("sparse mass matrix / Jacobian (nv > 32 or jacobian=sparse) is not implemented yet.")
-  for name in ("ntendon", "nflex", "nhfield"):
+  for name in ("ntendon", "nflex"):
     if getattr(mjm, name, 0):
       raise NotImplementedError(f"{name} > 0 is not implemented yet.")
   for t in np.asarray(mjm.actuator_trntype):
@@ -142,6 +142,8 @@ def host_model(mjm) -> SimpleNamespace:
   ints["mesh_vertnum"] = A("mesh_vertnum", i32) if nmesh else np.zeros(0, dtype=i32)
   ints["mesh_graphadr"] = A("mesh_graphadr", i32) if nmesh and hasattr(mjm, "mesh_graphadr") else np.full(nmesh, -1, dtype=i32)
   ints["mesh_graph"] = A("mesh_graph", i32).reshape(-1) if nmesh and hasattr(mjm, "mesh_graph") else np.zeros(0, dtype=i32)
+  for name in ("hfield_nrow", "hfield_ncol", "hfield_adr"):
+    ints[name] = A(name, i32) if int(getattr(mjm, "nhfield", 0)) else np.zeros(0, dtype=i32)
   for name in types.MODEL_REAL_FIELDS:
     if name == "mesh_vert":
       reals[name] = A(name, f64).reshape(-1, 3) if nmesh else np.zeros((0, 3))
@@ -149,6 +151,9 @@ def host_model(mjm) -> SimpleNamespace:
       reals[name] = A(name, f64).reshape(nu, 6)
     elif name == "group_sphere":
       continue  # derived below (two-level broadphase)
+    elif name in ("hfield_size", "hfield_data"):
+      nhf = int(getattr(mjm, "nhfield", 0))
+      reals[name] = (A(name, f64).reshape(-1, 4) if name == "hfield_size" else A(name, f64).reshape(-1)) if nhf else np.zeros((0, 4) if name == "hfield_size" else 0)
     else:
       reals[name] = A(name, f64)
 
@@ -324,6 +329,13 @@ def host_model(mjm) -> SimpleNamespace:
     (C.GeomType.CYLINDER, C.GeomType.MESH),
     (C.GeomType.BOX, C.GeomType.MESH),
     (C.GeomType.MESH, C.GeomType.MESH),
+    # height fields: one GJK / EPA run per prism of the sub-grid under the geom (collision_convex.py:158)
+    (C.GeomType.HFIELD, C.GeomType.SPHERE),
+    (C.GeomType.HFIELD, C.GeomType.CAPSULE),
+    (C.GeomType.HFIELD, C.GeomType.ELLIPSOID),
+    (C.GeomType.HFIELD, C.GeomType.CYLINDER),
+    (C.GeomType.HFIELD, C.GeomType.BOX),
+    (C.GeomType.HFIELD, C.GeomType.MESH),
   }
   gtype = ints["geom_type"]
   for ga, gb in ints["nxn_pair"]:
@@ -350,7 +362,7 @@ def host_model(mjm) -> SimpleNamespace:
     nmaxcondim=nmaxcondim, nmaxpyramid=int(max(1, 2 * (nmaxcondim - 1))),
     ngravcomp=int((reals["body_gravcomp"] != 0).sum()), is_sparse=int(sparse), nM=int(getattr(mjm, "nM", 0)),
     ntree=int(getattr(mjm, "ntree", 0)), ngeompair=int(len(geom1)), nmesh=nmesh, nmeshvert=int(reals["mesh_vert"].shape[0]), nmeshgraph=int(ints["mesh_graph"].size), blob_hot_bytes=0,
-    ngroup=ngroup, ngrouppair=ngrouppair,
+    ngroup=ngroup, ngrouppair=ngrouppair, nhfield=int(getattr(mjm, "nhfield", 0)), nhfielddata=int(reals["hfield_data"].size),
   )  # fmt: skip
   extra = dict(
     nsensordata=int(getattr(mjm, "nsensordata", 0)), ncam=int(getattr(mjm, "ncam", 0)), nlight=int(getattr(mjm, "nlight", 0)),
@@ -441,7 +453,7 @@ def put_model(mjm, device=None) -> types.Model:
   int_names, real_names = list(types.MODEL_INT_FIELDS), list(types.MODEL_REAL_FIELDS)
   # hot tables first, then the large / streamed ones (pair lists, mesh vertices and graphs): when the whole blob does not fit the
   # kernels' shared-memory budget they stage the hot prefix only and read the cold tables from global memory (mjb_types.cuh MIC / MRC)
-  cold = ("nxn_pair", "nxn_pairid", "nxn_lookup", "mesh_graph", "mesh_vert")
+  cold = ("nxn_pair", "nxn_pairid", "nxn_lookup", "mesh_graph", "mesh_vert", "hfield_data")
   offsets, off, hot_bytes = {}, 0, 0
   for name in [n for n in int_names + real_names if n not in cold] + list(cold):
     arr = hm.ints[name] if name in hm.ints else hm.reals[name]

@@ -419,6 +419,85 @@ def _parse_meshes(root, comp, defaults, basedir):
   return meshes
 
 
+def _read_png_gray(path):
+  """8 / 16-bit greyscale (optionally with alpha / RGB: first channel) non-interlaced PNG -> float array (rows, cols).  Enough of the
+  format for height-field images; no third-party imaging library is available here."""
+  import struct
+  import zlib
+
+  data = open(path, "rb").read()
+  if data[:8] != b"\x89PNG\r\n\x1a\n":
+    raise ValueError(f"{path}: not a PNG file")
+  pos, idat, hdr = 8, b"", None
+  while pos < len(data):
+    n, kind = struct.unpack(">I4s", data[pos : pos + 8])
+    body = data[pos + 8 : pos + 8 + n]
+    if kind == b"IHDR":
+      hdr = struct.unpack(">IIBBBBB", body)
+    elif kind == b"IDAT":
+      idat += body
+    pos += 12 + n
+  w, h, depth, ctype, _, _, interlace = hdr
+  if interlace or depth not in (8, 16) or ctype not in (0, 2, 4, 6):
+    raise NotImplementedError(f"{path}: PNG variant not supported (depth {depth}, colour type {ctype}, interlace {interlace})")
+  nch = {0: 1, 2: 3, 4: 2, 6: 4}[ctype]
+  bpp = nch * depth // 8
+  raw = np.frombuffer(zlib.decompress(idat), dtype=np.uint8).reshape(h, 1 + w * bpp)
+  out = np.zeros((h, w * bpp), dtype=np.uint8)
+  prev = np.zeros(w * bpp, dtype=np.int32)
+  for r in range(h):
+    f, line = int(raw[r, 0]), raw[r, 1:].astype(np.int32)
+    cur = np.zeros(w * bpp, dtype=np.int32)
+    if f == 0:
+      cur = line
+    elif f == 2:
+      cur = (line + prev) & 255
+    else:  # sub / average / paeth depend on the pixel to the left: byte-serial
+      for i in range(w * bpp):
+        a = cur[i - bpp] if i >= bpp else 0
+        b = prev[i]
+        c = prev[i - bpp] if i >= bpp else 0
+        if f == 1:
+          pred = a
+        elif f == 3:
+          pred = (a + b) >> 1
+        else:
+          pa, pb, pc = abs(b - c), abs(a - c), abs(a + b - 2 * c)
+          pred = a if (pa <= pb and pa <= pc) else (b if pb <= pc else c)
+        cur[i] = (line[i] + pred) & 255
+    out[r] = cur
+    prev = cur
+  px = out.reshape(h, w, nch, depth // 8)
+  val = px[..., 0].astype(np.float64) if depth == 8 else px[..., 0].astype(np.float64) * 256 + px[..., 1]
+  return val[:, :, 0]
+
+
+def _parse_hfields(root, comp, defaults, basedir):
+  """name -> (size[4], nrow, ncol, data) for every <asset><hfield>.  Like MuJoCo's compiler, elevation data are shifted and scaled
+  to [0, 1] and image rows are flipped (the first image row is the far edge, +y)."""
+  out = {}
+  for asset in root.findall("asset"):
+    for e in asset.findall("hfield"):
+      a = _resolve(defaults, e, None)
+      name = a.get("name") or os.path.splitext(os.path.basename(a.get("file", "")))[0]
+      size = _vec(a.get("size"), 4)
+      if "elevation" in a:
+        nrow, ncol = int(a["nrow"]), int(a["ncol"])
+        data = _vec(a["elevation"]).reshape(nrow, ncol)[::-1]
+      elif "file" in a:
+        path = os.path.join(basedir, comp.meshdir if not os.path.isfile(os.path.join(basedir, a["file"])) else "", a["file"])
+        data = _read_png_gray(path)[::-1]
+        nrow, ncol = data.shape
+      else:
+        nrow, ncol = int(a["nrow"]), int(a["ncol"])
+        data = np.zeros((nrow, ncol))
+      data = np.asarray(data, dtype=np.float64)
+      lo, hi = float(data.min()), float(data.max())
+      data = (data - lo) / (hi - lo) if hi > lo else np.zeros_like(data)
+      out[name] = (size, nrow, ncol, np.ascontiguousarray(data))
+  return out
+
+
 # ----------------------------------------------------------------------------- parse tree
 class _Compiler:
   def __init__(self):
@@ -841,11 +920,18 @@ def _finalize(root, comp, defaults, opt, bodies, joints, geoms, sites, basedir) 
   geom_mesh_com = np.zeros((ngeom, 3))  # mesh geoms: centre of mass in the geom (= mesh file) frame and the full tensor about it
   geom_mesh_inertia = np.zeros((ngeom, 3, 3))
   meshes = _parse_meshes(root, comp, defaults, basedir)
+  hfields = _parse_hfields(root, comp, defaults, basedir)
+  hfield_names = list(hfields)  # every height-field asset enters the model, in file order (geom_dataid indexes this list)
   mesh_ids = {}  # only meshes referenced by a geom enter the model, in order of first use
+  hfield_geoms = {}
   for i, g in enumerate(geoms):
     gt = _GEOM_TYPES[g.get("type", "mesh" if "mesh" in g else "sphere")]
+    if gt == C.GeomType.HFIELD and g.get("hfield") not in hfields:
+      raise NotImplementedError(f"geom type hfield needs an <asset><hfield> named '{g.get('hfield')}'")
     if gt == C.GeomType.HFIELD:
-      raise NotImplementedError("geom type hfield requires height-field assets (not supported by mjcf lite yet)")
+      hfield_geoms[i] = hfield_names.index(g["hfield"])
+      hs = hfields[g["hfield"]][0]
+      g = dict(g, size=f"{hs[0]} {hs[1]} {hs[2]}")  # bounds below; the collision code reads hfield_size
     if gt == C.GeomType.MESH:
       # Collision uses the convex hull of the asset's vertices, kept in the mesh file's frame: MuJoCo re-centres a mesh on its
       # inertial frame and folds that transform into geom_pos / geom_quat -- the world-space shape is the same, only the
@@ -911,7 +997,7 @@ def _finalize(root, comp, defaults, opt, bodies, joints, geoms, sites, basedir) 
       if key in g:
         v = _vec(g[key])
         arr[i, : v.size] = v
-    if gt != C.GeomType.PLANE:
+    if gt not in (C.GeomType.PLANE, C.GeomType.HFIELD):
       vol, inert = _geom_volume_inertia(gt, size)
       if "mass" in g:
         mass = float(g["mass"])
@@ -921,10 +1007,27 @@ def _finalize(root, comp, defaults, opt, bodies, joints, geoms, sites, basedir) 
         mass = dens * vol
       geom_mass[i] = mass
       geom_inertia[i] = inert * dens
-    m.geom_rbound[i], m.geom_aabb[i] = _geom_bounds(gt, size)
+    if gt == C.GeomType.HFIELD:
+      # bounding volume of the field: the box [-x, x] x [-y, y] x [-z_bottom, z_top] in the geom frame (MuJoCo's compiler is not
+      # available to compare with; these feed the broadphase filters only, the narrowphase reads hfield_size)
+      hs = hfields[hfield_names[hfield_geoms[i]]][0]
+      m.geom_dataid[i] = hfield_geoms[i]
+      m.geom_size[i] = [hs[0], hs[1], hs[2]]
+      m.geom_rbound[i] = float(np.sqrt(hs[0] ** 2 + hs[1] ** 2 + max(hs[2], hs[3]) ** 2))
+      m.geom_aabb[i] = [0, 0, 0.5 * (hs[2] - hs[3]), hs[0], hs[1], 0.5 * (hs[2] + hs[3])]
+    else:
+      m.geom_rbound[i], m.geom_aabb[i] = _geom_bounds(gt, size)
 
   # ---------------- mesh tables (convex hull vertices; no hill-climbing graph: mesh_graphadr = -1 selects the exhaustive support
   # search, reference collision_gjk.py:142)
+  m.nhfield = len(hfield_names)
+  m.hfield_names = hfield_names
+  m.hfield_size = np.array([hfields[n][0] for n in hfield_names], dtype=np.float64).reshape(-1, 4)
+  m.hfield_nrow = np.array([hfields[n][1] for n in hfield_names], dtype=i32)
+  m.hfield_ncol = np.array([hfields[n][2] for n in hfield_names], dtype=i32)
+  m.hfield_adr = np.concatenate(([0], np.cumsum(m.hfield_nrow * m.hfield_ncol)[:-1])).astype(i32) if hfield_names else np.zeros(0, dtype=i32)
+  m.hfield_data = np.concatenate([hfields[n][3].ravel() for n in hfield_names]) if hfield_names else np.zeros(0)
+  m.nhfielddata = int(m.hfield_data.size)
   names = sorted(mesh_ids, key=mesh_ids.get)
   m.nmesh = len(names)
   m.mesh_names = names
@@ -1210,7 +1313,7 @@ def _finalize_constraints(m, root, comp, defaults):
       m.pair_friction[i, : v.size] = v
 
   # absent features (sizes the device model expects)
-  m.ntendon = m.nflex = m.nsensor = m.nsensordata = m.nhfield = m.ncam = m.nlight = 0
+  m.ntendon = m.nflex = m.nsensor = m.nsensordata = m.ncam = m.nlight = 0
   m.nwrap = m.nJten = m.nflexvert = m.nflexedge = m.nflexelem = 0
   m.ngravcomp = int((m.body_gravcomp != 0).sum())
 

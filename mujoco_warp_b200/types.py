@@ -50,7 +50,7 @@ TILE_SIZE_JTDAJ_DENSE = 16  # reference types.py:35
 # ----------------------------------------------------------------------------------------------
 MODEL_SIZES = (
   "nq nv nu na nbody njnt ngeom nsite nmocap neq npair nxn nlevel nv_pad nlimit nlimitball "
-  "nfrictiondof neqjnt nJmom nmaxcondim nmaxpyramid ngravcomp is_sparse nM ntree ngeompair nmesh nmeshvert nmeshgraph neqconnect neqweld blob_hot_bytes ngroup ngrouppair"
+  "nfrictiondof neqjnt nJmom nmaxcondim nmaxpyramid ngravcomp is_sparse nM ntree ngeompair nmesh nmeshvert nmeshgraph neqconnect neqweld blob_hot_bytes nhfield nhfielddata ngroup ngrouppair"
 ).split()
 
 MODEL_INT_FIELDS = {
@@ -111,6 +111,9 @@ MODEL_INT_FIELDS = {
   "mesh_vertnum": ("nmesh",),
   "mesh_graphadr": ("nmesh",),
   "mesh_graph": ("nmeshgraph",),
+  "hfield_nrow": ("nhfield",),
+  "hfield_ncol": ("nhfield",),
+  "hfield_adr": ("nhfield",),
   "group_bodyid": ("ngroup",),
   "grouppair": ("ngrouppair", 2),
   "grouppair_adr": ("ngrouppair+1",),
@@ -174,6 +177,8 @@ MODEL_REAL_FIELDS = {
   "eq_solimp": ("neq", 5),
   "eq_data": ("neq", 11),
   "mesh_vert": ("nmeshvert", 3),
+  "hfield_size": ("nhfield", 4),
+  "hfield_data": ("nhfielddata",),
   "group_sphere": ("ngroup", 4),
 }
 

@@ -31,6 +31,8 @@ typedef double real;
 #define CCD_FN static inline
 #define CCD_SQRT sqrt
 #define CCD_FABS fabs
+#include <stdio.h>
+/* #define CCD_DEBUG_PRINT(...) fprintf(stderr, __VA_ARGS__)   -- traces the GJK / EPA of height-field x mesh pairs (mjb_ccd_core.h) */
 #include "../mujoco_warp_b200/csrc/mjb_ccd_core.h"
 
 #define MJ_MINVAL 1e-15
@@ -992,12 +994,151 @@ static int ccd_pair(const real* p1, const real* r1, const real* s1, int t1, cons
   return ncand;
 }
 
+/* collision_convex.py:56 _hfield_filter + :158 ccd_hfield_kernel (see MuJoCo mjc_ConvexHField): the geom is brought into the height
+ * field's frame, the grid cells under its bounding box are walked, every cell contributes two triangular prisms (bottom at
+ * -z_bottom, top at the elevations + margin) that run GJK / EPA against the geom, and up to four of the resulting contacts are kept:
+ * the deepest, the one furthest from it, the one furthest from their line, the one furthest from the other triangle edge. */
+#define MJ_MAXCONPAIR 50
+static int hfield_pair(const OModel* m, const OData* d, int g1, int g2, real margin, real tolerance, int iterations, OContactGeom* out) {
+  for (int k = 0; k < 4; k++) { out[k].id = k; out[k].dist = MJ_MAXVAL; memset(out[k].pos, 0, sizeof(out[k].pos)); memset(out[k].frame, 0, sizeof(out[k].frame)); }
+  const int hid = m->geom_dataid[g1];
+  const real* size1 = m->hfield_size + 4 * hid;
+  const real *pos1 = d->geom_xpos + 3 * g1, *mat1 = d->geom_xmat + 9 * g1, *pos2 = d->geom_xpos + 3 * g2, *mat2 = d->geom_xmat + 9 * g2;
+  real dp[3] = {pos2[0] - pos1[0], pos2[1] - pos1[1], pos2[2] - pos1[2]}, pos[3];
+  for (int i = 0; i < 3; i++) pos[i] = mat1[i] * dp[0] + mat1[3 + i] * dp[1] + mat1[6 + i] * dp[2];
+  const real r2 = m->geom_rbound[g2], fm = m->geom_margin[g1] + m->geom_margin[g2];
+  for (int i = 0; i < 2; i++)
+    if (size1[i] < pos[i] - r2 - fm || -size1[i] > pos[i] + r2 + fm) return 4;
+  if (size1[2] < pos[2] - r2 - fm) return 4;
+  if (-size1[3] > pos[2] + r2 + fm) return 4;
+  CcdGeom ga, gb;
+  memset(&ga, 0, sizeof(ga)); memset(&gb, 0, sizeof(gb));
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++) gb.rot[3 * i + j] = mat1[i] * mat2[j] + mat1[3 + i] * mat2[3 + j] + mat1[6 + i] * mat2[6 + j];
+  memcpy(gb.pos, pos, sizeof(pos));
+  memcpy(gb.size, m->geom_size + 3 * g2, 3 * sizeof(real));
+  gb.margin = 0.0; gb.type = m->geom_type[g2];
+  if (gb.type == GEOM_MESH) {
+    int id = m->geom_dataid[g2];
+    gb.vert = m->mesh_vert + 3 * m->mesh_vertadr[id];
+    gb.nvert = m->mesh_vertnum[id];
+    gb.graph = m->mesh_graphadr[id] >= 0 ? m->mesh_graph + m->mesh_graphadr[id] : 0;
+  }
+  real ext[6]; /* xmax xmin ymax ymin zmax zmin by support queries */
+  for (int a = 0; a < 3; a++)
+    for (int sgn = 0; sgn < 2; sgn++) {
+      real dir[3] = {0, 0, 0}, pnt[3];
+      int cache = -1;
+      dir[a] = sgn ? -1.0 : 1.0;
+      ccd_support(&gb, dir, pnt, &cache);
+      ext[2 * a + sgn] = pnt[a];
+    }
+  const real xmax = ext[0], xmin = ext[1], ymax = ext[2], ymin = ext[3], zmax = ext[4], zmin = ext[5];
+  if (xmin - fm > size1[0] || xmax + fm < -size1[0] || ymin - fm > size1[1] || ymax + fm < -size1[1] || zmin - fm > size1[2] || zmax + fm < -size1[3])
+    return 4;
+  ga.type = GEOM_HFIELD; ga.margin = 0.0;
+  ga.rot[0] = ga.rot[4] = ga.rot[8] = 1.0;
+  const int nrow = m->hfield_nrow[hid], ncol = m->hfield_ncol[hid], adr = m->hfield_adr[hid];
+  const real x_scale = 0.5 * (real)(ncol - 1) / size1[0], y_scale = 0.5 * (real)(nrow - 1) / size1[1];
+  int cmin = (int)floor((xmin + size1[0]) * x_scale), cmax = (int)ceil((xmax + size1[0]) * x_scale);
+  int rmin = (int)floor((ymin + size1[1]) * y_scale), rmax = (int)ceil((ymax + size1[1]) * y_scale);
+  if (cmin < 0) cmin = 0;
+  if (cmax > ncol - 1) cmax = ncol - 1;
+  if (rmin < 0) rmin = 0;
+  if (rmax > nrow - 1) rmax = nrow - 1;
+  const real dx = 2.0 * size1[0] / (real)(ncol - 1), dy = 2.0 * size1[1] / (real)(nrow - 1);
+  const int dr[2] = {1, 0};
+  real prism[6][3];
+  memset(prism, 0, sizeof(prism));
+  prism[0][2] = prism[1][2] = prism[2][2] = -size1[3];
+  real cdist[MJ_MAXCONPAIR], cpos[MJ_MAXCONPAIR][3], cnrm[MJ_MAXCONPAIR][3];
+  real min_dist = MJ_MAXVAL, min_normal[3] = {MJ_MAXVAL, MJ_MAXVAL, MJ_MAXVAL}, min_pos[3] = {MJ_MAXVAL, MJ_MAXVAL, MJ_MAXVAL};
+  int min_id = -1, count = 0;
+  gb.margin = margin;
+  static _Thread_local CcdPolytope pt;
+  CcdGjk res;
+  if (iterations > CCD_MAX_ITER) iterations = CCD_MAX_ITER;
+#define HF_ADD_VERT(cc, rr)                                                      \
+  do {                                                                           \
+    const real x_ = dx * (real)(cc) - size1[0], y_ = dy * (real)(rr) - size1[1]; \
+    const real z_ = m->hfield_data[adr + (rr) * ncol + (cc)] * size1[2] + margin; \
+    memcpy(prism[0], prism[1], sizeof(prism[0])); memcpy(prism[1], prism[2], sizeof(prism[0])); \
+    memcpy(prism[3], prism[4], sizeof(prism[0])); memcpy(prism[4], prism[5], sizeof(prism[0])); \
+    prism[2][0] = x_; prism[5][0] = x_; prism[2][1] = y_; prism[5][1] = y_; prism[5][2] = z_; \
+  } while (0)
+  for (int r = rmin; r < rmax; r++) {
+    for (int i = 0; i < 2; i++) HF_ADD_VERT(cmin, r + dr[i]);
+    for (int c = cmin + 1; c <= cmax; c++) {
+      for (int i = 0; i < 2; i++) {
+        if (count >= MJ_MAXCONPAIR) continue; /* the reference reports an overflow and skips (without advancing the prism) */
+        HF_ADD_VERT(c, r + dr[i]);
+        if (prism[3][2] < zmin && prism[4][2] < zmin && prism[5][2] < zmin) continue;
+        memcpy(ga.prism, prism, sizeof(prism));
+        for (int k = 0; k < 3; k++) ga.pos[k] = (prism[0][k] + prism[1][k] + prism[2][k] + prism[3][k] + prism[4][k] + prism[5][k]) * (1.0 / 6.0);
+        real dist, w1[3], w2[3];
+        int face_idx;
+        int nc = ccd_run(tolerance, 0.0, iterations, iterations, ga, gb, &pt, &res, &dist, w1, w2, &face_idx);
+        if (nc == 0) continue;
+        cdist[count] = dist;
+        real pl[3] = {0.5 * (w1[0] + w2[0]), 0.5 * (w1[1] + w2[1]), 0.5 * (w1[2] + w2[2])}, nl[3] = {w1[0] - w2[0], w1[1] - w2[1], w1[2] - w2[2]}, fr[9];
+        mat_vec(cpos[count], mat1, pl);
+        for (int k = 0; k < 3; k++) cpos[count][k] += pos1[k];
+        make_frame(fr, nl);
+        mat_vec(cnrm[count], mat1, fr);
+        if (dist < min_dist) { min_dist = dist; memcpy(min_normal, cnrm[count], sizeof(min_normal)); memcpy(min_pos, cpos[count], sizeof(min_pos)); min_id = count; }
+        count++;
+      }
+    }
+  }
+#undef HF_ADD_VERT
+#define HF_WRITE(k, dd, pp, nn) do { out[k].dist = (dd); memcpy(out[k].pos, (pp), 3 * sizeof(real)); make_frame(out[k].frame, (nn)); } while (0)
+  if (min_id < 0) return 4;
+  HF_WRITE(0, min_dist, min_pos, min_normal);
+  const real MIN_NEXT = 1.0e-3;
+  int id1 = -1, id2 = -1, id3 = -1;
+  real dist1 = -MJ_MAXVAL, dist12 = -MJ_MAXVAL, dist3 = -MJ_MAXVAL, v[3];
+  for (int i = 0; i < count; i++) {
+    if (i == min_id) continue;
+    for (int k = 0; k < 3; k++) v[k] = cpos[i][k] - min_pos[k];
+    real dd = norm3(v);
+    if (dd > dist1) { id1 = i; dist1 = dd; }
+  }
+  if (id1 == -1 || (0.0 < dist1 && dist1 < MIN_NEXT)) return 4;
+  HF_WRITE(1, cdist[id1], cpos[id1], cnrm[id1]);
+  real d_min1[3], t3[3];
+  for (int k = 0; k < 3; k++) t3[k] = min_pos[k] - cpos[id1][k];
+  cross3(d_min1, min_normal, t3);
+  for (int i = 0; i < count; i++) {
+    if (i == min_id || i == id1) continue;
+    for (int k = 0; k < 3; k++) v[k] = cpos[i][k] - min_pos[k];
+    real dd = fabs(dot3(v, d_min1));
+    if (dd > dist12) { id2 = i; dist12 = dd; }
+  }
+  if (id2 == -1 || (0.0 < dist12 && dist12 < MIN_NEXT)) return 4;
+  HF_WRITE(2, cdist[id2], cpos[id2], cnrm[id2]);
+  real vec_min2[3], vec_12[3], u3[3];
+  for (int k = 0; k < 3; k++) { t3[k] = min_pos[k] - cpos[id2][k]; u3[k] = cpos[id1][k] - cpos[id2][k]; }
+  cross3(vec_min2, min_normal, t3);
+  cross3(vec_12, min_normal, u3);
+  for (int i = 0; i < count; i++) {
+    if (i == min_id || i == id1 || i == id2) continue;
+    for (int k = 0; k < 3; k++) { v[k] = cpos[i][k] - min_pos[k]; u3[k] = cpos[id1][k] - cpos[i][k]; }
+    real dd = fabs(dot3(v, vec_min2)) + fabs(dot3(u3, vec_12));
+    if (dd > dist3) { id3 = i; dist3 = dd; }
+  }
+  if (id3 == -1 || (0.0 < dist3 && dist3 < MIN_NEXT)) return 4;
+  HF_WRITE(3, cdist[id3], cpos[id3], cnrm[id3]);
+#undef HF_WRITE
+  return 4;
+}
+
 static int narrowphase_pair(const OModel* m, const OData* d, int g1, int g2, real margin, real ccd_tolerance, int ccd_iterations,
                             int nativeccd, OContactGeom* out) {
   int t1 = m->geom_type[g1], t2 = m->geom_type[g2];
   const real *p1 = d->geom_xpos + 3 * g1, *p2 = d->geom_xpos + 3 * g2, *r1 = d->geom_xmat + 9 * g1, *r2 = d->geom_xmat + 9 * g2;
   const real *s1 = m->geom_size + 3 * g1, *s2 = m->geom_size + 3 * g2;
   real n1[3] = {r1[2], r1[5], r1[8]}, n2[3] = {r2[2], r2[5], r2[8]};
+  if (t1 == GEOM_HFIELD) return hfield_pair(m, d, g1, g2, margin, ccd_tolerance, ccd_iterations, out);
   /* collision_driver.py:74, :736: box-box goes through ccd + multicontact unless DisableBit.NATIVECCD */
   if (is_convex_pair_mesh(t1, t2) || (nativeccd && t1 == GEOM_BOX && t2 == GEOM_BOX)) {
     const real *v1 = 0, *v2 = 0;

@@ -41,8 +41,9 @@ _lib = None
 
 def build(force: bool = False) -> str:
   os.makedirs(os.path.dirname(LIB), exist_ok=True)
-  hdr = os.path.join(os.path.dirname(_HERE), "include", "mjb_fields.h")
-  if not force and os.path.exists(LIB) and os.path.getmtime(LIB) >= max(os.path.getmtime(SRC), os.path.getmtime(hdr)):
+  root = os.path.dirname(_HERE)
+  deps = [SRC, os.path.join(root, "include", "mjb_fields.h"), os.path.join(root, "mujoco_warp_b200", "csrc", "mjb_ccd_core.h")]
+  if not force and os.path.exists(LIB) and os.path.getmtime(LIB) >= max(os.path.getmtime(p) for p in deps):
     return LIB
   cmd = ["gcc", "-O3", "-march=x86-64-v3", "-fPIC", "-shared", "-fopenmp", "-o", LIB, SRC, "-lm"]
   res = subprocess.run(cmd, capture_output=True, text=True)

@@ -127,6 +127,33 @@ def _box_stack_states(mjm, nworld, seed):
   return qpos, np.zeros((nworld, mjm.nv)), np.zeros((nworld, mjm.nu))
 
 
+def _hfield_states(mjm, nworld, seed):
+  """Every free body dropped at a random spot of the terrain, a little into its surface (bilinear height at the spot), random
+  orientation; the bodies are kept apart from each other in x / y so that only terrain contacts arise."""
+  rng = np.random.default_rng(seed)
+  nb = mjm.nq // 7
+  size = np.asarray(mjm.hfield_size[0])
+  nrow, ncol = int(mjm.hfield_nrow[0]), int(mjm.hfield_ncol[0])
+  data = np.asarray(mjm.hfield_data).reshape(nrow, ncol)
+  gpos, gmat = np.asarray(mjm.geom_pos[0]), _quat_to_mat(np.asarray(mjm.geom_quat[0]))
+  qpos = np.zeros((nworld, mjm.nq))
+  for w in range(nworld):
+    cells = rng.permutation(6)[:nb]  # a 3 x 2 partition of the field, one body per cell
+    for b in range(nb):
+      cx, cy = cells[b] % 3, cells[b] // 3
+      lx = -size[0] + (cx + rng.uniform(0.3, 0.7)) * 2 * size[0] / 3
+      ly = -size[1] + (cy + rng.uniform(0.3, 0.7)) * 2 * size[1] / 2
+      fx, fy = (lx + size[0]) / (2 * size[0]) * (ncol - 1), (ly + size[1]) / (2 * size[1]) * (nrow - 1)
+      c0, r0 = min(int(fx), ncol - 2), min(int(fy), nrow - 2)
+      tx, ty = fx - c0, fy - r0
+      h = ((1 - tx) * (1 - ty) * data[r0, c0] + tx * (1 - ty) * data[r0, c0 + 1] + (1 - tx) * ty * data[r0 + 1, c0] + tx * ty * data[r0 + 1, c0 + 1]) * size[2]
+      p = gmat @ np.array([lx, ly, h + rng.uniform(0.02, 0.09)]) + gpos
+      q = rng.normal(size=4)
+      qpos[w, 7 * b : 7 * b + 3] = p
+      qpos[w, 7 * b + 3 : 7 * b + 7] = q / np.linalg.norm(q)
+  return qpos, np.zeros((nworld, mjm.nv)), np.zeros((nworld, mjm.nu))
+
+
 def _quat_to_mat(q):
   w, x, y, z = q / np.linalg.norm(q)
   return np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)],
@@ -237,6 +264,8 @@ CASES = {
   "apollo_step3": dict(model="apollo", nworld=3, seed=32, sink=0.03, mode="step", nstep=3, nconmax=16, njmax=64, states="humanoid", disable=["NATIVECCD"]),
   # box-box on the reference's DEFAULT route: GJK / EPA + multi-contact face clipping (flat faces 4 contacts, edge 2, corner 1)
   "box_stack_multicontact": dict(model="box_stack", nworld=12, seed=6, mode="forward", nconmax=32, njmax=160, states="box_stack"),
+  # height field against every convex geom type (collision_convex.py:56 _hfield_filter, :158 ccd_hfield_kernel)
+  "hfield_collision": dict(model="hfield", nworld=8, seed=14, mode="forward", nconmax=32, njmax=128, states="hfield"),
   "convex_pairs_collision": dict(model="convex_pairs", nworld=12, seed=4, mode="forward", nconmax=48, njmax=200, states="box_pairs"),
   "mesh_pairs_collision": dict(model="mesh_pairs", nworld=12, seed=9, mode="forward", nconmax=48, njmax=200, states="box_pairs"),
 }
@@ -279,6 +308,8 @@ def case_inputs(name):
     qpos, qvel, ctrl = _aloha_replay_states(mjm, c["nworld"], c["seed"])
   elif kind == "box_pairs":
     qpos, qvel, ctrl = _box_pair_states(mjm, c["nworld"], c["seed"])
+  elif kind == "hfield":
+    qpos, qvel, ctrl = _hfield_states(mjm, c["nworld"], c["seed"])
   elif kind == "box_stack":
     qpos, qvel, ctrl = _box_stack_states(mjm, c["nworld"], c["seed"])
   else:

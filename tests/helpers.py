@@ -241,3 +241,41 @@ def support_fill(rec, prefix, fields, assign):
   for f in fields:
     if prefix + f in rec:
       assign(f, rec[prefix + f])
+
+
+def match_contact_sets(ref, dev, nworld, atol_pos=1e-6, atol_dist=1e-7, atol_nrm=1e-6, strict=True):
+  """Compares two contact buffers as per-world, per-pair SETS of (dist, pos, normal): duplicates collapse and order is ignored.
+  Used where the reference's selection of a pair's contacts has rounding-level ties (height fields: two prisms of a cell report the
+  same contact, and which duplicate is kept is decided in the last bit).  `ref` / `dev`: dicts with nacon, contact_worldid, contact_geom,
+  contact_dist, contact_pos, contact_frame.  The touching pairs must be the same and the DEEPEST contact of every pair must match;
+  strict: every contact of either side must have a partner on the other.  Returns (matched reference contacts, reference contacts)."""
+  def unpack(o):
+    n = int(np.asarray(o["nacon"]).reshape(-1)[0])
+    return (np.asarray(o["contact_worldid"])[:n].reshape(-1), np.asarray(o["contact_geom"])[:n].reshape(n, 2), np.asarray(o["contact_dist"])[:n].reshape(-1),
+            np.asarray(o["contact_pos"])[:n].reshape(n, 3), np.asarray(o["contact_frame"])[:n].reshape(n, 9)[:, :3])  # fmt: skip
+
+  def err_to(b_d, b_p, b_n, d, p, n):
+    return np.maximum(np.abs(b_d - d) / atol_dist, np.maximum(np.abs(b_p - p).max(axis=1) / atol_pos, np.abs(b_n - n).max(axis=1) / atol_nrm))
+
+  rw, rg, rd, rp, rn = unpack(ref)
+  dw, dg, dd, dp, dn = unpack(dev)
+  matched = total = 0
+  for w in range(nworld):
+    pairs_r = {tuple(x) for x in rg[rw == w].tolist()}
+    pairs_d = {tuple(x) for x in dg[dw == w].tolist()}
+    assert pairs_r == pairs_d, (w, sorted(pairs_r ^ pairs_d))
+    for pair in pairs_r:
+      kr = (rw == w) & (rg == pair).all(axis=1)
+      kd = (dw == w) & (dg == pair).all(axis=1)
+      i0 = int(np.argmin(rd[kr]))  # the deepest contact is the minimum over all prisms: no selection involved
+      e0 = err_to(dd[kd], dp[kd], dn[kd], rd[kr][i0], rp[kr][i0], rn[kr][i0]).min()
+      assert e0 <= 1.0, (w, pair, "deepest contact", float(rd[kr][i0]), float(dd[kd].min()), float(e0))
+      for i in range(int(kr.sum())):
+        ok = err_to(dd[kd], dp[kd], dn[kd], rd[kr][i], rp[kr][i], rn[kr][i]).min() <= 1.0
+        assert ok or not strict, (w, pair, "ref->dev", float(rd[kr][i]), rp[kr][i].tolist())
+        matched += int(ok)
+        total += 1
+      if strict:
+        for i in range(int(kd.sum())):
+          assert err_to(rd[kr], rp[kr], rn[kr], dd[kd][i], dp[kd][i], dn[kd][i]).min() <= 1.0, (w, pair, "dev->ref", float(dd[kd][i]), dp[kd][i].tolist())
+  return matched, total

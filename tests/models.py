@@ -160,6 +160,27 @@ BOX_STACK_XML = """
   </worldbody>
 </mujoco>"""
 
+# a height field (inline elevations, 7 x 9 grid) under one free body of every convex type: hfield-vs-{sphere, capsule, ellipsoid,
+# cylinder, box, mesh} through the per-prism GJK / EPA of collision_convex.py:158
+HFIELD_XML = """
+<mujoco>
+  <option jacobian="dense"/>
+  <asset>
+    <hfield name="terrain" nrow="7" ncol="9" size="1.2 0.9 0.3 0.1"
+      elevation="0 1 2 3 2 1 0 1 2   1 2 3 4 3 2 1 2 3   2 3 5 6 5 3 2 3 4   1 2 4 7 4 2 1 2 3   0 1 3 5 3 1 0 1 2   1 1 2 3 2 1 1 2 2   2 1 1 2 1 1 2 3 1"/>
+    <mesh name="tetra" vertex="0 0 0.2  0.2 0 -0.08  -0.1 0.17 -0.08  -0.1 -0.17 -0.08"/>
+  </asset>
+  <worldbody>
+    <geom type="hfield" hfield="terrain" pos="0.1 -0.05 0.02" euler="0 0 15"/>
+    <body pos="0 0 1"><freejoint/><geom type="sphere" size=".12"/></body>
+    <body pos="0 0 1"><freejoint/><geom type="capsule" size=".06 .15"/></body>
+    <body pos="0 0 1"><freejoint/><geom type="box" size=".12 .08 .1"/></body>
+    <body pos="0 0 1"><freejoint/><geom type="ellipsoid" size=".14 .09 .07"/></body>
+    <body pos="0 0 1"><freejoint/><geom type="cylinder" size=".08 .1"/></body>
+    <body pos="0 0 1"><inertial pos="0 0 0" mass=".5" diaginertia=".01 .01 .01"/><freejoint/><geom type="mesh" mesh="tetra"/></body>
+  </worldbody>
+</mujoco>"""
+
 # every pair type of the convex (GJK / EPA) narrowphase plus the ellipsoid / cylinder primitives (collision_driver.py:43)
 CONVEX_PAIRS_XML = """
 <mujoco>
@@ -193,4 +214,4 @@ MESH_PAIRS_XML = """
   </worldbody>
 </mujoco>"""
 
-XML = dict(SMALL_MODELS, box_pairs=BOX_PAIRS_XML, box_stack=BOX_STACK_XML, convex_pairs=CONVEX_PAIRS_XML, mesh_pairs=MESH_PAIRS_XML)
+XML = dict(SMALL_MODELS, box_pairs=BOX_PAIRS_XML, box_stack=BOX_STACK_XML, hfield=HFIELD_XML, convex_pairs=CONVEX_PAIRS_XML, mesh_pairs=MESH_PAIRS_XML)

@@ -68,7 +68,7 @@ def tol_of(f, name):
 
 # box-box multi-contact: compared world by world below (an edge resting parallel to a face has no unique EPA witness, and which
 # polytope face the float32 EPA stops on decides whether the clipping finds the edge: one such world may keep a single contact)
-DEDICATED = ("box_stack_multicontact",)
+DEDICATED = ("box_stack_multicontact", "hfield_collision")
 
 
 @pytest.mark.parametrize("name", [n for n in RC.CASES if n not in DEDICATED])
@@ -139,3 +139,23 @@ def test_box_box_multicontact_matches_reference_execution():
       np.testing.assert_allclose(dev["frame"][kd].reshape(-1, 9)[:, :3], np.broadcast_to(ref["frame"][kr].reshape(-1, 9)[0, :3], (int(kd.sum()), 3)), atol=2e-3)
       compared += int(kr.sum())
   assert mismatched <= 1 and compared >= 50, (mismatched, compared)
+
+
+def test_hfield_contacts_match_reference_execution():
+  """Height field vs every convex geom type on the device (per-prism GJK / EPA, collision_convex.py:158): the distinct contacts of the
+  reference's execution are found to float32 tolerances (depth 2e-4: EPA stops on ccd_tolerance 1e-6 per prism, in float32)."""
+  name = "hfield_collision"
+  c = RC.CASES[name]
+  g = RC.load_golden(name)
+  mjm = RC.load_case_model(name)
+  m, d = H.device_data(mjw, mjm, g["in_qpos"], g["in_qvel"], g["in_ctrl"], c["nconmax"], c["njmax"])
+  mjw.kinematics(m, d)
+  mjw.com_pos(m, d)
+  mjw.collision(m, d)
+  torch.cuda.synchronize()
+  assert int(d.status.max()) == 0
+  dev = {f: H.dev_np(d, f) for f in ("nacon", "contact_worldid", "contact_geom", "contact_dist", "contact_pos", "contact_frame")}
+  # same touching pairs, the deepest contact of every pair matched; of the other (up to 3 per pair, chosen among the candidate prisms
+  # by distance-ranking rules with near-ties) at least 90 % must be the reference's choice
+  n, total = H.match_contact_sets(g, dev, c["nworld"], atol_pos=5e-4, atol_dist=2e-4, atol_nrm=5e-3, strict=False)
+  assert total >= 100 and n >= 0.9 * total, (n, total)
