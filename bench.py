@@ -39,6 +39,9 @@ CONFIGS = {
                       note="box-box pairs carry a margin: the reference's put_model only accepts this scene with DisableBit.NATIVECCD "
                            "(io.py:386-395), i.e. box-box through the box_box primitive, which is the route timed here"),
   "aloha_pot": dict(path="benchmarks/aloha_pot/scene.xml", nworld=4096, nconmax=24, njmax=128, replay="lift_pot"),
+  # not one of BASELINE.json's five configs (reference benchmarks/config.txt:18): the same robot on a 1121 x 588 height field; measured
+  # on request (--configs apollo_hfield), not part of the default line
+  "apollo_hfield": dict(path="benchmarks/apptronik_apollo/scene_hfield.xml", nworld=4096, nconmax=32, njmax=128, replay=None, disable=("NATIVECCD",)),
 }
 # Algorithmic traffic of each stage-group kernel: Data fields it must read (produced by an earlier
 # kernel or the caller) and fields it defines, write-once/read-once, capacity-sized for the pooled /
@@ -600,7 +603,7 @@ def main():
   # ---- BASELINE.json configs 3-5 (rank 0 only, one GPU: they are reported per GPU; the worlds shard like the humanoid's)
   secondary = {}
   if rank == 0:
-    for name in ("panda", "apollo_flat", "aloha_pot"):
+    for name in [k for k in CONFIGS if k != "humanoid"]:
       if name in blocks:
         secondary[name] = bench_secondary(name, CONFIGS[name]["nworld"], max(20, min(K, 100)), W, rank, peak,
                                           with_cpu=(not args.no_cpu_baseline and world == 1), nthread=nthread)

@@ -551,6 +551,56 @@ class MjModelLite(SimpleNamespace):
     )
 
 
+def save_model(mjm: MjModelLite, path: str) -> None:
+  """Writes a compiled host model to one .npz file (the on-disk model cache: compiling aloha_pot's 133 meshes -- hulls, mass
+  properties, hill-climbing graphs -- takes seconds, loading the cache milliseconds).  Arrays are stored as they are; scalars, name
+  lists and the option / statistic blocks travel in one JSON entry.  `load_model` restores an identical MjModelLite."""
+  import json
+
+  arrays, meta = {}, {"scalars": {}, "lists": {}, "ns": {}}
+  for k, v in vars(mjm).items():
+    if isinstance(v, np.ndarray):
+      arrays["a/" + k] = v
+    elif isinstance(v, SimpleNamespace):
+      meta["ns"][k] = {}
+      for kk, vv in vars(v).items():
+        if isinstance(vv, np.ndarray):
+          arrays[f"n/{k}/{kk}"] = vv
+        else:
+          meta["ns"][k][kk] = vv
+    elif isinstance(v, (list, tuple)):
+      meta["lists"][k] = list(v)
+    elif isinstance(v, (int, float, str, bool, np.integer, np.floating)) or v is None:
+      meta["scalars"][k] = v.item() if isinstance(v, (np.integer, np.floating)) else v
+    else:
+      raise TypeError(f"save_model: field {k} of type {type(v).__name__} is not serialisable")
+  arrays["meta"] = np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8)
+  with open(path, "wb") as fh:
+    np.savez_compressed(fh, **arrays)
+
+
+def load_model(path: str) -> MjModelLite:
+  """Reads a model written by `save_model`."""
+  import json
+
+  with np.load(path) as z:
+    meta = json.loads(bytes(z["meta"]).decode())
+    m = MjModelLite()
+    for k, v in meta["scalars"].items():
+      setattr(m, k, v)
+    for k, v in meta["lists"].items():
+      setattr(m, k, v)
+    for k, d in meta["ns"].items():
+      setattr(m, k, SimpleNamespace(**d))
+    for name in z.files:
+      if name.startswith("a/"):
+        setattr(m, name[2:], z[name])
+      elif name.startswith("n/"):
+        _, k, kk = name.split("/", 2)
+        setattr(getattr(m, k), kk, z[name])
+  return m
+
+
 def load_mjcf(path: str) -> MjModelLite:
   """Parse and compile an MJCF file."""
   tree = ET.parse(path)

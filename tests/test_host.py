@@ -278,3 +278,30 @@ def test_data_field_numel_matches_make_data(humanoid):
   sizes.update(d._sizes)
   for n in list(types.DATA_INT_FIELDS) + list(types.DATA_REAL_FIELDS):
     assert types.data_field_numel(n, sizes) == d.field(n).numel(), n
+
+
+def test_model_cache_round_trip(tmp_path):
+  """save_model / load_model: the .npz model cache restores a host model whose every kernel table is identical."""
+  import os
+  import time
+
+  from mujoco_warp_b200 import io as _io
+
+  path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "benchmarks", "aloha_pot", "scene.xml")
+  t0 = time.time()
+  mjm = mjw.load_mjcf(path)
+  t_compile = time.time() - t0
+  f = str(tmp_path / "aloha.npz")
+  mjw.save_model(mjm, f)
+  t0 = time.time()
+  back = mjw.load_model(f)
+  t_load = time.time() - t0
+  a, b = _io.host_model(mjm), _io.host_model(back)
+  assert a.sizes == b.sizes
+  for k in a.ints:
+    np.testing.assert_array_equal(a.ints[k], b.ints[k], err_msg=k)
+  for k in a.reals:
+    np.testing.assert_array_equal(a.reals[k], b.reals[k], err_msg=k)
+  assert back.key_names == mjm.key_names and float(back.opt.timestep) == float(mjm.opt.timestep)
+  np.testing.assert_array_equal(back.keyframe("lift_pot0").qpos, mjm.keyframe("lift_pot0").qpos)
+  assert t_load < t_compile
