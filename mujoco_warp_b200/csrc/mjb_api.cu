@@ -359,9 +359,14 @@ static int resolve_cfg(int g, int variant, const MjbModel* m, MjbData* d) {
   MjbData::GroupCfg& c = group_cfg(d, g, variant);
   if (c.ready) return 0;
   const int wpw = 32 / group_lw(g);  // worlds per warp
-  int wpb = warps_per_block(g == G_SOL ? group_threads(G_SOL) / 32 : wpw > 1 ? 4 : 8);
+  int wpb = warps_per_block(g == G_SOL ? group_threads(G_SOL) / 32 : wpw > 1 ? MJB_LW_WPB : 8);
   if (32 * wpb > group_threads(g)) wpb = group_threads(g) / 32;
   c.scratch_floats = group_scratch_floats(g, m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad, m->ms.ngeom, m->ms.nxn, variant, m->ms.ngroup);
+  // fewer warps per CTA when the per-world scratch of a large model would not fit beside the model tables
+  {
+    const size_t blob = group_uses_blob(g) && m->blob_hot <= 96 * 1024 ? (size_t)m->blob_hot + 16 : 0;
+    while (wpb > 1 && (size_t)wpb * wpw * c.scratch_floats * sizeof(float) + blob > (size_t)d->smem_optin) wpb--;
+  }
   const size_t scr_bytes = (size_t)wpb * wpw * c.scratch_floats * sizeof(float);
   const bool in_smem =
       group_uses_blob(g) && (size_t)m->blob_hot + 16 + scr_bytes <= (size_t)d->smem_optin && m->blob_hot <= 96 * 1024;

@@ -77,7 +77,7 @@ __host__ __device__ inline int group_scratch_floats(int g, int nv, int nv_pad, i
 #endif
 __host__ __device__ inline bool group_uses_blob(int g) { return g != G_SOL; }
 // lanes per world of a group's kernel (worlds per warp = 32 / lanes)
-__host__ __device__ constexpr int group_lw(int g) { return (g == G_POS || g == G_VEL || g == G_EUL) ? MJB_SMOOTH_LW : 32; }
+__host__ __device__ constexpr int group_lw(int g) { return g == G_POS ? MJB_POS_LW : g == G_VEL ? MJB_VEL_LW : g == G_EUL ? MJB_EUL_LW : 32; }
 
 // Stages the model blob into shared memory with one TMA bulk copy (cp.async.bulk, completion on
 // an mbarrier).  All threads of the CTA wait on the barrier's phase 0.

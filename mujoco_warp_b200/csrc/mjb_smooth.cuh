@@ -18,10 +18,11 @@
 // the lane inside the world's group and every loop strides by MJB_LW.  The tree recursions keep 2-3 lanes busy per level whatever
 // the group width, so narrower groups execute several worlds for the price of one; control flow in these stages depends on the
 // model only, so the groups of a warp stay convergent and __syncwarp() keeps its full mask.  Set per translation unit.
-// Measured on B200 (humanoid, 8192 worlds, 7 warps per CTA so that all worlds are resident in one wave): 8 lanes per world
-// smooth_position 69 -> 80 us, smooth_velocity 111 -> 95 us, euler 20 -> 18 us.  The stages are chains of dependent global-memory
-// round trips (parent poses, subtree sums, ancestor walks); with a quarter of the warps in flight those latencies are no longer
-// hidden, which cancels the saved instructions.  The default therefore stays at one warp per world (MJB_SMOOTH_LW = 32).
+// Measured on B200 (humanoid, 8192 worlds), 8 lanes per world and 7 warps (28 worlds) per CTA against one warp per world:
+// smooth_position 69 -> 80 us, smooth_velocity 111 -> 95 us, euler 20 -> 17 us; 16 lanes: 115 us; 4 or 8 warps per CTA: 153 / 132 us.
+// The stages are chains of dependent global-memory round trips (parent poses, subtree sums, ancestor walks): the narrower groups
+// save instructions but leave fewer warps in flight to hide those latencies, so the gain depends on the stage.  Defaults
+// (mjb_types.cuh): smooth_velocity and euler 8 lanes per world, smooth_position 32.  panda (8192 worlds): 29.0 -> 37.4 M env-steps/s.
 #ifndef MJB_LW
 #define MJB_LW 32
 #endif

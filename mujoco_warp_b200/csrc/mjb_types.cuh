@@ -18,6 +18,19 @@
 #ifndef MJB_SMOOTH_LW
 #define MJB_SMOOTH_LW 32
 #endif
+// per group (default: the common value); MJB_LW_WPB = warps per CTA of a group that carries several worlds per warp
+#ifndef MJB_POS_LW
+#define MJB_POS_LW MJB_SMOOTH_LW
+#endif
+#ifndef MJB_VEL_LW
+#define MJB_VEL_LW 8  // measured (B200, humanoid 8192 worlds): smooth_velocity 111 -> 95 us with 8 lanes per world and 7 warps per CTA
+#endif
+#ifndef MJB_EUL_LW
+#define MJB_EUL_LW 8  // euler 20 -> 17 us
+#endif
+#ifndef MJB_LW_WPB
+#define MJB_LW_WPB 7  // warps per CTA of those groups (28 worlds per CTA); 4 warps: 153 us
+#endif
 
 #define MJ_MINVAL 1e-15f
 #define MJ_MAXVAL 1e10f

@@ -800,6 +800,13 @@ def _tile_view(t, offset, shape=None, **kw):
   return a[tuple(sl)].view(Tile)
 
 
+def _tile_transpose(t):
+  """A VIEW of the tile: block_cholesky.py:60 solves in place into `wp.tile_transpose(A_ik_tile)` and then stores A_ik_tile."""
+  v = np.asarray(t).T.view(Tile)
+  v._etype = getattr(t, "_etype", None)
+  return v
+
+
 def _tile_assign(dst, src, offset):
   offset = _shape_t(offset)
   d, s = np.asarray(dst), np.asarray(src)
@@ -1022,7 +1029,7 @@ def build():
   wp.tile_cholesky, wp.tile_cholesky_solve = _cholesky, _tile_cholesky_solve
   wp.tile_lower_solve_inplace, wp.tile_upper_solve_inplace = _tile_lower_solve_inplace, _tile_upper_solve_inplace
   wp.tile_matmul = _tile_matmul
-  wp.tile_transpose = lambda t: _tile(np.asarray(t).T)
+  wp.tile_transpose = _tile_transpose
   wp.tile_map, wp.tile_reduce = _tile_map, _tile_reduce
   wp.tile_sum = lambda t: _tile(np.asarray([np.asarray(t).sum()]))
   wp.tile_zeros, wp.tile_ones = _tile_ctor(0), _tile_ctor(1)
