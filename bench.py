@@ -42,6 +42,8 @@ CONFIGS = {
   # not one of BASELINE.json's five configs (reference benchmarks/config.txt:18): the same robot on a 1121 x 588 height field; measured
   # on request (--configs apollo_hfield), not part of the default line
   "apollo_hfield": dict(path="benchmarks/apptronik_apollo/scene_hfield.xml", nworld=4096, nconmax=32, njmax=128, replay=None, disable=("NATIVECCD",)),
+  # reference benchmarks/config.txt:22 (nv = 81: the reference's sparse path; stored dense here), on request (--configs three_humanoids)
+  "three_humanoids": dict(path="benchmarks/humanoid/three_humanoids.xml", nworld=8192, nconmax=100, njmax=192, replay=None),
 }
 # Algorithmic traffic of each stage-group kernel: Data fields it must read (produced by an earlier
 # kernel or the caller) and fields it defines, write-once/read-once, capacity-sized for the pooled /

@@ -43,6 +43,7 @@
   X(jnt_type) X(jnt_qposadr) X(jnt_dofadr) X(jnt_bodyid) X(jnt_limited_adr) X(jnt_limited_ball_adr) \
   X(jnt_actfrclimited) X(jnt_actgravcomp) \
   X(dof_bodyid) X(dof_jntid) X(dof_parentid) X(dof_friction_adr) \
+  X(dof_tree0) /* first dof of the dof's kinematic tree: row i of qM is zero left of it (envelope of the factorisations) */ \
   X(geom_type) X(geom_bodyid) X(geom_condim) X(geom_priority) X(geom_static) \
   X(site_bodyid) \
   X(nxn_pair) X(nxn_pairid) \

@@ -60,7 +60,7 @@ struct MjbData {
   struct GroupCfg {  // launch configuration of one stage-group kernel, resolved on first use
     int ready, wpb, grid, in_smem, scratch_floats;
     size_t smem;
-  } cfg[G_COUNT + COLF_COUNT + 2];  // [G_COUNT + v]: collision variant v > 0; last two: elliptic make_constraint / solve
+  } cfg[G_COUNT + COLF_COUNT + 4];  // [G_COUNT + v]: collision variant v > 0; then elliptic make_constraint / solve, wide smooth_velocity / euler
 };
 
 // ---- field-table introspection --------------------------------------------------------------
@@ -140,9 +140,9 @@ extern "C" int mjb_model_create(const int* sizes, int nsizes, const void* blob, 
     delete m;
     return fail(-3, "sparse models are not implemented");
   }
-  if (m->ms.nv > 64) {
+  if (m->ms.nv > 128) {
     delete m;
-    return fail(-3, "nv > 64 is not implemented");
+    return fail(-3, "nv > 128 is not implemented");
   }
   m->blob = static_cast<const unsigned char*>(blob);
   m->blob_bytes = (int)nbytes;
@@ -335,9 +335,9 @@ static GroupKernel group_kernel_of(int g, bool in_smem, int variant) {
     case G_POS: return mjb_gk_pos(in_smem);
     case G_COL: return variant == COLF_COUNT - 1 ? mjb_gk_col_convex(in_smem) : mjb_gk_col(in_smem, variant);
     case G_CON: return mjb_gk_con(in_smem, variant);
-    case G_VEL: return mjb_gk_vel(in_smem);
+    case G_VEL: return variant ? mjb_gk_vel_wide(in_smem) : mjb_gk_vel(in_smem);
     case G_SOL: return mjb_gk_sol(in_smem, variant);
-    default: return mjb_gk_eul(in_smem);
+    default: return variant ? mjb_gk_eul_wide(in_smem) : mjb_gk_eul(in_smem);
   }
 }
 
@@ -348,17 +348,18 @@ static int group_variant(int g, const MjbModel* m, int broadphase, int cone, int
     const bool convex = (m->col_feat & COLF_CONVEX) || (m->has_boxbox && !(disableflags & DSBL_NATIVECCD));
     return convex ? COLF_COUNT - 1 : (m->col_feat | (broadphase != 0 ? COLF_SAP : 0));
   }
+  if (g == G_VEL || g == G_EUL) return m->ms.nv > 32 ? 1 : 0;  // one warp per world for the large dense factorisations
   return ((g == G_CON || g == G_SOL) && cone == 1) ? 1 : 0;
 }
 static MjbData::GroupCfg& group_cfg(MjbData* d, int g, int variant) {
-  return d->cfg[!variant ? g : g == G_COL ? G_COUNT + variant : G_COUNT + COLF_COUNT + (g == G_CON ? 0 : 1)];
+  return d->cfg[!variant ? g : g == G_COL ? G_COUNT + variant : G_COUNT + COLF_COUNT + (g == G_CON ? 0 : g == G_SOL ? 1 : g == G_VEL ? 2 : 3)];
 }
 // resolves (once) the launch configuration of a group kernel: CTA width, shared memory, resident grid.  Sets function attributes and
 // queries occupancy, so it must not run under stream capture: mjb_prepare() calls it ahead of time.
 static int resolve_cfg(int g, int variant, const MjbModel* m, MjbData* d) {
   MjbData::GroupCfg& c = group_cfg(d, g, variant);
   if (c.ready) return 0;
-  const int wpw = 32 / group_lw(g);  // worlds per warp
+  const int wpw = 32 / group_lw(g, variant);  // worlds per warp
   int wpb = warps_per_block(g == G_SOL ? group_threads(G_SOL) / 32 : wpw > 1 ? MJB_LW_WPB : 8);
   if (32 * wpb > group_threads(g)) wpb = group_threads(g) / 32;
   c.scratch_floats = group_scratch_floats(g, m->ms.nv, m->ms.nv_pad, d->dsz.njmax_pad, m->ms.ngeom, m->ms.nxn, variant, m->ms.ngroup);

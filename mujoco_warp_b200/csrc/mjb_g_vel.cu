@@ -1,4 +1,4 @@
-// mjb_g_vel.cu -- instantiations of the `smooth_velocity` stage-group kernel (see mjb_groups.h)
+// mjb_g_vel.cu -- instantiations of the `smooth_velocity` stage-group kernel (see mjb_groups.h): several worlds per warp
 #define MJB_UNIT_GROUP 3
 #include "mjb_groups.h"
 #define MJB_LW MJB_VEL_LW

@@ -11,8 +11,10 @@ GroupKernel mjb_gk_col(bool in_smem, int variant);  // primitive-only variants: 
 GroupKernel mjb_gk_col_convex(bool in_smem);        // all features (GJK / EPA, meshes)
 GroupKernel mjb_gk_con(bool in_smem, int variant);  // variant 1: elliptic cones
 GroupKernel mjb_gk_vel(bool in_smem);
+GroupKernel mjb_gk_vel_wide(bool in_smem);  // one warp per world (nv > 32)
 GroupKernel mjb_gk_sol(bool in_smem, int variant);  // variant 1: elliptic cones
 GroupKernel mjb_gk_eul(bool in_smem);
+GroupKernel mjb_gk_eul_wide(bool in_smem);
 // small utility kernels (mjb_g_util.cu)
 cudaError_t mjb_util_solve_m_smem(size_t smem);
 void mjb_util_solve_m(const KParams& K, int grid, int threads, size_t smem, cudaStream_t stream);

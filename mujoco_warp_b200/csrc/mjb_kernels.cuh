@@ -77,7 +77,11 @@ __host__ __device__ inline int group_scratch_floats(int g, int nv, int nv_pad, i
 #endif
 __host__ __device__ inline bool group_uses_blob(int g) { return g != G_SOL; }
 // lanes per world of a group's kernel (worlds per warp = 32 / lanes)
-__host__ __device__ constexpr int group_lw(int g) { return g == G_POS ? MJB_POS_LW : g == G_VEL ? MJB_VEL_LW : g == G_EUL ? MJB_EUL_LW : 32; }
+// lanes per world of a group kernel; variant 1 of smooth_velocity / euler is the one-warp-per-world build used for models with nv > 32
+// (their dense factorisations want all 32 lanes)
+__host__ __device__ constexpr int group_lw(int g, int v = 0) {
+  return g == G_POS ? MJB_POS_LW : g == G_VEL ? (v ? 32 : MJB_VEL_LW) : g == G_EUL ? (v ? 32 : MJB_EUL_LW) : 32;
+}
 
 // Stages the model blob into shared memory with one TMA bulk copy (cp.async.bulk, completion on
 // an mbarrier).  All threads of the CTA wait on the barrier's phase 0.
@@ -137,7 +141,7 @@ __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group
   // broadcast from lane 0 so that the compiler can treat the warp index (and every loop / branch
   // that depends on it) as warp-uniform
   // A warp carries WPW = 32 / LW worlds (LW lanes each); `lane` is the lane inside the world's group.
-  constexpr int LW = group_lw(G), WPW = 32 / LW;
+  constexpr int LW = group_lw(G, V), WPW = 32 / LW;
   static_assert(LW == 32 || LW == MJB_LW, "a sub-warp group kernel must be compiled with MJB_LW = its lane count");
   const int lane32 = threadIdx.x & 31, lane = lane32 % LW, grp = lane32 / LW;
   const int warp = __shfl_sync(FULL, threadIdx.x >> 5, 0), wpb = blockDim.x >> 5;
@@ -162,7 +166,7 @@ __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group
       if (st & MJB_STAGE_KINEMATICS) s_kinematics(K, mb, w, lane);
       if (st & MJB_STAGE_COM_POS) s_com_pos(K, mb, w, lane);
       if (st & MJB_STAGE_CRB) s_crb(K, mb, w, lane);
-      if (st & MJB_STAGE_FACTOR_M) s_factor_m(K, w, lane, scr);
+      if (st & MJB_STAGE_FACTOR_M) s_factor_m(K, mb, w, lane, scr);
       if (st & MJB_STAGE_TRANSMISSION) s_transmission(K, mb, w, lane);
     }
 #endif

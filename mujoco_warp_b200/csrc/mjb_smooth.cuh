@@ -413,7 +413,10 @@ static __device__ __noinline__ void warp_chol_solve_reg(const float* L, int ld, 
 
 __device__ __forceinline__ float dot4(const float4 a, const float4 b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
 
-static __device__ __noinline__ void warp_cholesky_blk(float* A, int ld, int n, float* rdiag, int lane) {
+// `env` (optional): env[i] = first column of row i that can be non-zero (the matrix's envelope: block-diagonal mass matrices of
+// several kinematic trees, Hessians whose constraint rows touch few trees).  A Cholesky factor keeps the envelope, so the row
+// updates start there and rows whose envelope begins right of a block column skip it: three 27-dof trees cost 3 x 27^3 instead of 81^3.
+static __device__ __noinline__ void warp_cholesky_blk(float* A, int ld, int n, float* rdiag, int lane, const int* env = nullptr) {
   const int nb = (n + 3) >> 2;
   #pragma unroll 1
   for (int J = 0; J < nb; J++) {
@@ -428,10 +431,12 @@ static __device__ __noinline__ void warp_cholesky_blk(float* A, int ld, int n, f
     #pragma unroll 1
     for (int i = lane; i < n; i += MJB_LW) {
       if (i < c0) continue;
+      const int e = env ? env[i] : 0;
+      if (e > c0 + 3) continue;  // the row is zero in this block column
       float4* own = reinterpret_cast<float4*>(A + i * ld);
       float4 acc = own[J];
       #pragma unroll 1
-      for (int q = 0; q < J; q++) {
+      for (int q = e >> 2; q < J; q++) {
         const float4 o = own[q];
         acc.x -= dot4(o, p0[q]);
         acc.y -= dot4(o, p1[q]);
@@ -455,6 +460,7 @@ static __device__ __noinline__ void warp_cholesky_blk(float* A, int ld, int n, f
     #pragma unroll 1
     for (int i = lane; i < n; i += MJB_LW) {
       if (i < c0) continue;
+      if (env && env[i] > c0 + 3) continue;
       float4* own = reinterpret_cast<float4*>(A + i * ld);
       const float4 a = own[J];
       const int m = i - c0;  // position inside the diagonal block (>= 4: below it)
@@ -505,7 +511,7 @@ __device__ __forceinline__ void chol_rdiag(const float* L, int ld, int n, float*
 // x <- (L L^T)^-1 x with L and x in shared memory (x padded to a multiple of 4 entries).
 // Blocked substitution: the 4x4 diagonal systems are solved redundantly by all lanes, the
 // off-diagonal part is one strip (forward: 128-bit row load, backward: four column loads) per lane.
-static __device__ __noinline__ void warp_chol_solve_blk(const float* L, int ld, int n, const float* rdiag, float* x, int lane) {
+static __device__ __noinline__ void warp_chol_solve_blk(const float* L, int ld, int n, const float* rdiag, float* x, int lane, const int* env = nullptr) {
   const int nb = (n + 3) >> 2;
   float4* x4 = reinterpret_cast<float4*>(x);
   #pragma unroll 1
@@ -523,7 +529,10 @@ static __device__ __noinline__ void warp_chol_solve_blk(const float* L, int ld, 
     __syncwarp();
     if (lane == 0) x4[J] = y;
     #pragma unroll 1
-    for (int i = 4 * J + 4 + lane; i < n; i += MJB_LW) x[i] -= dot4(reinterpret_cast<const float4*>(L + i * ld)[J], y);
+    for (int i = 4 * J + 4 + lane; i < n; i += MJB_LW) {
+      if (env && env[i] > 4 * J + 3) continue;
+      x[i] -= dot4(reinterpret_cast<const float4*>(L + i * ld)[J], y);
+    }
     __syncwarp();
   }
   #pragma unroll 1
@@ -543,8 +552,9 @@ static __device__ __noinline__ void warp_chol_solve_blk(const float* L, int ld, 
     const float* q2 = L + min(c0 + 2, n - 1) * ld;
     const float* q3 = L + min(c0 + 3, n - 1) * ld;
     // rows past n have z == 0 there (identity padding), so the aliased loads contribute nothing
+    const int i0 = env ? min(min(env[c0], env[min(c0 + 1, n - 1)]), min(env[min(c0 + 2, n - 1)], env[min(c0 + 3, n - 1)])) : 0;
     #pragma unroll 1
-    for (int i = lane; i < c0; i += MJB_LW) x[i] -= q0[i] * z.x + q1[i] * z.y + q2[i] * z.z + q3[i] * z.w;
+    for (int i = i0 + lane; i < c0; i += MJB_LW) x[i] -= q0[i] * z.x + q1[i] * z.y + q2[i] * z.z + q3[i] * z.w;
     __syncwarp();
   }
 }
@@ -553,9 +563,9 @@ static __device__ __noinline__ void warp_chol_solve_blk(const float* L, int ld, 
 // used by the solver kernel.  REG = false: blocked shared-memory variant with rolled loops (compact code,
 // few registers): used by the smooth-dynamics kernels, where occupancy matters more.
 template <bool REG>
-__device__ __forceinline__ void warp_cholesky(float* A, int ld, int n, float* rdiag, int lane) {
+__device__ __forceinline__ void warp_cholesky(float* A, int ld, int n, float* rdiag, int lane, const int* env = nullptr) {
   if (!REG) {
-    warp_cholesky_blk(A, ld, n, rdiag, lane);
+    warp_cholesky_blk(A, ld, n, rdiag, lane, env);
     return;
   }
   switch ((n + 3) >> 2) {
@@ -571,9 +581,9 @@ __device__ __forceinline__ void warp_cholesky(float* A, int ld, int n, float* rd
   }
 }
 template <bool REG>
-__device__ __forceinline__ void warp_chol_solve(const float* L, int ld, int n, const float* rdiag, float* x, int lane) {
+__device__ __forceinline__ void warp_chol_solve(const float* L, int ld, int n, const float* rdiag, float* x, int lane, const int* env = nullptr) {
   if (!REG) {
-    warp_chol_solve_blk(L, ld, n, rdiag, x, lane);
+    warp_chol_solve_blk(L, ld, n, rdiag, x, lane, env);
     return;
   }
   switch ((n + 3) >> 2) {
@@ -639,11 +649,15 @@ __device__ __forceinline__ void store_qLD(const KParams& K, int w, int lane, con
   }
 }
 
+// envelope of the mass matrix and of everything with its sparsity (qM - dt qDeriv, qM + dt diag): rows start at their tree's first
+// dof.  Only worth the extra loads when there is more than a warp's worth of dofs.
+__device__ __forceinline__ const int* mass_env(const KParams& K, const unsigned char* mb) { return K.ms.nv > 32 ? MI(dof_tree0) : nullptr; }
+
 // smooth.factor_m dense (smooth.py:1091-1109): qLD = chol(qM).
-__device__ __forceinline__ void s_factor_m(const KParams& K, int w, int lane, float* scr) {
+__device__ __forceinline__ void s_factor_m(const KParams& K, const unsigned char* mb, int w, int lane, float* scr) {
   const CholScr s = chol_scr(scr, K.ms.nv, K.ms.nv_pad);
   load_rows(s.L, s.ld, DW(qM), K.ms.nv_pad, K.ms.nv, lane, nullptr, 0.f);
-  warp_cholesky<false>(s.L, s.ld, K.ms.nv, s.rd, lane);
+  warp_cholesky<false>(s.L, s.ld, K.ms.nv, s.rd, lane, mass_env(K, mb));
   store_qLD(K, w, lane, s.L, s.ld);
   __syncwarp();
 }
@@ -944,14 +958,14 @@ __device__ __forceinline__ void s_fwd_acceleration(const KParams& K, const unsig
   __syncwarp();
   if (factorize) {
     load_rows(s.L, s.ld, DW(qM), K.ms.nv_pad, nv, lane, nullptr, 0.f);
-    warp_cholesky<false>(s.L, s.ld, nv, s.rd, lane);
+    warp_cholesky<false>(s.L, s.ld, nv, s.rd, lane, mass_env(K, mb));
     store_qLD(K, w, lane, s.L, s.ld);
   } else {
     load_rows(s.L, s.ld, DW(qLD), nv, nv, lane, nullptr, 0.f);
     chol_rdiag(s.L, s.ld, nv, s.rd, lane);
   }
   __syncwarp();
-  warp_chol_solve<false>(s.L, s.ld, nv, s.rd, x, lane);
+  warp_chol_solve<false>(s.L, s.ld, nv, s.rd, x, lane, mass_env(K, mb));
   for (int i = lane; i < nv; i += MJB_LW) DW(qacc_smooth)[i] = x[i];
   __syncwarp();
 }
@@ -1008,10 +1022,10 @@ __device__ __forceinline__ void s_integrate(const KParams& K, const unsigned cha
         __syncwarp();
       }
     }
-    warp_cholesky<false>(s.L, s.ld, nv, s.rd, lane);
+    warp_cholesky<false>(s.L, s.ld, nv, s.rd, lane, mass_env(K, mb));
     for (int i = lane; i < nv; i += MJB_LW) x[i] = DW(efc_Ma)[i];
     __syncwarp();
-    warp_chol_solve<false>(s.L, s.ld, nv, s.rd, x, lane);
+    warp_chol_solve<false>(s.L, s.ld, nv, s.rd, x, lane, mass_env(K, mb));
   } else {
     for (int i = lane; i < nv; i += MJB_LW) x[i] = DW(qacc)[i];
     __syncwarp();

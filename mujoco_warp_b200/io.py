@@ -22,6 +22,7 @@ from . import constants as C
 from . import types
 
 _NV_MAX_DENSE = 60  # reference io.py:142
+_NV_MAX = 128  # this library: dense storage for every model, the per-world Hessian and its factor live in shared memory
 
 
 # ----------------------------------------------------------------------------------------------
@@ -92,8 +93,11 @@ def _check_supported(mjm):
   if mjm.nv > _NV_MAX_DENSE and int(mjm.opt.jacobian) == C.JacobianType.DENSE:
     raise ValueError(f"Dense is unsupported for nv > {_NV_MAX_DENSE} (nv = {mjm.nv}).")
   # features of the reference that this library does not implement yet (scope)
-  if is_sparse(mjm):
-    raise NotImplementedError("sparse mass matrix / Jacobian (nv > 32 or jacobian=sparse) is not implemented yet.")
+  # Models the reference stores sparse (nv > 32 under jacobian=auto, or jacobian=sparse) are accepted and stored DENSE here: qM, qLD
+  # and efc.J keep their dense shapes (Model.is_sparse is False), every other field is identical.  One warp per world with the
+  # Hessian in shared memory bounds nv.
+  if mjm.nv > _NV_MAX:
+    raise NotImplementedError(f"nv > {_NV_MAX} is not implemented (nv = {mjm.nv}).")
   for name in ("ntendon", "nflex"):
     if getattr(mjm, name, 0):
       raise NotImplementedError(f"{name} > 0 is not implemented yet.")
@@ -194,6 +198,12 @@ def host_model(mjm) -> SimpleNamespace:
   ints["jnt_limited_adr"] = np.nonzero(limited & np.isin(jnt_type, (C.JointType.SLIDE, C.JointType.HINGE)))[0].astype(i32)
   ints["jnt_limited_ball_adr"] = np.nonzero(limited & (jnt_type == C.JointType.BALL))[0].astype(i32)
   ints["dof_friction_adr"] = np.nonzero(reals["dof_frictionloss"] > 0)[0].astype(i32)
+  tree0 = np.arange(nv, dtype=i32)  # first dof of the dof's kinematic tree (parents precede children)
+  for i in range(nv):
+    p = int(ints["dof_parentid"][i])
+    if p >= 0:
+      tree0[i] = tree0[p]
+  ints["dof_tree0"] = tree0
   ints["eq_objtype"] = np.asarray(getattr(mjm, "eq_objtype", np.ones(int(mjm.neq)))).astype(i32).reshape(-1)  # mjtObj: 1 body, 3 joint, 6 site
   ints["eq_jnt_adr"] = np.nonzero(ints["eq_type"] == C.EqType.JOINT)[0].astype(i32)
   ints["eq_connect_adr"] = np.nonzero(ints["eq_type"] == C.EqType.CONNECT)[0].astype(i32)  # reference io.py:445-446
@@ -350,8 +360,8 @@ def host_model(mjm) -> SimpleNamespace:
     jt = int(jnt_type[ints["actuator_trnid"][a, 0]])
     nJmom += 6 if jt == C.JointType.FREE else (3 if jt == C.JointType.BALL else 1)
 
-  sparse = is_sparse(mjm)
-  nv_pad = _get_padded_sizes(nv, 0, sparse, types.TILE_SIZE_JTDAJ_SPARSE if sparse else types.TILE_SIZE_JTDAJ_DENSE)[1]
+  sparse = False  # storage is dense for every model (see _check_supported); padded sizes do not depend on it (both tile sizes are 16)
+  nv_pad = _get_padded_sizes(nv, 0, is_sparse(mjm), types.TILE_SIZE_JTDAJ_SPARSE if sparse else types.TILE_SIZE_JTDAJ_DENSE)[1]
   nmaxcondim = int(np.concatenate(([0], ints["geom_condim"], ints["pair_dim"])).max())
   sizes = dict(
     nq=int(mjm.nq), nv=nv, nu=nu, na=int(mjm.na), nbody=nbody, njnt=njnt, ngeom=ngeom, nsite=int(mjm.nsite),

@@ -528,6 +528,183 @@ def _expand_includes(root, basedir):
           changed = True
 
 
+_NAME_REFS = ("joint", "joint1", "joint2", "body", "body1", "body2", "geom", "geom1", "geom2", "site", "site1", "site2", "target",
+              "jointinparent", "tendon", "objname", "refname")  # attributes that hold the name of another element
+
+
+def _rename_tree(elem, fn_name, fn_class):
+  """Applies fn_name to every name / name reference and fn_class to every class reference below (and at) elem."""
+  for e in elem.iter():
+    if "name" in e.attrib:
+      e.set("name", fn_name(e.get("name")))
+    for k in _NAME_REFS:
+      if k in e.attrib:
+        e.set(k, fn_name(e.get(k)))
+    for k in ("class", "childclass"):
+      if k in e.attrib:
+        e.set(k, fn_class(e.get(k)))
+
+
+def _expand_replicate(root):
+  """<replicate count offset euler sep>: N copies of the children, copy i inside a <frame> moved by the accumulated offset / rotation,
+  names (and the references to them inside the copy) suffixed with sep + i.  <attach> children remember the suffix for _expand_attach."""
+  import copy
+
+  while True:
+    hit = next(((p, c) for p in root.iter() for c in p if c.tag == "replicate"), None)
+    if hit is None:
+      return
+    parent, rep = hit
+    count = int(rep.get("count"))
+    sep = rep.get("sep", "")
+    width = len(str(count - 1))
+    idx = list(parent).index(rep)
+    parent.remove(rep)
+    local = {e.get("name") for e in rep.iter() if "name" in e.attrib}
+    for i in range(count):
+      suffix = sep + str(i).zfill(width)
+      fr = ET.Element("frame")
+      fr.set("_rep_offset", rep.get("offset", "0 0 0"))
+      fr.set("_rep_euler", rep.get("euler", "0 0 0"))
+      fr.set("_rep_index", str(i))
+      for child in rep:
+        c = copy.deepcopy(child)
+        _rename_tree(c, lambda n: n + suffix if n in local else n, lambda k: k)
+        for a in c.iter("attach"):  # includes c itself
+          a.set("_suffix", a.get("_suffix", "") + suffix)
+        fr.append(c)
+      parent.insert(idx + i, fr)
+
+
+def _expand_attach(root, basedir):
+  """<attach model body prefix>: the named body of a sub-model (<asset><model file>) is copied in place with prefixed names, together
+  with the sub-model's default classes and the actuators / contact pairs and excludes / equalities that refer to the copied subtree."""
+  import copy
+
+  models = {m.get("name", os.path.splitext(os.path.basename(m.get("file")))[0]): m.get("file") for a in root.findall("asset") for m in a.findall("model")}
+  subs = {}
+  done_defaults = set()
+  while True:
+    hit = next(((p, c) for p in root.iter() for c in p if c.tag == "attach"), None)
+    if hit is None:
+      break
+    parent, att = hit
+    mname, prefix, suffix = att.get("model"), att.get("prefix", ""), att.get("_suffix", "")
+    if mname not in subs:
+      path = os.path.join(basedir, models[mname])
+      sub = ET.parse(path).getroot()
+      _expand_includes(sub, os.path.dirname(path))
+      _expand_structure(sub, os.path.dirname(path))
+      for tag in ("compiler",):
+        if [dict(c.attrib) for c in sub.findall(tag)] != [dict(c.attrib) for c in root.findall(tag)]:
+          raise NotImplementedError("<attach>: sub-model and parent must use the same <compiler> settings")
+      subs[mname] = sub
+    sub = subs[mname]
+    body = next((b for b in sub.iter("body") if b.get("name") == att.get("body")), None)
+    if body is None:
+      raise ValueError(f"<attach>: body {att.get('body')!r} not found in model {mname!r}")
+    inside = {e.get("name") for e in body.iter() if "name" in e.attrib}
+    fn_name = lambda n: prefix + n + suffix if n in inside else n  # noqa: E731
+    fn_class = lambda k: prefix + k  # noqa: E731
+    main = prefix + "main"
+    if (mname, prefix) not in done_defaults:  # the sub-model's class tree, once, below the parent's main class
+      done_defaults.add((mname, prefix))
+      top = root.find("default")
+      if top is None:
+        top = ET.Element("default")
+        root.insert(0, top)
+      holder = ET.SubElement(top, "default")
+      holder.set("class", main)
+      for d in sub.findall("default"):
+        for e in d:
+          c = copy.deepcopy(e)
+          for n in c.iter("default"):  # includes c itself
+            n.set("class", prefix + n.get("class"))
+          for n in c.iter():
+            if n.tag != "default" and "class" in n.attrib:
+              n.set("class", prefix + n.get("class"))
+          holder.append(c)
+    b = copy.deepcopy(body)
+    _rename_tree(b, fn_name, fn_class)
+    if "childclass" not in b.attrib:
+      b.set("childclass", main)
+    idx = list(parent).index(att)
+    parent.remove(att)
+    parent.insert(idx, b)
+    for sec in ("actuator", "contact", "equality"):
+      for src in sub.findall(sec):
+        for e in src:
+          refs = [e.get(k) for k in _NAME_REFS if k in e.attrib]
+          if not refs or not all(r in inside or r == "world" for r in refs) or not any(r in inside for r in refs):
+            continue
+          c = copy.deepcopy(e)
+          if "name" in c.attrib:
+            c.set("name", prefix + c.get("name") + suffix)
+          for k in _NAME_REFS:
+            if k in c.attrib:
+              c.set(k, fn_name(c.get(k)))
+          c.set("class", prefix + c.get("class") if "class" in c.attrib else main)
+          dst = root.find(sec)
+          if dst is None:
+            dst = ET.SubElement(root, sec)
+          dst.append(c)
+  for a in root.findall("asset"):
+    for m in a.findall("model"):
+      a.remove(m)
+
+
+def _expand_frames(root, comp):
+  """<frame pos quat|euler|...>: a pure coordinate transform, folded into the pose of its children (bodies, geoms, sites, nested
+  frames; cameras and lights are not compiled).  Replicate frames carry their accumulated offset / rotation."""
+  while True:
+    hit = next(((p, c) for p in root.iter() for c in p if c.tag == "frame"), None)
+    if hit is None:
+      return
+    parent, fr = hit
+    fpos = _vec(fr.get("pos"), 3, [0, 0, 0])
+    fquat = _orientation(fr.attrib, comp)
+    if "_rep_index" in fr.attrib:  # copy i of a replicate: i accumulated steps of (offset, euler)
+      dq = _orientation({"euler": fr.get("_rep_euler")}, comp)
+      off = _vec(fr.get("_rep_offset"), 3)
+      fpos, fquat = np.zeros(3), np.array([1.0, 0, 0, 0])
+      for _ in range(int(fr.get("_rep_index"))):
+        fpos = fpos + rot_vec_quat(off, fquat)
+        fquat = quat_mul(fquat, dq)
+    idx = list(parent).index(fr)
+    parent.remove(fr)
+    for j, c in enumerate(list(fr)):
+      if c.tag in ("body", "geom", "site", "frame", "camera", "light"):
+        if "fromto" in c.attrib:
+          ft = _vec(c.get("fromto"), 6)
+          a, b = fpos + rot_vec_quat(ft[:3], fquat), fpos + rot_vec_quat(ft[3:], fquat)
+          c.set("fromto", " ".join(repr(float(x)) for x in np.concatenate([a, b])))
+        else:
+          cpos = _vec(c.get("pos"), 3, [0, 0, 0])
+          cquat = _orientation(c.attrib, comp)
+          for k in ("quat", "axisangle", "euler", "xyaxes", "zaxis"):
+            c.attrib.pop(k, None)
+          c.set("pos", " ".join(repr(float(x)) for x in fpos + rot_vec_quat(cpos, fquat)))
+          c.set("quat", " ".join(repr(float(x)) for x in quat_mul(fquat, cquat)))
+        if "childclass" in fr.attrib and c.tag in ("body", "frame") and "childclass" not in c.attrib:
+          c.set("childclass", fr.get("childclass"))
+      parent.insert(idx + j, c)
+
+
+def _expand_structure(root, basedir):
+  """Model-composition elements of MJCF, rewritten into plain bodies before compilation: <replicate>, <attach>, <frame>."""
+  if not any(e.tag in ("replicate", "attach", "frame") for e in root.iter()):
+    return
+  comp = _Compiler()
+  for c in root.findall("compiler"):
+    if "angle" in c.attrib:
+      comp.degree = c.get("angle") == "degree"
+    if "eulerseq" in c.attrib:
+      comp.eulerseq = c.get("eulerseq")
+  _expand_replicate(root)
+  _expand_attach(root, basedir)
+  _expand_frames(root, comp)
+
+
 def _bool(s, default=False):
   if s is None:
     return default
@@ -606,12 +783,14 @@ def load_mjcf(path: str) -> MjModelLite:
   tree = ET.parse(path)
   root = tree.getroot()
   _expand_includes(root, os.path.dirname(os.path.abspath(path)))
+  _expand_structure(root, os.path.dirname(os.path.abspath(path)))
   return _compile(root, os.path.dirname(os.path.abspath(path)))
 
 
 def load_mjcf_string(xml: str, basedir: str = ".") -> MjModelLite:
   root = ET.fromstring(xml)
   _expand_includes(root, basedir)
+  _expand_structure(root, basedir)
   return _compile(root, basedir)
 
 

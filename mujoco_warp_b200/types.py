@@ -78,6 +78,7 @@ MODEL_INT_FIELDS = {
   "dof_jntid": ("nv",),
   "dof_parentid": ("nv",),
   "dof_friction_adr": ("nfrictiondof",),
+  "dof_tree0": ("nv",),
   "geom_type": ("ngeom",),
   "geom_bodyid": ("ngeom",),
   "geom_condim": ("ngeom",),

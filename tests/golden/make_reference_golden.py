@@ -65,7 +65,40 @@ def run_reference(name):
     out["efc_" + f] = np.array(getattr(d.efc, f).numpy())
   for f in CON_REAL + CON_INT:
     out["contact_" + f] = np.array(getattr(d.contact, f).numpy())
+  if m.is_sparse:
+    _densify(m, d, mjm, out)
   return out
+
+
+def _densify(m, d, mjm, out):
+  """A model the reference stores sparse: qM (legacy format: dof_Madr + the walk up dof_parentid, smooth.py crb) and efc.J (rows as
+  rownnz / rowadr / colind) are stored DENSE in the fixture, which is the layout this library keeps for every model; qLD (sparse
+  L^T D L factor) has no dense-Cholesky counterpart and is left out."""
+  nv, nworld, njmax = int(mjm.nv), out["qM"].shape[0], int(d.njmax)
+  madr, parent = np.asarray(mjm.dof_Madr), np.asarray(mjm.dof_parentid)
+  qM = np.zeros((nworld, nv, nv))
+  src = out["qM"].reshape(nworld, -1)
+  for i in range(nv):
+    adr, j = int(madr[i]), i
+    while j >= 0:
+      qM[:, i, j] = qM[:, j, i] = src[:, adr]
+      adr, j = adr + 1, int(parent[j])
+  out["qM"] = qM
+  J = np.zeros((nworld, int(d.njmax_pad), int(m.nv_pad)))  # the dense path's padded shape (io.py:650)
+  val = out["efc_J"].reshape(nworld, -1)
+  rownnz, rowadr = d.efc.J_rownnz.numpy(), d.efc.J_rowadr.numpy()
+  colind = d.efc.J_colind.numpy().reshape(nworld, -1)
+  for w in range(nworld):
+    for r in range(int(out["nefc"][w])):
+      a, n = int(rowadr[w, r]), int(rownnz[w, r])
+      J[w, r, colind[w, a : a + n]] = val[w, a : a + n]
+  out["efc_J"] = J
+  out["efc_J_rownnz"] = np.array(rownnz)
+  del out["qLD"]
+  # solver.py:2189 zeroes qfrc_constraint of ALL worlds on every solver iteration of the sparse path, while the kernel that refills it
+  # (:1955) skips worlds that already converged: a world that finishes before the slowest one ends up with qfrc_constraint = 0.  An
+  # artefact of which worlds share a batch, not a property of the world: left out (J^T efc_force is checked through efc_J and efc_force).
+  del out["qfrc_constraint"]
 
 
 def main(argv):

@@ -45,6 +45,15 @@ def _states(mjm, nworld, seed, sink=0.0, key_first=True):
   return qpos, qvel, ctrl
 
 
+def _multi_root_states(mjm, nworld, seed, sink=0.0):
+  """make_states on a model without keyframes (several floating trees); every free root is lowered by `sink` in all worlds but the first."""
+  qpos, qvel, ctrl = H.make_states(mjm, nworld, seed=seed)
+  for j in range(mjm.njnt):
+    if int(mjm.jnt_type[j]) == 0:
+      qpos[1:, int(mjm.jnt_qposadr[j]) + 2] -= sink
+  return qpos, qvel, ctrl
+
+
 def _small_states(mjm, nworld, seed):
   rng = np.random.default_rng(seed)
   qpos = np.repeat(np.asarray(mjm.qpos0, dtype=np.float64)[None], nworld, axis=0)
@@ -266,6 +275,10 @@ CASES = {
   "box_stack_multicontact": dict(model="box_stack", nworld=12, seed=6, mode="forward", nconmax=32, njmax=160, states="box_stack"),
   # height field against every convex geom type (collision_convex.py:56 _hfield_filter, :158 ccd_hfield_kernel)
   "hfield_collision": dict(model="hfield", nworld=8, seed=14, mode="forward", nconmax=32, njmax=128, states="hfield"),
+  # nv = 81: the reference stores qM / qLD / efc.J sparse and factorises the Hessian in 16 x 16 blocks (solver.py:2758, block_cholesky.py);
+  # the generator stores qM and efc.J densified (make_reference_golden.py), qLD (sparse L^T D L) is not comparable with a Cholesky factor
+  "three_humanoids_forward": dict(model="three_humanoids", nworld=2, seed=41, sink=0.06, mode="forward", nconmax=48, njmax=192, states="multi_root"),
+  "three_humanoids_step2": dict(model="three_humanoids", nworld=2, seed=42, sink=0.04, mode="step", nstep=2, nconmax=48, njmax=192, states="multi_root"),
   "convex_pairs_collision": dict(model="convex_pairs", nworld=12, seed=4, mode="forward", nconmax=48, njmax=200, states="box_pairs"),
   "mesh_pairs_collision": dict(model="mesh_pairs", nworld=12, seed=9, mode="forward", nconmax=48, njmax=200, states="box_pairs"),
 }
@@ -274,6 +287,8 @@ CASES = {
 def load_model(key):
   if key == "humanoid":
     return mjw.load_mjcf(H.HUMANOID)
+  if key == "three_humanoids":
+    return mjw.load_mjcf(os.path.join(ROOT, "benchmarks", "humanoid", "three_humanoids.xml"))
   if key == "aloha":
     return mjw.load_mjcf(os.path.join(ROOT, "benchmarks", "aloha_pot", "scene.xml"))
   if key == "apollo":
@@ -300,6 +315,8 @@ def case_inputs(name):
   kind = c.get("states", "humanoid" if c["model"] == "humanoid" else "small")
   if kind == "humanoid":
     qpos, qvel, ctrl = _states(mjm, c["nworld"], c["seed"], c.get("sink", 0.0))
+  elif kind == "multi_root":
+    qpos, qvel, ctrl = _multi_root_states(mjm, c["nworld"], c["seed"], c.get("sink", 0.0))
   elif kind == "panda":
     qpos, qvel, ctrl = _panda_states(mjm, c["nworld"], c["seed"])
   elif kind == "aloha":

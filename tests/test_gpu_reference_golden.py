@@ -40,7 +40,9 @@ _CCD_TOL = {"contact_dist": 1e-3, "efc_pos": 1e-3, "contact_pos": 2e-3, "contact
 # aloha_pot (config 5): mesh contacts through the float32 GJK / EPA; polyhedral hulls pin the normal far better than the smooth shapes above
 # (measured on B200: contact_frame <= 2.8e-4, everything else inside the generic tolerances, solver outputs INCLUDED)
 _ALOHA_TOL = {"contact_frame": 1e-3}
-CASE_TOL = {"convex_pairs_collision": _CCD_TOL, "mesh_pairs_collision": _CCD_TOL, "aloha_pot_forward": _ALOHA_TOL, "aloha_pot_step3": _ALOHA_TOL,
+# nv = 81, 49 bodies: cfrc_int accumulates the subtree forces of three 16-body trees into the world body in float32 (measured 3.0e-4)
+_LARGE_NV_TOL = {"cfrc_int": 1e-3}
+CASE_TOL = {"three_humanoids_forward": _LARGE_NV_TOL, "three_humanoids_step2": _LARGE_NV_TOL, "convex_pairs_collision": _CCD_TOL, "mesh_pairs_collision": _CCD_TOL, "aloha_pot_forward": _ALOHA_TOL, "aloha_pot_step3": _ALOHA_TOL,
             "aloha_pot_cg_forward": _ALOHA_TOL, "aloha_lift_pot_replay20": _ALOHA_TOL}  # fmt: skip
 CASE_SKIP_SOLVER = ("convex_pairs_collision", "mesh_pairs_collision")
 FACTOR_FIELDS = ("qacc_smooth", "qLD")

@@ -81,7 +81,6 @@ def test_make_data_rejects_bad_sizes(humanoid, kwargs, msg):
 
 
 UNSUPPORTED = [
-  ('<option jacobian="sparse"/>', "sparse"),
   ('<option solver="PGS"/>', "PGS"),
   ('<option integrator="implicit"/>', "IMPLICIT"),
   ('<option noslip_iterations="2"/>', "noslip"),
@@ -94,6 +93,50 @@ def test_put_model_rejects_unsupported_features(snippet, msg):
   mjm = mjw.load_mjcf_string(xml)
   with pytest.raises(NotImplementedError, match=msg):
     mjw.put_model(mjm, device="cpu")
+
+
+def test_sparse_eligible_models_are_accepted_and_stored_dense():
+  """Models the reference stores sparse (jacobian=sparse, or nv > 32 under auto: io.py:67) keep the dense shapes of qM / qLD / efc.J."""
+  xml = """<mujoco><option jacobian="sparse"/><worldbody><body><joint type="slide"/><geom type="sphere" size=".1"/></body></worldbody></mujoco>"""
+  mjm = mjw.load_mjcf_string(xml)
+  assert mio.is_sparse(mjm)
+  m = mjw.put_model(mjm, device="cpu")
+  assert m.is_sparse is False
+  d = mjw.make_data(mjm, nworld=2, nconmax=4, njmax=8, device="cpu")
+  assert tuple(d.qM.shape) == (2, m.sizes["nv_pad"], m.sizes["nv_pad"]) and d.efc.J.dim() == 3 and d.efc.J.shape[2] == m.sizes["nv_pad"]
+
+
+def test_replicate_attach_frame_are_expanded():
+  """benchmarks/humanoid/three_humanoids.xml: <replicate> of a <frame> holding an <attach> of humanoid.xml's torso.  Three copies of the
+  humanoid's tree, defaults, actuators; copy i rotated by i * 16.36 degrees about z at radius 4."""
+  import os
+
+  from tests import helpers as H
+
+  one = mjw.load_mjcf(H.HUMANOID)
+  three = mjw.load_mjcf(os.path.join(os.path.dirname(H.HUMANOID), "three_humanoids.xml"))
+  assert (three.nv, three.nq, three.nu, three.nbody, three.ngeom) == (3 * one.nv, 3 * one.nq, 3 * one.nu, 3 * (one.nbody - 1) + 1, 3 * (one.ngeom - 1) + 1)
+  assert mio.is_sparse(three) and not mio.is_sparse(one)
+  nb = one.nbody - 1
+  for i in range(3):
+    a = np.deg2rad(16.36 * i)
+    np.testing.assert_allclose(three.body_pos[1 + nb * i], [4 * np.sin(a), -4 * np.cos(a), 1.282], atol=1e-12)
+    np.testing.assert_allclose(three.body_quat[1 + nb * i], [np.cos(a / 2), 0, 0, np.sin(a / 2)], atol=1e-12)
+    np.testing.assert_allclose(three.body_mass[1 + nb * i : 1 + nb * (i + 1)], one.body_mass[1:], rtol=1e-12)
+    np.testing.assert_allclose(three.dof_damping[one.nv * i : one.nv * (i + 1)], one.dof_damping)
+    np.testing.assert_allclose(three.dof_invweight0[one.nv * i : one.nv * (i + 1)], one.dof_invweight0, rtol=1e-9)
+    np.testing.assert_allclose(three.actuator_gear[one.nu * i : one.nu * (i + 1)], one.actuator_gear)
+    np.testing.assert_array_equal(three.actuator_trnid[one.nu * i : one.nu * (i + 1), 0], one.actuator_trnid[:, 0] + one.njnt * i)
+    np.testing.assert_allclose(three.jnt_range[one.njnt * i : one.njnt * (i + 1)], one.jnt_range)
+  assert len(set(three.names_body)) == three.nbody if hasattr(three, "names_body") else True
+  # an offset replicate of plain geoms, and a nested frame
+  xml = """<mujoco><worldbody>
+    <replicate count="3" offset="1 0 0" sep="_"><geom name="g" type="sphere" size=".1" pos="0 2 0"/></replicate>
+    <frame pos="0 0 1" euler="0 0 90"><frame pos="1 0 0"><body name="b" pos="0 1 0"><joint type="slide"/><geom type="sphere" size=".1"/></body></frame></frame>
+  </worldbody></mujoco>"""
+  mjm = mjw.load_mjcf_string(xml)
+  np.testing.assert_allclose(mjm.geom_pos[:3], [[0, 2, 0], [1, 2, 0], [2, 2, 0]], atol=1e-12)
+  np.testing.assert_allclose(mjm.body_pos[1], [-1, 1, 1], atol=1e-12)  # R_z(90) (1, 1, 0) + (0, 0, 1)
 
 
 def test_mesh_geoms_without_assets_are_rejected_and_every_pair_is_accepted():
