@@ -416,7 +416,16 @@ __device__ __forceinline__ float dot4(const float4 a, const float4 b) { return a
 // `env` (optional): env[i] = first column of row i that can be non-zero (the matrix's envelope: block-diagonal mass matrices of
 // several kinematic trees, Hessians whose constraint rows touch few trees).  A Cholesky factor keeps the envelope, so the row
 // updates start there and rows whose envelope begins right of a block column skip it: three 27-dof trees cost 3 x 27^3 instead of 81^3.
-static __device__ __noinline__ void warp_cholesky_blk(float* A, int ld, int n, float* rdiag, int lane, const int* env = nullptr) {
+// MJB_CHOL_ENV = 0 (set by the solver's translation unit, whose dense Hessians have no fixed envelope) compiles the argument away.
+#ifndef MJB_CHOL_ENV
+#define MJB_CHOL_ENV 1
+#endif
+static __device__ __noinline__ void warp_cholesky_blk(float* A, int ld, int n, float* rdiag, int lane, const int* env_arg = nullptr) {
+#if MJB_CHOL_ENV
+  const int* env = env_arg;
+#else
+  constexpr const int* env = nullptr;
+#endif
   const int nb = (n + 3) >> 2;
   #pragma unroll 1
   for (int J = 0; J < nb; J++) {
@@ -511,7 +520,12 @@ __device__ __forceinline__ void chol_rdiag(const float* L, int ld, int n, float*
 // x <- (L L^T)^-1 x with L and x in shared memory (x padded to a multiple of 4 entries).
 // Blocked substitution: the 4x4 diagonal systems are solved redundantly by all lanes, the
 // off-diagonal part is one strip (forward: 128-bit row load, backward: four column loads) per lane.
-static __device__ __noinline__ void warp_chol_solve_blk(const float* L, int ld, int n, const float* rdiag, float* x, int lane, const int* env = nullptr) {
+static __device__ __noinline__ void warp_chol_solve_blk(const float* L, int ld, int n, const float* rdiag, float* x, int lane, const int* env_arg = nullptr) {
+#if MJB_CHOL_ENV
+  const int* env = env_arg;
+#else
+  constexpr const int* env = nullptr;
+#endif
   const int nb = (n + 3) >> 2;
   float4* x4 = reinterpret_cast<float4*>(x);
   #pragma unroll 1
@@ -651,7 +665,13 @@ __device__ __forceinline__ void store_qLD(const KParams& K, int w, int lane, con
 
 // envelope of the mass matrix and of everything with its sparsity (qM - dt qDeriv, qM + dt diag): rows start at their tree's first
 // dof.  Only worth the extra loads when there is more than a warp's worth of dofs.
-__device__ __forceinline__ const int* mass_env(const KParams& K, const unsigned char* mb) { return K.ms.nv > 32 ? MI(dof_tree0) : nullptr; }
+__device__ __forceinline__ const int* mass_env(const KParams& K, const unsigned char* mb) {
+#if MJB_CHOL_ENV
+  return K.ms.nv > 32 ? MI(dof_tree0) : nullptr;
+#else
+  return nullptr;
+#endif
+}
 
 // smooth.factor_m dense (smooth.py:1091-1109): qLD = chol(qM).
 __device__ __forceinline__ void s_factor_m(const KParams& K, const unsigned char* mb, int w, int lane, float* scr) {
