@@ -201,6 +201,78 @@ __device__ __forceinline__ void cone_hessian(const KParams& K, int w, int lane, 
 
 // H(lower) += sum_r coef[r] * J[r]^T J[r], register tiles of 4 rows x 8 columns per lane over
 // 32x32 blocks (solver.py:2368 JTDAJ and :2055 incremental update in one routine).
+#ifndef MJB_SOL_HTRI
+#define MJB_SOL_HTRI 1
+#endif
+#if MJB_SOL_HTRI
+// Lower triangle only, in 4 x 4 tiles: tile t = bi (bi + 1) / 2 + bj (bj <= bi) belongs to lane t % 32, so a 27-dof model keeps 28
+// lanes busy with 16 useful FMAs per constraint row each (the 32 x 32-block mapping below spends 32 FMAs per lane on 20 lanes, half
+// of them above the diagonal).  Per element the rows are added in the same order as before: results are bit-identical.
+__device__ __forceinline__ void h_accumulate(const KParams& K, int w, int lane, const SolverScr& s, int nefc) {
+  const int nv = K.ms.nv, np = K.ms.nv_pad, ld = s.ld;
+  const float* J = DW(efc_J);
+  const int nb = (nv + 3) >> 2, ntile = (nb * (nb + 1)) >> 1;
+  const int nefc2 = (nefc + 1) & ~1;
+  MJB_ROLL
+  for (int t0 = 0; t0 < ntile; t0 += 32) {
+    const int t = t0 + lane;
+    const bool need = t < ntile;
+    int bi = (int)((sqrtf(8.f * (float)t + 1.f) - 1.f) * 0.5f);
+    if (((bi + 1) * (bi + 2)) >> 1 <= t) bi++;
+    if ((bi * (bi + 1)) >> 1 > t) bi--;
+    const int r0 = 4 * bi, c0 = 4 * (t - ((bi * (bi + 1)) >> 1));
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int j = 0; j < 4; j++) acc[i][j] = 0.f;
+    // two rows per iteration: the four 128-bit loads are issued before the 32 FMAs
+    MJB_ROLL
+    for (int r = 0; r < nefc2; r += 2) {
+      const float cf0 = s.coef[r], cf1 = (r + 1 < nefc) ? s.coef[r + 1] : 0.f;
+      if (cf0 == 0.f && cf1 == 0.f) continue;  // warp-uniform
+      if (need) {
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float* Jr0 = J + (size_t)r * np;
+        const float* Jr1 = J + (size_t)min(r + 1, nefc - 1) * np;
+        const bool u0 = cf0 != 0.f, u1 = cf1 != 0.f;
+        const float4 ji0 = u0 ? *reinterpret_cast<const float4*>(Jr0 + r0) : z4;
+        const float4 jj0 = u0 ? *reinterpret_cast<const float4*>(Jr0 + c0) : z4;
+        const float4 ji1 = u1 ? *reinterpret_cast<const float4*>(Jr1 + r0) : z4;
+        const float4 jj1 = u1 ? *reinterpret_cast<const float4*>(Jr1 + c0) : z4;
+        {
+          const float vi[4] = {ji0.x * cf0, ji0.y * cf0, ji0.z * cf0, ji0.w * cf0};
+          const float vj[4] = {jj0.x, jj0.y, jj0.z, jj0.w};
+#pragma unroll
+          for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int j = 0; j < 4; j++) acc[i][j] += vi[i] * vj[j];
+        }
+        {
+          const float vi[4] = {ji1.x * cf1, ji1.y * cf1, ji1.z * cf1, ji1.w * cf1};
+          const float vj[4] = {jj1.x, jj1.y, jj1.z, jj1.w};
+#pragma unroll
+          for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int j = 0; j < 4; j++) acc[i][j] += vi[i] * vj[j];
+        }
+      }
+    }
+    if (need) {  // whole tiles with 128-bit accesses; in a diagonal tile the elements above the diagonal get their symmetric values
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        if (r0 + i < nv) {
+          float4* h = reinterpret_cast<float4*>(s.H + (r0 + i) * ld + c0);
+          float4 v = h[0];
+          v.x += acc[i][0]; v.y += acc[i][1]; v.z += acc[i][2]; v.w += acc[i][3];
+          h[0] = v;
+        }
+      }
+    }
+  }
+  __syncwarp();
+}
+#else
 __device__ __forceinline__ void h_accumulate(const KParams& K, int w, int lane, const SolverScr& s, int nefc) {
   const int nv = K.ms.nv, np = K.ms.nv_pad, ld = s.ld;
   const float* J = DW(efc_J);
@@ -284,6 +356,8 @@ __device__ __forceinline__ void h_accumulate(const KParams& K, int w, int lane, 
   }
   __syncwarp();
 }
+
+#endif  // MJB_SOL_HTRI
 
 // The same update on the tensor cores: H(lower) += A B with A[m][k] = coef[k] J[k][m] (16 x 8 tiles) and B[k][n] = J[k][n] (8 x 8),
 // mma.sync m16n8k8 TF32 with the 3xTF32 split (a = a_hi + a_lo, products hi*hi + hi*lo + lo*hi, FP32 accumulate), which keeps the
