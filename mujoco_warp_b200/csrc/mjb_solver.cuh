@@ -496,30 +496,48 @@ __device__ __forceinline__ void update_constraint(const KParams& K, int w, int l
   any_change = __any_sync(FULL, changed);
   any_cone = ELL ? __any_sync(FULL, cone) : false;
   __syncwarp();
-  // qfrc_constraint = J^T force (solver.py:1988): lane = dof; four rows per iteration so that four
-  // independent (coalesced) global loads are in flight; groups of rows without force are skipped
+  // qfrc_constraint = J^T force (solver.py:1988).  Lane = (128-bit column group c, row group gi): the G = 4 / 2 / 1 lanes of a
+  // column group sit next to each other and take every G-th row, four rows per trip with their 128-bit loads issued together; rows
+  // without force multiply by zero instead of branching.  A 27-dof model: 7 column groups x 4 row groups = 28 lanes.
   const float* J = DW(efc_J);
-  const int nefc4 = (nefc + 3) & ~3, rlast = K.dsz.njmax - 1;
-  for (int r = nefc + lane; r < nefc4; r += 32) s.force[r] = 0.f;
-  __syncwarp();
+  const int n4 = np >> 2;
+  const int sh = n4 <= 8 ? 2 : n4 <= 16 ? 1 : 0, G = 1 << sh;
+  const int rlast = nefc - 1;  // rows past nefc may hold anything: never loaded, their force is zero
   float g = 0.f;
-  for (int i0 = 0; i0 < nv; i0 += 32) {
-    const int i = i0 + lane;
-    const float* Jc = J + (i < nv ? i : 0);
-    float q = 0.f;
+  MJB_ROLL
+  for (int cb = 0; cb < n4; cb += 32 >> sh) {
+    const int c = cb + (lane >> sh), gi = lane & (G - 1);
+    const bool cin = c < n4;
+    const float4* Jc = reinterpret_cast<const float4*>(J) + (cin ? c : 0);
+    float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
     MJB_ROLL
-    for (int r = 0; r < nefc4; r += 4) {
-      const float4 f = *reinterpret_cast<const float4*>(s.force + r);
-      if (f.x == 0.f && f.y == 0.f && f.z == 0.f && f.w == 0.f) continue;  // warp-uniform
-      const float j0 = Jc[(size_t)r * np], j1 = Jc[(size_t)min(r + 1, rlast) * np], j2 = Jc[(size_t)min(r + 2, rlast) * np],
-                  j3 = Jc[(size_t)min(r + 3, rlast) * np];
-      q += (f.x != 0.f ? j0 * f.x : 0.f) + (f.y != 0.f ? j1 * f.y : 0.f) + (f.z != 0.f ? j2 * f.z : 0.f) + (f.w != 0.f ? j3 * f.w : 0.f);
+    for (int r = gi; r < nefc; r += 4 * G) {
+      const int r1 = r + G, r2 = r + 2 * G, r3 = r + 3 * G;
+      const float f0 = s.force[r], f1 = r1 < nefc ? s.force[r1] : 0.f, f2 = r2 < nefc ? s.force[r2] : 0.f, f3 = r3 < nefc ? s.force[r3] : 0.f;
+      const float4 j0 = Jc[(size_t)r * n4], j1 = Jc[(size_t)min(r1, rlast) * n4], j2 = Jc[(size_t)min(r2, rlast) * n4], j3 = Jc[(size_t)min(r3, rlast) * n4];  // clamped rows were written this step
+      q.x += j0.x * f0 + j1.x * f1 + j2.x * f2 + j3.x * f3;
+      q.y += j0.y * f0 + j1.y * f1 + j2.y * f2 + j3.y * f3;
+      q.z += j0.z * f0 + j1.z * f1 + j2.z * f2 + j3.z * f3;
+      q.w += j0.w * f0 + j1.w * f1 + j2.w * f2 + j3.w * f3;
     }
-    if (i < nv) {
-      DW(qfrc_constraint)[i] = q;
-      // grad = Ma - qfrc_smooth - qfrc_constraint (solver.py:2238)
-      s.grad[i] = s.Ma[i] - s.qfs[i] - q;
-      g += (s.Ma[i] - s.qfs[i]) * (s.qacc[i] - DW(qacc_smooth)[i]);
+    for (int o = 1; o < G; o <<= 1) {
+      q.x += __shfl_xor_sync(FULL, q.x, o);
+      q.y += __shfl_xor_sync(FULL, q.y, o);
+      q.z += __shfl_xor_sync(FULL, q.z, o);
+      q.w += __shfl_xor_sync(FULL, q.w, o);
+    }
+    if (cin && gi == 0) {
+      const float qq[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const int i = 4 * c + k;
+        if (i < nv) {
+          DW(qfrc_constraint)[i] = qq[k];
+          // grad = Ma - qfrc_smooth - qfrc_constraint (solver.py:2238)
+          s.grad[i] = s.Ma[i] - s.qfs[i] - qq[k];
+          g += (s.Ma[i] - s.qfs[i]) * (s.qacc[i] - DW(qacc_smooth)[i]);
+        }
+      }
     }
   }
   gauss = 0.5f * warp_sum(g);
