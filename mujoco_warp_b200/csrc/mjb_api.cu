@@ -343,12 +343,21 @@ static GroupKernel group_kernel_of(int g, bool in_smem, int variant) {
 
 // kernel variant of a group under the given options: collision follows the model's pair types and the broadphase option of THIS
 // call; make_constraint / solve are compiled once per cone type
-static int group_variant(int g, const MjbModel* m, int broadphase, int cone, int disableflags) {
+static int group_variant(int g, const MjbModel* m, const MjbData* d, int broadphase, int cone, int disableflags) {
   if (g == G_COL) {
     const bool convex = (m->col_feat & COLF_CONVEX) || (m->has_boxbox && !(disableflags & DSBL_NATIVECCD));
     return convex ? COLF_COUNT - 1 : (m->col_feat | (broadphase != 0 ? COLF_SAP : 0));
   }
-  if (g == G_VEL || g == G_EUL) return m->ms.nv > 32 ? 1 : 0;  // one warp per world for the large dense factorisations
+  if (g == G_VEL || g == G_EUL) {
+    // Several worlds per warp (variant 0) save instructions but leave a quarter of the warps to hide the latencies of these stages: it
+    // pays once the GPU is full.  Measured on B200 (148 SMs), humanoid: 1024 worlds 240 -> 205 us/step with one warp per world (variant
+    // 1), 2048: 266 -> 236, 4096: equal, 8192: 564 -> 541 the other way; apollo and panda cross at the same place.  nv > 32 always takes
+    // the wide build (dense factorisations want all lanes).  MJB_SMOOTH_WIDE = 0 / 1 forces the choice.
+    static const int force = getenv("MJB_SMOOTH_WIDE") ? atoi(getenv("MJB_SMOOTH_WIDE")) : -1;
+    if (m->ms.nv > 32) return 1;
+    if (force >= 0) return force;
+    return d->dsz.nworld < 42 * d->nsm ? 1 : 0;
+  }
   return ((g == G_CON || g == G_SOL) && cone == 1) ? 1 : 0;
 }
 static MjbData::GroupCfg& group_cfg(MjbData* d, int g, int variant) {
@@ -390,7 +399,7 @@ static int resolve_cfg(int g, int variant, const MjbModel* m, MjbData* d) {
 }
 
 static int launch_group(int g, const MjbModel* m, MjbData* d, KParams& K, uint32_t stages, cudaStream_t stream) {
-  const int variant = group_variant(g, m, K.o.broadphase, K.o.cone, K.o.disableflags);
+  const int variant = group_variant(g, m, d, K.o.broadphase, K.o.cone, K.o.disableflags);
   {
     const int rc = resolve_cfg(g, variant, m, d);
     if (rc) return rc;
@@ -476,7 +485,7 @@ extern "C" int mjb_step(const MjbModel* m, MjbData* d, const MjbOption* opt, voi
 extern "C" int mjb_prepare(const MjbModel* m, MjbData* d, const MjbOption* opt) {
   if (!m || !d || !opt) return fail(-1, "null handle");
   for (int g = 0; g < G_COUNT; g++) {
-    const int rc = resolve_cfg(g, group_variant(g, m, opt->broadphase, opt->cone, opt->disableflags), m, d);
+    const int rc = resolve_cfg(g, group_variant(g, m, d, opt->broadphase, opt->cone, opt->disableflags), m, d);
     if (rc) return rc;
   }
   const size_t smem = (size_t)warps_per_block(4) * d->scratch_floats * sizeof(float);
