@@ -60,7 +60,7 @@ struct MjbData {
   struct GroupCfg {  // launch configuration of one stage-group kernel, resolved on first use
     int ready, wpb, grid, in_smem, scratch_floats;
     size_t smem;
-  } cfg[G_COUNT + COLF_COUNT + 4];  // [G_COUNT + v]: collision variant v > 0; then elliptic make_constraint / solve, wide smooth_velocity / euler
+  } cfg[G_COUNT + COLF_COUNT + 5];  // [G_COUNT + v]: collision variant v > 0; then elliptic make_constraint / solve, wide smooth_velocity / euler
 };
 
 // ---- field-table introspection --------------------------------------------------------------
@@ -332,7 +332,7 @@ static int timed_launch(cudaStream_t stream, F&& launch, int group = -1, bool co
 // the stage-group kernels are instantiated in their own translation units (mjb_g_*.cu), compiled in parallel
 static GroupKernel group_kernel_of(int g, bool in_smem, int variant) {
   switch (g) {
-    case G_POS: return mjb_gk_pos(in_smem);
+    case G_POS: return variant ? mjb_gk_pos_narrow(in_smem) : mjb_gk_pos(in_smem);
     case G_COL: return variant == COLF_COUNT - 1 ? mjb_gk_col_convex(in_smem) : mjb_gk_col(in_smem, variant);
     case G_CON: return mjb_gk_con(in_smem, variant);
     case G_VEL: return variant ? mjb_gk_vel_wide(in_smem) : mjb_gk_vel(in_smem);
@@ -348,6 +348,13 @@ static int group_variant(int g, const MjbModel* m, const MjbData* d, int broadph
     const bool convex = (m->col_feat & COLF_CONVEX) || (m->has_boxbox && !(disableflags & DSBL_NATIVECCD));
     return convex ? COLF_COUNT - 1 : (m->col_feat | (broadphase != 0 ? COLF_SAP : 0));
   }
+  if (g == G_POS) {
+    // smooth_position with four worlds per warp: measured on B200 at 8192 worlds, panda (nv 9) 224 -> 204 us/step, humanoid (nv 27)
+    // 69 -> 80 us for the group, apollo (nv 25) -2 %: only models whose trees fit a quarter warp gain.  MJB_POS_NARROW = 0 / 1 forces it.
+    static const int force = getenv("MJB_POS_NARROW") ? atoi(getenv("MJB_POS_NARROW")) : -1;
+    if (force >= 0) return m->ms.nv > 32 ? 0 : force;
+    return (m->ms.nv <= 16 && d->dsz.nworld >= 42 * d->nsm) ? 1 : 0;
+  }
   if (g == G_VEL || g == G_EUL) {
     // Several worlds per warp (variant 0) save instructions but leave a quarter of the warps to hide the latencies of these stages: it
     // pays once the GPU is full.  Measured on B200 (148 SMs), humanoid: 1024 worlds 240 -> 205 us/step with one warp per world (variant
@@ -361,7 +368,7 @@ static int group_variant(int g, const MjbModel* m, const MjbData* d, int broadph
   return ((g == G_CON || g == G_SOL) && cone == 1) ? 1 : 0;
 }
 static MjbData::GroupCfg& group_cfg(MjbData* d, int g, int variant) {
-  return d->cfg[!variant ? g : g == G_COL ? G_COUNT + variant : G_COUNT + COLF_COUNT + (g == G_CON ? 0 : g == G_SOL ? 1 : g == G_VEL ? 2 : 3)];
+  return d->cfg[!variant ? g : g == G_COL ? G_COUNT + variant : G_COUNT + COLF_COUNT + (g == G_CON ? 0 : g == G_SOL ? 1 : g == G_VEL ? 2 : g == G_EUL ? 3 : 4)];
 }
 // resolves (once) the launch configuration of a group kernel: CTA width, shared memory, resident grid.  Sets function attributes and
 // queries occupancy, so it must not run under stream capture: mjb_prepare() calls it ahead of time.

@@ -7,6 +7,7 @@
 
 typedef void (*GroupKernel)(const KParams);
 GroupKernel mjb_gk_pos(bool in_smem);
+GroupKernel mjb_gk_pos_narrow(bool in_smem);  // four worlds per warp (small models)
 GroupKernel mjb_gk_col(bool in_smem, int variant);  // primitive-only variants: CollisionFeature bits 0..3
 GroupKernel mjb_gk_col_convex(bool in_smem);        // all features (GJK / EPA, meshes)
 GroupKernel mjb_gk_con(bool in_smem, int variant);  // variant 1: elliptic cones

@@ -77,10 +77,10 @@ __host__ __device__ inline int group_scratch_floats(int g, int nv, int nv_pad, i
 #endif
 __host__ __device__ inline bool group_uses_blob(int g) { return g != G_SOL; }
 // lanes per world of a group's kernel (worlds per warp = 32 / lanes)
-// lanes per world of a group kernel; variant 1 of smooth_velocity / euler is the one-warp-per-world build used for models with nv > 32
-// (their dense factorisations want all 32 lanes)
+// lanes per world of a group kernel; variant 1 of smooth_velocity / euler is the one-warp-per-world build (nv > 32, or few worlds),
+// variant 1 of smooth_position the four-worlds-per-warp build (small models)
 __host__ __device__ constexpr int group_lw(int g, int v = 0) {
-  return g == G_POS ? MJB_POS_LW : g == G_VEL ? (v ? 32 : MJB_VEL_LW) : g == G_EUL ? (v ? 32 : MJB_EUL_LW) : 32;
+  return g == G_POS ? (v ? 8 : MJB_POS_LW) : g == G_VEL ? (v ? 32 : MJB_VEL_LW) : g == G_EUL ? (v ? 32 : MJB_EUL_LW) : 32;
 }
 
 // Stages the model blob into shared memory with one TMA bulk copy (cp.async.bulk, completion on
