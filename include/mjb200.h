@@ -99,6 +99,11 @@ long long mjb_rk_static_max_floats(void);
 
 /* smooth.solve_m (reference smooth.py:2848): x = M^-1 y using d.qLD; x, y are (nworld, nv). */
 int mjb_solve_m(const MjbModel* m, MjbData* d, float* x, const float* y, void* cuda_stream);
+/* support.xfrc_accumulate (reference support.py:229): qfrc (nworld, nv) += J^T d.xfrc_applied (needs kinematics + com_pos results). */
+int mjb_xfrc_accumulate(const MjbModel* m, MjbData* d, float* qfrc, void* cuda_stream);
+/* derivative.deriv_smooth_vel (reference derivative.py:321), dense: out (nworld, ld_out, ld_out), ld_out >= nv, receives
+ * qM - dt * qDeriv in its leading nv x nv entries (actuator velocity derivatives and joint damping, as the flags in opt allow). */
+int mjb_deriv_smooth_vel(const MjbModel* m, MjbData* d, const MjbOption* opt, float* out, int ld_out, void* cuda_stream);
 /* support.mul_m (reference support.py:133): res = qM @ vec; (nworld, nv). */
 int mjb_mul_m(const MjbModel* m, MjbData* d, float* res, const float* vec, void* cuda_stream);
 

@@ -141,6 +141,10 @@ def load():
     lib.mjb_solve_m.argtypes = [vp, vp, vp, vp, vp]
     lib.mjb_mul_m.restype = ctypes.c_int
     lib.mjb_mul_m.argtypes = [vp, vp, vp, vp, vp]
+    lib.mjb_xfrc_accumulate.restype = ctypes.c_int
+    lib.mjb_xfrc_accumulate.argtypes = [vp, vp, vp, vp]
+    lib.mjb_deriv_smooth_vel.restype = ctypes.c_int
+    lib.mjb_deriv_smooth_vel.argtypes = [vp, vp, vp, vp, ctypes.c_int, vp]
     lib.mjb_ctrl_noise.restype = ctypes.c_int
     lib.mjb_ctrl_noise.argtypes = [vp, vp, ctypes.POINTER(MjbOption), vp, ctypes.c_int, ctypes.c_float, ctypes.c_float, vp]
     lib.mjb_state_size.restype = ctypes.c_int

@@ -584,6 +584,31 @@ extern "C" int mjb_mul_m(const MjbModel* m, MjbData* d, float* res, const float*
   return timed_launch(stream, [&] { mjb_util_mul_m(K, (n + 255) / 256, stream); });
 }
 
+extern "C" int mjb_xfrc_accumulate(const MjbModel* m, MjbData* d, float* qfrc, void* s) {
+  if (!m || !d || !qfrc) return fail(-1, "null handle");
+  cudaStream_t stream = static_cast<cudaStream_t>(s);
+  KParams K;
+  MjbOption o;
+  memset(&o, 0, sizeof(o));
+  fill_params(K, m, d, &o, 0);
+  K.x = qfrc;
+  const int n = d->dsz.nworld * m->ms.nv;
+  if (n == 0) return 0;
+  return timed_launch(stream, [&] { mjb_util_xfrc_accumulate(K, (n + 255) / 256, stream); });
+}
+
+extern "C" int mjb_deriv_smooth_vel(const MjbModel* m, MjbData* d, const MjbOption* opt, float* out, int ld_out, void* s) {
+  if (!m || !d || !opt || !out) return fail(-1, "null handle");
+  if (ld_out < m->ms.nv) return fail(-2, "deriv_smooth_vel: out must hold nv x nv entries per world");
+  cudaStream_t stream = static_cast<cudaStream_t>(s);
+  KParams K;
+  fill_params(K, m, d, opt, 0);
+  K.x = out;
+  const int n = d->dsz.nworld * m->ms.nv * m->ms.nv;
+  if (n == 0) return 0;
+  return timed_launch(stream, [&] { mjb_util_deriv_smooth_vel(K, (n + 255) / 256, ld_out, stream); });
+}
+
 extern "C" int mjb_ctrl_noise(const MjbModel* m, MjbData* d, const MjbOption* opt, const float* ctrl_center, int step, float ctrlnoisestd,
                               float ctrlnoiserate, void* s) {
   if (!m || !d || !opt) return fail(-1, "null handle");

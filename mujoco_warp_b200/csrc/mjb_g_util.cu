@@ -35,6 +35,54 @@ __global__ void mjb_mul_m_kernel(const __grid_constant__ KParams K) {
   K.x[(size_t)w * nv + i] = s;
 }
 
+// support.xfrc_accumulate (support.py:229 -> apply_ft :175-216): qfrc += J^T xfrc_applied.  Thread = (world, dof); a dof collects the
+// wrenches of the bodies in its body's subtree (the bodies its motion moves), about the subtree's root centre of mass like cdof.
+__global__ void mjb_xfrc_accumulate_kernel(const __grid_constant__ KParams K) {
+  const unsigned char* mb = K.blob;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nv = K.ms.nv;
+  if (t >= K.dsz.nworld * nv) return;
+  const int w = t / nv, i = t - w * nv;
+  const float* xfrc = DW(xfrc_applied);
+  const S6 cd = ld6(DW(cdof) + 6 * i);
+  const int db = MI(dof_bodyid)[i], end = MI(body_subtreeend)[db];
+  float q = 0.f;
+  for (int b = db; b < end; b++) {
+    const S6 ft = ld6(xfrc + 6 * b);
+    const V3 off = ld3(DW(xipos) + 3 * b) - ld3(DW(subtree_com) + 3 * MI(body_rootid)[b]);
+    q += dot(bot(cd), top(ft)) + dot(top(cd), bot(ft)) + dot(cross(top(cd), off), top(ft));
+  }
+  K.x[(size_t)w * nv + i] += q;
+}
+
+// derivative.deriv_smooth_vel dense (derivative.py:321-420): out = qM - dt qDeriv with qDeriv = moment^T diag(d force / d velocity) moment
+// - diag(damping) (actuators unless DisableBit.ACTUATION, damping unless DisableBit.DAMPER).  Thread = (world, i, j); K.n = rows of out.
+__global__ void mjb_deriv_smooth_vel_kernel(const __grid_constant__ KParams K, int ld_out) {
+  const unsigned char* mb = K.blob;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nv = K.ms.nv, np = K.ms.nv_pad;
+  if (t >= K.dsz.nworld * nv * nv) return;
+  const int w = t / (nv * nv), e = t - w * nv * nv, i = e / nv, j = e - i * nv;
+  float q = 0.f;
+  if (K.ms.nu > 0 && !(K.o.disableflags & DSBL_ACTUATION)) {
+    for (int u = 0; u < K.ms.nu; u++) {
+      const float vel = act_vel_deriv(K, mb, w, u);
+      if (vel == 0.f) continue;
+      const int adr = DW(moment_rowadr)[u], nnz = DW(moment_rownnz)[u];
+      float mi = 0.f, mj = 0.f;
+      for (int k = 0; k < nnz; k++) {
+        const int c = DW(moment_colind)[adr + k];
+        const float v = DW(actuator_moment)[adr + k];
+        if (c == i) mi = v;
+        if (c == j) mj = v;
+      }
+      q += mi * mj * vel;
+    }
+  }
+  if (!(K.o.disableflags & DSBL_DAMPER) && i == j) q -= MR(dof_damping)[i];
+  K.x[((size_t)w * ld_out + i) * ld_out + j] = DW(qM)[(size_t)i * np + j] - K.o.timestep * q;
+}
+
 // util_misc.halton (util_misc.py:60-73)
 __device__ __forceinline__ float halton(int index, int base) {
   int n0 = index;
@@ -93,3 +141,6 @@ __global__ void mjb_clear_kernel(int* a, int* b, int* q, int nq) {
   if (q && t < nq) q[t] = 0;
 }
 void mjb_util_clear(int* a, int* b, int* q, int nq, cudaStream_t stream) { mjb_clear_kernel<<<1, 32, 0, stream>>>(a, b, q, nq); }
+
+void mjb_util_xfrc_accumulate(const KParams& K, int grid, cudaStream_t stream) { mjb_xfrc_accumulate_kernel<<<grid, 256, 0, stream>>>(K); }
+void mjb_util_deriv_smooth_vel(const KParams& K, int grid, int ld_out, cudaStream_t stream) { mjb_deriv_smooth_vel_kernel<<<grid, 256, 0, stream>>>(K, ld_out); }

@@ -20,6 +20,8 @@ GroupKernel mjb_gk_eul_wide(bool in_smem);
 cudaError_t mjb_util_solve_m_smem(size_t smem);
 void mjb_util_solve_m(const KParams& K, int grid, int threads, size_t smem, cudaStream_t stream);
 void mjb_util_mul_m(const KParams& K, int grid, cudaStream_t stream);
+void mjb_util_xfrc_accumulate(const KParams& K, int grid, cudaStream_t stream);
+void mjb_util_deriv_smooth_vel(const KParams& K, int grid, int ld_out, cudaStream_t stream);
 void mjb_util_ctrl_noise(const KParams& K, int grid, const float* ctrl_center, int step, float ctrlnoisestd, float ctrlnoiserate, cudaStream_t stream);
 // zeroes *a, *b (either may be null) and q[0..nq) (q may be null): the per-call counters of mjb_run_stages
 void mjb_util_clear(int* a, int* b, int* q, int nq, cudaStream_t stream);

@@ -226,6 +226,26 @@ def mul_m(m, d, res: torch.Tensor, vec: torch.Tensor):
   _lib.check(lib, lib.mjb_mul_m(m._handle, d._handle, ctypes.c_void_p(res.data_ptr()), ctypes.c_void_p(vec.data_ptr()), _lib.stream_ptr()))
 
 
+def xfrc_accumulate(m, d, qfrc: torch.Tensor):
+  """qfrc += J^T d.xfrc_applied (reference support.py:229)."""
+  lib = _lib.load()
+  _ensure_bound(m, d)
+  if tuple(qfrc.shape) != (d.nworld, m.nv) or qfrc.dtype != torch.float32 or not qfrc.is_contiguous() or not qfrc.is_cuda:
+    raise ValueError(f"qfrc must be a contiguous float32 CUDA tensor of shape {(d.nworld, m.nv)}")
+  _lib.check(lib, lib.mjb_xfrc_accumulate(m._handle, d._handle, ctypes.c_void_p(qfrc.data_ptr()), _lib.stream_ptr()))
+
+
+def deriv_smooth_vel(m, d, out: torch.Tensor):
+  """out = qM - dt * qDeriv, the matrix implicitfast factorises (reference derivative.py:321); out: (nworld, n, n) with n >= nv."""
+  lib = _lib.load()
+  _ensure_bound(m, d)
+  if out.dim() != 3 or out.shape[0] != d.nworld or out.shape[1] != out.shape[2] or out.shape[1] < m.nv or out.dtype != torch.float32 \
+      or not out.is_contiguous() or not out.is_cuda:
+    raise ValueError(f"out must be a contiguous float32 CUDA tensor of shape (nworld, n, n) with n >= nv = {m.nv}")
+  opt = _lib.make_option(m)
+  _lib.check(lib, lib.mjb_deriv_smooth_vel(m._handle, d._handle, ctypes.byref(opt), ctypes.c_void_p(out.data_ptr()), int(out.shape[1]), _lib.stream_ptr()))
+
+
 def ctrl_noise(m, d, step_index: int, ctrl_center=None, ctrlnoisestd: float = 0.01, ctrlnoiserate: float = 0.1):
   """Ornstein-Uhlenbeck control noise of the benchmark loop (reference benchmark.py:42)."""
   lib = _lib.load()

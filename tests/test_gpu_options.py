@@ -449,3 +449,66 @@ def test_sub_stage_functions_reproduce_fwd_velocity(humanoid):
   mjw.energy_vel(m, b)
   torch.testing.assert_close(a.energy, b.energy, rtol=1e-6, atol=1e-6)
   assert float(b.energy[:, 1].min()) > 0
+
+
+def test_xfrc_accumulate_matches_the_oracle(humanoid):
+  """support.xfrc_accumulate (support.py:229): J^T xfrc_applied.  The oracle folds it into qfrc_smooth (fwd_acceleration); the applied
+  part is what is left after the other terms are taken out."""
+  from oracle import oracle as O
+
+  rng = np.random.default_rng(5)
+  qpos, qvel, ctrl = H.make_states(humanoid, 6, seed=17)
+  xfrc = rng.uniform(-5, 5, (6, humanoid.nbody, 6))
+  xfrc[:, ::3] = 0.0
+  om, od = H.oracle_data(humanoid, qpos, qvel, ctrl, 24, 64)
+  od.xfrc_applied[:] = xfrc
+  O.run(om, od, "forward", nthread=4)
+  want = np.asarray(od.qfrc_smooth) - (np.asarray(od.qfrc_passive) - np.asarray(od.qfrc_bias) + np.asarray(od.qfrc_actuator) + np.asarray(od.qfrc_applied))
+  m, d = H.device_data(mjw, humanoid, qpos, qvel, ctrl, 24, 64)
+  d.xfrc_applied.copy_(torch.from_numpy(xfrc.astype(np.float32)))
+  mjw.kinematics(m, d)
+  mjw.com_pos(m, d)
+  base = torch.full((6, humanoid.nv), 0.5, device="cuda")
+  qfrc = base.clone()
+  mjw.xfrc_accumulate(m, d, qfrc)
+  torch.cuda.synchronize()
+  assert H.max_err((qfrc - base).cpu().numpy(), want) < 2e-5
+  with pytest.raises(ValueError):
+    mjw.xfrc_accumulate(m, d, torch.zeros((6, humanoid.nv + 1), device="cuda"))
+
+
+def test_deriv_smooth_vel_is_the_velocity_derivative_of_the_smooth_forces():
+  """derivative.deriv_smooth_vel (derivative.py:321): out = qM - dt * d(qfrc_actuator + damping force) / d qvel.  Both forces are
+  affine in qvel, so a central difference of the device's own fwd_velocity / fwd_actuation is exact up to rounding; the flags
+  that drop a term (DisableBit.ACTUATION, DisableBit.DAMPER) are checked the same way."""
+  mjm = mjw.load_mjcf_string(TM.XML["rk4_actuators"])
+  nw = 3
+  rng = np.random.default_rng(2)
+  qpos, qvel, ctrl = H.make_states(mjm, nw, seed=4)
+  for flags in (0, int(DB.ACTUATION), int(DB.DAMPER)):
+    m, d = H.device_data(mjw, mjm, qpos, qvel, ctrl, 16, 32)
+    m.opt.disableflags = flags
+    d.act.copy_(torch.from_numpy(rng.uniform(-0.2, 0.2, (nw, mjm.na)).astype(np.float32)))
+    mjw.forward(m, d)
+    nv, dt = mjm.nv, float(mjm.opt.timestep)
+    out = torch.full((nw, nv + 1, nv + 1), 7.0, device="cuda")
+    mjw.deriv_smooth_vel(m, d, out)
+    qM = d.qM[:, :nv, :nv].double().cpu().numpy()
+    got = out.double().cpu().numpy()
+    assert np.all(got[:, nv, :] == 7.0) and np.all(got[:, :, nv] == 7.0)  # only the leading nv x nv block is written
+
+    def forces(v):
+      d.qvel.copy_(torch.from_numpy(v.astype(np.float32)))
+      mjw.fwd_velocity(m, d)
+      mjw.fwd_actuation(m, d)
+      torch.cuda.synchronize()
+      return (d.qfrc_actuator.double() + d.qfrc_damper.double()).cpu().numpy()
+
+    eps = 0.25
+    deriv = np.zeros((nw, nv, nv))
+    for j in range(nv):
+      dv = np.zeros((nw, nv))
+      dv[:, j] = eps
+      deriv[:, :, j] = (forces(qvel + dv) - forces(qvel - dv)) / (2 * eps)
+    want = qM - dt * deriv
+    assert H.max_err(got[:, :nv, :nv], want) < 2e-4, flags
