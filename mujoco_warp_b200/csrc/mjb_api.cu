@@ -53,6 +53,7 @@ struct MjbData {
   int device;
   int nsm;
   int smem_optin;
+  float* hbuf;        // nv > 32: the solver's per-world Hessians (global memory), allocated at bind
   int* queue;         // G_COUNT dynamic world counters (one per stage group), zeroed at the start of every mjb_run_stages
   float* rk_scratch;  // Runge-Kutta temporaries (reference forward.py:465-475 allocates them per call): cudaMalloc'ed by mjb_prepare / on first use
   size_t rk_floats;
@@ -228,6 +229,7 @@ extern "C" int mjb_data_bind(const MjbModel* m, const int* sizes, int nsizes, in
   d->rk_scratch = nullptr;
   d->rk_floats = 0;
   d->queue = nullptr;
+  d->hbuf = nullptr;
   memset(d->cfg, 0, sizeof(d->cfg));
   cudaError_t e = cudaGetDevice(&d->device);
   if (e != cudaSuccess) {
@@ -244,10 +246,19 @@ extern "C" int mjb_data_bind(const MjbModel* m, const int* sizes, int nsizes, in
       return fail(-10, std::string("cudaMalloc of the world queue: ") + cudaGetErrorString(e));
     }
   }
+  if (m->ms.nv > 32 && d->dsz.nworld > 0) {  // solver Hessians of a large model (mjb_smooth.cuh:solver_scr)
+    e = cudaMalloc(&d->hbuf, (size_t)d->dsz.nworld * m->ms.nv * chol_ld(m->ms.nv_pad) * sizeof(float));
+    if (e != cudaSuccess) {
+      if (d->queue) cudaFree(d->queue);
+      delete d;
+      return fail(-10, std::string("cudaMalloc of the solver Hessians: ") + cudaGetErrorString(e));
+    }
+  }
   *out = d;
   return 0;
 }
 extern "C" void mjb_data_destroy(MjbData* d) {
+  if (d && d->hbuf) cudaFree(d->hbuf);
   if (d && d->rk_scratch) cudaFree(d->rk_scratch);
   if (d && d->queue) cudaFree(d->queue);
   delete d;
@@ -284,6 +295,7 @@ static void fill_params(KParams& K, const MjbModel* m, const MjbData* d, const M
   K.scratch_floats = d->scratch_floats;
   K.stages = stages;
   K.queue = d->queue;
+  K.hbuf = d->hbuf;
 }
 
 int mjb_internal_params(const MjbModel* m, const MjbData* d, KParams* K) {
@@ -383,6 +395,18 @@ static int resolve_cfg(int g, int variant, const MjbModel* m, MjbData* d) {
   {
     const size_t blob = group_uses_blob(g) && m->blob_hot <= 96 * 1024 ? (size_t)m->blob_hot + 16 : 0;
     while (wpb > 1 && (size_t)wpb * wpw * c.scratch_floats * sizeof(float) + blob > (size_t)d->smem_optin) wpb--;
+  }
+  if ((size_t)c.scratch_floats * sizeof(float) > 16 * 1024 && wpb > 1) {
+    // large per-world scratch: the widest CTA that fits may leave half an SM's shared memory unused (4 warps x 34 kB = one CTA per SM,
+    // 3 warps = two): pick the width with the most resident warps
+    const size_t blob = group_uses_blob(g) && m->blob_hot <= 96 * 1024 ? (size_t)m->blob_hot + 16 : 0;
+    int best = wpb, best_warps = 0;
+    for (int cand = wpb; cand >= 1; cand--) {
+      const size_t need = (size_t)cand * wpw * c.scratch_floats * sizeof(float) + blob;
+      const int per_sm = (int)(((size_t)d->smem_optin + 1024) / (need + 1024));  // 1 kB of shared memory is reserved per CTA
+      if (per_sm * cand > best_warps) { best_warps = per_sm * cand; best = cand; }
+    }
+    wpb = best;
   }
   const size_t scr_bytes = (size_t)wpb * wpw * c.scratch_floats * sizeof(float);
   const bool in_smem =

@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(group_threads(G), group_min_ctas(G)) mjb_group
   float* scr = scr_base + (size_t)(warp * WPW + grp) * K.scratch_floats;
   const uint32_t st = K.stages;
 #if MJB_SOL_SYNC && MJB_UNIT_IS(4)
-  if constexpr (G == G_SOL) {
+  if constexpr (G == G_SOL && (V & 1) == 0) {  // the pass-synchronous experiment has a pyramidal build only: elliptic models take the default path
     s_solve_cta(K, lane, warp, wpb, scr);
     return;
   }

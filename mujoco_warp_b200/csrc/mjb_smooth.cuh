@@ -264,13 +264,13 @@ struct SolverScr {
   int ld;
 };
 __host__ __device__ inline int solver_scratch_floats(int nv, int nv_pad, int njmax_pad) {
-  return 2 * nv * chol_ld(nv_pad) + 8 * nv_pad + 5 * njmax_pad;
+  return (nv > 32 ? 1 : 2) * nv * chol_ld(nv_pad) + 8 * nv_pad + 5 * njmax_pad;  // nv > 32: H lives in global memory (KParams.hbuf)
 }
-__device__ __forceinline__ SolverScr solver_scr(float* scr, int nv, int nvp, int njp) {
+__device__ __forceinline__ SolverScr solver_scr(float* scr, int nv, int nvp, int njp, float* hglobal = nullptr) {
   SolverScr s;
   s.ld = chol_ld(nvp);
-  s.H = scr;
-  s.L = s.H + nv * s.ld;
+  s.H = nv > 32 ? hglobal : scr;
+  s.L = nv > 32 ? scr : scr + nv * s.ld;
   float* v = s.L + nv * s.ld;
   s.x = v; s.grad = v + nvp; s.search = v + 2 * nvp; s.mv = v + 3 * nvp; s.qacc = v + 4 * nvp; s.Ma = v + 5 * nvp; s.qfs = v + 6 * nvp; s.rd = v + 7 * nvp;
   float* r = v + 8 * nvp;

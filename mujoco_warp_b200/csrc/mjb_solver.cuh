@@ -803,7 +803,7 @@ __device__ __forceinline__ void solve_finish(const KParams& K, int w, int lane, 
 // one world, start to finish (used when the solver is fused with other stages)
 template <bool ELL>
 __device__ __forceinline__ void s_solve(const KParams& K, const unsigned char* mb, int w, int lane, float* scr) {
-  const SolverScr s = solver_scr(scr, K.ms.nv, K.ms.nv_pad, K.dsz.njmax_pad);
+  const SolverScr s = solver_scr(scr, K.ms.nv, K.ms.nv_pad, K.dsz.njmax_pad, K.hbuf ? K.hbuf + (size_t)w * K.ms.nv * chol_ld(K.ms.nv_pad) : nullptr);
   SolveState st;
   if (!solve_begin(K, w, lane, s, st)) return;
   while (!solve_pass<ELL>(K, w, lane, s, st)) {

@@ -151,6 +151,7 @@ __global__ void __launch_bounds__(256) mjb_reset_world_kernel(const KParams K, c
       DW(nl)[0] = 0;
       DW(nefc)[0] = 0;
       DW(wcon_n)[0] = 0;  // library workspace: the world's contact index list is emptied with its contacts
+      DW(status)[0] = 0;  // the overflow / NaN bits of a world end with its episode (they are sticky otherwise)
       DW(time)[0] = 0.f;
       DW(energy)[0] = 0.f;
       DW(energy)[1] = 0.f;

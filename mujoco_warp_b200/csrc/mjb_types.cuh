@@ -103,6 +103,7 @@ struct KParams {
   int cold_global;            // 1: the cold tables (pair lists, mesh vertices / graphs) stay in global memory behind the staged prefix
   int scratch_floats;         // per-warp shared-memory scratch
   uint32_t stages;
+  float* hbuf;  // nv > 32: the solver's Hessians, nworld x nv x chol_ld floats in global memory (they would halve the warps per SM in shared memory); else null
   int* queue;  // dynamic world queue of this launch (zeroed by the host before the group kernels run), or null: static striding
   // optional extra operands for the small utility kernels
   float* x;
