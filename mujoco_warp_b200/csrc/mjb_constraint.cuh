@@ -1,3 +1,6 @@
+#ifndef MJB_CON_QUAD
+#define MJB_CON_QUAD 1
+#endif
 // mjb_constraint.cuh -- constraint.make_constraint (reference constraint.py:2210), one warp per world.
 //
 // Row classes are emitted in the reference's launch order (equality, friction, limit, contact;
@@ -356,7 +359,156 @@ __device__ __forceinline__ void s_make_constraint(const KParams& K, const unsign
         const int base = nefc + warp_excl_scan(nrow, lane);
         unsigned act = __ballot_sync(FULL, nrow > 0);
         nefc = __shfl_sync(FULL, base + nrow, 31);
-        // phase B, one active contact at a time, lane = dof: Jacobian rows and their velocities
+        // phase B: Jacobian rows and their velocities, FOUR active contacts at a time.  Lane = (contact slot, 128-bit group of dofs):
+        // the 8 lanes of a slot cover 32 dofs per pass, four dofs each, and write the rows with 128-bit stores; the row velocities
+        // J . qvel are summed over the 8 lanes of the slot.  (One contact at a time with lane = dof spent ~650 warp instructions per
+        // contact, most of them per-row address arithmetic, scalar stores and full-warp reductions: MJB_CON_QUAD = 0 keeps that version.)
+#if MJB_CON_QUAD
+        const int slot = lane >> 3, kq = lane & 7, np4 = np >> 2;
+        while (act) {
+          int srcl = -1;
+          {
+            unsigned t = act;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+              const int l = t ? __ffs(t) - 1 : -1;
+              t &= t - 1;  // 0 stays 0
+              if (slot == k) srcl = l;
+            }
+            act = t;
+          }
+          const bool valid = srcl >= 0;
+          const int sl = valid ? srcl : 0;
+          const int ccid = __shfl_sync(FULL, cid, sl), cdim = __shfl_sync(FULL, condim, sl);
+          const int cnrow_any = __shfl_sync(FULL, nrow, sl);
+          const int cnrow = valid ? cnrow_any : 0;
+          const int row0 = __shfl_sync(FULL, base, sl);
+          const float cpos_ = __shfl_sync(FULL, pos, sl), cmargin = __shfl_sync(FULL, includemargin, sl);
+          const float cD = __shfl_sync(FULL, ep.D, sl), cki = __shfl_sync(FULL, ep.ki, sl), cb = __shfl_sync(FULL, ep.b, sl);
+          float S[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // S[a] = sum_dof proj[a] * qvel[dof] (this lane's dofs, then the slot's)
+          int wb1 = 0, wb2 = 0;
+          const float* fri = K.d.contact_friction + 5 * (valid ? ccid : 0);
+          if (valid) {
+            const int b1 = MI(geom_bodyid)[K.d.contact_geom[2 * ccid]], b2 = MI(geom_bodyid)[K.d.contact_geom[2 * ccid + 1]];
+            wb1 = MI(body_weldid)[b1];
+            wb2 = MI(body_weldid)[b2];
+            const V3 cpos = ld3(K.d.contact_pos + 3 * ccid);
+            const M3 frame = ldm3(K.d.contact_frame + 9 * ccid);
+            const V3 off1 = cpos - ld3(scom + 3 * MI(body_rootid)[wb1]), off2 = cpos - ld3(scom + 3 * MI(body_rootid)[wb2]);
+            // rows of this contact: address = -1 if beyond njmax (constraint.py:1749)
+            for (int r = kq; r < cnrow; r += 8) K.d.contact_efc_address[ccid * nmp + r] = (row0 + r < njmax) ? row0 + r : -1;
+            for (int q0 = 0; q0 < np4; q0 += 8) {
+              const int qd = q0 + kq;
+              if (qd >= np4) continue;
+              // per-dof Jacobian differences projected on the frame axes (support.jac_dof, support.py:397)
+              // pr[0] = normal, pr[1..2] = tangents (translation), pr[3..5] = frame rows . rotation; [k] = dof 4 qd + k
+              float pr[6][4];
+#pragma unroll
+              for (int a2 = 0; a2 < 6; a2++)
+#pragma unroll
+                for (int k = 0; k < 4; k++) pr[a2][k] = 0.f;
+#pragma unroll
+              for (int k = 0; k < 4; k++) {
+                const int dof = 4 * qd + k;
+                if (dof < nv) {
+                  const int db = MI(dof_bodyid)[dof];
+                  // dof's body is an ancestor-or-self of body  <=>  db <= body < subtreeend[db]
+                  const int dend = MI(body_subtreeend)[db];
+                  const bool in1 = wb1 != 0 && db <= wb1 && wb1 < dend, in2 = wb2 != 0 && db <= wb2 && wb2 < dend;
+                  if (in1 != in2) {  // common ancestors contribute exactly zero
+                    const S6 cd = ld6(cdof + 6 * dof);
+                    const V3 ang = top(cd), lin = bot(cd);
+                    V3 dp = lin + cross(ang, in2 ? off2 : off1), dr = ang;
+                    if (in1) { dp = V3{0.f, 0.f, 0.f} - dp; dr = V3{0.f, 0.f, 0.f} - dr; }
+                    const float qv = qvel[dof];
+#pragma unroll
+                    for (int a2 = 0; a2 < 3; a2++) {
+                      pr[a2][k] = frame.m[3 * a2] * dp.x + frame.m[3 * a2 + 1] * dp.y + frame.m[3 * a2 + 2] * dp.z;
+                      pr[3 + a2][k] = frame.m[3 * a2] * dr.x + frame.m[3 * a2 + 1] * dr.y + frame.m[3 * a2 + 2] * dr.z;
+                      S[a2] += pr[a2][k] * qv;
+                      S[3 + a2] += pr[3 + a2][k] * qv;
+                    }
+                  }
+                }
+              }
+              float* Jp = DW(efc_J) + (size_t)row0 * np + 4 * qd;
+              const int rleft = njmax - row0;  // rows [0, rleft) of this contact exist
+              if (ELL || cdim == 1) {  // row a2 is the frame axis itself: normal, tangents, then the rotational rows
+#pragma unroll
+                for (int a2 = 0; a2 < 6; a2++)
+                  if (a2 < cnrow && a2 < rleft) *reinterpret_cast<float4*>(Jp + (size_t)a2 * np) = make_float4(pr[a2][0], pr[a2][1], pr[a2][2], pr[a2][3]);
+              } else {  // pyramid edges: rows 2 (a2 - 1), 2 (a2 - 1) + 1 = normal +- friction[a2 - 1] * axis a2
+#pragma unroll
+                for (int a2 = 1; a2 < 6; a2++) {
+                  if (a2 < cdim) {
+                    const float f = fri[a2 - 1];
+                    const int ra = 2 * (a2 - 1);
+                    if (ra < rleft)
+                      *reinterpret_cast<float4*>(Jp + (size_t)ra * np) =
+                          make_float4(pr[0][0] + f * pr[a2][0], pr[0][1] + f * pr[a2][1], pr[0][2] + f * pr[a2][2], pr[0][3] + f * pr[a2][3]);
+                    if (ra + 1 < rleft)
+                      *reinterpret_cast<float4*>(Jp + (size_t)(ra + 1) * np) =
+                          make_float4(pr[0][0] - f * pr[a2][0], pr[0][1] - f * pr[a2][1], pr[0][2] - f * pr[a2][2], pr[0][3] - f * pr[a2][3]);
+                  }
+                }
+              }
+            }
+          }
+          // efc_vel = J . qvel: sums over the 8 lanes of the slot (all lanes take part; idle slots add zeros)
+#pragma unroll
+          for (int a2 = 0; a2 < 6; a2++) {
+            if (a2 < K.ms.nmaxcondim) {  // warp-uniform
+              S[a2] += __shfl_xor_sync(FULL, S[a2], 1);
+              S[a2] += __shfl_xor_sync(FULL, S[a2], 2);
+              S[a2] += __shfl_xor_sync(FULL, S[a2], 4);
+            }
+          }
+          for (int r = kq; r < cnrow; r += 8) {  // the row scalars, one lane per row
+            if (row0 + r >= njmax) continue;
+            if (ELL) {  // constraint.py:2146-2206: per-row impedance parameters
+              float vel = S[0];
+#pragma unroll
+              for (int a2 = 1; a2 < 6; a2++) vel = (r == a2) ? S[a2] : vel;
+              float invweight = MR(body_invweight0)[2 * wb1] + MR(body_invweight0)[2 * wb2];  // after the weld mapping (:2049)
+              const float* ref = K.d.contact_solref + 2 * ccid;
+              if (r > 0) {
+                const float* srf = K.d.contact_solreffriction + 2 * ccid;
+                if (srf[0] != 0.f || srf[1] != 0.f) ref = srf;
+                invweight *= imp2;
+                if (r > 1) invweight *= fri[0] * fri[0] / (fri[r - 1] * fri[r - 1]);
+              }
+              const EfcParams p = efc_params(K, cpos_, invweight, ref, K.d.contact_solimp + 5 * ccid);
+              const float pos_aref = r == 0 ? cpos_ : 0.f;
+              EfcRow e;
+              e.D = p.D;
+              e.vel = vel;
+              e.aref = -p.ki * pos_aref - p.b * vel;
+              e.pos = pos_aref + cmargin;
+              e.margin = cmargin;
+              e.frictionloss = 0.f;
+              store_row(K, w, row0 + r, e, cdim == 1 ? CT_CONTACT_FRICTIONLESS : CT_CONTACT_ELLIPTIC, ccid);
+            } else {
+              float vel = S[0];
+              if (cdim > 1) {
+                const int dimid2 = r / 2 + 1;
+                float Si = S[1];
+#pragma unroll
+                for (int a2 = 2; a2 < 6; a2++) Si = (dimid2 == a2) ? S[a2] : Si;
+                const float frii = fri[dimid2 - 1];
+                vel += (r & 1) ? -Si * frii : Si * frii;
+              }
+              EfcRow e;
+              e.D = cD;
+              e.vel = vel;
+              e.aref = -cki * cpos_ - cb * vel;
+              e.pos = cpos_ + cmargin;
+              e.margin = cmargin;
+              e.frictionloss = 0.f;
+              store_row(K, w, row0 + r, e, cdim == 1 ? CT_CONTACT_FRICTIONLESS : CT_CONTACT_PYRAMIDAL, ccid);
+            }
+          }
+        }
+#else
         while (act) {
           const int src = __ffs(act) - 1;
           act &= act - 1;
@@ -464,6 +616,7 @@ __device__ __forceinline__ void s_make_constraint(const KParams& K, const unsign
             store_row(K, w, row0 + lane, e, cdim == 1 ? CT_CONTACT_FRICTIONLESS : CT_CONTACT_PYRAMIDAL, ccid);
           }
         }
+#endif  // MJB_CON_QUAD
       }
     }
   }

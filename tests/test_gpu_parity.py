@@ -172,8 +172,10 @@ def test_step1_step2_equals_step(humanoid):
   mjw.step(m, a)
   mjw.step1(m, b)
   mjw.step2(m, b)
+  # not bit-identical: step factorises qM inside the smooth_velocity launch (reciprocal pivots from rsqrt), step1 + step2 go through
+  # the stored qLD (reciprocals recomputed as 1 / L_ii); the solver amplifies that last-bit difference of qacc_smooth to ~1e-6
   for f in ["qpos", "qvel", "qacc", "time"]:
-    assert H.max_err(H.dev_np(a, f), H.dev_np(b, f)) < 1e-6, f
+    assert H.max_err(H.dev_np(a, f), H.dev_np(b, f)) < 5e-6, f
 
 
 def test_cuda_graph_replay_equals_eager(humanoid):
