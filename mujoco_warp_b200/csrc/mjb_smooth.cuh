@@ -629,7 +629,7 @@ void load_rows(float* A, int ld, const float* src, int ld_src, int n, int lane, 
     float4* a4 = reinterpret_cast<float4*>(A);
     if (c4 <= 8) {  // rows of <= 32 floats: 4 rows per pass, lane = (row % 4, float4 column)
       const int q = lane & 7;
-#pragma unroll 2
+#pragma unroll 4
       for (int i = lane >> 3; i < n; i += MJB_LW / 8)
         if (q < c4) a4[i * ld4 + q] = s4[i * c4 + q];
     } else {
@@ -649,17 +649,18 @@ void load_rows(float* A, int ld, const float* src, int ld_src, int n, int lane, 
   }
 }
 
-// writes the lower-triangular factor held in shared memory to d.qLD (nv x nv, zero upper part)
+// writes the lower-triangular factor held in shared memory to d.qLD (nv x nv).  Only the lower triangle is written: the strictly
+// upper part of d.qLD is zero from its allocation (make_data / put_data) and nothing ever writes there.
 __device__ __forceinline__ void store_qLD(const KParams& K, int w, int lane, const float* L, int ld) {
   const int nv = K.ms.nv;
   float* qLD = DW(qLD);
   if (MJB_LW == 32 && nv <= 32) {
 #pragma unroll 4
     for (int i = 0; i < nv; i++)
-      if (lane < nv) qLD[i * nv + lane] = (lane <= i) ? L[i * ld + lane] : 0.f;
+      if (lane <= i) qLD[i * nv + lane] = L[i * ld + lane];
   } else {
     for (int i = 0; i < nv; i++)
-      for (int j = lane; j < nv; j += MJB_LW) qLD[i * nv + j] = (j <= i) ? L[i * ld + j] : 0.f;
+      for (int j = lane; j <= i; j += MJB_LW) qLD[i * nv + j] = L[i * ld + j];
   }
 }
 
@@ -962,10 +963,18 @@ __device__ __forceinline__ void s_fwd_acceleration(const KParams& K, const unsig
   const CholScr s = chol_scr(scr, nv, K.ms.nv_pad);
   float* x = s.x;
   const float* xfrc = DW(xfrc_applied);
+  // any applied wrench in this world?  (usually none: one coalesced pass instead of a subtree scan per dof)
+  bool anyx = false;
+  for (int k = lane; k < 6 * K.ms.nbody; k += MJB_LW) anyx |= xfrc[k] != 0.f;
+  {
+    const unsigned bal = __ballot_sync(FULL, anyx);
+    const int g0 = (threadIdx.x & 31) & ~(MJB_LW - 1);
+    anyx = ((bal >> g0) & (MJB_LW == 32 ? 0xffffffffu : ((1u << (MJB_LW & 31)) - 1u))) != 0u;
+  }
   for (int i = lane; i < nv; i += MJB_LW) {
     float q = DW(qfrc_passive)[i] - DW(qfrc_bias)[i] + DW(qfrc_actuator)[i] + DW(qfrc_applied)[i];
     const S6 cd = ld6(DW(cdof) + 6 * i);
-    const int db = MI(dof_bodyid)[i], end = MI(body_subtreeend)[db];
+    const int db = MI(dof_bodyid)[i], end = anyx ? MI(body_subtreeend)[db] : db;
     for (int b = db; b < end; b++) {  // bodies in the subtree of the dof's body
       const S6 ft = ld6(xfrc + 6 * b);
       if (ft.v[0] == 0.f && ft.v[1] == 0.f && ft.v[2] == 0.f && ft.v[3] == 0.f && ft.v[4] == 0.f && ft.v[5] == 0.f) continue;
