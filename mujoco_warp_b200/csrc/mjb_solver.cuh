@@ -204,6 +204,9 @@ __device__ __forceinline__ void cone_hessian(const KParams& K, int w, int lane, 
 #ifndef MJB_SOL_HTRI
 #define MJB_SOL_HTRI 1
 #endif
+#ifndef MJB_SOL_HROWS
+#define MJB_SOL_HROWS 2  // measured on B200 (humanoid): 2 rows 196 us, 4 rows 199 us, 8 rows 218 us (registers)
+#endif
 #if MJB_SOL_HTRI
 // Lower triangle only, in 4 x 4 tiles: tile t = bi (bi + 1) / 2 + bj (bj <= bi) belongs to lane t % 32, so a 27-dof model keeps 28
 // lanes busy with 16 useful FMAs per constraint row each (the 32 x 32-block mapping below spends 32 FMAs per lane on 20 lanes, half
@@ -212,7 +215,6 @@ __device__ __forceinline__ void h_accumulate(const KParams& K, int w, int lane, 
   const int nv = K.ms.nv, np = K.ms.nv_pad, ld = s.ld;
   const float* J = DW(efc_J);
   const int nb = (nv + 3) >> 2, ntile = (nb * (nb + 1)) >> 1;
-  const int nefc2 = (nefc + 1) & ~1;
   MJB_ROLL
   for (int t0 = 0; t0 < ntile; t0 += 32) {
     const int t = t0 + lane;
@@ -226,31 +228,31 @@ __device__ __forceinline__ void h_accumulate(const KParams& K, int w, int lane, 
     for (int i = 0; i < 4; i++)
 #pragma unroll
       for (int j = 0; j < 4; j++) acc[i][j] = 0.f;
-    // two rows per iteration: the four 128-bit loads are issued before the 32 FMAs
+    // MJB_SOL_HROWS rows per iteration: their 128-bit loads are issued before the FMAs (rows in order: the sums keep their order)
     MJB_ROLL
-    for (int r = 0; r < nefc2; r += 2) {
-      const float cf0 = s.coef[r], cf1 = (r + 1 < nefc) ? s.coef[r + 1] : 0.f;
-      if (cf0 == 0.f && cf1 == 0.f) continue;  // warp-uniform
+    for (int r = 0; r < nefc; r += MJB_SOL_HROWS) {
+      float cf[MJB_SOL_HROWS];
+      bool any = false;
+#pragma unroll
+      for (int k = 0; k < MJB_SOL_HROWS; k++) {
+        cf[k] = (r + k < nefc) ? s.coef[r + k] : 0.f;
+        any = any || cf[k] != 0.f;
+      }
+      if (!any) continue;  // warp-uniform
       if (need) {
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        const float* Jr0 = J + (size_t)r * np;
-        const float* Jr1 = J + (size_t)min(r + 1, nefc - 1) * np;
-        const bool u0 = cf0 != 0.f, u1 = cf1 != 0.f;
-        const float4 ji0 = u0 ? *reinterpret_cast<const float4*>(Jr0 + r0) : z4;
-        const float4 jj0 = u0 ? *reinterpret_cast<const float4*>(Jr0 + c0) : z4;
-        const float4 ji1 = u1 ? *reinterpret_cast<const float4*>(Jr1 + r0) : z4;
-        const float4 jj1 = u1 ? *reinterpret_cast<const float4*>(Jr1 + c0) : z4;
-        {
-          const float vi[4] = {ji0.x * cf0, ji0.y * cf0, ji0.z * cf0, ji0.w * cf0};
-          const float vj[4] = {jj0.x, jj0.y, jj0.z, jj0.w};
+        float4 ji[MJB_SOL_HROWS], jj[MJB_SOL_HROWS];
 #pragma unroll
-          for (int i = 0; i < 4; i++)
-#pragma unroll
-            for (int j = 0; j < 4; j++) acc[i][j] += vi[i] * vj[j];
+        for (int k = 0; k < MJB_SOL_HROWS; k++) {
+          const float* Jr = J + (size_t)min(r + k, nefc - 1) * np;
+          const bool u = cf[k] != 0.f;
+          ji[k] = u ? *reinterpret_cast<const float4*>(Jr + r0) : z4;
+          jj[k] = u ? *reinterpret_cast<const float4*>(Jr + c0) : z4;
         }
-        {
-          const float vi[4] = {ji1.x * cf1, ji1.y * cf1, ji1.z * cf1, ji1.w * cf1};
-          const float vj[4] = {jj1.x, jj1.y, jj1.z, jj1.w};
+#pragma unroll
+        for (int k = 0; k < MJB_SOL_HROWS; k++) {
+          const float vi[4] = {ji[k].x * cf[k], ji[k].y * cf[k], ji[k].z * cf[k], ji[k].w * cf[k]};
+          const float vj[4] = {jj[k].x, jj[k].y, jj[k].z, jj[k].w};
 #pragma unroll
           for (int i = 0; i < 4; i++)
 #pragma unroll
