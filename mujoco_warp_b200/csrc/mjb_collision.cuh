@@ -201,8 +201,17 @@ static __device__ __noinline__ void c_hfield_pair(const KParams& K, const unsign
         int face_idx;
         const int nc = ccd_run(K.o.ccd_tolerance, 0.f, iterations, iterations, ga, gb, &pt, &res, &d, w1, w2, &face_idx);
         if (nc == 0) continue;
-        cdist[count] = d;
         const V3 pl{0.5f * (w1[0] + w2[0]), 0.5f * (w1[1] + w2[1]), 0.5f * (w1[2] + w2[2])};
+        {
+          // Float32 safeguard (not in the reference): the contact point lies between a point of the geom and a point at distance |d|
+          // from it, i.e. within rbound + |d| of the geom's centre.  A degenerate prism can make the float32 EPA return a witness
+          // hundreds of metres away (seen once in 4096 x 370 steps of the apollo height-field scene); such a contact row has a
+          // Jacobian norm ~500 and turns the world's solve into NaN.  Dropped instead.
+          const float ex = pl.x - pos[0], ey = pl.y - pos[1], ez = pl.z - pos[2];
+          const float lim = r2 + fabsf(d) + fm + 1e-3f * (1.0f + r2);
+          if (!(ex * ex + ey * ey + ez * ez <= lim * lim)) continue;
+        }
+        cdist[count] = d;
         const M3 fr = make_frame(V3{w1[0] - w2[0], w1[1] - w2[1], w1[2] - w2[2]});
         const M3 m1 = ldm3(mat1);
         const V3 pg = mat_vec(m1, pl) + ld3(pos1), ng = mat_vec(m1, V3{fr.m[0], fr.m[1], fr.m[2]});
