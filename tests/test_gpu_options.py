@@ -512,3 +512,34 @@ def test_deriv_smooth_vel_is_the_velocity_derivative_of_the_smooth_forces():
       deriv[:, :, j] = (forces(qvel + dv) - forces(qvel - dv)) / (2 * eps)
     want = qM - dt * deriv
     assert H.max_err(got[:, :nv, :nv], want) < 2e-4, flags
+
+
+@pytest.mark.parametrize("cone", [C.ConeType.PYRAMIDAL, C.ConeType.ELLIPTIC])
+def test_contact_rows_for_every_condim(cone):
+  """condim 1, 3, 4 and 6 contacts side by side (1, 4, 6, 10 pyramid rows / 1, 3, 4, 6 elliptic rows; constraint.py:1669, :1940), nine
+  active contacts per world so that make_constraint's four-contacts-per-pass loop runs full, partial and repeated passes."""
+  geoms = []
+  for i, cd in enumerate((1, 3, 4, 6, 3, 6, 1, 4, 3)):
+    shape = 'type="sphere" size=".1"' if i % 2 == 0 else 'type="box" size=".1 .08 .06"'
+    geoms.append(f'<body pos="{0.4 * i} 0 0.09"><freejoint/><geom {shape} condim="{cd}" friction="0.8 0.02 0.003"/></body>')
+  xml = f'<mujoco><option timestep="0.002"/><worldbody><geom type="plane" size="5 5 .1" condim="1"/>{"".join(geoms)}</worldbody></mujoco>'
+  mjm = mjw.load_mjcf_string(xml)
+  nw = 6
+  rng = np.random.default_rng(8)
+  qpos = np.repeat(np.asarray(mjm.qpos0)[None], nw, axis=0)
+  for j in range(mjm.njnt):
+    qa = int(mjm.jnt_qposadr[j])
+    qpos[:, qa + 2] -= rng.uniform(0.0, 0.03, nw)
+    q = qpos[:, qa + 3 : qa + 7] + rng.normal(0, 0.1, (nw, 4))
+    qpos[:, qa + 3 : qa + 7] = q / np.linalg.norm(q, axis=1, keepdims=True)
+  qvel = rng.uniform(-0.5, 0.5, (nw, mjm.nv))
+  ctrl = np.zeros((nw, mjm.nu))
+  opt = {"cone": int(cone)}
+  _, od, m, d = run_both(mjm, qpos, qvel, ctrl, 48, 160, opt=opt)
+  assert int(d.status.max()) == 0
+  assert int(od.nacon[0]) >= 9 * nw
+  for f in ["ne", "nf", "nl", "nefc", "wcon_n", "nacon"]:
+    np.testing.assert_array_equal(H.dev_np(d, f), getattr(od, f), err_msg=f)
+  np.testing.assert_array_equal(H.dev_np(d, "efc_type"), od.efc_type)
+  for f in H.EFC_FIELDS:
+    assert H.max_err(H.dev_np(d, f), getattr(od, f)) < 2e-3, f
