@@ -246,7 +246,7 @@ extern "C" int mjb_data_bind(const MjbModel* m, const int* sizes, int nsizes, in
       return fail(-10, std::string("cudaMalloc of the world queue: ") + cudaGetErrorString(e));
     }
   }
-  if (m->ms.nv > 32 && d->dsz.nworld > 0) {  // solver Hessians of a large model (mjb_smooth.cuh:solver_scr)
+  if ((m->ms.nv > 32 || MJB_SOL_JSMEM) && d->dsz.nworld > 0 && m->ms.nv > 0) {  // the solver's Hessians (mjb_smooth.cuh:solver_scr)
     e = cudaMalloc(&d->hbuf, (size_t)d->dsz.nworld * m->ms.nv * chol_ld(m->ms.nv_pad) * sizeof(float));
     if (e != cudaSuccess) {
       if (d->queue) cudaFree(d->queue);

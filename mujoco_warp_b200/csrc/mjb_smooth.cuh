@@ -259,22 +259,48 @@ __device__ __forceinline__ CholScr chol_scr(float* scr, int nv, int nvp) {
   c.rd = c.x + nvp;
   return c;
 }
+// MJB_SOL_JSMEM = 1 (nv <= 32): the world's constraint Jacobian rows are staged in shared memory for the whole solve and the Hessian
+// moves to a per-world global buffer (KParams.hbuf) to make room -- H is touched once per Hessian update and once per factorisation,
+// J four times per iteration; rows that do not fit (solver_jcap) leave the world on the global-memory path, and the 5 CTAs x 4 warps
+// per SM are kept.  Measured on B200 (humanoid, 8192 worlds, parity-green): solve 200.3 us against 194.6 us with J read through
+// L1 / L2 and H in shared memory -- the staging copy and the global-memory Hessian cost more than the shared-memory rows save.  Off.
+#ifndef MJB_SOL_JSMEM
+#define MJB_SOL_JSMEM 0
+#endif
 struct SolverScr {
   float *H, *L, *x, *grad, *search, *mv, *qacc, *Ma, *qfs, *rd, *Jaref, *jv, *D, *coef, *force;
-  int ld;
+  float* Jst;       // staging area for the rows of efc_J (jcap rows of nv_pad floats), or null
+  const float* Jw;  // where this world's rows are read from: Jst or the global array (set by solve_begin's caller)
+  int ld, jcap;
 };
+// shared-memory floats of one world without the staged rows
+__host__ __device__ inline int solver_base_floats(int nv, int nv_pad, int njmax_pad) {
+  return ((nv > 32 || MJB_SOL_JSMEM) ? 1 : 2) * nv * chol_ld(nv_pad) + 8 * nv_pad + 5 * njmax_pad;
+}
+// rows of J staged per world: what is left of the shared memory that lets 5 CTAs of 4 warps share an SM (227 kB - 1 kB per CTA)
+__host__ __device__ inline int solver_jcap(int nv, int nv_pad, int njmax_pad) {
+  if (!MJB_SOL_JSMEM || nv > 32) return 0;
+  const int budget = (227 * 1024 - 5 * 1024) / (5 * 4 * 4);  // floats per world
+  int cap = (budget - solver_base_floats(nv, nv_pad, njmax_pad)) / nv_pad;
+  cap = cap < 0 ? 0 : cap & ~3;
+  return cap < njmax_pad ? cap : njmax_pad;
+}
 __host__ __device__ inline int solver_scratch_floats(int nv, int nv_pad, int njmax_pad) {
-  return (nv > 32 ? 1 : 2) * nv * chol_ld(nv_pad) + 8 * nv_pad + 5 * njmax_pad;  // nv > 32: H lives in global memory (KParams.hbuf)
+  return solver_base_floats(nv, nv_pad, njmax_pad) + solver_jcap(nv, nv_pad, njmax_pad) * nv_pad;
 }
 __device__ __forceinline__ SolverScr solver_scr(float* scr, int nv, int nvp, int njp, float* hglobal = nullptr) {
   SolverScr s;
   s.ld = chol_ld(nvp);
-  s.H = nv > 32 ? hglobal : scr;
-  s.L = nv > 32 ? scr : scr + nv * s.ld;
+  const bool hg = nv > 32 || MJB_SOL_JSMEM;  // H in global memory
+  s.H = hg ? hglobal : scr;
+  s.L = hg ? scr : scr + nv * s.ld;
   float* v = s.L + nv * s.ld;
   s.x = v; s.grad = v + nvp; s.search = v + 2 * nvp; s.mv = v + 3 * nvp; s.qacc = v + 4 * nvp; s.Ma = v + 5 * nvp; s.qfs = v + 6 * nvp; s.rd = v + 7 * nvp;
   float* r = v + 8 * nvp;
   s.Jaref = r; s.jv = r + njp; s.D = r + 2 * njp; s.coef = r + 3 * njp; s.force = r + 4 * njp;
+  s.jcap = solver_jcap(nv, nvp, njp);
+  s.Jst = s.jcap > 0 ? r + 5 * njp : nullptr;
+  s.Jw = nullptr;
   return s;
 }
 

@@ -164,7 +164,7 @@ __device__ __forceinline__ Pt3 row_eval(const KParams& K, int w, const SolverScr
 // i.e. rank-one terms; p and q are staged in s.mv / s.x (both free between the constraint update and the solve).
 __device__ __forceinline__ void cone_hessian(const KParams& K, int w, int lane, const SolverScr& s, int nefc) {
   const int nv = K.ms.nv, np = K.ms.nv_pad, ld = s.ld, ncon = DW(wcon_n)[0];
-  const float* J = DW(efc_J);
+  const float* J = s.Jw;
   for (int k = 0; k < ncon; k++) {
     const int conid = DW(wcon)[k];
     const int dim = K.d.contact_dim[conid], r0 = K.d.contact_efc_address[conid * K.ms.nmaxpyramid];
@@ -213,7 +213,7 @@ __device__ __forceinline__ void cone_hessian(const KParams& K, int w, int lane, 
 // of them above the diagonal).  Per element the rows are added in the same order as before: results are bit-identical.
 __device__ __forceinline__ void h_accumulate(const KParams& K, int w, int lane, const SolverScr& s, int nefc) {
   const int nv = K.ms.nv, np = K.ms.nv_pad, ld = s.ld;
-  const float* J = DW(efc_J);
+  const float* J = s.Jw;
   const int nb = (nv + 3) >> 2, ntile = (nb * (nb + 1)) >> 1;
   MJB_ROLL
   for (int t0 = 0; t0 < ntile; t0 += 32) {
@@ -277,7 +277,7 @@ __device__ __forceinline__ void h_accumulate(const KParams& K, int w, int lane, 
 #else
 __device__ __forceinline__ void h_accumulate(const KParams& K, int w, int lane, const SolverScr& s, int nefc) {
   const int nv = K.ms.nv, np = K.ms.nv_pad, ld = s.ld;
-  const float* J = DW(efc_J);
+  const float* J = s.Jw;
   const int a = lane >> 2, b = lane & 3;
   const int nblk = (nv + 31) >> 5;
   MJB_ROLL
@@ -385,7 +385,7 @@ __device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], 
 }
 __device__ __forceinline__ void h_accumulate_mma(const KParams& K, int w, int lane, const SolverScr& s, int nefc) {
   const int nv = K.ms.nv, np = K.ms.nv_pad, ld = s.ld;
-  const float* J = DW(efc_J);
+  const float* J = s.Jw;
   const int g = lane >> 2, t = lane & 3;
   const int nmt = (nv + 15) >> 4, ntile = (nv + 7) >> 3;
   MJB_ROLL
@@ -501,7 +501,7 @@ __device__ __forceinline__ void update_constraint(const KParams& K, int w, int l
   // qfrc_constraint = J^T force (solver.py:1988).  Lane = (128-bit column group c, row group gi): the G = 4 / 2 / 1 lanes of a
   // column group sit next to each other and take every G-th row, four rows per trip with their 128-bit loads issued together; rows
   // without force multiply by zero instead of branching.  A 27-dof model: 7 column groups x 4 row groups = 28 lanes.
-  const float* J = DW(efc_J);
+  const float* J = s.Jw;
   const int n4 = np >> 2;
   const int sh = n4 <= 8 ? 2 : n4 <= 16 ? 1 : 0, G = 1 << sh;
   const int rlast = nefc - 1;  // rows past nefc may hold anything: never loaded, their force is zero
@@ -566,12 +566,12 @@ __device__ __forceinline__ void linesearch(const KParams& K, int w, int lane, co
   // mv = M search, jv = J search
 #if MJB_SOL_COMPACT
   mat_vec(DW(qM), n4, nv, s.search, s.mv, nullptr, lane);
-  mat_vec(DW(efc_J), n4, nefc, s.search, s.jv, nullptr, lane);
+  mat_vec(s.Jw, n4, nefc, s.search, s.jv, nullptr, lane);
 #else
   MJB_ROLL
   for (int i = lane; i < nv; i += 32) s.mv[i] = row_dot(DW(qM) + (size_t)i * np, s.search, n4);
   MJB_ROLL
-  for (int r = lane; r < nefc; r += 32) s.jv[r] = row_dot(DW(efc_J) + (size_t)r * np, s.search, n4);
+  for (int r = lane; r < nefc; r += 32) s.jv[r] = row_dot(s.Jw + (size_t)r * np, s.search, n4);
 #endif
   __syncwarp();
   const float scale = K.o.meaninertia * (float)nv;
@@ -657,7 +657,7 @@ __device__ __forceinline__ void solve_direction(const KParams& K, int w, int lan
   if (refactor) {
     const float4* h4 = reinterpret_cast<const float4*>(s.H);
     float4* l4 = reinterpret_cast<float4*>(s.L);
-    MJB_ROLL
+#pragma unroll 4
     for (int i = lane; i < (nv * ld) >> 2; i += 32) l4[i] = h4[i];
     __syncwarp();
     if (ELL && cones) cone_hessian(K, w, lane, s, nefc);
@@ -678,7 +678,7 @@ struct SolveState {
 
 // init_context part 1 (solver.py:3257): loads the world into shared memory.  Returns false when there is
 // nothing to solve (solver.py:3298).
-__device__ __forceinline__ bool solve_begin(const KParams& K, int w, int lane, const SolverScr& s, SolveState& st) {
+__device__ __forceinline__ bool solve_begin(const KParams& K, int w, int lane, SolverScr& s, SolveState& st) {
   const int nv = K.ms.nv, np = K.ms.nv_pad, njmax = K.dsz.njmax;
   if (njmax == 0 || nv == 0) {
     MJB_ROLL
@@ -690,6 +690,15 @@ __device__ __forceinline__ bool solve_begin(const KParams& K, int w, int lane, c
   st.nefc = uniform_i(min(DW(nefc)[0], njmax));
   st.ne = uniform_i(DW(ne)[0]);
   st.nf = uniform_i(DW(nf)[0]);
+  s.Jw = DW(efc_J);
+  if (s.Jst != nullptr && st.nefc <= s.jcap) {  // stage the world's rows: coalesced 128-bit copies, all in flight
+    const float4* g4 = reinterpret_cast<const float4*>(DW(efc_J));
+    float4* s4 = reinterpret_cast<float4*>(s.Jst);
+    const int n4tot = (st.nefc * np) >> 2;
+#pragma unroll 4
+    for (int i = lane; i < n4tot; i += 32) s4[i] = g4[i];
+    s.Jw = s.Jst;
+  }
   st.it = 0;
   st.niter = 0;
   st.had_cone = false;
@@ -708,11 +717,11 @@ __device__ __forceinline__ bool solve_begin(const KParams& K, int w, int lane, c
   // Jaref = J qacc - aref, Ma = M qacc
   const int n4 = np >> 2;
 #if MJB_SOL_COMPACT
-  mat_vec(DW(efc_J), n4, st.nefc, s.qacc, s.Jaref, DW(efc_aref), lane);
+  mat_vec(s.Jw, n4, st.nefc, s.qacc, s.Jaref, DW(efc_aref), lane);
   mat_vec(DW(qM), n4, nv, s.qacc, s.Ma, nullptr, lane);
 #else
   MJB_ROLL
-  for (int r = lane; r < st.nefc; r += 32) s.Jaref[r] = row_dot(DW(efc_J) + (size_t)r * np, s.qacc, n4) - DW(efc_aref)[r];
+  for (int r = lane; r < st.nefc; r += 32) s.Jaref[r] = row_dot(s.Jw + (size_t)r * np, s.qacc, n4) - DW(efc_aref)[r];
   MJB_ROLL
   for (int i = lane; i < nv; i += 32) s.Ma[i] = row_dot(DW(qM) + (size_t)i * np, s.qacc, n4);
 #endif
@@ -805,7 +814,7 @@ __device__ __forceinline__ void solve_finish(const KParams& K, int w, int lane, 
 // one world, start to finish (used when the solver is fused with other stages)
 template <bool ELL>
 __device__ __forceinline__ void s_solve(const KParams& K, const unsigned char* mb, int w, int lane, float* scr) {
-  const SolverScr s = solver_scr(scr, K.ms.nv, K.ms.nv_pad, K.dsz.njmax_pad, K.hbuf ? K.hbuf + (size_t)w * K.ms.nv * chol_ld(K.ms.nv_pad) : nullptr);
+  SolverScr s = solver_scr(scr, K.ms.nv, K.ms.nv_pad, K.dsz.njmax_pad, K.hbuf ? K.hbuf + (size_t)w * K.ms.nv * chol_ld(K.ms.nv_pad) : nullptr);
   SolveState st;
   if (!solve_begin(K, w, lane, s, st)) return;
   while (!solve_pass<ELL>(K, w, lane, s, st)) {
@@ -819,7 +828,7 @@ __device__ __forceinline__ void s_solve(const KParams& K, const unsigned char* m
 // an SM in the same phase of the (large) solver code, so they share instruction-cache lines instead of
 // evicting each other's.
 __device__ __forceinline__ void s_solve_cta(const KParams& K, int lane, int warp, int wpb, float* scr) {
-  const SolverScr s = solver_scr(scr, K.ms.nv, K.ms.nv_pad, K.dsz.njmax_pad);
+  SolverScr s = solver_scr(scr, K.ms.nv, K.ms.nv_pad, K.dsz.njmax_pad, K.hbuf);  // experiment: see the note at MJB_SOL_SYNC
   const int stride = gridDim.x * wpb;
   int w = blockIdx.x * wpb + warp;
   SolveState st;
